@@ -1,0 +1,226 @@
+"""Synthetic nodes, topologies and request streams.
+
+Pure numpy; no GPU, no oracle.  Shared by tests/ and bench.py so that the CUDA path, the
+oracle and the reference arm all consume byte-identical seeded inputs.
+
+Link types follow the enum of the reference's NVML binding
+(vendor/github.com/NVIDIA/gpu-monitoring-tools/bindings/go/nvml/nvml.go:132-154):
+0 Unknown/absent, 1 CrossCPU, 2 SameCPU, 3 HostBridge, 4 MultiSwitch, 5 SingleSwitch,
+6 SameBoard, 7..18 = 1..12 NVLinks.  A topology is an int32 array links2[n, n, 2] holding,
+per ordered pair, {PCIe-ancestry link, NVLink-count link} as gpuallocator.NewDevices
+records them (vendor/github.com/NVIDIA/go-gpuallocator/gpuallocator/device.go:49-69).
+"""
+import itertools
+import uuid as _uuid
+
+import numpy as np
+
+PCIE_SCORE = {1: 10, 2: 20, 3: 30, 4: 40, 5: 50, 6: 60}
+SCORE_TO_PCIE = {v: k for k, v in PCIE_SCORE.items()}
+
+
+def nvlink_type(nlinks):
+    """number of NVLinks (1..12) -> link-type enum value; 0 -> absent"""
+    return 0 if nlinks == 0 else 6 + int(nlinks)
+
+
+def _sym(n):
+    return np.zeros((n, n, 2), dtype=np.int32)
+
+
+def _set(links2, i, j, pcie, nvl=0):
+    links2[i, j, 0] = links2[j, i, 0] = pcie
+    links2[i, j, 1] = links2[j, i, 1] = nvl
+
+
+def topo_zero(n=8):
+    """T0: no links at all (every pair scores 0)."""
+    return _sym(n)
+
+
+def topo_uniform(n=8, pcie=1):
+    """T1: every pair CrossCPU (score 10, one link)."""
+    t = _sym(n)
+    for i, j in itertools.combinations(range(n), 2):
+        _set(t, i, j, pcie)
+    return t
+
+
+def topo_two_sockets(n=8):
+    """T2: an HGX B200 as the reference sees it — NVSwitch links are invisible to
+    nvml.GetNVLink (nvml.go:617-658, TODO at :655), so only PCIe ancestry is left:
+    SameCPU (20) inside each half, CrossCPU (10) across."""
+    t = _sym(n)
+    h = n // 2
+    for i, j in itertools.combinations(range(n), 2):
+        _set(t, i, j, 2 if (i < h) == (j < h) else 1)
+    return t
+
+
+def topo_dgx1v_like():
+    """T3: synthetic hybrid cube mesh in the style of a DGX-1V (not a claim about real
+    hardware).  PCIe: SingleSwitch for (0,1),(2,3),(4,5),(6,7); SameCPU inside each
+    quad; CrossCPU across.  NVLink: 2 links on the eight 'strong' pairs (which include the
+    four pairs hard-coded in gpuallocator/staticdgx_policies.go:76), 1 link on eight more."""
+    t = _sym(8)
+    for i, j in itertools.combinations(range(8), 2):
+        if (i, j) in ((0, 1), (2, 3), (4, 5), (6, 7)):
+            p = 5
+        elif (i < 4) == (j < 4):
+            p = 2
+        else:
+            p = 1
+        _set(t, i, j, p)
+    for i, j in ((0, 3), (0, 4), (1, 2), (1, 5), (2, 3), (4, 7), (5, 6), (6, 7)):
+        t[i, j, 1] = t[j, i, 1] = nvlink_type(2)
+    for i, j in ((0, 1), (0, 2), (1, 3), (2, 6), (3, 7), (4, 5), (4, 6), (5, 7)):
+        t[i, j, 1] = t[j, i, 1] = nvlink_type(1)
+    return t
+
+
+def topo_random(n, seed, max_nvlinks=6, p_nvlink=0.5):
+    """T4..: seeded random symmetric topology over {10..60} + {0,100,..,100*max_nvlinks}."""
+    rng = np.random.default_rng(seed)
+    t = _sym(n)
+    for i, j in itertools.combinations(range(n), 2):
+        pcie = int(rng.integers(1, 7))
+        nvl = int(rng.integers(1, max_nvlinks + 1)) if rng.random() < p_nvlink else 0
+        _set(t, i, j, pcie, nvlink_type(nvl))
+    return t
+
+
+def topo_spiked(n, seed, spike_pair=None, spike=250):
+    """D6 hazard vector: weights in {10,20,30} except one pair that is
+    worth `spike` (expressed as SingleSwitch 50 + 2 NVLinks = 250)."""
+    rng = np.random.default_rng(seed)
+    t = _sym(n)
+    for i, j in itertools.combinations(range(n), 2):
+        _set(t, i, j, int(rng.integers(1, 4)))
+    a, b = spike_pair if spike_pair else (n - 2, n - 1)
+    assert spike == 250
+    _set(t, a, b, 5, nvlink_type(2))
+    return t
+
+
+def standard_topologies():
+    """The 14 eight-GPU topologies of config 1: T0..T3 + ten seeded random ones."""
+    topos = [("T0_zero", topo_zero(8)), ("T1_uniform", topo_uniform(8)), ("T2_b200_as_ref_sees_it", topo_two_sockets(8)),
+             ("T3_dgx1v_like", topo_dgx1v_like())]
+    for s in range(10):
+        topos.append(("T%d_random" % (4 + s), topo_random(8, 1000 + s)))
+    return topos
+
+
+def links_to_weights(links2):
+    """W[i,j] = sum of link scores, nlinks[i,j] = number of links — numpy statement of
+    calculateGPUPairScore's switch (besteffort_policy.go:314-353); used to build inputs."""
+    score = np.zeros(19, dtype=np.int32)
+    for t, s in PCIE_SCORE.items():
+        score[t] = s
+    for k in range(1, 13):
+        score[6 + k] = 100 * k
+    W = score[links2[:, :, 0]] + score[links2[:, :, 1]]
+    nl = (links2[:, :, 0] != 0).astype(np.uint8) + (links2[:, :, 1] != 0).astype(np.uint8)
+    n = links2.shape[0]
+    W[np.arange(n), np.arange(n)] = 0
+    nl[np.arange(n), np.arange(n)] = 0
+    return W.astype(np.int32), nl.astype(np.uint8)
+
+
+def node_uuids(n, seed=1):
+    """UUIDs in NVML-index order, shaped like 'GPU-fef8089b-4820-abfc-e83e-94318197576e'."""
+    rng = np.random.default_rng(seed)
+    return ["GPU-" + str(_uuid.UUID(bytes=bytes(rng.integers(0, 256, 16, dtype=np.uint8).tolist()))) for _ in range(n)]
+
+
+def sorted_positions(uuids):
+    """NVML indices in byte-wise sorted-UUID order: the order stripReplicas hands to the
+    allocator (cmd/nvidia-device-plugin/replica.go:43, server.go:274)."""
+    return sorted(range(len(uuids)), key=lambda i: uuids[i].encode())
+
+
+def exhaustive_requests(order, seed=0, n_pairs=8):
+    """Config 1 request set: every non-empty availability mask x k=1..|mask| x required in
+    {none, each single available device, n_pairs seeded pairs}.  `order` = NVML indices in
+    allocator order.  Yields (avail list, required list, size)."""
+    rng = np.random.default_rng(seed)
+    n = len(order)
+    for mask in range(1, 1 << n):
+        avail = [order[p] for p in range(n) if mask >> p & 1]
+        pairs = []
+        if len(avail) >= 2:
+            for _ in range(n_pairs):
+                a, b = rng.choice(len(avail), 2, replace=False)
+                pairs.append([avail[int(a)], avail[int(b)]])
+        for k in range(1, len(avail) + 1):
+            yield avail, [], k
+            for d in avail:
+                yield avail, [d], k
+            for pr in pairs:
+                yield avail, pr, k
+
+
+# --------------------------------------------------------------------------------------
+# Packed batch format of gpa_besteffort_batch (include/gpualloc.h): one 32-byte record per
+# container request.
+REQ_DTYPE = np.dtype([("avail", np.uint8, 16), ("req_mask", np.uint16), ("n_avail", np.uint8), ("size", np.uint8),
+                      ("flags", np.uint8), ("pad", np.uint8, 11)])
+assert REQ_DTYPE.itemsize == 32
+RES_DTYPE = np.dtype([("dev", np.int8, 16)])
+FLAG_REQ_FOREIGN = 1  # some required device is not one of the available pointers (D4)
+
+
+def pack_requests(reqs):
+    """[(avail, required, size)] -> REQ_DTYPE array.  required devices are given as NVML
+    indices and stored as a bit mask over positions in `avail`."""
+    out = np.zeros(len(reqs), dtype=REQ_DTYPE)
+    for i, (avail, req, size) in enumerate(reqs):
+        out["avail"][i, :len(avail)] = avail
+        out["n_avail"][i] = len(avail)
+        out["size"][i] = size
+        m, fl = 0, 0
+        for d in req:
+            if d in avail:
+                m |= 1 << list(avail).index(d)
+            else:
+                fl |= FLAG_REQ_FOREIGN
+        if len(set(req)) != len(req):
+            raise ValueError("duplicate required device")
+        out["req_mask"][i] = m
+        out["flags"][i] = fl
+    return out
+
+
+def random_request_batch(n_dev, count, seed, order=None, p_required=0.25):
+    """Seeded stream of best-effort container requests on an n_dev-GPU node, built with
+    vectorised numpy so that millions of requests take seconds: availability mask uniform
+    over non-empty masks, size uniform in 1..|avail|, with probability p_required one
+    required device drawn from the available ones."""
+    rng = np.random.default_rng(seed)
+    order = np.arange(n_dev, dtype=np.uint8) if order is None else np.asarray(order, dtype=np.uint8)
+    masks = rng.integers(1, 1 << n_dev, size=count, dtype=np.int64)
+    bits = (masks[:, None] >> np.arange(n_dev)[None, :]) & 1          # [count, n_dev] by position
+    n_avail = bits.sum(1)
+    # stable compaction of the available positions to the front, keeping allocator order
+    key = np.where(bits == 1, np.arange(n_dev)[None, :], n_dev + np.arange(n_dev)[None, :])
+    pos = np.argsort(key, axis=1, kind="stable")
+    out = np.zeros(count, dtype=REQ_DTYPE)
+    av = order[pos]
+    av[np.arange(n_dev)[None, :] >= n_avail[:, None]] = 0
+    out["avail"][:, :n_dev] = av
+    out["n_avail"] = n_avail
+    out["size"] = 1 + (rng.integers(0, 1 << 30, size=count) % n_avail)
+    want_req = rng.random(count) < p_required
+    which = rng.integers(0, 1 << 30, size=count) % n_avail
+    out["req_mask"] = np.where(want_req, 1 << which, 0).astype(np.uint16)
+    return out
+
+
+def unpack_request(rec):
+    """REQ_DTYPE record -> (avail list, required list, size); foreign flag -> [-2]"""
+    n = int(rec["n_avail"])
+    avail = [int(x) for x in rec["avail"][:n]]
+    req = [avail[p] for p in range(n) if int(rec["req_mask"]) >> p & 1]
+    if int(rec["flags"]) & FLAG_REQ_FOREIGN:
+        req = req + [-2]
+    return avail, req, int(rec["size"])
