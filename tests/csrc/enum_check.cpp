@@ -1,0 +1,66 @@
+// Host-side unit harness for k8s-gpu-sharing-plugin_b200/csrc/gpa_enum.cuh.
+//
+// TEST CODE, not a product path: it runs the enumeration core that the CUDA kernels are
+// built from as a plain sequential loop over work items, so that the ordering / tie-break /
+// padding / aliasing logic can be checked against the oracle on a machine without a GPU.
+// The product library never contains this loop (it fails loudly without CUDA).
+#include <cstdint>
+#include <vector>
+
+#include "../../k8s-gpu-sharing-plugin_b200/csrc/gpa_enum.cuh"
+
+extern "C" int enum_check_search(int nt, const int32_t *W, const int32_t *avail, int n_avail, uint32_t rmask, int size,
+                                 int intended, unsigned long long want_items, int32_t *out, int *n_out,
+                                 unsigned long long *n_items, int *cut_depth) {
+  using namespace gpa;
+  *n_out = 0;
+  if (size < 2 || n_avail < size || n_avail > kMaxDevices) return -1;
+  BinomTable B;
+  fill_binom(B);
+  int n = n_avail;
+  std::vector<uint16_t> S((size_t)1 << n, 0);
+  for (uint32_t mask = 1; mask < (1u << n); mask++) {
+    int s = 0;
+    for (int a = 0; a < n; a++)
+      if (mask >> a & 1)
+        for (int b = a + 1; b < n; b++)
+          if (mask >> b & 1) s += W[avail[a] * nt + avail[b]];
+    S[mask] = (uint16_t)s;
+  }
+  auto Sf = [&](uint32_t mask) { return S[mask]; };
+  Geom g = make_geom(n, size, rmask);
+  Cut cut = choose_cut(g, B, want_items);
+  if (n_items) *n_items = cut.n_items;
+  if (cut_depth) *cut_depth = cut.d;
+  uint64_t key = 0;
+  for (uint64_t item = 0; item < cut.n_items; item++) {
+    int sc = search_item(g, cut, B, Sf, item);
+    if (sc >= 0) {
+      uint64_t kk = pack_key(sc, item);
+      if (kk > key) key = kk;
+    }
+  }
+  int8_t pos[32];
+  int cnt = finalize(g, cut, B, Sf, key, intended != 0, pos);
+  if (cnt < 0) return -2;
+  for (int i = 0; i < cnt; i++) out[i] = pos[i] < 0 ? -1 : avail[pos[i]];
+  *n_out = cnt;
+  return 0;
+}
+
+// exposes the stepper alone: all sets of one level, as masks (anchor included)
+extern "C" int enum_check_level_sets(int n, int k, int tok_present, uint32_t rem_reals, uint32_t *out, int cap) {
+  using namespace gpa;
+  Geom g = make_geom(n, k, 0);
+  uint32_t rem = rem_reals | (tok_present ? g.tok_bit : 0u);
+  uint32_t anchor;
+  Stepper st = make_stepper(g, rem, anchor);
+  uint32_t chosen;
+  int cnt = 0;
+  if (!st.first(chosen)) return 0;
+  do {
+    if (cnt < cap) out[cnt] = anchor | chosen;
+    cnt++;
+  } while (st.next(chosen));
+  return cnt;
+}

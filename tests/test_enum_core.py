@@ -1,0 +1,137 @@
+"""CPU check of the enumeration core the CUDA kernels are built from
+(k8s-gpu-sharing-plugin_b200/csrc/gpa_enum.cuh), run sequentially by the test harness
+tests/csrc/enum_check.cpp and compared with the oracle.  This is a unit test of shared
+header logic; the product path itself only exists as CUDA kernels."""
+import ctypes as C
+import itertools
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from k8s_gpu_sharing_plugin_b200 import synthetic as syn
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SRC = os.path.join(HERE, "csrc", "enum_check.cpp")
+HDR = os.path.join(HERE, "..", "k8s-gpu-sharing-plugin_b200", "csrc", "gpa_enum.cuh")
+SO = os.path.join(HERE, "csrc", "libenum_check.so")
+
+
+@pytest.fixture(scope="module")
+def harness():
+    if not os.path.exists(SO) or os.path.getmtime(SO) < max(os.path.getmtime(SRC), os.path.getmtime(HDR)):
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", SO, SRC])
+    L = C.CDLL(SO)
+    L.enum_check_search.restype = C.c_int
+    L.enum_check_search.argtypes = [C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int, C.c_uint32, C.c_int,
+                                    C.c_int, C.c_ulonglong, C.POINTER(C.c_int32), C.POINTER(C.c_int),
+                                    C.POINTER(C.c_ulonglong), C.POINTER(C.c_int)]
+    L.enum_check_level_sets.restype = C.c_int
+    L.enum_check_level_sets.argtypes = [C.c_int, C.c_int, C.c_int, C.c_uint32, C.POINTER(C.c_uint32), C.c_int]
+    return L
+
+
+def run(L, W, avail, req, k, intended, want_items):
+    W = np.ascontiguousarray(W, dtype=np.int32)
+    av = np.ascontiguousarray(avail, dtype=np.int32)
+    rmask = 0
+    for d in req:
+        rmask |= 1 << list(avail).index(d)
+    out = np.zeros(64, dtype=np.int32)
+    n_out, n_items, depth = C.c_int(0), C.c_ulonglong(0), C.c_int(0)
+    rc = L.enum_check_search(W.shape[0], W.ctypes.data_as(C.POINTER(C.c_int32)), av.ctypes.data_as(C.POINTER(C.c_int32)),
+                             len(av), rmask, k, int(intended), want_items, out.ctypes.data_as(C.POINTER(C.c_int32)),
+                             C.byref(n_out), C.byref(n_items), C.byref(depth))
+    assert rc == 0
+    return [int(x) for x in out[:n_out.value]], n_items.value, depth.value
+
+
+def test_stepper_emits_the_reference_level_order(harness):
+    """one iterate() level: anchor + every (k-1)-combination of the literal remainder in
+    lexicographic order, keeping those with 0 or all P nil pads (besteffort_policy.go:266-276)"""
+    for n, k in [(5, 3), (8, 3), (7, 4), (9, 4), (10, 3), (6, 5), (11, 6), (7, 2), (13, 5), (5, 5), (4, 3)]:
+        N = -(-n // k) * k
+        P = N - n
+        for tok_present in ([0, 1] if P else [0]):
+            # any remainder that a real walk can reach: r reals with r = j*k (no token) or j*k - P (token)
+            for j in range(1, N // k + 1):
+                r = j * k - (P if tok_present else 0)
+                if r < 1 or r > n:
+                    continue
+                rng = np.random.default_rng(n * 100 + k * 10 + j)
+                reals = sorted(int(x) for x in rng.choice(n, r, replace=False))
+                lit = reals + ([n + i for i in range(P)] if tok_present else [])
+                want = []
+                for combo in itertools.combinations(lit[1:], k - 1):
+                    pads = sum(1 for p in combo if p >= n)
+                    if pads not in (0, P):
+                        continue
+                    mask = 1 << lit[0]
+                    for p in combo:
+                        mask |= (1 << p) if p < n else (1 << n)
+                    want.append(mask)
+                buf = (C.c_uint32 * 20000)()
+                cnt = harness.enum_check_level_sets(n, k, tok_present, sum(1 << p for p in reals), buf, 20000)
+                assert [buf[i] for i in range(cnt)] == want, (n, k, tok_present, reals)
+
+
+@pytest.mark.parametrize("want_items", [1, 40, 10**12])
+@pytest.mark.parametrize("topo_i", [0, 2, 3, 5])
+def test_core_matches_oracle_exhaustive_n8(harness, oracle, topo_i, want_items):
+    name, t = syn.standard_topologies()[topo_i]
+    W, nl = syn.links_to_weights(t)
+    order = syn.sorted_positions(syn.node_uuids(8, seed=1))
+    cnt = 0
+    for avail, req, k in syn.exhaustive_requests(order, seed=topo_i, n_pairs=3):
+        if k < 2 or len(req) > k:
+            continue
+        if len(avail) < 6 and (cnt % 3):
+            cnt += 1
+            continue
+        want = oracle.besteffort(W, nl, avail, req, k, oracle.GO_FAITHFUL, "fast")
+        got, _, _ = run(harness, W, avail, req, k, False, want_items)
+        assert (oracle.OK, got) == want, (name, avail, req, k)
+        cnt += 1
+    assert cnt > 2000
+
+
+@pytest.mark.parametrize("n,k", [(9, 2), (9, 4), (10, 3), (10, 4), (11, 2), (11, 3), (11, 5), (12, 3), (12, 5), (12, 7),
+                                 (13, 2), (13, 3), (13, 6), (14, 2), (14, 4), (14, 5), (15, 2), (15, 4), (16, 2), (16, 5),
+                                 (16, 6), (16, 7), (16, 8), (16, 9), (16, 13), (12, 11), (16, 16)])
+def test_core_matches_oracle_seeded_large(harness, oracle, n, k):
+    big = oracle.partition_count(n, k) > 100000  # keep the CPU suite to minutes
+    for seed in range(1 if big else 2):
+        W, nl = syn.links_to_weights(syn.topo_random(n, 300 + seed))
+        rng = np.random.default_rng(seed)
+        avail = [int(x) for x in rng.permutation(n)]
+        reqs = [[], [avail[int(rng.integers(n))]]]
+        if k >= 3 and not big:
+            reqs.append([avail[int(x)] for x in rng.choice(n, 2, replace=False)])
+        for req in reqs:
+            for mode in ((oracle.GO_FAITHFUL,) if big and req else (oracle.GO_FAITHFUL, oracle.INTENDED)):
+                want = oracle.besteffort(W, nl, avail, req, k, mode, "fast")
+                for want_items in ((5000,) if big else (1, 5000, 10**12)):
+                    got, n_items, depth = run(harness, W, avail, req, k, mode == oracle.INTENDED, want_items)
+                    assert (oracle.OK, got) == want, (n, k, seed, req, mode, want_items, depth)
+
+
+@pytest.mark.parametrize("n", [13, 14, 15, 16])
+def test_core_reproduces_slice_aliasing_D6(harness, oracle, n):
+    for seed in range(3 if n <= 14 else 1):
+        W, nl = syn.links_to_weights(syn.topo_spiked(n, seed))
+        avail = list(range(n))
+        for mode in (oracle.GO_FAITHFUL, oracle.INTENDED):
+            want = oracle.besteffort(W, nl, avail, [], 2, mode, "fast")
+            got, _, _ = run(harness, W, avail, [], 2, mode == oracle.INTENDED, 20000)
+            assert (oracle.OK, got) == want, (n, seed, mode)
+
+
+def test_core_nil_pad_vector_D5(harness, oracle):
+    t = syn.topo_uniform(5)
+    for i, j in ((2, 3), (2, 4), (3, 4)):
+        t[i, j, 0] = t[j, i, 0] = 5
+    t[0, 1] = t[1, 0] = (5, syn.nvlink_type(1))
+    W, nl = syn.links_to_weights(t)
+    got, _, _ = run(harness, W, [0, 1, 2, 3, 4], [], 3, False, 1)
+    assert got == [0, 1, -1]
