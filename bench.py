@@ -1,0 +1,350 @@
+#!/usr/bin/env python3
+"""Benchmark of the GetPreferredAllocation best-effort path (contract: task brief §④).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One step = one batch of container requests (the r.ContainerRequests loop of
+GetPreferredAllocation, cmd/nvidia-device-plugin/server.go:273-311, each answered by
+Policy.Allocate at :298) over one seeded synthetic stream:
+
+    8-GPU node, replicas = 1 (the best-effort branch, server.go:297-301), topology T2
+    "B200 as the reference sees it" (NVSwitch links invisible to nvml.GetNVLink, so PCIe
+    ancestry only: SameCPU inside each socket, CrossCPU across), free-GPU count uniform in
+    1..8, allocation size uniform in 1..|free|, a required device with p = 0.25.
+
+Metric: decisions/s.  `value` times the batch kernel alone with inputs resident in HBM
+(CUDA events on the launching stream); `e2e` times the host-buffer C-ABI call
+gpa_besteffort_batch (pinned host memory -> HBM -> kernel -> pinned host memory);
+`cpu_baseline` is the oracle (the C restatement of the Go reference: there is no Go
+toolchain on this image) on a bounded sample, one core.  The line also carries the
+single-request machine-wide search (n = 16 physical, k = 3: 22.4 M candidate partitions)
+under "search_n16".
+
+Multi-GPU: the path does not shard: --gpus N runs N independent replicas,
+one process per GPU, each on its own seeded batch; value = total decisions / max time.
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import __graft_entry__ as entry  # noqa: E402
+
+entry.load_package()
+from k8s_gpu_sharing_plugin_b200 import synthetic as syn  # noqa: E402
+
+METRIC = "GetPreferredAllocation decisions/sec (best-effort policy, 8 physical GPUs)"
+UNIT = "decisions/s"
+BATCH = 1 << 22           # requests per step per GPU: 128 MiB in + 64 MiB out > 126 MB of L2
+REF_BATCH = 1 << 18       # requests per step of the reference arm (bounded CPU sample)
+CPU_SAMPLE = 1 << 21      # requests of the one-core cpu_baseline sample
+N_DEV = 8
+
+
+def workload_config(n_gpus):
+    return {
+        "workload": "configs[0]/[1] shape: 8-GPU node, replicas=1 (best-effort branch), topology T2 "
+                    "'B200 as the reference sees it', i.i.d. seeded stream: free GPUs U{1..8}, size U{1..free}, "
+                    "required device p=0.25",
+        "batch_requests_per_gpu": BATCH,
+        "request_bytes": 32, "result_bytes": 16,
+        "l2_policy": "inputs_larger_than_L2 (192 MiB touched per step)",
+        "mode": "go_faithful",
+        "parallelism": "replicas x%d (no collective; SURVEY.md 8e)" % n_gpus,
+    }
+
+
+def make_inputs(seed, count):
+    t = syn.topo_two_sockets(N_DEV)
+    W, nl = syn.links_to_weights(t)
+    order = syn.sorted_positions(syn.node_uuids(N_DEV, seed=1))
+    reqs = syn.random_request_batch(N_DEV, count, seed=seed, order=order)
+    return t, W, nl, reqs
+
+
+def algorithmic_pair_evals(reqs):
+    """pair_evals = partitions(n,k) * m * C(k,2) for the requests that reach the search"""
+    table = np.zeros((17, 17), dtype=np.float64)
+    for n in range(1, 17):
+        for k in range(2, n + 1):
+            N = -(-n // k) * k
+            P, m = N - n, N // k
+            f = math.factorial
+            parts = f(n) // (f(k) ** m * f(m)) if P == 0 else math.comb(n, k - P) * f((m - 1) * k) // (f(k) ** (m - 1) * f(m - 1))
+            table[n, k] = parts * m * math.comb(k, 2)
+    n = reqs["n_avail"].astype(np.int64)
+    k = reqs["size"].astype(np.int64)
+    searched = (k >= 2) & (k <= n) & ((reqs["flags"] & 1) == 0)
+    return float(table[np.clip(n, 0, 16), np.clip(k, 0, 16)][searched].sum())
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)"""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        super().__init__(daemon=True)
+        self.gpu = gpu_index
+        self.samples = []
+        self._stop = threading.Event()
+
+    def run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                if len(f) >= 9:
+                    self.samples.append(f)
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def stop(self):
+        self._stop.set()
+        self.join(timeout=6)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = sorted(float(s[1]) for s in self.samples)
+        reasons = set()
+        for s in self.samples:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), s[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.samples[0][2]), "samples": len(sm),
+                "power_w_max": max(float(s[3]) for s in self.samples), "reasons": sorted(reasons)}
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+# ---------------------------------------------------------------------------------------
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path.  The Go code cannot be
+    built here (no Go toolchain), so this times the oracle, its C restatement ("port"), sharded
+    over all host threads; rank 0 only."""
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return 0
+    from oracle import oracle as orc
+    orc.build()
+    _, W, nl, reqs = make_inputs(seed=1000, count=REF_BATCH)
+    cores = os.cpu_count() or 1
+    out = np.zeros(len(reqs), dtype=syn.RES_DTYPE)
+    for _ in range(max(args.warmup, 1)):
+        orc.besteffort_batch(W, nl, reqs, threads=cores, out=out)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        orc.besteffort_batch(W, nl, reqs, threads=cores, out=out)
+    dt = time.perf_counter() - t0
+    value = args.steps * len(reqs) / dt
+    sample = "%d requests/step of the same seeded stream, %d host threads" % (len(reqs), cores)
+    cfg = workload_config(args.gpus)
+    cfg["batch_requests_per_gpu"] = REF_BATCH
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "int32", "data": "synthetic", "config": cfg,
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "C restatement of the Go reference (oracle/), not Go: no Go toolchain on this image",
+    }))
+    return 0
+
+
+# ---------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    from k8s_gpu_sharing_plugin_b200 import _lib as gpa
+
+    rank, world, local = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fall-back")
+    torch.cuda.set_device(local)
+    use_dist = world > 1
+    if use_dist:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    ctx = gpa.Context(local)
+    t, W, nl, reqs = make_inputs(seed=1000 + rank, count=BATCH)
+    ctx.set_topology_links(t)
+
+    # ---- device-resident arm: `value` -------------------------------------------------
+    d_in = torch.from_numpy(reqs.view(np.uint8).reshape(-1, 32)).cuda()
+    d_out = torch.empty((len(reqs), 16), dtype=torch.int8, device="cuda")
+    stream = torch.cuda.current_stream()
+
+    def step_device():
+        ctx.besteffort_batch_device(d_in.data_ptr(), len(reqs), N_DEV, d_out.data_ptr(), stream=stream.cuda_stream)
+
+    def barrier():
+        if use_dist:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    launches0 = ctx.launch_count
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    e_all0, e_all1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e_all0.record(stream)
+    for a, b in evs:
+        a.record(stream)
+        step_device()
+        b.record(stream)
+    e_all1.record(stream)
+    barrier()
+    launches = ctx.launch_count - launches0
+    total_ms = e_all0.elapsed_time(e_all1)
+    kernel_ms = [a.elapsed_time(b) for a, b in evs]
+    sampler.stop()
+    if use_dist:
+        tt = torch.tensor([total_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        total_ms = float(tt.item())
+    value = world * args.steps * len(reqs) / (total_ms * 1e-3)
+
+    # ---- parity of what was just timed (outside the timed region) -----------------------
+    from oracle import oracle as orc
+    orc.build()
+    got = np.zeros(len(reqs), dtype=syn.RES_DTYPE)
+    got["dev"] = d_out.cpu().numpy()
+    idx = np.random.default_rng(rank).choice(len(reqs), 100000, replace=False)
+    want, _ = orc.besteffort_batch(W, nl, reqs[idx], threads=os.cpu_count() or 1)
+    mismatches = int((got["dev"][idx] != want["dev"]).any(axis=1).sum())
+
+    # ---- end-to-end arm: host buffers through the C ABI ---------------------------------
+    pin_in = gpa.PinnedBuffer(len(reqs), syn.REQ_DTYPE)
+    pin_out = gpa.PinnedBuffer(len(reqs), syn.RES_DTYPE)
+    pin_in.array[:] = reqs
+    for _ in range(args.warmup):
+        ctx.besteffort_batch(pin_in.array, out=pin_out.array)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        ctx.besteffort_batch(pin_in.array, out=pin_out.array)
+    e2e_s = time.perf_counter() - t0
+    if use_dist:
+        tt = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e_s = float(tt.item())
+    e2e_value = world * args.steps * len(reqs) / e2e_s
+    e2e_mismatch = int((pin_out.array["dev"][idx] != want["dev"]).any(axis=1).sum())
+
+    if rank != 0:
+        if use_dist:
+            dist.destroy_process_group()
+        return 0
+
+    # ---- roofline of the dominant kernel (the batch kernel is the only one in the step) --
+    pair_evals = algorithmic_pair_evals(reqs)
+    alg_bytes = 4.0 * pair_evals
+    avg_kernel_s = float(np.mean(kernel_ms)) * 1e-3
+    peak, peak_src = measured_peak()
+    achieved = alg_bytes / avg_kernel_s / 1e9
+    roofline = {
+        "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+        "kernel": "besteffort_batch_kernel", "peak_source": peak_src + ", burst",
+        "algorithmic_bytes_per_launch": alg_bytes,
+        "io_bytes_per_launch": 48.0 * len(reqs), "io_gbs": 48.0 * len(reqs) / avg_kernel_s / 1e9,
+        "note": "algorithmic bytes = 4 B x pair evaluations the reference performs (SURVEY.md 8d); the kernel reads "
+                "set scores from a shared-memory table instead, so this is not DRAM traffic; io_* is the real "
+                "request+result traffic",
+    }
+
+    # ---- CPU baseline: the oracle on one core, bounded sample ---------------------------
+    sample = reqs[:CPU_SAMPLE]
+    t0 = time.perf_counter()
+    orc.besteffort_batch(W, nl, sample, threads=1)
+    cpu_s = time.perf_counter() - t0
+    cpu_baseline = {"value": len(sample) / cpu_s, "unit": UNIT, "cores": 1, "kind": "port",
+                    "sample": "first %d requests of the step's batch, oracle/ref_besteffort.c (allocation-free "
+                              "restatement of the Go policy), one thread" % len(sample)}
+
+    # ---- the machine-wide single search (config 3b): n = 16 physical, k = 3 ---------------
+    t16 = syn.topo_random(16, 77)
+    W16, nl16 = syn.links_to_weights(t16)
+    ctx.set_topology_links(t16)
+    lat, kms = [], []
+    res16 = None
+    for i in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        res16 = ctx.besteffort(list(range(16)), [], 3)
+        dt = time.perf_counter() - t0
+        if i >= args.warmup:
+            lat.append(dt)
+            kms.append(ctx.search_stats()["kernel_ms"])
+    st = ctx.search_stats()
+    evals16 = st["partitions"] * st["sets"] * 3
+    search16 = {
+        "workload": "config 3b: n=16 physical, k=3, seeded random topology, one request",
+        "partitions": st["partitions"], "items": st["items"], "grid": st["grid"], "block": st["block"],
+        "kernel_ms": float(np.median(kms)), "call_ms_p50": float(np.median(lat)) * 1e3,
+        "algorithmic_gbs": 4.0 * evals16 / (float(np.median(kms)) * 1e-3) / 1e9,
+        "partitions_per_s": st["partitions"] / (float(np.median(kms)) * 1e-3),
+        "answer": res16[1],
+    }
+    ctx.set_topology_links(t)
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "int32", "data": "synthetic", "config": workload_config(world),
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 32 * len(reqs), "d2h_bytes_per_step": 16 * len(reqs),
+                "ms_per_step": e2e_s / args.steps * 1e3},
+        "gpu_launches": int(launches),
+        "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": sampler.summary(),
+        "parity": {"checked": int(len(idx)), "mismatches_device_arm": mismatches, "mismatches_e2e_arm": e2e_mismatch},
+        "search_n16": search16,
+    }
+    print(json.dumps(line))
+    if use_dist:
+        dist.destroy_process_group()
+    return 0 if mismatches == 0 and e2e_mismatch == 0 else 1
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

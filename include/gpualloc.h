@@ -1,0 +1,176 @@
+/*
+ * gpualloc.h — C ABI of libgpualloc.so, the B200-native GetPreferredAllocation path of
+ * the k8s GPU-sharing device plugin.
+ *
+ * Every entry point names the reference interface it stands in for ("ref:" lines; paths
+ * are relative to the reference repository, iktos/k8s-gpu-sharing-plugin).  Conventions:
+ *   - plain C types only; the caller owns every buffer it passes in or receives into;
+ *   - return value: GPA_OK (0) or a negative GPA_ERR_* code; no exception crosses the
+ *     boundary; gpa_strerror() gives the text;
+ *   - devices are identified by their NVML index (ref: gpuallocator.Device.Index,
+ *     vendor/github.com/NVIDIA/go-gpuallocator/gpuallocator/device.go:15-19);
+ *   - all entry points are thread-safe; calls on one context are serialised internally
+ *     (ref: grpc-go runs every RPC on its own goroutine and the reference holds no locks,
+ *     vendor/google.golang.org/grpc/server.go:742-747).
+ *   - the library needs a CUDA device for every allocation decision: there is no CPU
+ *     fall-back, and gpa_create() fails with GPA_ERR_CUDA when no device is usable.
+ */
+#ifndef GPUALLOC_H
+#define GPUALLOC_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GPA_OK 0
+#define GPA_ERR_INVALID (-1)       /* bad argument (null pointer, index out of range, duplicate device ...) */
+#define GPA_ERR_CUDA (-2)          /* CUDA runtime error; see gpa_last_error() */
+#define GPA_ERR_NO_TOPOLOGY (-3)   /* gpa_set_topology*() has not been called on this context */
+#define GPA_ERR_ASYMMETRIC (-4)    /* where Go panics: "all P2PLinks between 2 GPUs should be bidirectional"
+                                      (ref: gpuallocator/besteffort_policy.go:307-310) */
+#define GPA_ERR_TOO_LARGE (-5)     /* more than GPA_MAX_AVAILABLE devices, or a search beyond GPA_MAX_PARTITIONS */
+#define GPA_ERR_WEIGHT_RANGE (-6)  /* pair weights negative or too large for the 16-bit score table */
+#define GPA_ERR_BUFFER (-7)        /* caller's output buffer is too small */
+#define GPA_ERR_NVML (-8)          /* NVML could not be loaded / returned an error */
+#define GPA_ERR_PANIC (-9)         /* where Go panics in prioritizeDevices: make([]string, len(must), size) with
+                                      len > cap (ref: cmd/nvidia-device-plugin/replica.go:121) */
+#define GPA_ERR_NO_DEVICES_LEFT (-10) /* "no devices left to allocate" (ref: replica.go:183) */
+#define GPA_ERR_MUST_MISSING (-11) /* "device '%s' in mustIncludeDeviceIDs is missing from availableDeviceIDs"
+                                      (ref: replica.go:129,136) */
+#define GPA_ERR_UNKNOWN_DEVICE (-12) /* "no device with uuid: %v" (ref: gpuallocator/device.go:89-91) /
+                                        "unknown device" (ref: cmd/nvidia-device-plugin/server.go:321,330) */
+#define GPA_ERR_NOT_IMPLEMENTED (-13) /* "GetPreferredAllocation() not implemented in this case"
+                                         (ref: server.go:302-304) */
+
+#define GPA_MAX_TOPOLOGY 64     /* devices in a topology (NVML indices 0..63) */
+#define GPA_MAX_AVAILABLE 16    /* devices in one request's `available` list */
+#define GPA_MAX_PARTITIONS (1ull << 36) /* candidate partitions one search may visit */
+
+/* mode_flags */
+#define GPA_MODE_GO_FAITHFUL 0 /* bit-exact with the compiled Go reference, including the slice aliasing of
+                                  bestPartition — the default */
+#define GPA_MODE_INTENDED 1    /* what the Go source means: bestPartition keeps the best candidate intact */
+
+#define GPA_NIL (-1)     /* a nil *Device in a returned set (ref: SURVEY.md D5) */
+#define GPA_FOREIGN (-2) /* in `required`: a device pointer that is none of the `available` pointers — what the
+                            reference's own call site passes (ref: server.go:274,279) */
+
+typedef struct gpa_ctx gpa_ctx;
+
+/* ---- context ------------------------------------------------------------------------ */
+
+/* Binds a context to one CUDA device: stream, pinned mailbox, device scratch, tables.
+ * ref: gpuallocator.NewBestEffortPolicy(), gpuallocator/besteffort_policy.go:14-16 (the
+ * Go policy is stateless; the state here is what lets a request cost one launch). */
+int gpa_create(int cuda_device, gpa_ctx **out);
+void gpa_destroy(gpa_ctx *ctx);
+const char *gpa_strerror(int code);
+/* text of the last CUDA / NVML failure on this context ("" if none) */
+const char *gpa_last_error(gpa_ctx *ctx);
+/* number of kernels this context has launched so far (bench.py reports it as gpu_launches) */
+unsigned long long gpa_launch_count(gpa_ctx *ctx);
+
+/* ---- topology ----------------------------------------------------------------------- */
+
+/* Installs the pair-weight matrix: W[i*n+j] = what calculateGPUPairScore(gpu_i, gpu_j)
+ * adds up over gpu_i.Links[gpu_j.Index]; nlinks[i*n+j] = len(gpu_i.Links[gpu_j.Index]).
+ * Copy-on-write: requests already running keep the matrix they started with.
+ * ref: gpuallocator.NewDevices(), gpuallocator/device.go:33-72 (rebuilt from NVML on every
+ * request there; built once and cached here) and calculateGPUPairScore,
+ * gpuallocator/besteffort_policy.go:298-356. */
+int gpa_set_topology(gpa_ctx *ctx, int n, const int32_t *W, const uint8_t *nlinks);
+
+/* Same, from link types: links2[(i*n+j)*2 + {0,1}] = {PCIe-ancestry link, NVLink-count link}
+ * as nvml.P2PLinkType values (0 = absent).  Applies the score switch of
+ * gpuallocator/besteffort_policy.go:314-353 (10..60 for PCIe ancestry, 100 per NVLink).
+ * ref: nvml.P2PLinkType, vendor/github.com/NVIDIA/gpu-monitoring-tools/bindings/go/nvml/nvml.go:132-154. */
+int gpa_set_topology_links(gpa_ctx *ctx, int n, const int32_t *links2);
+
+/* The score switch alone, for one link type.  ref: besteffort_policy.go:314-353. */
+int gpa_link_type_score(int link_type);
+
+/* Reads the installed matrix back (n*n entries each); either pointer may be NULL. */
+int gpa_get_topology(gpa_ctx *ctx, int *n, int32_t *W, uint8_t *nlinks, int cap);
+
+/* ---- best-effort policy ------------------------------------------------------------- */
+
+/* One allocation decision.  avail[0..n_avail): NVML indices in the caller's order (the
+ * reference passes them sorted by UUID); req[0..n_req): NVML indices or GPA_FOREIGN.
+ * out (>= size entries) receives the chosen devices in `available` order, GPA_NIL for a nil
+ * pad; *n_out is `size` or 0 ("cannot allocate": Go returns an empty slice, never an error).
+ * ref: gpuallocator.Policy.Allocate(available, required []*Device, size int) []*Device,
+ * gpuallocator/allocator.go:24-32, as implemented by bestEffortPolicy.Allocate,
+ * gpuallocator/besteffort_policy.go:34-89; called at cmd/nvidia-device-plugin/server.go:298. */
+int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_t *req, int n_req, int size,
+                   int mode_flags, int32_t *out, int *n_out);
+
+/* Search statistics of the last gpa_besteffort() on this context (all optional). */
+typedef struct gpa_search_stats {
+  unsigned long long partitions; /* candidate partitions of the request (closed form) */
+  unsigned long long items;      /* independent work items the search was cut into */
+  int cut_depth;                 /* levels resolved from the item index */
+  int sets;                      /* m: sets per partition */
+  int padding;                   /* P: nil pads */
+  int best_score;                /* score of the winning partition, in units of `score_unit`; -1 if none */
+  int score_unit;                /* gcd of the pair weights (scores are kept divided by it on the device) */
+  int grid, block, smem_bytes;   /* launch shape of the search kernel, 0 if no kernel was needed */
+  float kernel_ms;               /* device time of the search kernel (CUDA events), 0 if none */
+} gpa_search_stats;
+int gpa_last_search_stats(gpa_ctx *ctx, gpa_search_stats *out);
+
+/* A batch of container requests against the installed topology, one 32-byte record each.
+ * ref: the loop over r.ContainerRequests in GetPreferredAllocation,
+ * cmd/nvidia-device-plugin/server.go:273-311, each iteration calling Policy.Allocate (:298). */
+typedef struct gpa_request {
+  uint8_t avail[GPA_MAX_AVAILABLE]; /* NVML indices in the caller's order */
+  uint16_t req_mask;                /* bit p set: avail[p] is required */
+  uint8_t n_avail;
+  uint8_t size;                     /* allocation size, 0..255 */
+  uint8_t flags;                    /* GPA_REQ_* */
+  uint8_t n_req_extra;              /* required devices beyond those in req_mask (only their count matters:
+                                       guard len(required) > size, besteffort_policy.go:43-45) */
+  uint8_t reserved[10];
+} gpa_request;
+#define GPA_REQ_FOREIGN 1 /* some required device is GPA_FOREIGN */
+
+typedef struct gpa_result {
+  int8_t dev[GPA_MAX_AVAILABLE]; /* chosen NVML indices in `available` order, GPA_NIL for a pad, then GPA_RES_END */
+} gpa_result;
+#define GPA_RES_END (-128)  /* unused tail of gpa_result.dev; dev[0] == GPA_RES_END: empty answer */
+#define GPA_RES_ERROR (-127) /* dev[0] == GPA_RES_ERROR: dev[1] holds the GPA_ERR_* code of this request */
+
+/* host buffers: copies in, launches, copies out, synchronises */
+int gpa_besteffort_batch(gpa_ctx *ctx, const gpa_request *reqs, int count, int mode_flags, gpa_result *out);
+/* device buffers, asynchronous on `stream` (a cudaStream_t; NULL = the context's stream): inputs already resident
+ * in HBM, nothing copied, nothing synchronised.  max_avail = largest n_avail in the batch (<= GPA_BATCH_MAX_AVAILABLE). */
+int gpa_besteffort_batch_device(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_avail, int mode_flags,
+                                gpa_result *d_out, void *stream);
+#define GPA_BATCH_MAX_AVAILABLE 12 /* larger requests go through gpa_besteffort() one by one */
+
+/* Page-locked host memory for batch buffers: gpa_besteffort_batch() DMAs such buffers directly and stages pageable
+ * ones through an internal pinned mailbox.  (No reference counterpart: Go has no device copies to feed.) */
+void *gpa_alloc_host(size_t bytes);
+void gpa_free_host(void *p);
+
+/* ---- replica ids (host code: string work, no parallelism) ---------------------------- */
+
+/* Results are written NUL-separated into outbuf; *n_out = number of strings.
+ * ref: stripReplicas(), cmd/nvidia-device-plugin/replica.go:32-45. */
+int gpa_strip_replicas(const char *const *ids, int n, char *outbuf, int outbuf_len, int *n_out);
+
+/* ref: prioritizeDevices(), cmd/nvidia-device-plugin/replica.go:96-198.
+ * Returns GPA_OK, or GPA_ERR_NO_DEVICES_LEFT / GPA_ERR_MUST_MISSING (offending id in errbuf) /
+ * GPA_ERR_PANIC.  *non_unique = 1 stands for &NonUniqueError{} (the result is still valid). */
+int gpa_prioritize_devices(const char *const *avail, int n_avail, const char *const *must, int n_must, int size,
+                           char *outbuf, int outbuf_len, int *n_out, int *non_unique, char *errbuf, int errbuf_len);
+
+/* ref: getAdditionalXids(), cmd/nvidia-device-plugin/nvidia.go:274-294. */
+int gpa_get_additional_xids(const char *input, uint64_t *out, int out_cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPUALLOC_H */

@@ -1,0 +1,251 @@
+"""ctypes binding of libgpualloc.so (the C ABI in include/gpualloc.h).
+
+The library is built in-tree by ``__graft_entry__.build()`` / ``make -C csrc``.  There is no
+Python or CPU implementation behind these calls: without the shared object, or without a
+CUDA device, they raise.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libgpualloc.so")
+
+OK = 0
+ERR_INVALID, ERR_CUDA, ERR_NO_TOPOLOGY, ERR_ASYMMETRIC, ERR_TOO_LARGE, ERR_WEIGHT_RANGE, ERR_BUFFER = -1, -2, -3, -4, -5, -6, -7
+ERR_NVML, ERR_PANIC, ERR_NO_DEVICES_LEFT, ERR_MUST_MISSING, ERR_UNKNOWN_DEVICE, ERR_NOT_IMPLEMENTED = -8, -9, -10, -11, -12, -13
+MODE_GO_FAITHFUL, MODE_INTENDED = 0, 1
+NIL, FOREIGN = -1, -2
+RES_END, RES_ERROR = -128, -127
+MAX_AVAILABLE, BATCH_MAX_AVAILABLE = 16, 12
+
+
+class GpaError(RuntimeError):
+    def __init__(self, code, detail=""):
+        self.code = code
+        msg = lib().gpa_strerror(code).decode()
+        super().__init__("%s (%d)%s" % (msg, code, (": " + detail) if detail else ""))
+
+
+class SearchStats(C.Structure):
+    _fields_ = [("partitions", C.c_ulonglong), ("items", C.c_ulonglong), ("cut_depth", C.c_int), ("sets", C.c_int),
+                ("padding", C.c_int), ("best_score", C.c_int), ("score_unit", C.c_int), ("grid", C.c_int),
+                ("block", C.c_int), ("smem_bytes", C.c_int), ("kernel_ms", C.c_float)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError("libgpualloc.so is not built (%s); run `python -c 'import __graft_entry__ as e; e.build()'`"
+                           % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    i32p, u8p, vp = C.POINTER(C.c_int32), C.POINTER(C.c_uint8), C.c_void_p
+    L.gpa_strerror.restype = C.c_char_p
+    L.gpa_strerror.argtypes = [C.c_int]
+    L.gpa_create.argtypes = [C.c_int, C.POINTER(vp)]
+    L.gpa_destroy.restype = None
+    L.gpa_destroy.argtypes = [vp]
+    L.gpa_last_error.restype = C.c_char_p
+    L.gpa_last_error.argtypes = [vp]
+    L.gpa_launch_count.restype = C.c_ulonglong
+    L.gpa_launch_count.argtypes = [vp]
+    L.gpa_set_topology.argtypes = [vp, C.c_int, i32p, u8p]
+    L.gpa_set_topology_links.argtypes = [vp, C.c_int, i32p]
+    L.gpa_link_type_score.argtypes = [C.c_int]
+    L.gpa_get_topology.argtypes = [vp, C.POINTER(C.c_int), i32p, u8p, C.c_int]
+    L.gpa_besteffort.argtypes = [vp, i32p, C.c_int, i32p, C.c_int, C.c_int, C.c_int, i32p, C.POINTER(C.c_int)]
+    L.gpa_last_search_stats.argtypes = [vp, C.POINTER(SearchStats)]
+    L.gpa_besteffort_batch.argtypes = [vp, vp, C.c_int, C.c_int, vp]
+    L.gpa_besteffort_batch_device.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp]
+    L.gpa_alloc_host.restype = vp
+    L.gpa_alloc_host.argtypes = [C.c_size_t]
+    L.gpa_free_host.restype = None
+    L.gpa_free_host.argtypes = [vp]
+    L.gpa_strip_replicas.argtypes = [C.POINTER(C.c_char_p), C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_int)]
+    L.gpa_prioritize_devices.argtypes = [C.POINTER(C.c_char_p), C.c_int, C.POINTER(C.c_char_p), C.c_int, C.c_int,
+                                         C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_char_p, C.c_int]
+    L.gpa_get_additional_xids.argtypes = [C.c_char_p, C.POINTER(C.c_uint64), C.c_int]
+    for name in ("gpa_create", "gpa_set_topology", "gpa_set_topology_links", "gpa_link_type_score", "gpa_get_topology",
+                 "gpa_besteffort", "gpa_last_search_stats", "gpa_besteffort_batch", "gpa_besteffort_batch_device",
+                 "gpa_strip_replicas", "gpa_prioritize_devices", "gpa_get_additional_xids"):
+        getattr(L, name).restype = C.c_int
+    _lib = L
+    return L
+
+
+def _strs(xs):
+    arr = (C.c_char_p * max(len(xs), 1))()
+    for i, x in enumerate(xs):
+        arr[i] = x.encode() if isinstance(x, str) else x
+    return arr
+
+
+def _unpack(buf, n):
+    out, off, raw = [], 0, buf.raw
+    for _ in range(n):
+        end = raw.index(b"\0", off)
+        out.append(raw[off:end].decode())
+        off = end + 1
+    return out
+
+
+def strip_replicas(ids):
+    """ref: stripReplicas, cmd/nvidia-device-plugin/replica.go:32-45"""
+    buf = C.create_string_buffer(sum(len(x) + 1 for x in ids) + 16)
+    n = C.c_int(0)
+    rc = lib().gpa_strip_replicas(_strs(ids), len(ids), buf, len(buf), C.byref(n))
+    if rc != OK:
+        raise GpaError(rc)
+    return _unpack(buf, n.value)
+
+
+def prioritize_devices(avail, must, size):
+    """ref: prioritizeDevices, cmd/nvidia-device-plugin/replica.go:96-198.
+    -> (ids or None, error kind in {none, non_unique, no_devices_left, must_missing, panic}, offending id)"""
+    buf = C.create_string_buffer(sum(len(x) + 1 for x in list(avail) + list(must)) + 16)
+    err = C.create_string_buffer(512)
+    n, nu = C.c_int(0), C.c_int(0)
+    rc = lib().gpa_prioritize_devices(_strs(avail), len(avail), _strs(must), len(must), int(size), buf, len(buf),
+                                      C.byref(n), C.byref(nu), err, len(err))
+    if rc == OK:
+        return _unpack(buf, n.value), ("non_unique" if nu.value else "none"), ""
+    kind = {ERR_NO_DEVICES_LEFT: "no_devices_left", ERR_MUST_MISSING: "must_missing", ERR_PANIC: "panic"}.get(rc)
+    if kind is None:
+        raise GpaError(rc)
+    return None, kind, err.value.decode()
+
+
+def get_additional_xids(s):
+    """ref: getAdditionalXids, cmd/nvidia-device-plugin/nvidia.go:274-294"""
+    out = (C.c_uint64 * 256)()
+    n = lib().gpa_get_additional_xids(s.encode() if isinstance(s, str) else s, out, 256)
+    if n < 0:
+        raise GpaError(n)
+    return [int(out[i]) for i in range(n)]
+
+
+def link_type_score(t):
+    return int(lib().gpa_link_type_score(int(t)))
+
+
+class Context:
+    """One gpa_ctx bound to a CUDA device."""
+
+    def __init__(self, device=0):
+        self._h = C.c_void_p()
+        rc = lib().gpa_create(int(device), C.byref(self._h))
+        if rc != OK:
+            raise GpaError(rc, "gpa_create(device=%d) — a CUDA device is required, there is no CPU fall-back" % device)
+
+    def close(self):
+        if self._h:
+            lib().gpa_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != OK:
+            raise GpaError(rc, lib().gpa_last_error(self._h).decode())
+
+    @property
+    def launch_count(self):
+        return int(lib().gpa_launch_count(self._h))
+
+    def set_topology(self, W, nlinks):
+        W = np.ascontiguousarray(W, dtype=np.int32)
+        nl = np.ascontiguousarray(nlinks, dtype=np.uint8)
+        self._check(lib().gpa_set_topology(self._h, W.shape[0], W.ctypes.data_as(C.POINTER(C.c_int32)),
+                                           nl.ctypes.data_as(C.POINTER(C.c_uint8))))
+
+    def set_topology_links(self, links2):
+        l2 = np.ascontiguousarray(links2, dtype=np.int32)
+        self._check(lib().gpa_set_topology_links(self._h, l2.shape[0], l2.ctypes.data_as(C.POINTER(C.c_int32))))
+
+    def get_topology(self):
+        n = C.c_int(0)
+        self._check(lib().gpa_get_topology(self._h, C.byref(n), None, None, 0))
+        W = np.zeros((n.value, n.value), dtype=np.int32)
+        nl = np.zeros((n.value, n.value), dtype=np.uint8)
+        self._check(lib().gpa_get_topology(self._h, C.byref(n), W.ctypes.data_as(C.POINTER(C.c_int32)),
+                                           nl.ctypes.data_as(C.POINTER(C.c_uint8)), n.value * n.value))
+        return W, nl
+
+    def besteffort(self, avail, req, size, mode=MODE_GO_FAITHFUL):
+        """Policy.Allocate(available, required, size) -> (rc, [NVML indices, NIL for a pad])"""
+        av = np.ascontiguousarray(avail, dtype=np.int32)
+        rq = np.ascontiguousarray(req, dtype=np.int32)
+        out = np.full(max(int(size), 1) + 32, -9, dtype=np.int32)
+        n_out = C.c_int(0)
+        rc = lib().gpa_besteffort(self._h, av.ctypes.data_as(C.POINTER(C.c_int32)), len(av),
+                                  rq.ctypes.data_as(C.POINTER(C.c_int32)), len(rq), int(size), int(mode),
+                                  out.ctypes.data_as(C.POINTER(C.c_int32)), C.byref(n_out))
+        return rc, [int(x) for x in out[:n_out.value]]
+
+    def search_stats(self):
+        st = SearchStats()
+        self._check(lib().gpa_last_search_stats(self._h, C.byref(st)))
+        return {f: getattr(st, f) for f, _ in SearchStats._fields_}
+
+    def besteffort_batch(self, reqs, mode=MODE_GO_FAITHFUL, out=None):
+        """reqs: numpy array of synthetic.REQ_DTYPE (host memory) -> array of RES_DTYPE"""
+        from . import synthetic as syn
+        reqs = np.ascontiguousarray(reqs)
+        assert reqs.dtype == syn.REQ_DTYPE
+        if out is None:
+            out = np.zeros(len(reqs), dtype=syn.RES_DTYPE)
+        self._check(lib().gpa_besteffort_batch(self._h, reqs.ctypes.data, len(reqs), int(mode), out.ctypes.data))
+        return out
+
+    def besteffort_batch_device(self, d_reqs_ptr, count, max_avail, d_out_ptr, mode=MODE_GO_FAITHFUL, stream=None):
+        self._check(lib().gpa_besteffort_batch_device(self._h, C.c_void_p(d_reqs_ptr), int(count), int(max_avail),
+                                                      int(mode), C.c_void_p(d_out_ptr), C.c_void_p(stream or 0)))
+
+
+def decode_result(rec):
+    """RES_DTYPE record -> (rc, [devices])"""
+    dev = rec["dev"]
+    if dev[0] == RES_ERROR:
+        return int(dev[1]), []
+    out = []
+    for d in dev:
+        if d == RES_END:
+            break
+        out.append(int(d))
+    return OK, out
+
+
+class PinnedBuffer:
+    """Page-locked host memory from gpa_alloc_host, viewed as a numpy array (``.array``)."""
+
+    def __init__(self, count, dtype):
+        dtype = np.dtype(dtype)
+        self.nbytes = max(int(count) * dtype.itemsize, 1)
+        self.ptr = lib().gpa_alloc_host(self.nbytes)
+        if not self.ptr:
+            raise GpaError(ERR_CUDA, "gpa_alloc_host(%d)" % self.nbytes)
+        self._buf = (C.c_uint8 * self.nbytes).from_address(self.ptr)
+        self.array = np.frombuffer(self._buf, dtype=dtype, count=int(count))
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            self._buf = None
+            lib().gpa_free_host(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass

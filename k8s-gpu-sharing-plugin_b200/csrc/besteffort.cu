@@ -1,0 +1,728 @@
+// Best-effort partition search on the GPU: kernels, context and the C ABI around them.
+//
+// Replaces, behind include/gpualloc.h, the reference's
+//   bestEffortPolicy.Allocate   vendor/github.com/NVIDIA/go-gpuallocator/gpuallocator/besteffort_policy.go:34-89
+//   iterateGPUPartitions        ... :209-290
+//   calculateGPU{Pair,Set,Partition}Score ... :298-380
+// and the per-request weight source gpuallocator.NewDevices (gpuallocator/device.go:33-72),
+// which becomes a device-resident matrix installed once by gpa_set_topology().
+//
+// Two kernels, both built from the enumeration core in gpa_enum.cuh:
+//   besteffort_search_kernel : ONE request, the whole machine.  The partition tree is cut
+//       into order-numbered work items; every CTA builds the set-score table in shared
+//       memory, threads walk items grid-stride, a 64-bit (score, ~item) key is max-reduced
+//       warp -> CTA -> one global atomicMax, and the last CTA to finish replays the winning
+//       item and writes the answer.  No second launch, no host round trip in between.
+//   besteffort_batch_kernel  : MANY requests (the ContainerRequests loop), one warp each.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/gpualloc.h"
+#include "gpa_enum.cuh"
+
+namespace {
+
+using namespace gpa;
+
+__constant__ BinomTable c_binom;
+
+constexpr int kSearchBlockSmall = 256;   // score table <= 32 KB: several CTAs per SM
+constexpr int kSearchBlockLarge = 1024;  // 64-128 KB table: one or two CTAs per SM, so make them wide
+constexpr int kBatchWarps = 8;
+constexpr int kScoreCap = 65535;                        // uint16 set-score table
+constexpr int kMaxPairs = (kMaxDevices * (kMaxDevices - 1)) / 2;  // 120
+
+struct STab {
+  const uint16_t *s;
+  __device__ __forceinline__ uint32_t operator()(uint32_t mask) const { return s[mask]; }
+};
+
+struct SearchParams {
+  Geom g;
+  Cut cut;
+  int intended;
+  uint16_t wp[kMaxDevices * kMaxDevices];  // scaled weight of (earlier position a, later position b) at [a*16+b]
+};
+
+struct SearchResult {
+  int32_t count;  // k, 0 = empty answer, -1 = internal inconsistency
+  int32_t best_score;
+  int8_t pos[32];  // positions, -1 = nil pad
+  unsigned long long key;
+};
+
+// Score table of every mask a set can be: k reals, or k-P reals next to the pads.
+__device__ __forceinline__ void fill_score_table(uint16_t *S, const uint16_t *wp, const Geom &g, int tid, int nthreads) {
+  const uint32_t total = 1u << g.n;
+  const int kp = g.P ? g.k - g.P : -1;
+  for (uint32_t mask = tid; mask < total; mask += nthreads) {
+    int pc = __popc(mask);
+    if (pc != g.k && pc != kp) continue;
+    uint32_t sum = 0;
+    uint32_t ma = mask;
+    while (ma) {
+      int a = __ffs(ma) - 1;
+      ma &= ma - 1;
+      uint32_t mb = ma;
+      while (mb) {
+        int b = __ffs(mb) - 1;
+        mb &= mb - 1;
+        sum += wp[a * kMaxDevices + b];
+      }
+    }
+    S[mask] = (uint16_t)sum;
+  }
+}
+
+__device__ __forceinline__ unsigned long long warp_max_u64(unsigned long long v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    unsigned long long u = __shfl_xor_sync(0xffffffffu, v, o);
+    v = u > v ? u : v;
+  }
+  return v;
+}
+
+template <int kSearchBlock>
+__global__ void __launch_bounds__(kSearchBlock) besteffort_search_kernel(const SearchParams p, unsigned long long *g_key,
+                                                                          unsigned int *g_ticket, SearchResult *g_res) {
+  extern __shared__ __align__(16) uint16_t S[];
+  __shared__ uint16_t wp[kMaxDevices * kMaxDevices];
+  __shared__ unsigned long long wkey[kSearchBlock / 32];
+  __shared__ int is_last;
+
+  const int tid = threadIdx.x;
+  for (int i = tid; i < kMaxDevices * kMaxDevices; i += kSearchBlock) wp[i] = p.wp[i];
+  __syncthreads();
+  fill_score_table(S, wp, p.g, tid, kSearchBlock);
+  __syncthreads();
+
+  const STab stab{S};
+  unsigned long long best = 0;
+  const unsigned long long stride = (unsigned long long)gridDim.x * kSearchBlock;
+  for (unsigned long long item = (unsigned long long)blockIdx.x * kSearchBlock + tid; item < p.cut.n_items; item += stride) {
+    int sc = search_item(p.g, p.cut, c_binom, stab, item);
+    if (sc >= 0) {
+      unsigned long long kk = pack_key(sc, item);
+      best = kk > best ? kk : best;
+    }
+  }
+  best = warp_max_u64(best);
+  if ((tid & 31) == 0) wkey[tid >> 5] = best;
+  __syncthreads();
+  if (tid == 0) {
+    unsigned long long b = wkey[0];
+#pragma unroll
+    for (int w = 1; w < kSearchBlock / 32; w++) b = wkey[w] > b ? wkey[w] : b;
+    if (b) atomicMax(g_key, b);
+    __threadfence();
+    unsigned int t = atomicAdd(g_ticket, 1u);
+    is_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (is_last && tid == 0) {
+    // every CTA's atomicMax is visible: its fence preceded its ticket
+    unsigned long long key = atomicMax(g_key, 0ull);
+    SearchResult r;
+    r.key = key;
+    r.best_score = key ? key_score(key) : -1;
+    r.count = finalize(p.g, p.cut, c_binom, stab, key, p.intended != 0, r.pos);
+    *g_res = r;
+    *g_key = 0ull;  // leave the scratch clean for the next launch on this stream
+    *g_ticket = 0u;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// Batch: one warp per container request.
+
+struct BatchTopo {
+  const uint16_t *wq;   // nt*nt scaled weights
+  const uint8_t *asym;  // nt*nt, 1 where the link counts of (i,j) and (j,i) differ
+  int nt;
+};
+
+__device__ __forceinline__ void write_result(gpa_result *out, const int8_t *dev) {
+  const int4 *src = reinterpret_cast<const int4 *>(dev);
+  *reinterpret_cast<int4 *>(out->dev) = *src;
+}
+
+__global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_kernel(const gpa_request *__restrict__ reqs, int count,
+                                                                            int n_cap, int intended, BatchTopo topo,
+                                                                            gpa_result *__restrict__ out) {
+  extern __shared__ __align__(16) uint16_t smem[];
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  uint16_t *S = smem + (size_t)warp * ((1u << n_cap) + kMaxDevices * kMaxDevices);
+  uint16_t *wp = S + (1u << n_cap);
+  const STab stab{S};
+
+  for (int r = blockIdx.x * kBatchWarps + warp; r < count; r += gridDim.x * kBatchWarps) {
+    // 32-byte record, same address in every lane: one broadcast transaction each
+    const uint4 lo = __ldg(reinterpret_cast<const uint4 *>(reqs + r));
+    const uint4 hi = __ldg(reinterpret_cast<const uint4 *>(reqs + r) + 1);
+    const uint32_t availw[4] = {lo.x, lo.y, lo.z, lo.w};
+    const uint32_t rmask = hi.x & 0xFFFFu;
+    const int n = (hi.x >> 16) & 0xFF;
+    const int size = (hi.x >> 24) & 0xFF;
+    const int flags = hi.y & 0xFF;
+    const int n_req = __popc(rmask) + ((hi.y >> 8) & 0xFF);
+    auto dev_at = [&](int pidx) -> int { return (availw[pidx >> 2] >> ((pidx & 3) * 8)) & 0xFF; };
+
+    __align__(16) int8_t res[GPA_MAX_AVAILABLE];
+#pragma unroll
+    for (int i = 0; i < GPA_MAX_AVAILABLE; i++) res[i] = GPA_RES_END;
+    int err = 0;
+    bool done = false;
+
+    // guards of besteffort_policy.go:35-45, in the reference's order
+    if (size <= 0 || n < size || n_req > size) done = true;
+    if (!done) {
+      if (n > n_cap || n > GPA_BATCH_MAX_AVAILABLE) {
+        err = GPA_ERR_TOO_LARGE;
+      } else {
+        unsigned long long seen = 0;
+        for (int a = 0; a < n; a++) {
+          int d = dev_at(a);
+          if (d >= topo.nt) {
+            err = GPA_ERR_INVALID;
+          } else {
+            if (seen >> d & 1ull) err = GPA_ERR_INVALID;  // the same device twice
+            seen |= 1ull << d;
+          }
+        }
+        if ((rmask >> n) != 0) err = GPA_ERR_INVALID;
+      }
+      if (err) done = true;
+    }
+    if (!done && (flags & GPA_REQ_FOREIGN)) done = true;  // no candidate can contain a foreign pointer (:53)
+    if (!done && size == 1) {
+      // :219-224 — single-device candidates in `available` order, first accepted wins (score 0 never beats 0)
+      res[0] = (int8_t)dev_at(rmask ? __ffs(rmask) - 1 : 0);
+      done = true;
+    }
+    if (!done) {
+      // link-count symmetry over the available devices (where calculateGPUPairScore would panic, :307-310)
+      int bad = 0;
+      for (int i = lane; i < n * n; i += 32) {
+        int a = i / n, b = i - a * n;
+        int da = dev_at(a), db = dev_at(b);
+        bad |= topo.asym[da * topo.nt + db];
+        if (a < b) wp[a * kMaxDevices + b] = topo.wq[da * topo.nt + db];
+      }
+      bad = __any_sync(0xffffffffu, bad);
+      if (bad) {
+        err = GPA_ERR_ASYMMETRIC;
+        done = true;
+      }
+    }
+    if (!done) {
+      __syncwarp();
+      const Geom g = make_geom(n, size, rmask);
+      fill_score_table(S, wp, g, lane, 32);
+      __syncwarp();
+      const Cut cut = choose_cut(g, c_binom, 64);
+      unsigned long long best = 0;
+      for (unsigned long long item = lane; item < cut.n_items; item += 32) {
+        int sc = search_item(g, cut, c_binom, stab, item);
+        if (sc >= 0) {
+          unsigned long long kk = pack_key(sc, item);
+          best = kk > best ? kk : best;
+        }
+      }
+      best = warp_max_u64(best);
+      if (lane == 0) {
+        int8_t pos[32];
+        int cnt = finalize(g, cut, c_binom, stab, best, intended != 0, pos);
+        if (cnt < 0) {
+          err = GPA_ERR_INVALID;
+        } else {
+          for (int i = 0; i < cnt; i++) res[i] = pos[i] < 0 ? (int8_t)GPA_NIL : (int8_t)dev_at(pos[i]);
+        }
+      }
+      __syncwarp();  // S / wp are reused by the next request of this warp
+    }
+    if (lane == 0) {
+      if (err) {
+        res[0] = GPA_RES_ERROR;
+        res[1] = (int8_t)err;
+      }
+      write_result(out + r, res);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// Host side
+
+#define CUDA_TRY(ctx, expr)                                                                   \
+  do {                                                                                        \
+    cudaError_t e_ = (expr);                                                                  \
+    if (e_ != cudaSuccess) {                                                                  \
+      (ctx)->last_error = std::string(#expr) + ": " + cudaGetErrorString(e_);                 \
+      return GPA_ERR_CUDA;                                                                    \
+    }                                                                                         \
+  } while (0)
+
+struct Topology {
+  int n = 0;
+  int unit = 1;  // gcd of the weights; device tables hold W / unit
+  std::vector<int32_t> W;
+  std::vector<uint8_t> nlinks;
+  std::vector<uint16_t> wq;
+  std::vector<uint8_t> asym;
+};
+
+}  // namespace
+
+struct gpa_ctx {
+  int device = 0;
+  int sm_count = 0;
+  int max_smem_optin = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  std::mutex mu;
+  std::string last_error;
+  unsigned long long launches = 0;
+  // scratch + mailbox
+  unsigned long long *d_key = nullptr;
+  unsigned int *d_ticket = nullptr;
+  SearchResult *d_res = nullptr;
+  SearchResult *h_res = nullptr;  // pinned
+  // topology (host copy + device tables)
+  Topology topo;
+  bool has_topo = false;
+  uint16_t *d_wq = nullptr;
+  uint8_t *d_asym = nullptr;
+  // batch staging
+  gpa_request *d_reqs = nullptr;
+  gpa_result *d_out = nullptr;
+  size_t batch_cap = 0;
+  gpa_request *h_reqs = nullptr;  // pinned staging
+  gpa_result *h_out = nullptr;
+  size_t h_batch_cap = 0;
+  BinomTable binom;
+  gpa_search_stats stats{};
+};
+
+namespace {
+
+int gcd_int(int a, int b) {
+  while (b) {
+    int t = a % b;
+    a = b;
+    b = t;
+  }
+  return a;
+}
+
+int ensure_batch_capacity(gpa_ctx *ctx, size_t count, bool host_staging) {
+  if (count > ctx->batch_cap) {
+    if (ctx->d_reqs) cudaFree(ctx->d_reqs);
+    if (ctx->d_out) cudaFree(ctx->d_out);
+    ctx->d_reqs = nullptr;
+    ctx->d_out = nullptr;
+    ctx->batch_cap = 0;
+    size_t cap = count + count / 4 + 1024;
+    CUDA_TRY(ctx, cudaMalloc(&ctx->d_reqs, cap * sizeof(gpa_request)));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->d_out, cap * sizeof(gpa_result)));
+    ctx->batch_cap = cap;
+  }
+  if (host_staging && count > ctx->h_batch_cap) {
+    if (ctx->h_reqs) cudaFreeHost(ctx->h_reqs);
+    if (ctx->h_out) cudaFreeHost(ctx->h_out);
+    ctx->h_reqs = nullptr;
+    ctx->h_out = nullptr;
+    ctx->h_batch_cap = 0;
+    size_t cap = count + count / 4 + 1024;
+    CUDA_TRY(ctx, cudaMallocHost(&ctx->h_reqs, cap * sizeof(gpa_request)));
+    CUDA_TRY(ctx, cudaMallocHost(&ctx->h_out, cap * sizeof(gpa_result)));
+    ctx->h_batch_cap = cap;
+  }
+  return GPA_OK;
+}
+
+int launch_batch(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_avail, int mode_flags, gpa_result *d_out,
+                 cudaStream_t stream) {
+  if (count == 0) return GPA_OK;
+  int n_cap = max_avail < 2 ? 2 : max_avail;
+  if (n_cap > GPA_BATCH_MAX_AVAILABLE) n_cap = GPA_BATCH_MAX_AVAILABLE;
+  size_t smem = (size_t)kBatchWarps * (((size_t)1 << n_cap) + kMaxDevices * kMaxDevices) * sizeof(uint16_t);
+  if (smem > 48 * 1024)
+    CUDA_TRY(ctx, cudaFuncSetAttribute(besteffort_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 1;
+  CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, besteffort_batch_kernel, kBatchWarps * 32, smem));
+  if (occ < 1) occ = 1;
+  long long want = ((long long)count + kBatchWarps - 1) / kBatchWarps;
+  long long cap = (long long)ctx->sm_count * occ;  // persistent: one wave, warps stride over the requests
+  int grid = (int)(want < cap ? want : cap);
+  BatchTopo t{ctx->d_wq, ctx->d_asym, ctx->topo.n};
+  besteffort_batch_kernel<<<grid, kBatchWarps * 32, smem, stream>>>(d_reqs, count, n_cap, mode_flags & GPA_MODE_INTENDED, t,
+                                                                    d_out);
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return GPA_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *gpa_strerror(int code) {
+  switch (code) {
+    case GPA_OK: return "ok";
+    case GPA_ERR_INVALID: return "invalid argument";
+    case GPA_ERR_CUDA: return "CUDA error";
+    case GPA_ERR_NO_TOPOLOGY: return "no topology installed";
+    case GPA_ERR_ASYMMETRIC:
+      return "Internal error in bestEffort GPU allocator: all P2PLinks between 2 GPUs should be bidirectional";
+    case GPA_ERR_TOO_LARGE: return "request too large";
+    case GPA_ERR_WEIGHT_RANGE: return "pair weights out of range for the score table";
+    case GPA_ERR_BUFFER: return "output buffer too small";
+    case GPA_ERR_NVML: return "NVML error";
+    case GPA_ERR_PANIC: return "runtime error: makeslice: cap out of range";
+    case GPA_ERR_NO_DEVICES_LEFT: return "no devices left to allocate";
+    case GPA_ERR_MUST_MISSING: return "device in mustIncludeDeviceIDs is missing from availableDeviceIDs";
+    case GPA_ERR_UNKNOWN_DEVICE: return "unknown device";
+    case GPA_ERR_NOT_IMPLEMENTED: return "GetPreferredAllocation() not implemented in this case";
+    default: return "unknown error";
+  }
+}
+
+int gpa_create(int cuda_device, gpa_ctx **out) {
+  if (!out) return GPA_ERR_INVALID;
+  *out = nullptr;
+  gpa_ctx *ctx = new gpa_ctx();
+  ctx->device = cuda_device;
+  auto fail = [&](int code) {
+    // keep the text reachable for the caller's log
+    fprintf(stderr, "gpa_create: %s\n", ctx->last_error.c_str());
+    gpa_destroy(ctx);
+    return code;
+  };
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || cuda_device < 0 || cuda_device >= ndev) {
+    ctx->last_error = e != cudaSuccess ? cudaGetErrorString(e) : "no such CUDA device";
+    return fail(GPA_ERR_CUDA);
+  }
+#define CREATE_TRY(expr)                                              \
+  do {                                                                \
+    cudaError_t e_ = (expr);                                          \
+    if (e_ != cudaSuccess) {                                          \
+      ctx->last_error = std::string(#expr) + ": " + cudaGetErrorString(e_); \
+      return fail(GPA_ERR_CUDA);                                      \
+    }                                                                 \
+  } while (0)
+  CREATE_TRY(cudaSetDevice(cuda_device));
+  CREATE_TRY(cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, cuda_device));
+  CREATE_TRY(cudaDeviceGetAttribute(&ctx->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, cuda_device));
+  CREATE_TRY(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  CREATE_TRY(cudaEventCreate(&ctx->ev0));
+  CREATE_TRY(cudaEventCreate(&ctx->ev1));
+  CREATE_TRY(cudaMalloc(&ctx->d_key, sizeof(unsigned long long)));
+  CREATE_TRY(cudaMalloc(&ctx->d_ticket, sizeof(unsigned int)));
+  CREATE_TRY(cudaMalloc(&ctx->d_res, sizeof(SearchResult)));
+  CREATE_TRY(cudaMallocHost(&ctx->h_res, sizeof(SearchResult)));
+  CREATE_TRY(cudaMemset(ctx->d_key, 0, sizeof(unsigned long long)));
+  CREATE_TRY(cudaMemset(ctx->d_ticket, 0, sizeof(unsigned int)));
+  fill_binom(ctx->binom);
+  CREATE_TRY(cudaMemcpyToSymbol(c_binom, &ctx->binom, sizeof(BinomTable)));
+  CREATE_TRY(cudaDeviceSynchronize());
+#undef CREATE_TRY
+  *out = ctx;
+  return GPA_OK;
+}
+
+void gpa_destroy(gpa_ctx *ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  if (ctx->d_key) cudaFree(ctx->d_key);
+  if (ctx->d_ticket) cudaFree(ctx->d_ticket);
+  if (ctx->d_res) cudaFree(ctx->d_res);
+  if (ctx->h_res) cudaFreeHost(ctx->h_res);
+  if (ctx->d_wq) cudaFree(ctx->d_wq);
+  if (ctx->d_asym) cudaFree(ctx->d_asym);
+  if (ctx->d_reqs) cudaFree(ctx->d_reqs);
+  if (ctx->d_out) cudaFree(ctx->d_out);
+  if (ctx->h_reqs) cudaFreeHost(ctx->h_reqs);
+  if (ctx->h_out) cudaFreeHost(ctx->h_out);
+  if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+  if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+const char *gpa_last_error(gpa_ctx *ctx) { return ctx ? ctx->last_error.c_str() : ""; }
+
+unsigned long long gpa_launch_count(gpa_ctx *ctx) {
+  if (!ctx) return 0;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  return ctx->launches;
+}
+
+int gpa_link_type_score(int link_type) {
+  // the switch of besteffort_policy.go:314-353 over nvml.P2PLinkType (nvml.go:132-154):
+  // six PCIe-ancestry levels worth 10..60, then n NVLinks worth 100 each
+  if (link_type >= 1 && link_type <= 6) return 10 * link_type;
+  if (link_type >= 7 && link_type <= 18) return 100 * (link_type - 6);
+  return 0;
+}
+
+int gpa_set_topology(gpa_ctx *ctx, int n, const int32_t *W, const uint8_t *nlinks) {
+  if (!ctx || !W || !nlinks || n < 1 || n > GPA_MAX_TOPOLOGY) return GPA_ERR_INVALID;
+  Topology t;
+  t.n = n;
+  t.W.assign(W, W + (size_t)n * n);
+  t.nlinks.assign(nlinks, nlinks + (size_t)n * n);
+  int g = 0, mx = 0;
+  for (int i = 0; i < n; i++)
+    for (int j = 0; j < n; j++) {
+      if (i == j) continue;  // a device is never paired with itself (:303-305)
+      int w = W[i * n + j];
+      if (w < 0) return GPA_ERR_WEIGHT_RANGE;
+      g = gcd_int(g, w);
+      mx = w > mx ? w : mx;
+    }
+  if (g == 0) g = 1;
+  if ((long long)(mx / g) * kMaxPairs > kScoreCap) return GPA_ERR_WEIGHT_RANGE;
+  t.unit = g;
+  t.wq.assign((size_t)n * n, 0);
+  t.asym.assign((size_t)n * n, 0);
+  for (int i = 0; i < n; i++)
+    for (int j = 0; j < n; j++) {
+      if (i == j) continue;
+      t.wq[i * n + j] = (uint16_t)(W[i * n + j] / g);
+      t.asym[i * n + j] = nlinks[i * n + j] != nlinks[j * n + i];
+    }
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  // Requests are serialised on ctx->mu and each one finishes before it returns, so no
+  // kernel can still be reading the old tables here.
+  uint16_t *d_wq = nullptr;
+  uint8_t *d_asym = nullptr;
+  CUDA_TRY(ctx, cudaMalloc(&d_wq, t.wq.size() * sizeof(uint16_t)));
+  CUDA_TRY(ctx, cudaMalloc(&d_asym, t.asym.size()));
+  CUDA_TRY(ctx, cudaMemcpy(d_wq, t.wq.data(), t.wq.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
+  CUDA_TRY(ctx, cudaMemcpy(d_asym, t.asym.data(), t.asym.size(), cudaMemcpyHostToDevice));
+  if (ctx->d_wq) cudaFree(ctx->d_wq);
+  if (ctx->d_asym) cudaFree(ctx->d_asym);
+  ctx->d_wq = d_wq;
+  ctx->d_asym = d_asym;
+  ctx->topo = std::move(t);
+  ctx->has_topo = true;
+  return GPA_OK;
+}
+
+int gpa_set_topology_links(gpa_ctx *ctx, int n, const int32_t *links2) {
+  if (!ctx || !links2 || n < 1 || n > GPA_MAX_TOPOLOGY) return GPA_ERR_INVALID;
+  std::vector<int32_t> W((size_t)n * n, 0);
+  std::vector<uint8_t> nl((size_t)n * n, 0);
+  for (int i = 0; i < n; i++)
+    for (int j = 0; j < n; j++) {
+      if (i == j) continue;
+      for (int s = 0; s < 2; s++) {
+        int t = links2[((size_t)i * n + j) * 2 + s];
+        if (t != 0) {  // device.go:56-58, :64-66 — P2PLinkUnknown is not recorded
+          W[i * n + j] += gpa_link_type_score(t);
+          nl[i * n + j]++;
+        }
+      }
+    }
+  return gpa_set_topology(ctx, n, W.data(), nl.data());
+}
+
+int gpa_get_topology(gpa_ctx *ctx, int *n, int32_t *W, uint8_t *nlinks, int cap) {
+  if (!ctx || !n) return GPA_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  if (!ctx->has_topo) return GPA_ERR_NO_TOPOLOGY;
+  *n = ctx->topo.n;
+  int need = ctx->topo.n * ctx->topo.n;
+  if ((W || nlinks) && cap < need) return GPA_ERR_BUFFER;
+  if (W) memcpy(W, ctx->topo.W.data(), sizeof(int32_t) * (size_t)need);
+  if (nlinks) memcpy(nlinks, ctx->topo.nlinks.data(), (size_t)need);
+  return GPA_OK;
+}
+
+int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_t *req, int n_req, int size,
+                   int mode_flags, int32_t *out, int *n_out) {
+  if (!ctx || !n_out || n_avail < 0 || n_req < 0 || (n_avail > 0 && !avail) || (n_req > 0 && !req)) return GPA_ERR_INVALID;
+  *n_out = 0;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  if (!ctx->has_topo) return GPA_ERR_NO_TOPOLOGY;
+  const Topology &T = ctx->topo;
+  memset(&ctx->stats, 0, sizeof ctx->stats);
+  ctx->stats.best_score = -1;
+  ctx->stats.score_unit = T.unit;
+
+  // argument hygiene (the Go seam takes pointers, which cannot be out of range)
+  unsigned long long seen = 0;
+  for (int i = 0; i < n_avail; i++) {
+    if (avail[i] < 0 || avail[i] >= T.n) return GPA_ERR_INVALID;
+    if (seen >> avail[i] & 1ull) return GPA_ERR_INVALID;  // the same pointer twice: outside the reference's domain
+    seen |= 1ull << avail[i];
+  }
+  bool foreign = false;
+  unsigned long long rseen = 0;
+  for (int i = 0; i < n_req; i++) {
+    if (req[i] == GPA_FOREIGN) {
+      foreign = true;
+      continue;
+    }
+    if (req[i] < 0 || req[i] >= T.n) return GPA_ERR_INVALID;
+    if (rseen >> req[i] & 1ull) return GPA_ERR_INVALID;
+    rseen |= 1ull << req[i];
+    if (!(seen >> req[i] & 1ull)) foreign = true;  // required but not available: contained in no set
+  }
+
+  // besteffort_policy.go:35-45
+  if (size <= 0) return GPA_OK;
+  if (n_avail < size) return GPA_OK;
+  if (n_req > size) return GPA_OK;
+  if (n_avail > GPA_MAX_AVAILABLE) return GPA_ERR_TOO_LARGE;
+  if (!out) return GPA_ERR_INVALID;
+  // a required pointer that is in no candidate set: the filter at :53 rejects everything
+  if (foreign) return GPA_OK;
+
+  uint32_t rmask = 0;
+  for (int i = 0; i < n_req; i++)
+    for (int p = 0; p < n_avail; p++)
+      if (avail[p] == req[i]) rmask |= 1u << p;
+
+  if (size == 1) {
+    // :219-224 — one single-device candidate per device, in order; all score 0, so the first accepted one stays
+    int p = 0;
+    if (rmask) p = __builtin_ctz(rmask);
+    out[0] = avail[p];
+    *n_out = 1;
+    return GPA_OK;
+  }
+
+  // where calculateGPUPairScore panics (:307-310); see DESIGN.md for the (conservative) scope of this check
+  for (int a = 0; a < n_avail; a++)
+    for (int b = 0; b < n_avail; b++)
+      if (a != b && T.asym[avail[a] * T.n + avail[b]]) return GPA_ERR_ASYMMETRIC;
+
+  SearchParams sp;
+  memset(&sp, 0, sizeof sp);
+  sp.g = make_geom(n_avail, size, rmask);
+  sp.intended = (mode_flags & GPA_MODE_INTENDED) ? 1 : 0;
+  for (int a = 0; a < n_avail; a++)
+    for (int b = a + 1; b < n_avail; b++) sp.wp[a * kMaxDevices + b] = T.wq[avail[a] * T.n + avail[b]];
+  const uint64_t parts = partition_count(sp.g, ctx->binom);
+  if (parts > GPA_MAX_PARTITIONS) return GPA_ERR_TOO_LARGE;
+
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  size_t smem = ((size_t)1 << n_avail) * sizeof(uint16_t);
+  if (smem < 64) smem = 64;
+  if ((int)smem > ctx->max_smem_optin - 2048) return GPA_ERR_TOO_LARGE;
+  const bool large = smem > 32 * 1024;
+  const int block = large ? kSearchBlockLarge : kSearchBlockSmall;
+  auto kern = large ? besteffort_search_kernel<kSearchBlockLarge> : besteffort_search_kernel<kSearchBlockSmall>;
+  if (large) CUDA_TRY(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 1;
+  CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, block, smem));
+  if (occ < 1) occ = 1;
+  const uint64_t resident_threads = (uint64_t)ctx->sm_count * occ * block;
+  sp.cut = choose_cut(sp.g, ctx->binom, resident_threads * 4);
+  uint64_t blocks = (sp.cut.n_items + block - 1) / block;
+  uint64_t cap = (uint64_t)ctx->sm_count * occ;
+  int grid = (int)(blocks < cap ? blocks : cap);
+  if (grid < 1) grid = 1;
+
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  kern<<<grid, block, smem, ctx->stream>>>(sp, ctx->d_key, ctx->d_ticket, ctx->d_res);
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_res, ctx->d_res, sizeof(SearchResult), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+
+  ctx->stats.partitions = parts;
+  ctx->stats.items = sp.cut.n_items;
+  ctx->stats.cut_depth = sp.cut.d;
+  ctx->stats.sets = sp.g.m;
+  ctx->stats.padding = sp.g.P;
+  ctx->stats.best_score = ctx->h_res->best_score;
+  ctx->stats.grid = grid;
+  ctx->stats.block = block;
+  ctx->stats.smem_bytes = (int)smem;
+  ctx->stats.kernel_ms = ms;
+
+  const SearchResult &r = *ctx->h_res;
+  if (r.count < 0) {
+    ctx->last_error = "search epilogue could not replay the winning item";
+    return GPA_ERR_CUDA;
+  }
+  for (int i = 0; i < r.count; i++) out[i] = r.pos[i] < 0 ? GPA_NIL : avail[r.pos[i]];
+  *n_out = r.count;
+  return GPA_OK;
+}
+
+int gpa_last_search_stats(gpa_ctx *ctx, gpa_search_stats *out) {
+  if (!ctx || !out) return GPA_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  *out = ctx->stats;
+  return GPA_OK;
+}
+
+int gpa_besteffort_batch_device(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_avail, int mode_flags,
+                                gpa_result *d_out, void *stream) {
+  if (!ctx || count < 0 || (count > 0 && (!d_reqs || !d_out))) return GPA_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  if (!ctx->has_topo) return GPA_ERR_NO_TOPOLOGY;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  return launch_batch(ctx, d_reqs, count, max_avail, mode_flags, d_out, stream ? (cudaStream_t)stream : ctx->stream);
+}
+
+int gpa_besteffort_batch(gpa_ctx *ctx, const gpa_request *reqs, int count, int mode_flags, gpa_result *out) {
+  if (!ctx || count < 0 || (count > 0 && (!reqs || !out))) return GPA_ERR_INVALID;
+  if (count == 0) return GPA_OK;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  if (!ctx->has_topo) return GPA_ERR_NO_TOPOLOGY;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  // Pinned caller buffers (cudaMallocHost / cudaHostRegister) are DMA'd directly; pageable
+  // ones are staged through the context's pinned mailbox so that both copies stay async.
+  cudaPointerAttributes pa_in{}, pa_out{};
+  bool pinned = cudaPointerGetAttributes(&pa_in, reqs) == cudaSuccess && pa_in.type == cudaMemoryTypeHost &&
+                cudaPointerGetAttributes(&pa_out, out) == cudaSuccess && pa_out.type == cudaMemoryTypeHost;
+  cudaGetLastError();  // a pageable pointer may leave a sticky-free error behind on old drivers
+  int rc = ensure_batch_capacity(ctx, (size_t)count, !pinned);
+  if (rc != GPA_OK) return rc;
+  int max_avail = 0;
+  for (int i = 0; i < count; i++) {
+    int na = reqs[i].n_avail;
+    if (!pinned) ctx->h_reqs[i] = reqs[i];
+    if (na > max_avail && na <= GPA_BATCH_MAX_AVAILABLE) max_avail = na;
+  }
+  const gpa_request *src = pinned ? reqs : ctx->h_reqs;
+  gpa_result *dst = pinned ? out : ctx->h_out;
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->d_reqs, src, (size_t)count * sizeof(gpa_request), cudaMemcpyHostToDevice, ctx->stream));
+  rc = launch_batch(ctx, ctx->d_reqs, count, max_avail, mode_flags, ctx->d_out, ctx->stream);
+  if (rc != GPA_OK) return rc;
+  CUDA_TRY(ctx, cudaMemcpyAsync(dst, ctx->d_out, (size_t)count * sizeof(gpa_result), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (!pinned) memcpy(out, ctx->h_out, (size_t)count * sizeof(gpa_result));
+  return GPA_OK;
+}
+
+/* pinned host memory for batch buffers (so gpa_besteffort_batch can skip its staging copy) */
+void *gpa_alloc_host(size_t bytes) {
+  void *p = nullptr;
+  if (cudaMallocHost(&p, bytes) != cudaSuccess) return nullptr;
+  return p;
+}
+void gpa_free_host(void *p) {
+  if (p) cudaFreeHost(p);
+}
+
+}  // extern "C"

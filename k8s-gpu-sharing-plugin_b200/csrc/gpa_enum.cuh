@@ -430,7 +430,7 @@ GPA_HD int finalize(const Geom &g, const Cut &cut, const BinomTable &B, const ST
 
 // Number of candidate partitions the reference visits (closed form of SURVEY.md §8a A3):
 // P = 0: n!/((k!)^m m!);  P > 0: C(n, k-P) * ((m-1)k)!/((k!)^(m-1) (m-1)!).
-inline uint64_t partition_count(const Geom &g, const BinomTable &B) {
+GPA_HD uint64_t partition_count(const Geom &g, const BinomTable &B) {
   uint64_t full = 1;
   int mm = g.P == 0 ? g.m : g.m - 1;
   for (int r = mm * g.k; r > 0; r -= g.k) full *= binom_at(B, r - 1, g.k - 1);
@@ -443,7 +443,7 @@ inline uint64_t partition_count(const Geom &g, const BinomTable &B) {
 // the LITERAL item count (which includes the children the padding filter drops) dwarfs the
 // number of real partitions: with many pads (k close to n) almost every literal child is
 // dropped, and the stepper inside one item skips them for free.
-inline Cut choose_cut(const Geom &g, const BinomTable &B, uint64_t want_items) {
+GPA_HD Cut choose_cut(const Geom &g, const BinomTable &B, uint64_t want_items) {
   Cut c;
   c.d = 0;
   c.n_items = 1;

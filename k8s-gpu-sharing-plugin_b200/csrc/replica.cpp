@@ -1,0 +1,215 @@
+// Replica-id helpers and the replica-aware prioritiser, host C++ behind the C ABI.
+//
+// ref: cmd/nvidia-device-plugin/replica.go (stripReplica :28, stripReplicas :32,
+// devCount :62-84, prioritizeDevices :96-198) and getAdditionalXids,
+// cmd/nvidia-device-plugin/nvidia.go:274-294.  These are string-keyed O(size x #GPUs)
+// procedures with no parallel work, so they stay on the host; what
+// changes against the Go code is the data layout: ids are string_views into the caller's
+// buffers, physical GPUs live in one sorted vector, each group is an index window.
+#include <algorithm>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <string_view>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/gpualloc.h"
+
+namespace {
+
+constexpr std::string_view kJoin = "-replica-";  // replica.go:26
+
+// everything before the first "-replica-" (strings.Split(id, joinStr)[0], replica.go:28-30)
+std::string_view physical_of(std::string_view id) {
+  size_t p = id.find(kJoin);
+  return p == std::string_view::npos ? id : id.substr(0, p);
+}
+
+int pack_out(const std::vector<std::string_view> &v, char *outbuf, int outbuf_len, int *n_out) {
+  size_t need = 0;
+  for (auto s : v) need += s.size() + 1;
+  if ((long long)need > (long long)outbuf_len) return GPA_ERR_BUFFER;
+  char *w = outbuf;
+  for (auto s : v) {
+    memcpy(w, s.data(), s.size());
+    w[s.size()] = 0;
+    w += s.size() + 1;
+  }
+  *n_out = (int)v.size();
+  return GPA_OK;
+}
+
+struct Group {
+  std::string_view phys;
+  std::vector<std::string_view> names;  // free replicas; [head, names.size()) is the live window
+  size_t head = 0;
+  bool allocated = false;
+  size_t free_count() const { return names.size() - head; }
+};
+
+}  // namespace
+
+extern "C" {
+
+int gpa_strip_replicas(const char *const *ids, int n, char *outbuf, int outbuf_len, int *n_out) {
+  if (n < 0 || (n > 0 && !ids) || !n_out || (!outbuf && outbuf_len > 0)) return GPA_ERR_INVALID;
+  std::vector<std::string_view> uniq;
+  uniq.reserve((size_t)n);
+  for (int i = 0; i < n; i++) uniq.push_back(physical_of(ids[i]));
+  // dedupe + sort.Strings (replica.go:38-43): the first-seen order is erased by the sort
+  std::sort(uniq.begin(), uniq.end());
+  uniq.erase(std::unique(uniq.begin(), uniq.end()), uniq.end());
+  return pack_out(uniq, outbuf, outbuf_len, n_out);
+}
+
+int gpa_prioritize_devices(const char *const *avail, int n_avail, const char *const *must, int n_must, int size,
+                           char *outbuf, int outbuf_len, int *n_out, int *non_unique, char *errbuf, int errbuf_len) {
+  if (n_avail < 0 || n_must < 0 || (n_avail > 0 && !avail) || (n_must > 0 && !must) || !n_out) return GPA_ERR_INVALID;
+  *n_out = 0;
+  if (non_unique) *non_unique = 0;
+  if (errbuf && errbuf_len > 0) errbuf[0] = 0;
+
+  // replica.go:98-117 — group the replica ids by physical GPU, each group sorted byte-wise
+  std::vector<Group> groups;
+  std::unordered_map<std::string_view, size_t> index;
+  index.reserve((size_t)n_avail * 2 + 1);
+  for (int i = 0; i < n_avail; i++) {
+    std::string_view id = avail[i];
+    std::string_view phys = physical_of(id);
+    auto it = index.find(phys);
+    if (it == index.end()) {
+      it = index.emplace(phys, groups.size()).first;
+      groups.emplace_back();
+      groups.back().phys = phys;
+    }
+    groups[it->second].names.push_back(id);
+  }
+  for (auto &g : groups) std::sort(g.names.begin(), g.names.end());
+
+  // replica.go:121 — make([]string, len(must), allocationSize)
+  if (size < 0 || n_must > size) return GPA_ERR_PANIC;
+
+  std::vector<std::string_view> allocated;
+  allocated.reserve((size_t)size);
+  bool unique = true;
+
+  // replica.go:126-139 — must-includes; removal swaps the last free replica into the hole (:56-60)
+  for (int i = 0; i < n_must; i++) {
+    std::string_view id = must[i];
+    auto it = index.find(physical_of(id));
+    Group *g = it == index.end() ? nullptr : &groups[it->second];
+    size_t at = 0;
+    bool found = false;
+    if (g) {
+      for (at = g->head; at < g->names.size(); at++)
+        if (g->names[at] == id) {
+          found = true;
+          break;
+        }
+    }
+    if (g && g->allocated) unique = false;  // :131-134 is evaluated before the replica lookup fails (:135)
+    if (!found) {
+      if (errbuf && errbuf_len > 0) snprintf(errbuf, (size_t)errbuf_len, "%.*s", (int)id.size(), id.data());
+      return GPA_ERR_MUST_MISSING;
+    }
+    g->names[at] = g->names.back();
+    g->names.pop_back();
+    g->allocated = true;
+    allocated.push_back(id);
+  }
+
+  // replica.go:143-147 — physical ids in byte-wise order decide ties
+  std::vector<Group *> order;
+  order.reserve(groups.size());
+  for (auto &g : groups) order.push_back(&g);
+  std::sort(order.begin(), order.end(), [](const Group *a, const Group *b) { return a->phys < b->phys; });
+
+  // replica.go:149-190 — prefer an untouched GPU with the most free replicas, else a touched one
+  for (int i = (int)allocated.size(); i < size; i++) {
+    Group *fresh = nullptr, *used = nullptr;
+    size_t fresh_best = 0, used_best = 0;
+    for (Group *g : order) {
+      size_t c = g->free_count();
+      if (g->allocated) {
+        if (c > used_best) {
+          used = g;
+          used_best = c;
+        }
+      } else if (c > fresh_best) {
+        fresh = g;
+        fresh_best = c;
+      }
+    }
+    Group *pick = fresh ? fresh : used;
+    if (!pick) return GPA_ERR_NO_DEVICES_LEFT;
+    if (pick->allocated) unique = false;
+    allocated.push_back(pick->names[pick->head++]);  // allocateAny(): the group's first free replica (:79-84)
+    pick->allocated = true;
+  }
+  std::sort(allocated.begin(), allocated.end());  // :191
+  int rc = pack_out(allocated, outbuf, outbuf_len, n_out);
+  if (rc != GPA_OK) return rc;
+  if (non_unique) *non_unique = unique ? 0 : 1;  // :193-197 &NonUniqueError{}
+  return GPA_OK;
+}
+
+int gpa_get_additional_xids(const char *input, uint64_t *out, int out_cap) {
+  if (!input || (!out && out_cap > 0)) return GPA_ERR_INVALID;
+  std::string_view s = input;
+  if (s.empty()) return 0;  // nvidia.go:275-277
+  auto is_space = [](std::string_view v, size_t i, bool from_end, size_t *w) {
+    // strings.TrimSpace: ASCII white space plus the two Latin-1 spaces U+0085 / U+00A0
+    unsigned char c = (unsigned char)v[i];
+    *w = 1;
+    if (c == ' ' || (c >= '\t' && c <= '\r')) return true;
+    if (!from_end && c == 0xC2 && i + 1 < v.size()) {
+      unsigned char d = (unsigned char)v[i + 1];
+      if (d == 0x85 || d == 0xA0) {
+        *w = 2;
+        return true;
+      }
+    }
+    if (from_end && (c == 0x85 || c == 0xA0) && i >= 1 && (unsigned char)v[i - 1] == 0xC2) {
+      *w = 2;
+      return true;
+    }
+    return false;
+  };
+  int n = 0;
+  size_t pos = 0;
+  for (;;) {
+    size_t comma = s.find(',', pos);
+    std::string_view tok = s.substr(pos, comma == std::string_view::npos ? std::string_view::npos : comma - pos);
+    size_t w;
+    while (!tok.empty() && is_space(tok, 0, false, &w)) tok.remove_prefix(w);
+    while (!tok.empty() && is_space(tok, tok.size() - 1, true, &w)) tok.remove_suffix(w);
+    if (!tok.empty()) {
+      // strconv.ParseUint(tok, 10, 64): decimal digits only, no sign, no underscore, <= 2^64-1
+      bool ok = true;
+      uint64_t v = 0;
+      for (char ch : tok) {
+        if (ch < '0' || ch > '9') {
+          ok = false;
+          break;
+        }
+        uint64_t d = (uint64_t)(ch - '0');
+        if (v > (UINT64_MAX - d) / 10) {
+          ok = false;
+          break;
+        }
+        v = v * 10 + d;
+      }
+      if (ok) {
+        if (n >= out_cap) return GPA_ERR_BUFFER;
+        out[n++] = v;
+      }
+    }
+    if (comma == std::string_view::npos) break;
+    pos = comma + 1;
+  }
+  return n;
+}
+
+}  // extern "C"

@@ -164,7 +164,7 @@ def exhaustive_requests(order, seed=0, n_pairs=8):
 # Packed batch format of gpa_besteffort_batch (include/gpualloc.h): one 32-byte record per
 # container request.
 REQ_DTYPE = np.dtype([("avail", np.uint8, 16), ("req_mask", np.uint16), ("n_avail", np.uint8), ("size", np.uint8),
-                      ("flags", np.uint8), ("pad", np.uint8, 11)])
+                      ("flags", np.uint8), ("n_req_extra", np.uint8), ("reserved", np.uint8, 10)])
 assert REQ_DTYPE.itemsize == 32
 RES_DTYPE = np.dtype([("dev", np.int8, 16)])
 FLAG_REQ_FOREIGN = 1  # some required device is not one of the available pointers (D4)
@@ -178,32 +178,36 @@ def pack_requests(reqs):
         out["avail"][i, :len(avail)] = avail
         out["n_avail"][i] = len(avail)
         out["size"][i] = size
-        m, fl = 0, 0
+        m, fl, extra = 0, 0, 0
         for d in req:
             if d in avail:
                 m |= 1 << list(avail).index(d)
             else:
                 fl |= FLAG_REQ_FOREIGN
-        if len(set(req)) != len(req):
+                extra += 1
+        if len(set(x for x in req if x >= 0)) != len([x for x in req if x >= 0]):
             raise ValueError("duplicate required device")
         out["req_mask"][i] = m
         out["flags"][i] = fl
+        out["n_req_extra"][i] = extra
     return out
 
 
 def random_request_batch(n_dev, count, seed, order=None, p_required=0.25):
-    """Seeded stream of best-effort container requests on an n_dev-GPU node, built with
-    vectorised numpy so that millions of requests take seconds: availability mask uniform
-    over non-empty masks, size uniform in 1..|avail|, with probability p_required one
-    required device drawn from the available ones."""
+    """Seeded i.i.d. stream of best-effort container requests on an n_dev-GPU node, built
+    with vectorised numpy so that millions of requests take seconds.  Number of free GPUs
+    uniform in 1..n_dev, which ones uniform among the subsets of that size (kept in
+    allocator order), allocation size uniform in 1..|free|, and with probability p_required
+    one required device drawn from the free ones."""
     rng = np.random.default_rng(seed)
     order = np.arange(n_dev, dtype=np.uint8) if order is None else np.asarray(order, dtype=np.uint8)
-    masks = rng.integers(1, 1 << n_dev, size=count, dtype=np.int64)
-    bits = (masks[:, None] >> np.arange(n_dev)[None, :]) & 1          # [count, n_dev] by position
-    n_avail = bits.sum(1)
-    # stable compaction of the available positions to the front, keeping allocator order
-    key = np.where(bits == 1, np.arange(n_dev)[None, :], n_dev + np.arange(n_dev)[None, :])
-    pos = np.argsort(key, axis=1, kind="stable")
+    n_avail = rng.integers(1, n_dev + 1, size=count)
+    # random subset of size n_avail: the n_avail smallest of n_dev random keys, then sorted by position
+    keys = rng.random((count, n_dev))
+    rank = np.argsort(np.argsort(keys, axis=1), axis=1)              # rank of each position's key
+    free = rank < n_avail[:, None]                                    # [count, n_dev] by position
+    sel = np.where(free, np.arange(n_dev)[None, :], n_dev + np.arange(n_dev)[None, :])
+    pos = np.argsort(sel, axis=1, kind="stable")                      # free positions first, ascending
     out = np.zeros(count, dtype=REQ_DTYPE)
     av = order[pos]
     av[np.arange(n_dev)[None, :] >= n_avail[:, None]] = 0
@@ -222,5 +226,5 @@ def unpack_request(rec):
     avail = [int(x) for x in rec["avail"][:n]]
     req = [avail[p] for p in range(n) if int(rec["req_mask"]) >> p & 1]
     if int(rec["flags"]) & FLAG_REQ_FOREIGN:
-        req = req + [-2]
+        req = req + [-2] * max(int(rec["n_req_extra"]), 1)
     return avail, req, int(rec["size"])

@@ -23,7 +23,7 @@ ERR_KIND_NAMES = {0: "none", 1: "non_unique", 2: "no_devices_left", 3: "must_mis
 
 
 def build(force=False):
-    srcs = [os.path.join(HERE, f) for f in ("ref_besteffort.c", "ref_replica.c")]
+    srcs = [os.path.join(HERE, f) for f in ("ref_besteffort.c", "ref_replica.c", "ref_batch.c")]
     if force or not os.path.exists(LIB) or any(os.path.getmtime(s) > os.path.getmtime(LIB) for s in srcs):
         subprocess.check_call(["make", "-C", HERE, "-s", "-B", "liboracle.so"])
     return LIB
@@ -56,6 +56,8 @@ def lib():
         L.ref_prioritize_devices.restype = C.c_int
         L.ref_prioritize_devices.argtypes = [C.POINTER(C.c_char_p), C.c_int, C.POINTER(C.c_char_p), C.c_int, C.c_int,
                                              C.c_char_p, C.c_int, C.POINTER(C.c_int), C.c_char_p, C.c_int]
+        L.ref_besteffort_batch.restype = C.c_ulonglong
+        L.ref_besteffort_batch.argtypes = [C.c_int, i32p, u8p, C.c_void_p, C.c_longlong, C.c_int, C.c_void_p, C.c_int]
         L.ref_get_additional_xids.restype = C.c_int
         L.ref_get_additional_xids.argtypes = [C.c_char_p, C.POINTER(C.c_uint64), C.c_int]
         _lib = L
@@ -144,3 +146,17 @@ def get_additional_xids(s):
     out = (C.c_uint64 * 256)()
     n = lib().ref_get_additional_xids(s.encode() if isinstance(s, str) else s, out, 256)
     return [int(out[i]) for i in range(n)]
+
+
+def besteffort_batch(W, nlinks, reqs, mode=GO_FAITHFUL, threads=1, out=None):
+    """packed gpa_request records (numpy, 32 B each) -> packed results (16 B each), visited"""
+    W = np.ascontiguousarray(W, dtype=np.int32)
+    nl = np.ascontiguousarray(nlinks, dtype=np.uint8)
+    reqs = np.ascontiguousarray(reqs)
+    assert reqs.dtype.itemsize == 32
+    if out is None:
+        out = np.zeros(len(reqs), dtype=np.dtype([("dev", np.int8, 16)]))
+    visited = lib().ref_besteffort_batch(W.shape[0], W.ctypes.data_as(C.POINTER(C.c_int32)),
+                                         nl.ctypes.data_as(C.POINTER(C.c_uint8)), reqs.ctypes.data, len(reqs), int(mode),
+                                         out.ctypes.data, int(threads))
+    return out, int(visited)

@@ -1,0 +1,256 @@
+"""Parity of the CUDA best-effort path with the oracle, through the C ABI (ctypes).
+
+Bit-exact on every request: integer/index work, no tolerance.  Nothing here reads
+/root/reference; inputs are seeded synthetic topologies."""
+import numpy as np
+import pytest
+
+from k8s_gpu_sharing_plugin_b200 import _lib as gpa
+from k8s_gpu_sharing_plugin_b200 import synthetic as syn
+
+pytestmark = pytest.mark.gpu
+
+ORDER8 = syn.sorted_positions(syn.node_uuids(8, seed=1))
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = gpa.Context(0)
+    yield c
+    c.close()
+
+
+def install(ctx, links2):
+    W, nl = syn.links_to_weights(links2)
+    ctx.set_topology_links(links2)
+    W2, nl2 = ctx.get_topology()
+    assert (W2 == W).all() and (nl2 == nl).all()  # the ABI's score switch == the numpy statement of it
+    return W, nl
+
+
+def oracle_batch(oracle, W, nl, reqs, mode):
+    out, _ = oracle.besteffort_batch(W, nl, reqs, mode=mode, threads=8)
+    return out
+
+
+def assert_batch_equal(got, want, reqs, what):
+    bad = np.nonzero((got["dev"] != want["dev"]).any(axis=1))[0]
+    if len(bad):
+        i = int(bad[0])
+        raise AssertionError("%s: %d mismatches; first at %d: request %r got %r want %r" % (
+            what, len(bad), i, syn.unpack_request(reqs[i]), got["dev"][i].tolist(), want["dev"][i].tolist()))
+
+
+@pytest.mark.parametrize("topo_i", range(14))
+def test_batch_exhaustive_n8_all_masks_all_sizes(ctx, oracle, topo_i):
+    """config 1: every non-empty mask x k = 1..|mask| x required in {none, each single, seeded pairs}"""
+    name, t = syn.standard_topologies()[topo_i]
+    W, nl = install(ctx, t)
+    reqs = syn.pack_requests(list(syn.exhaustive_requests(ORDER8, seed=topo_i, n_pairs=8)))
+    assert len(reqs) > 9000
+    for mode in (gpa.MODE_GO_FAITHFUL, gpa.MODE_INTENDED):
+        got = ctx.besteffort_batch(reqs, mode)
+        assert_batch_equal(got, oracle_batch(oracle, W, nl, reqs, mode), reqs, name)
+
+
+def test_single_request_api_matches_batch_and_oracle_n8(ctx, oracle):
+    name, t = syn.standard_topologies()[3]
+    W, nl = install(ctx, t)
+    rng = np.random.default_rng(5)
+    all_reqs = list(syn.exhaustive_requests(ORDER8, seed=3, n_pairs=2))
+    for i in rng.choice(len(all_reqs), 400, replace=False):
+        avail, req, k = all_reqs[int(i)]
+        want = oracle.besteffort(W, nl, avail, req, k)
+        assert ctx.besteffort(avail, req, k) == (gpa.OK, want[1]), (avail, req, k)
+
+
+def test_guards_and_trivial_answers(ctx, oracle):
+    W, nl = install(ctx, syn.topo_zero(8))
+    av = [3, 1, 4, 0, 5]
+    assert ctx.besteffort(av, [], 0) == (gpa.OK, [])           # size <= 0
+    assert ctx.besteffort(av, [], -3) == (gpa.OK, [])
+    assert ctx.besteffort(av, [], 6) == (gpa.OK, [])           # len(available) < size
+    assert ctx.besteffort(av, [3, 1, 4], 2) == (gpa.OK, [])    # len(required) > size
+    for k in range(1, 6):
+        assert ctx.besteffort(av, [], k) == (gpa.OK, av[:k])   # all-zero W: first k devices
+    assert ctx.besteffort(av, [0], 1) == (gpa.OK, [0])         # size 1: the required device
+    assert ctx.besteffort([], [], 1) == (gpa.OK, [])
+    assert ctx.besteffort(av, [gpa.FOREIGN], 2) == (gpa.OK, [])  # D4: a pointer that is in no set
+    assert ctx.besteffort(av, [7], 2) == (gpa.OK, [])          # required but not available
+    assert ctx.besteffort([0, 0, 1], [], 2)[0] == gpa.ERR_INVALID
+    assert ctx.besteffort([0, 9], [], 2)[0] == gpa.ERR_INVALID
+    # the same through the packed batch format
+    reqs = syn.pack_requests([(av, [], 0), (av, [], 6), (av, [3, 1, 4], 2), (av, [], 3), (av, [0], 1), (av, [-2], 2),
+                              (av, [7], 2), ([2], [], 1), (av, [5, 4], 2)])
+    got = ctx.besteffort_batch(reqs)
+    want = oracle_batch(oracle, W, nl, reqs, 0)
+    assert_batch_equal(got, want, reqs, "guards")
+    assert gpa.decode_result(got[3]) == (gpa.OK, [3, 1, 4]) and gpa.decode_result(got[8]) == (gpa.OK, [4, 5])
+
+
+def test_nil_pad_vector_D5(ctx, oracle):
+    t = syn.topo_uniform(5)
+    for i, j in ((2, 3), (2, 4), (3, 4)):
+        t[i, j, 0] = t[j, i, 0] = 5
+    t[0, 1] = t[1, 0] = (5, syn.nvlink_type(1))
+    W, nl = install(ctx, t)
+    assert ctx.besteffort([0, 1, 2, 3, 4], [], 3) == (gpa.OK, [0, 1, gpa.NIL])
+    got = ctx.besteffort_batch(syn.pack_requests([([0, 1, 2, 3, 4], [], 3)]))
+    assert gpa.decode_result(got[0]) == (gpa.OK, [0, 1, gpa.NIL])
+
+
+def test_asymmetric_link_counts_are_reported_where_go_panics(ctx, oracle):
+    W, nl = syn.links_to_weights(syn.topo_uniform(4))
+    nl = nl.copy()
+    nl[0, 1] = 2
+    ctx.set_topology(W, nl)
+    assert ctx.besteffort([0, 1, 2, 3], [], 2)[0] == gpa.ERR_ASYMMETRIC
+    assert ctx.besteffort([0, 1, 2, 3], [], 1) == (gpa.OK, [0])   # size 1 scores no pair
+    assert ctx.besteffort([2, 3], [], 2) == (gpa.OK, [2, 3])
+    reqs = syn.pack_requests([([0, 1, 2, 3], [], 2), ([0, 1, 2, 3], [], 1), ([2, 3], [], 2)])
+    got = ctx.besteffort_batch(reqs)
+    assert_batch_equal(got, oracle_batch(oracle, W, nl, reqs, 0), reqs, "asym")
+    assert gpa.decode_result(got[0])[0] == gpa.ERR_ASYMMETRIC
+
+
+def test_asymmetric_weights_use_the_earlier_devices_view(ctx, oracle):
+    W = np.zeros((3, 3), dtype=np.int32)
+    nl = np.ones((3, 3), dtype=np.uint8)
+    W[0, 1], W[1, 0] = 10, 500
+    W[0, 2], W[2, 0] = 100, 100
+    ctx.set_topology(W, nl)
+    assert ctx.besteffort([0, 1, 2], [], 2) == (gpa.OK, [0, 2])
+    assert ctx.besteffort([1, 0, 2], [], 2) == (gpa.OK, [1, 0])
+
+
+def test_weight_range_is_checked(ctx):
+    W = np.zeros((4, 4), dtype=np.int32)
+    nl = np.ones((4, 4), dtype=np.uint8)
+    W[0, 1] = W[1, 0] = 1 << 20
+    W[2, 3] = W[3, 2] = 7
+    with pytest.raises(gpa.GpaError) as e:
+        ctx.set_topology(W, nl)
+    assert e.value.code == gpa.ERR_WEIGHT_RANGE
+    W[0, 1] = W[1, 0] = -5
+    with pytest.raises(gpa.GpaError):
+        ctx.set_topology(W, nl)
+
+
+@pytest.mark.parametrize("n,k", [(9, 2), (9, 4), (10, 3), (10, 4), (11, 2), (11, 3), (11, 5), (12, 3), (12, 5), (12, 7),
+                                 (12, 11), (13, 2), (13, 3), (13, 6), (14, 2), (14, 4), (14, 5), (15, 2), (15, 4),
+                                 (16, 2), (16, 4), (16, 5), (16, 6), (16, 7), (16, 8), (16, 9), (16, 13), (16, 16)])
+def test_single_search_seeded_large(ctx, oracle, n, k):
+    """config 3b: synthetic n = 9..16 physical devices, both alias modes, with and without required devices"""
+    for seed in range(2):
+        W, nl = install(ctx, syn.topo_random(n, 300 + seed))
+        rng = np.random.default_rng(seed)
+        avail = [int(x) for x in rng.permutation(n)]
+        reqs = [[], [avail[int(rng.integers(n))]]]
+        if k >= 3:
+            reqs.append([avail[int(x)] for x in rng.choice(n, 2, replace=False)])
+        for req in reqs:
+            for mode in (gpa.MODE_GO_FAITHFUL, gpa.MODE_INTENDED):
+                want = oracle.besteffort(W, nl, avail, req, k, mode, "fast")
+                got = ctx.besteffort(avail, req, k, mode)
+                assert got == (gpa.OK, want[1]), (n, k, seed, req, mode, ctx.search_stats())
+                st = ctx.search_stats()
+                assert st["partitions"] == oracle.partition_count(n, k)
+
+
+def test_full_size_n16_k3_matches_oracle(ctx, oracle):
+    """the largest search of BASELINE config 3b: 22 422 400 candidate partitions"""
+    W, nl = install(ctx, syn.topo_random(16, 77))
+    avail = list(range(16))
+    want = oracle.besteffort(W, nl, avail, [], 3, oracle.GO_FAITHFUL, "fast")
+    assert ctx.besteffort(avail, [], 3) == (gpa.OK, want[1])
+    st = ctx.search_stats()
+    assert st["partitions"] == 22422400 and st["sets"] == 6 and st["padding"] == 2
+
+
+@pytest.mark.parametrize("n", [13, 14, 15, 16])
+def test_slice_aliasing_D6(ctx, oracle, n):
+    """m = 7 / 8 sets: go_faithful must return what the aliased Go slices return, intended
+    must find the spiked pair"""
+    for seed in range(3):
+        W, nl = install(ctx, syn.topo_spiked(n, seed))
+        avail = list(range(n))
+        for mode in (gpa.MODE_GO_FAITHFUL, gpa.MODE_INTENDED):
+            want = oracle.besteffort(W, nl, avail, [], 2, mode, "fast")
+            assert ctx.besteffort(avail, [], 2, mode) == (gpa.OK, want[1]), (n, seed, mode)
+        assert ctx.besteffort(avail, [], 2, gpa.MODE_INTENDED)[1] == [n - 2, n - 1]
+
+
+def test_batch_n9_to_n12(ctx, oracle):
+    """the batch kernel up to GPA_BATCH_MAX_AVAILABLE devices per request"""
+    W, nl = install(ctx, syn.topo_random(12, 11))
+    reqs = syn.random_request_batch(12, 3000, seed=12)
+    for mode in (gpa.MODE_GO_FAITHFUL, gpa.MODE_INTENDED):
+        got = ctx.besteffort_batch(reqs, mode)
+        assert_batch_equal(got, oracle_batch(oracle, W, nl, reqs, mode), reqs, "n12")
+
+
+def test_batch_stream_scale_independent_properties(ctx, oracle):
+    """full bench-size batch (2^20 requests): (1) equals the oracle on a seeded sample,
+    (2) every answer is empty or `size` distinct available devices containing the required
+    one, (3) relabelling invariance: scaling all weights by a constant changes nothing,
+    (4) a second identical call gives identical bytes (no state leaks between launches)"""
+    W, nl = install(ctx, syn.topo_dgx1v_like())
+    reqs = syn.random_request_batch(8, 1 << 20, seed=2, order=ORDER8)
+    got = ctx.besteffort_batch(reqs)
+    idx = np.random.default_rng(0).choice(len(reqs), 50000, replace=False)
+    want = oracle_batch(oracle, W, nl, reqs[idx], 0)
+    assert_batch_equal(got[idx], want, reqs[idx], "sample")
+    dev = got["dev"].astype(np.int16)
+    n_out = (dev != gpa.RES_END).sum(axis=1)
+    assert ((n_out == 0) | (n_out == reqs["size"])).all()
+    assert (dev[:, 0] != gpa.RES_ERROR).all()
+    # each answer is a subset of the available devices and holds the required one
+    avail_bits = np.zeros(len(reqs), dtype=np.int64)
+    for p in range(8):
+        avail_bits |= np.where(p < reqs["n_avail"], 1 << reqs["avail"][:, p].astype(np.int64), 0)
+    ans_bits = np.zeros(len(reqs), dtype=np.int64)
+    for s in range(16):
+        d = dev[:, s]
+        ans_bits |= np.where(d >= 0, 1 << np.clip(d, 0, 62).astype(np.int64), 0)
+    assert ((ans_bits & ~avail_bits) == 0).all()
+    ctx.set_topology(W * 3, nl)
+    assert (ctx.besteffort_batch(reqs)["dev"] == got["dev"]).all()
+    ctx.set_topology(W, nl)
+    assert (ctx.besteffort_batch(reqs)["dev"] == got["dev"]).all()
+
+
+def test_device_resident_batch_on_a_torch_stream(ctx, oracle):
+    """gpa_besteffort_batch_device: inputs and outputs already in HBM, caller's stream"""
+    import torch
+    W, nl = install(ctx, syn.topo_two_sockets(8))
+    reqs = syn.random_request_batch(8, 100000, seed=7, order=ORDER8)
+    d_in = torch.from_numpy(reqs.view(np.uint8).reshape(-1, 32)).cuda()
+    d_out = torch.zeros((len(reqs), 16), dtype=torch.int8, device="cuda")
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        ctx.besteffort_batch_device(d_in.data_ptr(), len(reqs), 8, d_out.data_ptr(), stream=s.cuda_stream)
+    s.synchronize()
+    got = np.zeros(len(reqs), dtype=syn.RES_DTYPE)
+    got["dev"] = d_out.cpu().numpy()
+    assert_batch_equal(got, oracle_batch(oracle, W, nl, reqs, 0), reqs, "device-resident")
+
+
+def test_pinned_host_buffers(ctx, oracle):
+    W, nl = install(ctx, syn.topo_two_sockets(8))
+    reqs = syn.random_request_batch(8, 50000, seed=8, order=ORDER8)
+    pin_in = gpa.PinnedBuffer(len(reqs), syn.REQ_DTYPE)
+    pin_out = gpa.PinnedBuffer(len(reqs), syn.RES_DTYPE)
+    pin_in.array[:] = reqs
+    got = ctx.besteffort_batch(pin_in.array, out=pin_out.array)
+    assert_batch_equal(got, oracle_batch(oracle, W, nl, reqs, 0), reqs, "pinned")
+    pin_in.free()
+    pin_out.free()
+
+
+def test_launch_counter_counts_kernels(ctx):
+    install(ctx, syn.topo_two_sockets(8))
+    before = ctx.launch_count
+    ctx.besteffort(list(range(8)), [], 4)
+    ctx.besteffort_batch(syn.random_request_batch(8, 100, seed=1))
+    ctx.besteffort(list(range(8)), [], 1)  # answered by the guards: no kernel
+    assert ctx.launch_count == before + 2
