@@ -142,10 +142,14 @@ typedef struct gpa_result {
 #define GPA_RES_END (-128)  /* unused tail of gpa_result.dev; dev[0] == GPA_RES_END: empty answer */
 #define GPA_RES_ERROR (-127) /* dev[0] == GPA_RES_ERROR: dev[1] holds the GPA_ERR_* code of this request */
 
-/* host buffers: copies in, launches, copies out, synchronises */
-int gpa_besteffort_batch(gpa_ctx *ctx, const gpa_request *reqs, int count, int mode_flags, gpa_result *out);
-/* device buffers, asynchronous on `stream` (a cudaStream_t; NULL = the context's stream): inputs already resident
- * in HBM, nothing copied, nothing synchronised.  max_avail = largest n_avail in the batch (<= GPA_BATCH_MAX_AVAILABLE). */
+/* host buffers: copies in, launches, copies out (in overlapping chunks), synchronises.
+ * max_avail = largest n_avail in the batch, e.g. the node's GPU count (<= GPA_BATCH_MAX_AVAILABLE); 0 = unknown,
+ * the library scans the records for it.  A record with more than max_avail devices gets GPA_ERR_TOO_LARGE. */
+int gpa_besteffort_batch(gpa_ctx *ctx, const gpa_request *reqs, int count, int max_avail, int mode_flags,
+                         gpa_result *out);
+/* device buffers, asynchronous on `stream` (a cudaStream_t; NULL = the legacy default stream): inputs already
+ * resident in HBM, nothing copied, nothing synchronised.  The call only enqueues; it must not overlap with a
+ * gpa_set_topology*() on the same context. */
 int gpa_besteffort_batch_device(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_avail, int mode_flags,
                                 gpa_result *d_out, void *stream);
 #define GPA_BATCH_MAX_AVAILABLE 12 /* larger requests go through gpa_besteffort() one by one */

@@ -61,7 +61,7 @@ def lib():
     L.gpa_get_topology.argtypes = [vp, C.POINTER(C.c_int), i32p, u8p, C.c_int]
     L.gpa_besteffort.argtypes = [vp, i32p, C.c_int, i32p, C.c_int, C.c_int, C.c_int, i32p, C.POINTER(C.c_int)]
     L.gpa_last_search_stats.argtypes = [vp, C.POINTER(SearchStats)]
-    L.gpa_besteffort_batch.argtypes = [vp, vp, C.c_int, C.c_int, vp]
+    L.gpa_besteffort_batch.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp]
     L.gpa_besteffort_batch_device.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp]
     L.gpa_alloc_host.restype = vp
     L.gpa_alloc_host.argtypes = [C.c_size_t]
@@ -197,14 +197,15 @@ class Context:
         self._check(lib().gpa_last_search_stats(self._h, C.byref(st)))
         return {f: getattr(st, f) for f, _ in SearchStats._fields_}
 
-    def besteffort_batch(self, reqs, mode=MODE_GO_FAITHFUL, out=None):
+    def besteffort_batch(self, reqs, mode=MODE_GO_FAITHFUL, out=None, max_avail=0):
         """reqs: numpy array of synthetic.REQ_DTYPE (host memory) -> array of RES_DTYPE"""
         from . import synthetic as syn
         reqs = np.ascontiguousarray(reqs)
         assert reqs.dtype == syn.REQ_DTYPE
         if out is None:
             out = np.zeros(len(reqs), dtype=syn.RES_DTYPE)
-        self._check(lib().gpa_besteffort_batch(self._h, reqs.ctypes.data, len(reqs), int(mode), out.ctypes.data))
+        self._check(lib().gpa_besteffort_batch(self._h, reqs.ctypes.data, len(reqs), int(max_avail), int(mode),
+                                               out.ctypes.data))
         return out
 
     def besteffort_batch_device(self, d_reqs_ptr, count, max_avail, d_out_ptr, mode=MODE_GO_FAITHFUL, stream=None):

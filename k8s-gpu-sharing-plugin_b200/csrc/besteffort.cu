@@ -286,6 +286,7 @@ struct gpa_ctx {
   int sm_count = 0;
   int max_smem_optin = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t pipe[4] = {nullptr, nullptr, nullptr, nullptr};  // copy/compute pipeline of the host-buffer batch call
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   std::mutex mu;
   std::string last_error;
@@ -424,6 +425,7 @@ int gpa_create(int cuda_device, gpa_ctx **out) {
   CREATE_TRY(cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, cuda_device));
   CREATE_TRY(cudaDeviceGetAttribute(&ctx->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, cuda_device));
   CREATE_TRY(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  for (auto &ps : ctx->pipe) CREATE_TRY(cudaStreamCreateWithFlags(&ps, cudaStreamNonBlocking));
   CREATE_TRY(cudaEventCreate(&ctx->ev0));
   CREATE_TRY(cudaEventCreate(&ctx->ev1));
   CREATE_TRY(cudaMalloc(&ctx->d_key, sizeof(unsigned long long)));
@@ -456,6 +458,8 @@ void gpa_destroy(gpa_ctx *ctx) {
   if (ctx->h_out) cudaFreeHost(ctx->h_out);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+  for (auto &ps : ctx->pipe)
+    if (ps) cudaStreamDestroy(ps);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -681,36 +685,52 @@ int gpa_besteffort_batch_device(gpa_ctx *ctx, const gpa_request *d_reqs, int cou
   std::lock_guard<std::mutex> lk(ctx->mu);
   if (!ctx->has_topo) return GPA_ERR_NO_TOPOLOGY;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-  return launch_batch(ctx, d_reqs, count, max_avail, mode_flags, d_out, stream ? (cudaStream_t)stream : ctx->stream);
+  return launch_batch(ctx, d_reqs, count, max_avail, mode_flags, d_out, (cudaStream_t)stream);
 }
 
-int gpa_besteffort_batch(gpa_ctx *ctx, const gpa_request *reqs, int count, int mode_flags, gpa_result *out) {
-  if (!ctx || count < 0 || (count > 0 && (!reqs || !out))) return GPA_ERR_INVALID;
+int gpa_besteffort_batch(gpa_ctx *ctx, const gpa_request *reqs, int count, int max_avail, int mode_flags, gpa_result *out) {
+  if (!ctx || count < 0 || max_avail < 0 || (count > 0 && (!reqs || !out))) return GPA_ERR_INVALID;
   if (count == 0) return GPA_OK;
   std::lock_guard<std::mutex> lk(ctx->mu);
   if (!ctx->has_topo) return GPA_ERR_NO_TOPOLOGY;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-  // Pinned caller buffers (cudaMallocHost / cudaHostRegister) are DMA'd directly; pageable
-  // ones are staged through the context's pinned mailbox so that both copies stay async.
+  // Pinned caller buffers (gpa_alloc_host / cudaHostRegister) are DMA'd directly; pageable
+  // ones are staged through the context's pinned mailbox so that every copy stays async.
   cudaPointerAttributes pa_in{}, pa_out{};
   bool pinned = cudaPointerGetAttributes(&pa_in, reqs) == cudaSuccess && pa_in.type == cudaMemoryTypeHost &&
                 cudaPointerGetAttributes(&pa_out, out) == cudaSuccess && pa_out.type == cudaMemoryTypeHost;
-  cudaGetLastError();  // a pageable pointer may leave a sticky-free error behind on old drivers
+  cudaGetLastError();
   int rc = ensure_batch_capacity(ctx, (size_t)count, !pinned);
   if (rc != GPA_OK) return rc;
-  int max_avail = 0;
-  for (int i = 0; i < count; i++) {
-    int na = reqs[i].n_avail;
-    if (!pinned) ctx->h_reqs[i] = reqs[i];
-    if (na > max_avail && na <= GPA_BATCH_MAX_AVAILABLE) max_avail = na;
+  if (max_avail == 0) {  // caller does not know: one pass over the records
+    for (int i = 0; i < count; i++) {
+      int na = reqs[i].n_avail;
+      if (na > max_avail && na <= GPA_BATCH_MAX_AVAILABLE) max_avail = na;
+    }
   }
+  if (!pinned) memcpy(ctx->h_reqs, reqs, (size_t)count * sizeof(gpa_request));
   const gpa_request *src = pinned ? reqs : ctx->h_reqs;
   gpa_result *dst = pinned ? out : ctx->h_out;
-  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->d_reqs, src, (size_t)count * sizeof(gpa_request), cudaMemcpyHostToDevice, ctx->stream));
-  rc = launch_batch(ctx, ctx->d_reqs, count, max_avail, mode_flags, ctx->d_out, ctx->stream);
+  // Chunks ride a ring of streams: while chunk i is in the kernel, chunk i+1 is on the H2D
+  // copy engine and chunk i-1 on the D2H one.
+  const int kChunk = 1 << 18;
+  int c = 0;
+  for (int off = 0; off < count; off += kChunk, c++) {
+    int cnt = count - off < kChunk ? count - off : kChunk;
+    cudaStream_t st = ctx->pipe[c & 3];
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->d_reqs + off, src + off, (size_t)cnt * sizeof(gpa_request), cudaMemcpyHostToDevice, st));
+    rc = launch_batch(ctx, ctx->d_reqs + off, cnt, max_avail, mode_flags, ctx->d_out + off, st);
+    if (rc != GPA_OK) break;
+    CUDA_TRY(ctx, cudaMemcpyAsync(dst + off, ctx->d_out + off, (size_t)cnt * sizeof(gpa_result), cudaMemcpyDeviceToHost, st));
+  }
+  for (auto &ps : ctx->pipe) {
+    cudaError_t e = cudaStreamSynchronize(ps);
+    if (e != cudaSuccess && rc == GPA_OK) {
+      ctx->last_error = std::string("cudaStreamSynchronize: ") + cudaGetErrorString(e);
+      rc = GPA_ERR_CUDA;
+    }
+  }
   if (rc != GPA_OK) return rc;
-  CUDA_TRY(ctx, cudaMemcpyAsync(dst, ctx->d_out, (size_t)count * sizeof(gpa_result), cudaMemcpyDeviceToHost, ctx->stream));
-  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   if (!pinned) memcpy(out, ctx->h_out, (size_t)count * sizeof(gpa_result));
   return GPA_OK;
 }

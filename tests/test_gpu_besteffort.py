@@ -247,6 +247,16 @@ def test_pinned_host_buffers(ctx, oracle):
     pin_out.free()
 
 
+def test_batch_max_avail_hint(ctx, oracle):
+    W, nl = install(ctx, syn.topo_two_sockets(8))
+    reqs = syn.pack_requests([([0, 1, 2, 3, 4, 5], [], 2), ([0, 1, 2], [], 2)])
+    got = ctx.besteffort_batch(reqs, max_avail=4)      # the caller lied: 6 devices in the first record
+    assert gpa.decode_result(got[0])[0] == gpa.ERR_TOO_LARGE
+    assert gpa.decode_result(got[1]) == (gpa.OK, oracle.besteffort(W, nl, [0, 1, 2], [], 2)[1])
+    got = ctx.besteffort_batch(reqs, max_avail=8)
+    assert_batch_equal(got, oracle_batch(oracle, W, nl, reqs, 0), reqs, "hint")
+
+
 def test_launch_counter_counts_kernels(ctx):
     install(ctx, syn.topo_two_sockets(8))
     before = ctx.launch_count
