@@ -159,6 +159,33 @@ int gpa_besteffort_batch_device(gpa_ctx *ctx, const gpa_request *d_reqs, int cou
 void *gpa_alloc_host(size_t bytes);
 void gpa_free_host(void *p);
 
+/* Allocation-free variant of gpa_besteffort_batch().  No counterpart in the reference (Go never touches device
+ * memory); it exists for callers that must not allocate when a request arrives: the plugin runs on GPUs it has
+ * handed to pods, so (a) their HBM may be full and a cudaMalloc at decision time would fail when the node is
+ * busiest, and (b) cudaMalloc / cudaFree synchronise the whole device and would stall every tenant.
+ *
+ * It needs no gpa_ctx.  The caller passes the topology (as gpa_set_topology takes it), the request records and the
+ * result buffer — all in HOST memory, pageable or pinned — plus the stream to run on (NULL = legacy default
+ * stream).  Device-side staging (topology tables, request records, result records) lives in ONE file-scope
+ * `static __device__` array of GPA_NOALLOC_SCRATCH_BYTES that every GPU loading this library holds until the
+ * process exits.  The call makes no cudaMalloc / cudaMallocHost / cudaFree / stream or event creation; it copies
+ * in, launches besteffort_batch_kernel, copies out and synchronises `stream` before returning.
+ *
+ *   - limits: count <= GPA_NOALLOC_MAX_REQUESTS and n_topology <= GPA_MAX_TOPOLOGY, else GPA_ERR_TOO_LARGE with
+ *     the reason in errbuf (optional, may be NULL);
+ *   - the first call on a device resolves the array's device address (cudaGetSymbolAddress, with that device
+ *     current) and loads a constant table; make that first call before any stream capture begins;
+ *   - the call leaves cuda_device as the calling thread's current device;
+ *   - all calls share the array and it keeps the last call's contents.  Calls are serialised inside one process
+ *     and each waits for its stream, so they do not overlap; work that a caller enqueues by other means and that
+ *     touches the array concurrently on the GPU would race.  Result records are cleared before each launch. */
+#define GPA_NOALLOC_MAX_REQUESTS 4096
+#define GPA_NOALLOC_SCRATCH_BYTES (2 * GPA_MAX_TOPOLOGY * GPA_MAX_TOPOLOGY + GPA_MAX_TOPOLOGY * GPA_MAX_TOPOLOGY + \
+                                   (32 + 16) * GPA_NOALLOC_MAX_REQUESTS) /* 208 896 bytes per GPU */
+int gpa_besteffort_batch_noalloc(int cuda_device, int n_topology, const int32_t *W, const uint8_t *nlinks,
+                                 const gpa_request *reqs, int count, int max_avail, int mode_flags, gpa_result *out,
+                                 void *stream, char *errbuf, int errbuf_len);
+
 /* ---- replica ids (host code: string work, no parallelism) ---------------------------- */
 
 /* Results are written NUL-separated into outbuf; *n_out = number of strings.

@@ -746,3 +746,175 @@ void gpa_free_host(void *p) {
 }
 
 }  // extern "C"
+
+// =======================================================================================
+// Allocation-free batch entry point.
+//
+// Who needs it.  This library decides GPU allocations on a node whose GPUs are SHARED: the
+// same device that runs these kernels also holds the memory of the pods the plugin has
+// handed it to.  Two kinds of caller therefore must not allocate when a request comes in:
+//   * a daemon on a GPU whose tenants have filled HBM — cudaMalloc would fail exactly when
+//     the node is busiest, and an allocation decision must not depend on free device memory;
+//   * a caller that may not stall its tenants — cudaMalloc / cudaFree synchronise the
+//     whole device, so every pod sharing the GPU would feel each request.
+// gpa_create() + gpa_besteffort_batch() allocate (context, staging buffers, topology
+// tables).  This entry point takes everything from the caller and keeps the device-side
+// staging that the batch path needs — topology tables, request records, result records — in
+// ONE fixed array that is part of the loaded module.  The price: the array is resident on
+// every GPU that loads the library until the process exits, its size caps the batch, and it
+// is shared by all calls.
+// =======================================================================================
+namespace {
+
+constexpr size_t kNaWqOff = 0;                                                                      // uint16[64*64]
+constexpr size_t kNaAsymOff = kNaWqOff + sizeof(uint16_t) * GPA_MAX_TOPOLOGY * GPA_MAX_TOPOLOGY;    // uint8[64*64]
+constexpr size_t kNaReqOff = kNaAsymOff + (size_t)GPA_MAX_TOPOLOGY * GPA_MAX_TOPOLOGY;              // gpa_request[max]
+constexpr size_t kNaResOff = kNaReqOff + sizeof(gpa_request) * GPA_NOALLOC_MAX_REQUESTS;            // gpa_result[max]
+constexpr size_t kNaBytes = kNaResOff + sizeof(gpa_result) * GPA_NOALLOC_MAX_REQUESTS;              // 208 896 B
+static_assert(kNaReqOff % 256 == 0 && kNaResOff % 256 == 0, "sub-buffers keep the 256-byte alignment");
+static_assert(kNaBytes == GPA_NOALLOC_SCRATCH_BYTES, "header and implementation agree on the footprint");
+
+}  // namespace
+
+// The scratch itself, at file scope.  In HOST code this name is only a handle for the
+// runtime: it is not a device address and must never be passed to a kernel.  The address
+// comes from cudaGetSymbolAddress (noalloc_setup below).
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNaBytes];
+
+namespace {
+
+struct NoallocDevice {
+  bool ready = false;
+  unsigned char *base = nullptr;  // device address of g_noalloc_scratch on this GPU
+  int sm_count = 0;
+};
+NoallocDevice g_noalloc_dev[64];
+std::mutex g_noalloc_mu;
+
+void na_msg(char *errbuf, int errbuf_len, const std::string &m) {
+  if (errbuf && errbuf_len > 0) snprintf(errbuf, (size_t)errbuf_len, "%s", m.c_str());
+}
+
+// Once per device, with that device current: resolve the array's device address and load the
+// constant table the kernels read.  Neither call allocates.
+int noalloc_setup(int dev, char *errbuf, int errbuf_len) {
+  NoallocDevice &d = g_noalloc_dev[dev];
+  if (d.ready) return GPA_OK;
+  void *p = nullptr;
+  cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+  if (e != cudaSuccess || p == nullptr) {
+    na_msg(errbuf, errbuf_len, std::string("cudaGetSymbolAddress(g_noalloc_scratch): ") + cudaGetErrorString(e));
+    return GPA_ERR_CUDA;
+  }
+  BinomTable b;
+  fill_binom(b);
+  e = cudaMemcpyToSymbol(c_binom, &b, sizeof b);
+  if (e == cudaSuccess) e = cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, dev);
+  if (e != cudaSuccess) {
+    na_msg(errbuf, errbuf_len, std::string("no-alloc set-up: ") + cudaGetErrorString(e));
+    return GPA_ERR_CUDA;
+  }
+  d.base = static_cast<unsigned char *>(p);
+  d.ready = true;
+  return GPA_OK;
+}
+
+}  // namespace
+
+extern "C" int gpa_besteffort_batch_noalloc(int cuda_device, int n_topology, const int32_t *W, const uint8_t *nlinks,
+                                            const gpa_request *reqs, int count, int max_avail, int mode_flags,
+                                            gpa_result *out, void *stream, char *errbuf, int errbuf_len) {
+  na_msg(errbuf, errbuf_len, "");
+  if (cuda_device < 0 || cuda_device >= 64 || !W || !nlinks || count < 0 || max_avail < 0 || (count > 0 && (!reqs || !out))) {
+    na_msg(errbuf, errbuf_len, "invalid argument");
+    return GPA_ERR_INVALID;
+  }
+  if (n_topology < 1 || n_topology > GPA_MAX_TOPOLOGY) {
+    na_msg(errbuf, errbuf_len, "topology of " + std::to_string(n_topology) + " devices: the fixed scratch holds tables for 1.." +
+                                   std::to_string(GPA_MAX_TOPOLOGY) + " devices");
+    return GPA_ERR_TOO_LARGE;
+  }
+  if (count > GPA_NOALLOC_MAX_REQUESTS) {
+    na_msg(errbuf, errbuf_len, "batch of " + std::to_string(count) + " requests exceeds the fixed scratch of this entry point (" +
+                                   std::to_string(GPA_NOALLOC_MAX_REQUESTS) + " requests); split the batch or use gpa_besteffort_batch");
+    return GPA_ERR_TOO_LARGE;
+  }
+  if (count == 0) return GPA_OK;
+
+  // weights -> the 16-bit scaled table the kernel reads (same rule as gpa_set_topology)
+  const int n = n_topology;
+  uint16_t wq[GPA_MAX_TOPOLOGY * GPA_MAX_TOPOLOGY];
+  uint8_t asym[GPA_MAX_TOPOLOGY * GPA_MAX_TOPOLOGY];
+  int g = 0, mx = 0;
+  for (int i = 0; i < n; i++)
+    for (int j = 0; j < n; j++) {
+      if (i == j) continue;
+      int w = W[i * n + j];
+      if (w < 0) {
+        na_msg(errbuf, errbuf_len, "negative pair weight");
+        return GPA_ERR_WEIGHT_RANGE;
+      }
+      g = gcd_int(g, w);
+      mx = w > mx ? w : mx;
+    }
+  if (g == 0) g = 1;
+  if ((long long)(mx / g) * kMaxPairs > kScoreCap) {
+    na_msg(errbuf, errbuf_len, "pair weights too large for the 16-bit score table");
+    return GPA_ERR_WEIGHT_RANGE;
+  }
+  for (int i = 0; i < n; i++)
+    for (int j = 0; j < n; j++) {
+      wq[i * n + j] = i == j ? 0 : (uint16_t)(W[i * n + j] / g);
+      asym[i * n + j] = i != j && nlinks[i * n + j] != nlinks[j * n + i];
+    }
+  if (max_avail == 0)
+    for (int i = 0; i < count; i++)
+      if (reqs[i].n_avail > max_avail && reqs[i].n_avail <= GPA_BATCH_MAX_AVAILABLE) max_avail = reqs[i].n_avail;
+
+  // One call at a time per process: every call uses the same array.
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  cudaError_t e = cudaSetDevice(cuda_device);
+  if (e != cudaSuccess) {
+    na_msg(errbuf, errbuf_len, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
+    return GPA_ERR_CUDA;
+  }
+  int rc = noalloc_setup(cuda_device, errbuf, errbuf_len);
+  if (rc != GPA_OK) return rc;
+  const NoallocDevice &d = g_noalloc_dev[cuda_device];
+  cudaStream_t st = (cudaStream_t)stream;
+  uint16_t *d_wq = reinterpret_cast<uint16_t *>(d.base + kNaWqOff);
+  uint8_t *d_asym = d.base + kNaAsymOff;
+  gpa_request *d_reqs = reinterpret_cast<gpa_request *>(d.base + kNaReqOff);
+  gpa_result *d_out = reinterpret_cast<gpa_result *>(d.base + kNaResOff);
+
+#define NA_TRY(expr)                                                              \
+  do {                                                                            \
+    cudaError_t e_ = (expr);                                                      \
+    if (e_ != cudaSuccess) {                                                      \
+      na_msg(errbuf, errbuf_len, std::string(#expr) + ": " + cudaGetErrorString(e_)); \
+      return GPA_ERR_CUDA;                                                        \
+    }                                                                             \
+  } while (0)
+  NA_TRY(cudaMemcpyAsync(d_wq, wq, sizeof(uint16_t) * (size_t)n * n, cudaMemcpyHostToDevice, st));
+  NA_TRY(cudaMemcpyAsync(d_asym, asym, (size_t)n * n, cudaMemcpyHostToDevice, st));
+  NA_TRY(cudaMemcpyAsync(d_reqs, reqs, sizeof(gpa_request) * (size_t)count, cudaMemcpyHostToDevice, st));
+  // The array still holds the previous call's answers.  The kernel writes every record it is
+  // asked for; clearing them first means a launch that fails cannot hand back stale answers.
+  NA_TRY(cudaMemsetAsync(d_out, 0, sizeof(gpa_result) * (size_t)count, st));
+
+  int n_cap = max_avail < 2 ? 2 : max_avail;
+  if (n_cap > GPA_BATCH_MAX_AVAILABLE) n_cap = GPA_BATCH_MAX_AVAILABLE;
+  size_t smem = (size_t)kBatchWarps * (((size_t)1 << n_cap) + kMaxDevices * kMaxDevices) * sizeof(uint16_t);
+  if (smem > 48 * 1024)
+    NA_TRY(cudaFuncSetAttribute(besteffort_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int blocks = (count + kBatchWarps - 1) / kBatchWarps;
+  int cap = d.sm_count * 4;
+  int grid = blocks < cap ? blocks : cap;
+  BatchTopo t{d_wq, d_asym, n};
+  besteffort_batch_kernel<<<grid, kBatchWarps * 32, smem, st>>>(d_reqs, count, n_cap, mode_flags & GPA_MODE_INTENDED, t, d_out);
+  NA_TRY(cudaGetLastError());
+  NA_TRY(cudaMemcpyAsync(out, d_out, sizeof(gpa_result) * (size_t)count, cudaMemcpyDeviceToHost, st));
+  NA_TRY(cudaStreamSynchronize(st));
+#undef NA_TRY
+  return GPA_OK;
+}
