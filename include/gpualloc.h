@@ -201,6 +201,115 @@ int gpa_prioritize_devices(const char *const *avail, int n_avail, const char *co
 /* ref: getAdditionalXids(), cmd/nvidia-device-plugin/nvidia.go:274-294. */
 int gpa_get_additional_xids(const char *input, uint64_t *out, int out_cap);
 
+/* ---- NVML: link matrix and health events ------------------------------------------------ */
+
+typedef struct gpa_nvml gpa_nvml;
+
+/* dlopen()s NVML and calls nvmlInit_v2.  libpath NULL = "libnvidia-ml.so.1".
+ * ref: nvml.Init -> dlhandles.nvmlInit, vendor/github.com/NVIDIA/gpu-monitoring-tools/bindings/go/nvml/
+ * nvml_dl.go:30-37, bindings.go:94-106. */
+int gpa_nvml_open(const char *libpath, gpa_nvml **out);
+void gpa_nvml_close(gpa_nvml *nv);
+const char *gpa_nvml_last_error(gpa_nvml *nv);
+/* ref: nvml.GetDeviceCount, nvml.go:348 ; Device.UUID, nvml.go:380-447 */
+int gpa_nvml_device_count(gpa_nvml *nv, int *n);
+int gpa_nvml_device_uuid(gpa_nvml *nv, int index, char *buf, int cap);
+
+#define GPA_TOPO_PARITY 0          /* the matrix the reference builds: NVLinks counted only when the far end of a
+                                      link IS the peer GPU (so none through an NVSwitch), links 0..11 only */
+#define GPA_TOPO_NVSWITCH_AWARE 1  /* extension, no reference counterpart: all 18 links, and two GPUs that both
+                                      hang off the switch fabric count min(their switch links) links */
+/* Reads the link matrix: links2[(i*n+j)*2 + {0,1}] = {PCIe-ancestry link, NVLink-count link} as nvml.P2PLinkType
+ * values, 0 = absent; feed it to gpa_set_topology_links().  links2 may be NULL to query n.  *nvml_calls (optional)
+ * = NVML entry points invoked by this build.
+ * ref: gpuallocator.NewDevices, vendor/github.com/NVIDIA/go-gpuallocator/gpuallocator/device.go:33-72;
+ * nvml.GetP2PLink nvml.go:592-615; nvml.GetNVLink nvml.go:617-658. */
+int gpa_nvml_read_topology(gpa_nvml *nv, int flags, int *n, int32_t *links2, int cap, unsigned long long *nvml_calls);
+/* read + install: what the daemon does once at start-up instead of once per request */
+int gpa_set_topology_from_nvml(gpa_ctx *ctx, gpa_nvml *nv, int flags);
+
+typedef struct gpa_health gpa_health;
+/* Starts the XID watcher for the given device ids (full-GPU UUIDs).  disable_env = the value of
+ * DP_DISABLE_HEALTHCHECKS (NULL = read the environment): "all" or anything containing "xids" disables the
+ * watcher, otherwise it is a comma-separated list of additional XIDs to ignore on top of 13, 31, 43, 45, 68.
+ * wait_timeout_ms <= 0 = the reference's 5000 ms.
+ * ref: checkHealth, cmd/nvidia-device-plugin/nvidia.go:181-269. */
+int gpa_health_open(gpa_nvml *nv, const char *const *device_ids, int n, const char *disable_env, int wait_timeout_ms,
+                    gpa_health **out);
+/* Next device that went unhealthy (the reference's `unhealthy <- d`, nvidia.go:222,248,265): returns 1 and the
+ * index into device_ids (+ the XID, 0 for "health checking not supported"), or 0 after timeout_ms. */
+int gpa_health_poll(gpa_health *h, int timeout_ms, int *device_index, unsigned long long *xid);
+int gpa_health_stats(gpa_health *h, unsigned long long *events_seen, unsigned long long *events_skipped, int *disabled);
+void gpa_health_close(gpa_health *h);
+
+/* ---- device-plugin server bodies (host code) ------------------------------------------------ */
+
+#define GPA_LIST_STRATEGY_ENVVAR 0        /* DeviceListStrategyEnvvar */
+#define GPA_LIST_STRATEGY_VOLUME_MOUNTS 1 /* DeviceListStrategyVolumeMounts */
+#define GPA_ID_STRATEGY_UUID 0            /* DeviceIDStrategyUUID */
+#define GPA_ID_STRATEGY_INDEX 1           /* DeviceIDStrategyIndex */
+/* fixes: 0 keeps the reference's behaviour bit for bit (SURVEY.md defects D1, D3, D4) */
+#define GPA_FIX_HEALTH_PROPAGATION 1 /* D1: an unhealthy GPU marks all of its replicas Unhealthy in ListAndWatch */
+#define GPA_FIX_REPLICA_SUFFIX 2     /* D3: best-effort answers carry the "-replica-0" suffix kubelet knows */
+#define GPA_FIX_REQUIRED_IDENTITY 4  /* D4: MustIncludeDeviceIDs are matched by uuid, not by pointer */
+
+typedef struct gpa_plugin gpa_plugin;
+typedef struct gpa_plugin_config { /* ref: NvidiaDevicePlugin + config.Flags, server.go:56-71 */
+  const char *resource_name;       /* resourceName */
+  const char *device_list_envvar;  /* deviceListEnvvar, e.g. "NVIDIA_VISIBLE_DEVICES" */
+  const char *driver_root;         /* config.Flags.NvidiaDriverRoot */
+  uint32_t replicas;               /* replicas */
+  int auto_replicas;               /* autoReplicas: TotalMemory / 1000 replicas per device (server.go:100-103) */
+  int device_list_strategy;        /* GPA_LIST_STRATEGY_* */
+  int device_id_strategy;          /* GPA_ID_STRATEGY_* */
+  int pass_device_specs;           /* config.Flags.PassDeviceSpecs */
+  int has_policy;                  /* allocatePolicy != nil */
+  int fixes;                       /* GPA_FIX_* */
+} gpa_plugin_config;
+typedef struct gpa_plugin_device { /* ref: Device, cmd/nvidia-device-plugin/nvidia.go:41-46 */
+  const char *id;                  /* pluginapi.Device.ID = GPU UUID */
+  const char *index;               /* Index */
+  const char *const *paths;        /* Paths */
+  int n_paths;
+  unsigned long long total_memory_mib; /* TotalMemory */
+  int numa_node;                   /* Topology.Nodes[0].ID, -1 = none */
+  int nvml_index;                  /* gpuallocator.Device.Index */
+} gpa_plugin_device;
+
+/* ref: NewNvidiaDevicePlugin + initialize(), server.go:74-116.  ctx may be NULL when has_policy == 0. */
+int gpa_plugin_create(gpa_ctx *ctx, const gpa_plugin_config *cfg, const gpa_plugin_device *devs, int n_devs,
+                      gpa_plugin **out);
+void gpa_plugin_destroy(gpa_plugin *p);
+/* ref: GetDevicePluginOptions, server.go:243-248 */
+int gpa_plugin_get_options(gpa_plugin *p, int *pre_start_required, int *get_preferred_allocation_available);
+int gpa_plugin_device_count(gpa_plugin *p, int *n_cached, int *n_replicas);
+/* ref: apiDevices(), server.go:415-421 — the payload of every ListAndWatchResponse, as JSON
+ * [{"ID":..,"health":"Healthy"|"Unhealthy","topology":{"nodes":[{"ID":n}]}}] */
+int gpa_plugin_list_devices(gpa_plugin *p, char *json, int cap);
+/* ref: `case d := <-m.health`, server.go:258-262.  Returns the number of list entries that changed. */
+int gpa_plugin_mark_unhealthy(gpa_plugin *p, int cached_index);
+/* ref: one iteration of the ContainerRequests loop of GetPreferredAllocation, server.go:273-311.
+ * Device ids are written NUL-separated into outbuf; errbuf receives the reference's error string. */
+int gpa_plugin_get_preferred_allocation(gpa_plugin *p, const char *const *avail, int n_avail, const char *const *must,
+                                        int n_must, int size, char *outbuf, int outbuf_len, int *n_out, char *errbuf,
+                                        int errbuf_len);
+/* ref: one iteration of the ContainerRequests loop of Allocate, server.go:318-350.  The ContainerAllocateResponse
+ * as JSON {"envs":{..},"mounts":[{"container_path","host_path"}],"devices":[{"container_path","host_path","permissions"}]} */
+int gpa_plugin_allocate(gpa_plugin *p, const char *const *ids, int n, char *json, int cap, char *errbuf, int errbuf_len);
+
+/* ---- topology validation probes (no reference counterpart: the reference never touches device memory;
+ *      `north_star` asks for them to check the NVML-reported topology against measured bandwidth) ---------- */
+
+/* Per-GPU HBM streaming kernel over `bytes` of device memory, `reps` timed launches after warm-up.
+ * mode 0: read-only (bytes counted = bytes read); mode 1: copy (bytes counted = read + written). GB/s. */
+int gpa_probe_hbm(int cuda_device, unsigned long long bytes, int reps, int mode, double *best_gbs, double *median_gbs,
+                  char *errbuf, int errbuf_len);
+/* n x n bandwidth matrix, GB/s one way: row = GPU that pulls, column = GPU whose HBM is read; the diagonal is the
+ * local copy.  mode 0: peer-load kernel (LDG.128 on a peer-mapped pointer, over NVLink/NVSwitch when NVML says
+ * so); mode 1: cudaMemcpyPeerAsync.  can_access (optional, n x n) = cudaDeviceCanAccessPeer. */
+int gpa_probe_p2p(int n_devices, unsigned long long bytes, int reps, int mode, double *matrix_gbs, int *can_access,
+                  char *errbuf, int errbuf_len);
+
 #ifdef __cplusplus
 }
 #endif

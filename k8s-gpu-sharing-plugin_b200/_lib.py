@@ -250,3 +250,243 @@ class PinnedBuffer:
             self.free()
         except Exception:
             pass
+
+
+# ---------------------------------------------------------------------------------------
+# NVML topology + health, plugin server bodies (host code of the path)
+
+TOPO_PARITY, TOPO_NVSWITCH_AWARE = 0, 1
+LIST_ENVVAR, LIST_VOLUME_MOUNTS = 0, 1
+ID_UUID, ID_INDEX = 0, 1
+FIX_HEALTH_PROPAGATION, FIX_REPLICA_SUFFIX, FIX_REQUIRED_IDENTITY = 1, 2, 4
+
+
+class PluginConfig(C.Structure):
+    _fields_ = [("resource_name", C.c_char_p), ("device_list_envvar", C.c_char_p), ("driver_root", C.c_char_p),
+                ("replicas", C.c_uint32), ("auto_replicas", C.c_int), ("device_list_strategy", C.c_int),
+                ("device_id_strategy", C.c_int), ("pass_device_specs", C.c_int), ("has_policy", C.c_int),
+                ("fixes", C.c_int)]
+
+
+class PluginDevice(C.Structure):
+    _fields_ = [("id", C.c_char_p), ("index", C.c_char_p), ("paths", C.POINTER(C.c_char_p)), ("n_paths", C.c_int),
+                ("total_memory_mib", C.c_ulonglong), ("numa_node", C.c_int), ("nvml_index", C.c_int)]
+
+
+def _bind_host(L):
+    vp = C.c_void_p
+    if getattr(L, "_gpa_host_bound", False):
+        return L
+    L.gpa_nvml_open.argtypes = [C.c_char_p, C.POINTER(vp)]
+    L.gpa_nvml_close.restype = None
+    L.gpa_nvml_close.argtypes = [vp]
+    L.gpa_nvml_last_error.restype = C.c_char_p
+    L.gpa_nvml_last_error.argtypes = [vp]
+    L.gpa_nvml_device_count.argtypes = [vp, C.POINTER(C.c_int)]
+    L.gpa_nvml_device_uuid.argtypes = [vp, C.c_int, C.c_char_p, C.c_int]
+    L.gpa_nvml_read_topology.argtypes = [vp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int32), C.c_int,
+                                         C.POINTER(C.c_ulonglong)]
+    L.gpa_set_topology_from_nvml.argtypes = [vp, vp, C.c_int]
+    L.gpa_health_open.argtypes = [vp, C.POINTER(C.c_char_p), C.c_int, C.c_char_p, C.c_int, C.POINTER(vp)]
+    L.gpa_health_poll.argtypes = [vp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_ulonglong)]
+    L.gpa_health_stats.argtypes = [vp, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong), C.POINTER(C.c_int)]
+    L.gpa_health_close.restype = None
+    L.gpa_health_close.argtypes = [vp]
+    L.gpa_plugin_create.argtypes = [vp, C.POINTER(PluginConfig), C.POINTER(PluginDevice), C.c_int, C.POINTER(vp)]
+    L.gpa_plugin_destroy.restype = None
+    L.gpa_plugin_destroy.argtypes = [vp]
+    L.gpa_plugin_get_options.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.gpa_plugin_device_count.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.gpa_plugin_list_devices.argtypes = [vp, C.c_char_p, C.c_int]
+    L.gpa_plugin_mark_unhealthy.argtypes = [vp, C.c_int]
+    L.gpa_plugin_get_preferred_allocation.argtypes = [vp, C.POINTER(C.c_char_p), C.c_int, C.POINTER(C.c_char_p), C.c_int,
+                                                      C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_int), C.c_char_p, C.c_int]
+    L.gpa_plugin_allocate.argtypes = [vp, C.POINTER(C.c_char_p), C.c_int, C.c_char_p, C.c_int, C.c_char_p, C.c_int]
+    for name in ("gpa_nvml_open", "gpa_nvml_device_count", "gpa_nvml_device_uuid", "gpa_nvml_read_topology",
+                 "gpa_set_topology_from_nvml", "gpa_health_open", "gpa_health_poll", "gpa_health_stats", "gpa_plugin_create",
+                 "gpa_plugin_get_options", "gpa_plugin_device_count", "gpa_plugin_list_devices", "gpa_plugin_mark_unhealthy",
+                 "gpa_plugin_get_preferred_allocation", "gpa_plugin_allocate"):
+        getattr(L, name).restype = C.c_int
+    L._gpa_host_bound = True
+    return L
+
+
+class Nvml:
+    """gpa_nvml: NVML reached through dlopen (libpath=None -> libnvidia-ml.so.1)."""
+
+    def __init__(self, libpath=None):
+        L = _bind_host(lib())
+        self._h = C.c_void_p()
+        rc = L.gpa_nvml_open(libpath.encode() if libpath else None, C.byref(self._h))
+        if rc != OK:
+            raise GpaError(rc, "gpa_nvml_open(%s)" % (libpath or "libnvidia-ml.so.1"))
+
+    def close(self):
+        if self._h:
+            lib().gpa_nvml_close(self._h)
+            self._h = C.c_void_p()
+
+    def _check(self, rc):
+        if rc != OK:
+            raise GpaError(rc, lib().gpa_nvml_last_error(self._h).decode())
+
+    def device_count(self):
+        n = C.c_int(0)
+        self._check(lib().gpa_nvml_device_count(self._h, C.byref(n)))
+        return n.value
+
+    def device_uuid(self, i):
+        buf = C.create_string_buffer(96)
+        self._check(lib().gpa_nvml_device_uuid(self._h, i, buf, len(buf)))
+        return buf.value.decode()
+
+    def read_topology(self, flags=TOPO_PARITY):
+        """-> (links2[n, n, 2] int32, nvml_calls)"""
+        n = C.c_int(0)
+        self._check(lib().gpa_nvml_read_topology(self._h, flags, C.byref(n), None, 0, None))
+        links = np.zeros((n.value, n.value, 2), dtype=np.int32)
+        calls = C.c_ulonglong(0)
+        self._check(lib().gpa_nvml_read_topology(self._h, flags, C.byref(n), links.ctypes.data_as(C.POINTER(C.c_int32)),
+                                                 links.size, C.byref(calls)))
+        return links, int(calls.value)
+
+    def install_topology(self, ctx, flags=TOPO_PARITY):
+        self._check(lib().gpa_set_topology_from_nvml(ctx._h, self._h, flags))
+
+
+class HealthWatcher:
+    """gpa_health: the XID watcher of checkHealth (cmd/nvidia-device-plugin/nvidia.go:181-269)."""
+
+    def __init__(self, nvml, device_ids, disable_env="", wait_timeout_ms=0):
+        L = _bind_host(lib())
+        self._nv = nvml
+        self._h = C.c_void_p()
+        rc = L.gpa_health_open(nvml._h, _strs(device_ids), len(device_ids),
+                               None if disable_env is None else disable_env.encode(), wait_timeout_ms, C.byref(self._h))
+        if rc != OK:
+            raise GpaError(rc, lib().gpa_nvml_last_error(nvml._h).decode())
+
+    def poll(self, timeout_ms=0):
+        """-> (device index, xid) or None"""
+        idx, xid = C.c_int(-1), C.c_ulonglong(0)
+        rc = lib().gpa_health_poll(self._h, timeout_ms, C.byref(idx), C.byref(xid))
+        if rc < 0:
+            raise GpaError(rc)
+        return (idx.value, int(xid.value)) if rc == 1 else None
+
+    def stats(self):
+        a, b, d = C.c_ulonglong(0), C.c_ulonglong(0), C.c_int(0)
+        lib().gpa_health_stats(self._h, C.byref(a), C.byref(b), C.byref(d))
+        return {"events_seen": int(a.value), "events_skipped": int(b.value), "disabled": bool(d.value)}
+
+    def close(self):
+        if self._h:
+            lib().gpa_health_close(self._h)
+            self._h = C.c_void_p()
+
+
+class PluginError(RuntimeError):
+    def __init__(self, code, message):
+        self.code = code
+        super().__init__(message)
+
+
+class Plugin:
+    """gpa_plugin: the RPC bodies of NvidiaDevicePlugin (cmd/nvidia-device-plugin/server.go) without the transport."""
+
+    def __init__(self, devices, ctx=None, resource_name="nvidia.com/gpu", envvar="NVIDIA_VISIBLE_DEVICES", driver_root="/",
+                 replicas=1, auto_replicas=False, list_strategy=LIST_ENVVAR, id_strategy=ID_UUID, pass_device_specs=False,
+                 has_policy=True, fixes=0):
+        import json
+        self._json = json
+        L = _bind_host(lib())
+        self._keep = []
+        cfg = PluginConfig(resource_name.encode(), envvar.encode(), driver_root.encode(), replicas, int(auto_replicas),
+                           list_strategy, id_strategy, int(pass_device_specs), int(has_policy), fixes)
+        arr = (PluginDevice * max(len(devices), 1))()
+        for i, d in enumerate(devices):
+            paths = _strs(d.get("paths", []))
+            self._keep.append(paths)
+            arr[i] = PluginDevice(d["id"].encode(), str(d.get("index", i)).encode(), paths, len(d.get("paths", [])),
+                                  int(d.get("total_memory", 0)), int(d.get("numa", -1)), int(d.get("nvml_index", i)))
+        self._h = C.c_void_p()
+        rc = L.gpa_plugin_create(ctx._h if ctx is not None else None, C.byref(cfg), arr, len(devices), C.byref(self._h))
+        if rc != OK:
+            raise GpaError(rc)
+
+    def close(self):
+        if self._h:
+            lib().gpa_plugin_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def options(self):
+        a, b = C.c_int(0), C.c_int(0)
+        lib().gpa_plugin_get_options(self._h, C.byref(a), C.byref(b))
+        return {"pre_start_required": bool(a.value), "get_preferred_allocation_available": bool(b.value)}
+
+    def device_count(self):
+        a, b = C.c_int(0), C.c_int(0)
+        lib().gpa_plugin_device_count(self._h, C.byref(a), C.byref(b))
+        return a.value, b.value
+
+    def api_devices(self):
+        _, nrep = self.device_count()
+        buf = C.create_string_buffer(256 * nrep + 64)
+        rc = lib().gpa_plugin_list_devices(self._h, buf, len(buf))
+        if rc != OK:
+            raise GpaError(rc)
+        return self._json.loads(buf.value.decode())
+
+    def mark_unhealthy(self, cached_index):
+        rc = lib().gpa_plugin_mark_unhealthy(self._h, cached_index)
+        if rc < 0:
+            raise GpaError(rc)
+        return rc
+
+    def get_preferred_allocation(self, available_ids, must_ids, size):
+        buf = C.create_string_buffer(sum(len(x) + 16 for x in list(available_ids) + list(must_ids)) + 64)
+        err = C.create_string_buffer(1024)
+        n = C.c_int(0)
+        rc = lib().gpa_plugin_get_preferred_allocation(self._h, _strs(available_ids), len(available_ids), _strs(must_ids),
+                                                       len(must_ids), int(size), buf, len(buf), C.byref(n), err, len(err))
+        if rc != OK:
+            raise PluginError(rc, err.value.decode() or lib().gpa_strerror(rc).decode())
+        return _unpack(buf, n.value)
+
+    def allocate(self, ids):
+        buf = C.create_string_buffer(4096 + 512 * len(ids))
+        err = C.create_string_buffer(1024)
+        rc = lib().gpa_plugin_allocate(self._h, _strs(ids), len(ids), buf, len(buf), err, len(err))
+        if rc != OK:
+            raise PluginError(rc, err.value.decode() or lib().gpa_strerror(rc).decode())
+        return self._json.loads(buf.value.decode())
+
+
+def probe_hbm(device=0, nbytes=4 << 30, reps=20, mode=1):
+    """-> (best GB/s, median GB/s); mode 0 = read-only, 1 = copy (read + write bytes)"""
+    L = lib()
+    L.gpa_probe_hbm.restype = C.c_int
+    L.gpa_probe_hbm.argtypes = [C.c_int, C.c_ulonglong, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                C.c_char_p, C.c_int]
+    best, med = C.c_double(0), C.c_double(0)
+    err = C.create_string_buffer(256)
+    rc = L.gpa_probe_hbm(device, nbytes, reps, mode, C.byref(best), C.byref(med), err, len(err))
+    if rc != OK:
+        raise GpaError(rc, err.value.decode())
+    return best.value, med.value
+
+
+def probe_p2p(n_devices, nbytes=1 << 30, reps=10, mode=0):
+    """-> (matrix[n, n] GB/s one way: row pulls from column, can_access[n, n])"""
+    L = lib()
+    L.gpa_probe_p2p.restype = C.c_int
+    L.gpa_probe_p2p.argtypes = [C.c_int, C.c_ulonglong, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int),
+                                C.c_char_p, C.c_int]
+    m = np.zeros((n_devices, n_devices), dtype=np.float64)
+    acc = np.zeros((n_devices, n_devices), dtype=np.int32)
+    err = C.create_string_buffer(256)
+    rc = L.gpa_probe_p2p(n_devices, nbytes, reps, mode, m.ctypes.data_as(C.POINTER(C.c_double)),
+                         acc.ctypes.data_as(C.POINTER(C.c_int)), err, len(err))
+    if rc != OK:
+        raise GpaError(rc, err.value.decode())
+    return m, acc
