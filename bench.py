@@ -195,6 +195,8 @@ def run_ours(args):
     ctx = gpa.Context(local)
     t, W, nl, reqs = make_inputs(seed=1000 + rank, count=BATCH)
     ctx.set_topology_links(t)
+    order = syn.sorted_positions(syn.node_uuids(N_DEV, seed=1))
+    ctx.set_device_order(order)  # the node's sorted-UUID order, which is how the reference lists devices
 
     # ---- device-resident arm: `value` -------------------------------------------------
     d_in = torch.from_numpy(reqs.view(np.uint8).reshape(-1, 32)).cuda()
@@ -317,6 +319,7 @@ def run_ours(args):
         "answer": res16[1],
     }
     ctx.set_topology_links(t)
+    ctx.set_device_order(order)
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

@@ -92,6 +92,13 @@ int gpa_set_topology_links(gpa_ctx *ctx, int n, const int32_t *links2);
 /* The score switch alone, for one link type.  ref: besteffort_policy.go:314-353. */
 int gpa_link_type_score(int link_type);
 
+/* Declares the node-wide order in which requests list their devices: order[label] = NVML index, a permutation of
+ * 0..n-1 (default: identity).  Batch requests whose `avail` list is ascending in this order take a faster kernel
+ * path (one score table per node instead of one per request); others are still answered, just slower.
+ * ref: the reference always lists devices in byte-wise sorted-UUID order, stripReplicas,
+ * cmd/nvidia-device-plugin/replica.go:43 -> server.go:274 — pass that order here. */
+int gpa_set_device_order(gpa_ctx *ctx, const int32_t *order, int n);
+
 /* Reads the installed matrix back (n*n entries each); either pointer may be NULL. */
 int gpa_get_topology(gpa_ctx *ctx, int *n, int32_t *W, uint8_t *nlinks, int cap);
 
@@ -144,7 +151,7 @@ typedef struct gpa_result {
 
 /* host buffers: copies in, launches, copies out (in overlapping chunks), synchronises.
  * max_avail = largest n_avail in the batch, e.g. the node's GPU count (<= GPA_BATCH_MAX_AVAILABLE); 0 = unknown,
- * the library scans the records for it.  A record with more than max_avail devices gets GPA_ERR_TOO_LARGE. */
+ * the library scans the records for it.  A record with more than max_avail devices may get GPA_ERR_TOO_LARGE. */
 int gpa_besteffort_batch(gpa_ctx *ctx, const gpa_request *reqs, int count, int max_avail, int mode_flags,
                          gpa_result *out);
 /* device buffers, asynchronous on `stream` (a cudaStream_t; NULL = the legacy default stream): inputs already

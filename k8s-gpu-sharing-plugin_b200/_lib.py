@@ -58,6 +58,8 @@ def lib():
     L.gpa_set_topology.argtypes = [vp, C.c_int, i32p, u8p]
     L.gpa_set_topology_links.argtypes = [vp, C.c_int, i32p]
     L.gpa_link_type_score.argtypes = [C.c_int]
+    L.gpa_set_device_order.restype = C.c_int
+    L.gpa_set_device_order.argtypes = [vp, i32p, C.c_int]
     L.gpa_get_topology.argtypes = [vp, C.POINTER(C.c_int), i32p, u8p, C.c_int]
     L.gpa_besteffort.argtypes = [vp, i32p, C.c_int, i32p, C.c_int, C.c_int, C.c_int, i32p, C.POINTER(C.c_int)]
     L.gpa_last_search_stats.argtypes = [vp, C.POINTER(SearchStats)]
@@ -171,6 +173,11 @@ class Context:
     def set_topology_links(self, links2):
         l2 = np.ascontiguousarray(links2, dtype=np.int32)
         self._check(lib().gpa_set_topology_links(self._h, l2.shape[0], l2.ctypes.data_as(C.POINTER(C.c_int32))))
+
+    def set_device_order(self, order):
+        """order[label] = NVML index: the node-wide order requests list their devices in (sorted-UUID order)"""
+        o = np.ascontiguousarray(order, dtype=np.int32)
+        self._check(lib().gpa_set_device_order(self._h, o.ctypes.data_as(C.POINTER(C.c_int32)), len(o)))
 
     def get_topology(self):
         n = C.c_int(0)

@@ -31,6 +31,8 @@ namespace {
 using namespace gpa;
 
 __constant__ BinomTable c_binom;
+// candidate partitions of (n available, size k), n,k <= 12, saturated at 2^32-1: work estimate of the fast batch path
+__constant__ uint32_t c_parts[13][13];
 
 constexpr int kSearchBlockSmall = 256;   // score table <= 32 KB: several CTAs per SM
 constexpr int kSearchBlockLarge = 1024;  // 64-128 KB table: one or two CTAs per SM, so make them wide
@@ -142,6 +144,8 @@ __global__ void __launch_bounds__(kSearchBlock) besteffort_search_kernel(const S
 // ---------------------------------------------------------------------------------------
 // Batch: one warp per container request.
 
+constexpr int8_t kResDefer = -126;  // internal: "left to the general kernel"; never leaves the library
+
 struct BatchTopo {
   const uint16_t *wq;   // nt*nt scaled weights
   const uint8_t *asym;  // nt*nt, 1 where the link counts of (i,j) and (j,i) differ
@@ -153,9 +157,12 @@ __device__ __forceinline__ void write_result(gpa_result *out, const int8_t *dev)
   *reinterpret_cast<int4 *>(out->dev) = *src;
 }
 
+// General batch kernel: any `available` order, per-request score table, one warp per request.
+// With deferred_only it answers just the records the fast kernel marked GPA_RES_DEFER: each
+// warp scans 32 result records at a time (one coalesced load) and works on the marked ones.
 __global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_kernel(const gpa_request *__restrict__ reqs, int count,
                                                                             int n_cap, int intended, BatchTopo topo,
-                                                                            gpa_result *__restrict__ out) {
+                                                                            gpa_result *out, int deferred_only) {
   extern __shared__ __align__(16) uint16_t smem[];
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
@@ -163,7 +170,7 @@ __global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_kernel(cons
   uint16_t *wp = S + (1u << n_cap);
   const STab stab{S};
 
-  for (int r = blockIdx.x * kBatchWarps + warp; r < count; r += gridDim.x * kBatchWarps) {
+  auto process = [&](int r) {
     // 32-byte record, same address in every lane: one broadcast transaction each
     const uint4 lo = __ldg(reinterpret_cast<const uint4 *>(reqs + r));
     const uint4 hi = __ldg(reinterpret_cast<const uint4 *>(reqs + r) + 1);
@@ -255,6 +262,203 @@ __global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_kernel(cons
       }
       write_result(out + r, res);
     }
+  };
+
+  if (!deferred_only) {
+    for (int r = blockIdx.x * kBatchWarps + warp; r < count; r += gridDim.x * kBatchWarps) process(r);
+  } else {
+    for (long long base = ((long long)blockIdx.x * kBatchWarps + warp) * 32; base < count;
+         base += (long long)gridDim.x * kBatchWarps * 32) {
+      const long long r = base + lane;
+      const bool marked = r < count && out[r].dev[0] == kResDefer;
+      unsigned todo = __ballot_sync(0xffffffffu, marked);
+      while (todo) {
+        const int b = __ffs(todo) - 1;
+        todo &= todo - 1;
+        process((int)(base + b));
+        __syncwarp();
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// Fast batch kernel for requests in CANONICAL order: the devices of every request are listed
+// in one node-wide order (the reference always does: stripReplicas sorts the UUIDs,
+// cmd/nvidia-device-plugin/replica.go:43).  Devices are relabelled by their rank in that
+// order, so a request is just a label MASK, positions are labels, and one score table over
+// all 2^nt label masks serves every request of the node: no per-request table, no gather.
+//   * phase 1, one LANE per request: parse, guards, size-1 answers, tiny searches;
+//   * phase 2, the whole WARP per heavy request: items strided over lanes, shuffle max;
+//   * phase 3, one lane per request again: epilogue and a coalesced 16-byte store.
+// Anything unusual (non-canonical order, unknown device, too many devices) is marked
+// GPA_RES_DEFER for the general kernel.
+constexpr int kFastMaxTopo = 12;
+constexpr uint32_t kLightMaxPartitions = 24;
+
+struct FastTopo {
+  const uint16_t *s_full;  // [1 << nt] scaled set scores over label masks
+  int nt;
+  uint8_t order[16];  // label -> NVML index
+  uint8_t rank[GPA_MAX_TOPOLOGY];  // NVML index -> label, 0xFF = not on this node
+};
+
+__device__ __noinline__ int fast_search_item(const Geom &g, const Cut &cut, const uint16_t *S, unsigned long long item) {
+  return search_item(g, cut, c_binom, STab{S}, item);
+}
+__device__ __noinline__ int fast_finalize(const Geom &g, const Cut &cut, const uint16_t *S, unsigned long long key, bool intended,
+                                          uint32_t &best_set) {
+  return finalize_set(g, cut, c_binom, STab{S}, key, intended, best_set);
+}
+
+__device__ __forceinline__ void res_set_byte(unsigned long long &r0, unsigned long long &r1, int i, int v) {
+  unsigned long long b = (unsigned long long)(v & 0xFF);
+  if (i < 8) r0 = (r0 & ~(0xFFull << (8 * i))) | (b << (8 * i));
+  else r1 = (r1 & ~(0xFFull << (8 * (i - 8)))) | (b << (8 * (i - 8)));
+}
+
+__global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_fast_kernel(const gpa_request *__restrict__ reqs, int count,
+                                                                                 int intended, const FastTopo ft,
+                                                                                 gpa_result *__restrict__ out) {
+  extern __shared__ __align__(16) uint16_t S[];
+  {
+    const uint32_t total = 1u << ft.nt;
+    for (uint32_t i = threadIdx.x; i < total; i += kBatchWarps * 32) S[i] = ft.s_full[i];
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  enum { kDone = 0, kLight = 1, kHeavy = 2, kDefer = 3, kIdle = 4 };
+
+  for (long long base = ((long long)blockIdx.x * kBatchWarps + warp) * 32; base < count;
+       base += (long long)gridDim.x * kBatchWarps * 32) {
+    const long long r = base + lane;
+    int status = kIdle;
+    unsigned long long r0 = 0x8080808080808080ull, r1 = 0x8080808080808080ull;  // 16 x GPA_RES_END
+    uint32_t mask = 0, rlab = 0;
+    int size = 0;
+    unsigned long long key = 0;
+    if (r < count) {
+      const uint4 lo = __ldg(reinterpret_cast<const uint4 *>(reqs + r));
+      const uint4 hi = __ldg(reinterpret_cast<const uint4 *>(reqs + r) + 1);
+      const uint32_t rmask = hi.x & 0xFFFFu;
+      const int n = (hi.x >> 16) & 0xFF;
+      size = (hi.x >> 24) & 0xFF;
+      const int flags = hi.y & 0xFF;
+      const int n_req = __popc(rmask) + ((hi.y >> 8) & 0xFF);
+      status = kDone;
+      // guards of besteffort_policy.go:35-45
+      if (!(size <= 0 || n < size || n_req > size)) {
+        if (n > kFastMaxTopo || (rmask >> n) != 0) {
+          status = kDefer;
+        } else {
+          // relabel: device -> rank in the node order; the list must be strictly ascending
+          const uint32_t w[4] = {lo.x, lo.y, lo.z, lo.w};
+          int prev = -1;
+          int first_dev = 0, first_req_dev = -1;
+#pragma unroll
+          for (int p = 0; p < kFastMaxTopo; p++) {
+            if (p < n) {
+              const int d = (w[p >> 2] >> ((p & 3) * 8)) & 0xFF;
+              const int lab = d < GPA_MAX_TOPOLOGY ? ft.rank[d] : 0xFF;
+              if (lab == 0xFF || lab <= prev) status = kDefer;
+              prev = lab;
+              mask |= 1u << (lab & 31);
+              if (rmask >> p & 1u) {
+                rlab |= 1u << (lab & 31);
+                if (first_req_dev < 0) first_req_dev = d;
+              }
+              if (p == 0) first_dev = d;
+            }
+          }
+          if (status != kDefer) {
+            if (flags & GPA_REQ_FOREIGN) {
+              // a required pointer that is in no set: every candidate is rejected (:53) -> empty answer
+            } else if (size == 1) {
+              // :219-224 — first accepted single-device candidate
+              res_set_byte(r0, r1, 0, first_req_dev >= 0 ? first_req_dev : first_dev);
+            } else {
+              const uint32_t parts = c_parts[n][size];
+              const int m = (n + size - 1) / size;
+              status = (parts <= kLightMaxPartitions && m <= kMaxSuffix) ? kLight : kHeavy;
+            }
+          }
+        }
+      }
+    }
+
+    // phase 1b: tiny searches, one lane each
+    if (status == kLight) {
+      const Geom g = make_geom_sparse(mask, size, rlab, ft.nt);
+      Cut cut;
+      cut.d = 0;
+      cut.n_items = 1;
+#pragma unroll
+      for (int j = 0; j < kMaxCutDepth; j++) cut.radix[j] = 1;
+      const int sc = fast_search_item(g, cut, S, 0);
+      key = sc >= 0 ? pack_key(sc, 0) : 0ull;
+    }
+
+    // phase 2: heavy searches, the whole warp on one request at a time
+    unsigned heavy = __ballot_sync(0xffffffffu, status == kHeavy);
+    while (heavy) {
+      const int h = __ffs(heavy) - 1;
+      heavy &= heavy - 1;
+      const uint32_t hmask = __shfl_sync(0xffffffffu, mask, h);
+      const uint32_t hrlab = __shfl_sync(0xffffffffu, rlab, h);
+      const int hsize = __shfl_sync(0xffffffffu, size, h);
+      const Geom g = make_geom_sparse(hmask, hsize, hrlab, ft.nt);
+      const Cut cut = choose_cut(g, c_binom, 96);
+      unsigned long long best = 0;
+      for (unsigned long long item = lane; item < cut.n_items; item += 32) {
+        const int sc = fast_search_item(g, cut, S, item);
+        if (sc >= 0) {
+          const unsigned long long kk = pack_key(sc, item);
+          best = kk > best ? kk : best;
+        }
+      }
+      best = warp_max_u64(best);
+      if (lane == h) key = best;
+    }
+
+    // phase 3: epilogue per lane (light and heavy alike), then one coalesced store per lane
+    if (status == kLight || status == kHeavy) {
+      const Geom g = make_geom_sparse(mask, size, rlab, ft.nt);
+      Cut cut;
+      if (status == kHeavy) {
+        cut = choose_cut(g, c_binom, 96);
+      } else {
+        cut.d = 0;
+        cut.n_items = 1;
+#pragma unroll
+        for (int j = 0; j < kMaxCutDepth; j++) cut.radix[j] = 1;
+      }
+      uint32_t best_set = 0;
+      const int rc = fast_finalize(g, cut, S, key, intended != 0, best_set);
+      if (rc < 0) {
+        res_set_byte(r0, r1, 0, GPA_RES_ERROR);
+        res_set_byte(r0, r1, 1, GPA_ERR_INVALID);
+      } else if (rc > 0) {
+        int o = 0;
+        uint32_t reals = best_set & g.real_mask;
+        while (reals) {
+          const int lab = __ffs(reals) - 1;
+          reals &= reals - 1;
+          res_set_byte(r0, r1, o++, ft.order[lab]);
+        }
+        if (best_set & g.tok_bit)
+          for (int i = 0; i < g.P; i++) res_set_byte(r0, r1, o++, GPA_NIL);
+      }
+    }
+    if (status == kDefer) res_set_byte(r0, r1, 0, kResDefer);
+    if (status != kIdle) {
+      uint4 v;
+      v.x = (uint32_t)r0;
+      v.y = (uint32_t)(r0 >> 32);
+      v.z = (uint32_t)r1;
+      v.w = (uint32_t)(r1 >> 32);
+      *reinterpret_cast<uint4 *>(out[r].dev) = v;
+    }
   }
 }
 
@@ -277,6 +481,8 @@ struct Topology {
   std::vector<uint8_t> nlinks;
   std::vector<uint16_t> wq;
   std::vector<uint8_t> asym;
+  bool any_asym = false;
+  std::vector<int> order;  // label -> NVML index: the node-wide order requests list their devices in
 };
 
 }  // namespace
@@ -301,6 +507,8 @@ struct gpa_ctx {
   bool has_topo = false;
   uint16_t *d_wq = nullptr;
   uint8_t *d_asym = nullptr;
+  uint16_t *d_sfull = nullptr;  // fast batch path: set scores over label masks, nullptr = path unavailable
+  FastTopo fast{};
   // batch staging
   gpa_request *d_reqs = nullptr;
   gpa_result *d_out = nullptr;
@@ -349,9 +557,8 @@ int ensure_batch_capacity(gpa_ctx *ctx, size_t count, bool host_staging) {
   return GPA_OK;
 }
 
-int launch_batch(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_avail, int mode_flags, gpa_result *d_out,
-                 cudaStream_t stream) {
-  if (count == 0) return GPA_OK;
+int launch_general(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_avail, int mode_flags, gpa_result *d_out,
+                   cudaStream_t stream, int deferred_only) {
   int n_cap = max_avail < 2 ? 2 : max_avail;
   if (n_cap > GPA_BATCH_MAX_AVAILABLE) n_cap = GPA_BATCH_MAX_AVAILABLE;
   size_t smem = (size_t)kBatchWarps * (((size_t)1 << n_cap) + kMaxDevices * kMaxDevices) * sizeof(uint16_t);
@@ -360,14 +567,74 @@ int launch_batch(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_ava
   int occ = 1;
   CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, besteffort_batch_kernel, kBatchWarps * 32, smem));
   if (occ < 1) occ = 1;
-  long long want = ((long long)count + kBatchWarps - 1) / kBatchWarps;
+  long long per_block = deferred_only ? (long long)kBatchWarps * 32 : kBatchWarps;
+  long long want = ((long long)count + per_block - 1) / per_block;
   long long cap = (long long)ctx->sm_count * occ;  // persistent: one wave, warps stride over the requests
   int grid = (int)(want < cap ? want : cap);
   BatchTopo t{ctx->d_wq, ctx->d_asym, ctx->topo.n};
   besteffort_batch_kernel<<<grid, kBatchWarps * 32, smem, stream>>>(d_reqs, count, n_cap, mode_flags & GPA_MODE_INTENDED, t,
-                                                                    d_out);
+                                                                    d_out, deferred_only);
   ctx->launches++;
   CUDA_TRY(ctx, cudaGetLastError());
+  return GPA_OK;
+}
+
+int launch_batch(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_avail, int mode_flags, gpa_result *d_out,
+                 cudaStream_t stream) {
+  if (count == 0) return GPA_OK;
+  if (!ctx->d_sfull) return launch_general(ctx, d_reqs, count, max_avail, mode_flags, d_out, stream, 0);
+  // canonical-order fast path, then the general kernel mops up whatever was deferred
+  size_t smem = ((size_t)1 << ctx->fast.nt) * sizeof(uint16_t);
+  int occ = 1;
+  CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, besteffort_batch_fast_kernel, kBatchWarps * 32, smem));
+  if (occ < 1) occ = 1;
+  long long want = ((long long)count + kBatchWarps * 32 - 1) / (kBatchWarps * 32);
+  long long cap = (long long)ctx->sm_count * occ;
+  int grid = (int)(want < cap ? want : cap);
+  besteffort_batch_fast_kernel<<<grid, kBatchWarps * 32, smem, stream>>>(d_reqs, count, mode_flags & GPA_MODE_INTENDED, ctx->fast,
+                                                                         d_out);
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return launch_general(ctx, d_reqs, count, max_avail, mode_flags, d_out, stream, 1);
+}
+
+// (Re)builds what the fast batch path needs from the installed topology and device order: the
+// label <-> NVML index maps and the score table over all label masks.  The path is available
+// for nodes of up to kFastMaxTopo devices whose link counts are symmetric.
+int rebuild_fast(gpa_ctx *ctx) {
+  Topology &T = ctx->topo;
+  if (ctx->d_sfull) {
+    cudaFree(ctx->d_sfull);
+    ctx->d_sfull = nullptr;
+  }
+  if (T.n > kFastMaxTopo || T.any_asym) return GPA_OK;
+  if ((int)T.order.size() != T.n) {
+    T.order.resize(T.n);
+    for (int i = 0; i < T.n; i++) T.order[i] = i;
+  }
+  FastTopo f;
+  memset(&f, 0, sizeof f);
+  f.nt = T.n;
+  memset(f.rank, 0xFF, sizeof f.rank);
+  for (int lab = 0; lab < T.n; lab++) {
+    f.order[lab] = (uint8_t)T.order[lab];
+    f.rank[T.order[lab]] = (uint8_t)lab;
+  }
+  std::vector<uint16_t> sfull((size_t)1 << T.n, 0);
+  for (uint32_t mask = 1; mask < (1u << T.n); mask++) {
+    // score of the set without its lowest label, plus that label's pairs (earlier label's view, :314)
+    const int a = __builtin_ctz(mask);
+    const uint32_t rest = mask & (mask - 1);
+    uint32_t sum = sfull[rest];
+    for (uint32_t mb = rest; mb; mb &= mb - 1) sum += T.wq[T.order[a] * T.n + T.order[__builtin_ctz(mb)]];
+    sfull[mask] = (uint16_t)(sum > 65535u ? 65535u : sum);
+  }
+  uint16_t *d = nullptr;
+  CUDA_TRY(ctx, cudaMalloc(&d, sfull.size() * sizeof(uint16_t)));
+  CUDA_TRY(ctx, cudaMemcpy(d, sfull.data(), sfull.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
+  f.s_full = d;
+  ctx->d_sfull = d;
+  ctx->fast = f;
   return GPA_OK;
 }
 
@@ -436,6 +703,16 @@ int gpa_create(int cuda_device, gpa_ctx **out) {
   CREATE_TRY(cudaMemset(ctx->d_ticket, 0, sizeof(unsigned int)));
   fill_binom(ctx->binom);
   CREATE_TRY(cudaMemcpyToSymbol(c_binom, &ctx->binom, sizeof(BinomTable)));
+  {
+    uint32_t parts[13][13];
+    memset(parts, 0, sizeof parts);
+    for (int n = 2; n <= 12; n++)
+      for (int k = 2; k <= n; k++) {
+        uint64_t c = partition_count(make_geom(n, k, 0), ctx->binom);
+        parts[n][k] = c > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)c;
+      }
+    CREATE_TRY(cudaMemcpyToSymbol(c_parts, parts, sizeof parts));
+  }
   CREATE_TRY(cudaDeviceSynchronize());
 #undef CREATE_TRY
   *out = ctx;
@@ -452,6 +729,7 @@ void gpa_destroy(gpa_ctx *ctx) {
   if (ctx->h_res) cudaFreeHost(ctx->h_res);
   if (ctx->d_wq) cudaFree(ctx->d_wq);
   if (ctx->d_asym) cudaFree(ctx->d_asym);
+  if (ctx->d_sfull) cudaFree(ctx->d_sfull);
   if (ctx->d_reqs) cudaFree(ctx->d_reqs);
   if (ctx->d_out) cudaFree(ctx->d_out);
   if (ctx->h_reqs) cudaFreeHost(ctx->h_reqs);
@@ -505,8 +783,10 @@ int gpa_set_topology(gpa_ctx *ctx, int n, const int32_t *W, const uint8_t *nlink
       if (i == j) continue;
       t.wq[i * n + j] = (uint16_t)(W[i * n + j] / g);
       t.asym[i * n + j] = nlinks[i * n + j] != nlinks[j * n + i];
+      t.any_asym = t.any_asym || t.asym[i * n + j];
     }
   std::lock_guard<std::mutex> lk(ctx->mu);
+  if ((int)ctx->topo.order.size() == n) t.order = ctx->topo.order;  // a device order set earlier survives a re-install
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   // Requests are serialised on ctx->mu and each one finishes before it returns, so no
   // kernel can still be reading the old tables here.
@@ -522,7 +802,22 @@ int gpa_set_topology(gpa_ctx *ctx, int n, const int32_t *W, const uint8_t *nlink
   ctx->d_asym = d_asym;
   ctx->topo = std::move(t);
   ctx->has_topo = true;
-  return GPA_OK;
+  return rebuild_fast(ctx);
+}
+
+int gpa_set_device_order(gpa_ctx *ctx, const int32_t *order, int n) {
+  if (!ctx || !order || n < 1) return GPA_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  if (!ctx->has_topo) return GPA_ERR_NO_TOPOLOGY;
+  if (n != ctx->topo.n) return GPA_ERR_INVALID;
+  unsigned long long seen = 0;
+  for (int i = 0; i < n; i++) {
+    if (order[i] < 0 || order[i] >= n || (seen >> order[i] & 1ull)) return GPA_ERR_INVALID;  // must be a permutation
+    seen |= 1ull << order[i];
+  }
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  ctx->topo.order.assign(order, order + n);
+  return rebuild_fast(ctx);
 }
 
 int gpa_set_topology_links(gpa_ctx *ctx, int n, const int32_t *links2) {
@@ -911,7 +1206,7 @@ extern "C" int gpa_besteffort_batch_noalloc(int cuda_device, int n_topology, con
   int cap = d.sm_count * 4;
   int grid = blocks < cap ? blocks : cap;
   BatchTopo t{d_wq, d_asym, n};
-  besteffort_batch_kernel<<<grid, kBatchWarps * 32, smem, st>>>(d_reqs, count, n_cap, mode_flags & GPA_MODE_INTENDED, t, d_out);
+  besteffort_batch_kernel<<<grid, kBatchWarps * 32, smem, st>>>(d_reqs, count, n_cap, mode_flags & GPA_MODE_INTENDED, t, d_out, 0);
   NA_TRY(cudaGetLastError());
   NA_TRY(cudaMemcpyAsync(out, d_out, sizeof(gpa_result) * (size_t)count, cudaMemcpyDeviceToHost, st));
   NA_TRY(cudaStreamSynchronize(st));

@@ -70,7 +70,8 @@ struct Geom {
   int m;               // sets per partition, N / k
   int t;               // picks per set besides the anchor, k - 1
   uint32_t real_mask;  // (1 << n) - 1
-  uint32_t tok_bit;    // P ? 1 << n : 0      — stands for all P nil pads
+  uint32_t tok_bit;    // P ? 1 << tok_pos : 0 — stands for all P nil pads
+  int tok_pos;         // position of the pads: n for dense positions, above every device for sparse ones
   uint32_t rmask;      // positions of the `required` devices
 };
 
@@ -84,6 +85,25 @@ GPA_HD Geom make_geom(int n, int k, uint32_t rmask) {
   g.t = k - 1;
   g.real_mask = (n >= 32) ? 0xFFFFFFFFu : ((1u << n) - 1u);
   g.tok_bit = g.P ? (1u << n) : 0u;
+  g.tok_pos = n;
+  g.rmask = rmask;
+  return g;
+}
+
+// Same request over SPARSE positions: the devices sit at the set bits of real_mask (their
+// ascending bit order is the caller's `available` order) and the pads at tok_pos, above all
+// of them.  Everything downstream only ever asks for "lowest bit", "bits above" and "count".
+GPA_HD Geom make_geom_sparse(uint32_t real_mask, int k, uint32_t rmask, int tok_pos) {
+  Geom g;
+  g.n = popc32(real_mask);
+  g.k = k;
+  int N = ((g.n + k - 1) / k) * k;
+  g.P = N - g.n;
+  g.m = N / k;
+  g.t = k - 1;
+  g.real_mask = real_mask;
+  g.tok_bit = g.P ? (1u << tok_pos) : 0u;
+  g.tok_pos = tok_pos;
   g.rmask = rmask;
   return g;
 }
@@ -278,8 +298,8 @@ template <typename STab>
 GPA_HD ItemState decode_item(const Geom &g, const Cut &cut, const BinomTable &B, const STab &S, uint64_t item,
                              uint32_t *sets_out) {
   ItemState st;
-  const int N = g.m * g.k;
-  uint32_t lit = (N >= 32) ? 0xFFFFFFFFu : ((1u << N) - 1u);  // literal remainder
+  // literal remainder: the devices plus P separate pad positions tok_pos .. tok_pos+P-1
+  uint32_t lit = g.real_mask | (g.P ? (((1u << g.P) - 1u) << g.tok_pos) : 0u);
   const uint32_t nil_lit = lit & ~g.real_mask;
   st.acc = 0;
   st.ok = false;
@@ -361,10 +381,12 @@ GPA_HD int fresh_slots(int m) {
 // Epilogue (:65-88) for the winning item: replay it to recover the first best partition,
 // apply what Go's slice aliasing does to the saved bestPartition (go_faithful), filter
 // the sets by `required` and return the first best-scoring one.
-//   out_pos[0..k): positions in ascending order, -1 for each nil pad.  returns k, or 0.
+//   returns 1 and the winning set (positions + token bit) in best_set, 0 for the empty
+//   answer, -1 if the key cannot be replayed (cannot happen for a key from this request).
 template <typename STab>
-GPA_HD int finalize(const Geom &g, const Cut &cut, const BinomTable &B, const STab &S, uint64_t key, bool intended,
-                    int8_t *out_pos) {
+GPA_HD int finalize_set(const Geom &g, const Cut &cut, const BinomTable &B, const STab &S, uint64_t key, bool intended,
+                        uint32_t &best_set) {
+  best_set = 0;
   if (key == 0) return 0;  // bestPartition == nil -> empty answer (:72-74)
   Replay rec;
   rec.target = key_score(key);
@@ -373,7 +395,7 @@ GPA_HD int finalize(const Geom &g, const Cut &cut, const BinomTable &B, const ST
   ItemState st = decode_item(g, cut, B, S, key_item(key), rec.sets);
   int dummy = -1;
   walk_dyn(g.m - cut.d, g, S, st.rem, st.acc, st.ok, dummy, &rec);
-  if (!st.valid || !rec.found) return -1;  // cannot happen: the key came from this item
+  if (!st.valid || !rec.found) return -1;
 
   if (!intended) {
     // D6: slots fresh..m-1 of the saved candidate are shared with every later candidate
@@ -405,7 +427,6 @@ GPA_HD int finalize(const Geom &g, const Cut &cut, const BinomTable &B, const ST
 
   // :65-85 — no padding test here: a padded set can win (defect D5)
   int best = -1;
-  uint32_t best_set = 0;
   for (int s = 0; s < g.m; s++) {
     uint32_t set = rec.sets[s];
     if ((set & g.rmask) != g.rmask) continue;
@@ -415,7 +436,16 @@ GPA_HD int finalize(const Geom &g, const Cut &cut, const BinomTable &B, const ST
       best_set = set;
     }
   }
-  if (best < 0) return 0;
+  return best < 0 ? 0 : 1;
+}
+
+//   out_pos[0..k): positions in ascending order, -1 for each nil pad.  returns k, 0, or -1.
+template <typename STab>
+GPA_HD int finalize(const Geom &g, const Cut &cut, const BinomTable &B, const STab &S, uint64_t key, bool intended,
+                    int8_t *out_pos) {
+  uint32_t best_set;
+  int rc = finalize_set(g, cut, B, S, key, intended, best_set);
+  if (rc <= 0) return rc;
   int o = 0;
   uint32_t reals = best_set & g.real_mask;
   while (reals) {

@@ -64,3 +64,41 @@ extern "C" int enum_check_level_sets(int n, int k, int tok_present, uint32_t rem
   } while (st.next(chosen));
   return cnt;
 }
+
+// Sparse variant: devices are the set bits of real_mask (labels 0..nt-1, ascending label order =
+// `available` order), the pads sit at position nt, and set scores come from ONE table over all
+// 2^nt label masks — the layout of the canonical-order fast path of the batch kernel.
+extern "C" int enum_check_search_sparse(int nt, const int32_t *W, uint32_t real_mask, uint32_t rmask, int size, int intended,
+                                        unsigned long long want_items, int32_t *out, int *n_out) {
+  using namespace gpa;
+  *n_out = 0;
+  BinomTable B;
+  fill_binom(B);
+  std::vector<uint16_t> S((size_t)1 << nt, 0);
+  for (uint32_t mask = 1; mask < (1u << nt); mask++) {
+    int s = 0;
+    for (int a = 0; a < nt; a++)
+      if (mask >> a & 1)
+        for (int b = a + 1; b < nt; b++)
+          if (mask >> b & 1) s += W[a * nt + b];
+    S[mask] = (uint16_t)s;
+  }
+  auto Sf = [&](uint32_t mask) { return S[mask]; };
+  Geom g = make_geom_sparse(real_mask, size, rmask, nt);
+  if (size < 2 || g.n < size) return -1;
+  Cut cut = choose_cut(g, B, want_items);
+  uint64_t key = 0;
+  for (uint64_t item = 0; item < cut.n_items; item++) {
+    int sc = search_item(g, cut, B, Sf, item);
+    if (sc >= 0) {
+      uint64_t kk = pack_key(sc, item);
+      if (kk > key) key = kk;
+    }
+  }
+  int8_t pos[32];
+  int cnt = finalize(g, cut, B, Sf, key, intended != 0, pos);
+  if (cnt < 0) return -2;
+  for (int i = 0; i < cnt; i++) out[i] = pos[i];
+  *n_out = cnt;
+  return 0;
+}

@@ -27,6 +27,9 @@ def harness():
     L.enum_check_search.argtypes = [C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int, C.c_uint32, C.c_int,
                                     C.c_int, C.c_ulonglong, C.POINTER(C.c_int32), C.POINTER(C.c_int),
                                     C.POINTER(C.c_ulonglong), C.POINTER(C.c_int)]
+    L.enum_check_search_sparse.restype = C.c_int
+    L.enum_check_search_sparse.argtypes = [C.c_int, C.POINTER(C.c_int32), C.c_uint32, C.c_uint32, C.c_int, C.c_int,
+                                           C.c_ulonglong, C.POINTER(C.c_int32), C.POINTER(C.c_int)]
     L.enum_check_level_sets.restype = C.c_int
     L.enum_check_level_sets.argtypes = [C.c_int, C.c_int, C.c_int, C.c_uint32, C.POINTER(C.c_uint32), C.c_int]
     return L
@@ -135,3 +138,33 @@ def test_core_nil_pad_vector_D5(harness, oracle):
     W, nl = syn.links_to_weights(t)
     got, _, _ = run(harness, W, [0, 1, 2, 3, 4], [], 3, False, 1)
     assert got == [0, 1, -1]
+
+
+@pytest.mark.parametrize("nt", [8, 12])
+def test_core_sparse_label_masks_match_oracle(harness, oracle, nt):
+    """the canonical-order layout: devices = set bits of a label mask, one score table per topology"""
+    rng = np.random.default_rng(nt)
+    W, nl = syn.links_to_weights(syn.topo_random(nt, 40 + nt))
+    # asymmetric weights too: the earlier label's view must be used
+    W = W.copy()
+    W[np.triu_indices(nt, 1)] += 10
+    Wc = np.ascontiguousarray(W, dtype=np.int32)
+    done = 0
+    for _ in range(600):
+        mask = int(rng.integers(1, 1 << nt))
+        labels = [b for b in range(nt) if mask >> b & 1]
+        if len(labels) < 2 or oracle.partition_count(len(labels), 2) > 20000:
+            continue
+        k = int(rng.integers(2, len(labels) + 1))
+        req = [int(x) for x in rng.choice(labels, size=int(rng.integers(0, min(k, 2) + 1)), replace=False)]
+        rmask = sum(1 << r for r in req)
+        for mode in (oracle.GO_FAITHFUL, oracle.INTENDED):
+            want = oracle.besteffort(W, nl, labels, req, k, mode, "fast")
+            out = np.zeros(64, dtype=np.int32)
+            n_out = C.c_int(0)
+            rc = harness.enum_check_search_sparse(nt, Wc.ctypes.data_as(C.POINTER(C.c_int32)), mask, rmask, k,
+                                                  int(mode == oracle.INTENDED), int(rng.choice([1, 50, 10**9])),
+                                                  out.ctypes.data_as(C.POINTER(C.c_int32)), C.byref(n_out))
+            assert rc == 0 and (oracle.OK, [int(x) for x in out[:n_out.value]]) == want, (mask, k, req, mode)
+        done += 1
+    assert done > 300

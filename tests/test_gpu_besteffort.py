@@ -20,9 +20,11 @@ def ctx():
     c.close()
 
 
-def install(ctx, links2):
+def install(ctx, links2, order=None):
+    """installs a topology; order = the node-wide device order (None = NVML index order)"""
     W, nl = syn.links_to_weights(links2)
     ctx.set_topology_links(links2)
+    ctx.set_device_order(list(range(links2.shape[0])) if order is None else order)
     W2, nl2 = ctx.get_topology()
     assert (W2 == W).all() and (nl2 == nl).all()  # the ABI's score switch == the numpy statement of it
     return W, nl
@@ -41,11 +43,14 @@ def assert_batch_equal(got, want, reqs, what):
             what, len(bad), i, syn.unpack_request(reqs[i]), got["dev"][i].tolist(), want["dev"][i].tolist()))
 
 
+@pytest.mark.parametrize("canonical", [True, False], ids=["canonical-order", "foreign-order"])
 @pytest.mark.parametrize("topo_i", range(14))
-def test_batch_exhaustive_n8_all_masks_all_sizes(ctx, oracle, topo_i):
-    """config 1: every non-empty mask x k = 1..|mask| x required in {none, each single, seeded pairs}"""
+def test_batch_exhaustive_n8_all_masks_all_sizes(ctx, oracle, topo_i, canonical):
+    """config 1: every non-empty mask x k = 1..|mask| x required in {none, each single, seeded pairs}.
+    canonical: the context knows the node's sorted-UUID order, so every request takes the fast kernel;
+    otherwise the requests' order is foreign to the context and the general kernel answers them."""
     name, t = syn.standard_topologies()[topo_i]
-    W, nl = install(ctx, t)
+    W, nl = install(ctx, t, ORDER8 if canonical else None)
     reqs = syn.pack_requests(list(syn.exhaustive_requests(ORDER8, seed=topo_i, n_pairs=8)))
     assert len(reqs) > 9000
     for mode in (gpa.MODE_GO_FAITHFUL, gpa.MODE_INTENDED):
@@ -180,13 +185,55 @@ def test_slice_aliasing_D6(ctx, oracle, n):
         assert ctx.besteffort(avail, [], 2, gpa.MODE_INTENDED)[1] == [n - 2, n - 1]
 
 
-def test_batch_n9_to_n12(ctx, oracle):
-    """the batch kernel up to GPA_BATCH_MAX_AVAILABLE devices per request"""
-    W, nl = install(ctx, syn.topo_random(12, 11))
-    reqs = syn.random_request_batch(12, 3000, seed=12)
+@pytest.mark.parametrize("canonical", [True, False])
+def test_batch_n9_to_n12(ctx, oracle, canonical):
+    """the batch kernels up to GPA_BATCH_MAX_AVAILABLE devices per request"""
+    order = [int(x) for x in np.random.default_rng(3).permutation(12)]
+    W, nl = install(ctx, syn.topo_random(12, 11), order if canonical else None)
+    reqs = syn.random_request_batch(12, 3000, seed=12, order=order)
     for mode in (gpa.MODE_GO_FAITHFUL, gpa.MODE_INTENDED):
         got = ctx.besteffort_batch(reqs, mode)
         assert_batch_equal(got, oracle_batch(oracle, W, nl, reqs, mode), reqs, "n12")
+
+
+def test_batch_mixed_canonical_and_foreign_orders_in_one_launch(ctx, oracle):
+    """half the records list devices in the node order (fast kernel), half in a shuffled order (deferred to the
+    general kernel inside the same call); plus records with an unknown device and with a duplicate"""
+    W, nl = install(ctx, syn.topo_dgx1v_like(), ORDER8)
+    a = syn.random_request_batch(8, 20000, seed=31, order=ORDER8)
+    rng = np.random.default_rng(32)
+    b_list = []
+    for _ in range(5000):
+        n = int(rng.integers(1, 9))
+        avail = [int(x) for x in rng.permutation(8)[:n]]
+        req = [avail[int(rng.integers(n))]] if rng.random() < 0.3 else []
+        b_list.append((avail, req, int(rng.integers(1, n + 1))))
+    b = syn.pack_requests(b_list)
+    reqs = np.concatenate([a, b])
+    reqs = reqs[rng.permutation(len(reqs))]
+    got = ctx.besteffort_batch(reqs)
+    assert_batch_equal(got, oracle_batch(oracle, W, nl, reqs, 0), reqs, "mixed")
+    assert (got["dev"][:, 0] != -126).all()  # the internal "deferred" mark never leaves the library
+    odd = syn.pack_requests([([0, 1, 200], [], 2), ([0, 1, 1], [], 2), ([5, 3], [], 2)])
+    res = ctx.besteffort_batch(odd)
+    assert gpa.decode_result(res[0])[0] == gpa.ERR_INVALID and gpa.decode_result(res[1])[0] == gpa.ERR_INVALID
+    assert gpa.decode_result(res[2]) == (gpa.OK, [5, 3])
+
+
+def test_fast_path_is_bypassed_for_big_or_asymmetric_nodes(ctx, oracle):
+    """more than 12 devices on the node, or asymmetric link counts: the general kernel takes the whole batch"""
+    W, nl = install(ctx, syn.topo_random(16, 2))
+    reqs = syn.random_request_batch(16, 2000, seed=5)
+    reqs = reqs[reqs["n_avail"] <= 12]
+    assert_batch_equal(ctx.besteffort_batch(reqs), oracle_batch(oracle, W, nl, reqs, 0), reqs, "nt16")
+    W, nl = syn.links_to_weights(syn.topo_random(8, 3))
+    nl = nl.copy()
+    nl[2, 5] += 1
+    ctx.set_topology(W, nl)
+    reqs = syn.random_request_batch(8, 4000, seed=6)
+    got = ctx.besteffort_batch(reqs)
+    assert_batch_equal(got, oracle_batch(oracle, W, nl, reqs, 0), reqs, "asym")
+    assert (got["dev"][:, 0] == gpa.RES_ERROR).sum() > 50
 
 
 def test_batch_stream_scale_independent_properties(ctx, oracle):
@@ -194,7 +241,7 @@ def test_batch_stream_scale_independent_properties(ctx, oracle):
     (2) every answer is empty or `size` distinct available devices containing the required
     one, (3) relabelling invariance: scaling all weights by a constant changes nothing,
     (4) a second identical call gives identical bytes (no state leaks between launches)"""
-    W, nl = install(ctx, syn.topo_dgx1v_like())
+    W, nl = install(ctx, syn.topo_dgx1v_like(), ORDER8)
     reqs = syn.random_request_batch(8, 1 << 20, seed=2, order=ORDER8)
     got = ctx.besteffort_batch(reqs)
     idx = np.random.default_rng(0).choice(len(reqs), 50000, replace=False)
@@ -222,7 +269,7 @@ def test_batch_stream_scale_independent_properties(ctx, oracle):
 def test_device_resident_batch_on_a_torch_stream(ctx, oracle):
     """gpa_besteffort_batch_device: inputs and outputs already in HBM, caller's stream"""
     import torch
-    W, nl = install(ctx, syn.topo_two_sockets(8))
+    W, nl = install(ctx, syn.topo_two_sockets(8), ORDER8)
     reqs = syn.random_request_batch(8, 100000, seed=7, order=ORDER8)
     d_in = torch.from_numpy(reqs.view(np.uint8).reshape(-1, 32)).cuda()
     d_out = torch.zeros((len(reqs), 16), dtype=torch.int8, device="cuda")
@@ -250,7 +297,12 @@ def test_pinned_host_buffers(ctx, oracle):
 def test_batch_max_avail_hint(ctx, oracle):
     W, nl = install(ctx, syn.topo_two_sockets(8))
     reqs = syn.pack_requests([([0, 1, 2, 3, 4, 5], [], 2), ([0, 1, 2], [], 2)])
+    want0 = oracle.besteffort(W, nl, [0, 1, 2, 3, 4, 5], [], 2)[1]
     got = ctx.besteffort_batch(reqs, max_avail=4)      # the caller lied: 6 devices in the first record
+    # the fast kernel does not need the hint and answers; the general kernel sizes its tables by it and refuses
+    assert gpa.decode_result(got[0]) in ((gpa.ERR_TOO_LARGE, []), (gpa.OK, want0))
+    ctx.set_device_order([5, 4, 3, 2, 1, 0, 6, 7])     # now the records are not in node order: general kernel
+    got = ctx.besteffort_batch(reqs, max_avail=4)
     assert gpa.decode_result(got[0])[0] == gpa.ERR_TOO_LARGE
     assert gpa.decode_result(got[1]) == (gpa.OK, oracle.besteffort(W, nl, [0, 1, 2], [], 2)[1])
     got = ctx.besteffort_batch(reqs, max_avail=8)
@@ -261,6 +313,6 @@ def test_launch_counter_counts_kernels(ctx):
     install(ctx, syn.topo_two_sockets(8))
     before = ctx.launch_count
     ctx.besteffort(list(range(8)), [], 4)
-    ctx.besteffort_batch(syn.random_request_batch(8, 100, seed=1))
+    ctx.besteffort_batch(syn.random_request_batch(8, 100, seed=1))  # fast kernel + the general kernel's deferred pass
     ctx.besteffort(list(range(8)), [], 1)  # answered by the guards: no kernel
-    assert ctx.launch_count == before + 2
+    assert ctx.launch_count == before + 3
