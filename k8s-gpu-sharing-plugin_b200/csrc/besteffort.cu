@@ -288,13 +288,23 @@ __global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_kernel(cons
 // cmd/nvidia-device-plugin/replica.go:43).  Devices are relabelled by their rank in that
 // order, so a request is just a label MASK, positions are labels, and one score table over
 // all 2^nt label masks serves every request of the node: no per-request table, no gather.
-//   * phase 1, one LANE per request: parse, guards, size-1 answers, tiny searches;
-//   * phase 2, the whole WARP per heavy request: items strided over lanes, shuffle max;
-//   * phase 3, one lane per request again: epilogue and a coalesced 16-byte store.
-// Anything unusual (non-canonical order, unknown device, too many devices) is marked
+//
+// One LANE answers one request.  Requests of different shapes (n available, size k) walk
+// differently shaped trees, and lanes of a warp that take different paths run one after the
+// other, so each CTA first BINS its tile of kTile requests by shape in shared memory
+// (counting sort on n*13+k) and then hands the sorted order to its threads: the 32 lanes of
+// a warp get neighbours in that order, i.e. (almost always) the same shape.
+//   pass 1  coalesced load, parse, guards; trivial answers are stored at once; searches leave
+//           a compact record {label mask, required mask, size} and take a rank in their bin;
+//   pass 2  one warp turns the bin counts into offsets;
+//   pass 3  records are threaded into the sorted index;
+//   pass 4  lane p takes sorted record p: search, epilogue, 16-byte store.
+// Anything unusual (order foreign to the node, unknown device, more than 12 devices) is marked
 // GPA_RES_DEFER for the general kernel.
 constexpr int kFastMaxTopo = 12;
-constexpr uint32_t kLightMaxPartitions = 24;
+constexpr int kTile = 4096;
+constexpr int kFastThreads = 256;
+constexpr int kShapeBins = 13 * 13 + 7;  // n*13 + k for n,k <= 12, padded to 176
 
 struct FastTopo {
   const uint16_t *s_full;  // [1 << nt] scaled set scores over label masks
@@ -316,123 +326,168 @@ __device__ __forceinline__ void res_set_byte(unsigned long long &r0, unsigned lo
   if (i < 8) r0 = (r0 & ~(0xFFull << (8 * i))) | (b << (8 * i));
   else r1 = (r1 & ~(0xFFull << (8 * (i - 8)))) | (b << (8 * (i - 8)));
 }
+__device__ __forceinline__ void res_store(gpa_result *dst, unsigned long long r0, unsigned long long r1) {
+  uint4 v;
+  v.x = (uint32_t)r0;
+  v.y = (uint32_t)(r0 >> 32);
+  v.z = (uint32_t)r1;
+  v.w = (uint32_t)(r1 >> 32);
+  *reinterpret_cast<uint4 *>(dst->dev) = v;
+}
 
-__global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_fast_kernel(const gpa_request *__restrict__ reqs, int count,
-                                                                                 int intended, const FastTopo ft,
-                                                                                 gpa_result *__restrict__ out) {
-  extern __shared__ __align__(16) uint16_t S[];
-  {
-    const uint32_t total = 1u << ft.nt;
-    for (uint32_t i = threadIdx.x; i < total; i += kBatchWarps * 32) S[i] = ft.s_full[i];
-  }
-  __syncthreads();
-  const int lane = threadIdx.x & 31;
-  const int warp = threadIdx.x >> 5;
-  enum { kDone = 0, kLight = 1, kHeavy = 2, kDefer = 3, kIdle = 4 };
+constexpr size_t fast_smem_bytes(int nt) {
+  return ((size_t)1 << nt) * sizeof(uint16_t)  // S
+         + (size_t)kTile * sizeof(uint32_t)    // w_mr
+         + (size_t)kTile * sizeof(uint16_t) * 2  // w_rank, sorted_idx
+         + (size_t)kTile * 2                     // w_k, w_key
+         + (size_t)(kShapeBins + 1) * sizeof(uint32_t) * 2;  // hist, offs
+}
 
-  for (long long base = ((long long)blockIdx.x * kBatchWarps + warp) * 32; base < count;
-       base += (long long)gridDim.x * kBatchWarps * 32) {
-    const long long r = base + lane;
-    int status = kIdle;
-    unsigned long long r0 = 0x8080808080808080ull, r1 = 0x8080808080808080ull;  // 16 x GPA_RES_END
-    uint32_t mask = 0, rlab = 0;
-    int size = 0;
-    unsigned long long key = 0;
-    if (r < count) {
-      const uint4 lo = __ldg(reinterpret_cast<const uint4 *>(reqs + r));
-      const uint4 hi = __ldg(reinterpret_cast<const uint4 *>(reqs + r) + 1);
-      const uint32_t rmask = hi.x & 0xFFFFu;
-      const int n = (hi.x >> 16) & 0xFF;
-      size = (hi.x >> 24) & 0xFF;
-      const int flags = hi.y & 0xFF;
-      const int n_req = __popc(rmask) + ((hi.y >> 8) & 0xFF);
-      status = kDone;
-      // guards of besteffort_policy.go:35-45
-      if (!(size <= 0 || n < size || n_req > size)) {
-        if (n > kFastMaxTopo || (rmask >> n) != 0) {
-          status = kDefer;
-        } else {
-          // relabel: device -> rank in the node order; the list must be strictly ascending
-          const uint32_t w[4] = {lo.x, lo.y, lo.z, lo.w};
-          int prev = -1;
-          int first_dev = 0, first_req_dev = -1;
+__global__ void __launch_bounds__(kFastThreads) besteffort_batch_fast_kernel(const gpa_request *__restrict__ reqs, int count,
+                                                                             int intended, const FastTopo ft,
+                                                                             gpa_result *__restrict__ out) {
+  extern __shared__ __align__(16) unsigned char fsmem[];
+  uint32_t *w_mr = reinterpret_cast<uint32_t *>(fsmem);
+  uint32_t *hist = w_mr + kTile;
+  uint32_t *offs = hist + (kShapeBins + 1);
+  uint16_t *S = reinterpret_cast<uint16_t *>(offs + (kShapeBins + 1));
+  uint16_t *w_rank = S + ((size_t)1 << ft.nt);
+  uint16_t *sorted_idx = w_rank + kTile;
+  uint8_t *w_k = reinterpret_cast<uint8_t *>(sorted_idx + kTile);
+  uint8_t *w_key = w_k + kTile;
+
+  const int tid = threadIdx.x;
+  for (uint32_t i = tid; i < (1u << ft.nt); i += kFastThreads) S[i] = ft.s_full[i];
+
+  const long long n_tiles = ((long long)count + kTile - 1) / kTile;
+  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const long long tile_base = tile * kTile;
+    for (int b = tid; b <= kShapeBins; b += kFastThreads) hist[b] = 0;
+    __syncthreads();
+
+    // ---- pass 1: parse; answer the trivial ones; bin the searches by shape
+#pragma unroll 1
+    for (int i = tid; i < kTile; i += kFastThreads) {
+      const long long r = tile_base + i;
+      int bin = 0xFF;
+      if (r < count) {
+        const uint4 lo = __ldg(reinterpret_cast<const uint4 *>(reqs + r));
+        const uint4 hi = __ldg(reinterpret_cast<const uint4 *>(reqs + r) + 1);
+        const uint32_t rmask = hi.x & 0xFFFFu;
+        const int n = (hi.x >> 16) & 0xFF;
+        const int size = (hi.x >> 24) & 0xFF;
+        const int flags = hi.y & 0xFF;
+        const int n_req = __popc(rmask) + ((hi.y >> 8) & 0xFF);
+        unsigned long long r0 = 0x8080808080808080ull, r1 = 0x8080808080808080ull;  // 16 x GPA_RES_END
+        bool search = false;
+        // guards of besteffort_policy.go:35-45
+        if (!(size <= 0 || n < size || n_req > size)) {
+          if (n > kFastMaxTopo || (rmask >> n) != 0) {
+            res_set_byte(r0, r1, 0, kResDefer);
+          } else {
+            // relabel: device -> rank in the node order; the list must be strictly ascending
+            const uint32_t w[4] = {lo.x, lo.y, lo.z, lo.w};
+            uint32_t mask = 0, rlab = 0;
+            int prev = -1, first_dev = 0, first_req_dev = -1;
+            bool defer = false;
 #pragma unroll
-          for (int p = 0; p < kFastMaxTopo; p++) {
-            if (p < n) {
-              const int d = (w[p >> 2] >> ((p & 3) * 8)) & 0xFF;
-              const int lab = d < GPA_MAX_TOPOLOGY ? ft.rank[d] : 0xFF;
-              if (lab == 0xFF || lab <= prev) status = kDefer;
-              prev = lab;
-              mask |= 1u << (lab & 31);
-              if (rmask >> p & 1u) {
-                rlab |= 1u << (lab & 31);
-                if (first_req_dev < 0) first_req_dev = d;
+            for (int p = 0; p < kFastMaxTopo; p++) {
+              if (p < n) {
+                const int d = (w[p >> 2] >> ((p & 3) * 8)) & 0xFF;
+                const int lab = d < GPA_MAX_TOPOLOGY ? ft.rank[d] : 0xFF;
+                defer = defer || lab == 0xFF || lab <= prev;
+                prev = lab;
+                mask |= 1u << (lab & 31);
+                if (rmask >> p & 1u) {
+                  rlab |= 1u << (lab & 31);
+                  if (first_req_dev < 0) first_req_dev = d;
+                }
+                if (p == 0) first_dev = d;
               }
-              if (p == 0) first_dev = d;
             }
-          }
-          if (status != kDefer) {
-            if (flags & GPA_REQ_FOREIGN) {
+            if (defer) {
+              res_set_byte(r0, r1, 0, kResDefer);
+            } else if (flags & GPA_REQ_FOREIGN) {
               // a required pointer that is in no set: every candidate is rejected (:53) -> empty answer
             } else if (size == 1) {
               // :219-224 — first accepted single-device candidate
               res_set_byte(r0, r1, 0, first_req_dev >= 0 ? first_req_dev : first_dev);
             } else {
-              const uint32_t parts = c_parts[n][size];
-              const int m = (n + size - 1) / size;
-              status = (parts <= kLightMaxPartitions && m <= kMaxSuffix) ? kLight : kHeavy;
+              search = true;
+              w_mr[i] = (mask & 0xFFFFu) | (rlab << 16);
+              w_k[i] = (uint8_t)size;
+              bin = n * 13 + size;
+              w_rank[i] = (uint16_t)atomicAdd(&hist[bin], 1u);
             }
           }
         }
+        if (!search) res_store(out + r, r0, r1);
       }
+      w_key[i] = (uint8_t)bin;
     }
+    __syncthreads();
 
-    // phase 1b: tiny searches, one lane each
-    if (status == kLight) {
-      const Geom g = make_geom_sparse(mask, size, rlab, ft.nt);
-      Cut cut;
-      cut.d = 0;
-      cut.n_items = 1;
+    // ---- pass 2: bin counts -> offsets (one warp, 6 bins per lane)
+    if (tid < 32) {
+      constexpr int kPer = (kShapeBins + 31) / 32;
+      uint32_t local[kPer];
+      uint32_t sum = 0;
 #pragma unroll
-      for (int j = 0; j < kMaxCutDepth; j++) cut.radix[j] = 1;
-      const int sc = fast_search_item(g, cut, S, 0);
-      key = sc >= 0 ? pack_key(sc, 0) : 0ull;
-    }
-
-    // phase 2: heavy searches, the whole warp on one request at a time
-    unsigned heavy = __ballot_sync(0xffffffffu, status == kHeavy);
-    while (heavy) {
-      const int h = __ffs(heavy) - 1;
-      heavy &= heavy - 1;
-      const uint32_t hmask = __shfl_sync(0xffffffffu, mask, h);
-      const uint32_t hrlab = __shfl_sync(0xffffffffu, rlab, h);
-      const int hsize = __shfl_sync(0xffffffffu, size, h);
-      const Geom g = make_geom_sparse(hmask, hsize, hrlab, ft.nt);
-      const Cut cut = choose_cut(g, c_binom, 96);
-      unsigned long long best = 0;
-      for (unsigned long long item = lane; item < cut.n_items; item += 32) {
-        const int sc = fast_search_item(g, cut, S, item);
-        if (sc >= 0) {
-          const unsigned long long kk = pack_key(sc, item);
-          best = kk > best ? kk : best;
-        }
+      for (int q = 0; q < kPer; q++) {
+        const int b = tid * kPer + q;
+        local[q] = b < kShapeBins ? hist[b] : 0u;
+        sum += local[q];
       }
-      best = warp_max_u64(best);
-      if (lane == h) key = best;
+      uint32_t incl = sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (tid >= o) incl += v;
+      }
+      uint32_t run = incl - sum;
+#pragma unroll
+      for (int q = 0; q < kPer; q++) {
+        const int b = tid * kPer + q;
+        if (b < kShapeBins) offs[b] = run;
+        run += local[q];
+      }
+      if (tid == 31) offs[kShapeBins] = incl;
     }
+    __syncthreads();
 
-    // phase 3: epilogue per lane (light and heavy alike), then one coalesced store per lane
-    if (status == kLight || status == kHeavy) {
-      const Geom g = make_geom_sparse(mask, size, rlab, ft.nt);
+    // ---- pass 3: thread the records into shape order
+#pragma unroll 1
+    for (int i = tid; i < kTile; i += kFastThreads) {
+      const int bin = w_key[i];
+      if (bin != 0xFF) sorted_idx[offs[bin] + w_rank[i]] = (uint16_t)i;
+    }
+    __syncthreads();
+
+    // ---- pass 4: one lane per search, neighbours in shape order
+    const int n_search = (int)offs[kShapeBins];
+#pragma unroll 1
+    for (int p = tid; p < n_search; p += kFastThreads) {
+      const int i = sorted_idx[p];
+      const uint32_t mr = w_mr[i];
+      const Geom g = make_geom_sparse(mr & 0xFFFFu, w_k[i], mr >> 16, ft.nt);
       Cut cut;
-      if (status == kHeavy) {
-        cut = choose_cut(g, c_binom, 96);
-      } else {
+      if (g.m <= kMaxSuffix) {
         cut.d = 0;
         cut.n_items = 1;
 #pragma unroll
         for (int j = 0; j < kMaxCutDepth; j++) cut.radix[j] = 1;
+      } else {
+        cut = choose_cut(g, c_binom, 1);  // deep trees: the first m - 4 levels come from an item index
       }
+      unsigned long long key = 0;
+      for (unsigned long long item = 0; item < cut.n_items; item++) {
+        const int sc = fast_search_item(g, cut, S, item);
+        if (sc >= 0) {
+          const unsigned long long kk = pack_key(sc, item);
+          key = kk > key ? kk : key;
+        }
+      }
+      unsigned long long r0 = 0x8080808080808080ull, r1 = 0x8080808080808080ull;
       uint32_t best_set = 0;
       const int rc = fast_finalize(g, cut, S, key, intended != 0, best_set);
       if (rc < 0) {
@@ -447,18 +502,11 @@ __global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_fast_kernel
           res_set_byte(r0, r1, o++, ft.order[lab]);
         }
         if (best_set & g.tok_bit)
-          for (int i = 0; i < g.P; i++) res_set_byte(r0, r1, o++, GPA_NIL);
+          for (int q = 0; q < g.P; q++) res_set_byte(r0, r1, o++, GPA_NIL);
       }
+      res_store(out + tile_base + i, r0, r1);
     }
-    if (status == kDefer) res_set_byte(r0, r1, 0, kResDefer);
-    if (status != kIdle) {
-      uint4 v;
-      v.x = (uint32_t)r0;
-      v.y = (uint32_t)(r0 >> 32);
-      v.z = (uint32_t)r1;
-      v.w = (uint32_t)(r1 >> 32);
-      *reinterpret_cast<uint4 *>(out[r].dev) = v;
-    }
+    __syncthreads();  // the tile's shared arrays are reused by the next tile
   }
 }
 
@@ -584,15 +632,17 @@ int launch_batch(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_ava
   if (count == 0) return GPA_OK;
   if (!ctx->d_sfull) return launch_general(ctx, d_reqs, count, max_avail, mode_flags, d_out, stream, 0);
   // canonical-order fast path, then the general kernel mops up whatever was deferred
-  size_t smem = ((size_t)1 << ctx->fast.nt) * sizeof(uint16_t);
+  size_t smem = fast_smem_bytes(ctx->fast.nt);
+  if (smem > 48 * 1024)
+    CUDA_TRY(ctx, cudaFuncSetAttribute(besteffort_batch_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 1;
-  CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, besteffort_batch_fast_kernel, kBatchWarps * 32, smem));
+  CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, besteffort_batch_fast_kernel, kFastThreads, smem));
   if (occ < 1) occ = 1;
-  long long want = ((long long)count + kBatchWarps * 32 - 1) / (kBatchWarps * 32);
+  long long want = ((long long)count + kTile - 1) / kTile;
   long long cap = (long long)ctx->sm_count * occ;
   int grid = (int)(want < cap ? want : cap);
-  besteffort_batch_fast_kernel<<<grid, kBatchWarps * 32, smem, stream>>>(d_reqs, count, mode_flags & GPA_MODE_INTENDED, ctx->fast,
-                                                                         d_out);
+  besteffort_batch_fast_kernel<<<grid, kFastThreads, smem, stream>>>(d_reqs, count, mode_flags & GPA_MODE_INTENDED, ctx->fast,
+                                                                     d_out);
   ctx->launches++;
   CUDA_TRY(ctx, cudaGetLastError());
   return launch_general(ctx, d_reqs, count, max_avail, mode_flags, d_out, stream, 1);

@@ -304,11 +304,21 @@ GPA_HD ItemState decode_item(const Geom &g, const Cut &cut, const BinomTable &B,
   st.acc = 0;
   st.ok = false;
   st.valid = true;
-  // digits, most significant first
+  // digits, most significant first.  64-bit division is emulated on the GPU (~100 instructions), so it
+  // is only used for the rare searches with more than 2^32 items.
   uint32_t digit[kMaxCutDepth];
-  for (int j = cut.d - 1; j >= 0; j--) {
-    digit[j] = (uint32_t)(item % cut.radix[j]);
-    item /= cut.radix[j];
+  if (cut.n_items <= 0xFFFFFFFFull) {
+    uint32_t it = (uint32_t)item;
+    for (int j = cut.d - 1; j >= 0; j--) {
+      const uint32_t q = it / cut.radix[j];
+      digit[j] = it - q * cut.radix[j];
+      it = q;
+    }
+  } else {
+    for (int j = cut.d - 1; j >= 0; j--) {
+      digit[j] = (uint32_t)(item % cut.radix[j]);
+      item /= cut.radix[j];
+    }
   }
   for (int j = 0; j < cut.d; j++) {
     uint32_t anchor = low_bit(lit);
