@@ -19,8 +19,10 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <algorithm>
 #include <mutex>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/gpualloc.h"
@@ -33,6 +35,9 @@ using namespace gpa;
 __constant__ BinomTable c_binom;
 // candidate partitions of (n available, size k), n,k <= 12, saturated at 2^32-1: work estimate of the fast batch path
 __constant__ uint32_t c_parts[13][13];
+// shape (n, k) -> bin of the fast batch kernel's counting sort: bins are numbered by DESCENDING work, so the sorted
+// order of a tile starts with its most expensive searches (longest-processing-time-first scheduling)
+__constant__ uint8_t c_shape_bin[13][13];
 
 constexpr int kSearchBlockSmall = 256;   // score table <= 32 KB: several CTAs per SM
 constexpr int kSearchBlockLarge = 1024;  // 64-128 KB table: one or two CTAs per SM, so make them wide
@@ -416,7 +421,7 @@ __global__ void __launch_bounds__(kFastThreads) besteffort_batch_fast_kernel(con
               search = true;
               w_mr[i] = (mask & 0xFFFFu) | (rlab << 16);
               w_k[i] = (uint8_t)size;
-              bin = n * 13 + size;
+              bin = c_shape_bin[n][size];
               w_rank[i] = (uint16_t)atomicAdd(&hist[bin], 1u);
             }
           }
@@ -463,10 +468,19 @@ __global__ void __launch_bounds__(kFastThreads) besteffort_batch_fast_kernel(con
     }
     __syncthreads();
 
-    // ---- pass 4: one lane per search, neighbours in shape order
+    // ---- pass 4: one lane per search, neighbours in shape order.  Warps draw chunks of 32 sorted records from
+    // a shared cursor (hist[kShapeBins], zero after pass 1), heaviest shapes first, so no warp is left holding
+    // a long tail while the others wait at the barrier.
     const int n_search = (int)offs[kShapeBins];
+    const int lane = tid & 31;
 #pragma unroll 1
-    for (int p = tid; p < n_search; p += kFastThreads) {
+    for (;;) {
+      int p0 = 0;
+      if (lane == 0) p0 = (int)atomicAdd(&hist[kShapeBins], 32u);
+      p0 = __shfl_sync(0xffffffffu, p0, 0);
+      if (p0 >= n_search) break;
+      const int p = p0 + lane;
+      if (p >= n_search) continue;
       const int i = sorted_idx[p];
       const uint32_t mr = w_mr[i];
       const Geom g = make_geom_sparse(mr & 0xFFFFu, w_k[i], mr >> 16, ft.nt);
@@ -762,6 +776,16 @@ int gpa_create(int cuda_device, gpa_ctx **out) {
         parts[n][k] = c > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)c;
       }
     CREATE_TRY(cudaMemcpyToSymbol(c_parts, parts, sizeof parts));
+    // bins by descending work; at most 13*13 = 169 shapes < kShapeBins
+    std::vector<std::pair<uint32_t, int>> shapes;
+    for (int n = 0; n <= 12; n++)
+      for (int k = 0; k <= 12; k++) shapes.push_back({parts[n][k], n * 13 + k});
+    std::sort(shapes.begin(), shapes.end(), [](const std::pair<uint32_t, int> &a, const std::pair<uint32_t, int> &b) {
+      return a.first != b.first ? a.first > b.first : a.second < b.second;
+    });
+    uint8_t bins[13][13];
+    for (size_t r = 0; r < shapes.size(); r++) bins[shapes[r].second / 13][shapes[r].second % 13] = (uint8_t)r;
+    CREATE_TRY(cudaMemcpyToSymbol(c_shape_bin, bins, sizeof bins));
   }
   CREATE_TRY(cudaDeviceSynchronize());
 #undef CREATE_TRY
