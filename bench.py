@@ -276,14 +276,24 @@ def run_ours(args):
     avg_kernel_s = float(np.mean(kernel_ms)) * 1e-3
     peak, peak_src = measured_peak()
     achieved = alg_bytes / avg_kernel_s / 1e9
+    traffic, traffic_src = None, None
+    tp = os.path.join(ROOT, "profiles", "latest_traffic.json")
+    if os.path.exists(tp):
+        tj = json.load(open(tp))
+        if tj.get("requests_per_launch") == len(reqs):
+            traffic = float(tj["dram_bytes_read"] + tj["dram_bytes_write"])
+            traffic_src = tj["source"]
     roofline = {
-        "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-        "kernel": "besteffort_batch_kernel", "peak_source": peak_src + ", burst",
+        "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+        "traffic_source": traffic_src,
+        "kernel": "besteffort_batch_fast_kernel (+ besteffort_batch_kernel deferred pass, ~1% of the step)",
+        "peak_source": peak_src + ", burst",
         "algorithmic_bytes_per_launch": alg_bytes,
         "io_bytes_per_launch": 48.0 * len(reqs), "io_gbs": 48.0 * len(reqs) / avg_kernel_s / 1e9,
         "note": "algorithmic bytes = 4 B x pair evaluations the reference performs (SURVEY.md 8d); the kernel reads "
                 "set scores from a shared-memory table instead, so this is not DRAM traffic; io_* is the real "
-                "request+result traffic",
+                "request+result traffic and `traffic` the DRAM bytes ncu saw for one launch. The kernel is "
+                "instruction-issue bound, not HBM bound (DESIGN.md 4)",
     }
 
     # ---- CPU baseline: the oracle on one core, bounded sample ---------------------------
@@ -321,6 +331,75 @@ def run_ours(args):
     ctx.set_topology_links(t)
     ctx.set_device_order(order)
 
+    # ---- latency of ONE decision through the C ABI, next to the oracle: small searches lose to the CPU -------
+    lat_n8 = []
+    for i in range(2200):
+        t0 = time.perf_counter()
+        ctx.besteffort(order, [], 3)          # n = 8, k = 3: 280 candidate partitions, one launch + D2H + sync
+        lat_n8.append(time.perf_counter() - t0)
+    lat_n8 = np.array(lat_n8[200:]) * 1e6
+    cpu_n8 = []
+    for i in range(2200):
+        t0 = time.perf_counter()
+        orc.besteffort(W, nl, order, [], 3)
+        cpu_n8.append(time.perf_counter() - t0)
+    cpu_n8 = np.array(cpu_n8[200:]) * 1e6
+    t0 = time.perf_counter()
+    orc.besteffort(W16, nl16, list(range(16)), [], 3)
+    cpu_n16_ms = (time.perf_counter() - t0) * 1e3
+    latency = {
+        "single_decision_n8_k3_us": {"gpu_call_p50": float(np.percentile(lat_n8, 50)), "gpu_call_p99": float(np.percentile(lat_n8, 99)),
+                                     "oracle_call_p50": float(np.percentile(cpu_n8, 50)), "oracle_call_p99": float(np.percentile(cpu_n8, 99)),
+                                     "note": "both timed from Python through ctypes; for n <= 8 the CPU path wins on latency"},
+        "single_decision_n16_k3_ms": {"gpu_call_p50": search16["call_ms_p50"], "oracle_call": cpu_n16_ms},
+    }
+
+    # ---- replica mode (replicas > 1): the reference answers with prioritizeDevices (server.go:285-296), host code
+    #      here too; decisions/s and Allocate latency at 32 / 128 / 256 virtual devices through the plugin mirror ----
+    replica_mode = {}
+    for reps in (4, 16, 32):
+        uu = syn.node_uuids(N_DEV, seed=1)
+        devs = [{"id": uu[i], "index": str(i), "paths": ["/dev/nvidia%d" % i], "total_memory": 183359, "numa": i // 4,
+                 "nvml_index": i} for i in range(N_DEV)]
+        plug = gpa.Plugin(devs, ctx=ctx, replicas=reps, has_policy=True)
+        ids = [d["ID"] for d in plug.api_devices()]
+        rng = np.random.default_rng(reps)
+        streams = []
+        for _ in range(300):
+            free = [x for x in ids if rng.random() < 0.5]
+            rng.shuffle(free)
+            streams.append(([str(x) for x in free], int(rng.choice([1, 2, 4, 8]))))
+        t0 = time.perf_counter()
+        n_dec = 0
+        answers = []
+        for free, size in streams:
+            try:
+                answers.append(plug.get_preferred_allocation(free, [], size))
+            except gpa.PluginError:
+                answers.append(None)
+            n_dec += 1
+        dt_ours = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        ref_answers = []
+        for free, size in streams:
+            res, kind, _ = orc.prioritize_devices(free, [], size)
+            ref_answers.append(res if kind in ("none", "non_unique") else None)
+        dt_ref = time.perf_counter() - t0
+        alloc_lat = []
+        for a in [x for x in answers if x][:300] * 4:
+            t0 = time.perf_counter()
+            plug.allocate(a)
+            alloc_lat.append(time.perf_counter() - t0)
+        alloc_lat = np.array(alloc_lat) * 1e6
+        replica_mode["%d_virtual_devices" % (N_DEV * reps)] = {
+            "get_preferred_allocation_per_s": n_dec / dt_ours, "oracle_prioritize_per_s": n_dec / dt_ref,
+            "mismatches": int(sum(1 for a, b in zip(answers, ref_answers) if a != b)),
+            "allocate_call_us_p50": float(np.percentile(alloc_lat, 50)), "allocate_call_us_p99": float(np.percentile(alloc_lat, 99)),
+        }
+        plug.close()
+    replica_mode["note"] = ("host C++ behind the C ABI on both sides of the comparison (no parallel work on this branch); timed from "
+                            "Python through ctypes, string marshalling included")
+
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -331,7 +410,7 @@ def run_ours(args):
         "gpu_launches": int(launches),
         "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": sampler.summary(),
         "parity": {"checked": int(len(idx)), "mismatches_device_arm": mismatches, "mismatches_e2e_arm": e2e_mismatch},
-        "search_n16": search16,
+        "search_n16": search16, "latency": latency, "replica_mode": replica_mode,
     }
     print(json.dumps(line))
     if use_dist:
