@@ -326,6 +326,24 @@ __device__ __noinline__ int fast_finalize(const Geom &g, const Cut &cut, const u
   return finalize_set(g, cut, c_binom, STab{S}, key, intended, best_set);
 }
 
+// Whole-tree search of a shallow request (m <= 4 sets) in one lane; returns like finalize_set.
+__device__ __forceinline__ int fast_tracked_search(const Geom &g, const uint16_t *S, bool intended, uint32_t &best_set) {
+  const STab stab{S};
+  Track tr;
+  tr.best = -1;
+  uint32_t path[kMaxSuffix];
+  const uint32_t all = g.real_mask | g.tok_bit;
+  switch (g.m) {
+    case 1: walk_track<1, 1>(g, stab, all, 0, false, path, tr); break;
+    case 2: walk_track<2, 2>(g, stab, all, 0, false, path, tr); break;
+    case 3: walk_track<3, 3>(g, stab, all, 0, false, path, tr); break;
+    default: walk_track<4, 4>(g, stab, all, 0, false, path, tr); break;
+  }
+  best_set = 0;
+  if (tr.best < 0) return 0;  // no accepted partition: bestPartition == nil (:72-74)
+  return choose_from_partition(g, stab, tr.sets, intended, best_set);
+}
+
 __device__ __forceinline__ void res_set_byte(unsigned long long &r0, unsigned long long &r1, int i, int v) {
   unsigned long long b = (unsigned long long)(v & 0xFF);
   if (i < 8) r0 = (r0 & ~(0xFFull << (8 * i))) | (b << (8 * i));
@@ -484,26 +502,25 @@ __global__ void __launch_bounds__(kFastThreads) besteffort_batch_fast_kernel(con
       const int i = sorted_idx[p];
       const uint32_t mr = w_mr[i];
       const Geom g = make_geom_sparse(mr & 0xFFFFu, w_k[i], mr >> 16, ft.nt);
-      Cut cut;
-      if (g.m <= kMaxSuffix) {
-        cut.d = 0;
-        cut.n_items = 1;
-#pragma unroll
-        for (int j = 0; j < kMaxCutDepth; j++) cut.radix[j] = 1;
-      } else {
-        cut = choose_cut(g, c_binom, 1);  // deep trees: the first m - 4 levels come from an item index
-      }
-      unsigned long long key = 0;
-      for (unsigned long long item = 0; item < cut.n_items; item++) {
-        const int sc = fast_search_item(g, cut, S, item);
-        if (sc >= 0) {
-          const unsigned long long kk = pack_key(sc, item);
-          key = kk > key ? kk : key;
-        }
-      }
       unsigned long long r0 = 0x8080808080808080ull, r1 = 0x8080808080808080ull;
       uint32_t best_set = 0;
-      const int rc = fast_finalize(g, cut, S, key, intended != 0, best_set);
+      int rc;
+      if (g.m <= kMaxSuffix) {
+        // the whole tree in this lane, best partition tracked in registers
+        rc = fast_tracked_search(g, S, intended != 0, best_set);
+      } else {
+        // deep trees (k = 2 on 9+ devices): the first m - 4 levels come from an item index, then replay
+        const Cut cut = choose_cut(g, c_binom, 1);
+        unsigned long long key = 0;
+        for (unsigned long long item = 0; item < cut.n_items; item++) {
+          const int sc = fast_search_item(g, cut, S, item);
+          if (sc >= 0) {
+            const unsigned long long kk = pack_key(sc, item);
+            key = kk > key ? kk : key;
+          }
+        }
+        rc = fast_finalize(g, cut, S, key, intended != 0, best_set);
+      }
       if (rc < 0) {
         res_set_byte(r0, r1, 0, GPA_RES_ERROR);
         res_set_byte(r0, r1, 1, GPA_ERR_INVALID);

@@ -263,6 +263,43 @@ GPA_HD void walk_dyn(int L, const Geom &g, const STab &S, uint32_t rem, int acc,
   }
 }
 
+// Tracked walk, for callers that own a whole (shallow) tree: the sets of the first best leaf are kept
+// in registers as the walk goes, so no replay is needed afterwards.  L0 = depth of the tree (all m sets),
+// L = levels still to choose; every index into path[] / tr.sets[] is a compile-time constant.
+struct Track {
+  int best;  // score of the first best accepted leaf, -1 = none
+  uint32_t sets[kMaxSuffix];
+};
+
+template <int L0, int L, typename STab>
+GPA_HD void walk_track(const Geom &g, const STab &S, uint32_t rem, int acc, bool ok, uint32_t (&path)[kMaxSuffix], Track &tr) {
+  if constexpr (L == 1) {
+    bool okk = ok;
+    account_required(g, rem, okk);
+    int sc = acc + (int)S(rem & g.real_mask);
+    if (okk && sc > tr.best) {  // strict `>`: the first best leaf in reference order stays (:57)
+      tr.best = sc;
+#if defined(__CUDACC__)
+#pragma unroll
+#endif
+      for (int i = 0; i < L0 - 1; i++) tr.sets[i] = path[i];
+      tr.sets[L0 - 1] = rem;
+    }
+  } else {
+    uint32_t anchor;
+    Stepper st = make_stepper(g, rem, anchor);
+    uint32_t chosen;
+    if (!st.first(chosen)) return;
+    do {
+      uint32_t set = anchor | chosen;
+      bool okk = ok;
+      if (!account_required(g, set, okk)) continue;
+      path[L0 - L] = set;
+      walk_track<L0, L - 1>(g, S, rem & ~set, acc + (int)S(set & g.real_mask), okk, path, tr);
+    } while (st.next(chosen));
+  }
+}
+
 // ---------------------------------------------------------------------------------------
 // Work items: the first d levels, decoded from a mixed-radix index over LITERAL positions
 // (the P nil pads as positions n..N-1), where every node at depth j has exactly
@@ -388,6 +425,53 @@ GPA_HD int fresh_slots(int m) {
   return L + 1;
 }
 
+// What Allocate() does with the saved bestPartition (:65-88): the partition `sets` (m sets in visiting order)
+// first suffers what Go's aliased append did to it (go_faithful), then the sets containing all `required`
+// devices compete on their own score, first best wins.  returns 1 and the set, or 0 for the empty answer.
+template <typename STab>
+GPA_HD int choose_from_partition(const Geom &g, const STab &S, uint32_t *sets, bool intended, uint32_t &best_set) {
+  if (!intended) {
+    // D6: slots fresh..m-1 of the saved candidate are shared with every later candidate
+    // under the same prefix and end up holding the LAST one: anchor + the highest picks.
+    int f = fresh_slots(g.m);
+    if (f < g.m) {
+      uint32_t rem = g.real_mask | g.tok_bit;
+      for (int s = 0; s < f; s++) rem &= ~sets[s];
+      for (int s = f; s < g.m; s++) {
+        uint32_t reals = rem & g.real_mask;
+        uint32_t set = low_bit(reals);
+        uint32_t cand = reals ^ set;
+        int need = g.t;
+        if (rem & g.tok_bit) {  // the last k-1 literal elements include all P nils
+          set |= g.tok_bit;
+          need -= g.P;
+        }
+        while (need > 0) {
+          uint32_t hp = top_bit(cand);
+          set |= hp;
+          cand ^= hp;
+          need--;
+        }
+        sets[s] = set;
+        rem &= ~set;
+      }
+    }
+  }
+  // :65-85 — no padding test here: a padded set can win (defect D5)
+  int best = -1;
+  best_set = 0;
+  for (int s = 0; s < g.m; s++) {
+    uint32_t set = sets[s];
+    if ((set & g.rmask) != g.rmask) continue;
+    int sc = (int)S(set & g.real_mask);
+    if (sc > best) {
+      best = sc;
+      best_set = set;
+    }
+  }
+  return best < 0 ? 0 : 1;
+}
+
 // Epilogue (:65-88) for the winning item: replay it to recover the first best partition,
 // apply what Go's slice aliasing does to the saved bestPartition (go_faithful), filter
 // the sets by `required` and return the first best-scoring one.
@@ -407,46 +491,7 @@ GPA_HD int finalize_set(const Geom &g, const Cut &cut, const BinomTable &B, cons
   walk_dyn(g.m - cut.d, g, S, st.rem, st.acc, st.ok, dummy, &rec);
   if (!st.valid || !rec.found) return -1;
 
-  if (!intended) {
-    // D6: slots fresh..m-1 of the saved candidate are shared with every later candidate
-    // under the same prefix and end up holding the LAST one: anchor + the highest picks.
-    int f = fresh_slots(g.m);
-    if (f < g.m) {
-      uint32_t rem = g.real_mask | g.tok_bit;
-      for (int s = 0; s < f; s++) rem &= ~rec.sets[s];
-      for (int s = f; s < g.m; s++) {
-        uint32_t reals = rem & g.real_mask;
-        uint32_t set = low_bit(reals);
-        uint32_t cand = reals ^ set;
-        int need = g.t;
-        if (rem & g.tok_bit) {  // the last k-1 literal elements include all P nils
-          set |= g.tok_bit;
-          need -= g.P;
-        }
-        while (need > 0) {
-          uint32_t hp = top_bit(cand);
-          set |= hp;
-          cand ^= hp;
-          need--;
-        }
-        rec.sets[s] = set;
-        rem &= ~set;
-      }
-    }
-  }
-
-  // :65-85 — no padding test here: a padded set can win (defect D5)
-  int best = -1;
-  for (int s = 0; s < g.m; s++) {
-    uint32_t set = rec.sets[s];
-    if ((set & g.rmask) != g.rmask) continue;
-    int sc = (int)S(set & g.real_mask);
-    if (sc > best) {
-      best = sc;
-      best_set = set;
-    }
-  }
-  return best < 0 ? 0 : 1;
+  return choose_from_partition(g, S, rec.sets, intended, best_set);
 }
 
 //   out_pos[0..k): positions in ascending order, -1 for each nil pad.  returns k, 0, or -1.

@@ -102,3 +102,43 @@ extern "C" int enum_check_search_sparse(int nt, const int32_t *W, uint32_t real_
   *n_out = cnt;
   return 0;
 }
+
+// Tracked whole-tree walk (the lane-per-request path of the fast batch kernel), sparse layout.
+extern "C" int enum_check_tracked_sparse(int nt, const int32_t *W, uint32_t real_mask, uint32_t rmask, int size, int intended,
+                                         int32_t *out, int *n_out) {
+  using namespace gpa;
+  *n_out = 0;
+  std::vector<uint16_t> S((size_t)1 << nt, 0);
+  for (uint32_t mask = 1; mask < (1u << nt); mask++) {
+    int s = 0;
+    for (int a = 0; a < nt; a++)
+      if (mask >> a & 1)
+        for (int b = a + 1; b < nt; b++)
+          if (mask >> b & 1) s += W[a * nt + b];
+    S[mask] = (uint16_t)s;
+  }
+  auto Sf = [&](uint32_t mask) { return S[mask]; };
+  Geom g = make_geom_sparse(real_mask, size, rmask, nt);
+  if (size < 2 || g.n < size || g.m > kMaxSuffix) return -1;
+  Track tr;
+  tr.best = -1;
+  uint32_t path[kMaxSuffix];
+  const uint32_t all = g.real_mask | g.tok_bit;
+  switch (g.m) {
+    case 1: walk_track<1, 1>(g, Sf, all, 0, false, path, tr); break;
+    case 2: walk_track<2, 2>(g, Sf, all, 0, false, path, tr); break;
+    case 3: walk_track<3, 3>(g, Sf, all, 0, false, path, tr); break;
+    default: walk_track<4, 4>(g, Sf, all, 0, false, path, tr); break;
+  }
+  if (tr.best < 0) return 0;
+  uint32_t best_set = 0;
+  if (choose_from_partition(g, Sf, tr.sets, intended != 0, best_set) > 0) {
+    int o = 0;
+    for (int b = 0; b < nt; b++)
+      if (best_set >> b & 1) out[o++] = b;
+    if (best_set & g.tok_bit)
+      for (int i = 0; i < g.P; i++) out[o++] = -1;
+    *n_out = o;
+  }
+  return 0;
+}

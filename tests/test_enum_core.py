@@ -30,6 +30,9 @@ def harness():
     L.enum_check_search_sparse.restype = C.c_int
     L.enum_check_search_sparse.argtypes = [C.c_int, C.POINTER(C.c_int32), C.c_uint32, C.c_uint32, C.c_int, C.c_int,
                                            C.c_ulonglong, C.POINTER(C.c_int32), C.POINTER(C.c_int)]
+    L.enum_check_tracked_sparse.restype = C.c_int
+    L.enum_check_tracked_sparse.argtypes = [C.c_int, C.POINTER(C.c_int32), C.c_uint32, C.c_uint32, C.c_int, C.c_int,
+                                            C.POINTER(C.c_int32), C.POINTER(C.c_int)]
     L.enum_check_level_sets.restype = C.c_int
     L.enum_check_level_sets.argtypes = [C.c_int, C.c_int, C.c_int, C.c_uint32, C.POINTER(C.c_uint32), C.c_int]
     return L
@@ -166,5 +169,12 @@ def test_core_sparse_label_masks_match_oracle(harness, oracle, nt):
                                                   int(mode == oracle.INTENDED), int(rng.choice([1, 50, 10**9])),
                                                   out.ctypes.data_as(C.POINTER(C.c_int32)), C.byref(n_out))
             assert rc == 0 and (oracle.OK, [int(x) for x in out[:n_out.value]]) == want, (mask, k, req, mode)
+            if -(-len(labels) // k) <= 4:  # the tracked whole-tree walk covers trees of up to 4 sets
+                out2 = np.zeros(64, dtype=np.int32)
+                n2 = C.c_int(0)
+                rc = harness.enum_check_tracked_sparse(nt, Wc.ctypes.data_as(C.POINTER(C.c_int32)), mask, rmask, k,
+                                                       int(mode == oracle.INTENDED), out2.ctypes.data_as(C.POINTER(C.c_int32)),
+                                                       C.byref(n2))
+                assert rc == 0 and (oracle.OK, [int(x) for x in out2[:n2.value]]) == want, ("tracked", mask, k, req, mode)
         done += 1
     assert done > 300
