@@ -161,6 +161,28 @@ int gpa_besteffort_batch_device(gpa_ctx *ctx, const gpa_request *d_reqs, int cou
                                 gpa_result *d_out, void *stream);
 #define GPA_BATCH_MAX_AVAILABLE 12 /* larger requests go through gpa_besteffort() one by one */
 
+/* The same batch for callers that already hold device MASKS: bit b of a mask = the device with rank b in the order
+ * given to gpa_set_device_order() (sorted-UUID order in the reference).  8 bytes in, 4 bytes out per decision instead
+ * of 32 + 16, which matters when the records cross PCIe.  Available for nodes of up to 12 GPUs with symmetric link
+ * counts (else GPA_ERR_TOO_LARGE).  `available` is by construction in node order, the reference's own order.
+ * ref: the same loop over r.ContainerRequests, server.go:273-311 -> Policy.Allocate (:298). */
+typedef struct gpa_mask_request {
+  uint16_t avail_mask;   /* available devices */
+  uint16_t req_mask;     /* required devices; one that is not available makes the answer empty */
+  uint8_t size;          /* allocation size */
+  uint8_t flags;         /* GPA_REQ_* */
+  uint8_t n_req_extra;   /* required devices not representable in req_mask (count only, for the len(required) > size guard) */
+  uint8_t reserved;
+} gpa_mask_request;
+typedef struct gpa_mask_result {
+  uint16_t chosen_mask;  /* chosen devices; 0 with n_nil == 0: the empty answer */
+  uint8_t n_nil;         /* nil pads in the returned set */
+  int8_t status;         /* GPA_OK or a GPA_ERR_* code for this record */
+} gpa_mask_result;
+int gpa_besteffort_batch_masks(gpa_ctx *ctx, const gpa_mask_request *reqs, int count, int mode_flags, gpa_mask_result *out);
+int gpa_besteffort_batch_masks_device(gpa_ctx *ctx, const gpa_mask_request *d_reqs, int count, int mode_flags,
+                                      gpa_mask_result *d_out, void *stream);
+
 /* Page-locked host memory for batch buffers: gpa_besteffort_batch() DMAs such buffers directly and stages pageable
  * ones through an internal pinned mailbox.  (No reference counterpart: Go has no device copies to feed.) */
 void *gpa_alloc_host(size_t bytes);

@@ -65,6 +65,10 @@ def lib():
     L.gpa_last_search_stats.argtypes = [vp, C.POINTER(SearchStats)]
     L.gpa_besteffort_batch.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp]
     L.gpa_besteffort_batch_device.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp]
+    L.gpa_besteffort_batch_masks.restype = C.c_int
+    L.gpa_besteffort_batch_masks.argtypes = [vp, vp, C.c_int, C.c_int, vp]
+    L.gpa_besteffort_batch_masks_device.restype = C.c_int
+    L.gpa_besteffort_batch_masks_device.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp]
     L.gpa_alloc_host.restype = vp
     L.gpa_alloc_host.argtypes = [C.c_size_t]
     L.gpa_free_host.restype = None
@@ -214,6 +218,20 @@ class Context:
         self._check(lib().gpa_besteffort_batch(self._h, reqs.ctypes.data, len(reqs), int(max_avail), int(mode),
                                                out.ctypes.data))
         return out
+
+    def besteffort_batch_masks(self, reqs, mode=MODE_GO_FAITHFUL, out=None):
+        """reqs: numpy array of synthetic.MASK_REQ_DTYPE (host memory) -> array of MASK_RES_DTYPE"""
+        from . import synthetic as syn
+        reqs = np.ascontiguousarray(reqs)
+        assert reqs.dtype == syn.MASK_REQ_DTYPE
+        if out is None:
+            out = np.zeros(len(reqs), dtype=syn.MASK_RES_DTYPE)
+        self._check(lib().gpa_besteffort_batch_masks(self._h, reqs.ctypes.data, len(reqs), int(mode), out.ctypes.data))
+        return out
+
+    def besteffort_batch_masks_device(self, d_reqs_ptr, count, d_out_ptr, mode=MODE_GO_FAITHFUL, stream=None):
+        self._check(lib().gpa_besteffort_batch_masks_device(self._h, C.c_void_p(d_reqs_ptr), int(count), int(mode),
+                                                            C.c_void_p(d_out_ptr), C.c_void_p(stream or 0)))
 
     def besteffort_batch_device(self, d_reqs_ptr, count, max_avail, d_out_ptr, mode=MODE_GO_FAITHFUL, stream=None):
         self._check(lib().gpa_besteffort_batch_device(self._h, C.c_void_p(d_reqs_ptr), int(count), int(max_avail),

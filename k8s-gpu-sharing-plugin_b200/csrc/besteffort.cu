@@ -440,9 +440,16 @@ constexpr size_t fast_smem_bytes(int nt) {
          + (size_t)(kShapeBins + 1) * sizeof(uint32_t) * 2;  // hist, offs
 }
 
-__global__ void __launch_bounds__(kFastThreads) besteffort_batch_fast_kernel(const gpa_request *__restrict__ reqs, int count,
+// kMasks = false: 32-byte gpa_request in, 16-byte gpa_result out.
+// kMasks = true : 8-byte gpa_mask_request in (the caller already holds label masks), 4-byte gpa_mask_result out.
+template <bool kMasks>
+__global__ void __launch_bounds__(kFastThreads) besteffort_batch_fast_kernel(const void *__restrict__ reqs_v, int count,
                                                                              int intended, const FastTopo ft,
-                                                                             gpa_result *__restrict__ out) {
+                                                                             void *__restrict__ out_v) {
+  const gpa_request *__restrict__ reqs = static_cast<const gpa_request *>(reqs_v);
+  gpa_result *__restrict__ out = static_cast<gpa_result *>(out_v);
+  const uint2 *__restrict__ mreqs = static_cast<const uint2 *>(reqs_v);
+  uint32_t *__restrict__ mout = static_cast<uint32_t *>(out_v);
   extern __shared__ __align__(16) unsigned char fsmem[];
   uint32_t *w_mr = reinterpret_cast<uint32_t *>(fsmem);
   uint32_t *hist = w_mr + kTile;
@@ -468,6 +475,32 @@ __global__ void __launch_bounds__(kFastThreads) besteffort_batch_fast_kernel(con
       const long long r = tile_base + i;
       int bin = 0xFF;
       if (r < count) {
+        if constexpr (kMasks) {
+          // {avail_mask:16, req_mask:16} {size:8, flags:8, n_req_extra:8, reserved:8}
+          const uint2 rec = __ldg(mreqs + r);
+          const uint32_t mask = rec.x & 0xFFFFu, rlab_in = rec.x >> 16;
+          const int size = rec.y & 0xFF, flags = (rec.y >> 8) & 0xFF;
+          const int n = __popc(mask);
+          const int n_req = __popc(rlab_in) + ((rec.y >> 16) & 0xFF);
+          uint32_t result = 0;  // {chosen_mask:16, n_nil:8, status:8}: the empty answer
+          bool search = false;
+          if ((mask >> ft.nt) != 0 || (rlab_in >> ft.nt) != 0) {
+            result = (uint32_t)(GPA_ERR_INVALID & 0xFF) << 24;
+          } else if (!(size <= 0 || n < size || n_req > size)) {  // guards of besteffort_policy.go:35-45
+            if ((flags & GPA_REQ_FOREIGN) || (rlab_in & ~mask) != 0) {
+              // a required device that is not available is in no set (:53) -> empty answer
+            } else if (size == 1) {
+              result = rlab_in ? (rlab_in & (0u - rlab_in)) : (mask & (0u - mask));  // :219-224
+            } else {
+              search = true;
+              w_mr[i] = mask | (rlab_in << 16);
+              w_k[i] = (uint8_t)size;
+              bin = c_shape_bin[n][size];
+              w_rank[i] = (uint16_t)atomicAdd(&hist[bin], 1u);
+            }
+          }
+          if (!search) mout[r] = result;
+        } else {
         const uint4 lo = __ldg(reinterpret_cast<const uint4 *>(reqs + r));
         const uint4 hi = __ldg(reinterpret_cast<const uint4 *>(reqs + r) + 1);
         const uint32_t rmask = hi.x & 0xFFFFu;
@@ -519,6 +552,7 @@ __global__ void __launch_bounds__(kFastThreads) besteffort_batch_fast_kernel(con
           }
         }
         if (!search) res_store(out + r, r0, r1);
+        }
       }
       w_key[i] = (uint8_t)bin;
     }
@@ -595,21 +629,28 @@ __global__ void __launch_bounds__(kFastThreads) besteffort_batch_fast_kernel(con
         }
         rc = fast_finalize(g, cut, S, key, intended != 0, best_set);
       }
-      if (rc < 0) {
-        res_set_byte(r0, r1, 0, GPA_RES_ERROR);
-        res_set_byte(r0, r1, 1, GPA_ERR_INVALID);
-      } else if (rc > 0) {
-        int o = 0;
-        uint32_t reals = best_set & g.real_mask;
-        while (reals) {
-          const int lab = __ffs(reals) - 1;
-          reals &= reals - 1;
-          res_set_byte(r0, r1, o++, ft.order[lab]);
+      if constexpr (kMasks) {
+        uint32_t result = 0;
+        if (rc < 0) result = (uint32_t)(GPA_ERR_INVALID & 0xFF) << 24;
+        else if (rc > 0) result = (best_set & g.real_mask) | ((best_set & g.tok_bit) ? ((uint32_t)g.P << 16) : 0u);
+        mout[tile_base + i] = result;
+      } else {
+        if (rc < 0) {
+          res_set_byte(r0, r1, 0, GPA_RES_ERROR);
+          res_set_byte(r0, r1, 1, GPA_ERR_INVALID);
+        } else if (rc > 0) {
+          int o = 0;
+          uint32_t reals = best_set & g.real_mask;
+          while (reals) {
+            const int lab = __ffs(reals) - 1;
+            reals &= reals - 1;
+            res_set_byte(r0, r1, o++, ft.order[lab]);
+          }
+          if (best_set & g.tok_bit)
+            for (int q = 0; q < g.P; q++) res_set_byte(r0, r1, o++, GPA_NIL);
         }
-        if (best_set & g.tok_bit)
-          for (int q = 0; q < g.P; q++) res_set_byte(r0, r1, o++, GPA_NIL);
+        res_store(out + tile_base + i, r0, r1);
       }
-      res_store(out + tile_base + i, r0, r1);
     }
     __syncthreads();  // the tile's shared arrays are reused by the next tile
   }
@@ -732,24 +773,29 @@ int launch_general(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_a
   return GPA_OK;
 }
 
+int launch_fast(gpa_ctx *ctx, const void *d_reqs, int count, int mode_flags, void *d_out, cudaStream_t stream, bool masks) {
+  auto kern = masks ? besteffort_batch_fast_kernel<true> : besteffort_batch_fast_kernel<false>;
+  size_t smem = fast_smem_bytes(ctx->fast.nt);
+  if (smem > 48 * 1024) CUDA_TRY(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 1;
+  CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kFastThreads, smem));
+  if (occ < 1) occ = 1;
+  long long want = ((long long)count + kTile - 1) / kTile;
+  long long cap = (long long)ctx->sm_count * occ;
+  int grid = (int)(want < cap ? want : cap);
+  kern<<<grid, kFastThreads, smem, stream>>>(d_reqs, count, mode_flags & GPA_MODE_INTENDED, ctx->fast, d_out);
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return GPA_OK;
+}
+
 int launch_batch(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_avail, int mode_flags, gpa_result *d_out,
                  cudaStream_t stream) {
   if (count == 0) return GPA_OK;
   if (!ctx->d_sfull) return launch_general(ctx, d_reqs, count, max_avail, mode_flags, d_out, stream, 0);
   // canonical-order fast path, then the general kernel mops up whatever was deferred
-  size_t smem = fast_smem_bytes(ctx->fast.nt);
-  if (smem > 48 * 1024)
-    CUDA_TRY(ctx, cudaFuncSetAttribute(besteffort_batch_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int occ = 1;
-  CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, besteffort_batch_fast_kernel, kFastThreads, smem));
-  if (occ < 1) occ = 1;
-  long long want = ((long long)count + kTile - 1) / kTile;
-  long long cap = (long long)ctx->sm_count * occ;
-  int grid = (int)(want < cap ? want : cap);
-  besteffort_batch_fast_kernel<<<grid, kFastThreads, smem, stream>>>(d_reqs, count, mode_flags & GPA_MODE_INTENDED, ctx->fast,
-                                                                     d_out);
-  ctx->launches++;
-  CUDA_TRY(ctx, cudaGetLastError());
+  int rc = launch_fast(ctx, d_reqs, count, mode_flags, d_out, stream, false);
+  if (rc != GPA_OK) return rc;
   return launch_general(ctx, d_reqs, count, max_avail, mode_flags, d_out, stream, 1);
 }
 
@@ -1191,6 +1237,60 @@ int gpa_besteffort_batch(gpa_ctx *ctx, const gpa_request *reqs, int count, int m
   }
   if (rc != GPA_OK) return rc;
   if (!pinned) memcpy(out, ctx->h_out, (size_t)count * sizeof(gpa_result));
+  return GPA_OK;
+}
+
+int gpa_besteffort_batch_masks_device(gpa_ctx *ctx, const gpa_mask_request *d_reqs, int count, int mode_flags,
+                                      gpa_mask_result *d_out, void *stream) {
+  if (!ctx || count < 0 || (count > 0 && (!d_reqs || !d_out))) return GPA_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  if (!ctx->has_topo) return GPA_ERR_NO_TOPOLOGY;
+  if (!ctx->d_sfull) return GPA_ERR_TOO_LARGE;  // masks need the node-wide score table: <= 12 GPUs, symmetric link counts
+  if (count == 0) return GPA_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  return launch_fast(ctx, d_reqs, count, mode_flags, d_out, (cudaStream_t)stream, true);
+}
+
+int gpa_besteffort_batch_masks(gpa_ctx *ctx, const gpa_mask_request *reqs, int count, int mode_flags, gpa_mask_result *out) {
+  if (!ctx || count < 0 || (count > 0 && (!reqs || !out))) return GPA_ERR_INVALID;
+  if (count == 0) return GPA_OK;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  if (!ctx->has_topo) return GPA_ERR_NO_TOPOLOGY;
+  if (!ctx->d_sfull) return GPA_ERR_TOO_LARGE;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  cudaPointerAttributes pa_in{}, pa_out{};
+  bool pinned = cudaPointerGetAttributes(&pa_in, reqs) == cudaSuccess && pa_in.type == cudaMemoryTypeHost &&
+                cudaPointerGetAttributes(&pa_out, out) == cudaSuccess && pa_out.type == cudaMemoryTypeHost;
+  cudaGetLastError();
+  // the staging buffers are sized for the 32/16-byte records, so count/4 of them hold count mask records
+  int rc = ensure_batch_capacity(ctx, (size_t)count / 4 + 1, !pinned);
+  if (rc != GPA_OK) return rc;
+  gpa_mask_request *d_in = reinterpret_cast<gpa_mask_request *>(ctx->d_reqs);
+  gpa_mask_result *d_res = reinterpret_cast<gpa_mask_result *>(ctx->d_out);
+  gpa_mask_request *h_in = reinterpret_cast<gpa_mask_request *>(ctx->h_reqs);
+  gpa_mask_result *h_res = reinterpret_cast<gpa_mask_result *>(ctx->h_out);
+  if (!pinned) memcpy(h_in, reqs, (size_t)count * sizeof(gpa_mask_request));
+  const gpa_mask_request *src = pinned ? reqs : h_in;
+  gpa_mask_result *dst = pinned ? out : h_res;
+  const int kChunk = 1 << 20;
+  int c = 0;
+  for (int off = 0; off < count; off += kChunk, c++) {
+    int cnt = count - off < kChunk ? count - off : kChunk;
+    cudaStream_t st = ctx->pipe[c & 3];
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_in + off, src + off, (size_t)cnt * sizeof(gpa_mask_request), cudaMemcpyHostToDevice, st));
+    rc = launch_fast(ctx, d_in + off, cnt, mode_flags, d_res + off, st, true);
+    if (rc != GPA_OK) break;
+    CUDA_TRY(ctx, cudaMemcpyAsync(dst + off, d_res + off, (size_t)cnt * sizeof(gpa_mask_result), cudaMemcpyDeviceToHost, st));
+  }
+  for (auto &ps : ctx->pipe) {
+    cudaError_t e = cudaStreamSynchronize(ps);
+    if (e != cudaSuccess && rc == GPA_OK) {
+      ctx->last_error = std::string("cudaStreamSynchronize: ") + cudaGetErrorString(e);
+      rc = GPA_ERR_CUDA;
+    }
+  }
+  if (rc != GPA_OK) return rc;
+  if (!pinned) memcpy(out, h_res, (size_t)count * sizeof(gpa_mask_result));
   return GPA_OK;
 }
 

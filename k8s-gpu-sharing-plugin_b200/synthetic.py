@@ -228,3 +228,53 @@ def unpack_request(rec):
     if int(rec["flags"]) & FLAG_REQ_FOREIGN:
         req = req + [-2] * max(int(rec["n_req_extra"]), 1)
     return avail, req, int(rec["size"])
+
+
+# --------------------------------------------------------------------------------------
+# Mask format of gpa_besteffort_batch_masks: bit b = the device with rank b in the node order.
+MASK_REQ_DTYPE = np.dtype([("avail_mask", np.uint16), ("req_mask", np.uint16), ("size", np.uint8), ("flags", np.uint8),
+                           ("n_req_extra", np.uint8), ("reserved", np.uint8)])
+MASK_RES_DTYPE = np.dtype([("chosen_mask", np.uint16), ("n_nil", np.uint8), ("status", np.int8)])
+assert MASK_REQ_DTYPE.itemsize == 8 and MASK_RES_DTYPE.itemsize == 4
+
+
+def records_to_masks(reqs, order):
+    """REQ_DTYPE records whose device lists follow `order` (label -> NVML index) -> MASK_REQ_DTYPE records"""
+    rank = np.full(256, 255, dtype=np.int64)
+    rank[np.asarray(order, dtype=np.int64)] = np.arange(len(order))
+    out = np.zeros(len(reqs), dtype=MASK_REQ_DTYPE)
+    avail_mask = np.zeros(len(reqs), dtype=np.int64)
+    req_mask = np.zeros(len(reqs), dtype=np.int64)
+    n = reqs["n_avail"].astype(np.int64)
+    for p in range(16):
+        lab = rank[reqs["avail"][:, p]]
+        live = p < n
+        assert (lab[live] < 255).all(), "device outside the node order"
+        bit = np.where(live, 1 << np.where(live, lab, 0), 0)
+        avail_mask |= bit
+        req_mask |= np.where((reqs["req_mask"].astype(np.int64) >> p) & 1 == 1, bit, 0)
+    out["avail_mask"], out["req_mask"] = avail_mask, req_mask
+    out["size"], out["flags"], out["n_req_extra"] = reqs["size"], reqs["flags"], reqs["n_req_extra"]
+    return out
+
+
+def mask_results_to_records(res, order):
+    """MASK_RES_DTYPE -> RES_DTYPE (devices in node order, then nil pads), for comparison with the record path"""
+    order = np.asarray(order, dtype=np.int64)
+    out = np.full((len(res), 16), -128, dtype=np.int8)
+    fill = np.zeros(len(res), dtype=np.int64)
+    chosen = res["chosen_mask"].astype(np.int64)
+    for lab in range(len(order)):
+        hit = (chosen >> lab) & 1 == 1
+        out[np.nonzero(hit)[0], fill[hit]] = order[lab]
+        fill += hit
+    for _ in range(int(res["n_nil"].max()) if len(res) else 0):
+        more = (fill - np.array([bin(int(c)).count("1") for c in chosen])) < res["n_nil"]
+        out[np.nonzero(more)[0], fill[more]] = -1
+        fill += more
+    err = res["status"] != 0
+    out[err, 0] = -127
+    out[err, 1] = res["status"][err]
+    r = np.zeros(len(res), dtype=RES_DTYPE)
+    r["dev"] = out
+    return r

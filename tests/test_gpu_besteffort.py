@@ -309,6 +309,32 @@ def test_batch_max_avail_hint(ctx, oracle):
     assert_batch_equal(got, oracle_batch(oracle, W, nl, reqs, 0), reqs, "hint")
 
 
+def test_mask_format_matches_record_format_and_oracle(ctx, oracle):
+    """gpa_besteffort_batch_masks: 8-byte label-mask records; same decisions as the 32-byte records"""
+    for nt, topo, order in ((8, syn.topo_dgx1v_like(), ORDER8),
+                            (12, syn.topo_random(12, 11), [int(x) for x in np.random.default_rng(3).permutation(12)])):
+        W, nl = install(ctx, topo, order)
+        reqs = syn.random_request_batch(nt, 60000, seed=50 + nt, order=order)
+        reqs = reqs[reqs["n_avail"] <= 12]
+        masks = syn.records_to_masks(reqs, order)
+        for mode in (gpa.MODE_GO_FAITHFUL, gpa.MODE_INTENDED):
+            want = oracle_batch(oracle, W, nl, reqs, mode)
+            got = syn.mask_results_to_records(ctx.besteffort_batch_masks(masks, mode), order)
+            # the record path lists the chosen devices in `available` order = node order, like the mask path
+            assert_batch_equal(got, want, reqs, "masks nt=%d" % nt)
+            assert_batch_equal(ctx.besteffort_batch(reqs, mode), want, reqs, "records nt=%d" % nt)
+    # guards, foreign / unavailable required devices, size 1, bad masks
+    W, nl = install(ctx, syn.topo_dgx1v_like(), ORDER8)
+    m = np.zeros(7, dtype=syn.MASK_REQ_DTYPE)
+    m["avail_mask"] = [0b1111, 0b1111, 0b1111, 0b0110, 0b0110, 0b1 << 9, 0b1111]
+    m["req_mask"] = [0, 0, 0b10000, 0b0100, 0, 0, 0]
+    m["size"] = [0, 5, 2, 1, 1, 1, 2]
+    m["flags"] = [0, 0, 0, 0, 0, 0, 1]
+    r = ctx.besteffort_batch_masks(m)
+    assert r["chosen_mask"].tolist()[:5] == [0, 0, 0, 0b0100, 0b0010] and r["status"].tolist()[:5] == [0] * 5
+    assert r["status"][5] == gpa.ERR_INVALID and r["chosen_mask"][6] == 0 and r["status"][6] == 0
+
+
 def test_launch_counter_counts_kernels(ctx):
     install(ctx, syn.topo_two_sockets(8))
     before = ctx.launch_count
