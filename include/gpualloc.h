@@ -53,6 +53,9 @@ extern "C" {
 #define GPA_MODE_GO_FAITHFUL 0 /* bit-exact with the compiled Go reference, including the slice aliasing of
                                   bestPartition — the default */
 #define GPA_MODE_INTENDED 1    /* what the Go source means: bestPartition keeps the best candidate intact */
+#define GPA_MODE_FORCE_ENUM 2  /* gpa_besteffort(): visit every partition (one launch), whatever the size */
+#define GPA_MODE_FORCE_DP 4    /* gpa_besteffort(): subset dynamic programme (one launch per layer), whatever the size;
+                                  default: enumeration up to 10^5 candidate partitions, the DP beyond.  Same answers. */
 
 #define GPA_NIL (-1)     /* a nil *Device in a returned set (ref: SURVEY.md D5) */
 #define GPA_FOREIGN (-2) /* in `required`: a device pointer that is none of the `available` pointers — what the
@@ -124,7 +127,8 @@ typedef struct gpa_search_stats {
   int best_score;                /* score of the winning partition, in units of `score_unit`; -1 if none */
   int score_unit;                /* gcd of the pair weights (scores are kept divided by it on the device) */
   int grid, block, smem_bytes;   /* launch shape of the search kernel, 0 if no kernel was needed */
-  float kernel_ms;               /* device time of the search kernel (CUDA events), 0 if none */
+  float kernel_ms;               /* device time of the search kernel(s) (CUDA events), 0 if none */
+  int algorithm;                 /* 0 answered by the guards, 1 enumeration, 2 subset dynamic programme */
 } gpa_search_stats;
 int gpa_last_search_stats(gpa_ctx *ctx, gpa_search_stats *out);
 

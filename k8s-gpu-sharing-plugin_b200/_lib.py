@@ -16,6 +16,7 @@ OK = 0
 ERR_INVALID, ERR_CUDA, ERR_NO_TOPOLOGY, ERR_ASYMMETRIC, ERR_TOO_LARGE, ERR_WEIGHT_RANGE, ERR_BUFFER = -1, -2, -3, -4, -5, -6, -7
 ERR_NVML, ERR_PANIC, ERR_NO_DEVICES_LEFT, ERR_MUST_MISSING, ERR_UNKNOWN_DEVICE, ERR_NOT_IMPLEMENTED = -8, -9, -10, -11, -12, -13
 MODE_GO_FAITHFUL, MODE_INTENDED = 0, 1
+MODE_FORCE_ENUM, MODE_FORCE_DP = 2, 4
 NIL, FOREIGN = -1, -2
 RES_END, RES_ERROR = -128, -127
 MAX_AVAILABLE, BATCH_MAX_AVAILABLE = 16, 12
@@ -31,7 +32,7 @@ class GpaError(RuntimeError):
 class SearchStats(C.Structure):
     _fields_ = [("partitions", C.c_ulonglong), ("items", C.c_ulonglong), ("cut_depth", C.c_int), ("sets", C.c_int),
                 ("padding", C.c_int), ("best_score", C.c_int), ("score_unit", C.c_int), ("grid", C.c_int),
-                ("block", C.c_int), ("smem_bytes", C.c_int), ("kernel_ms", C.c_float)]
+                ("block", C.c_int), ("smem_bytes", C.c_int), ("kernel_ms", C.c_float), ("algorithm", C.c_int)]
 
 
 _lib = None

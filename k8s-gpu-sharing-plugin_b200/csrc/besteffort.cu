@@ -221,6 +221,114 @@ __global__ void __launch_bounds__(kSearchBlock, kSearchBlock >= 1024 ? 1 : 4) be
 }
 
 // ---------------------------------------------------------------------------------------
+// Subset dynamic programme for ONE large request (gpa_enum.cuh "Subset dynamic programme"): instead of visiting
+// every partition, fill best[R] for every reachable remainder R, one data-parallel pass per layer, then rebuild the
+// first best partition.  n = 16, k = 3: ~1 M (mask, set) pairs instead of 22.4 M partitions.  Tables live in global
+// memory (128 KB + 64 KB, L2-resident); each layer is its own launch, which is the grid-wide barrier between layers.
+struct DpParams {
+  Geom g;
+  int intended;
+  uint32_t rbit;  // lowest required position as a bit, 0 if none
+  uint16_t wp[kMaxDevices * kMaxDevices];
+};
+struct TabAny {
+  const uint16_t *t;
+  __device__ __forceinline__ uint32_t operator()(uint32_t mask) const { return t[mask]; }
+};
+struct TabOk {
+  const uint16_t *t;
+  uint32_t rbit;
+  __device__ __forceinline__ uint32_t operator()(uint32_t mask) const { return t[dp_ok_index(mask, rbit)]; }
+};
+constexpr int kDpThreads = 256;
+
+// layer 1: the score of every mask a set can be
+__global__ void __launch_bounds__(kDpThreads) dp_scores_kernel(const DpParams p, uint16_t *__restrict__ T) {
+  __shared__ uint16_t wp[kMaxDevices * kMaxDevices];
+  for (int i = threadIdx.x; i < kMaxDevices * kMaxDevices; i += kDpThreads) wp[i] = p.wp[i];
+  __syncthreads();
+  fill_score_table(T, wp, p.g, blockIdx.x * kDpThreads + threadIdx.x, gridDim.x * kDpThreads);
+}
+
+// layer j in 2..m-1: best completion of every remainder of j sets, both tables
+__global__ void __launch_bounds__(kDpThreads) dp_layer_kernel(const DpParams p, int j, uint16_t *T, uint16_t *Tok) {
+  const uint32_t total = 1u << p.g.n;
+  const TabAny tany{T};
+  const TabOk tok{Tok, p.rbit};
+  for (uint32_t R = blockIdx.x * kDpThreads + threadIdx.x; R < total; R += gridDim.x * kDpThreads) {
+    if (dp_layer_of(p.g, R) != j) continue;
+    // reads touch layers 1 and j-1 only, writes layer j only: no hazard inside the launch
+    const uint32_t va = dp_value(p.g, tany, tok, R, false);
+    T[R] = (uint16_t)va;
+    if (p.g.rmask != 0 && (R & p.g.rmask) == p.g.rmask) Tok[dp_ok_index(R, p.rbit)] = (uint16_t)dp_value(p.g, tany, tok, R, true);
+  }
+}
+
+// top layer + reconstruction: the first-level sets are spread over one CTA by item index, the (value, ~item) key picks
+// the first best of them, one thread rebuilds the levels below from the tables and applies the epilogue
+__global__ void __launch_bounds__(1024) dp_final_kernel(const DpParams p, const uint16_t *T, const uint16_t *Tok, SearchResult *g_res) {
+  __shared__ unsigned long long wkey[32];
+  const TabAny tany{T};
+  const TabOk tok{Tok, p.rbit};
+  const Geom &g = p.g;
+  const int tid = threadIdx.x;
+  Cut cut;
+  cut.d = g.m >= 2 ? 1 : 0;
+  for (int q = 0; q < kMaxCutDepth; q++) cut.radix[q] = 1;
+  if (cut.d) cut.radix[0] = binom_at(c_binom, g.m * g.k - 1, g.k - 1);
+  cut.n_items = cut.radix[0];
+  unsigned long long best = 0;
+  if (cut.d) {
+    for (unsigned long long item = tid; item < cut.n_items; item += 1024) {
+      const ItemState st = decode_item(g, cut, c_binom, tany, item, nullptr);
+      if (!st.valid) continue;
+      const uint32_t rest = st.rem & g.real_mask;
+      const bool need_ok = g.rmask != 0 && !st.ok;
+      const uint32_t t = !need_ok ? tany(rest) : (g.m == 2 ? dp_ok_base(g, tany(rest), rest) : tok(rest));
+      if (t == kDpInvalid) continue;
+      const unsigned long long kk = pack_key(st.acc + (int)t, item);
+      best = kk > best ? kk : best;
+    }
+  }
+  best = warp_max_u64(best);
+  if ((tid & 31) == 0) wkey[tid >> 5] = best;
+  __syncthreads();
+  if (tid == 0) {
+    for (int w = 1; w < 32; w++) best = wkey[w] > best ? wkey[w] : best;
+    SearchResult r;
+    r.key = best;
+    r.count = 0;
+    r.best_score = -1;
+    uint32_t sets[kMaxSets];
+    bool have = false;
+    if (!cut.d) {
+      have = dp_reconstruct(g, tany, tok, g.real_mask, g.rmask != 0, 0, sets);
+      if (have) r.best_score = (int)tany(g.real_mask);
+    } else if (best != 0) {
+      const ItemState st = decode_item(g, cut, c_binom, tany, key_item(best), sets);
+      have = dp_reconstruct(g, tany, tok, st.rem & g.real_mask, g.rmask != 0 && !st.ok, 1, sets);
+      r.best_score = key_score(best);
+      if (!have) r.count = -1;  // the key came from this item: cannot happen
+    }
+    if (have) {
+      uint32_t best_set = 0;
+      if (choose_from_partition(g, tany, sets, p.intended != 0, best_set) > 0) {
+        int o = 0;
+        uint32_t reals = best_set & g.real_mask;
+        while (reals) {
+          r.pos[o++] = (int8_t)(__ffs(reals) - 1);
+          reals &= reals - 1;
+        }
+        if (best_set & g.tok_bit)
+          for (int q = 0; q < g.P; q++) r.pos[o++] = -1;
+        r.count = o;
+      }
+    }
+    *g_res = r;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
 // Batch: one warp per container request.
 
 constexpr int8_t kResDefer = -126;  // internal: "left to the general kernel"; never leaves the library
@@ -701,6 +809,8 @@ struct gpa_ctx {
   bool has_topo = false;
   uint16_t *d_wq = nullptr;
   uint8_t *d_asym = nullptr;
+  uint16_t *d_dp_any = nullptr;  // subset DP tables of gpa_besteffort(): 2^16 and 2^15 uint16
+  uint16_t *d_dp_ok = nullptr;
   uint16_t *d_sfull = nullptr;  // fast batch path: set scores over label masks, nullptr = path unavailable
   FastTopo fast{};
   // batch staging
@@ -899,6 +1009,8 @@ int gpa_create(int cuda_device, gpa_ctx **out) {
   CREATE_TRY(cudaMalloc(&ctx->d_key, 2 * sizeof(unsigned long long)));  // [0] reduction key, [1] item cursor
   CREATE_TRY(cudaMalloc(&ctx->d_ticket, sizeof(unsigned int)));
   CREATE_TRY(cudaMalloc(&ctx->d_res, sizeof(SearchResult)));
+  CREATE_TRY(cudaMalloc(&ctx->d_dp_any, ((size_t)1 << kMaxDevices) * sizeof(uint16_t)));
+  CREATE_TRY(cudaMalloc(&ctx->d_dp_ok, ((size_t)1 << (kMaxDevices - 1)) * sizeof(uint16_t)));
   CREATE_TRY(cudaMallocHost(&ctx->h_res, sizeof(SearchResult)));
   CREATE_TRY(cudaMemset(ctx->d_key, 0, 2 * sizeof(unsigned long long)));
   CREATE_TRY(cudaMemset(ctx->d_ticket, 0, sizeof(unsigned int)));
@@ -937,6 +1049,8 @@ void gpa_destroy(gpa_ctx *ctx) {
   if (ctx->d_key) cudaFree(ctx->d_key);
   if (ctx->d_ticket) cudaFree(ctx->d_ticket);
   if (ctx->d_res) cudaFree(ctx->d_res);
+  if (ctx->d_dp_any) cudaFree(ctx->d_dp_any);
+  if (ctx->d_dp_ok) cudaFree(ctx->d_dp_ok);
   if (ctx->h_res) cudaFreeHost(ctx->h_res);
   if (ctx->d_wq) cudaFree(ctx->d_wq);
   if (ctx->d_asym) cudaFree(ctx->d_asym);
@@ -1130,9 +1244,37 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
   if (parts > GPA_MAX_PARTITIONS) return GPA_ERR_TOO_LARGE;
 
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  // Enumeration visits every partition in one launch; the subset DP needs m launches but far less work.  The DP wins
+  // once the tree is large (crossover measured around 10^5 partitions on B200).
+  const bool use_dp = (mode_flags & GPA_MODE_FORCE_DP) || (!(mode_flags & GPA_MODE_FORCE_ENUM) && parts > 100000ull);
+  int grid = 0, block = 0;
+  size_t smem = 0;
+  if (use_dp) {
+    DpParams dp;
+    memset(&dp, 0, sizeof dp);
+    dp.g = sp.g;
+    dp.intended = sp.intended;
+    dp.rbit = rmask ? (rmask & (0u - rmask)) : 0u;
+    memcpy(dp.wp, sp.wp, sizeof dp.wp);
+    const uint32_t total = 1u << n_avail;
+    grid = (int)((total + kDpThreads - 1) / kDpThreads);
+    if (grid > ctx->sm_count * 8) grid = ctx->sm_count * 8;
+    block = kDpThreads;
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    dp_scores_kernel<<<grid, kDpThreads, 0, ctx->stream>>>(dp, ctx->d_dp_any);
+    ctx->launches++;
+    for (int j = 2; j < dp.g.m; j++) {
+      dp_layer_kernel<<<grid, kDpThreads, 0, ctx->stream>>>(dp, j, ctx->d_dp_any, ctx->d_dp_ok);
+      ctx->launches++;
+    }
+    dp_final_kernel<<<1, 1024, 0, ctx->stream>>>(dp, ctx->d_dp_any, ctx->d_dp_ok, ctx->d_res);
+    ctx->launches++;
+    sp.cut.d = dp.g.m >= 2 ? 1 : 0;
+    sp.cut.n_items = dp.g.m >= 2 ? binom_at(ctx->binom, dp.g.m * dp.g.k - 1, dp.g.k - 1) : 1;
+  } else {
   const bool large = ((size_t)1 << n_avail) * sizeof(uint16_t) > 32 * 1024;
-  const int block = large ? kSearchBlockLarge : kSearchBlockSmall;
-  const size_t smem = search_smem_bytes(n_avail, block);
+  block = large ? kSearchBlockLarge : kSearchBlockSmall;
+  smem = search_smem_bytes(n_avail, block);
   if ((int)smem > ctx->max_smem_optin - 2048) return GPA_ERR_TOO_LARGE;
   auto kern = large ? besteffort_search_kernel<kSearchBlockLarge> : besteffort_search_kernel<kSearchBlockSmall>;
   if (smem > 40 * 1024) CUDA_TRY(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -1143,12 +1285,13 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
   sp.cut = choose_cut(sp.g, ctx->binom, resident_threads * 4);
   uint64_t blocks = (sp.cut.n_items + block - 1) / block;
   uint64_t cap = (uint64_t)ctx->sm_count * occ;
-  int grid = (int)(blocks < cap ? blocks : cap);
+  grid = (int)(blocks < cap ? blocks : cap);
   if (grid < 1) grid = 1;
 
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
   kern<<<grid, block, smem, ctx->stream>>>(sp, ctx->d_key, ctx->d_ticket, ctx->d_res);
   ctx->launches++;
+  }
   CUDA_TRY(ctx, cudaGetLastError());
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
   CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_res, ctx->d_res, sizeof(SearchResult), cudaMemcpyDeviceToHost, ctx->stream));
@@ -1166,6 +1309,7 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
   ctx->stats.block = block;
   ctx->stats.smem_bytes = (int)smem;
   ctx->stats.kernel_ms = ms;
+  ctx->stats.algorithm = use_dp ? 2 : 1;
 
   const SearchResult &r = *ctx->h_res;
   if (r.count < 0) {

@@ -513,6 +513,127 @@ GPA_HD int finalize(const Geom &g, const Cut &cut, const BinomTable &B, const ST
   return o;
 }
 
+// ---------------------------------------------------------------------------------------
+// Subset dynamic programme: the same answer without visiting every partition.
+//
+//   best[R] = max over the sets s that iterate() would try first on remainder R of  S[s] + best[R \ s]
+//
+// R is a mask of real devices; whether the pads are still in it follows from its size (|R| = j*k without pads,
+// j*k - P with them), so one table indexed by the real mask holds every layer j = 1..m, and layer 1 IS the set
+// score table S.  Filling layer j needs only layers 1 and j-1, so the layers are m-1 data-parallel passes.
+// The reference's answer is the FIRST best partition in visiting order (strict `>` at :57); that one is rebuilt
+// level by level afterwards: at each level the first set, in stepper order, whose value reaches best[R].
+// `required` devices add a second table for "a set holding all of them, unpadded, is still to come" (:53, :112-119),
+// defined on the masks that contain them all and indexed with the lowest required bit squeezed out.
+constexpr uint32_t kDpInvalid = 0xFFFFu;  // no acceptable completion (scores stay below: 120 pairs x 546)
+
+GPA_HD uint32_t dp_ok_index(uint32_t R, uint32_t rbit) {
+  return ((R >> 1) & ~(rbit - 1u)) | (R & (rbit - 1u));
+}
+// layer of a real mask, 0 if its size belongs to none (sizes j*k, and j*k - P when there are pads)
+GPA_HD int dp_layer_of(const Geom &g, uint32_t R) {
+  int pc = popc32(R);
+  if (pc == 0) return 0;
+  if (pc % g.k == 0) return pc / g.k;
+  if (g.P && (pc + g.P) % g.k == 0) return (pc + g.P) / g.k;
+  return 0;
+}
+
+// base of the required-still-to-come recursion: R is the last set, acceptable iff it holds them all unpadded
+GPA_HD uint32_t dp_ok_base(const Geom &g, uint32_t S_of_R, uint32_t R) {
+  return (popc32(R) == g.k && (R & g.rmask) == g.rmask) ? S_of_R : kDpInvalid;
+}
+
+// value of best[R] in the plain (want_ok = false) or the required-still-to-come (true) table; layers below filled
+template <typename TAny, typename TOk>
+GPA_HD uint32_t dp_value(const Geom &g, const TAny &Tany, const TOk &Tok, uint32_t R, bool want_ok) {
+  const bool last_pair = dp_layer_of(g, R) == 2;  // what is left after one more set is a single, final set
+  const bool has_tok = g.P != 0 && (popc32(R) % g.k) != 0;
+  const uint32_t rem = R | (has_tok ? g.tok_bit : 0u);
+  uint32_t anchor;
+  Stepper st = make_stepper(g, rem, anchor);
+  uint32_t chosen;
+  int best = -1;
+  if (!st.first(chosen)) return kDpInvalid;
+  do {
+    const uint32_t set = anchor | chosen;
+    const uint32_t sr = set & g.real_mask;
+    const uint32_t rest = R & ~sr;
+    int v;
+    if (!want_ok) {
+      v = (int)Tany(sr) + (int)Tany(rest);
+    } else {
+      const uint32_t hit = sr & g.rmask;
+      if (hit == 0) {
+        const uint32_t t = last_pair ? dp_ok_base(g, Tany(rest), rest) : Tok(rest);
+        if (t == kDpInvalid) continue;
+        v = (int)Tany(sr) + (int)t;
+      } else if (hit == g.rmask && (set & g.tok_bit) == 0) {
+        v = (int)Tany(sr) + (int)Tany(rest);
+      } else {
+        continue;  // the required devices are split, or sit in the padded set: never acceptable (:112-119)
+      }
+    }
+    best = v > best ? v : best;
+  } while (st.next(chosen));
+  return best < 0 ? kDpInvalid : (uint32_t)best;
+}
+
+
+// Rebuilds the first best partition from filled tables, starting below `level0` sets already fixed in sets[]
+// (R = what is left, need_ok = no fixed set holds the required devices yet).  Returns false if none is acceptable.
+template <typename TAny, typename TOk>
+GPA_HD bool dp_reconstruct(const Geom &g, const TAny &Tany, const TOk &Tok, uint32_t R, bool need_ok, int level0, uint32_t *sets) {
+  for (int level = level0; level < g.m; level++) {
+    const int left = g.m - level;
+    const bool has_tok = g.P != 0 && (popc32(R) % g.k) != 0;
+    if (left == 1) {
+      if (need_ok && !((R & g.rmask) == g.rmask && !has_tok)) return false;
+      sets[level] = R | (has_tok ? g.tok_bit : 0u);
+      return true;
+    }
+    const uint32_t target = need_ok ? Tok(R) : Tany(R);
+    if (target == kDpInvalid) return false;
+    const uint32_t rem = R | (has_tok ? g.tok_bit : 0u);
+    uint32_t anchor;
+    Stepper st = make_stepper(g, rem, anchor);
+    uint32_t chosen;
+    bool found = false;
+    if (!st.first(chosen)) return false;
+    do {
+      const uint32_t set = anchor | chosen;
+      const uint32_t sr = set & g.real_mask;
+      const uint32_t rest = R & ~sr;
+      bool next_need = need_ok;
+      uint32_t v;
+      if (!need_ok) {
+        v = Tany(sr) + Tany(rest);
+      } else {
+        const uint32_t hit = sr & g.rmask;
+        if (hit == 0) {
+          const uint32_t t = left == 2 ? dp_ok_base(g, Tany(rest), rest) : Tok(rest);
+          if (t == kDpInvalid) continue;
+          v = Tany(sr) + t;
+        } else if (hit == g.rmask && (set & g.tok_bit) == 0) {
+          v = Tany(sr) + Tany(rest);
+          next_need = false;
+        } else {
+          continue;
+        }
+      }
+      if (v == target) {
+        sets[level] = set;
+        R = rest;
+        need_ok = next_need;
+        found = true;
+        break;
+      }
+    } while (st.next(chosen));
+    if (!found) return false;
+  }
+  return true;
+}
+
 // Number of candidate partitions the reference visits (closed form of SURVEY.md §8a A3):
 // P = 0: n!/((k!)^m m!);  P > 0: C(n, k-P) * ((m-1)k)!/((k!)^(m-1) (m-1)!).
 GPA_HD uint64_t partition_count(const Geom &g, const BinomTable &B) {

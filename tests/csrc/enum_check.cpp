@@ -142,3 +142,47 @@ extern "C" int enum_check_tracked_sparse(int nt, const int32_t *W, uint32_t real
   }
   return 0;
 }
+
+// Subset dynamic programme (gpa_enum.cuh dp_*), run layer by layer on the CPU: dense positions 0..n-1.
+extern "C" int enum_check_dp(int nt, const int32_t *W, const int32_t *avail, int n_avail, uint32_t rmask, int size, int intended,
+                             int32_t *out, int *n_out) {
+  using namespace gpa;
+  *n_out = 0;
+  if (size < 2 || n_avail < size || n_avail > kMaxDevices) return -1;
+  const int n = n_avail;
+  Geom g = make_geom(n, size, rmask);
+  std::vector<uint16_t> T((size_t)1 << n, 0), Tok((size_t)1 << (n > 0 ? n - 1 : 0), (uint16_t)kDpInvalid);
+  const uint32_t rbit = rmask ? (rmask & (0u - rmask)) : 0u;
+  auto Tany = [&](uint32_t m) -> uint32_t { return T[m]; };
+  auto TokF = [&](uint32_t m) -> uint32_t { return Tok[dp_ok_index(m, rbit)]; };
+  for (uint32_t mask = 1; mask < (1u << n); mask++) {  // layer 1 = set scores
+    if (dp_layer_of(g, mask) != 1) continue;
+    int s = 0;
+    for (int a = 0; a < n; a++)
+      if (mask >> a & 1)
+        for (int b = a + 1; b < n; b++)
+          if (mask >> b & 1) s += W[avail[a] * nt + avail[b]];
+    T[mask] = (uint16_t)s;
+  }
+  for (int j = 2; j <= g.m; j++)
+    for (uint32_t mask = 1; mask < (1u << n); mask++) {
+      if (dp_layer_of(g, mask) != j) continue;
+      // both tables of layer j are computed from layer j-1 before either is stored
+      uint32_t va = dp_value(g, Tany, TokF, mask, false);
+      uint32_t vo = (rmask && (mask & rmask) == rmask) ? dp_value(g, Tany, TokF, mask, true) : kDpInvalid;
+      T[mask] = (uint16_t)va;
+      if (rmask && (mask & rmask) == rmask) Tok[dp_ok_index(mask, rbit)] = (uint16_t)vo;
+    }
+  uint32_t sets[kMaxSets];
+  if (!dp_reconstruct(g, Tany, TokF, g.real_mask, rmask != 0, 0, sets)) return 0;
+  uint32_t best_set = 0;
+  if (choose_from_partition(g, Tany, sets, intended != 0, best_set) > 0) {
+    int o = 0;
+    for (int b = 0; b < n; b++)
+      if (best_set >> b & 1) out[o++] = avail[b];
+    if (best_set & g.tok_bit)
+      for (int i = 0; i < g.P; i++) out[o++] = -1;
+    *n_out = o;
+  }
+  return 0;
+}

@@ -33,6 +33,9 @@ def harness():
     L.enum_check_tracked_sparse.restype = C.c_int
     L.enum_check_tracked_sparse.argtypes = [C.c_int, C.POINTER(C.c_int32), C.c_uint32, C.c_uint32, C.c_int, C.c_int,
                                             C.POINTER(C.c_int32), C.POINTER(C.c_int)]
+    L.enum_check_dp.restype = C.c_int
+    L.enum_check_dp.argtypes = [C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int, C.c_uint32, C.c_int, C.c_int,
+                                C.POINTER(C.c_int32), C.POINTER(C.c_int)]
     L.enum_check_level_sets.restype = C.c_int
     L.enum_check_level_sets.argtypes = [C.c_int, C.c_int, C.c_int, C.c_uint32, C.POINTER(C.c_uint32), C.c_int]
     return L
@@ -178,3 +181,66 @@ def test_core_sparse_label_masks_match_oracle(harness, oracle, nt):
                 assert rc == 0 and (oracle.OK, [int(x) for x in out2[:n2.value]]) == want, ("tracked", mask, k, req, mode)
         done += 1
     assert done > 300
+
+
+def run_dp(L, W, avail, req, k, intended):
+    W = np.ascontiguousarray(W, dtype=np.int32)
+    av = np.ascontiguousarray(avail, dtype=np.int32)
+    rmask = 0
+    for d in req:
+        rmask |= 1 << list(avail).index(d)
+    out = np.zeros(64, dtype=np.int32)
+    n_out = C.c_int(0)
+    rc = L.enum_check_dp(W.shape[0], W.ctypes.data_as(C.POINTER(C.c_int32)), av.ctypes.data_as(C.POINTER(C.c_int32)), len(av),
+                         rmask, k, int(intended), out.ctypes.data_as(C.POINTER(C.c_int32)), C.byref(n_out))
+    assert rc == 0
+    return [int(x) for x in out[:n_out.value]]
+
+
+@pytest.mark.parametrize("topo_i", [0, 2, 3, 5, 9])
+def test_subset_dp_matches_oracle_exhaustive_n8(harness, oracle, topo_i):
+    """the subset dynamic programme must return the FIRST best partition's set, like the enumeration"""
+    name, t = syn.standard_topologies()[topo_i]
+    W, nl = syn.links_to_weights(t)
+    order = syn.sorted_positions(syn.node_uuids(8, seed=1))
+    cnt = 0
+    for avail, req, k in syn.exhaustive_requests(order, seed=topo_i, n_pairs=4):
+        if k < 2 or len(req) > k:
+            continue
+        want = oracle.besteffort(W, nl, avail, req, k, oracle.GO_FAITHFUL, "fast")
+        assert (oracle.OK, run_dp(harness, W, avail, req, k, False)) == want, (name, avail, req, k)
+        cnt += 1
+    assert cnt > 4000
+
+
+@pytest.mark.parametrize("n,k", [(9, 2), (9, 4), (10, 3), (10, 4), (11, 2), (11, 3), (11, 5), (12, 3), (12, 5), (12, 7), (12, 11),
+                                 (13, 2), (13, 3), (13, 6), (14, 2), (14, 4), (14, 5), (15, 2), (15, 4), (16, 2), (16, 3), (16, 4),
+                                 (16, 5), (16, 6), (16, 7), (16, 8), (16, 9), (16, 13), (16, 16)])
+def test_subset_dp_matches_oracle_seeded_large(harness, oracle, n, k):
+    big = oracle.partition_count(n, k) > 3000000
+    for seed in range(1 if big else 2):
+        W, nl = syn.links_to_weights(syn.topo_random(n, 300 + seed))
+        rng = np.random.default_rng(seed)
+        avail = [int(x) for x in rng.permutation(n)]
+        reqs = [[], [avail[int(rng.integers(n))]]]
+        if k >= 3 and not big:
+            reqs.append([avail[int(x)] for x in rng.choice(n, 2, replace=False)])
+        for req in reqs:
+            for mode in ((oracle.GO_FAITHFUL,) if big else (oracle.GO_FAITHFUL, oracle.INTENDED)):
+                want = oracle.besteffort(W, nl, avail, req, k, mode, "fast")
+                assert (oracle.OK, run_dp(harness, W, avail, req, k, mode == oracle.INTENDED)) == want, (n, k, seed, req, mode)
+
+
+def test_subset_dp_handles_ties_spikes_and_pads(harness, oracle):
+    for n in (13, 14):  # D6 vectors: go_faithful differs from intended
+        for seed in range(3):
+            W, nl = syn.links_to_weights(syn.topo_spiked(n, seed))
+            for mode in (oracle.GO_FAITHFUL, oracle.INTENDED):
+                want = oracle.besteffort(W, nl, list(range(n)), [], 2, mode, "fast")
+                assert (oracle.OK, run_dp(harness, W, list(range(n)), [], 2, mode == oracle.INTENDED)) == want
+    for n in range(2, 11):  # all-equal weights: every partition ties, the very first must win
+        W, nl = syn.links_to_weights(syn.topo_uniform(n))
+        for k in range(2, n + 1):
+            for req in ([], [n - 1]):
+                want = oracle.besteffort(W, nl, list(range(n)), req, k, oracle.GO_FAITHFUL, "fast")
+                assert (oracle.OK, run_dp(harness, W, list(range(n)), req, k, False)) == want, (n, k, req)

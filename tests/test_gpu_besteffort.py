@@ -67,6 +67,7 @@ def test_single_request_api_matches_batch_and_oracle_n8(ctx, oracle):
         avail, req, k = all_reqs[int(i)]
         want = oracle.besteffort(W, nl, avail, req, k)
         assert ctx.besteffort(avail, req, k) == (gpa.OK, want[1]), (avail, req, k)
+        assert ctx.besteffort(avail, req, k, gpa.MODE_FORCE_DP) == (gpa.OK, want[1]), ("dp", avail, req, k)
 
 
 def test_guards_and_trivial_answers(ctx, oracle):
@@ -156,10 +157,12 @@ def test_single_search_seeded_large(ctx, oracle, n, k):
         for req in reqs:
             for mode in (gpa.MODE_GO_FAITHFUL, gpa.MODE_INTENDED):
                 want = oracle.besteffort(W, nl, avail, req, k, mode, "fast")
-                got = ctx.besteffort(avail, req, k, mode)
-                assert got == (gpa.OK, want[1]), (n, k, seed, req, mode, ctx.search_stats())
-                st = ctx.search_stats()
-                assert st["partitions"] == oracle.partition_count(n, k)
+                # both search algorithms: every partition visited / subset dynamic programme
+                for algo, code in ((gpa.MODE_FORCE_ENUM, 1), (gpa.MODE_FORCE_DP, 2)):
+                    got = ctx.besteffort(avail, req, k, mode | algo)
+                    st = ctx.search_stats()
+                    assert got == (gpa.OK, want[1]), (n, k, seed, req, mode, st)
+                    assert st["partitions"] == oracle.partition_count(n, k) and st["algorithm"] == code
 
 
 def test_full_size_n16_k3_matches_oracle(ctx, oracle):
@@ -167,9 +170,11 @@ def test_full_size_n16_k3_matches_oracle(ctx, oracle):
     W, nl = install(ctx, syn.topo_random(16, 77))
     avail = list(range(16))
     want = oracle.besteffort(W, nl, avail, [], 3, oracle.GO_FAITHFUL, "fast")
-    assert ctx.besteffort(avail, [], 3) == (gpa.OK, want[1])
+    assert ctx.besteffort(avail, [], 3, gpa.MODE_FORCE_ENUM) == (gpa.OK, want[1])
     st = ctx.search_stats()
-    assert st["partitions"] == 22422400 and st["sets"] == 6 and st["padding"] == 2
+    assert st["partitions"] == 22422400 and st["sets"] == 6 and st["padding"] == 2 and st["algorithm"] == 1
+    assert ctx.besteffort(avail, [], 3) == (gpa.OK, want[1])   # default: the subset DP at this size
+    assert ctx.search_stats()["algorithm"] == 2
 
 
 @pytest.mark.parametrize("n", [13, 14, 15, 16])
@@ -181,7 +186,8 @@ def test_slice_aliasing_D6(ctx, oracle, n):
         avail = list(range(n))
         for mode in (gpa.MODE_GO_FAITHFUL, gpa.MODE_INTENDED):
             want = oracle.besteffort(W, nl, avail, [], 2, mode, "fast")
-            assert ctx.besteffort(avail, [], 2, mode) == (gpa.OK, want[1]), (n, seed, mode)
+            for algo in (gpa.MODE_FORCE_ENUM, gpa.MODE_FORCE_DP):
+                assert ctx.besteffort(avail, [], 2, mode | algo) == (gpa.OK, want[1]), (n, seed, mode, algo)
         assert ctx.besteffort(avail, [], 2, gpa.MODE_INTENDED)[1] == [n - 2, n - 1]
 
 
