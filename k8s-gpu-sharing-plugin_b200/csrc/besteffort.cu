@@ -45,6 +45,14 @@ constexpr int kBatchWarps = 8;
 constexpr int kScoreCap = 65535;                        // uint16 set-score table
 constexpr int kMaxPairs = (kMaxDevices * (kMaxDevices - 1)) / 2;  // 120
 
+// The binomial table is read with a DIFFERENT index in every lane while item ranks are decoded; constant memory
+// serialises such reads one address at a time, shared memory does not, so kernels that decode stage it first.
+__device__ __forceinline__ void stage_binom(BinomTable &dst, int tid, int nthreads) {
+  const uint32_t *src = &c_binom.c[0][0];
+  uint32_t *d = &dst.c[0][0];
+  for (int i = tid; i < 32 * 17; i += nthreads) d[i] = src[i];
+}
+
 struct STab {
   const uint16_t *s;
   __device__ __forceinline__ uint32_t operator()(uint32_t mask) const { return s[mask]; }
@@ -117,6 +125,8 @@ __global__ void __launch_bounds__(kSearchBlock, kSearchBlock >= 1024 ? 1 : 4) be
   __shared__ uint16_t wp[kMaxDevices * kMaxDevices];
   __shared__ unsigned long long wkey[kSearchBlock / 32];
   __shared__ int is_last;
+  __shared__ BinomTable s_binom;
+  stage_binom(s_binom, threadIdx.x, kSearchBlock);
   unsigned long long *g_key = g_scratch;
   unsigned long long *g_cursor = g_scratch + 1;
 
@@ -161,7 +171,7 @@ __global__ void __launch_bounds__(kSearchBlock, kSearchBlock >= 1024 ? 1 : 4) be
       chunk_left--;
       ItemState st;
       st.valid = false;
-      if (item < p.cut.n_items) st = decode_item(p.g, p.cut, c_binom, stab, item, nullptr);
+      if (item < p.cut.n_items) st = decode_item(p.g, p.cut, s_binom, stab, item, nullptr);
       const unsigned vm = __ballot_sync(0xffffffffu, st.valid);
       if (st.valid) {
         QueuedItem e;
@@ -212,7 +222,7 @@ __global__ void __launch_bounds__(kSearchBlock, kSearchBlock >= 1024 ? 1 : 4) be
     SearchResult r;
     r.key = key;
     r.best_score = key ? key_score(key) : -1;
-    r.count = finalize(p.g, p.cut, c_binom, stab, key, p.intended != 0, r.pos);
+    r.count = finalize(p.g, p.cut, s_binom, stab, key, p.intended != 0, r.pos);
     *g_res = r;
     *g_key = 0ull;  // leave the scratch clean for the next launch on this stream
     *g_cursor = 0ull;
@@ -264,55 +274,120 @@ __global__ void __launch_bounds__(kDpThreads) dp_layer_kernel(const DpParams p, 
   }
 }
 
-// top layer + reconstruction: the first-level sets are spread over one CTA by item index, the (value, ~item) key picks
-// the first best of them, one thread rebuilds the levels below from the tables and applies the epilogue
+// One level of the recursion for remainder R, spread over threads: every first set iterate() would try on R, by its
+// literal rank (decode_item on the sub-request "R with j sets to go"), valued with the tables of the layer below.
+// Returns the thread's best (value, ~rank) key; rank order is visiting order, so the max key is the FIRST best set.
+__device__ __forceinline__ unsigned long long dp_level_key(const Geom &g, const BinomTable &binom, uint32_t R, bool need_ok,
+                                                           const TabAny &tany, const TabOk &tok, int first, int stride,
+                                                           Cut &cut_out) {
+  const Geom sg = make_geom_sparse(R, g.k, need_ok ? g.rmask : 0u, g.tok_pos);
+  Cut cut;
+  cut.d = 1;
+#pragma unroll
+  for (int q = 0; q < kMaxCutDepth; q++) cut.radix[q] = 1;
+  cut.radix[0] = binom_at(binom, sg.m * sg.k - 1, sg.k - 1);
+  cut.n_items = cut.radix[0];
+  cut_out = cut;
+  unsigned long long best = 0;
+  for (unsigned long long item = first; item < cut.n_items; item += stride) {
+    const ItemState st = decode_item(sg, cut, binom, tany, item, nullptr);
+    if (!st.valid) continue;
+    const uint32_t rest = st.rem & g.real_mask;
+    const bool need2 = need_ok && !st.ok;
+    const uint32_t t = !need2 ? tany(rest) : (sg.m == 2 ? dp_ok_base(g, tany(rest), rest) : tok(rest));
+    if (t == kDpInvalid) continue;
+    const unsigned long long kk = pack_key(st.acc + (int)t, item);
+    best = kk > best ? kk : best;
+  }
+  return best;
+}
+
+// layer j, ONE WARP per remainder: for layers whose remainders have many first sets (large k) a single thread
+// walking them one after the other would be the tail of the whole search
+__global__ void __launch_bounds__(kDpThreads) dp_layer_warp_kernel(const DpParams p, int j, uint16_t *T, uint16_t *Tok) {
+  __shared__ BinomTable s_binom;
+  stage_binom(s_binom, threadIdx.x, kDpThreads);
+  __syncthreads();
+  const uint32_t total = 1u << p.g.n;
+  const TabAny tany{T};
+  const TabOk tok{Tok, p.rbit};
+  const int lane = threadIdx.x & 31;
+  const uint32_t warps = gridDim.x * (kDpThreads / 32);
+  for (uint32_t R = blockIdx.x * (kDpThreads / 32) + (threadIdx.x >> 5); R < total; R += warps) {
+    if (dp_layer_of(p.g, R) != j) continue;
+    Cut cut;
+    unsigned long long ka = warp_max_u64(dp_level_key(p.g, s_binom, R, false, tany, tok, lane, 32, cut));
+    unsigned long long ko = 0;
+    const bool has_req = p.g.rmask != 0 && (R & p.g.rmask) == p.g.rmask;
+    if (has_req) ko = warp_max_u64(dp_level_key(p.g, s_binom, R, true, tany, tok, lane, 32, cut));
+    if (lane == 0) {
+      T[R] = (uint16_t)(ka ? (uint32_t)key_score(ka) : kDpInvalid);
+      if (has_req) Tok[dp_ok_index(R, p.rbit)] = (uint16_t)(ko ? (uint32_t)key_score(ko) : kDpInvalid);
+    }
+  }
+}
+
+// top layer + reconstruction in one CTA: level by level, all threads value the first sets of the current remainder,
+// the block-wide max key names the first best one, and the remainder shrinks by it.  No serial replay.
 __global__ void __launch_bounds__(1024) dp_final_kernel(const DpParams p, const uint16_t *T, const uint16_t *Tok, SearchResult *g_res) {
   __shared__ unsigned long long wkey[32];
+  __shared__ unsigned long long level_key;
+  __shared__ uint32_t sets[kMaxSets];
+  __shared__ BinomTable s_binom;
+  stage_binom(s_binom, threadIdx.x, 1024);
+  __syncthreads();
   const TabAny tany{T};
   const TabOk tok{Tok, p.rbit};
   const Geom &g = p.g;
   const int tid = threadIdx.x;
-  Cut cut;
-  cut.d = g.m >= 2 ? 1 : 0;
-  for (int q = 0; q < kMaxCutDepth; q++) cut.radix[q] = 1;
-  if (cut.d) cut.radix[0] = binom_at(c_binom, g.m * g.k - 1, g.k - 1);
-  cut.n_items = cut.radix[0];
-  unsigned long long best = 0;
-  if (cut.d) {
-    for (unsigned long long item = tid; item < cut.n_items; item += 1024) {
-      const ItemState st = decode_item(g, cut, c_binom, tany, item, nullptr);
-      if (!st.valid) continue;
-      const uint32_t rest = st.rem & g.real_mask;
-      const bool need_ok = g.rmask != 0 && !st.ok;
-      const uint32_t t = !need_ok ? tany(rest) : (g.m == 2 ? dp_ok_base(g, tany(rest), rest) : tok(rest));
-      if (t == kDpInvalid) continue;
-      const unsigned long long kk = pack_key(st.acc + (int)t, item);
-      best = kk > best ? kk : best;
+  uint32_t R = g.real_mask;
+  bool need = g.rmask != 0;
+  bool have = true;
+  int top_score = -1;
+  for (int level = 0; level < g.m; level++) {
+    const int left = g.m - level;
+    const bool has_tok = g.P != 0 && (__popc(R) % g.k) != 0;
+    if (left == 1) {
+      if (need && !((R & g.rmask) == g.rmask && !has_tok)) have = false;
+      if (tid == 0) sets[level] = R | (has_tok ? g.tok_bit : 0u);
+      if (level == 0 && have) top_score = (int)tany(R);
+      break;
     }
+    Cut cut;
+    unsigned long long best = warp_max_u64(dp_level_key(g, s_binom, R, need, tany, tok, tid, 1024, cut));
+    if ((tid & 31) == 0) wkey[tid >> 5] = best;
+    __syncthreads();
+    if (tid == 0) {
+      for (int w = 1; w < 32; w++) best = wkey[w] > best ? wkey[w] : best;
+      level_key = best;
+    }
+    __syncthreads();
+    const unsigned long long key = level_key;
+    if (key == 0) {
+      have = false;
+      break;
+    }
+    if (level == 0) top_score = key_score(key);
+    // every thread decodes the winner, so R and `need` stay uniform without another broadcast
+    const Geom sg = make_geom_sparse(R, g.k, need ? g.rmask : 0u, g.tok_pos);
+    uint32_t set = 0;
+    const ItemState st = decode_item(sg, cut, s_binom, tany, key_item(key), &set);
+    if (tid == 0) sets[level] = set;
+    R = st.rem & g.real_mask;
+    need = need && !st.ok;
+    __syncthreads();  // wkey / level_key are reused by the next level
   }
-  best = warp_max_u64(best);
-  if ((tid & 31) == 0) wkey[tid >> 5] = best;
   __syncthreads();
   if (tid == 0) {
-    for (int w = 1; w < 32; w++) best = wkey[w] > best ? wkey[w] : best;
     SearchResult r;
-    r.key = best;
+    r.key = 0;
     r.count = 0;
-    r.best_score = -1;
-    uint32_t sets[kMaxSets];
-    bool have = false;
-    if (!cut.d) {
-      have = dp_reconstruct(g, tany, tok, g.real_mask, g.rmask != 0, 0, sets);
-      if (have) r.best_score = (int)tany(g.real_mask);
-    } else if (best != 0) {
-      const ItemState st = decode_item(g, cut, c_binom, tany, key_item(best), sets);
-      have = dp_reconstruct(g, tany, tok, st.rem & g.real_mask, g.rmask != 0 && !st.ok, 1, sets);
-      r.best_score = key_score(best);
-      if (!have) r.count = -1;  // the key came from this item: cannot happen
-    }
+    r.best_score = have ? top_score : -1;
     if (have) {
+      uint32_t local_sets[kMaxSets];
+      for (int q = 0; q < g.m; q++) local_sets[q] = sets[q];
       uint32_t best_set = 0;
-      if (choose_from_partition(g, tany, sets, p.intended != 0, best_set) > 0) {
+      if (choose_from_partition(g, tany, local_sets, p.intended != 0, best_set) > 0) {
         int o = 0;
         uint32_t reals = best_set & g.real_mask;
         while (reals) {
@@ -351,6 +426,9 @@ __global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_kernel(cons
                                                                             int n_cap, int intended, BatchTopo topo,
                                                                             gpa_result *out, int deferred_only) {
   extern __shared__ __align__(16) uint16_t smem[];
+  __shared__ BinomTable s_binom;
+  stage_binom(s_binom, threadIdx.x, kBatchWarps * 32);
+  __syncthreads();
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   uint16_t *S = smem + (size_t)warp * ((1u << n_cap) + kMaxDevices * kMaxDevices);
@@ -421,10 +499,10 @@ __global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_kernel(cons
       const Geom g = make_geom(n, size, rmask);
       fill_score_table(S, wp, g, lane, 32);
       __syncwarp();
-      const Cut cut = choose_cut(g, c_binom, 64);
+      const Cut cut = choose_cut(g, s_binom, 64);
       unsigned long long best = 0;
       for (unsigned long long item = lane; item < cut.n_items; item += 32) {
-        int sc = search_item(g, cut, c_binom, stab, item);
+        int sc = search_item(g, cut, s_binom, stab, item);
         if (sc >= 0) {
           unsigned long long kk = pack_key(sc, item);
           best = kk > best ? kk : best;
@@ -433,7 +511,7 @@ __global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_kernel(cons
       best = warp_max_u64(best);
       if (lane == 0) {
         int8_t pos[32];
-        int cnt = finalize(g, cut, c_binom, stab, best, intended != 0, pos);
+        int cnt = finalize(g, cut, s_binom, stab, best, intended != 0, pos);
         if (cnt < 0) {
           err = GPA_ERR_INVALID;
         } else {
@@ -1264,7 +1342,16 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
     dp_scores_kernel<<<grid, kDpThreads, 0, ctx->stream>>>(dp, ctx->d_dp_any);
     ctx->launches++;
     for (int j = 2; j < dp.g.m; j++) {
-      dp_layer_kernel<<<grid, kDpThreads, 0, ctx->stream>>>(dp, j, ctx->d_dp_any, ctx->d_dp_ok);
+      // A thread per remainder walks its first sets one after the other; a warp per remainder spreads them over its lanes
+      // by literal rank.  Measured on B200 (tools/search_sweep.py): the warp form wins once a remainder has ~100 first sets.
+      const double t_warp = 0.0, t_thread = binom_at(ctx->binom, j * dp.g.k - 1, dp.g.k - 1) >= 96u ? 1.0 : -1.0;
+      if (t_warp < t_thread) {
+        int wgrid = (int)((total + kDpThreads / 32 - 1) / (kDpThreads / 32));
+        if (wgrid > ctx->sm_count * 8) wgrid = ctx->sm_count * 8;
+        dp_layer_warp_kernel<<<wgrid, kDpThreads, 0, ctx->stream>>>(dp, j, ctx->d_dp_any, ctx->d_dp_ok);
+      } else {
+        dp_layer_kernel<<<grid, kDpThreads, 0, ctx->stream>>>(dp, j, ctx->d_dp_any, ctx->d_dp_ok);
+      }
       ctx->launches++;
     }
     dp_final_kernel<<<1, 1024, 0, ctx->stream>>>(dp, ctx->d_dp_any, ctx->d_dp_ok, ctx->d_res);
