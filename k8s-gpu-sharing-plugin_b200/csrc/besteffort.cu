@@ -1344,8 +1344,7 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
     for (int j = 2; j < dp.g.m; j++) {
       // A thread per remainder walks its first sets one after the other; a warp per remainder spreads them over its lanes
       // by literal rank.  Measured on B200 (tools/search_sweep.py): the warp form wins once a remainder has ~100 first sets.
-      const double t_warp = 0.0, t_thread = binom_at(ctx->binom, j * dp.g.k - 1, dp.g.k - 1) >= 96u ? 1.0 : -1.0;
-      if (t_warp < t_thread) {
+      if (binom_at(ctx->binom, j * dp.g.k - 1, dp.g.k - 1) >= 96u) {
         int wgrid = (int)((total + kDpThreads / 32 - 1) / (kDpThreads / 32));
         if (wgrid > ctx->sm_count * 8) wgrid = ctx->sm_count * 8;
         dp_layer_warp_kernel<<<wgrid, kDpThreads, 0, ctx->stream>>>(dp, j, ctx->d_dp_any, ctx->d_dp_ok);

@@ -41,9 +41,17 @@ int pack_out(const std::vector<std::string_view> &v, char *outbuf, int outbuf_le
   return GPA_OK;
 }
 
+// One free replica id: the whole id plus its tail after the physical id.  Ids of one group share the physical id
+// and the separator, so ordering them by the tail is ordering them byte-wise as whole strings (sort.Strings, :116)
+// at a fraction of the comparison cost.
+struct Replica {
+  std::string_view id;
+  std::string_view tail;
+};
+
 struct Group {
   std::string_view phys;
-  std::vector<std::string_view> names;  // free replicas; [head, names.size()) is the live window
+  std::vector<Replica> names;  // free replicas; [head, names.size()) is the live window
   size_t head = 0;
   bool allocated = false;
   size_t free_count() const { return names.size() - head; }
@@ -71,22 +79,38 @@ int gpa_prioritize_devices(const char *const *avail, int n_avail, const char *co
   if (non_unique) *non_unique = 0;
   if (errbuf && errbuf_len > 0) errbuf[0] = 0;
 
-  // replica.go:98-117 — group the replica ids by physical GPU, each group sorted byte-wise
+  // replica.go:98-117 — group the replica ids by physical GPU, each group sorted byte-wise.  A node has a handful of
+  // physical GPUs, so the group of an id is found by scanning them (length first, then bytes); the hash map only takes
+  // over on unusually wide nodes.
   std::vector<Group> groups;
+  groups.reserve(16);
   std::unordered_map<std::string_view, size_t> index;
-  index.reserve((size_t)n_avail * 2 + 1);
+  auto group_of = [&](std::string_view phys) -> Group * {
+    if (groups.size() <= 32) {
+      for (Group &g : groups)
+        if (g.phys.size() == phys.size() && memcmp(g.phys.data(), phys.data(), phys.size()) == 0) return &g;
+      return nullptr;
+    }
+    if (index.empty())
+      for (size_t i = 0; i < groups.size(); i++) index.emplace(groups[i].phys, i);
+    auto it = index.find(phys);
+    return it == index.end() ? nullptr : &groups[it->second];
+  };
   for (int i = 0; i < n_avail; i++) {
     std::string_view id = avail[i];
     std::string_view phys = physical_of(id);
-    auto it = index.find(phys);
-    if (it == index.end()) {
-      it = index.emplace(phys, groups.size()).first;
+    Group *g = group_of(phys);
+    if (!g) {
       groups.emplace_back();
-      groups.back().phys = phys;
+      g = &groups.back();
+      g->phys = phys;
+      g->names.reserve(64);
+      if (!index.empty()) index.emplace(phys, groups.size() - 1);
     }
-    groups[it->second].names.push_back(id);
+    g->names.push_back({id, id.substr(phys.size())});
   }
-  for (auto &g : groups) std::sort(g.names.begin(), g.names.end());
+  for (auto &g : groups)
+    std::sort(g.names.begin(), g.names.end(), [](const Replica &a, const Replica &b) { return a.tail < b.tail; });
 
   // replica.go:121 — make([]string, len(must), allocationSize)
   if (size < 0 || n_must > size) return GPA_ERR_PANIC;
@@ -98,13 +122,12 @@ int gpa_prioritize_devices(const char *const *avail, int n_avail, const char *co
   // replica.go:126-139 — must-includes; removal swaps the last free replica into the hole (:56-60)
   for (int i = 0; i < n_must; i++) {
     std::string_view id = must[i];
-    auto it = index.find(physical_of(id));
-    Group *g = it == index.end() ? nullptr : &groups[it->second];
+    Group *g = group_of(physical_of(id));
     size_t at = 0;
     bool found = false;
     if (g) {
       for (at = g->head; at < g->names.size(); at++)
-        if (g->names[at] == id) {
+        if (g->names[at].id == id) {
           found = true;
           break;
         }
@@ -145,7 +168,7 @@ int gpa_prioritize_devices(const char *const *avail, int n_avail, const char *co
     Group *pick = fresh ? fresh : used;
     if (!pick) return GPA_ERR_NO_DEVICES_LEFT;
     if (pick->allocated) unique = false;
-    allocated.push_back(pick->names[pick->head++]);  // allocateAny(): the group's first free replica (:79-84)
+    allocated.push_back(pick->names[pick->head++].id);  // allocateAny(): the group's first free replica (:79-84)
     pick->allocated = true;
   }
   std::sort(allocated.begin(), allocated.end());  // :191
