@@ -29,7 +29,6 @@ import math
 import os
 import subprocess
 import sys
-import threading
 import time
 
 import numpy as np
@@ -87,34 +86,42 @@ def algorithmic_pair_evals(reqs):
     return float(table[np.clip(n, 0, 16), np.clip(k, 0, 16)][searched].sum())
 
 
-class ClockSampler(threading.Thread):
-    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)"""
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons DURING the timed regions (B200_PROFILING.md recipe): one nvidia-smi process
+    in loop mode, started before the first timed region and stopped after the last."""
 
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, gpu_index):
-        super().__init__(daemon=True)
         self.gpu = gpu_index
+        self.proc = None
         self.samples = []
-        self._halt = threading.Event()
 
-    def run(self):
-        while not self._halt.is_set():
-            try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                f = [x.strip() for x in out.strip().split(",")]
-                if len(f) >= 9:
-                    self.samples.append(f)
-            except Exception:
-                pass
-            self._halt.wait(0.2)
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
 
     def stop(self):
-        self._halt.set()
-        self.join(timeout=6)
+        if self.proc is None:
+            return
+        try:
+            self.proc.terminate()
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            out = ""
+        for line in out.splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) >= 9:
+                try:
+                    float(f[1])
+                    self.samples.append(f)
+                except ValueError:
+                    pass
 
     def summary(self):
         if not self.samples:
@@ -126,7 +133,8 @@ class ClockSampler(threading.Thread):
                 if v.lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.samples[0][2]), "samples": len(sm),
-                "power_w_max": max(float(s[3]) for s in self.samples), "reasons": sorted(reasons)}
+                "power_w_max": max(float(s[3]) for s in self.samples), "reasons": sorted(reasons),
+                "window": "all timed regions of this run (device-resident, end-to-end and mask-format arms)"}
 
 
 def measured_peak():
@@ -229,7 +237,6 @@ def run_ours(args):
     launches = ctx.launch_count - launches0
     total_ms = e_all0.elapsed_time(e_all1)
     kernel_ms = [a.elapsed_time(b) for a, b in evs]
-    sampler.stop()
     if use_dist:
         tt = torch.tensor([total_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -289,6 +296,7 @@ def run_ours(args):
     for _ in range(args.steps):
         ctx.besteffort_batch_masks(pin_min.array, out=pin_mout.array)
     masks_e2e_s = (time.perf_counter() - t0) / args.steps
+    sampler.stop()
     got_m = syn.mask_results_to_records(pin_mout.array[idx].copy(), order)
     masks_mismatch = int((got_m["dev"] != want["dev"]).any(axis=1).sum())
     if use_dist:
@@ -461,7 +469,7 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     args = ap.parse_args()
