@@ -1,19 +1,21 @@
-// Best-effort partition search on the GPU: kernels, context and the C ABI around them.
+// libgpualloc.so, CUDA side: context, topology tables, launch logic and the C ABI (include/gpualloc.h) around the
+// allocation kernels.
 //
-// Replaces, behind include/gpualloc.h, the reference's
+// Replaces the reference's
 //   bestEffortPolicy.Allocate   vendor/github.com/NVIDIA/go-gpuallocator/gpuallocator/besteffort_policy.go:34-89
 //   iterateGPUPartitions        ... :209-290
 //   calculateGPU{Pair,Set,Partition}Score ... :298-380
-// and the per-request weight source gpuallocator.NewDevices (gpuallocator/device.go:33-72),
-// which becomes a device-resident matrix installed once by gpa_set_topology().
+// and the per-request weight source gpuallocator.NewDevices (gpuallocator/device.go:33-72), which becomes
+// device-resident tables installed once by gpa_set_topology*().
 //
-// Two kernels, both built from the enumeration core in gpa_enum.cuh:
-//   besteffort_search_kernel : ONE request, the whole machine.  The partition tree is cut
-//       into order-numbered work items; every CTA builds the set-score table in shared
-//       memory, threads walk items grid-stride, a 64-bit (score, ~item) key is max-reduced
-//       warp -> CTA -> one global atomicMax, and the last CTA to finish replays the winning
-//       item and writes the answer.  No second launch, no host round trip in between.
-//   besteffort_batch_kernel  : MANY requests (the ContainerRequests loop), one warp each.
+// One translation unit; the kernels live in the headers included below and are all built from the enumeration core
+// gpa_enum.cuh:
+//   search_kernel.cuh  besteffort_search_kernel    ONE request, every partition visited, whole machine
+//   dp_kernels.cuh     dp_scores/layer/final       ONE large request by subset dynamic programme (a launch per layer)
+//   batch_kernels.cuh  besteffort_batch_fast_kernel  MANY requests in node order: tile-binned, one lane per request
+//                      besteffort_batch_kernel       MANY requests, any order: one warp per request (also the
+//                                                    "deferred" pass after the fast kernel)
+// The allocation-free entry point and its static device scratch are at the end of this file.
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -28,819 +30,12 @@
 #include "../../include/gpualloc.h"
 #include "gpa_enum.cuh"
 
+#include "kernels_common.cuh"
+#include "search_kernel.cuh"
+#include "dp_kernels.cuh"
+#include "batch_kernels.cuh"
+
 namespace {
-
-using namespace gpa;
-
-__constant__ BinomTable c_binom;
-// candidate partitions of (n available, size k), n,k <= 12, saturated at 2^32-1: work estimate of the fast batch path
-__constant__ uint32_t c_parts[13][13];
-// shape (n, k) -> bin of the fast batch kernel's counting sort: bins are numbered by DESCENDING work, so the sorted
-// order of a tile starts with its most expensive searches (longest-processing-time-first scheduling)
-__constant__ uint8_t c_shape_bin[13][13];
-
-constexpr int kSearchBlockSmall = 256;   // score table <= 32 KB: several CTAs per SM
-constexpr int kSearchBlockLarge = 1024;  // 64-128 KB table: one or two CTAs per SM, so make them wide
-constexpr int kBatchWarps = 8;
-constexpr int kScoreCap = 65535;                        // uint16 set-score table
-constexpr int kMaxPairs = (kMaxDevices * (kMaxDevices - 1)) / 2;  // 120
-
-// The binomial table is read with a DIFFERENT index in every lane while item ranks are decoded; constant memory
-// serialises such reads one address at a time, shared memory does not, so kernels that decode stage it first.
-__device__ __forceinline__ void stage_binom(BinomTable &dst, int tid, int nthreads) {
-  const uint32_t *src = &c_binom.c[0][0];
-  uint32_t *d = &dst.c[0][0];
-  for (int i = tid; i < 32 * 17; i += nthreads) d[i] = src[i];
-}
-
-struct STab {
-  const uint16_t *s;
-  __device__ __forceinline__ uint32_t operator()(uint32_t mask) const { return s[mask]; }
-};
-
-struct SearchParams {
-  Geom g;
-  Cut cut;
-  int intended;
-  uint16_t wp[kMaxDevices * kMaxDevices];  // scaled weight of (earlier position a, later position b) at [a*16+b]
-};
-
-struct SearchResult {
-  int32_t count;  // k, 0 = empty answer, -1 = internal inconsistency
-  int32_t best_score;
-  int8_t pos[32];  // positions, -1 = nil pad
-  unsigned long long key;
-};
-
-// Score table of every mask a set can be: k reals, or k-P reals next to the pads.
-__device__ __forceinline__ void fill_score_table(uint16_t *S, const uint16_t *wp, const Geom &g, int tid, int nthreads) {
-  const uint32_t total = 1u << g.n;
-  const int kp = g.P ? g.k - g.P : -1;
-  for (uint32_t mask = tid; mask < total; mask += nthreads) {
-    int pc = __popc(mask);
-    if (pc != g.k && pc != kp) continue;
-    uint32_t sum = 0;
-    uint32_t ma = mask;
-    while (ma) {
-      int a = __ffs(ma) - 1;
-      ma &= ma - 1;
-      uint32_t mb = ma;
-      while (mb) {
-        int b = __ffs(mb) - 1;
-        mb &= mb - 1;
-        sum += wp[a * kMaxDevices + b];
-      }
-    }
-    S[mask] = (uint16_t)sum;
-  }
-}
-
-__device__ __forceinline__ unsigned long long warp_max_u64(unsigned long long v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    unsigned long long u = __shfl_xor_sync(0xffffffffu, v, o);
-    v = u > v ? u : v;
-  }
-  return v;
-}
-
-// One decoded work item waiting for its walk.
-struct QueuedItem {
-  unsigned long long item;
-  uint32_t rem;
-  int32_t acc_ok;  // acc | ok << 30
-};
-constexpr int kQueueSlots = 64;  // per warp: at most 31 left over + 32 new
-constexpr int kGrabChunks = 8;   // a warp draws 8 x 32 consecutive items per visit to the global cursor
-
-constexpr size_t search_smem_bytes(int n, int block) {
-  return ((((size_t)1 << n) * sizeof(uint16_t) + 15) & ~(size_t)15) + (size_t)(block / 32) * kQueueSlots * sizeof(QueuedItem);
-}
-
-// g_scratch[0] = reduction key, g_scratch[1] = item cursor; both zero between launches.
-template <int kSearchBlock>
-__global__ void __launch_bounds__(kSearchBlock, kSearchBlock >= 1024 ? 1 : 4) besteffort_search_kernel(const SearchParams p, unsigned long long *g_scratch,
-                                                                          unsigned int *g_ticket, SearchResult *g_res) {
-  extern __shared__ __align__(16) uint16_t S[];
-  __shared__ uint16_t wp[kMaxDevices * kMaxDevices];
-  __shared__ unsigned long long wkey[kSearchBlock / 32];
-  __shared__ int is_last;
-  __shared__ BinomTable s_binom;
-  stage_binom(s_binom, threadIdx.x, kSearchBlock);
-  unsigned long long *g_key = g_scratch;
-  unsigned long long *g_cursor = g_scratch + 1;
-
-  const int tid = threadIdx.x;
-  const int lane = tid & 31;
-  for (int i = tid; i < kMaxDevices * kMaxDevices; i += kSearchBlock) wp[i] = p.wp[i];
-  __syncthreads();
-  fill_score_table(S, wp, p.g, tid, kSearchBlock);
-  __syncthreads();
-
-  const STab stab{S};
-  QueuedItem *q = reinterpret_cast<QueuedItem *>(reinterpret_cast<unsigned char *>(S) +
-                                                 ((((size_t)1 << p.g.n) * sizeof(uint16_t) + 15) & ~(size_t)15)) +
-                  (tid >> 5) * kQueueSlots;
-  const int suffix = p.g.m - p.cut.d;
-  unsigned long long best = 0;
-  unsigned qhead = 0, qtail = 0;  // warp-uniform
-
-  // Items are decoded one per lane, but about half of them die in the padding / `required` filters and the rest
-  // walk a few hundred leaves each.  Survivors are therefore compacted into a per-warp queue and walked 32 at a
-  // time, so the expensive part runs with full warps; warps draw their items from a global cursor, so a warp
-  // whose items happen to be cheap simply comes back for more.
-  // small searches take one chunk per visit so that every warp gets a share; big ones amortise the atomic
-  const unsigned long long per_warp = p.cut.n_items / ((unsigned long long)gridDim.x * (kSearchBlock / 32) * 32ull);
-  const int grab = per_warp >= (unsigned long long)kGrabChunks ? kGrabChunks : (per_warp < 1 ? 1 : (int)per_warp);
-  unsigned long long base = 0;
-  int chunk_left = 0;
-  bool exhausted = false;
-  for (;;) {
-    // refill: decode chunks until a full warp of survivors is waiting (or the items ran out)
-    while (qtail - qhead < 32u && !exhausted) {
-      if (chunk_left == 0) {
-        if (lane == 0) base = atomicAdd(g_cursor, (unsigned long long)(32 * grab));
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= p.cut.n_items) {
-          exhausted = true;
-          break;
-        }
-        chunk_left = grab;
-      }
-      const unsigned long long item = base + (unsigned long long)(grab - chunk_left) * 32 + lane;
-      chunk_left--;
-      ItemState st;
-      st.valid = false;
-      if (item < p.cut.n_items) st = decode_item(p.g, p.cut, s_binom, stab, item, nullptr);
-      const unsigned vm = __ballot_sync(0xffffffffu, st.valid);
-      if (st.valid) {
-        QueuedItem e;
-        e.item = item;
-        e.rem = st.rem;
-        e.acc_ok = st.acc | (st.ok ? (1 << 30) : 0);
-        q[(qtail + __popc(vm & ((1u << lane) - 1u))) & (kQueueSlots - 1)] = e;
-      }
-      qtail += __popc(vm);
-      __syncwarp();
-    }
-    const unsigned waiting = qtail - qhead;
-    if (waiting == 0) break;
-    const unsigned take = waiting < 32u ? waiting : 32u;
-    QueuedItem e;
-    e.item = 0;
-    e.rem = 0;
-    e.acc_ok = 0;
-    if (lane < take) e = q[(qhead + lane) & (kQueueSlots - 1)];
-    qhead += take;
-    __syncwarp();
-    if (lane < take) {
-      int b = -1;
-      walk_dyn(suffix, p.g, stab, e.rem, e.acc_ok & 0x3FFFFFFF, (e.acc_ok >> 30) != 0, b, nullptr);
-      if (b >= 0) {
-        const unsigned long long kk = pack_key(b, e.item);
-        best = kk > best ? kk : best;
-      }
-    }
-  }
-
-  best = warp_max_u64(best);
-  if ((tid & 31) == 0) wkey[tid >> 5] = best;
-  __syncthreads();
-  if (tid == 0) {
-    unsigned long long b = wkey[0];
-#pragma unroll
-    for (int w = 1; w < kSearchBlock / 32; w++) b = wkey[w] > b ? wkey[w] : b;
-    if (b) atomicMax(g_key, b);
-    __threadfence();
-    unsigned int t = atomicAdd(g_ticket, 1u);
-    is_last = (t == gridDim.x - 1);
-  }
-  __syncthreads();
-  if (is_last && tid == 0) {
-    // every CTA's atomicMax is visible: its fence preceded its ticket
-    unsigned long long key = atomicMax(g_key, 0ull);
-    SearchResult r;
-    r.key = key;
-    r.best_score = key ? key_score(key) : -1;
-    r.count = finalize(p.g, p.cut, s_binom, stab, key, p.intended != 0, r.pos);
-    *g_res = r;
-    *g_key = 0ull;  // leave the scratch clean for the next launch on this stream
-    *g_cursor = 0ull;
-    *g_ticket = 0u;
-  }
-}
-
-// ---------------------------------------------------------------------------------------
-// Subset dynamic programme for ONE large request (gpa_enum.cuh "Subset dynamic programme"): instead of visiting
-// every partition, fill best[R] for every reachable remainder R, one data-parallel pass per layer, then rebuild the
-// first best partition.  n = 16, k = 3: ~1 M (mask, set) pairs instead of 22.4 M partitions.  Tables live in global
-// memory (128 KB + 64 KB, L2-resident); each layer is its own launch, which is the grid-wide barrier between layers.
-struct DpParams {
-  Geom g;
-  int intended;
-  uint32_t rbit;  // lowest required position as a bit, 0 if none
-  uint16_t wp[kMaxDevices * kMaxDevices];
-};
-struct TabAny {
-  const uint16_t *t;
-  __device__ __forceinline__ uint32_t operator()(uint32_t mask) const { return t[mask]; }
-};
-struct TabOk {
-  const uint16_t *t;
-  uint32_t rbit;
-  __device__ __forceinline__ uint32_t operator()(uint32_t mask) const { return t[dp_ok_index(mask, rbit)]; }
-};
-constexpr int kDpThreads = 256;
-
-// layer 1: the score of every mask a set can be
-__global__ void __launch_bounds__(kDpThreads) dp_scores_kernel(const DpParams p, uint16_t *__restrict__ T) {
-  __shared__ uint16_t wp[kMaxDevices * kMaxDevices];
-  for (int i = threadIdx.x; i < kMaxDevices * kMaxDevices; i += kDpThreads) wp[i] = p.wp[i];
-  __syncthreads();
-  fill_score_table(T, wp, p.g, blockIdx.x * kDpThreads + threadIdx.x, gridDim.x * kDpThreads);
-}
-
-// layer j in 2..m-1: best completion of every remainder of j sets, both tables
-__global__ void __launch_bounds__(kDpThreads) dp_layer_kernel(const DpParams p, int j, uint16_t *T, uint16_t *Tok) {
-  const uint32_t total = 1u << p.g.n;
-  const TabAny tany{T};
-  const TabOk tok{Tok, p.rbit};
-  for (uint32_t R = blockIdx.x * kDpThreads + threadIdx.x; R < total; R += gridDim.x * kDpThreads) {
-    if (dp_layer_of(p.g, R) != j) continue;
-    // reads touch layers 1 and j-1 only, writes layer j only: no hazard inside the launch
-    const uint32_t va = dp_value(p.g, tany, tok, R, false);
-    T[R] = (uint16_t)va;
-    if (p.g.rmask != 0 && (R & p.g.rmask) == p.g.rmask) Tok[dp_ok_index(R, p.rbit)] = (uint16_t)dp_value(p.g, tany, tok, R, true);
-  }
-}
-
-// One level of the recursion for remainder R, spread over threads: every first set iterate() would try on R, by its
-// literal rank (decode_item on the sub-request "R with j sets to go"), valued with the tables of the layer below.
-// Returns the thread's best (value, ~rank) key; rank order is visiting order, so the max key is the FIRST best set.
-__device__ __forceinline__ unsigned long long dp_level_key(const Geom &g, const BinomTable &binom, uint32_t R, bool need_ok,
-                                                           const TabAny &tany, const TabOk &tok, int first, int stride,
-                                                           Cut &cut_out) {
-  const Geom sg = make_geom_sparse(R, g.k, need_ok ? g.rmask : 0u, g.tok_pos);
-  Cut cut;
-  cut.d = 1;
-#pragma unroll
-  for (int q = 0; q < kMaxCutDepth; q++) cut.radix[q] = 1;
-  cut.radix[0] = binom_at(binom, sg.m * sg.k - 1, sg.k - 1);
-  cut.n_items = cut.radix[0];
-  cut_out = cut;
-  unsigned long long best = 0;
-  for (unsigned long long item = first; item < cut.n_items; item += stride) {
-    const ItemState st = decode_item(sg, cut, binom, tany, item, nullptr);
-    if (!st.valid) continue;
-    const uint32_t rest = st.rem & g.real_mask;
-    const bool need2 = need_ok && !st.ok;
-    const uint32_t t = !need2 ? tany(rest) : (sg.m == 2 ? dp_ok_base(g, tany(rest), rest) : tok(rest));
-    if (t == kDpInvalid) continue;
-    const unsigned long long kk = pack_key(st.acc + (int)t, item);
-    best = kk > best ? kk : best;
-  }
-  return best;
-}
-
-// layer j, ONE WARP per remainder: for layers whose remainders have many first sets (large k) a single thread
-// walking them one after the other would be the tail of the whole search
-__global__ void __launch_bounds__(kDpThreads) dp_layer_warp_kernel(const DpParams p, int j, uint16_t *T, uint16_t *Tok) {
-  __shared__ BinomTable s_binom;
-  stage_binom(s_binom, threadIdx.x, kDpThreads);
-  __syncthreads();
-  const uint32_t total = 1u << p.g.n;
-  const TabAny tany{T};
-  const TabOk tok{Tok, p.rbit};
-  const int lane = threadIdx.x & 31;
-  const uint32_t warps = gridDim.x * (kDpThreads / 32);
-  for (uint32_t R = blockIdx.x * (kDpThreads / 32) + (threadIdx.x >> 5); R < total; R += warps) {
-    if (dp_layer_of(p.g, R) != j) continue;
-    Cut cut;
-    unsigned long long ka = warp_max_u64(dp_level_key(p.g, s_binom, R, false, tany, tok, lane, 32, cut));
-    unsigned long long ko = 0;
-    const bool has_req = p.g.rmask != 0 && (R & p.g.rmask) == p.g.rmask;
-    if (has_req) ko = warp_max_u64(dp_level_key(p.g, s_binom, R, true, tany, tok, lane, 32, cut));
-    if (lane == 0) {
-      T[R] = (uint16_t)(ka ? (uint32_t)key_score(ka) : kDpInvalid);
-      if (has_req) Tok[dp_ok_index(R, p.rbit)] = (uint16_t)(ko ? (uint32_t)key_score(ko) : kDpInvalid);
-    }
-  }
-}
-
-// top layer + reconstruction in one CTA: level by level, all threads value the first sets of the current remainder,
-// the block-wide max key names the first best one, and the remainder shrinks by it.  No serial replay.
-__global__ void __launch_bounds__(1024) dp_final_kernel(const DpParams p, const uint16_t *T, const uint16_t *Tok, SearchResult *g_res) {
-  __shared__ unsigned long long wkey[32];
-  __shared__ unsigned long long level_key;
-  __shared__ uint32_t sets[kMaxSets];
-  __shared__ BinomTable s_binom;
-  stage_binom(s_binom, threadIdx.x, 1024);
-  __syncthreads();
-  const TabAny tany{T};
-  const TabOk tok{Tok, p.rbit};
-  const Geom &g = p.g;
-  const int tid = threadIdx.x;
-  uint32_t R = g.real_mask;
-  bool need = g.rmask != 0;
-  bool have = true;
-  int top_score = -1;
-  for (int level = 0; level < g.m; level++) {
-    const int left = g.m - level;
-    const bool has_tok = g.P != 0 && (__popc(R) % g.k) != 0;
-    if (left == 1) {
-      if (need && !((R & g.rmask) == g.rmask && !has_tok)) have = false;
-      if (tid == 0) sets[level] = R | (has_tok ? g.tok_bit : 0u);
-      if (level == 0 && have) top_score = (int)tany(R);
-      break;
-    }
-    Cut cut;
-    unsigned long long best = warp_max_u64(dp_level_key(g, s_binom, R, need, tany, tok, tid, 1024, cut));
-    if ((tid & 31) == 0) wkey[tid >> 5] = best;
-    __syncthreads();
-    if (tid == 0) {
-      for (int w = 1; w < 32; w++) best = wkey[w] > best ? wkey[w] : best;
-      level_key = best;
-    }
-    __syncthreads();
-    const unsigned long long key = level_key;
-    if (key == 0) {
-      have = false;
-      break;
-    }
-    if (level == 0) top_score = key_score(key);
-    // every thread decodes the winner, so R and `need` stay uniform without another broadcast
-    const Geom sg = make_geom_sparse(R, g.k, need ? g.rmask : 0u, g.tok_pos);
-    uint32_t set = 0;
-    const ItemState st = decode_item(sg, cut, s_binom, tany, key_item(key), &set);
-    if (tid == 0) sets[level] = set;
-    R = st.rem & g.real_mask;
-    need = need && !st.ok;
-    __syncthreads();  // wkey / level_key are reused by the next level
-  }
-  __syncthreads();
-  if (tid == 0) {
-    SearchResult r;
-    r.key = 0;
-    r.count = 0;
-    r.best_score = have ? top_score : -1;
-    if (have) {
-      uint32_t local_sets[kMaxSets];
-      for (int q = 0; q < g.m; q++) local_sets[q] = sets[q];
-      uint32_t best_set = 0;
-      if (choose_from_partition(g, tany, local_sets, p.intended != 0, best_set) > 0) {
-        int o = 0;
-        uint32_t reals = best_set & g.real_mask;
-        while (reals) {
-          r.pos[o++] = (int8_t)(__ffs(reals) - 1);
-          reals &= reals - 1;
-        }
-        if (best_set & g.tok_bit)
-          for (int q = 0; q < g.P; q++) r.pos[o++] = -1;
-        r.count = o;
-      }
-    }
-    *g_res = r;
-  }
-}
-
-// ---------------------------------------------------------------------------------------
-// Batch: one warp per container request.
-
-constexpr int8_t kResDefer = -126;  // internal: "left to the general kernel"; never leaves the library
-
-struct BatchTopo {
-  const uint16_t *wq;   // nt*nt scaled weights
-  const uint8_t *asym;  // nt*nt, 1 where the link counts of (i,j) and (j,i) differ
-  int nt;
-};
-
-__device__ __forceinline__ void write_result(gpa_result *out, const int8_t *dev) {
-  const int4 *src = reinterpret_cast<const int4 *>(dev);
-  *reinterpret_cast<int4 *>(out->dev) = *src;
-}
-
-// General batch kernel: any `available` order, per-request score table, one warp per request.
-// With deferred_only it answers just the records the fast kernel marked GPA_RES_DEFER: each
-// warp scans 32 result records at a time (one coalesced load) and works on the marked ones.
-__global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_kernel(const gpa_request *__restrict__ reqs, int count,
-                                                                            int n_cap, int intended, BatchTopo topo,
-                                                                            gpa_result *out, int deferred_only) {
-  extern __shared__ __align__(16) uint16_t smem[];
-  __shared__ BinomTable s_binom;
-  stage_binom(s_binom, threadIdx.x, kBatchWarps * 32);
-  __syncthreads();
-  const int lane = threadIdx.x & 31;
-  const int warp = threadIdx.x >> 5;
-  uint16_t *S = smem + (size_t)warp * ((1u << n_cap) + kMaxDevices * kMaxDevices);
-  uint16_t *wp = S + (1u << n_cap);
-  const STab stab{S};
-
-  auto process = [&](int r) {
-    // 32-byte record, same address in every lane: one broadcast transaction each
-    const uint4 lo = __ldg(reinterpret_cast<const uint4 *>(reqs + r));
-    const uint4 hi = __ldg(reinterpret_cast<const uint4 *>(reqs + r) + 1);
-    const uint32_t availw[4] = {lo.x, lo.y, lo.z, lo.w};
-    const uint32_t rmask = hi.x & 0xFFFFu;
-    const int n = (hi.x >> 16) & 0xFF;
-    const int size = (hi.x >> 24) & 0xFF;
-    const int flags = hi.y & 0xFF;
-    const int n_req = __popc(rmask) + ((hi.y >> 8) & 0xFF);
-    auto dev_at = [&](int pidx) -> int { return (availw[pidx >> 2] >> ((pidx & 3) * 8)) & 0xFF; };
-
-    __align__(16) int8_t res[GPA_MAX_AVAILABLE];
-#pragma unroll
-    for (int i = 0; i < GPA_MAX_AVAILABLE; i++) res[i] = GPA_RES_END;
-    int err = 0;
-    bool done = false;
-
-    // guards of besteffort_policy.go:35-45, in the reference's order
-    if (size <= 0 || n < size || n_req > size) done = true;
-    if (!done) {
-      if (n > n_cap || n > GPA_BATCH_MAX_AVAILABLE) {
-        err = GPA_ERR_TOO_LARGE;
-      } else {
-        unsigned long long seen = 0;
-        for (int a = 0; a < n; a++) {
-          int d = dev_at(a);
-          if (d >= topo.nt) {
-            err = GPA_ERR_INVALID;
-          } else {
-            if (seen >> d & 1ull) err = GPA_ERR_INVALID;  // the same device twice
-            seen |= 1ull << d;
-          }
-        }
-        if ((rmask >> n) != 0) err = GPA_ERR_INVALID;
-      }
-      if (err) done = true;
-    }
-    if (!done && (flags & GPA_REQ_FOREIGN)) done = true;  // no candidate can contain a foreign pointer (:53)
-    if (!done && size == 1) {
-      // :219-224 — single-device candidates in `available` order, first accepted wins (score 0 never beats 0)
-      res[0] = (int8_t)dev_at(rmask ? __ffs(rmask) - 1 : 0);
-      done = true;
-    }
-    if (!done) {
-      // link-count symmetry over the available devices (where calculateGPUPairScore would panic, :307-310)
-      int bad = 0;
-      for (int i = lane; i < n * n; i += 32) {
-        int a = i / n, b = i - a * n;
-        int da = dev_at(a), db = dev_at(b);
-        bad |= topo.asym[da * topo.nt + db];
-        if (a < b) wp[a * kMaxDevices + b] = topo.wq[da * topo.nt + db];
-      }
-      bad = __any_sync(0xffffffffu, bad);
-      if (bad) {
-        err = GPA_ERR_ASYMMETRIC;
-        done = true;
-      }
-    }
-    if (!done) {
-      __syncwarp();
-      const Geom g = make_geom(n, size, rmask);
-      fill_score_table(S, wp, g, lane, 32);
-      __syncwarp();
-      const Cut cut = choose_cut(g, s_binom, 64);
-      unsigned long long best = 0;
-      for (unsigned long long item = lane; item < cut.n_items; item += 32) {
-        int sc = search_item(g, cut, s_binom, stab, item);
-        if (sc >= 0) {
-          unsigned long long kk = pack_key(sc, item);
-          best = kk > best ? kk : best;
-        }
-      }
-      best = warp_max_u64(best);
-      if (lane == 0) {
-        int8_t pos[32];
-        int cnt = finalize(g, cut, s_binom, stab, best, intended != 0, pos);
-        if (cnt < 0) {
-          err = GPA_ERR_INVALID;
-        } else {
-          for (int i = 0; i < cnt; i++) res[i] = pos[i] < 0 ? (int8_t)GPA_NIL : (int8_t)dev_at(pos[i]);
-        }
-      }
-      __syncwarp();  // S / wp are reused by the next request of this warp
-    }
-    if (lane == 0) {
-      if (err) {
-        res[0] = GPA_RES_ERROR;
-        res[1] = (int8_t)err;
-      }
-      write_result(out + r, res);
-    }
-  };
-
-  if (!deferred_only) {
-    for (int r = blockIdx.x * kBatchWarps + warp; r < count; r += gridDim.x * kBatchWarps) process(r);
-  } else {
-    for (long long base = ((long long)blockIdx.x * kBatchWarps + warp) * 32; base < count;
-         base += (long long)gridDim.x * kBatchWarps * 32) {
-      const long long r = base + lane;
-      const bool marked = r < count && out[r].dev[0] == kResDefer;
-      unsigned todo = __ballot_sync(0xffffffffu, marked);
-      while (todo) {
-        const int b = __ffs(todo) - 1;
-        todo &= todo - 1;
-        process((int)(base + b));
-        __syncwarp();
-      }
-    }
-  }
-}
-
-// ---------------------------------------------------------------------------------------
-// Fast batch kernel for requests in CANONICAL order: the devices of every request are listed
-// in one node-wide order (the reference always does: stripReplicas sorts the UUIDs,
-// cmd/nvidia-device-plugin/replica.go:43).  Devices are relabelled by their rank in that
-// order, so a request is just a label MASK, positions are labels, and one score table over
-// all 2^nt label masks serves every request of the node: no per-request table, no gather.
-//
-// One LANE answers one request.  Requests of different shapes (n available, size k) walk
-// differently shaped trees, and lanes of a warp that take different paths run one after the
-// other, so each CTA first BINS its tile of kTile requests by shape in shared memory
-// (counting sort on n*13+k) and then hands the sorted order to its threads: the 32 lanes of
-// a warp get neighbours in that order, i.e. (almost always) the same shape.
-//   pass 1  coalesced load, parse, guards; trivial answers are stored at once; searches leave
-//           a compact record {label mask, required mask, size} and take a rank in their bin;
-//   pass 2  one warp turns the bin counts into offsets;
-//   pass 3  records are threaded into the sorted index;
-//   pass 4  lane p takes sorted record p: search, epilogue, 16-byte store.
-// Anything unusual (order foreign to the node, unknown device, more than 12 devices) is marked
-// GPA_RES_DEFER for the general kernel.
-constexpr int kFastMaxTopo = 12;
-constexpr int kTile = 4096;
-constexpr int kFastThreads = 256;
-constexpr int kShapeBins = 13 * 13 + 7;  // n*13 + k for n,k <= 12, padded to 176
-
-struct FastTopo {
-  const uint16_t *s_full;  // [1 << nt] scaled set scores over label masks
-  int nt;
-  uint8_t order[16];  // label -> NVML index
-  uint8_t rank[GPA_MAX_TOPOLOGY];  // NVML index -> label, 0xFF = not on this node
-};
-
-__device__ __noinline__ int fast_search_item(const Geom &g, const Cut &cut, const uint16_t *S, unsigned long long item) {
-  return search_item(g, cut, c_binom, STab{S}, item);
-}
-__device__ __noinline__ int fast_finalize(const Geom &g, const Cut &cut, const uint16_t *S, unsigned long long key, bool intended,
-                                          uint32_t &best_set) {
-  return finalize_set(g, cut, c_binom, STab{S}, key, intended, best_set);
-}
-
-// Whole-tree search of a shallow request (m <= 4 sets) in one lane; returns like finalize_set.
-__device__ __forceinline__ int fast_tracked_search(const Geom &g, const uint16_t *S, bool intended, uint32_t &best_set) {
-  const STab stab{S};
-  Track tr;
-  tr.best = -1;
-  uint32_t path[kMaxSuffix];
-  const uint32_t all = g.real_mask | g.tok_bit;
-  switch (g.m) {
-    case 1: walk_track<1, 1>(g, stab, all, 0, false, path, tr); break;
-    case 2: walk_track<2, 2>(g, stab, all, 0, false, path, tr); break;
-    case 3: walk_track<3, 3>(g, stab, all, 0, false, path, tr); break;
-    default: walk_track<4, 4>(g, stab, all, 0, false, path, tr); break;
-  }
-  best_set = 0;
-  if (tr.best < 0) return 0;  // no accepted partition: bestPartition == nil (:72-74)
-  return choose_from_partition(g, stab, tr.sets, intended, best_set);
-}
-
-__device__ __forceinline__ void res_set_byte(unsigned long long &r0, unsigned long long &r1, int i, int v) {
-  unsigned long long b = (unsigned long long)(v & 0xFF);
-  if (i < 8) r0 = (r0 & ~(0xFFull << (8 * i))) | (b << (8 * i));
-  else r1 = (r1 & ~(0xFFull << (8 * (i - 8)))) | (b << (8 * (i - 8)));
-}
-__device__ __forceinline__ void res_store(gpa_result *dst, unsigned long long r0, unsigned long long r1) {
-  uint4 v;
-  v.x = (uint32_t)r0;
-  v.y = (uint32_t)(r0 >> 32);
-  v.z = (uint32_t)r1;
-  v.w = (uint32_t)(r1 >> 32);
-  *reinterpret_cast<uint4 *>(dst->dev) = v;
-}
-
-constexpr size_t fast_smem_bytes(int nt) {
-  return ((size_t)1 << nt) * sizeof(uint16_t)  // S
-         + (size_t)kTile * sizeof(uint32_t)    // w_mr
-         + (size_t)kTile * sizeof(uint16_t) * 2  // w_rank, sorted_idx
-         + (size_t)kTile * 2                     // w_k, w_key
-         + (size_t)(kShapeBins + 1) * sizeof(uint32_t) * 2;  // hist, offs
-}
-
-// kMasks = false: 32-byte gpa_request in, 16-byte gpa_result out.
-// kMasks = true : 8-byte gpa_mask_request in (the caller already holds label masks), 4-byte gpa_mask_result out.
-template <bool kMasks>
-__global__ void __launch_bounds__(kFastThreads) besteffort_batch_fast_kernel(const void *__restrict__ reqs_v, int count,
-                                                                             int intended, const FastTopo ft,
-                                                                             void *__restrict__ out_v) {
-  const gpa_request *__restrict__ reqs = static_cast<const gpa_request *>(reqs_v);
-  gpa_result *__restrict__ out = static_cast<gpa_result *>(out_v);
-  const uint2 *__restrict__ mreqs = static_cast<const uint2 *>(reqs_v);
-  uint32_t *__restrict__ mout = static_cast<uint32_t *>(out_v);
-  extern __shared__ __align__(16) unsigned char fsmem[];
-  uint32_t *w_mr = reinterpret_cast<uint32_t *>(fsmem);
-  uint32_t *hist = w_mr + kTile;
-  uint32_t *offs = hist + (kShapeBins + 1);
-  uint16_t *S = reinterpret_cast<uint16_t *>(offs + (kShapeBins + 1));
-  uint16_t *w_rank = S + ((size_t)1 << ft.nt);
-  uint16_t *sorted_idx = w_rank + kTile;
-  uint8_t *w_k = reinterpret_cast<uint8_t *>(sorted_idx + kTile);
-  uint8_t *w_key = w_k + kTile;
-
-  const int tid = threadIdx.x;
-  for (uint32_t i = tid; i < (1u << ft.nt); i += kFastThreads) S[i] = ft.s_full[i];
-
-  const long long n_tiles = ((long long)count + kTile - 1) / kTile;
-  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const long long tile_base = tile * kTile;
-    for (int b = tid; b <= kShapeBins; b += kFastThreads) hist[b] = 0;
-    __syncthreads();
-
-    // ---- pass 1: parse; answer the trivial ones; bin the searches by shape
-#pragma unroll 1
-    for (int i = tid; i < kTile; i += kFastThreads) {
-      const long long r = tile_base + i;
-      int bin = 0xFF;
-      if (r < count) {
-        if constexpr (kMasks) {
-          // {avail_mask:16, req_mask:16} {size:8, flags:8, n_req_extra:8, reserved:8}
-          const uint2 rec = __ldg(mreqs + r);
-          const uint32_t mask = rec.x & 0xFFFFu, rlab_in = rec.x >> 16;
-          const int size = rec.y & 0xFF, flags = (rec.y >> 8) & 0xFF;
-          const int n = __popc(mask);
-          const int n_req = __popc(rlab_in) + ((rec.y >> 16) & 0xFF);
-          uint32_t result = 0;  // {chosen_mask:16, n_nil:8, status:8}: the empty answer
-          bool search = false;
-          if ((mask >> ft.nt) != 0 || (rlab_in >> ft.nt) != 0) {
-            result = (uint32_t)(GPA_ERR_INVALID & 0xFF) << 24;
-          } else if (!(size <= 0 || n < size || n_req > size)) {  // guards of besteffort_policy.go:35-45
-            if ((flags & GPA_REQ_FOREIGN) || (rlab_in & ~mask) != 0) {
-              // a required device that is not available is in no set (:53) -> empty answer
-            } else if (size == 1) {
-              result = rlab_in ? (rlab_in & (0u - rlab_in)) : (mask & (0u - mask));  // :219-224
-            } else {
-              search = true;
-              w_mr[i] = mask | (rlab_in << 16);
-              w_k[i] = (uint8_t)size;
-              bin = c_shape_bin[n][size];
-              w_rank[i] = (uint16_t)atomicAdd(&hist[bin], 1u);
-            }
-          }
-          if (!search) mout[r] = result;
-        } else {
-        const uint4 lo = __ldg(reinterpret_cast<const uint4 *>(reqs + r));
-        const uint4 hi = __ldg(reinterpret_cast<const uint4 *>(reqs + r) + 1);
-        const uint32_t rmask = hi.x & 0xFFFFu;
-        const int n = (hi.x >> 16) & 0xFF;
-        const int size = (hi.x >> 24) & 0xFF;
-        const int flags = hi.y & 0xFF;
-        const int n_req = __popc(rmask) + ((hi.y >> 8) & 0xFF);
-        unsigned long long r0 = 0x8080808080808080ull, r1 = 0x8080808080808080ull;  // 16 x GPA_RES_END
-        bool search = false;
-        // guards of besteffort_policy.go:35-45
-        if (!(size <= 0 || n < size || n_req > size)) {
-          if (n > kFastMaxTopo || (rmask >> n) != 0) {
-            res_set_byte(r0, r1, 0, kResDefer);
-          } else {
-            // relabel: device -> rank in the node order; the list must be strictly ascending
-            const uint32_t w[4] = {lo.x, lo.y, lo.z, lo.w};
-            uint32_t mask = 0, rlab = 0;
-            int prev = -1, first_dev = 0, first_req_dev = -1;
-            bool defer = false;
-#pragma unroll
-            for (int p = 0; p < kFastMaxTopo; p++) {
-              if (p < n) {
-                const int d = (w[p >> 2] >> ((p & 3) * 8)) & 0xFF;
-                const int lab = d < GPA_MAX_TOPOLOGY ? ft.rank[d] : 0xFF;
-                defer = defer || lab == 0xFF || lab <= prev;
-                prev = lab;
-                mask |= 1u << (lab & 31);
-                if (rmask >> p & 1u) {
-                  rlab |= 1u << (lab & 31);
-                  if (first_req_dev < 0) first_req_dev = d;
-                }
-                if (p == 0) first_dev = d;
-              }
-            }
-            if (defer) {
-              res_set_byte(r0, r1, 0, kResDefer);
-            } else if (flags & GPA_REQ_FOREIGN) {
-              // a required pointer that is in no set: every candidate is rejected (:53) -> empty answer
-            } else if (size == 1) {
-              // :219-224 — first accepted single-device candidate
-              res_set_byte(r0, r1, 0, first_req_dev >= 0 ? first_req_dev : first_dev);
-            } else {
-              search = true;
-              w_mr[i] = (mask & 0xFFFFu) | (rlab << 16);
-              w_k[i] = (uint8_t)size;
-              bin = c_shape_bin[n][size];
-              w_rank[i] = (uint16_t)atomicAdd(&hist[bin], 1u);
-            }
-          }
-        }
-        if (!search) res_store(out + r, r0, r1);
-        }
-      }
-      w_key[i] = (uint8_t)bin;
-    }
-    __syncthreads();
-
-    // ---- pass 2: bin counts -> offsets (one warp, 6 bins per lane)
-    if (tid < 32) {
-      constexpr int kPer = (kShapeBins + 31) / 32;
-      uint32_t local[kPer];
-      uint32_t sum = 0;
-#pragma unroll
-      for (int q = 0; q < kPer; q++) {
-        const int b = tid * kPer + q;
-        local[q] = b < kShapeBins ? hist[b] : 0u;
-        sum += local[q];
-      }
-      uint32_t incl = sum;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
-        if (tid >= o) incl += v;
-      }
-      uint32_t run = incl - sum;
-#pragma unroll
-      for (int q = 0; q < kPer; q++) {
-        const int b = tid * kPer + q;
-        if (b < kShapeBins) offs[b] = run;
-        run += local[q];
-      }
-      if (tid == 31) offs[kShapeBins] = incl;
-    }
-    __syncthreads();
-
-    // ---- pass 3: thread the records into shape order
-#pragma unroll 1
-    for (int i = tid; i < kTile; i += kFastThreads) {
-      const int bin = w_key[i];
-      if (bin != 0xFF) sorted_idx[offs[bin] + w_rank[i]] = (uint16_t)i;
-    }
-    __syncthreads();
-
-    // ---- pass 4: one lane per search, neighbours in shape order.  Warps draw chunks of 32 sorted records from
-    // a shared cursor (hist[kShapeBins], zero after pass 1), heaviest shapes first, so no warp is left holding
-    // a long tail while the others wait at the barrier.
-    const int n_search = (int)offs[kShapeBins];
-    const int lane = tid & 31;
-#pragma unroll 1
-    for (;;) {
-      int p0 = 0;
-      if (lane == 0) p0 = (int)atomicAdd(&hist[kShapeBins], 32u);
-      p0 = __shfl_sync(0xffffffffu, p0, 0);
-      if (p0 >= n_search) break;
-      const int p = p0 + lane;
-      if (p >= n_search) continue;
-      const int i = sorted_idx[p];
-      const uint32_t mr = w_mr[i];
-      const Geom g = make_geom_sparse(mr & 0xFFFFu, w_k[i], mr >> 16, ft.nt);
-      unsigned long long r0 = 0x8080808080808080ull, r1 = 0x8080808080808080ull;
-      uint32_t best_set = 0;
-      int rc;
-      if (g.m <= kMaxSuffix) {
-        // the whole tree in this lane, best partition tracked in registers
-        rc = fast_tracked_search(g, S, intended != 0, best_set);
-      } else {
-        // deep trees (k = 2 on 9+ devices): the first m - 4 levels come from an item index, then replay
-        const Cut cut = choose_cut(g, c_binom, 1);
-        unsigned long long key = 0;
-        for (unsigned long long item = 0; item < cut.n_items; item++) {
-          const int sc = fast_search_item(g, cut, S, item);
-          if (sc >= 0) {
-            const unsigned long long kk = pack_key(sc, item);
-            key = kk > key ? kk : key;
-          }
-        }
-        rc = fast_finalize(g, cut, S, key, intended != 0, best_set);
-      }
-      if constexpr (kMasks) {
-        uint32_t result = 0;
-        if (rc < 0) result = (uint32_t)(GPA_ERR_INVALID & 0xFF) << 24;
-        else if (rc > 0) result = (best_set & g.real_mask) | ((best_set & g.tok_bit) ? ((uint32_t)g.P << 16) : 0u);
-        mout[tile_base + i] = result;
-      } else {
-        if (rc < 0) {
-          res_set_byte(r0, r1, 0, GPA_RES_ERROR);
-          res_set_byte(r0, r1, 1, GPA_ERR_INVALID);
-        } else if (rc > 0) {
-          int o = 0;
-          uint32_t reals = best_set & g.real_mask;
-          while (reals) {
-            const int lab = __ffs(reals) - 1;
-            reals &= reals - 1;
-            res_set_byte(r0, r1, o++, ft.order[lab]);
-          }
-          if (best_set & g.tok_bit)
-            for (int q = 0; q < g.P; q++) res_set_byte(r0, r1, o++, GPA_NIL);
-        }
-        res_store(out + tile_base + i, r0, r1);
-      }
-    }
-    __syncthreads();  // the tile's shared arrays are reused by the next tile
-  }
-}
 
 // ---------------------------------------------------------------------------------------
 // Host side

@@ -1,0 +1,82 @@
+// Shared device-side pieces of the allocation kernels: constant tables, score-table fill, reductions.
+// Part of the single translation unit gpualloc.cu (the kernels share __constant__ tables and the
+// enumeration core); not compiled on its own.
+#pragma once
+
+namespace {
+
+using namespace gpa;
+
+__constant__ BinomTable c_binom;
+// candidate partitions of (n available, size k), n,k <= 12, saturated at 2^32-1: work estimate of the fast batch path
+__constant__ uint32_t c_parts[13][13];
+// shape (n, k) -> bin of the fast batch kernel's counting sort: bins are numbered by DESCENDING work, so the sorted
+// order of a tile starts with its most expensive searches (longest-processing-time-first scheduling)
+__constant__ uint8_t c_shape_bin[13][13];
+
+constexpr int kSearchBlockSmall = 256;   // score table <= 32 KB: several CTAs per SM
+constexpr int kSearchBlockLarge = 1024;  // 64-128 KB table: one or two CTAs per SM, so make them wide
+constexpr int kBatchWarps = 8;
+constexpr int kScoreCap = 65535;                        // uint16 set-score table
+constexpr int kMaxPairs = (kMaxDevices * (kMaxDevices - 1)) / 2;  // 120
+
+// The binomial table is read with a DIFFERENT index in every lane while item ranks are decoded; constant memory
+// serialises such reads one address at a time, shared memory does not, so kernels that decode stage it first.
+__device__ __forceinline__ void stage_binom(BinomTable &dst, int tid, int nthreads) {
+  const uint32_t *src = &c_binom.c[0][0];
+  uint32_t *d = &dst.c[0][0];
+  for (int i = tid; i < 32 * 17; i += nthreads) d[i] = src[i];
+}
+
+struct STab {
+  const uint16_t *s;
+  __device__ __forceinline__ uint32_t operator()(uint32_t mask) const { return s[mask]; }
+};
+
+struct SearchParams {
+  Geom g;
+  Cut cut;
+  int intended;
+  uint16_t wp[kMaxDevices * kMaxDevices];  // scaled weight of (earlier position a, later position b) at [a*16+b]
+};
+
+struct SearchResult {
+  int32_t count;  // k, 0 = empty answer, -1 = internal inconsistency
+  int32_t best_score;
+  int8_t pos[32];  // positions, -1 = nil pad
+  unsigned long long key;
+};
+
+// Score table of every mask a set can be: k reals, or k-P reals next to the pads.
+__device__ __forceinline__ void fill_score_table(uint16_t *S, const uint16_t *wp, const Geom &g, int tid, int nthreads) {
+  const uint32_t total = 1u << g.n;
+  const int kp = g.P ? g.k - g.P : -1;
+  for (uint32_t mask = tid; mask < total; mask += nthreads) {
+    int pc = __popc(mask);
+    if (pc != g.k && pc != kp) continue;
+    uint32_t sum = 0;
+    uint32_t ma = mask;
+    while (ma) {
+      int a = __ffs(ma) - 1;
+      ma &= ma - 1;
+      uint32_t mb = ma;
+      while (mb) {
+        int b = __ffs(mb) - 1;
+        mb &= mb - 1;
+        sum += wp[a * kMaxDevices + b];
+      }
+    }
+    S[mask] = (uint16_t)sum;
+  }
+}
+
+__device__ __forceinline__ unsigned long long warp_max_u64(unsigned long long v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    unsigned long long u = __shfl_xor_sync(0xffffffffu, v, o);
+    v = u > v ? u : v;
+  }
+  return v;
+}
+
+}  // namespace
