@@ -14,6 +14,7 @@ namespace {
 struct DpParams {
   Geom g;
   int intended;
+  unsigned int seq;
   uint32_t rbit;  // lowest required position as a bit, 0 if none
   uint16_t wp[kMaxDevices * kMaxDevices];
 };
@@ -159,6 +160,8 @@ __global__ void __launch_bounds__(1024) dp_final_kernel(const DpParams p, const 
     r.key = 0;
     r.count = 0;
     r.best_score = have ? top_score : -1;
+#pragma unroll
+    for (int q = 0; q < 32; q++) r.pos[q] = 0;
     if (have) {
       uint32_t local_sets[kMaxSets];
       for (int q = 0; q < g.m; q++) local_sets[q] = sets[q];
@@ -175,7 +178,7 @@ __global__ void __launch_bounds__(1024) dp_final_kernel(const DpParams p, const 
         r.count = o;
       }
     }
-    *g_res = r;
+    publish_result(g_res, r, p.seq);
   }
 }
 

@@ -22,6 +22,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
 #include <mutex>
 #include <string>
 #include <utility>
@@ -75,8 +76,10 @@ struct gpa_ctx {
   // scratch + mailbox
   unsigned long long *d_key = nullptr;
   unsigned int *d_ticket = nullptr;
-  SearchResult *d_res = nullptr;
-  SearchResult *h_res = nullptr;  // pinned
+  SearchResult *h_res = nullptr;  // pinned + device-mapped mailbox the search kernels answer into
+  SearchResult *d_res = nullptr;  // the same memory as the device sees it
+  unsigned int seq = 0;           // launch number of the last single-request search
+  bool timing_pending = false;    // ev0/ev1 of the last search not read back yet
   // topology (host copy + device tables)
   Topology topo;
   bool has_topo = false;
@@ -281,10 +284,11 @@ int gpa_create(int cuda_device, gpa_ctx **out) {
   CREATE_TRY(cudaEventCreate(&ctx->ev1));
   CREATE_TRY(cudaMalloc(&ctx->d_key, 2 * sizeof(unsigned long long)));  // [0] reduction key, [1] item cursor
   CREATE_TRY(cudaMalloc(&ctx->d_ticket, sizeof(unsigned int)));
-  CREATE_TRY(cudaMalloc(&ctx->d_res, sizeof(SearchResult)));
+  CREATE_TRY(cudaHostAlloc(&ctx->h_res, sizeof(SearchResult), cudaHostAllocMapped));
+  memset(ctx->h_res, 0, sizeof(SearchResult));
+  CREATE_TRY(cudaHostGetDevicePointer(&ctx->d_res, ctx->h_res, 0));
   CREATE_TRY(cudaMalloc(&ctx->d_dp_any, ((size_t)1 << kMaxDevices) * sizeof(uint16_t)));
   CREATE_TRY(cudaMalloc(&ctx->d_dp_ok, ((size_t)1 << (kMaxDevices - 1)) * sizeof(uint16_t)));
-  CREATE_TRY(cudaMallocHost(&ctx->h_res, sizeof(SearchResult)));
   CREATE_TRY(cudaMemset(ctx->d_key, 0, 2 * sizeof(unsigned long long)));
   CREATE_TRY(cudaMemset(ctx->d_ticket, 0, sizeof(unsigned int)));
   fill_binom(ctx->binom);
@@ -321,7 +325,6 @@ void gpa_destroy(gpa_ctx *ctx) {
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   if (ctx->d_key) cudaFree(ctx->d_key);
   if (ctx->d_ticket) cudaFree(ctx->d_ticket);
-  if (ctx->d_res) cudaFree(ctx->d_res);
   if (ctx->d_dp_any) cudaFree(ctx->d_dp_any);
   if (ctx->d_dp_ok) cudaFree(ctx->d_dp_ok);
   if (ctx->h_res) cudaFreeHost(ctx->h_res);
@@ -456,6 +459,7 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
   if (!ctx->has_topo) return GPA_ERR_NO_TOPOLOGY;
   const Topology &T = ctx->topo;
   memset(&ctx->stats, 0, sizeof ctx->stats);
+  ctx->timing_pending = false;
   ctx->stats.best_score = -1;
   ctx->stats.score_unit = T.unit;
 
@@ -511,6 +515,8 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
   memset(&sp, 0, sizeof sp);
   sp.g = make_geom(n_avail, size, rmask);
   sp.intended = (mode_flags & GPA_MODE_INTENDED) ? 1 : 0;
+  sp.seq = ++ctx->seq;
+  if (sp.seq == 0) sp.seq = ++ctx->seq;  // 0 is the mailbox's initial value
   for (int a = 0; a < n_avail; a++)
     for (int b = a + 1; b < n_avail; b++) sp.wp[a * kMaxDevices + b] = T.wq[avail[a] * T.n + avail[b]];
   const uint64_t parts = partition_count(sp.g, ctx->binom);
@@ -527,6 +533,7 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
     memset(&dp, 0, sizeof dp);
     dp.g = sp.g;
     dp.intended = sp.intended;
+    dp.seq = sp.seq;
     dp.rbit = rmask ? (rmask & (0u - rmask)) : 0u;
     memcpy(dp.wp, sp.wp, sizeof dp.wp);
     const uint32_t total = 1u << n_avail;
@@ -575,10 +582,29 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
   }
   CUDA_TRY(ctx, cudaGetLastError());
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
-  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_res, ctx->d_res, sizeof(SearchResult), cudaMemcpyDeviceToHost, ctx->stream));
-  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-  float ms = 0;
-  cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+  // Wait for the answer where it lands: the kernel's last thread writes the record into the mapped mailbox and then
+  // its launch number.  The stream is polled now and then so that a failed launch ends the wait.
+  {
+    volatile unsigned int *seq = &ctx->h_res->seq;
+    unsigned spins = 0;
+    while (*seq != sp.seq) {
+      if ((++spins & 0x3FFu) == 0) {
+        cudaError_t q = cudaStreamQuery(ctx->stream);
+        if (q != cudaErrorNotReady) {
+          if (q != cudaSuccess) {
+            ctx->last_error = std::string("search kernel: ") + cudaGetErrorString(q);
+            return GPA_ERR_CUDA;
+          }
+          if (*seq != sp.seq) {  // stream drained without an answer: cannot happen unless the kernel was not run
+            ctx->last_error = "search kernel finished without publishing its answer";
+            return GPA_ERR_CUDA;
+          }
+        }
+      }
+    }
+    std::atomic_thread_fence(std::memory_order_acquire);
+  }
+  ctx->timing_pending = true;
 
   ctx->stats.partitions = parts;
   ctx->stats.items = sp.cut.n_items;
@@ -589,7 +615,7 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
   ctx->stats.grid = grid;
   ctx->stats.block = block;
   ctx->stats.smem_bytes = (int)smem;
-  ctx->stats.kernel_ms = ms;
+  ctx->stats.kernel_ms = 0;
   ctx->stats.algorithm = use_dp ? 2 : 1;
 
   const SearchResult &r = *ctx->h_res;
@@ -605,6 +631,12 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
 int gpa_last_search_stats(gpa_ctx *ctx, gpa_search_stats *out) {
   if (!ctx || !out) return GPA_ERR_INVALID;
   std::lock_guard<std::mutex> lk(ctx->mu);
+  if (ctx->timing_pending) {  // the device time of the last search is read here, off the decision's critical path
+    float ms = 0;
+    if (cudaEventSynchronize(ctx->ev1) == cudaSuccess && cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1) == cudaSuccess)
+      ctx->stats.kernel_ms = ms;
+    ctx->timing_pending = false;
+  }
   *out = ctx->stats;
   return GPA_OK;
 }

@@ -2,6 +2,7 @@
 // Part of the single translation unit gpualloc.cu (the kernels share __constant__ tables and the
 // enumeration core); not compiled on its own.
 #pragma once
+#include <cstddef>
 
 namespace {
 
@@ -37,15 +38,34 @@ struct SearchParams {
   Geom g;
   Cut cut;
   int intended;
+  unsigned int seq;
   uint16_t wp[kMaxDevices * kMaxDevices];  // scaled weight of (earlier position a, later position b) at [a*16+b]
 };
 
-struct SearchResult {
+// Answer of a single-request search.  It lives in PINNED, DEVICE-MAPPED host memory: the last thread of the search
+// writes the record straight across PCIe, fences, and then publishes `seq`; the host spins on `seq` instead of paying
+// for a D2H copy and a stream synchronisation (about 10 us of a 30 us call).
+struct __align__(16) SearchResult {
   int32_t count;  // k, 0 = empty answer, -1 = internal inconsistency
   int32_t best_score;
   int8_t pos[32];  // positions, -1 = nil pad
   unsigned long long key;
+  unsigned int seq;  // launch number this record belongs to; written last
+  unsigned int reserved;
 };
+
+static_assert(sizeof(SearchResult) == 64 && offsetof(SearchResult, seq) == 48, "three 16-byte stores cover everything before seq");
+
+__device__ __forceinline__ void publish_result(SearchResult *dst, const SearchResult &r, unsigned int seq) {
+  // 48 bytes of payload as three 16-byte stores (one PCIe write each), then the fence, then the flag
+  const uint4 *src = reinterpret_cast<const uint4 *>(&r);
+  uint4 *out = reinterpret_cast<uint4 *>(dst);
+  out[0] = src[0];
+  out[1] = src[1];
+  out[2] = src[2];
+  __threadfence_system();
+  *reinterpret_cast<volatile unsigned int *>(&dst->seq) = seq;
+}
 
 // Score table of every mask a set can be: k reals, or k-P reals next to the pads.
 __device__ __forceinline__ void fill_score_table(uint16_t *S, const uint16_t *wp, const Geom &g, int tid, int nthreads) {

@@ -124,11 +124,13 @@ __global__ void __launch_bounds__(kSearchBlock, kSearchBlock >= 1024 ? 1 : 4) be
     SearchResult r;
     r.key = key;
     r.best_score = key ? key_score(key) : -1;
+#pragma unroll
+    for (int i = 0; i < 32; i++) r.pos[i] = 0;
     r.count = finalize(p.g, p.cut, s_binom, stab, key, p.intended != 0, r.pos);
-    *g_res = r;
     *g_key = 0ull;  // leave the scratch clean for the next launch on this stream
     *g_cursor = 0ull;
     *g_ticket = 0u;
+    publish_result(g_res, r, p.seq);
   }
 }
 

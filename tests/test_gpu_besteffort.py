@@ -341,6 +341,82 @@ def test_mask_format_matches_record_format_and_oracle(ctx, oracle):
     assert r["status"][5] == gpa.ERR_INVALID and r["chosen_mask"][6] == 0 and r["status"][6] == 0
 
 
+def test_maximum_sizes(ctx, oracle):
+    """64-device topology (GPA_MAX_TOPOLOGY), 16 available devices (GPA_MAX_AVAILABLE), one too many of each"""
+    t = syn.topo_random(64, 9)
+    W, nl = install(ctx, t)
+    rng = np.random.default_rng(1)
+    for n, k in ((16, 8), (16, 16), (12, 4), (5, 2)):
+        avail = [int(x) for x in rng.choice(64, n, replace=False)]
+        want = oracle.besteffort(W, nl, avail, [], k)
+        assert ctx.besteffort(avail, [], k) == (gpa.OK, want[1])
+    avail17 = [int(x) for x in rng.choice(64, 17, replace=False)]
+    assert ctx.besteffort(avail17, [], 2)[0] == gpa.ERR_TOO_LARGE
+    assert ctx.besteffort(avail17, [], 18) == (gpa.OK, [])       # the guard len(available) < size answers first
+    reqs = syn.pack_requests([([int(x) for x in rng.choice(64, int(rng.integers(1, 13)), replace=False)], [], 1 + int(rng.integers(0, 3)))
+                              for _ in range(2000)])
+    assert_batch_equal(ctx.besteffort_batch(reqs), oracle_batch(oracle, W, nl, reqs, 0), reqs, "nt64")
+    with pytest.raises(gpa.GpaError):
+        ctx.set_topology(np.zeros((65, 65), dtype=np.int32), np.zeros((65, 65), dtype=np.uint8))
+    # sizes up to 255 travel in the packed record
+    big = syn.pack_requests([([1, 2, 3], [], 255), ([1, 2, 3], [], 3)])
+    got = ctx.besteffort_batch(big)
+    assert gpa.decode_result(got[0]) == (gpa.OK, []) and gpa.decode_result(got[1]) == (gpa.OK, [1, 2, 3])
+
+
+def test_concurrent_callers_share_one_context(ctx, oracle):
+    """grpc-go runs every RPC on its own goroutine (SURVEY.md §8b threading): calls on one context are serialised
+    inside the library and every caller gets its own answer"""
+    import threading
+    t = syn.topo_random(12, 21)
+    W, nl = install(ctx, t)
+    rng = np.random.default_rng(2)
+    cases = []
+    for _ in range(64):
+        n = int(rng.integers(4, 13))
+        avail = [int(x) for x in rng.permutation(12)[:n]]
+        k = int(rng.integers(2, n + 1))
+        cases.append((avail, k, oracle.besteffort(W, nl, avail, [], k)[1]))
+    batch = syn.random_request_batch(12, 5000, seed=77)
+    want_batch = oracle_batch(oracle, W, nl, batch, 0)
+    errors = []
+
+    def single(tid):
+        for i in range(tid, len(cases), 4):
+            avail, k, want = cases[i]
+            for _ in range(5):
+                if ctx.besteffort(avail, [], k) != (gpa.OK, want):
+                    errors.append(("single", avail, k))
+
+    def batched():
+        for _ in range(5):
+            if (ctx.besteffort_batch(batch)["dev"] != want_batch["dev"]).any():
+                errors.append(("batch",))
+
+    threads = [threading.Thread(target=single, args=(i,)) for i in range(4)] + [threading.Thread(target=batched) for _ in range(2)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errors, errors[:3]
+
+
+def test_two_contexts_are_independent(oracle):
+    a, b = gpa.Context(0), gpa.Context(0)
+    try:
+        ta, tb = syn.topo_dgx1v_like(), syn.topo_two_sockets(8)
+        a.set_topology_links(ta)
+        b.set_topology_links(tb)
+        Wa, nla = syn.links_to_weights(ta)
+        Wb, nlb = syn.links_to_weights(tb)
+        for k in range(2, 8):
+            assert a.besteffort(list(range(8)), [], k)[1] == oracle.besteffort(Wa, nla, list(range(8)), [], k)[1]
+            assert b.besteffort(list(range(8)), [], k)[1] == oracle.besteffort(Wb, nlb, list(range(8)), [], k)[1]
+    finally:
+        a.close()
+        b.close()
+
+
 def test_launch_counter_counts_kernels(ctx):
     install(ctx, syn.topo_two_sockets(8))
     before = ctx.launch_count

@@ -1,0 +1,67 @@
+// Native (no Python) latency of ONE allocation decision through the C ABI, next to the oracle: the honest small-request
+// comparison.  n = 8 devices (T3 topology), every size k = 1..8, no required devices.
+//   g++ -O2 -std=c++17 tools/latency.cpp -o /tmp/latency -I include -L k8s-gpu-sharing-plugin_b200 -lgpualloc -L oracle -loracle
+#include <algorithm>
+#include <chrono>
+#include <cstdint>
+#include <cstdio>
+#include <vector>
+
+#include "gpualloc.h"
+
+extern "C" int ref_besteffort_fast(int nt, const int32_t *W, const uint8_t *nlinks, const int32_t *avail, int n_avail, const int32_t *req,
+                                   int n_req, int size, int mode, int32_t *out, int *n_out, unsigned long long *visited);
+
+int main() {
+  const int n = 8;
+  // synthetic hybrid cube mesh (synthetic.topo_dgx1v_like): PCIe + NVLink weights
+  int32_t W[64];
+  uint8_t nl[64];
+  auto pcie = [](int i, int j) {
+    if ((i ^ j) == 1 && (i / 2) == (j / 2)) return 50;
+    return (i < 4) == (j < 4) ? 20 : 10;
+  };
+  const int two[8][2] = {{0, 3}, {0, 4}, {1, 2}, {1, 5}, {2, 3}, {4, 7}, {5, 6}, {6, 7}};
+  const int one[8][2] = {{0, 1}, {0, 2}, {1, 3}, {2, 6}, {3, 7}, {4, 5}, {4, 6}, {5, 7}};
+  for (int i = 0; i < n; i++)
+    for (int j = 0; j < n; j++) {
+      W[i * n + j] = i == j ? 0 : pcie(i, j);
+      nl[i * n + j] = i == j ? 0 : 1;
+    }
+  for (auto &p : two) {
+    W[p[0] * n + p[1]] += 200; W[p[1] * n + p[0]] += 200;
+    nl[p[0] * n + p[1]] = nl[p[1] * n + p[0]] = 2;
+  }
+  for (auto &p : one) {
+    W[p[0] * n + p[1]] += 100; W[p[1] * n + p[0]] += 100;
+    nl[p[0] * n + p[1]] = nl[p[1] * n + p[0]] = 2;
+  }
+  gpa_ctx *ctx = nullptr;
+  if (gpa_create(0, &ctx) != GPA_OK) return 2;
+  if (gpa_set_topology(ctx, n, W, nl) != GPA_OK) return 3;
+  int32_t avail[8] = {0, 1, 2, 3, 4, 5, 6, 7}, out[16], out2[16];
+  printf("{\"what\": \"one decision, n=8, native C ABI vs oracle (one host thread), microseconds\", \"cases\": [");
+  for (int k = 1; k <= 8; k++) {
+    std::vector<double> g, c;
+    int n_out = 0, n_out2 = 0;
+    for (int i = 0; i < 2200; i++) {
+      auto t0 = std::chrono::steady_clock::now();
+      gpa_besteffort(ctx, avail, n, nullptr, 0, k, GPA_MODE_GO_FAITHFUL, out, &n_out);
+      auto t1 = std::chrono::steady_clock::now();
+      ref_besteffort_fast(n, W, nl, avail, n, nullptr, 0, k, 0, out2, &n_out2, nullptr);
+      auto t2 = std::chrono::steady_clock::now();
+      if (i >= 200) {
+        g.push_back(std::chrono::duration<double, std::micro>(t1 - t0).count());
+        c.push_back(std::chrono::duration<double, std::micro>(t2 - t1).count());
+      }
+    }
+    bool same = n_out == n_out2 && std::equal(out, out + n_out, out2);
+    std::sort(g.begin(), g.end());
+    std::sort(c.begin(), c.end());
+    printf("%s{\"k\": %d, \"gpu_p50\": %.1f, \"gpu_p99\": %.1f, \"oracle_p50\": %.2f, \"oracle_p99\": %.2f, \"same\": %s}", k > 1 ? ", " : "", k,
+           g[g.size() / 2], g[(size_t)(g.size() * 0.99)], c[c.size() / 2], c[(size_t)(c.size() * 0.99)], same ? "true" : "false");
+  }
+  printf("]}\n");
+  gpa_destroy(ctx);
+  return 0;
+}
