@@ -106,7 +106,7 @@ __global__ void __launch_bounds__(kDpThreads) dp_layer_warp_kernel(const DpParam
 
 // top layer + reconstruction in one CTA: level by level, all threads value the first sets of the current remainder,
 // the block-wide max key names the first best one, and the remainder shrinks by it.  No serial replay.
-__global__ void __launch_bounds__(1024) dp_final_kernel(const DpParams p, const uint16_t *T, const uint16_t *Tok, SearchResult *g_res) {
+__device__ __forceinline__ void dp_final_stage(const DpParams &p, const uint16_t *T, const uint16_t *Tok, SearchResult *g_res) {
   __shared__ unsigned long long wkey[32];
   __shared__ unsigned long long level_key;
   __shared__ uint32_t sets[kMaxSets];
@@ -180,6 +180,10 @@ __global__ void __launch_bounds__(1024) dp_final_kernel(const DpParams p, const 
     }
     publish_result(g_res, r, p.seq);
   }
+}
+
+__global__ void __launch_bounds__(1024) dp_final_kernel(const DpParams p, const uint16_t *T, const uint16_t *Tok, SearchResult *g_res) {
+  dp_final_stage(p, T, Tok, g_res);
 }
 
 }  // namespace

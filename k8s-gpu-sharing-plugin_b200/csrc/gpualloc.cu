@@ -525,6 +525,10 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   // Enumeration visits every partition in one launch; the subset DP needs m launches but far less work.  The DP wins
   // once the tree is large (crossover measured around 10^5 partitions on B200).
+  // Enumeration visits every partition in one launch; the subset DP needs a launch per layer but far less work.  The DP
+  // wins once the tree is large (crossover measured around 10^5 partitions on B200, tools/search_sweep.py).  A one-CTA
+  // DP with its tables in shared memory was tried for <= 14 devices and measured 3-12x SLOWER than the layered launches
+  // (one SM cannot issue the ~10^5..10^6 stepper iterations fast enough), so it is not kept.
   const bool use_dp = (mode_flags & GPA_MODE_FORCE_DP) || (!(mode_flags & GPA_MODE_FORCE_ENUM) && parts > 100000ull);
   int grid = 0, block = 0;
   size_t smem = 0;
@@ -537,26 +541,28 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
     dp.rbit = rmask ? (rmask & (0u - rmask)) : 0u;
     memcpy(dp.wp, sp.wp, sizeof dp.wp);
     const uint32_t total = 1u << n_avail;
-    grid = (int)((total + kDpThreads - 1) / kDpThreads);
-    if (grid > ctx->sm_count * 8) grid = ctx->sm_count * 8;
-    block = kDpThreads;
     CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-    dp_scores_kernel<<<grid, kDpThreads, 0, ctx->stream>>>(dp, ctx->d_dp_any);
-    ctx->launches++;
-    for (int j = 2; j < dp.g.m; j++) {
-      // A thread per remainder walks its first sets one after the other; a warp per remainder spreads them over its lanes
-      // by literal rank.  Measured on B200 (tools/search_sweep.py): the warp form wins once a remainder has ~100 first sets.
-      if (binom_at(ctx->binom, j * dp.g.k - 1, dp.g.k - 1) >= 96u) {
-        int wgrid = (int)((total + kDpThreads / 32 - 1) / (kDpThreads / 32));
-        if (wgrid > ctx->sm_count * 8) wgrid = ctx->sm_count * 8;
-        dp_layer_warp_kernel<<<wgrid, kDpThreads, 0, ctx->stream>>>(dp, j, ctx->d_dp_any, ctx->d_dp_ok);
-      } else {
-        dp_layer_kernel<<<grid, kDpThreads, 0, ctx->stream>>>(dp, j, ctx->d_dp_any, ctx->d_dp_ok);
+    {
+      grid = (int)((total + kDpThreads - 1) / kDpThreads);
+      if (grid > ctx->sm_count * 8) grid = ctx->sm_count * 8;
+      block = kDpThreads;
+      dp_scores_kernel<<<grid, kDpThreads, 0, ctx->stream>>>(dp, ctx->d_dp_any);
+      ctx->launches++;
+      for (int j = 2; j < dp.g.m; j++) {
+        // A thread per remainder walks its first sets one after the other; a warp per remainder spreads them over its
+        // lanes by literal rank.  Measured: the warp form wins once a remainder has ~100 first sets.
+        if (binom_at(ctx->binom, j * dp.g.k - 1, dp.g.k - 1) >= 96u) {
+          int wgrid = (int)((total + kDpThreads / 32 - 1) / (kDpThreads / 32));
+          if (wgrid > ctx->sm_count * 8) wgrid = ctx->sm_count * 8;
+          dp_layer_warp_kernel<<<wgrid, kDpThreads, 0, ctx->stream>>>(dp, j, ctx->d_dp_any, ctx->d_dp_ok);
+        } else {
+          dp_layer_kernel<<<grid, kDpThreads, 0, ctx->stream>>>(dp, j, ctx->d_dp_any, ctx->d_dp_ok);
+        }
+        ctx->launches++;
       }
+      dp_final_kernel<<<1, 1024, 0, ctx->stream>>>(dp, ctx->d_dp_any, ctx->d_dp_ok, ctx->d_res);
       ctx->launches++;
     }
-    dp_final_kernel<<<1, 1024, 0, ctx->stream>>>(dp, ctx->d_dp_any, ctx->d_dp_ok, ctx->d_res);
-    ctx->launches++;
     sp.cut.d = dp.g.m >= 2 ? 1 : 0;
     sp.cut.n_items = dp.g.m >= 2 ? binom_at(ctx->binom, dp.g.m * dp.g.k - 1, dp.g.k - 1) : 1;
   } else {
