@@ -55,7 +55,8 @@ extern "C" {
 #define GPA_MODE_INTENDED 1    /* what the Go source means: bestPartition keeps the best candidate intact */
 #define GPA_MODE_FORCE_ENUM 2  /* gpa_besteffort(): visit every partition (one launch), whatever the size */
 #define GPA_MODE_FORCE_DP 4    /* gpa_besteffort(): subset dynamic programme (one launch per layer), whatever the size;
-                                  default: enumeration up to 10^5 candidate partitions, the DP beyond.  Same answers. */
+                                  default: the DP for 15-16 devices or more than 1.5 x 10^5 candidate partitions, else enumeration.
+                                  Same answers. */
 
 #define GPA_NIL (-1)     /* a nil *Device in a returned set (ref: SURVEY.md D5) */
 #define GPA_FOREIGN (-2) /* in `required`: a device pointer that is none of the `available` pointers — what the

@@ -529,7 +529,9 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
   // wins once the tree is large (crossover measured around 10^5 partitions on B200, tools/search_sweep.py).  A one-CTA
   // DP with its tables in shared memory was tried for <= 14 devices and measured 3-12x SLOWER than the layered launches
   // (one SM cannot issue the ~10^5..10^6 stepper iterations fast enough), so it is not kept.
-  const bool use_dp = (mode_flags & GPA_MODE_FORCE_DP) || (!(mode_flags & GPA_MODE_FORCE_ENUM) && parts > 100000ull);
+  // With 15-16 devices the enumeration kernel's per-CTA score table (64-128 KB) costs more than the whole DP, whatever k.
+  const bool use_dp = (mode_flags & GPA_MODE_FORCE_DP) ||
+                      (!(mode_flags & GPA_MODE_FORCE_ENUM) && (parts > 150000ull || n_avail >= 15));
   int grid = 0, block = 0;
   size_t smem = 0;
   if (use_dp) {
