@@ -175,8 +175,17 @@ constexpr int kTile = 4096;
 constexpr int kFastThreads = 256;
 constexpr int kShapeBins = 13 * 13 + 7;  // n*13 + k for n,k <= 12, padded to 176
 
+// Partition lists for small nodes.  Which partitions iterate() visits, and in which order, depends only on the
+// availability mask and the size, not on the weights; for a node of up to 8 GPUs all of them (6 289 for 8 GPUs) fit a
+// 25 KB table: one 32-bit word per partition, byte j = device mask of its j-th set (a padded set is the one with
+// fewer than k devices).  A lane then scores a partition with one table word and m score lookups instead of
+// stepping through combinations.  Built once per node size on the host with the same stepper (gpualloc.cu).
+constexpr int kPartTableMaxTopo = 8;
+
 struct FastTopo {
   const uint16_t *s_full;  // [1 << nt] scaled set scores over label masks
+  const uint32_t *part_words;  // partition words, grouped by (mask, size); nullptr: no table (more than 8 GPUs)
+  const uint32_t *part_index;  // [256 * 9]: offset | count << 16 of the group of (mask, size)
   int nt;
   uint8_t order[16];  // label -> NVML index
   uint8_t rank[GPA_MAX_TOPOLOGY];  // NVML index -> label, 0xFF = not on this node
@@ -206,6 +215,41 @@ __device__ __forceinline__ int fast_tracked_search(const Geom &g, const uint16_t
   best_set = 0;
   if (tr.best < 0) return 0;  // no accepted partition: bestPartition == nil (:72-74)
   return choose_from_partition(g, stab, tr.sets, intended, best_set);
+}
+
+// Table-driven search for nodes of up to 8 GPUs (m <= 4 sets): same result as fast_tracked_search.
+__device__ __forceinline__ int fast_table_search(const Geom &g, const FastTopo &ft, const uint16_t *S, bool intended,
+                                                 uint32_t &best_set) {
+  const uint32_t entry = __ldg(ft.part_index + g.real_mask * 9 + g.k);
+  const uint32_t *w = ft.part_words + (entry & 0xFFFFu);
+  const int count = (int)(entry >> 16);
+  const uint32_t rl = g.rmask;
+  int best = -1;
+  uint32_t best_word = 0;
+  for (int i = 0; i < count; i++) {
+    const uint32_t word = __ldg(w + i);
+    const uint32_t s0 = word & 0xFFu, s1 = (word >> 8) & 0xFFu, s2 = (word >> 16) & 0xFFu, s3 = word >> 24;
+    const int sc = (int)S[s0] + (int)S[s1] + (int)S[s2] + (int)S[s3];  // S[0] == 0 for the unused bytes
+    bool ok = true;
+    if (rl != 0) {
+      // :53 / :112-119 — some set holds every required device and is not the padded one
+      ok = ((s0 & rl) == rl && __popc(s0) == g.k) || ((s1 & rl) == rl && __popc(s1) == g.k) ||
+           ((s2 & rl) == rl && __popc(s2) == g.k) || ((s3 & rl) == rl && __popc(s3) == g.k);
+    }
+    if (ok && sc > best) {  // strict `>`: first best partition in visiting order (:57)
+      best = sc;
+      best_word = word;
+    }
+  }
+  best_set = 0;
+  if (best < 0) return 0;
+  uint32_t sets[kMaxSuffix];
+#pragma unroll
+  for (int j = 0; j < kMaxSuffix; j++) {
+    const uint32_t sj = (best_word >> (8 * j)) & 0xFFu;
+    sets[j] = sj | ((j < g.m && __popc(sj) < g.k) ? g.tok_bit : 0u);
+  }
+  return choose_from_partition(g, STab{S}, sets, intended, best_set);
 }
 
 __device__ __forceinline__ void res_set_byte(unsigned long long &r0, unsigned long long &r1, int i, int v) {
@@ -403,7 +447,10 @@ __global__ void __launch_bounds__(kFastThreads) besteffort_batch_fast_kernel(con
       unsigned long long r0 = 0x8080808080808080ull, r1 = 0x8080808080808080ull;
       uint32_t best_set = 0;
       int rc;
-      if (g.m <= kMaxSuffix) {
+      if (ft.part_words != nullptr) {
+        // small node: the partitions of (mask, size) come from the table
+        rc = fast_table_search(g, ft, S, intended != 0, best_set);
+      } else if (g.m <= kMaxSuffix) {
         // the whole tree in this lane, best partition tracked in registers
         rc = fast_tracked_search(g, S, intended != 0, best_set);
       } else {

@@ -88,6 +88,9 @@ struct gpa_ctx {
   uint16_t *d_dp_any = nullptr;  // subset DP tables of gpa_besteffort(): 2^16 and 2^15 uint16
   uint16_t *d_dp_ok = nullptr;
   uint16_t *d_sfull = nullptr;  // fast batch path: set scores over label masks, nullptr = path unavailable
+  uint32_t *d_part_words = nullptr;  // partition table of the fast batch path (nodes of up to 8 GPUs)
+  uint32_t *d_part_index = nullptr;
+  int part_table_nt = 0;             // node size the table was built for, 0 = none
   FastTopo fast{};
   // batch staging
   gpa_request *d_reqs = nullptr;
@@ -185,6 +188,51 @@ int launch_batch(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_ava
   return launch_general(ctx, d_reqs, count, max_avail, mode_flags, d_out, stream, 1);
 }
 
+// Every partition iterate() visits for (availability mask, size) on a node of nt <= 8 GPUs, in visiting order, one word
+// each (byte j = device mask of set j); see FastTopo.  Generated with the same stepper the kernels walk with.
+void gen_partitions(const Geom &g, uint32_t rem, int level, uint32_t word, std::vector<uint32_t> &out) {
+  if (level == g.m - 1) {  // base case :245-248 — the remainder is the last set
+    out.push_back(word | ((rem & g.real_mask) << (8 * level)));
+    return;
+  }
+  uint32_t anchor;
+  Stepper st = make_stepper(g, rem, anchor);
+  uint32_t chosen;
+  if (!st.first(chosen)) return;
+  do {
+    const uint32_t set = anchor | chosen;
+    gen_partitions(g, rem & ~set, level + 1, word | ((set & g.real_mask) << (8 * level)), out);
+  } while (st.next(chosen));
+}
+
+int ensure_partition_table(gpa_ctx *ctx, int nt) {
+  if (ctx->part_table_nt == nt) return GPA_OK;
+  if (ctx->d_part_words) cudaFree(ctx->d_part_words);
+  if (ctx->d_part_index) cudaFree(ctx->d_part_index);
+  ctx->d_part_words = ctx->d_part_index = nullptr;
+  ctx->part_table_nt = 0;
+  std::vector<uint32_t> words;
+  std::vector<uint32_t> index(256 * 9, 0);
+  for (uint32_t mask = 1; mask < (1u << nt); mask++) {
+    const int n = __builtin_popcount(mask);
+    for (int k = 2; k <= n; k++) {
+      const Geom g = make_geom_sparse(mask, k, 0, nt);
+      const size_t off = words.size();
+      gen_partitions(g, g.real_mask | g.tok_bit, 0, 0, words);
+      const size_t cnt = words.size() - off;
+      if (off > 0xFFFF || cnt > 0xFFFF) return GPA_ERR_TOO_LARGE;  // cannot happen for nt <= 8 (6 289 words)
+      index[mask * 9 + k] = (uint32_t)off | ((uint32_t)cnt << 16);
+    }
+  }
+  if (words.empty()) words.push_back(0);
+  CUDA_TRY(ctx, cudaMalloc(&ctx->d_part_words, words.size() * sizeof(uint32_t)));
+  CUDA_TRY(ctx, cudaMalloc(&ctx->d_part_index, index.size() * sizeof(uint32_t)));
+  CUDA_TRY(ctx, cudaMemcpy(ctx->d_part_words, words.data(), words.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+  CUDA_TRY(ctx, cudaMemcpy(ctx->d_part_index, index.data(), index.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+  ctx->part_table_nt = nt;
+  return GPA_OK;
+}
+
 // (Re)builds what the fast batch path needs from the installed topology and device order: the
 // label <-> NVML index maps and the score table over all label masks.  The path is available
 // for nodes of up to kFastMaxTopo devices whose link counts are symmetric.
@@ -221,6 +269,12 @@ int rebuild_fast(gpa_ctx *ctx) {
   CUDA_TRY(ctx, cudaMemcpy(d, sfull.data(), sfull.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
   f.s_full = d;
   ctx->d_sfull = d;
+  if (T.n <= kPartTableMaxTopo) {
+    int rc = ensure_partition_table(ctx, T.n);
+    if (rc != GPA_OK) return rc;
+    f.part_words = ctx->d_part_words;
+    f.part_index = ctx->d_part_index;
+  }
   ctx->fast = f;
   return GPA_OK;
 }
@@ -331,6 +385,8 @@ void gpa_destroy(gpa_ctx *ctx) {
   if (ctx->d_wq) cudaFree(ctx->d_wq);
   if (ctx->d_asym) cudaFree(ctx->d_asym);
   if (ctx->d_sfull) cudaFree(ctx->d_sfull);
+  if (ctx->d_part_words) cudaFree(ctx->d_part_words);
+  if (ctx->d_part_index) cudaFree(ctx->d_part_index);
   if (ctx->d_reqs) cudaFree(ctx->d_reqs);
   if (ctx->d_out) cudaFree(ctx->d_out);
   if (ctx->h_reqs) cudaFreeHost(ctx->h_reqs);
