@@ -226,8 +226,10 @@ __device__ __forceinline__ int fast_table_search(const Geom &g, const FastTopo &
   const uint32_t rl = g.rmask;
   int best = -1;
   uint32_t best_word = 0;
+  uint32_t next_word = count > 0 ? __ldg(w) : 0u;
   for (int i = 0; i < count; i++) {
-    const uint32_t word = __ldg(w + i);
+    const uint32_t word = next_word;
+    if (i + 1 < count) next_word = __ldg(w + i + 1);  // the next word is in flight while this one is scored
     const uint32_t s0 = word & 0xFFu, s1 = (word >> 8) & 0xFFu, s2 = (word >> 16) & 0xFFu, s3 = word >> 24;
     const int sc = (int)S[s0] + (int)S[s1] + (int)S[s2] + (int)S[s3];  // S[0] == 0 for the unused bytes
     bool ok = true;
@@ -271,7 +273,8 @@ constexpr size_t fast_smem_bytes(int nt) {
          + (size_t)kTile * sizeof(uint32_t)    // w_mr
          + (size_t)kTile * sizeof(uint16_t) * 2  // w_rank, sorted_idx
          + (size_t)kTile * 2                     // w_k, w_key
-         + (size_t)(kShapeBins + 1) * sizeof(uint32_t) * 2;  // hist, offs
+         + (size_t)(kShapeBins + 1) * sizeof(uint32_t) * 2  // hist, offs
+         + GPA_MAX_TOPOLOGY + 16;                            // rank, order
 }
 
 // kMasks = false: 32-byte gpa_request in, 16-byte gpa_result out.
@@ -293,9 +296,14 @@ __global__ void __launch_bounds__(kFastThreads) besteffort_batch_fast_kernel(con
   uint16_t *sorted_idx = w_rank + kTile;
   uint8_t *w_k = reinterpret_cast<uint8_t *>(sorted_idx + kTile);
   uint8_t *w_key = w_k + kTile;
+  // the relabelling tables are read with a different index in every lane: shared memory, not the constant bank
+  uint8_t *s_rank = w_key + kTile;
+  uint8_t *s_order = s_rank + GPA_MAX_TOPOLOGY;
 
   const int tid = threadIdx.x;
   for (uint32_t i = tid; i < (1u << ft.nt); i += kFastThreads) S[i] = ft.s_full[i];
+  if (tid < GPA_MAX_TOPOLOGY) s_rank[tid] = ft.rank[tid];
+  if (tid < 16) s_order[tid] = ft.order[tid];
 
   const long long n_tiles = ((long long)count + kTile - 1) / kTile;
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -350,23 +358,23 @@ __global__ void __launch_bounds__(kFastThreads) besteffort_batch_fast_kernel(con
             res_set_byte(r0, r1, 0, kResDefer);
           } else {
             // relabel: device -> rank in the node order; the list must be strictly ascending
-            const uint32_t w[4] = {lo.x, lo.y, lo.z, lo.w};
+            unsigned long long bytes = (unsigned long long)lo.x | ((unsigned long long)lo.y << 32);
+            const unsigned long long bytes_hi = (unsigned long long)lo.z | ((unsigned long long)lo.w << 32);
             uint32_t mask = 0, rlab = 0;
-            int prev = -1, first_dev = 0, first_req_dev = -1;
+            int prev = -1, first_req_dev = -1;
+            const int first_dev = (int)(lo.x & 0xFFu);
             bool defer = false;
-#pragma unroll
-            for (int p = 0; p < kFastMaxTopo; p++) {
-              if (p < n) {
-                const int d = (w[p >> 2] >> ((p & 3) * 8)) & 0xFF;
-                const int lab = d < GPA_MAX_TOPOLOGY ? ft.rank[d] : 0xFF;
-                defer = defer || lab == 0xFF || lab <= prev;
-                prev = lab;
-                mask |= 1u << (lab & 31);
-                if (rmask >> p & 1u) {
-                  rlab |= 1u << (lab & 31);
-                  if (first_req_dev < 0) first_req_dev = d;
-                }
-                if (p == 0) first_dev = d;
+#pragma unroll 1
+            for (int p = 0; p < n; p++) {
+              const int d = (int)(bytes & 0xFFu);
+              bytes = p == 7 ? bytes_hi : bytes >> 8;
+              const int lab = d < GPA_MAX_TOPOLOGY ? s_rank[d] : 0xFF;
+              defer = defer || lab == 0xFF || lab <= prev;
+              prev = lab;
+              mask |= 1u << (lab & 31);
+              if (rmask >> p & 1u) {
+                rlab |= 1u << (lab & 31);
+                if (first_req_dev < 0) first_req_dev = d;
               }
             }
             if (defer) {
@@ -481,7 +489,7 @@ __global__ void __launch_bounds__(kFastThreads) besteffort_batch_fast_kernel(con
           while (reals) {
             const int lab = __ffs(reals) - 1;
             reals &= reals - 1;
-            res_set_byte(r0, r1, o++, ft.order[lab]);
+            res_set_byte(r0, r1, o++, s_order[lab]);
           }
           if (best_set & g.tok_bit)
             for (int q = 0; q < g.P; q++) res_set_byte(r0, r1, o++, GPA_NIL);
