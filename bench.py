@@ -329,6 +329,19 @@ def run_ours(args):
         if tj.get("requests_per_launch") == len(reqs):
             traffic = float(tj["dram_bytes_read"] + tj["dram_bytes_write"])
             traffic_src = tj["source"]
+    issue = None
+    if traffic is not None and tj.get("warp_instructions"):
+        sm_count = torch.cuda.get_device_properties(local).multi_processor_count
+        issue_peak = sm_count * 4 * 1.965e9  # 4 schedulers per SM, one warp instruction per clock each, max SM clock
+        issue = {"warp_instructions_per_launch": tj["warp_instructions"], "achieved_per_s": tj["warp_instructions"] / avg_kernel_s,
+                 "peak_per_s": issue_peak, "frac": tj["warp_instructions"] / avg_kernel_s / issue_peak,
+                 "note": "the binding ceiling of this kernel: warp instructions (ncu, profiles/) over SM issue slots"}
+    lut = None
+    try:
+        g = gpa.probe_lut(local, 8, 5)  # 2^8 entries = the score table of an 8-GPU node
+        lut = {"ceiling_glookups_per_s": g, "what": "dependent uint16 gathers from a 256-entry shared-memory table + IADD (SURVEY.md 8d)"}
+    except Exception as e:  # noqa: BLE001
+        lut = {"error": str(e)}
     roofline = {
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
         "traffic_source": traffic_src,
@@ -336,6 +349,7 @@ def run_ours(args):
         "peak_source": peak_src + ", burst",
         "algorithmic_bytes_per_launch": alg_bytes,
         "io_bytes_per_launch": 48.0 * len(reqs), "io_gbs": 48.0 * len(reqs) / avg_kernel_s / 1e9,
+        "issue": issue, "smem_lut": lut,
         "note": "algorithmic bytes = 4 B x pair evaluations the reference performs (SURVEY.md 8d); the kernel reads "
                 "set scores from a shared-memory table instead, so this is not DRAM traffic; io_* is the real "
                 "request+result traffic and `traffic` the DRAM bytes ncu saw for one launch. The kernel is "

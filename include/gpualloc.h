@@ -338,6 +338,9 @@ int gpa_plugin_allocate(gpa_plugin *p, const char *const *ids, int n, char *json
  * mode 0: read-only (bytes counted = bytes read); mode 1: copy (bytes counted = read + written). GB/s. */
 int gpa_probe_hbm(int cuda_device, unsigned long long bytes, int reps, int mode, double *best_gbs, double *median_gbs,
                   char *errbuf, int errbuf_len);
+/* Ceiling of the allocation kernels' inner operation: dependent gathers from a 2^log2_entries-entry uint16 table in
+ * shared memory plus an integer add, in 10^9 lookups/s over the whole GPU ("measure this ceiling"). */
+int gpa_probe_lut(int cuda_device, int log2_entries, int reps, double *best_glookups_per_s, char *errbuf, int errbuf_len);
 /* n x n bandwidth matrix, GB/s one way: row = GPU that pulls, column = GPU whose HBM is read; the diagonal is the
  * local copy.  mode 0: peer-load kernel (LDG.128 on a peer-mapped pointer, over NVLink/NVSwitch when NVML says
  * so); mode 1: cudaMemcpyPeerAsync.  can_access (optional, n x n) = cudaDeviceCanAccessPeer. */

@@ -516,3 +516,16 @@ def probe_p2p(n_devices, nbytes=1 << 30, reps=10, mode=0):
     if rc != OK:
         raise GpaError(rc, err.value.decode())
     return m, acc
+
+
+def probe_lut(device=0, log2_entries=8, reps=5):
+    """shared-memory table gather + integer add ceiling, 10^9 lookups/s over the whole GPU"""
+    L = lib()
+    L.gpa_probe_lut.restype = C.c_int
+    L.gpa_probe_lut.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.c_char_p, C.c_int]
+    best = C.c_double(0)
+    err = C.create_string_buffer(256)
+    rc = L.gpa_probe_lut(device, log2_entries, reps, C.byref(best), err, len(err))
+    if rc != OK:
+        raise GpaError(rc, err.value.decode())
+    return best.value

@@ -79,6 +79,28 @@ __global__ void fill_kernel(uint4 *p, size_t n_vec, unsigned int seed) {
   }
 }
 
+// Ceiling of what the allocation kernels do at their core: a dependent-address gather from a shared-memory table
+// plus an integer add (SURVEY.md 8d asks for this figure).  Every lane chases its own index through a 2^log2-entry
+// uint16 table; 4 independent chains per lane hide the LDS latency.
+__global__ void __launch_bounds__(256) lut_kernel(int log2_entries, int iters, unsigned int *__restrict__ sink) {
+  extern __shared__ uint16_t lut[];
+  const uint32_t n = 1u << log2_entries;
+  for (uint32_t i = threadIdx.x; i < n; i += 256) lut[i] = (uint16_t)((i * 40503u + 7u) & 0xFFFFu);
+  __syncthreads();
+  const uint32_t m = n - 1u;
+  uint32_t a = threadIdx.x & m, b = (threadIdx.x * 7u + 1u) & m, c = (threadIdx.x * 13u + 2u) & m, d = (threadIdx.x * 29u + 3u) & m;
+  uint32_t acc = blockIdx.x;
+  for (int i = 0; i < iters; i++) {
+    const uint32_t va = lut[a], vb = lut[b], vc = lut[c], vd = lut[d];
+    acc += va + vb + vc + vd;
+    a = (a + va) & m;
+    b = (b + vb) & m;
+    c = (c + vc) & m;
+    d = (d + vd) & m;
+  }
+  if (acc == 0x9E3779B9u) atomicAdd(sink, 1u);
+}
+
 #define PROBE_TRY(expr)                                            \
   do {                                                             \
     cudaError_t e_ = (expr);                                       \
@@ -145,6 +167,47 @@ int gpa_probe_hbm(int cuda_device, unsigned long long bytes, int reps, int mode,
 fail:
   if (a) cudaFree(a);
   if (b) cudaFree(b);
+  if (sink) cudaFree(sink);
+  if (e0) cudaEventDestroy(e0);
+  if (e1) cudaEventDestroy(e1);
+  return GPA_ERR_CUDA;
+}
+
+// Shared-memory table gather + integer add rate, in 10^9 lookups per second over the whole GPU.
+int gpa_probe_lut(int cuda_device, int log2_entries, int reps, double *best_glookups_per_s, char *errbuf, int errbuf_len) {
+  if (log2_entries < 4 || log2_entries > 15 || reps < 1 || !best_glookups_per_s) return GPA_ERR_INVALID;
+  unsigned int *sink = nullptr;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  const int iters = 4096;
+  const size_t smem = ((size_t)1 << log2_entries) * sizeof(uint16_t);
+  int sms = 148, occ = 1, grid;
+  double best = 0;
+  PROBE_TRY(cudaSetDevice(cuda_device));
+  PROBE_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cuda_device));
+  if (smem > 48 * 1024) PROBE_TRY(cudaFuncSetAttribute(lut_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  PROBE_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, lut_kernel, 256, smem));
+  grid = sms * (occ < 1 ? 1 : occ);
+  PROBE_TRY(cudaMalloc(&sink, sizeof(unsigned int)));
+  PROBE_TRY(cudaMemset(sink, 0, sizeof(unsigned int)));
+  PROBE_TRY(cudaEventCreate(&e0));
+  PROBE_TRY(cudaEventCreate(&e1));
+  for (int r = 0; r < reps + 2; r++) {
+    PROBE_TRY(cudaEventRecord(e0));
+    lut_kernel<<<grid, 256, smem>>>(log2_entries, iters, sink);
+    PROBE_TRY(cudaEventRecord(e1));
+    PROBE_TRY(cudaEventSynchronize(e1));
+    float t = 0;
+    PROBE_TRY(cudaEventElapsedTime(&t, e0, e1));
+    const double g = (double)grid * 256.0 * iters * 4.0 / (t * 1e-3) / 1e9;
+    if (r >= 2 && g > best) best = g;
+  }
+  PROBE_TRY(cudaGetLastError());
+  *best_glookups_per_s = best;
+  cudaFree(sink);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  return GPA_OK;
+fail:
   if (sink) cudaFree(sink);
   if (e0) cudaEventDestroy(e0);
   if (e1) cudaEventDestroy(e1);

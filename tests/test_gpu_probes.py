@@ -34,3 +34,11 @@ def test_probe_argument_checks():
         gpa.probe_hbm(0, 1024, 1, mode=0)
     with pytest.raises(gpa.GpaError):
         gpa.probe_p2p(99, 1 << 30, 1, mode=0)
+
+
+def test_lut_probe_reports_a_plausible_ceiling():
+    g = gpa.probe_lut(0, 8, 2)
+    # 148 SMs x 32 shared-memory lanes x ~1.9 GHz = ~9 000 G lookups/s at best
+    assert 500 < g < 12000
+    with pytest.raises(gpa.GpaError):
+        gpa.probe_lut(0, 20, 1)
