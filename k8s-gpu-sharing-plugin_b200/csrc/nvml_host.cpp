@@ -18,6 +18,7 @@
 #include <dlfcn.h>
 #include <nvml.h>
 
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
@@ -317,7 +318,21 @@ int gpa_set_topology_from_nvml(gpa_ctx *ctx, gpa_nvml *nv, int flags) {
   std::vector<int32_t> links((size_t)n * n * 2);
   rc = gpa_nvml_read_topology(nv, flags, &n, links.data(), (int)links.size(), nullptr);
   if (rc != GPA_OK) return rc;
-  return gpa_set_topology_links(ctx, n, links.data());
+  rc = gpa_set_topology_links(ctx, n, links.data());
+  if (rc != GPA_OK) return rc;
+  // Requests list devices in byte-wise sorted-UUID order (stripReplicas, cmd/nvidia-device-plugin/replica.go:43):
+  // declare that order, so that batches of such requests take the fast kernel.
+  std::vector<std::string> uuids(n);
+  for (int i = 0; i < n; i++) {
+    char buf[96];
+    rc = gpa_nvml_device_uuid(nv, i, buf, sizeof buf);
+    if (rc != GPA_OK) return rc;
+    uuids[i] = buf;
+  }
+  std::vector<int32_t> order(n);
+  for (int i = 0; i < n; i++) order[i] = i;
+  std::sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return uuids[a] < uuids[b]; });
+  return gpa_set_device_order(ctx, order.data(), n);
 }
 
 // ---------------------------------------------------------------------------------------

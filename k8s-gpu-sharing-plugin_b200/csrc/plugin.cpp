@@ -147,6 +147,23 @@ int gpa_plugin_create(gpa_ctx *ctx, const gpa_plugin_config *cfg, const gpa_plug
       p->replicas_.push_back(std::move(r));
     }
   }
+  // The plugin always hands the allocator its devices in sorted-UUID order (stripReplicas, replica.go:43): tell the
+  // context, when its topology covers exactly these devices, so that batched decisions take the fast kernel.
+  if (ctx && p->has_policy) {
+    int nt = 0;
+    if (gpa_get_topology(ctx, &nt, nullptr, nullptr, 0) == GPA_OK && nt == (int)p->cached.size()) {
+      std::vector<int32_t> order;
+      std::vector<const Device *> by_id;
+      for (const Device &d : p->cached) by_id.push_back(&d);
+      std::sort(by_id.begin(), by_id.end(), [](const Device *a, const Device *b) { return a->id < b->id; });
+      bool ok = true;
+      for (const Device *d : by_id) {
+        ok = ok && d->nvml_index >= 0 && d->nvml_index < nt;
+        order.push_back(d->nvml_index);
+      }
+      if (ok) gpa_set_device_order(ctx, order.data(), nt);  // a non-permutation is refused there and changes nothing
+    }
+  }
   *out = p;
   return GPA_OK;
 }
