@@ -129,7 +129,8 @@ typedef struct gpa_search_stats {
   int score_unit;                /* gcd of the pair weights (scores are kept divided by it on the device) */
   int grid, block, smem_bytes;   /* launch shape of the search kernel, 0 if no kernel was needed */
   float kernel_ms;               /* device time of the search kernel(s) (CUDA events), 0 if none */
-  int algorithm;                 /* 0 answered by the guards, 1 enumeration, 2 subset dynamic programme */
+  int algorithm;                 /* 0 answered by the guards, 1 enumeration, 2 subset dynamic programme,
+                                    3 partition table (nodes of up to 8 GPUs, devices listed in node order) */
 } gpa_search_stats;
 int gpa_last_search_stats(gpa_ctx *ctx, gpa_search_stats *out);
 

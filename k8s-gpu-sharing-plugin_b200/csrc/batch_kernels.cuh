@@ -254,6 +254,70 @@ __device__ __forceinline__ int fast_table_search(const Geom &g, const FastTopo &
   return choose_from_partition(g, STab{S}, sets, intended, best_set);
 }
 
+// ONE small request on a small node, one warp: the partitions of (mask, size) come from the table, lanes stride over
+// them, a shuffle max of (score, ~index) keys names the first best one, lane 0 applies the epilogue and publishes the
+// answer into the mapped mailbox.  A few hundred instructions end to end: this is what a single kubelet request costs.
+struct GlobalScores {
+  const uint16_t *s;
+  __device__ __forceinline__ uint32_t operator()(uint32_t mask) const { return __ldg(s + mask); }
+};
+
+__global__ void __launch_bounds__(32) besteffort_small_kernel(const FastTopo ft, uint32_t mask, uint32_t rlab, int k, int intended,
+                                                              unsigned int seq, SearchResult *g_res) {
+  const int lane = threadIdx.x;
+  const Geom g = make_geom_sparse(mask, k, rlab, ft.nt);
+  const GlobalScores S{ft.s_full};
+  const uint32_t entry = __ldg(ft.part_index + mask * 9 + k);
+  const uint32_t *w = ft.part_words + (entry & 0xFFFFu);
+  const int count = (int)(entry >> 16);
+  unsigned long long best = 0;
+  for (int i = lane; i < count; i += 32) {
+    const uint32_t word = __ldg(w + i);
+    const uint32_t s0 = word & 0xFFu, s1 = (word >> 8) & 0xFFu, s2 = (word >> 16) & 0xFFu, s3 = word >> 24;
+    const int sc = (int)S(s0) + (int)S(s1) + (int)S(s2) + (int)S(s3);
+    bool ok = true;
+    if (rlab != 0)
+      ok = ((s0 & rlab) == rlab && __popc(s0) == k) || ((s1 & rlab) == rlab && __popc(s1) == k) ||
+           ((s2 & rlab) == rlab && __popc(s2) == k) || ((s3 & rlab) == rlab && __popc(s3) == k);
+    if (ok) {
+      const unsigned long long kk = pack_key(sc, (unsigned long long)i);
+      best = kk > best ? kk : best;
+    }
+  }
+  best = warp_max_u64(best);
+  if (lane == 0) {
+    SearchResult r;
+    r.key = best;
+    r.count = 0;
+    r.best_score = best ? key_score(best) : -1;
+#pragma unroll
+    for (int q = 0; q < 32; q++) r.pos[q] = 0;
+    if (best != 0) {
+      const uint32_t word = __ldg(w + (int)key_item(best));
+      uint32_t sets[kMaxSuffix];
+#pragma unroll
+      for (int j = 0; j < kMaxSuffix; j++) {
+        const uint32_t sj = (word >> (8 * j)) & 0xFFu;
+        sets[j] = sj | ((j < g.m && __popc(sj) < g.k) ? g.tok_bit : 0u);
+      }
+      uint32_t best_set = 0;
+      if (choose_from_partition(g, S, sets, intended != 0, best_set) > 0) {
+        int o = 0;
+        uint32_t reals = best_set & g.real_mask;
+        while (reals) {
+          const uint32_t b = reals & (0u - reals);
+          reals ^= b;
+          r.pos[o++] = (int8_t)__popc(mask & (b - 1u));  // position of that device in the caller's `available`
+        }
+        if (best_set & g.tok_bit)
+          for (int q = 0; q < g.P; q++) r.pos[o++] = -1;
+        r.count = o;
+      }
+    }
+    publish_result(g_res, r, seq);
+  }
+}
+
 __device__ __forceinline__ void res_set_byte(unsigned long long &r0, unsigned long long &r1, int i, int v) {
   unsigned long long b = (unsigned long long)(v & 0xFF);
   if (i < 8) r0 = (r0 & ~(0xFFull << (8 * i))) | (b << (8 * i));

@@ -579,6 +579,20 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
   if (parts > GPA_MAX_PARTITIONS) return GPA_ERR_TOO_LARGE;
 
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  // A small node with its partition table installed, devices listed in node order: one warp answers.
+  bool use_small = false;
+  uint32_t small_mask = 0, small_rlab = 0;
+  if (ctx->d_sfull && ctx->fast.part_words && !(mode_flags & (GPA_MODE_FORCE_ENUM | GPA_MODE_FORCE_DP))) {
+    use_small = true;
+    int prev = -1;
+    for (int p = 0; p < n_avail && use_small; p++) {
+      const int lab = ctx->fast.rank[avail[p]];
+      if (lab == 0xFF || lab <= prev) use_small = false;
+      prev = lab;
+      small_mask |= 1u << (lab & 31);
+      if (rmask >> p & 1u) small_rlab |= 1u << (lab & 31);
+    }
+  }
   // Enumeration visits every partition in one launch; the subset DP needs m launches but far less work.  The DP wins
   // once the tree is large (crossover measured around 10^5 partitions on B200).
   // Enumeration visits every partition in one launch; the subset DP needs a launch per layer but far less work.  The DP
@@ -590,7 +604,15 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
                       (!(mode_flags & GPA_MODE_FORCE_ENUM) && (parts > 150000ull || n_avail >= 15));
   int grid = 0, block = 0;
   size_t smem = 0;
-  if (use_dp) {
+  if (use_small) {
+    grid = 1;
+    block = 32;
+    // no event pair around this one: two cudaEventRecord calls cost as much as the kernel itself (kernel_ms stays 0)
+    besteffort_small_kernel<<<1, 32, 0, ctx->stream>>>(ctx->fast, small_mask, small_rlab, size, sp.intended, sp.seq, ctx->d_res);
+    ctx->launches++;
+    sp.cut.d = 0;
+    sp.cut.n_items = parts;
+  } else if (use_dp) {
     DpParams dp;
     memset(&dp, 0, sizeof dp);
     dp.g = sp.g;
@@ -645,7 +667,7 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
   ctx->launches++;
   }
   CUDA_TRY(ctx, cudaGetLastError());
-  CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  if (!use_small) CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
   // Wait for the answer where it lands: the kernel's last thread writes the record into the mapped mailbox and then
   // its launch number.  The stream is polled now and then so that a failed launch ends the wait.
   {
@@ -668,7 +690,7 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
     }
     std::atomic_thread_fence(std::memory_order_acquire);
   }
-  ctx->timing_pending = true;
+  ctx->timing_pending = !use_small;
 
   ctx->stats.partitions = parts;
   ctx->stats.items = sp.cut.n_items;
@@ -680,7 +702,7 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
   ctx->stats.block = block;
   ctx->stats.smem_bytes = (int)smem;
   ctx->stats.kernel_ms = 0;
-  ctx->stats.algorithm = use_dp ? 2 : 1;
+  ctx->stats.algorithm = use_small ? 3 : (use_dp ? 2 : 1);
 
   const SearchResult &r = *ctx->h_res;
   if (r.count < 0) {

@@ -70,6 +70,35 @@ def test_single_request_api_matches_batch_and_oracle_n8(ctx, oracle):
         assert ctx.besteffort(avail, req, k, gpa.MODE_FORCE_DP) == (gpa.OK, want[1]), ("dp", avail, req, k)
 
 
+@pytest.mark.parametrize("topo_i", [0, 3, 8])
+def test_single_request_on_a_small_node_takes_the_one_warp_kernel(ctx, oracle, topo_i):
+    """8-GPU node, devices listed in node order: the partition-table kernel answers (algorithm 3), both modes,
+    with and without required devices, every mask and size"""
+    name, t = syn.standard_topologies()[topo_i]
+    W, nl = install(ctx, t, ORDER8)
+    n = 0
+    for avail, req, k in syn.exhaustive_requests(ORDER8, seed=topo_i, n_pairs=2):
+        if k < 2 or len(req) > k or (n % 5 and len(avail) < 7):
+            n += 1
+            continue
+        for mode in (gpa.MODE_GO_FAITHFUL, gpa.MODE_INTENDED):
+            want = oracle.besteffort(W, nl, avail, req, k, mode)
+            assert ctx.besteffort(avail, req, k, mode) == (gpa.OK, want[1]), (name, avail, req, k, mode)
+            assert ctx.search_stats()["algorithm"] == 3
+        n += 1
+    # the same node, devices listed in another order: falls back to the general search, same answer
+    avail = [int(x) for x in reversed(ORDER8)]
+    assert ctx.besteffort(avail, [], 3) == (gpa.OK, oracle.besteffort(W, nl, avail, [], 3)[1])
+    assert ctx.search_stats()["algorithm"] == 1
+    # D5 on this path: a nil-padded winner
+    t5 = syn.topo_uniform(5)
+    for i, j in ((2, 3), (2, 4), (3, 4)):
+        t5[i, j, 0] = t5[j, i, 0] = 5
+    t5[0, 1] = t5[1, 0] = (5, syn.nvlink_type(1))
+    install(ctx, t5)
+    assert ctx.besteffort([0, 1, 2, 3, 4], [], 3) == (gpa.OK, [0, 1, gpa.NIL]) and ctx.search_stats()["algorithm"] == 3
+
+
 def test_guards_and_trivial_answers(ctx, oracle):
     W, nl = install(ctx, syn.topo_zero(8))
     av = [3, 1, 4, 0, 5]
