@@ -462,6 +462,39 @@ def run_ours(args):
     replica_mode["note"] = ("host C++ behind the C ABI on both sides of the comparison (no parallel work on this branch); timed from "
                             "Python through ctypes, string marshalling included")
 
+    # ---- replica-set search (north_star's "k-subsets of the available replica set"; no reference counterpart - the
+    #      reference answers replicas with prioritizeDevices above): one request at 32 / 128 / 256 virtual devices, half of
+    #      them free, 4 wanted; count-vector kernel (the default), literal kernel, literal oracle -------------------
+    replica_set = {"workload": "8 GPUs x 4 / 16 / 32 replicas, each free with p = 0.5 (seed 3), size 4, one must-include replica",
+                   "note": "decisions/s here = 1 / call time of ONE request through the C ABI from Python (launch + mailbox); "
+                           "the oracle walks C(free, 4) combinations, the literal kernel the same ones on the GPU, the "
+                           "count-vector kernel the <= 330 classes of interchangeable replicas"}
+    rng3 = np.random.default_rng(3)
+    for reps in (4, 16, 32):
+        free = [g for g in range(N_DEV) for _ in range(reps) if rng3.random() < 0.5]
+        must = [int(rng3.integers(len(free)))]
+        row = {"free": len(free)}
+        for name, flag in (("count_vectors", 0), ("literal", gpa.MODE_FORCE_ENUM)):
+            lat, kms, ans = [], [], None
+            for i in range(args.warmup + 200):
+                t0 = time.perf_counter()
+                ans = ctx.subset_besteffort(free, must, 4, flag)
+                dt = time.perf_counter() - t0
+                if i >= args.warmup:
+                    lat.append(dt)
+                    kms.append(ctx.search_stats()["kernel_ms"])
+            st = ctx.search_stats()
+            row[name] = {"candidates": st["partitions"], "grid": st["grid"], "call_us_p50": float(np.percentile(lat, 50)) * 1e6,
+                         "call_us_p99": float(np.percentile(lat, 99)) * 1e6, "decisions_per_s": 1.0 / float(np.median(lat)),
+                         "kernel_ms": float(np.median(kms)), "answer": ans[1]}
+            if name == "literal" and np.median(kms) > 0:
+                row[name]["candidates_per_s"] = st["partitions"] / (float(np.median(kms)) * 1e-3)
+        t0 = time.perf_counter()
+        want = orc.subset_besteffort(W, nl, free, must, 4)
+        row["oracle_call_us"] = (time.perf_counter() - t0) * 1e6
+        row["mismatches"] = int(row["count_vectors"]["answer"] != want[1]) + int(row["literal"]["answer"] != want[1])
+        replica_set["%d_virtual_devices" % (N_DEV * reps)] = row
+
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -473,6 +506,7 @@ def run_ours(args):
         "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": sampler.summary(),
         "parity": {"checked": int(len(idx)), "mismatches_device_arm": mismatches, "mismatches_e2e_arm": e2e_mismatch},
         "mask_format": mask_format, "search_n16": search16, "latency": latency, "replica_mode": replica_mode,
+        "replica_set": replica_set,
     }
     print(json.dumps(line))
     if use_dist:

@@ -118,7 +118,7 @@ int gpa_get_topology(gpa_ctx *ctx, int *n, int32_t *W, uint8_t *nlinks, int cap)
 int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_t *req, int n_req, int size,
                    int mode_flags, int32_t *out, int *n_out);
 
-/* Search statistics of the last gpa_besteffort() on this context (all optional). */
+/* Search statistics of the last gpa_besteffort() / gpa_subset_besteffort() on this context (all optional). */
 typedef struct gpa_search_stats {
   unsigned long long partitions; /* candidate partitions of the request (closed form) */
   unsigned long long items;      /* independent work items the search was cut into */
@@ -130,7 +130,8 @@ typedef struct gpa_search_stats {
   int grid, block, smem_bytes;   /* launch shape of the search kernel, 0 if no kernel was needed */
   float kernel_ms;               /* device time of the search kernel(s) (CUDA events), 0 if none */
   int algorithm;                 /* 0 answered by the guards, 1 enumeration, 2 subset dynamic programme,
-                                    3 partition table (nodes of up to 8 GPUs, devices listed in node order) */
+                                    3 partition table (nodes of up to 8 GPUs, devices listed in node order),
+                                    4 / 5 gpa_subset_besteffort(): count vectors / literal combinations */
 } gpa_search_stats;
 int gpa_last_search_stats(gpa_ctx *ctx, gpa_search_stats *out);
 
@@ -220,6 +221,37 @@ void gpa_free_host(void *p);
 int gpa_besteffort_batch_noalloc(int cuda_device, int n_topology, const int32_t *W, const uint8_t *nlinks,
                                  const gpa_request *reqs, int count, int max_avail, int mode_flags, gpa_result *out,
                                  void *stream, char *errbuf, int errbuf_len);
+
+/* ---- replica-set search (no reference counterpart as a whole) ------------------------- */
+
+/* Which `size` of the available SHARED replicas are best connected.  The reference never asks this: with
+ * replicas > 1 it answers GetPreferredAllocation with prioritizeDevices (cmd/nvidia-device-plugin/replica.go:96-198,
+ * here gpa_prioritize_devices) and ignores links.  This is BASELINE.json north_star's "all k-subsets of the available
+ * replica set scored against the link-weight matrix" (SURVEY.md 8d, config 3c), defined from reference pieces:
+ *   candidates  every `size`-combination of positions 0..n_avail-1 in lexicographic index order (iterateGPUSets,
+ *               gpuallocator/besteffort_policy.go:155-204) that holds all required positions (:102-110);
+ *   score       sum over pairs a < b of calculateGPUPairScore(gpu(a), gpu(b)) (:298-356, :360-368): the earlier
+ *               position's links, and 0 for two replicas of one GPU (same *Device, :303-305);
+ *   choice      the FIRST candidate with the highest score (strict `>`, :55 / :81);
+ *   guards      size <= 0, n_avail < size, n_req > size => *n_out = 0 (:35-45).
+ * phys[p] = NVML index of the GPU behind available virtual device p (caller order); req_pos[] = positions into
+ * phys[] (distinct); out_pos (>= size entries) receives the chosen positions ascending.
+ * Two kernels give the same answer: per-GPU COUNT vectors (replicas of one GPU are interchangeable for the score:
+ * C(K+G-1, G-1) classes instead of C(n_avail, size) subsets) when the positions of every GPU are contiguous - the
+ * plugin's sorted id order, replica.go:41 - and the literal walk otherwise or with GPA_MODE_FORCE_ENUM.
+ * Limits (else GPA_ERR_TOO_LARGE): GPA_SUBSET_MAX_AVAILABLE positions, GPA_SUBSET_MAX_GPUS distinct GPUs,
+ * size <= GPA_SUBSET_MAX_SIZE; counts: size - n_req <= 64 and <= GPA_SUBSET_MAX_CLASSES count vectors; literal:
+ * n_avail - n_req <= 256, size - n_req <= 8, <= GPA_SUBSET_MAX_CANDIDATES combinations.
+ * GPA_ERR_ASYMMETRIC where a candidate would make calculateGPUPairScore panic (checked over every pair of distinct GPUs
+ * behind the available replicas when size >= 2).  gpa_last_search_stats(): algorithm 4 = counts, 5 = literal;
+ * `partitions` = candidates of the form used. */
+#define GPA_SUBSET_MAX_AVAILABLE 4096
+#define GPA_SUBSET_MAX_GPUS 16
+#define GPA_SUBSET_MAX_SIZE 128
+#define GPA_SUBSET_MAX_CLASSES (1ull << 27)
+#define GPA_SUBSET_MAX_CANDIDATES (1ull << 33)
+int gpa_subset_besteffort(gpa_ctx *ctx, const int32_t *phys, int n_avail, const int32_t *req_pos, int n_req, int size,
+                          int mode_flags, int32_t *out_pos, int *n_out);
 
 /* ---- replica ids (host code: string work, no parallelism) ---------------------------- */
 

@@ -64,6 +64,7 @@ def lib():
     L.gpa_get_topology.argtypes = [vp, C.POINTER(C.c_int), i32p, u8p, C.c_int]
     L.gpa_besteffort.argtypes = [vp, i32p, C.c_int, i32p, C.c_int, C.c_int, C.c_int, i32p, C.POINTER(C.c_int)]
     L.gpa_last_search_stats.argtypes = [vp, C.POINTER(SearchStats)]
+    L.gpa_subset_besteffort.argtypes = [vp, i32p, C.c_int, i32p, C.c_int, C.c_int, C.c_int, i32p, C.POINTER(C.c_int)]
     L.gpa_besteffort_batch.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp]
     L.gpa_besteffort_batch_device.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp]
     L.gpa_besteffort_batch_masks.restype = C.c_int
@@ -202,6 +203,18 @@ class Context:
         rc = lib().gpa_besteffort(self._h, av.ctypes.data_as(C.POINTER(C.c_int32)), len(av),
                                   rq.ctypes.data_as(C.POINTER(C.c_int32)), len(rq), int(size), int(mode),
                                   out.ctypes.data_as(C.POINTER(C.c_int32)), C.byref(n_out))
+        return rc, [int(x) for x in out[:n_out.value]]
+
+    def subset_besteffort(self, phys, req_pos, size, mode=MODE_GO_FAITHFUL):
+        """Replica-set search (no reference counterpart, see gpualloc.h): phys[p] = NVML index of the GPU behind
+        available virtual device p, req_pos = positions that must be chosen -> (rc, [positions, ascending])"""
+        ph = np.ascontiguousarray(phys, dtype=np.int32)
+        rq = np.ascontiguousarray(req_pos, dtype=np.int32)
+        out = np.full(max(int(size), 1) + 8, -9, dtype=np.int32)
+        n_out = C.c_int(0)
+        rc = lib().gpa_subset_besteffort(self._h, ph.ctypes.data_as(C.POINTER(C.c_int32)), len(ph),
+                                         rq.ctypes.data_as(C.POINTER(C.c_int32)), len(rq), int(size), int(mode),
+                                         out.ctypes.data_as(C.POINTER(C.c_int32)), C.byref(n_out))
         return rc, [int(x) for x in out[:n_out.value]]
 
     def search_stats(self):

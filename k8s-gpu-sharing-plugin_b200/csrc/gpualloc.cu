@@ -15,6 +15,7 @@
 //   batch_kernels.cuh  besteffort_batch_fast_kernel  MANY requests in node order: tile-binned, one lane per request
 //                      besteffort_batch_kernel       MANY requests, any order: one warp per request (also the
 //                                                    "deferred" pass after the fast kernel)
+//   subset_kernels.cuh subset_counts/enum_kernel   ONE request over shared replicas (no reference counterpart)
 // The allocation-free entry point and its static device scratch are at the end of this file.
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -35,6 +36,8 @@
 #include "search_kernel.cuh"
 #include "dp_kernels.cuh"
 #include "batch_kernels.cuh"
+#include "subset_kernels.cuh"
+#include "subset_plan.h"
 
 namespace {
 
@@ -90,6 +93,9 @@ struct gpa_ctx {
   uint16_t *d_sfull = nullptr;  // fast batch path: set scores over label masks, nullptr = path unavailable
   uint32_t *d_part_words = nullptr;  // partition table of the fast batch path (nodes of up to 8 GPUs)
   uint32_t *d_part_index = nullptr;
+  uint64_t *d_sub_binom = nullptr;   // C(n, j) table of the literal replica-set kernel, built on first use
+  std::vector<uint64_t> sub_binom;
+  SubsetPlan sub_plan;               // plan of the last gpa_subset_besteffort() (kept for its buffers)
   int part_table_nt = 0;             // node size the table was built for, 0 = none
   FastTopo fast{};
   // batch staging
@@ -279,6 +285,36 @@ int rebuild_fast(gpa_ctx *ctx) {
   return GPA_OK;
 }
 
+// Waits for the answer of a single-request kernel where it lands: the kernel's last thread writes the record into the
+// mapped mailbox and then its launch number.  The stream is polled now and then so that a failed launch ends the wait.
+int wait_mailbox(gpa_ctx *ctx, unsigned int want) {
+  volatile unsigned int *seq = &ctx->h_res->seq;
+  unsigned spins = 0;
+  while (*seq != want) {
+    if ((++spins & 0x3FFu) == 0) {
+      cudaError_t q = cudaStreamQuery(ctx->stream);
+      if (q != cudaErrorNotReady) {
+        if (q != cudaSuccess) {
+          ctx->last_error = std::string("search kernel: ") + cudaGetErrorString(q);
+          return GPA_ERR_CUDA;
+        }
+        if (*seq != want) {  // stream drained without an answer: cannot happen unless the kernel was not run
+          ctx->last_error = "search kernel finished without publishing its answer";
+          return GPA_ERR_CUDA;
+        }
+      }
+    }
+  }
+  std::atomic_thread_fence(std::memory_order_acquire);
+  return GPA_OK;
+}
+
+unsigned int next_seq(gpa_ctx *ctx) {
+  unsigned int s = ++ctx->seq;
+  if (s == 0) s = ++ctx->seq;  // 0 is the mailbox's initial value
+  return s;
+}
+
 }  // namespace
 
 extern "C" {
@@ -387,6 +423,7 @@ void gpa_destroy(gpa_ctx *ctx) {
   if (ctx->d_sfull) cudaFree(ctx->d_sfull);
   if (ctx->d_part_words) cudaFree(ctx->d_part_words);
   if (ctx->d_part_index) cudaFree(ctx->d_part_index);
+  if (ctx->d_sub_binom) cudaFree(ctx->d_sub_binom);
   if (ctx->d_reqs) cudaFree(ctx->d_reqs);
   if (ctx->d_out) cudaFree(ctx->d_out);
   if (ctx->h_reqs) cudaFreeHost(ctx->h_reqs);
@@ -571,8 +608,7 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
   memset(&sp, 0, sizeof sp);
   sp.g = make_geom(n_avail, size, rmask);
   sp.intended = (mode_flags & GPA_MODE_INTENDED) ? 1 : 0;
-  sp.seq = ++ctx->seq;
-  if (sp.seq == 0) sp.seq = ++ctx->seq;  // 0 is the mailbox's initial value
+  sp.seq = next_seq(ctx);
   for (int a = 0; a < n_avail; a++)
     for (int b = a + 1; b < n_avail; b++) sp.wp[a * kMaxDevices + b] = T.wq[avail[a] * T.n + avail[b]];
   const uint64_t parts = partition_count(sp.g, ctx->binom);
@@ -668,27 +704,9 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
   }
   CUDA_TRY(ctx, cudaGetLastError());
   if (!use_small) CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
-  // Wait for the answer where it lands: the kernel's last thread writes the record into the mapped mailbox and then
-  // its launch number.  The stream is polled now and then so that a failed launch ends the wait.
   {
-    volatile unsigned int *seq = &ctx->h_res->seq;
-    unsigned spins = 0;
-    while (*seq != sp.seq) {
-      if ((++spins & 0x3FFu) == 0) {
-        cudaError_t q = cudaStreamQuery(ctx->stream);
-        if (q != cudaErrorNotReady) {
-          if (q != cudaSuccess) {
-            ctx->last_error = std::string("search kernel: ") + cudaGetErrorString(q);
-            return GPA_ERR_CUDA;
-          }
-          if (*seq != sp.seq) {  // stream drained without an answer: cannot happen unless the kernel was not run
-            ctx->last_error = "search kernel finished without publishing its answer";
-            return GPA_ERR_CUDA;
-          }
-        }
-      }
-    }
-    std::atomic_thread_fence(std::memory_order_acquire);
+    int rc = wait_mailbox(ctx, sp.seq);
+    if (rc != GPA_OK) return rc;
   }
   ctx->timing_pending = !use_small;
 
@@ -836,6 +854,8 @@ int gpa_besteffort_batch_masks(gpa_ctx *ctx, const gpa_mask_request *reqs, int c
   if (!pinned) memcpy(out, h_res, (size_t)count * sizeof(gpa_mask_result));
   return GPA_OK;
 }
+
+#include "subset_host.inc"
 
 /* pinned host memory for batch buffers (so gpa_besteffort_batch can skip its staging copy) */
 void *gpa_alloc_host(size_t bytes) {

@@ -1,0 +1,173 @@
+// Core of the replica-set search: which `size` of the available SHARED replicas are best connected.
+//
+// NO reference counterpart as a whole.  The reference answers a request over replicas with prioritizeDevices
+// (cmd/replica.go:96-198) and never looks at links between replicas; BASELINE.json's north_star and SURVEY.md 8d
+// ("config 3c") ask for the search the best-effort policy WOULD do if it were handed the replicas: every k-subset of the
+// available virtual devices, scored against the link-weight matrix.  It is assembled from reference pieces only:
+//   candidates   every `size`-combination of the available positions in lexicographic index order
+//                (iterateGPUSets, vendor/github.com/NVIDIA/go-gpuallocator/gpuallocator/besteffort_policy.go:155-204)
+//                that contains all `required` positions (gpuSetContainsAll, :102-110)
+//   score        sum over pairs a < b of calculateGPUPairScore(dev(a), dev(b)) (:298-356, :360-368): the links of the
+//                EARLIER position's GPU towards the later one, and 0 for two replicas of one GPU (same *Device, :303-305)
+//   choice       the first candidate with the highest score (strict `>`, as at :55 and :81)
+//
+// Two equivalent forms, both here for host and device:
+//   literal      walk the combinations (SubsetEnum): C(R, K) candidates
+//   counts       replicas of one GPU are interchangeable for the score, so a candidate class is a vector of per-GPU
+//                COUNTS c_g with r_g <= c_g <= r_g + f_g (required / free replicas of GPU g) and sum = size; its score is
+//                sum_{g<h} c_g c_h w[g][h], and the lexicographically first member of a class takes the first free
+//                replicas of every GPU.  When the positions of every GPU are contiguous (the plugin's sorted id order,
+//                cmd/replica.go:41) a class with a LARGER count in the first differing group starts earlier, so
+//                enumerating count vectors in descending lexicographic order with first-wins gives the literal answer.
+//                C(K+G-1, G-1) classes at most instead of C(R, K): 330 instead of 174 792 640 for 4 of 256 replicas
+//                on 8 GPUs.
+#pragma once
+#include <stdint.h>
+
+#include "gpa_enum.cuh"
+
+namespace gpa {
+
+constexpr int kSubGroups = 16;          // GPUs behind one request
+constexpr int kSubMaxExtra = 64;        // replicas to choose beyond the required ones (counts form)
+constexpr int kSubCntStride = kSubMaxExtra + 1;
+constexpr uint64_t kSubSat = 1ull << 62;  // class counts saturate here; ranks stay far below
+constexpr int kSubEnumMaxFree = 256;    // literal form: free positions
+constexpr int kSubEnumMaxExtra = 8;     // literal form: replicas to choose beyond the required ones
+
+// --------------------------------------------------------------------------------------------------------------------
+// counts form
+
+struct SubsetCounts {
+  int32_t G;                           // groups (GPUs) in order of their first position
+  int32_t K;                           // replicas to choose beyond the required ones, 1..kSubMaxExtra
+  uint8_t f[kSubGroups];               // free non-required replicas of the group, clamped to K
+  uint8_t r[kSubGroups];               // required replicas of the group
+  uint16_t w[kSubGroups * kSubGroups];  // scaled pair weight, [g * 16 + h] for group ranks g < h
+};
+
+GPA_HD uint64_t sub_sat_add(uint64_t a, uint64_t b) {
+  const uint64_t s = a + b;
+  return s > kSubSat ? kSubSat : s;
+}
+
+// One level of the class-count table: cnt[g][s] = number of ways groups g.. can take s more replicas.
+// Level G is {1, 0, 0, ...}; callers fill levels G-1 .. 0, entry s of a level depends on the level below only.
+GPA_HD uint64_t sub_cnt_entry(const SubsetCounts &q, const uint64_t *cnt, int g, int s) {
+  uint64_t sum = 0;
+  const int hi = q.f[g] < s ? q.f[g] : s;
+  for (int x = 0; x <= hi; x++) sum = sub_sat_add(sum, cnt[(g + 1) * kSubCntStride + s - x]);
+  return sum;
+}
+
+// Class `rank` in descending lexicographic order of the count vectors -> its score; x_out (optional) gets the counts
+// beyond the required ones.  rank < cnt[0][K].
+GPA_HD uint32_t sub_unrank_score(const SubsetCounts &q, const uint64_t *cnt, const uint16_t *w, uint64_t rank, uint8_t *x_out) {
+  uint32_t c[kSubGroups];
+  uint32_t score = 0;
+  int left = q.K;
+#pragma unroll
+  for (int g = 0; g < kSubGroups; g++) {
+    if (g < q.G) {
+      int x = q.f[g] < left ? q.f[g] : left;
+      while (x > 0) {
+        const uint64_t below = cnt[(g + 1) * kSubCntStride + left - x];
+        if (rank < below) break;
+        rank -= below;
+        x--;
+      }
+      left -= x;
+      if (x_out) x_out[g] = (uint8_t)x;
+      c[g] = (uint32_t)q.r[g] + (uint32_t)x;
+      uint32_t lin = 0;
+#pragma unroll
+      for (int i = 0; i < kSubGroups; i++)
+        if (i < g) lin += c[i] * w[i * kSubGroups + g];
+      score += c[g] * lin;
+    }
+  }
+  return score;
+}
+
+// --------------------------------------------------------------------------------------------------------------------
+// literal form: K-combinations of the R free positions, required positions folded into `wreq` and `base`
+
+struct SubsetEnum {
+  int32_t R;                               // free (non-required) positions, in position order
+  int32_t K;                               // how many of them to choose, 1..kSubEnumMaxExtra
+  uint32_t base;                           // score of the required positions among themselves
+  uint8_t grp[kSubEnumMaxFree];            // group of free position i
+  uint32_t wreq[kSubEnumMaxFree];          // score of free position i against all required positions
+  uint16_t w[kSubGroups * kSubGroups];     // scaled pair weight [g * 16 + h]: earlier position in g, later in h; 0 for g == h
+};
+
+// C(n, j) for n <= 256, j <= 8, saturated: row-major [n * 9 + j]
+constexpr int kSubBinomRows = kSubEnumMaxFree + 1;
+constexpr int kSubBinomCols = kSubEnumMaxExtra + 1;
+
+inline void sub_fill_binom(uint64_t *b) {
+  for (int n = 0; n < kSubBinomRows; n++)
+    for (int j = 0; j < kSubBinomCols; j++) {
+      uint64_t v;
+      if (j == 0)
+        v = 1;
+      else if (n == 0)
+        v = 0;
+      else
+        v = sub_sat_add(b[(n - 1) * kSubBinomCols + j - 1], b[(n - 1) * kSubBinomCols + j]);
+      b[n * kSubBinomCols + j] = v;
+    }
+}
+
+// Combination number `rank` (lexicographic) of K out of R -> e[0..K)
+template <int K>
+GPA_HD void sub_comb_unrank(const uint64_t *binom, int R, uint64_t rank, int (&e)[K]) {
+  int v = 0;
+#pragma unroll
+  for (int i = 0; i < K; i++) {
+    for (;; v++) {
+      const uint64_t with_v = binom[(R - 1 - v) * kSubBinomCols + (K - 1 - i)];  // combinations whose i-th pick is v
+      if (rank < with_v) break;
+      rank -= with_v;
+    }
+    e[i] = v++;
+  }
+}
+
+// prefix scores: ps[t + 1] = score of (required + e[0..t]); levels < from are kept
+template <int K>
+GPA_HD void sub_comb_rescore(const uint8_t *grp, const uint32_t *wreq, const uint16_t *w, const int (&e)[K],
+                             int (&ge)[K], uint32_t (&ps)[K + 1], int from) {
+#pragma unroll
+  for (int t = 0; t < K; t++) {
+    if (t >= from) {
+      const int g = grp[e[t]];
+      uint32_t s = ps[t] + wreq[e[t]];
+#pragma unroll
+      for (int u = 0; u < K; u++)
+        if (u < t) s += w[ge[u] + g];
+      ge[t] = g * kSubGroups;
+      ps[t + 1] = s;
+    }
+  }
+}
+
+// next combination in lexicographic order; returns the lowest level that changed, or -1 after the last one
+template <int K>
+GPA_HD int sub_comb_next(int R, int (&e)[K]) {
+  int j = K - 1;
+#pragma unroll
+  for (int t = K - 1; t >= 0; t--)
+    if (j == t && e[t] == R - K + t) j = t - 1;
+  if (j < 0) return -1;
+#pragma unroll
+  for (int t = 0; t < K; t++) {
+    if (t == j)
+      e[t]++;
+    else if (t > j && t > 0)
+      e[t] = e[t > 0 ? t - 1 : 0] + 1;
+  }
+  return j;
+}
+
+}  // namespace gpa

@@ -278,3 +278,18 @@ def mask_results_to_records(res, order):
     r = np.zeros(len(res), dtype=RES_DTYPE)
     r["dev"] = out
     return r
+
+
+def random_subset_request(rng, n_gpus, replicas, p_free=0.5, grouped=True, max_size=8, p_required=0.3, max_required=2):
+    """One replica-set request (gpa_subset_besteffort): (phys, req_pos, size).  Each of n_gpus * replicas virtual
+    devices is free with probability p_free; positions follow the GPU order (the plugin's sorted ids, SURVEY.md 8d
+    config 3) or, with grouped=False, a shuffle of it."""
+    phys = [g for g in range(n_gpus) for _ in range(replicas) if rng.random() < p_free]
+    if not grouped:
+        rng.shuffle(phys)
+    size = int(rng.integers(1, max_size + 1))
+    req = []
+    if phys and rng.random() < p_required:
+        n_req = int(rng.integers(1, max_required + 1))
+        req = [int(x) for x in rng.choice(len(phys), size=min(n_req, len(phys)), replace=False)]
+    return [int(x) for x in phys], req, size

@@ -23,7 +23,7 @@ ERR_KIND_NAMES = {0: "none", 1: "non_unique", 2: "no_devices_left", 3: "must_mis
 
 
 def build(force=False):
-    srcs = [os.path.join(HERE, f) for f in ("ref_besteffort.c", "ref_replica.c", "ref_batch.c")]
+    srcs = [os.path.join(HERE, f) for f in ("ref_besteffort.c", "ref_replica.c", "ref_batch.c", "ref_subset.c")]
     if force or not os.path.exists(LIB) or any(os.path.getmtime(s) > os.path.getmtime(LIB) for s in srcs):
         subprocess.check_call(["make", "-C", HERE, "-s", "-B", "liboracle.so"])
     return LIB
@@ -60,6 +60,9 @@ def lib():
         L.ref_besteffort_batch.argtypes = [C.c_int, i32p, u8p, C.c_void_p, C.c_longlong, C.c_int, C.c_void_p, C.c_int]
         L.ref_get_additional_xids.restype = C.c_int
         L.ref_get_additional_xids.argtypes = [C.c_char_p, C.POINTER(C.c_uint64), C.c_int]
+        L.ref_subset_besteffort.restype = C.c_int
+        L.ref_subset_besteffort.argtypes = [C.c_int, i32p, u8p, i32p, C.c_int, i32p, C.c_int, C.c_int, i32p,
+                                            C.POINTER(C.c_int), C.POINTER(C.c_longlong), C.POINTER(C.c_ulonglong)]
         _lib = L
     return _lib
 
@@ -160,3 +163,20 @@ def besteffort_batch(W, nlinks, reqs, mode=GO_FAITHFUL, threads=1, out=None):
                                          nl.ctypes.data_as(C.POINTER(C.c_uint8)), reqs.ctypes.data, len(reqs), int(mode),
                                          out.ctypes.data, int(threads))
     return out, int(visited)
+
+
+def subset_besteffort(W, nlinks, phys, req_pos, size, want_stats=False):
+    """Replica-set search, literal form (oracle/ref_subset.c) -> (rc, [positions]) [, best score, candidates seen]"""
+    W = np.ascontiguousarray(W, dtype=np.int32)
+    nl = np.ascontiguousarray(nlinks, dtype=np.uint8)
+    ph, php = _i32(phys)
+    rq, rqp = _i32(req_pos)
+    out = np.full(max(int(size), 1), -9, dtype=np.int32)
+    n_out = C.c_int(0)
+    score = C.c_longlong(0)
+    seen = C.c_ulonglong(0)
+    rc = lib().ref_subset_besteffort(W.shape[0], W.ctypes.data_as(C.POINTER(C.c_int32)), nl.ctypes.data_as(C.POINTER(C.c_uint8)),
+                                     php, len(ph), rqp, len(rq), int(size), out.ctypes.data_as(C.POINTER(C.c_int32)),
+                                     C.byref(n_out), C.byref(score), C.byref(seen))
+    res = (rc, [int(x) for x in out[:n_out.value]])
+    return res + (score.value, seen.value) if want_stats else res

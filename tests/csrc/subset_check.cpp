@@ -1,0 +1,85 @@
+// CPU harness for the replica-set search: the product's own plan / rank / score / decode code
+// (csrc/subset_plan.h, csrc/subset_core.cuh) with a sequential loop standing where the CUDA kernels are.
+// Test infrastructure; built by tests/test_subset_core.py with g++.
+#include <stdint.h>
+
+#include <vector>
+
+#include "../../k8s-gpu-sharing-plugin_b200/csrc/subset_plan.h"
+
+namespace {
+
+template <int K>
+uint64_t walk_literal(const gpa::SubsetPlan &pl, const uint64_t *binom, unsigned chunk) {
+  using namespace gpa;
+  uint64_t best = 0;
+  // the kernel's loop: every thread visit unranks the start of its run and steps through it
+  for (uint64_t start = 0; start < pl.total; start += chunk) {
+    int e[K], ge[K];
+    uint32_t ps[K + 1];
+    sub_comb_unrank<K>(binom, pl.qe.R, start, e);
+    ps[0] = pl.qe.base;
+    sub_comb_rescore<K>(pl.qe.grp, pl.qe.wreq, pl.qe.w, e, ge, ps, 0);
+    const uint64_t end = start + chunk < pl.total ? start + chunk : pl.total;
+    for (uint64_t rank = start;;) {
+      const uint64_t key = pack_key((int)ps[K], rank);
+      best = key > best ? key : best;
+      if (++rank >= end) break;
+      const int j = sub_comb_next<K>(pl.qe.R, e);
+      if (j < 0) return 0;  // ran off the end before `total`: the rank arithmetic is wrong
+      sub_comb_rescore<K>(pl.qe.grp, pl.qe.wreq, pl.qe.w, e, ge, ps, j);
+    }
+  }
+  return best;
+}
+
+}  // namespace
+
+// W: n_topo x n_topo weights (already scaled), asym: n_topo x n_topo flags.  -> GPA_* code; *form = 0 none, 4 counts, 5 literal
+extern "C" int subset_check(int n_topo, const uint16_t *wq, const uint8_t *asym, const int32_t *phys, int n_avail,
+                            const int32_t *req_pos, int n_req, int size, int mode_flags, unsigned chunk, int32_t *out_pos, int *n_out,
+                            int *form, unsigned long long *total, int *best_score) {
+  using namespace gpa;
+  static std::vector<uint64_t> binom;
+  if (binom.empty()) {
+    binom.resize((size_t)kSubBinomRows * kSubBinomCols);
+    sub_fill_binom(binom.data());
+  }
+  *n_out = 0;
+  *form = 0;
+  *total = 0;
+  *best_score = -1;
+  SubsetPlan pl;
+  int rc = subset_plan(n_topo, wq, asym, binom.data(), phys, n_avail, req_pos, n_req, size, mode_flags, pl);
+  if (rc != GPA_OK) return rc;
+  if (!pl.done) {
+    uint64_t best = 0;
+    if (!pl.literal) {
+      for (uint64_t rank = 0; rank < pl.total; rank++) {
+        const uint32_t s = sub_unrank_score(pl.qc, pl.cnt.data(), pl.qc.w, rank, nullptr);
+        const uint64_t key = pack_key((int)s, rank);
+        best = key > best ? key : best;
+      }
+    } else {
+      if (chunk < 1) chunk = 1;
+      switch (pl.K) {
+        case 1: best = walk_literal<1>(pl, binom.data(), chunk); break;
+        case 2: best = walk_literal<2>(pl, binom.data(), chunk); break;
+        case 3: best = walk_literal<3>(pl, binom.data(), chunk); break;
+        case 4: best = walk_literal<4>(pl, binom.data(), chunk); break;
+        case 5: best = walk_literal<5>(pl, binom.data(), chunk); break;
+        case 6: best = walk_literal<6>(pl, binom.data(), chunk); break;
+        case 7: best = walk_literal<7>(pl, binom.data(), chunk); break;
+        case 8: best = walk_literal<8>(pl, binom.data(), chunk); break;
+        default: return -100;
+      }
+    }
+    if (!best || !subset_decode(pl, binom.data(), best)) return -101;
+    *form = pl.literal ? 5 : 4;
+    *total = pl.total;
+    *best_score = key_score(best);
+  }
+  for (size_t i = 0; i < pl.answer.size(); i++) out_pos[i] = pl.answer[i];
+  *n_out = (int)pl.answer.size();
+  return GPA_OK;
+}
