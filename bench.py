@@ -495,6 +495,61 @@ def run_ours(args):
         row["mismatches"] = int(row["count_vectors"]["answer"] != want[1]) + int(row["literal"]["answer"] != want[1])
         replica_set["%d_virtual_devices" % (N_DEV * reps)] = row
 
+    # ---- the same search for MANY requests in count form (gpa_subset_batch): the metric's "decisions/s at 32 / 128 / 256
+    #      virtual devices" with GPU work behind it; only rank 0's numbers are reported (replicas only, no collective) ----
+    from math import comb
+    SUB_BATCH = 1 << 20
+    sub_steps = max(3, min(args.steps, 10))
+    batch_rows = {"workload": "2^20 requests per step, 8 GPUs x replicas, every replica free with p drawn from {0.1, 0.5, 0.9} per "
+                              "request, size from {1, 2, 4, 8}, 10 % with one must-include replica; 48-byte count records in, "
+                              "24-byte records out"}
+    for reps in (4, 16, 32):
+        sreqs = syn.random_subset_batch(N_DEV, reps, SUB_BATCH, seed=300 + reps)
+        d_sin = torch.from_numpy(sreqs.view(np.uint8).reshape(-1, 48)).cuda()
+        d_sout = torch.empty((len(sreqs), 24), dtype=torch.uint8, device="cuda")
+        for _ in range(args.warmup):
+            ctx.subset_batch_device(d_sin.data_ptr(), len(sreqs), d_sout.data_ptr(), stream=stream.cuda_stream)
+        barrier()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record(stream)
+        for _ in range(sub_steps):
+            ctx.subset_batch_device(d_sin.data_ptr(), len(sreqs), d_sout.data_ptr(), stream=stream.cuda_stream)
+        s1.record(stream)
+        barrier()
+        sub_ms = s0.elapsed_time(s1) / sub_steps
+        got_s = d_sout.cpu().numpy().view(syn.SUBSET_RES_DTYPE).reshape(-1)
+        spin_in = gpa.PinnedBuffer(len(sreqs), syn.SUBSET_REQ_DTYPE)
+        spin_out = gpa.PinnedBuffer(len(sreqs), syn.SUBSET_RES_DTYPE)
+        spin_in.array[:] = sreqs
+        for _ in range(2):
+            ctx.subset_batch(spin_in.array, out=spin_out.array)
+        t0 = time.perf_counter()
+        for _ in range(sub_steps):
+            ctx.subset_batch(spin_in.array, out=spin_out.array)
+        sub_e2e_s = (time.perf_counter() - t0) / sub_steps
+        e2e_same = bool((spin_out.array.view(np.uint8) == got_s.view(np.uint8)).all())
+        # the literal oracle on a bounded sample: only records it can finish (C(available, size) <= 2e5), ~2 s of CPU
+        n_av = sreqs["free"].sum(axis=1).astype(np.int64) + sreqs["must"].sum(axis=1)
+        small = [i for i in range(4000) if comb(int(n_av[i]), max(int(sreqs["size"][i]), 0)) <= 200000][:600]
+        t0 = time.perf_counter()
+        bad = 0
+        for i in small:
+            phys_lab, rq = syn.subset_record_to_positions(sreqs[i])
+            rc, pos = orc.subset_besteffort(W, nl, [order[g] for g in phys_lab], rq, int(sreqs["size"][i]))
+            want_take = syn.positions_to_take(phys_lab, set(rq), pos) if pos else [0] * 16
+            bad += int(got_s["take"][i].tolist() != want_take or int(got_s["n_out"][i]) != len(pos))
+        orc_s = time.perf_counter() - t0
+        batch_rows["%d_virtual_devices" % (N_DEV * reps)] = {
+            "value": len(sreqs) / (sub_ms * 1e-3), "unit": UNIT, "ms_per_step": sub_ms,
+            "e2e": {"value": len(sreqs) / sub_e2e_s, "unit": UNIT, "h2d_bytes_per_step": 48 * len(sreqs),
+                    "d2h_bytes_per_step": 24 * len(sreqs), "same_bytes_as_device_arm": e2e_same},
+            "oracle_sample": {"requests": len(small), "decisions_per_s": len(small) / orc_s, "mismatches": bad,
+                              "what": "records of the first 4000 with C(available, size) <= 2e5, oracle/ref_subset.c, one thread "
+                                      "(python call overhead included)"},
+        }
+        del d_sin, d_sout
+    replica_set["batch"] = batch_rows
+
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

@@ -253,6 +253,34 @@ int gpa_besteffort_batch_noalloc(int cuda_device, int n_topology, const int32_t 
 int gpa_subset_besteffort(gpa_ctx *ctx, const int32_t *phys, int n_avail, const int32_t *req_pos, int n_req, int size,
                           int mode_flags, int32_t *out_pos, int *n_out);
 
+/* Many replica-set decisions per call, in COUNT form: what matters about a request on a node is how many replicas
+ * of each GPU are free and how many must be included, because replicas of one GPU are interchangeable for the score.
+ * Index g of the arrays is the LABEL of a GPU in the node order given to gpa_set_device_order() (the plugin's sorted
+ * id order), i.e. the request is gpa_subset_besteffort() over positions grouped by label.  The answer is how many
+ * FURTHER replicas to take from each GPU; the first candidate of the winning class takes the first `take[g]` free
+ * replicas of GPU g in id order next to the must-include ones.  One warp per request, one launch per call.
+ * Per-record status: GPA_OK, GPA_ERR_INVALID (replicas of a GPU the node does not have), GPA_ERR_ASYMMETRIC,
+ * GPA_ERR_TOO_LARGE (size > GPA_SUBSET_MAX_SIZE, size - sum(must) > GPA_SUBSET_BATCH_MAX_EXTRA, or more than
+ * GPA_SUBSET_BATCH_MAX_CLASSES count vectors by the estimate C(K + g - 1, g - 1), K = size - sum(must), g = GPUs with free
+ * replicas: use the single call for those).
+ * Nodes of up to 16 GPUs (else the call returns GPA_ERR_TOO_LARGE).  No reference counterpart (see above). */
+#define GPA_SUBSET_BATCH_MAX_EXTRA 15
+#define GPA_SUBSET_BATCH_MAX_CLASSES (1u << 20)
+typedef struct gpa_subset_request {
+  uint8_t free_replicas[16]; /* free replicas of GPU label g that are NOT in must-include */
+  uint8_t must_replicas[16]; /* must-include replicas of GPU label g */
+  int32_t size;              /* allocation size */
+  uint8_t reserved[12];
+} gpa_subset_request;
+typedef struct gpa_subset_result {
+  uint8_t take[16]; /* further replicas to take from GPU label g */
+  int32_t score;    /* score of the answer in units of gpa_search_stats.score_unit; -1 for the empty answer */
+  int16_t n_out;    /* `size`, or 0: the empty answer (guards at besteffort_policy.go:35-45) or an error status */
+  int16_t status;   /* GPA_OK or a GPA_ERR_* code for this record */
+} gpa_subset_result;
+int gpa_subset_batch(gpa_ctx *ctx, const gpa_subset_request *reqs, int count, gpa_subset_result *out);
+int gpa_subset_batch_device(gpa_ctx *ctx, const gpa_subset_request *d_reqs, int count, gpa_subset_result *d_out, void *stream);
+
 /* ---- replica ids (host code: string work, no parallelism) ---------------------------- */
 
 /* Results are written NUL-separated into outbuf; *n_out = number of strings.

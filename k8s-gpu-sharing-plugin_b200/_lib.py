@@ -64,6 +64,8 @@ def lib():
     L.gpa_get_topology.argtypes = [vp, C.POINTER(C.c_int), i32p, u8p, C.c_int]
     L.gpa_besteffort.argtypes = [vp, i32p, C.c_int, i32p, C.c_int, C.c_int, C.c_int, i32p, C.POINTER(C.c_int)]
     L.gpa_last_search_stats.argtypes = [vp, C.POINTER(SearchStats)]
+    L.gpa_subset_batch.argtypes = [vp, vp, C.c_int, vp]
+    L.gpa_subset_batch_device.argtypes = [vp, vp, C.c_int, vp, vp]
     L.gpa_subset_besteffort.argtypes = [vp, i32p, C.c_int, i32p, C.c_int, C.c_int, C.c_int, i32p, C.POINTER(C.c_int)]
     L.gpa_besteffort_batch.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp]
     L.gpa_besteffort_batch_device.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp]
@@ -216,6 +218,20 @@ class Context:
                                          rq.ctypes.data_as(C.POINTER(C.c_int32)), len(rq), int(size), int(mode),
                                          out.ctypes.data_as(C.POINTER(C.c_int32)), C.byref(n_out))
         return rc, [int(x) for x in out[:n_out.value]]
+
+    def subset_batch(self, reqs, out=None):
+        """reqs: numpy array of synthetic.SUBSET_REQ_DTYPE (host memory) -> array of SUBSET_RES_DTYPE"""
+        from . import synthetic as syn
+        reqs = np.ascontiguousarray(reqs)
+        assert reqs.dtype == syn.SUBSET_REQ_DTYPE
+        if out is None:
+            out = np.zeros(len(reqs), dtype=syn.SUBSET_RES_DTYPE)
+        self._check(lib().gpa_subset_batch(self._h, reqs.ctypes.data, len(reqs), out.ctypes.data))
+        return out
+
+    def subset_batch_device(self, d_reqs_ptr, count, d_out_ptr, stream=None):
+        self._check(lib().gpa_subset_batch_device(self._h, C.c_void_p(d_reqs_ptr), int(count), C.c_void_p(d_out_ptr),
+                                                  C.c_void_p(stream or 0)))
 
     def search_stats(self):
         st = SearchStats()

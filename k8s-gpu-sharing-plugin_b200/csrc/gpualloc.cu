@@ -96,6 +96,9 @@ struct gpa_ctx {
   uint64_t *d_sub_binom = nullptr;   // C(n, j) table of the literal replica-set kernel, built on first use
   std::vector<uint64_t> sub_binom;
   SubsetPlan sub_plan;               // plan of the last gpa_subset_besteffort() (kept for its buffers)
+  gpa_subset_request *d_sub_reqs = nullptr;  // staging of gpa_subset_batch()
+  gpa_subset_result *d_sub_out = nullptr;
+  size_t sub_batch_cap = 0;
   int part_table_nt = 0;             // node size the table was built for, 0 = none
   FastTopo fast{};
   // batch staging
@@ -424,6 +427,8 @@ void gpa_destroy(gpa_ctx *ctx) {
   if (ctx->d_part_words) cudaFree(ctx->d_part_words);
   if (ctx->d_part_index) cudaFree(ctx->d_part_index);
   if (ctx->d_sub_binom) cudaFree(ctx->d_sub_binom);
+  if (ctx->d_sub_reqs) cudaFree(ctx->d_sub_reqs);
+  if (ctx->d_sub_out) cudaFree(ctx->d_sub_out);
   if (ctx->d_reqs) cudaFree(ctx->d_reqs);
   if (ctx->d_out) cudaFree(ctx->d_out);
   if (ctx->h_reqs) cudaFreeHost(ctx->h_reqs);

@@ -61,24 +61,27 @@ GPA_HD uint64_t sub_cnt_entry(const SubsetCounts &q, const uint64_t *cnt, int g,
 }
 
 // Class `rank` in descending lexicographic order of the count vectors -> its score; x_out (optional) gets the counts
-// beyond the required ones.  rank < cnt[0][K].
-GPA_HD uint32_t sub_unrank_score(const SubsetCounts &q, const uint64_t *cnt, const uint16_t *w, uint64_t rank, uint8_t *x_out) {
+// beyond the required ones.  rank < cnt[0][K].  f / r: free and required replicas per group; cnt rows are kStride apart.
+template <typename CntT, int kStride>
+GPA_HD uint32_t sub_unrank_score_t(int G, int K, const uint8_t *f, const uint8_t *r, const CntT *cnt, const uint16_t *w, uint64_t rank,
+                                   uint8_t *x_out) {
   uint32_t c[kSubGroups];
   uint32_t score = 0;
-  int left = q.K;
+  int left = K;
 #pragma unroll
   for (int g = 0; g < kSubGroups; g++) {
-    if (g < q.G) {
-      int x = q.f[g] < left ? q.f[g] : left;
+    if (g < G) {
+      const int fg = f[g];
+      int x = fg < left ? fg : left;
       while (x > 0) {
-        const uint64_t below = cnt[(g + 1) * kSubCntStride + left - x];
+        const uint64_t below = cnt[(g + 1) * kStride + left - x];
         if (rank < below) break;
         rank -= below;
         x--;
       }
       left -= x;
       if (x_out) x_out[g] = (uint8_t)x;
-      c[g] = (uint32_t)q.r[g] + (uint32_t)x;
+      c[g] = (uint32_t)r[g] + (uint32_t)x;
       uint32_t lin = 0;
 #pragma unroll
       for (int i = 0; i < kSubGroups; i++)
@@ -87,6 +90,10 @@ GPA_HD uint32_t sub_unrank_score(const SubsetCounts &q, const uint64_t *cnt, con
     }
   }
   return score;
+}
+
+GPA_HD uint32_t sub_unrank_score(const SubsetCounts &q, const uint64_t *cnt, const uint16_t *w, uint64_t rank, uint8_t *x_out) {
+  return sub_unrank_score_t<uint64_t, kSubCntStride>(q.G, q.K, q.f, q.r, cnt, w, rank, x_out);
 }
 
 // --------------------------------------------------------------------------------------------------------------------

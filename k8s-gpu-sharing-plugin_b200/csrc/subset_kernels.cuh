@@ -118,4 +118,199 @@ __global__ void __launch_bounds__(kSubThreads) subset_enum_kernel(const SubsetEn
   subset_reduce_publish(best, p.size, p.seq, g_scratch, g_ticket, g_res);
 }
 
+// --------------------------------------------------------------------------------------------------------------------
+// MANY replica-set requests in count form (gpa_subset_request): one warp per request.
+// Labels of the node order stand for the groups (a GPU with no replica in the request is a group that can take
+// nothing), so the class order and the tie-break are those of the single-request kernel.
+//
+// The count vectors are walked depth first, one GPU per level, in descending order of the count at every level
+// (= descending lexicographic order of the vectors).  The score sum_{g<h} c_g c_h w[g][h] is carried down the walk: P =
+// score of the levels above, L[h] = sum_{g above} c_g w[g][h], so a step at level g costs G-g-1 additions and a leaf two
+// operations, instead of the G^2/2 of scoring a vector from scratch.  The lanes of the warp split the walk by the counts
+// of the first kSubPrefix GPUs (an "item"), item t to lane t mod 32; a lane keeps its first best, lanes are merged on
+// (score, earliest item).
+
+constexpr int kSubBatchMaxExtra = GPA_SUBSET_BATCH_MAX_EXTRA;  // replicas to choose beyond the required ones
+constexpr int kSubBatchWarps = kSubThreads / 32;
+constexpr int kSubPrefix = 4;
+static_assert(kSubBatchMaxExtra <= 15, "a count beyond the required ones is packed in 4 bits");
+
+struct SubsetBatchTopo {
+  uint16_t w[kSubGroups * kSubGroups];  // scaled pair weight in LABEL space, [a * 16 + b] for labels a < b
+  uint16_t asym_row[kSubGroups];        // bit b of row a: link counts of labels a and b differ (calculateGPUPairScore panics)
+  int32_t nt;                           // GPUs of the node
+};
+
+static_assert(sizeof(gpa_subset_request) == 48 && sizeof(gpa_subset_result) == 24, "record layouts of gpualloc.h");
+
+template <int G, int g>
+struct SubDfs {
+  static __device__ __forceinline__ void run(const uint8_t *f, const uint8_t *r, const uint16_t *cap, const uint16_t *w, int left, int P,
+                                             int (&L)[G], int (&xs)[G], int &bs, unsigned long long &bp) {
+    const int rg = r[g];
+    const int fg = f[g];
+    const int hi = fg < left ? fg : left;
+    const int rest = left - (int)cap[g + 1];  // what the GPUs below cannot absorb
+    const int lo = rest > 0 ? rest : 0;
+#pragma unroll
+    for (int h = g + 1; h < G; h++) L[h] += (rg + hi) * (int)w[g * kSubGroups + h];
+    for (int x = hi; x >= lo; x--) {
+      xs[g] = x;
+      SubDfs<G, g + 1>::run(f, r, cap, w, left - x, P + (rg + x) * L[g], L, xs, bs, bp);
+#pragma unroll
+      for (int h = g + 1; h < G; h++) L[h] -= (int)w[g * kSubGroups + h];
+    }
+#pragma unroll
+    for (int h = g + 1; h < G; h++) L[h] -= (rg + lo - 1) * (int)w[g * kSubGroups + h];  // back to the caller's L
+  }
+};
+
+template <int G>
+struct SubDfs<G, G - 1> {  // the last GPU takes what is left (the level above made sure it can)
+  static __device__ __forceinline__ void run(const uint8_t *, const uint8_t *r, const uint16_t *, const uint16_t *, int left, int P,
+                                             int (&L)[G], int (&xs)[G], int &bs, unsigned long long &bp) {
+    const int score = P + ((int)r[G - 1] + left) * L[G - 1];
+    if (score > bs) {  // strict: the first best vector of the walk stays
+      bs = score;
+      xs[G - 1] = left;
+      unsigned long long pk = 0;
+#pragma unroll
+      for (int i = 0; i < G; i++) pk |= (unsigned long long)(unsigned)xs[i] << (4 * i);
+      bp = pk;
+    }
+  }
+};
+
+template <int G>
+__global__ void __launch_bounds__(kSubThreads) subset_batch_kernel(const gpa_subset_request *__restrict__ reqs, int count,
+                                                                    const SubsetBatchTopo t, gpa_subset_result *__restrict__ out) {
+  __shared__ uint16_t w[kSubGroups * kSubGroups];
+  __shared__ uint8_t fr_all[kSubBatchWarps][2 * kSubGroups];
+  __shared__ uint16_t cap_all[kSubBatchWarps][kSubGroups + 1];
+  __shared__ uint16_t asym_row[kSubGroups];
+  __shared__ BinomTable s_binom;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  stage_binom(s_binom, tid, kSubThreads);
+  for (int i = tid; i < kSubGroups * kSubGroups; i += kSubThreads) w[i] = t.w[i];
+  if (tid < kSubGroups) asym_row[tid] = t.asym_row[tid];
+  __syncthreads();
+  uint8_t *f = fr_all[warp];
+  uint8_t *r = f + kSubGroups;
+  uint16_t *cap = cap_all[warp];
+
+  for (long long i = (long long)blockIdx.x * kSubBatchWarps + warp; i < count; i += (long long)gridDim.x * kSubBatchWarps) {
+    // 48-byte record = 12 words: 0-3 free[], 4-7 must[], 8 size
+    const uint32_t *rec = reinterpret_cast<const uint32_t *>(reqs + i);
+    const uint32_t word = lane < 12 ? __ldg(rec + lane) : 0u;
+    const int size = (int)__shfl_sync(0xffffffffu, word, 8);
+    const uint32_t fw = __shfl_sync(0xffffffffu, word, (lane >> 2) & 3);
+    const uint32_t rw = __shfl_sync(0xffffffffu, word, 4 + ((lane >> 2) & 3));
+    const int my_f = lane < kSubGroups ? (int)((fw >> (8 * (lane & 3))) & 0xFFu) : 0;
+    const int my_r = lane < kSubGroups ? (int)((rw >> (8 * (lane & 3))) & 0xFFu) : 0;
+    const unsigned present = __ballot_sync(0xffffffffu, my_f + my_r > 0);
+    const unsigned has_free = __ballot_sync(0xffffffffu, my_f > 0);
+    int n_free = my_f, n_req = my_r;
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) {  // lanes 16.. hold zeros
+      n_free += __shfl_xor_sync(0xffffffffu, n_free, o);
+      n_req += __shfl_xor_sync(0xffffffffu, n_req, o);
+    }
+    n_free = __shfl_sync(0xffffffffu, n_free, 0);
+    n_req = __shfl_sync(0xffffffffu, n_req, 0);
+    const int K = size - n_req;
+    int status = GPA_OK;
+    bool search = true;
+    if (present >> t.nt) {
+      status = GPA_ERR_INVALID;  // replicas of a GPU the node does not have
+      search = false;
+    } else if (size <= 0 || n_free + n_req < size || n_req > size) {
+      search = false;  // besteffort_policy.go:35-45: the empty answer
+    } else if (size > GPA_SUBSET_MAX_SIZE || K > kSubBatchMaxExtra ||
+               binom_at(s_binom, K + __popc(has_free) - 1, __popc(has_free) - 1) > (uint32_t)GPA_SUBSET_BATCH_MAX_CLASSES) {
+      status = GPA_ERR_TOO_LARGE;  // (K > 0 implies a GPU with free replicas here, so the binomial is well formed)
+      search = false;
+    } else if (size >= 2) {
+      const bool bad = lane < kSubGroups && (present >> lane & 1u) && (asym_row[lane] & present);
+      if (__any_sync(0xffffffffu, bad)) {
+        status = GPA_ERR_ASYMMETRIC;
+        search = false;
+      }
+    }
+    if (search) {
+      // free counts clamped to K, required counts, and what the GPUs from g on can still absorb
+      const int fc = my_f < K ? my_f : K;
+      int suffix = lane < kSubGroups ? fc : 0;
+#pragma unroll
+      for (int o = 1; o < kSubGroups; o <<= 1) {  // inclusive suffix sum over lanes 0..15
+        const int up = __shfl_down_sync(0xffffffffu, suffix, o);
+        if (lane + o < kSubGroups) suffix += up;
+      }
+      if (lane < kSubGroups) {
+        f[lane] = (uint8_t)fc;
+        r[lane] = (uint8_t)my_r;
+        cap[lane] = (uint16_t)suffix;
+      }
+      if (lane == 0) cap[kSubGroups] = 0;
+      __syncwarp();
+
+      int bs = -1;
+      unsigned long long bp = 0;
+      uint32_t bt = 0;
+      const uint32_t n_items = binom_at(s_binom, K + kSubPrefix, kSubPrefix);  // count prefixes with sum <= K
+      for (uint32_t item = lane; item < n_items; item += 32) {
+        int xs[G];
+        int left = K;
+        uint32_t rest = item;
+        bool ok = true;
+#pragma unroll
+        for (int p = 0; p < kSubPrefix; p++) {  // prefix number `item` in descending lexicographic order
+          const int parts = kSubPrefix - p;     // the later prefix GPUs plus "everything below"
+          int v = left;
+          while (v > 0) {
+            const uint32_t with_v = binom_at(s_binom, left - v + parts - 1, parts - 1);
+            if (rest < with_v) break;
+            rest -= with_v;
+            v--;
+          }
+          xs[p] = v;
+          left -= v;
+          ok = ok && v <= (int)f[p];
+        }
+        if (!ok || left > (int)cap[kSubPrefix]) continue;
+        int L[G];
+#pragma unroll
+        for (int h = 0; h < G; h++) L[h] = 0;
+        int P = 0;
+#pragma unroll
+        for (int p = 0; p < kSubPrefix; p++) {
+          const int c = (int)r[p] + xs[p];
+          P += c * L[p];
+#pragma unroll
+          for (int h = p + 1; h < G; h++) L[h] += c * (int)w[p * kSubGroups + h];
+        }
+        const int before = bs;
+        SubDfs<G, kSubPrefix>::run(f, r, cap, w, left, P, L, xs, bs, bp);
+        if (bs > before) bt = item;
+      }
+      const unsigned long long mine = bs >= 0 ? ((unsigned long long)(unsigned)(bs + 1) << 32) | (0xFFFFFFFFu - bt) : 0ull;
+      const unsigned long long best = warp_max_u64(mine);
+      if (mine == best && best) {  // exactly one lane: items are distinct
+        uint2 *dst = reinterpret_cast<uint2 *>(out + i);
+        uint32_t take[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+        for (int g = 0; g < G; g++) take[g >> 2] |= (uint32_t)((bp >> (4 * g)) & 0xFull) << (8 * (g & 3));
+        dst[0] = make_uint2(take[0], take[1]);
+        dst[1] = make_uint2(take[2], take[3]);
+        dst[2] = make_uint2((uint32_t)bs, (uint32_t)(uint16_t)size | ((uint32_t)(uint16_t)GPA_OK << 16));
+      }
+      __syncwarp();  // f / r / cap are rewritten for the warp's next request
+    } else if (lane == 0) {
+      uint2 *dst = reinterpret_cast<uint2 *>(out + i);
+      dst[0] = make_uint2(0u, 0u);
+      dst[1] = make_uint2(0u, 0u);
+      dst[2] = make_uint2(0xFFFFFFFFu, (uint32_t)(uint16_t)0 | ((uint32_t)(uint16_t)(int16_t)status << 16));
+    }
+  }
+}
+
 }  // namespace

@@ -293,3 +293,54 @@ def random_subset_request(rng, n_gpus, replicas, p_free=0.5, grouped=True, max_s
         n_req = int(rng.integers(1, max_required + 1))
         req = [int(x) for x in rng.choice(len(phys), size=min(n_req, len(phys)), replace=False)]
     return [int(x) for x in phys], req, size
+
+
+# --------------------------------------------------------------------------------------
+# Count form of gpa_subset_batch: index g = the GPU with rank g in the node order.
+SUBSET_REQ_DTYPE = np.dtype([("free", np.uint8, 16), ("must", np.uint8, 16), ("size", np.int32), ("reserved", np.uint8, 12)])
+SUBSET_RES_DTYPE = np.dtype([("take", np.uint8, 16), ("score", np.int32), ("n_out", np.int16), ("status", np.int16)])
+assert SUBSET_REQ_DTYPE.itemsize == 48 and SUBSET_RES_DTYPE.itemsize == 24
+
+
+def random_subset_batch(n_gpus, replicas, count, seed, p_free=(0.1, 0.5, 0.9), sizes=(1, 2, 4, 8), p_must=0.1):
+    """Fragmented availability: every replica free with probability p (one p per request, drawn
+    from p_free), size drawn from `sizes`, and with probability p_must one free replica is must-include."""
+    rng = np.random.default_rng(seed)
+    reqs = np.zeros(count, dtype=SUBSET_REQ_DTYPE)
+    p = rng.choice(np.asarray(p_free, dtype=np.float64), size=count)
+    free = rng.binomial(replicas, p[:, None], size=(count, n_gpus)).astype(np.uint8)
+    reqs["size"] = rng.choice(np.asarray(sizes, dtype=np.int32), size=count)
+    must_row = np.nonzero(rng.random(count) < p_must)[0]
+    for i in must_row:
+        g = np.nonzero(free[i])[0]
+        if len(g):
+            j = int(rng.choice(g))
+            free[i, j] -= 1
+            reqs["must"][i, j] = 1
+    reqs["free"][:, :n_gpus] = free
+    return reqs
+
+
+def subset_record_to_positions(rec, rng=None):
+    """count record -> (phys, req_pos) for gpa_subset_besteffort / the oracle: positions grouped by label; WHICH replicas
+    of a GPU are the must-include ones does not matter for the counts (any choice gives the same take[])"""
+    phys, req = [], []
+    for g in range(16):
+        n = int(rec["free"][g]) + int(rec["must"][g])
+        pick = list(range(n))
+        if rng is not None:
+            rng.shuffle(pick)
+        must_local = set(pick[:int(rec["must"][g])])
+        for j in range(n):
+            if j in must_local:
+                req.append(len(phys))
+            phys.append(g)
+    return phys, req
+
+
+def positions_to_take(phys, req_pos, positions):
+    take = [0] * 16
+    for p in positions:
+        if p not in req_pos:
+            take[phys[p]] += 1
+    return take

@@ -143,3 +143,74 @@ def test_large_requests_only_the_count_vectors_can_answer(ctx):
     assert rc == 0 and st["algorithm"] == 4 and st["partitions"] == 490314     # C(23, 15) count vectors
     score = sum(int(W16[free16[a], free16[b]]) for i, a in enumerate(pos) for b in pos[i + 1:] if free16[a] != free16[b])
     assert score == st["best_score"] * st["score_unit"]
+
+
+def test_batch_in_count_form_matches_the_oracle(ctx, oracle):
+    """gpa_subset_batch: fragmented availability at 8 GPUs x 4 replicas (config 2), every record against the literal oracle
+    on its expansion to positions, and against the single-request call"""
+    order = syn.sorted_positions(syn.node_uuids(8, seed=1))
+    for ti in (1, 3, 6, 11):
+        name, t = syn.standard_topologies()[ti]
+        ctx.set_topology_links(t)
+        ctx.set_device_order(order)
+        W, nl = syn.links_to_weights(t)
+        reqs = syn.random_subset_batch(8, 4, 400, seed=20 + ti, sizes=(1, 2, 3, 4, 5), p_must=0.3)
+        reqs["size"][:4] = (0, -1, 40, 33)                       # guards
+        got = ctx.subset_batch(reqs)
+        unit = None
+        rng = np.random.default_rng(ti)
+        for i, rec in enumerate(reqs):
+            phys_lab, req = syn.subset_record_to_positions(rec, rng)
+            phys = [order[g] for g in phys_lab]                   # label -> NVML index
+            rc, pos, score, _ = oracle.subset_besteffort(W, nl, phys, req, int(rec["size"]), True)
+            assert rc == 0 and got["status"][i] == 0
+            assert int(got["n_out"][i]) == len(pos), (name, i)
+            if pos:
+                assert got["take"][i].tolist() == syn.positions_to_take(phys_lab, set(req), pos), (name, i, rec)
+                if unit is None and score > 0:
+                    assert score % int(got["score"][i]) == 0
+                    unit = score // int(got["score"][i])
+                if unit is not None:
+                    assert int(got["score"][i]) * unit == score
+            else:
+                assert not got["take"][i].any() and int(got["score"][i]) == -1
+            if i < 60:
+                assert ctx.subset_besteffort(phys, req, int(rec["size"])) == (0, pos)
+
+
+def test_batch_statuses_and_larger_nodes(ctx, oracle):
+    W, nl = syn.links_to_weights(syn.topo_uniform(8))
+    anl = nl.copy()
+    anl[2, 5] = 2
+    ctx.set_topology(W, anl)
+    reqs = np.zeros(6, dtype=syn.SUBSET_REQ_DTYPE)
+    reqs["free"][0, [2, 5]] = 2; reqs["size"][0] = 2             # scores the asymmetric pair: the reference panics
+    reqs["free"][1, [2, 5]] = 2; reqs["size"][1] = 1             # size 1 scores nothing
+    reqs["free"][2, [0, 2]] = 2; reqs["size"][2] = 3
+    reqs["free"][3, 9] = 1; reqs["size"][3] = 1                  # the node has 8 GPUs
+    reqs["free"][4, :8] = 30; reqs["size"][4] = 17               # beyond the batch form
+    reqs["must"][5, :8] = 20; reqs["size"][5] = 160              # beyond GPA_SUBSET_MAX_SIZE
+    got = ctx.subset_batch(reqs)
+    assert got["status"].tolist() == [gpa.ERR_ASYMMETRIC, 0, 0, gpa.ERR_INVALID, gpa.ERR_TOO_LARGE, gpa.ERR_TOO_LARGE]
+    assert got["n_out"].tolist() == [0, 1, 3, 0, 0, 0]
+    assert got["take"][1].tolist()[:8] == [0, 0, 1, 0, 0, 0, 0, 0] and got["take"][2].tolist()[:3] == [2, 0, 1]
+    # a 16-GPU node, deep replicas, sizes up to 16: against the single-request kernel (same classes, one request a launch)
+    t16 = syn.topo_random(16, 78)
+    ctx.set_topology_links(t16)
+    big = syn.random_subset_batch(16, 8, 64, seed=5, sizes=(2, 4, 8, 12), p_must=0.5)
+    got = ctx.subset_batch(big)
+    from math import comb
+    n_large = 0
+    for i, rec in enumerate(big):
+        phys, req = syn.subset_record_to_positions(rec)
+        K, g = int(rec["size"]) - len(req), int((rec["free"] > 0).sum())
+        if len(phys) >= int(rec["size"]) and comb(K + g - 1, g - 1) > (1 << 20):     # the batch form's work limit
+            assert got["status"][i] == gpa.ERR_TOO_LARGE
+            n_large += 1
+            continue
+        rc, pos = ctx.subset_besteffort(phys, req, int(rec["size"]))
+        assert rc == 0 and got["status"][i] == 0 and int(got["n_out"][i]) == len(pos)
+        if pos:
+            assert got["take"][i].tolist() == syn.positions_to_take(phys, set(req), pos), i
+            assert int(got["score"][i]) == ctx.search_stats()["best_score"] or len(req) == int(rec["size"])
+    assert 0 < n_large < len(big) // 2
