@@ -347,6 +347,10 @@ void gpa_health_close(gpa_health *h);
 #define GPA_FIX_HEALTH_PROPAGATION 1 /* D1: an unhealthy GPU marks all of its replicas Unhealthy in ListAndWatch */
 #define GPA_FIX_REPLICA_SUFFIX 2     /* D3: best-effort answers carry the "-replica-0" suffix kubelet knows */
 #define GPA_FIX_REQUIRED_IDENTITY 4  /* D4: MustIncludeDeviceIDs are matched by uuid, not by pointer */
+#define GPA_OPT_REPLICA_TOPOLOGY 8   /* NOT a fix - an option with no reference counterpart: with replicas > 1,
+                                        GetPreferredAllocation picks the best-connected replicas (gpa_subset_besteffort
+                                        over the byte-wise sorted ids) instead of prioritizeDevices; needs a policy
+                                        context.  Error texts stay those of replica.go:129,136,183. */
 
 typedef struct gpa_plugin gpa_plugin;
 typedef struct gpa_plugin_config { /* ref: NvidiaDevicePlugin + config.Flags, server.go:56-71 */

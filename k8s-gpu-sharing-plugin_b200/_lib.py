@@ -314,6 +314,7 @@ TOPO_PARITY, TOPO_NVSWITCH_AWARE = 0, 1
 LIST_ENVVAR, LIST_VOLUME_MOUNTS = 0, 1
 ID_UUID, ID_INDEX = 0, 1
 FIX_HEALTH_PROPAGATION, FIX_REPLICA_SUFFIX, FIX_REQUIRED_IDENTITY = 1, 2, 4
+OPT_REPLICA_TOPOLOGY = 8  # not a fix: replica requests answered by the replica-set search (gpualloc.h)
 
 
 class PluginConfig(C.Structure):

@@ -222,6 +222,60 @@ int gpa_plugin_mark_unhealthy(gpa_plugin *p, int cached_index) {
   return changed;
 }
 
+// GPA_OPT_REPLICA_TOPOLOGY (no reference counterpart): the replica branch of GetPreferredAllocation answered by the
+// replica-set search instead of prioritizeDevices.  The ids are sorted byte-wise first (what prioritizeDevices' callers
+// see in the end, replica.go:191), so the replicas of a GPU are contiguous and the answer does not depend on the order
+// kubelet listed them in.  Errors keep the reference's kinds and texts: replica.go:121 (panic), :136, :183.
+static int preferred_by_topology(gpa_plugin *p, const char *const *avail, int n_avail, const char *const *must, int n_must, int size,
+                                 char *outbuf, int outbuf_len, int *n_out, char *errbuf, int errbuf_len) {
+  if (n_must > size) {
+    set_err(errbuf, errbuf_len, "runtime error: makeslice: cap out of range");
+    return GPA_ERR_PANIC;
+  }
+  std::vector<std::string> ids;
+  ids.reserve((size_t)n_avail);
+  for (int i = 0; i < n_avail; i++) ids.emplace_back(avail[i]);
+  std::sort(ids.begin(), ids.end());
+  ids.erase(std::unique(ids.begin(), ids.end()), ids.end());
+  std::vector<int32_t> phys(ids.size()), req;
+  for (size_t i = 0; i < ids.size(); i++) {
+    const size_t cut = ids[i].find("-replica-");  // stripReplica, replica.go:28-30
+    auto it = p->cached_by_id.find(cut == std::string::npos ? ids[i] : ids[i].substr(0, cut));
+    if (it == p->cached_by_id.end()) return GPA_ERR_UNKNOWN_DEVICE;  // cannot happen: resolve() has seen every id
+    phys[i] = p->cached[it->second].nvml_index;
+  }
+  for (int i = 0; i < n_must; i++) {
+    auto it = std::lower_bound(ids.begin(), ids.end(), std::string(must[i]));
+    if (it == ids.end() || *it != must[i]) {
+      set_err(errbuf, errbuf_len, std::string("device '") + must[i] + "' in mustIncludeDeviceIDs is missing from availableDeviceIDs");
+      return GPA_ERR_MUST_MISSING;
+    }
+    const int32_t pos = (int32_t)(it - ids.begin());
+    if (std::find(req.begin(), req.end(), pos) == req.end()) req.push_back(pos);
+  }
+  if (size <= 0) return GPA_OK;
+  if ((int)ids.size() < size) {
+    set_err(errbuf, errbuf_len, "no devices left to allocate");
+    return GPA_ERR_NO_DEVICES_LEFT;
+  }
+  std::vector<int32_t> out((size_t)size + 1);
+  int cnt = 0;
+  int rc = gpa_subset_besteffort(p->ctx, phys.data(), (int)phys.size(), req.data(), (int)req.size(), size, 0, out.data(), &cnt);
+  if (rc != GPA_OK) {
+    set_err(errbuf, errbuf_len, std::string(gpa_strerror(rc)) + ": " + gpa_last_error(p->ctx));
+    return rc;
+  }
+  std::string packed;
+  for (int i = 0; i < cnt; i++) {
+    packed += ids[(size_t)out[i]];
+    packed.push_back('\0');
+  }
+  if ((int)packed.size() > outbuf_len) return GPA_ERR_BUFFER;
+  if (!packed.empty()) memcpy(outbuf, packed.data(), packed.size());
+  *n_out = cnt;
+  return GPA_OK;
+}
+
 // One iteration of the loop over r.ContainerRequests in GetPreferredAllocation (server.go:273-311).
 int gpa_plugin_get_preferred_allocation(gpa_plugin *p, const char *const *avail, int n_avail, const char *const *must,
                                         int n_must, int size, char *outbuf, int outbuf_len, int *n_out, char *errbuf,
@@ -255,6 +309,8 @@ int gpa_plugin_get_preferred_allocation(gpa_plugin *p, const char *const *avail,
   rc = resolve(must, n_must, "required", required);  // :279
   if (rc != GPA_OK) return rc;
 
+  if ((p->replicas > 1 || p->auto_replicas) && (p->fixes & GPA_OPT_REPLICA_TOPOLOGY) && p->ctx && p->has_policy)
+    return preferred_by_topology(p, avail, n_avail, must, n_must, size, outbuf, outbuf_len, n_out, errbuf, errbuf_len);
   if (p->replicas > 1 || p->auto_replicas) {
     // :285-296
     int non_unique = 0;

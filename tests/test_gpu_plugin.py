@@ -118,3 +118,47 @@ def test_real_nvml_topology_and_health_open():
         h.close()
     finally:
         nv.close()
+
+
+def test_replica_requests_by_topology_option():
+    """GPA_OPT_REPLICA_TOPOLOGY (no reference counterpart): with replicas > 1 GetPreferredAllocation returns the
+    best-connected replicas - checked against the replica-set oracle on the byte-wise sorted ids - while the default stays
+    prioritizeDevices; error kinds and texts stay the reference's (replica.go:121,136,183)."""
+    from oracle import oracle as orc
+    t = syn.topo_dgx1v_like()
+    W, nl = syn.links_to_weights(t)
+    devices = make_devices(8)
+    ctx = gpa.Context(0)
+    ctx.set_topology_links(t)
+    plug = gpa.Plugin(devices, ctx=ctx, replicas=4, has_policy=True, fixes=gpa.OPT_REPLICA_TOPOLOGY)
+    plain = gpa.Plugin(devices, ctx=ctx, replicas=4, has_policy=True)
+    index_of = {d["id"]: d["nvml_index"] for d in devices}
+    try:
+        ids = [d["ID"] for d in plug.api_devices()]
+        assert len(ids) == 32
+        rng = np.random.default_rng(5)
+        differs = 0
+        for _ in range(200):
+            avail = [str(x) for x in rng.permutation(ids)[: int(rng.integers(2, 33))]]
+            size = int(rng.integers(1, min(len(avail), 6) + 1))
+            must = [avail[int(rng.integers(len(avail)))]] if rng.random() < 0.3 else []
+            got = plug.get_preferred_allocation(avail, must, size)
+            srt = sorted(avail)                                   # sort.Strings order: byte-wise
+            phys = [index_of[x.split("-replica-")[0]] for x in srt]
+            rc, pos = orc.subset_besteffort(W, nl, phys, [srt.index(m) for m in must], size)
+            assert rc == 0 and got == [srt[p] for p in pos], (avail, must, size)
+            assert got == sorted(got) and set(must) <= set(got)
+            assert got == plug.get_preferred_allocation(avail[::-1], must, size)      # order kubelet lists ids in: irrelevant
+            differs += got != plain.get_preferred_allocation(avail, must, size)
+        assert differs > 20                                       # it IS a different policy from prioritizeDevices
+        a = [ids[0], ids[5]]
+        assert call(plug.get_preferred_allocation, a, [ids[9]], 1) == call(plain.get_preferred_allocation, a, [ids[9]], 1)
+        assert "missing from availableDeviceIDs" in call(plug.get_preferred_allocation, a, [ids[9]], 1)[1]
+        assert call(plug.get_preferred_allocation, a, [], 3) == call(plain.get_preferred_allocation, a, [], 3)
+        assert "no devices left" in call(plug.get_preferred_allocation, a, [], 3)[1]
+        assert call(plug.get_preferred_allocation, a, a, 1) == call(plain.get_preferred_allocation, a, a, 1)   # :121 panic
+        assert plug.get_preferred_allocation(a, [], 0) == []
+    finally:
+        plug.close()
+        plain.close()
+        ctx.close()
