@@ -495,6 +495,31 @@ def run_ours(args):
         row["mismatches"] = int(row["count_vectors"]["answer"] != want[1]) + int(row["literal"]["answer"] != want[1])
         replica_set["%d_virtual_devices" % (N_DEV * reps)] = row
 
+    # the largest literal walk the configs define: 4 of 256 replicas, all free (C(256, 4) candidates)
+    all256 = [g for g in range(N_DEV) for _ in range(32)]
+    stress = {}
+    for name, flag in (("count_vectors", 0), ("literal", gpa.MODE_FORCE_ENUM)):
+        lat, kms, ans = [], [], None
+        for i in range(args.warmup + 20):
+            t0 = time.perf_counter()
+            ans = ctx.subset_besteffort(all256, [], 4, flag)
+            dt = time.perf_counter() - t0
+            if i >= args.warmup:
+                lat.append(dt)
+                kms.append(ctx.search_stats()["kernel_ms"])
+        st = ctx.search_stats()
+        stress[name] = {"candidates": st["partitions"], "grid": st["grid"], "call_us_p50": float(np.percentile(lat, 50)) * 1e6,
+                        "kernel_ms": float(np.median(kms)), "answer": ans[1]}
+        if np.median(kms) > 0:
+            stress[name]["candidates_per_s"] = st["partitions"] / (float(np.median(kms)) * 1e-3)
+            stress[name]["algorithmic_gbs"] = 4.0 * 6 * st["partitions"] / (float(np.median(kms)) * 1e-3) / 1e9
+    t0 = time.perf_counter()
+    want = orc.subset_besteffort(W, nl, all256, [], 4)
+    stress["oracle_call_ms"] = (time.perf_counter() - t0) * 1e3
+    stress["mismatches"] = int(stress["count_vectors"]["answer"] != want[1]) + int(stress["literal"]["answer"] != want[1])
+    stress["note"] = "algorithmic_gbs = 4 B x C(4, 2) pair evaluations per candidate, as SURVEY.md 8d counts them"
+    replica_set["256_virtual_devices_all_free"] = stress
+
     # ---- the same search for MANY requests in count form (gpa_subset_batch): the metric's "decisions/s at 32 / 128 / 256
     #      virtual devices" with GPU work behind it; only rank 0's numbers are reported (replicas only, no collective) ----
     from math import comb

@@ -126,18 +126,29 @@ inline void sub_fill_binom(uint64_t *b) {
     }
 }
 
-// Combination number `rank` (lexicographic) of K out of R -> e[0..K)
+// Combination number `rank` (lexicographic) of K out of R -> e[0..K).  The combinations whose next pick lies d or more
+// places further on are the LAST C(n - d, k) of the C(n, k) that remain, so the pick follows from a binary search for the
+// largest d with C(n - d, k) >= (combinations from this one to the end): 8 probes per pick instead of a scan.
 template <int K>
 GPA_HD void sub_comb_unrank(const uint64_t *binom, int R, uint64_t rank, int (&e)[K]) {
-  int v = 0;
+  int n = R;     // pool left
+  int base = 0;  // index of the pool's first member
 #pragma unroll
   for (int i = 0; i < K; i++) {
-    for (;; v++) {
-      const uint64_t with_v = binom[(R - 1 - v) * kSubBinomCols + (K - 1 - i)];  // combinations whose i-th pick is v
-      if (rank < with_v) break;
-      rank -= with_v;
+    const int k = K - i;
+    const uint64_t to_end = binom[n * kSubBinomCols + k] - rank;
+    int lo = 0, hi = n - k;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (binom[(n - mid) * kSubBinomCols + k] >= to_end)
+        lo = mid;
+      else
+        hi = mid - 1;
     }
-    e[i] = v++;
+    rank -= binom[n * kSubBinomCols + k] - binom[(n - lo) * kSubBinomCols + k];
+    e[i] = base + lo;
+    base += lo + 1;
+    n -= lo + 1;
   }
 }
 

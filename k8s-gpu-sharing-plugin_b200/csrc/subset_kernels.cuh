@@ -90,7 +90,9 @@ __global__ void __launch_bounds__(kSubThreads) subset_enum_kernel(const SubsetEn
   __shared__ uint8_t grp[kSubEnumMaxFree];
   __shared__ uint32_t wreq[kSubEnumMaxFree];
   __shared__ uint16_t w[kSubGroups * kSubGroups];
+  __shared__ uint64_t s_binom[kSubBinomRows * kSubBinomCols];  // 18.5 KB: every lane probes its own entries while unranking
   const int tid = threadIdx.x;
+  for (int i = tid; i < kSubBinomRows * kSubBinomCols; i += kSubThreads) s_binom[i] = binom[i];
   for (int i = tid; i < kSubEnumMaxFree; i += kSubThreads) {
     grp[i] = p.q.grp[i];
     wreq[i] = p.q.wreq[i];
@@ -103,7 +105,7 @@ __global__ void __launch_bounds__(kSubThreads) subset_enum_kernel(const SubsetEn
   for (unsigned long long start = ((unsigned long long)blockIdx.x * kSubThreads + tid) * p.chunk; start < p.total; start += stride) {
     int e[K], ge[K];
     uint32_t ps[K + 1];
-    sub_comb_unrank<K>(binom, R, start, e);
+    sub_comb_unrank<K>(s_binom, R, start, e);
     ps[0] = p.q.base;
     sub_comb_rescore<K>(grp, wreq, w, e, ge, ps, 0);
     const unsigned long long end = start + p.chunk < p.total ? start + p.chunk : p.total;
@@ -182,11 +184,12 @@ struct SubDfs<G, G - 1> {  // the last GPU takes what is left (the level above m
 };
 
 template <int G>
-__global__ void __launch_bounds__(kSubThreads) subset_batch_kernel(const gpa_subset_request *__restrict__ reqs, int count,
+__global__ void __launch_bounds__(kSubThreads, G <= 8 ? 3 : 1) subset_batch_kernel(const gpa_subset_request *__restrict__ reqs, int count,
                                                                     const SubsetBatchTopo t, gpa_subset_result *__restrict__ out) {
   __shared__ uint16_t w[kSubGroups * kSubGroups];
   __shared__ uint8_t fr_all[kSubBatchWarps][2 * kSubGroups];
   __shared__ uint16_t cap_all[kSubBatchWarps][kSubGroups + 1];
+  __shared__ uint32_t ways_all[kSubBatchWarps][(kSubPrefix + 1) * 16];
   __shared__ uint16_t asym_row[kSubGroups];
   __shared__ BinomTable s_binom;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -197,6 +200,7 @@ __global__ void __launch_bounds__(kSubThreads) subset_batch_kernel(const gpa_sub
   uint8_t *f = fr_all[warp];
   uint8_t *r = f + kSubGroups;
   uint16_t *cap = cap_all[warp];
+  uint32_t *ways = ways_all[warp];  // [p * 16 + left]: valid ways for prefix GPUs p.. to leave something the rest can absorb
 
   for (long long i = (long long)blockIdx.x * kSubBatchWarps + warp; i < count; i += (long long)gridDim.x * kSubBatchWarps) {
     // 48-byte record = 12 words: 0-3 free[], 4-7 must[], 8 size
@@ -253,30 +257,41 @@ __global__ void __launch_bounds__(kSubThreads) subset_batch_kernel(const gpa_sub
       if (lane == 0) cap[kSubGroups] = 0;
       __syncwarp();
 
+      // Items = count prefixes of the first kSubPrefix GPUs that respect the free counts and leave no more than the GPUs
+      // below can absorb.  ways[] counts them per (level, replicas left) so that item numbers unrank to VALID prefixes only
+      // (with fragmented availability most of the C(K + 4, 4) unconstrained prefixes are not).
+      if (lane <= K) ways[kSubPrefix * 16 + lane] = lane <= (int)cap[kSubPrefix] ? 1u : 0u;
+      __syncwarp();
+#pragma unroll
+      for (int p = kSubPrefix - 1; p >= 0; p--) {
+        if (lane <= K) {
+          uint32_t sum = 0;
+          const int hi = (int)f[p] < lane ? (int)f[p] : lane;
+          for (int x = 0; x <= hi; x++) sum += ways[(p + 1) * 16 + lane - x];
+          ways[p * 16 + lane] = sum;
+        }
+        __syncwarp();
+      }
       int bs = -1;
       unsigned long long bp = 0;
       uint32_t bt = 0;
-      const uint32_t n_items = binom_at(s_binom, K + kSubPrefix, kSubPrefix);  // count prefixes with sum <= K
+      const uint32_t n_items = ways[K];
       for (uint32_t item = lane; item < n_items; item += 32) {
         int xs[G];
         int left = K;
         uint32_t rest = item;
-        bool ok = true;
 #pragma unroll
         for (int p = 0; p < kSubPrefix; p++) {  // prefix number `item` in descending lexicographic order
-          const int parts = kSubPrefix - p;     // the later prefix GPUs plus "everything below"
-          int v = left;
+          int v = (int)f[p] < left ? (int)f[p] : left;
           while (v > 0) {
-            const uint32_t with_v = binom_at(s_binom, left - v + parts - 1, parts - 1);
+            const uint32_t with_v = ways[(p + 1) * 16 + left - v];
             if (rest < with_v) break;
             rest -= with_v;
             v--;
           }
           xs[p] = v;
           left -= v;
-          ok = ok && v <= (int)f[p];
         }
-        if (!ok || left > (int)cap[kSubPrefix]) continue;
         int L[G];
 #pragma unroll
         for (int h = 0; h < G; h++) L[h] = 0;

@@ -12,6 +12,9 @@
 extern "C" int ref_besteffort_fast(int nt, const int32_t *W, const uint8_t *nlinks, const int32_t *avail, int n_avail, const int32_t *req,
                                    int n_req, int size, int mode, int32_t *out, int *n_out, unsigned long long *visited);
 
+extern "C" int ref_subset_besteffort(int nt, const int32_t *W, const uint8_t *nlinks, const int32_t *phys, int n_avail, const int32_t *req_pos,
+                                     int n_req, int size, int32_t *out_pos, int *n_out, long long *best_score, unsigned long long *visited);
+
 int main() {
   const int n = 8;
   // synthetic hybrid cube mesh (synthetic.topo_dgx1v_like): PCIe + NVLink weights
@@ -60,6 +63,36 @@ int main() {
     std::sort(c.begin(), c.end());
     printf("%s{\"k\": %d, \"gpu_p50\": %.1f, \"gpu_p99\": %.1f, \"oracle_p50\": %.2f, \"oracle_p99\": %.2f, \"same\": %s}", k > 1 ? ", " : "", k,
            g[g.size() / 2], g[(size_t)(g.size() * 0.99)], c[c.size() / 2], c[(size_t)(c.size() * 0.99)], same ? "true" : "false");
+  }
+  printf("],\n \"replica_set\": [");
+  // replica-set search (gpa_subset_besteffort, count-vector kernel): 4 of the free replicas, every second replica free
+  const int reps_of[3] = {4, 16, 32};
+  for (int c = 0; c < 3; c++) {
+    std::vector<int32_t> phys;
+    for (int g = 0; g < n; g++)
+      for (int r = 0; r < reps_of[c]; r += 2) phys.push_back(g);
+    int32_t pos[8], pos2[8];
+    std::vector<double> g, cpu;
+    int n_out = 0, n_out2 = 0;
+    const int cpu_every = c == 0 ? 1 : (c == 1 ? 20 : 200);  // the literal oracle walks C(free, 4) combinations
+    for (int i = 0; i < 2200; i++) {
+      auto t0 = std::chrono::steady_clock::now();
+      gpa_subset_besteffort(ctx, phys.data(), (int)phys.size(), nullptr, 0, 4, 0, pos, &n_out);
+      auto t1 = std::chrono::steady_clock::now();
+      if (i >= 200) g.push_back(std::chrono::duration<double, std::micro>(t1 - t0).count());
+      if (i % cpu_every == 0) {
+        auto t2 = std::chrono::steady_clock::now();
+        ref_subset_besteffort(n, W, nl, phys.data(), (int)phys.size(), nullptr, 0, 4, pos2, &n_out2, nullptr, nullptr);
+        auto t3 = std::chrono::steady_clock::now();
+        cpu.push_back(std::chrono::duration<double, std::micro>(t3 - t2).count());
+      }
+    }
+    bool same = n_out == n_out2 && std::equal(pos, pos + n_out, pos2);
+    std::sort(g.begin(), g.end());
+    std::sort(cpu.begin(), cpu.end());
+    printf("%s{\"virtual_devices\": %d, \"free\": %d, \"size\": 4, \"gpu_p50\": %.1f, \"gpu_p99\": %.1f, \"oracle_p50\": %.1f, \"same\": %s}",
+           c ? ", " : "", n * reps_of[c], (int)phys.size(), g[g.size() / 2], g[(size_t)(g.size() * 0.99)], cpu[cpu.size() / 2],
+           same ? "true" : "false");
   }
   printf("]}\n");
   gpa_destroy(ctx);
