@@ -129,8 +129,7 @@ __global__ void __launch_bounds__(kSubThreads) subset_enum_kernel(const SubsetEn
 // (= descending lexicographic order of the vectors).  The score sum_{g<h} c_g c_h w[g][h] is carried down the walk: P =
 // score of the levels above, L[h] = sum_{g above} c_g w[g][h], so a step at level g costs G-g-1 additions and a leaf two
 // operations, instead of the G^2/2 of scoring a vector from scratch.  The lanes of the warp split the walk by the counts
-// of the first kSubPrefix GPUs (an "item"), item t to lane t mod 32; a lane keeps its first best, lanes are merged on
-// (score, earliest item).
+// of the first kSubPrefix GPUs (an "item"); bests are merged on (score, lexicographically largest vector).
 
 constexpr int kSubBatchMaxExtra = GPA_SUBSET_BATCH_MAX_EXTRA;  // replicas to choose beyond the required ones
 constexpr int kSubBatchWarps = kSubThreads / 32;
@@ -189,7 +188,7 @@ __global__ void __launch_bounds__(kSubThreads, G <= 8 ? 3 : 1) subset_batch_kern
   __shared__ uint16_t w[kSubGroups * kSubGroups];
   __shared__ uint8_t fr_all[kSubBatchWarps][2 * kSubGroups];
   __shared__ uint16_t cap_all[kSubBatchWarps][kSubGroups + 1];
-  __shared__ uint32_t ways_all[kSubBatchWarps][(kSubPrefix + 1) * 16];
+  __shared__ uint32_t exact_all[kSubBatchWarps][(kSubPrefix + 1) * 16];
   __shared__ uint16_t asym_row[kSubGroups];
   __shared__ BinomTable s_binom;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -200,7 +199,7 @@ __global__ void __launch_bounds__(kSubThreads, G <= 8 ? 3 : 1) subset_batch_kern
   uint8_t *f = fr_all[warp];
   uint8_t *r = f + kSubGroups;
   uint16_t *cap = cap_all[warp];
-  uint32_t *ways = ways_all[warp];  // [p * 16 + left]: valid ways for prefix GPUs p.. to leave something the rest can absorb
+  uint32_t *exact = exact_all[warp];
 
   for (long long i = (long long)blockIdx.x * kSubBatchWarps + warp; i < count; i += (long long)gridDim.x * kSubBatchWarps) {
     // 48-byte record = 12 words: 0-3 free[], 4-7 must[], 8 size
@@ -258,39 +257,46 @@ __global__ void __launch_bounds__(kSubThreads, G <= 8 ? 3 : 1) subset_batch_kern
       __syncwarp();
 
       // Items = count prefixes of the first kSubPrefix GPUs that respect the free counts and leave no more than the GPUs
-      // below can absorb.  ways[] counts them per (level, replicas left) so that item numbers unrank to VALID prefixes only
-      // (with fragmented availability most of the C(K + 4, 4) unconstrained prefixes are not).
-      if (lane <= K) ways[kSubPrefix * 16 + lane] = lane <= (int)cap[kSubPrefix] ? 1u : 0u;
+      // below can absorb.  Items that leave the SAME number of replicas walk identical subtrees below the prefix (only P
+      // and L differ), so they are numbered class by class - most left first - and a warp's 32 lanes run in lockstep
+      // except where a round straddles two classes.  exact[p][s] = ways for prefix GPUs p.. to take exactly s.
+      if (lane <= K) exact[kSubPrefix * 16 + lane] = lane == 0 ? 1u : 0u;
       __syncwarp();
 #pragma unroll
       for (int p = kSubPrefix - 1; p >= 0; p--) {
         if (lane <= K) {
           uint32_t sum = 0;
           const int hi = (int)f[p] < lane ? (int)f[p] : lane;
-          for (int x = 0; x <= hi; x++) sum += ways[(p + 1) * 16 + lane - x];
-          ways[p * 16 + lane] = sum;
+          for (int x = 0; x <= hi; x++) sum += exact[(p + 1) * 16 + lane - x];
+          exact[p * 16 + lane] = sum;
         }
         __syncwarp();
       }
+      const int s_lo = K > (int)cap[kSubPrefix] ? K - (int)cap[kSubPrefix] : 0;  // the prefix must take at least this much
+      uint32_t n_items = 0;
+      for (int sp = s_lo; sp <= K; sp++) n_items += exact[sp];
       int bs = -1;
       unsigned long long bp = 0;
-      uint32_t bt = 0;
-      const uint32_t n_items = ways[K];
+      uint32_t blex = 0;
       for (uint32_t item = lane; item < n_items; item += 32) {
-        int xs[G];
-        int left = K;
         uint32_t rest = item;
+        int sp = s_lo;
+        while (rest >= exact[sp]) rest -= exact[sp++];
+        int xs[G];
+        int todo = sp;
+        uint32_t lex = 0;
 #pragma unroll
-        for (int p = 0; p < kSubPrefix; p++) {  // prefix number `item` in descending lexicographic order
-          int v = (int)f[p] < left ? (int)f[p] : left;
+        for (int p = 0; p < kSubPrefix; p++) {  // prefix number `rest` of its class, descending lexicographic order
+          int v = (int)f[p] < todo ? (int)f[p] : todo;
           while (v > 0) {
-            const uint32_t with_v = ways[(p + 1) * 16 + left - v];
+            const uint32_t with_v = exact[(p + 1) * 16 + todo - v];
             if (rest < with_v) break;
             rest -= with_v;
             v--;
           }
           xs[p] = v;
-          left -= v;
+          todo -= v;
+          lex = (lex << 4) | (uint32_t)v;
         }
         int L[G];
 #pragma unroll
@@ -303,13 +309,18 @@ __global__ void __launch_bounds__(kSubThreads, G <= 8 ? 3 : 1) subset_batch_kern
 #pragma unroll
           for (int h = p + 1; h < G; h++) L[h] += c * (int)w[p * kSubGroups + h];
         }
-        const int before = bs;
-        SubDfs<G, kSubPrefix>::run(f, r, cap, w, left, P, L, xs, bs, bp);
-        if (bs > before) bt = item;
+        int is = -1;  // this item's first best
+        unsigned long long ip = 0;
+        SubDfs<G, kSubPrefix>::run(f, r, cap, w, K - sp, P, L, xs, is, ip);
+        if (is > bs || (is == bs && lex > blex)) {  // items do not come in vector order: ties go to the larger prefix
+          bs = is;
+          bp = ip;
+          blex = lex;
+        }
       }
-      const unsigned long long mine = bs >= 0 ? ((unsigned long long)(unsigned)(bs + 1) << 32) | (0xFFFFFFFFu - bt) : 0ull;
+      const unsigned long long mine = bs >= 0 ? ((unsigned long long)(unsigned)(bs + 1) << 32) | blex : 0ull;
       const unsigned long long best = warp_max_u64(mine);
-      if (mine == best && best) {  // exactly one lane: items are distinct
+      if (mine == best && best) {  // exactly one lane: prefixes are distinct
         uint2 *dst = reinterpret_cast<uint2 *>(out + i);
         uint32_t take[4] = {0u, 0u, 0u, 0u};
 #pragma unroll
