@@ -296,6 +296,23 @@ int gpa_prioritize_devices(const char *const *avail, int n_avail, const char *co
 /* ref: getAdditionalXids(), cmd/nvidia-device-plugin/nvidia.go:274-294. */
 int gpa_get_additional_xids(const char *input, uint64_t *out, int out_cap);
 
+/* --resource-config "orig:new:replicas,..." -> variants, in first-seen order (a later entry for the same `orig`
+ * replaces the earlier one, as the Go map does).  replicas == -1 selects auto replicas (replicas = 1, auto = 1); any
+ * other value is converted the way Go's uint(int64) does.  Errors carry the reference's texts in errbuf:
+ * GPA_ERR_INVALID "an entry must have three parts separated by a semicolon" / "replica must be an integer"
+ * (strconv.ParseInt(s, 10, 32): optional sign, decimal digits, 32-bit range).
+ * ref: parseResourceConfig(), cmd/nvidia-device-plugin/main.go:171-203; type variant, mig-strategy.go:57-62. */
+typedef struct gpa_resource_variant {
+  char orig[64];               /* resource the entry applies to ("gpu", or a MIG profile name) */
+  char name[64];               /* advertised as "nvidia.com/<name>" */
+  unsigned long long replicas; /* variant.Replicas */
+  int auto_replicas;           /* variant.AutoReplicas */
+} gpa_resource_variant;
+int gpa_parse_resource_config(const char *config, gpa_resource_variant *out, int cap, int *n_out, char *errbuf, int errbuf_len);
+/* ref: resourceConfiguration.Get(), mig-strategy.go:66-76: an absent resource keeps its name and gets ZERO replicas
+ * (so a daemon started without --resource-config advertises no device). */
+void gpa_resource_config_get(const gpa_resource_variant *variants, int n, const char *orig, gpa_resource_variant *out);
+
 /* ---- NVML: link matrix and health events ------------------------------------------------ */
 
 typedef struct gpa_nvml gpa_nvml;

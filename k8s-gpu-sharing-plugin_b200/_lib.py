@@ -140,6 +140,41 @@ def get_additional_xids(s):
     return [int(out[i]) for i in range(n)]
 
 
+class ResourceVariant(C.Structure):
+    _fields_ = [("orig", C.c_char * 64), ("name", C.c_char * 64), ("replicas", C.c_ulonglong), ("auto_replicas", C.c_int)]
+
+
+def parse_resource_config(config):
+    """ref: parseResourceConfig, cmd/nvidia-device-plugin/main.go:171-203.
+    -> {orig: {"name", "replicas", "auto_replicas"}} in first-seen order; raises ValueError with the reference's text"""
+    L = lib()
+    L.gpa_parse_resource_config.argtypes = [C.c_char_p, C.POINTER(ResourceVariant), C.c_int, C.POINTER(C.c_int), C.c_char_p, C.c_int]
+    out = (ResourceVariant * 64)()
+    n = C.c_int(0)
+    err = C.create_string_buffer(256)
+    rc = L.gpa_parse_resource_config(config.encode() if isinstance(config, str) else config, out, 64, C.byref(n), err, len(err))
+    if rc == ERR_INVALID and err.value:
+        raise ValueError(err.value.decode())
+    if rc != OK:
+        raise GpaError(rc)
+    return {out[i].orig.decode(): {"name": out[i].name.decode(), "replicas": int(out[i].replicas),
+                                   "auto_replicas": bool(out[i].auto_replicas)} for i in range(n.value)}
+
+
+def resource_config_get(variants, orig):
+    """ref: resourceConfiguration.Get, mig-strategy.go:66-76 (absent => same name, ZERO replicas)"""
+    L = lib()
+    L.gpa_resource_config_get.restype = None
+    L.gpa_resource_config_get.argtypes = [C.POINTER(ResourceVariant), C.c_int, C.c_char_p, C.POINTER(ResourceVariant)]
+    arr = (ResourceVariant * max(len(variants), 1))()
+    for i, (k, v) in enumerate(variants.items()):
+        arr[i].orig, arr[i].name = k.encode(), v["name"].encode()
+        arr[i].replicas, arr[i].auto_replicas = v["replicas"], int(v["auto_replicas"])
+    out = ResourceVariant()
+    L.gpa_resource_config_get(arr, len(variants), orig.encode(), C.byref(out))
+    return {"name": out.name.decode(), "replicas": int(out.replicas), "auto_replicas": bool(out.auto_replicas)}
+
+
 def link_type_score(t):
     return int(lib().gpa_link_type_score(int(t)))
 

@@ -59,6 +59,38 @@ struct Group {
 
 }  // namespace
 
+namespace {
+
+// strings.TrimSpace: ASCII white space plus the two Latin-1 spaces U+0085 / U+00A0 (as UTF-8)
+std::string_view go_trim_space(std::string_view v) {
+  for (;;) {
+    if (v.empty()) return v;
+    const unsigned char c = (unsigned char)v[0];
+    if (c == ' ' || (c >= '\t' && c <= '\r')) {
+      v.remove_prefix(1);
+    } else if (c == 0xC2 && v.size() >= 2 && ((unsigned char)v[1] == 0x85 || (unsigned char)v[1] == 0xA0)) {
+      v.remove_prefix(2);
+    } else {
+      break;
+    }
+  }
+  for (;;) {
+    if (v.empty()) return v;
+    const unsigned char c = (unsigned char)v.back();
+    if (c == ' ' || (c >= '\t' && c <= '\r')) {
+      v.remove_suffix(1);
+    } else if ((c == 0x85 || c == 0xA0) && v.size() >= 2 && (unsigned char)v[v.size() - 2] == 0xC2) {
+      v.remove_suffix(2);
+    } else {
+      break;
+    }
+  }
+  return v;
+}
+
+}  // namespace
+
+
 extern "C" {
 
 int gpa_strip_replicas(const char *const *ids, int n, char *outbuf, int outbuf_len, int *n_out) {
@@ -182,32 +214,12 @@ int gpa_get_additional_xids(const char *input, uint64_t *out, int out_cap) {
   if (!input || (!out && out_cap > 0)) return GPA_ERR_INVALID;
   std::string_view s = input;
   if (s.empty()) return 0;  // nvidia.go:275-277
-  auto is_space = [](std::string_view v, size_t i, bool from_end, size_t *w) {
-    // strings.TrimSpace: ASCII white space plus the two Latin-1 spaces U+0085 / U+00A0
-    unsigned char c = (unsigned char)v[i];
-    *w = 1;
-    if (c == ' ' || (c >= '\t' && c <= '\r')) return true;
-    if (!from_end && c == 0xC2 && i + 1 < v.size()) {
-      unsigned char d = (unsigned char)v[i + 1];
-      if (d == 0x85 || d == 0xA0) {
-        *w = 2;
-        return true;
-      }
-    }
-    if (from_end && (c == 0x85 || c == 0xA0) && i >= 1 && (unsigned char)v[i - 1] == 0xC2) {
-      *w = 2;
-      return true;
-    }
-    return false;
-  };
   int n = 0;
   size_t pos = 0;
   for (;;) {
     size_t comma = s.find(',', pos);
     std::string_view tok = s.substr(pos, comma == std::string_view::npos ? std::string_view::npos : comma - pos);
-    size_t w;
-    while (!tok.empty() && is_space(tok, 0, false, &w)) tok.remove_prefix(w);
-    while (!tok.empty() && is_space(tok, tok.size() - 1, true, &w)) tok.remove_suffix(w);
+    tok = go_trim_space(tok);
     if (!tok.empty()) {
       // strconv.ParseUint(tok, 10, 64): decimal digits only, no sign, no underscore, <= 2^64-1
       bool ok = true;
@@ -233,6 +245,87 @@ int gpa_get_additional_xids(const char *input, uint64_t *out, int out_cap) {
     pos = comma + 1;
   }
   return n;
+}
+
+// parseResourceConfig, cmd/nvidia-device-plugin/main.go:171-203
+int gpa_parse_resource_config(const char *config, gpa_resource_variant *out, int cap, int *n_out, char *errbuf, int errbuf_len) {
+  if (!config || !n_out || cap < 0 || (cap > 0 && !out)) return GPA_ERR_INVALID;
+  *n_out = 0;
+  auto fail = [&](const char *msg) {
+    if (errbuf && errbuf_len > 0) snprintf(errbuf, (size_t)errbuf_len, "%s", msg);
+    return GPA_ERR_INVALID;
+  };
+  if (errbuf && errbuf_len > 0) errbuf[0] = 0;
+  std::string_view s = config;
+  int n = 0;
+  size_t pos = 0;
+  for (;;) {
+    const size_t comma = s.find(',', pos);
+    std::string_view entry = go_trim_space(s.substr(pos, comma == std::string_view::npos ? std::string_view::npos : comma - pos));  // :175
+    if (!entry.empty()) {                                                                                                          // :176-178
+      std::string_view parts[3];
+      int np = 0;
+      size_t q = 0;
+      for (;;) {  // strings.Split(entry, ":")
+        const size_t colon = entry.find(':', q);
+        if (np < 3) parts[np] = entry.substr(q, colon == std::string_view::npos ? std::string_view::npos : colon - q);
+        np++;
+        if (colon == std::string_view::npos) break;
+        q = colon + 1;
+      }
+      if (np != 3) return fail("an entry must have three parts separated by a semicolon");  // :180-182
+      // strconv.ParseInt(parts[2], 10, 32): optional sign, decimal digits only, range of int32   (:185-188)
+      std::string_view num = parts[2];
+      bool neg = false;
+      if (!num.empty() && (num[0] == '+' || num[0] == '-')) {
+        neg = num[0] == '-';
+        num.remove_prefix(1);
+      }
+      if (num.empty()) return fail("replica must be an integer");
+      long long v = 0;
+      for (char ch : num) {
+        if (ch < '0' || ch > '9') return fail("replica must be an integer");
+        v = v * 10 + (ch - '0');
+        if (v > 2147483648ll) return fail("replica must be an integer");  // out of range is an error too
+      }
+      if (neg) v = -v;
+      if (v > 2147483647ll) return fail("replica must be an integer");
+      gpa_resource_variant var;
+      memset(&var, 0, sizeof var);
+      if (parts[0].size() >= sizeof var.orig || parts[1].size() >= sizeof var.name) return GPA_ERR_BUFFER;
+      memcpy(var.orig, parts[0].data(), parts[0].size());
+      memcpy(var.name, parts[1].data(), parts[1].size());
+      var.auto_replicas = v == -1;            // :189-193
+      if (v == -1) v = 1;
+      var.replicas = (unsigned long long)v;   // uint(replicas): a negative count wraps, as in Go
+      int slot = -1;
+      for (int i = 0; i < n; i++)
+        if (strcmp(out[i].orig, var.orig) == 0) slot = i;  // the map keeps one variant per origName (:195)
+      if (slot < 0) {
+        if (n >= cap) return GPA_ERR_BUFFER;
+        slot = n++;
+      }
+      out[slot] = var;
+    }
+    if (comma == std::string_view::npos) break;
+    pos = comma + 1;
+  }
+  *n_out = n;
+  return GPA_OK;
+}
+
+// resourceConfiguration.Get, mig-strategy.go:66-76
+void gpa_resource_config_get(const gpa_resource_variant *variants, int n, const char *orig, gpa_resource_variant *out) {
+  if (!out) return;
+  memset(out, 0, sizeof *out);
+  if (!orig) return;
+  for (int i = 0; i < n && variants; i++)
+    if (strcmp(variants[i].orig, orig) == 0) {
+      *out = variants[i];
+      return;
+    }
+  snprintf(out->orig, sizeof out->orig, "%s", orig);
+  snprintf(out->name, sizeof out->name, "%s", orig);
 }
 
 }  // extern "C"

@@ -176,3 +176,43 @@ def check_health_events(device_ids, events, disable_env=""):
             continue
         out += [i for i, d in enumerate(device_ids) if d == uuid]
     return out
+
+
+def _go_parse_int32(s):
+    """strconv.ParseInt(s, 10, 32): optional sign, decimal digits, int32 range; anything else is an error"""
+    body = s[1:] if s[:1] in ("+", "-") else s
+    if not body or any(c not in "0123456789" for c in body):
+        raise ValueError
+    v = int(body) * (-1 if s[:1] == "-" else 1)
+    if not -(1 << 31) <= v < (1 << 31):
+        raise ValueError
+    return v
+
+
+_GO_SPACE = " \t\n\v\f\r\x85\xa0"
+
+
+def parse_resource_config(config):
+    """parseResourceConfig, cmd/main.go:171-203 -> {origName: (newName, replicas, autoReplicas)} or raises ValueError(text)"""
+    out = {}
+    for entry in config.split(","):          # :174
+        entry = entry.strip(_GO_SPACE)        # :175
+        if len(entry) == 0:                   # :176-178
+            continue
+        parts = entry.split(":")              # :179
+        if len(parts) != 3:                   # :180-182
+            raise ValueError("an entry must have three parts separated by a semicolon")
+        try:
+            replicas = _go_parse_int32(parts[2])  # :185
+        except ValueError:
+            raise ValueError("replica must be an integer") from None
+        auto = False
+        if replicas == -1:                    # :189-193
+            auto, replicas = True, 1
+        out[parts[0]] = (parts[1], replicas % (1 << 64), auto)   # uint(replicas), :195-199
+    return out
+
+
+def resource_config_get(cfg, name):
+    """resourceConfiguration.Get, cmd/mig-strategy.go:66-76"""
+    return cfg.get(name, (name, 0, False))

@@ -21,3 +21,20 @@ def oracle():
     from oracle import oracle as orc
     orc.build()
     return orc
+
+
+@pytest.fixture(scope="session")
+def fake_nvml():
+    """tests/csrc/fake_nvml.c built and loaded (a scriptable stand-in for libnvidia-ml.so.1) -> (ctypes handle, path)"""
+    import ctypes as C
+    import subprocess
+    entry.build_native()
+    here = os.path.dirname(os.path.abspath(__file__))
+    src = os.path.join(here, "csrc", "fake_nvml.c")
+    so = os.path.join(here, "csrc", "libfake-nvidia-ml.so.1")
+    if not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["gcc", "-O1", "-fPIC", "-shared", "-I/usr/local/cuda/include", "-o", so, src, "-lpthread"])
+    F = C.CDLL(so, mode=C.RTLD_GLOBAL)
+    F.fake_nvml_inject.argtypes = [C.c_int, C.c_ulonglong, C.c_ulonglong]
+    F.fake_nvml_set_device.argtypes = [C.c_int, C.c_char_p, C.c_char_p]
+    return F, so
