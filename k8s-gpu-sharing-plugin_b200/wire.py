@@ -5,9 +5,8 @@ code (vendor/k8s.io/kubelet/pkg/apis/deviceplugin/v1beta1/api.proto:50-76, api.p
 drop-in claim of this repository is about what travels on that wire, so this module rebuilds
 the message types at run time from a FileDescriptorProto with the SAME package, message
 names, field names and field numbers (there is no protoc in the image), and serves the four
-RPCs of the path from a `_lib.Plugin` (C++ behind the C ABI).  It is plumbing for wire-level
-tests, not the product: lifecycle, registration and restart logic of cmd/main.go stay out of
-scope.
+RPCs of the path from a `_lib.Plugin` (C++ behind the C ABI).  Registration with kubelet and
+the restart loop of cmd/main.go are in lifecycle.py.
 
 Errors: the reference returns plain `fmt.Errorf` values, which grpc-go maps to status
 UNKNOWN with the message text (server.go:276,281,303,321,330); this shim does the same.

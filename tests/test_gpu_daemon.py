@@ -4,6 +4,7 @@ GetPreferredAllocation over the unix socket answered by the CUDA policy (replica
 import os
 import tempfile
 
+import grpc
 import numpy as np
 import pytest
 
@@ -53,16 +54,20 @@ def test_daemon_with_real_nvml_and_cuda_policy(config, fixes):
                 for _ in range(50):
                     avail = [str(x) for x in rng.permutation(ids)[: int(rng.integers(1, len(ids) + 1))]]
                     size = int(rng.integers(1, min(len(avail), 4) + 1))
-                    got = preferred(c, avail, [], size)
                     if reps == 1:   # server.go:297-301: bare UUIDs of Policy.Allocate over the sorted physical ids
                         phys = sorted(x.split("-replica-")[0] for x in avail)
                         rc, want = orc.besteffort(W, nl, [index_of[u] for u in phys], [], size)
                         by_index = {v: k for k, v in index_of.items()}
-                        assert rc == 0 and got == [by_index[i] for i in want]
-                    else:           # GPA_OPT_REPLICA_TOPOLOGY: the replica-set search over the sorted ids
-                        srt = sorted(avail)
-                        rc, pos = orc.subset_besteffort(W, nl, [index_of[x.split("-replica-")[0]] for x in srt], [], size)
-                        assert rc == 0 and got == [srt[p] for p in pos]
+                        if orc.NIL in want:   # the Go handler dereferences nil; the RPC fails
+                            with pytest.raises(grpc.RpcError):
+                                preferred(c, avail, [], size)
+                            continue
+                        assert rc == 0 and preferred(c, avail, [], size) == [by_index[i] for i in want]
+                        continue
+                    got = preferred(c, avail, [], size)
+                    srt = sorted(avail)     # GPA_OPT_REPLICA_TOPOLOGY: the replica-set search over the sorted ids
+                    rc, pos = orc.subset_besteffort(W, nl, [index_of[x.split("-replica-")[0]] for x in srt], [], size)
+                    assert rc == 0 and got == [srt[p] for p in pos]
                 areq = wire.MSG["AllocateRequest"]()
                 areq.container_requests.add().devicesIDs.extend(ids[:1])
                 envs = dict(c.Allocate(areq).container_responses[0].envs)
