@@ -170,3 +170,30 @@ def test_large_requests_beyond_the_literal_form(harness):
                 s = sum(int(W[free[x], free[y]]) for i, x in enumerate(alt) for y in alt[i + 1:] if free[x] != free[y])
                 assert s <= score
     assert len(free) >= 70 and run(harness, W, nl, free, [], 70)[0] == ERR_TOO_LARGE   # more than 64 beyond the required
+
+
+def test_fuzz_small_requests_any_order_any_weights(harness):
+    """hypothesis: tiny requests with arbitrary (also asymmetric-valued) weights, any position order, any required set;
+    both forms where they apply must equal the literal oracle"""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=300, deadline=None)
+    @given(st.integers(2, 5), st.integers(0, 2**32 - 1), st.lists(st.integers(0, 4), min_size=1, max_size=9),
+           st.integers(1, 5), st.integers(0, 3), st.booleans())
+    def check(n_gpus, seed, phys, size, n_req, sort_positions):
+        rng = np.random.default_rng(seed)
+        W = rng.integers(0, 40, size=(n_gpus, n_gpus)).astype(np.int32) * 10     # W[i][j] != W[j][i] is allowed (:314)
+        np.fill_diagonal(W, 0)
+        nl = np.ones((n_gpus, n_gpus), np.uint8) - np.eye(n_gpus, dtype=np.uint8)
+        phys = [p % n_gpus for p in phys]
+        if sort_positions:
+            phys.sort()
+        req = [int(x) for x in rng.choice(len(phys), size=min(n_req, len(phys)), replace=False)]
+        want = orc.subset_besteffort(W, nl, phys, req, size, True)
+        for mode in (0, FORCE_ENUM):
+            rc, pos, form, total, score = run(harness, W, nl, phys, req, size, mode, chunk=int(rng.integers(1, 9)))
+            assert (rc, pos) == want[:2], (W.tolist(), phys, req, size, mode)
+            if form:
+                assert score == want[2]
+
+    check()
