@@ -173,7 +173,7 @@ __global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_kernel(cons
 constexpr int kFastMaxTopo = 12;
 constexpr int kTile = 4096;
 constexpr int kFastThreads = 256;
-constexpr int kShapeBins = 13 * 13 + 7;  // n*13 + k for n,k <= 12, padded to 176
+constexpr int kShapeBins = 176;  // 2 x (shape bin of c_shape_bin, 66 shapes with 2 <= k <= n <= 12) + (has required devices)
 
 // Partition lists for small nodes.  Which partitions iterate() visits, and in which order, depends only on the
 // availability mask and the size, not on the weights; for a node of up to 8 GPUs all of them (6 289 for 8 GPUs) fit a
@@ -186,6 +186,7 @@ struct FastTopo {
   const uint16_t *s_full;  // [1 << nt] scaled set scores over label masks
   const uint32_t *part_words;  // partition words, grouped by (mask, size); nullptr: no table (more than 8 GPUs)
   const uint32_t *part_index;  // [256 * 9]: offset | count << 16 of the group of (mask, size)
+  const uint32_t *part_key;    // per partition word: its score under the installed weights << 16 | (0xFFFF - index in its group)
   int nt;
   uint8_t order[16];  // label -> NVML index
   uint8_t rank[GPA_MAX_TOPOLOGY];  // NVML index -> label, 0xFF = not on this node
@@ -223,28 +224,35 @@ __device__ __forceinline__ int fast_table_search(const Geom &g, const FastTopo &
   const uint32_t entry = __ldg(ft.part_index + g.real_mask * 9 + g.k);
   const uint32_t *w = ft.part_words + (entry & 0xFFFFu);
   const int count = (int)(entry >> 16);
+  const uint32_t *pk = ft.part_key + (entry & 0xFFFFu);
   const uint32_t rl = g.rmask;
-  int best = -1;
-  uint32_t best_word = 0;
-  uint32_t next_word = count > 0 ? __ldg(w) : 0u;
-  for (int i = 0; i < count; i++) {
-    const uint32_t word = next_word;
-    if (i + 1 < count) next_word = __ldg(w + i + 1);  // the next word is in flight while this one is scored
-    const uint32_t s0 = word & 0xFFu, s1 = (word >> 8) & 0xFFu, s2 = (word >> 16) & 0xFFu, s3 = word >> 24;
-    const int sc = (int)S[s0] + (int)S[s1] + (int)S[s2] + (int)S[s3];  // S[0] == 0 for the unused bytes
-    bool ok = true;
-    if (rl != 0) {
-      // :53 / :112-119 — some set holds every required device and is not the padded one
-      ok = ((s0 & rl) == rl && __popc(s0) == g.k) || ((s1 & rl) == rl && __popc(s1) == g.k) ||
-           ((s2 & rl) == rl && __popc(s2) == g.k) || ((s3 & rl) == rl && __popc(s3) == g.k);
+  // A partition's score depends on the node's weights only, so it is tabulated with them (like S), packed with the
+  // partition's place in its group: key = score << 16 | (0xFFFF - index).  The first best partition in visiting order
+  // (strict `>`, :57) is then simply the LARGEST key among the partitions the `required` filter lets through.
+  // Requests with and without required devices sit in different bins, so a warp takes one branch.
+  uint32_t best = 0;
+  if (rl == 0) {
+    int i = 0;
+    for (; i < count && ((reinterpret_cast<uintptr_t>(pk + i) & 15u) != 0); i++) best = max(best, __ldg(pk + i));
+    for (; i + 4 <= count; i += 4) {
+      const uint4 q = __ldg(reinterpret_cast<const uint4 *>(pk + i));
+      best = max(best, max(max(q.x, q.y), max(q.z, q.w)));
     }
-    if (ok && sc > best) {  // strict `>`: first best partition in visiting order (:57)
-      best = sc;
-      best_word = word;
+    for (; i < count; i++) best = max(best, __ldg(pk + i));
+  } else {
+    for (int i = 0; i < count; i++) {
+      const uint32_t word = __ldg(w + i);
+      const uint32_t key = __ldg(pk + i);
+      const uint32_t s0 = word & 0xFFu, s1 = (word >> 8) & 0xFFu, s2 = (word >> 16) & 0xFFu, s3 = word >> 24;
+      // :53 / :112-119 — some set holds every required device and is not the padded one
+      const bool ok = ((s0 & rl) == rl && __popc(s0) == g.k) || ((s1 & rl) == rl && __popc(s1) == g.k) ||
+                      ((s2 & rl) == rl && __popc(s2) == g.k) || ((s3 & rl) == rl && __popc(s3) == g.k);
+      if (ok) best = max(best, key);
     }
   }
   best_set = 0;
-  if (best < 0) return 0;
+  if (best == 0) return 0;  // no accepted partition (a key is never 0: index < 0xFFFF)
+  const uint32_t best_word = __ldg(w + (0xFFFFu - (best & 0xFFFFu)));
   uint32_t sets[kMaxSuffix];
 #pragma unroll
   for (int j = 0; j < kMaxSuffix; j++) {
@@ -401,7 +409,7 @@ __global__ void __launch_bounds__(kFastThreads) besteffort_batch_fast_kernel(con
               search = true;
               w_mr[i] = mask | (rlab_in << 16);
               w_k[i] = (uint8_t)size;
-              bin = c_shape_bin[n][size];
+              bin = 2 * c_shape_bin[n][size] + (rlab_in != 0);
               w_rank[i] = (uint16_t)atomicAdd(&hist[bin], 1u);
             }
           }
@@ -452,7 +460,7 @@ __global__ void __launch_bounds__(kFastThreads) besteffort_batch_fast_kernel(con
               search = true;
               w_mr[i] = (mask & 0xFFFFu) | (rlab << 16);
               w_k[i] = (uint8_t)size;
-              bin = c_shape_bin[n][size];
+              bin = 2 * c_shape_bin[n][size] + (rlab != 0);
               w_rank[i] = (uint16_t)atomicAdd(&hist[bin], 1u);
             }
           }

@@ -93,6 +93,8 @@ struct gpa_ctx {
   uint16_t *d_sfull = nullptr;  // fast batch path: set scores over label masks, nullptr = path unavailable
   uint32_t *d_part_words = nullptr;  // partition table of the fast batch path (nodes of up to 8 GPUs)
   uint32_t *d_part_index = nullptr;
+  uint32_t *d_part_key = nullptr;  // per partition word: score under the installed weights << 16 | (0xFFFF - index in group)
+  std::vector<uint32_t> h_part_words, h_part_index;
   uint64_t *d_sub_binom = nullptr;   // C(n, j) table of the literal replica-set kernel, built on first use
   std::vector<uint64_t> sub_binom;
   SubsetPlan sub_plan;               // plan of the last gpa_subset_besteffort() (kept for its buffers)
@@ -238,6 +240,8 @@ int ensure_partition_table(gpa_ctx *ctx, int nt) {
   CUDA_TRY(ctx, cudaMalloc(&ctx->d_part_index, index.size() * sizeof(uint32_t)));
   CUDA_TRY(ctx, cudaMemcpy(ctx->d_part_words, words.data(), words.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
   CUDA_TRY(ctx, cudaMemcpy(ctx->d_part_index, index.data(), index.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+  ctx->h_part_words = words;
+  ctx->h_part_index = index;
   ctx->part_table_nt = nt;
   return GPA_OK;
 }
@@ -283,6 +287,25 @@ int rebuild_fast(gpa_ctx *ctx) {
     if (rc != GPA_OK) return rc;
     f.part_words = ctx->d_part_words;
     f.part_index = ctx->d_part_index;
+    // partition keys under these weights: score << 16 | (0xFFFF - index in the (mask, size) group).  The score is the sum
+    // of the set scores of the word's bytes and never exceeds 65 535: the sets of a partition are disjoint, so its pairs
+    // are among the node's 120 at most, which gpa_set_topology bounds.
+    std::vector<uint32_t> pkey(ctx->h_part_words.size(), 0);
+    for (uint32_t mask = 1; mask < (1u << T.n); mask++)
+      for (int k = 2; k <= 8; k++) {
+        const uint32_t e = ctx->h_part_index[mask * 9 + k];
+        const uint32_t off = e & 0xFFFFu, cnt = e >> 16;
+        for (uint32_t i = 0; i < cnt; i++) {
+          const uint32_t wd = ctx->h_part_words[off + i];
+          const uint32_t sc = (uint32_t)sfull[wd & 0xFFu] + sfull[(wd >> 8) & 0xFFu] + sfull[(wd >> 16) & 0xFFu] + sfull[wd >> 24];
+          pkey[off + i] = ((sc > 0xFFFFu ? 0xFFFFu : sc) << 16) | (0xFFFFu - i);
+        }
+      }
+    if (ctx->d_part_key) cudaFree(ctx->d_part_key);
+    ctx->d_part_key = nullptr;
+    CUDA_TRY(ctx, cudaMalloc(&ctx->d_part_key, (pkey.size() + 4) * sizeof(uint32_t)));
+    CUDA_TRY(ctx, cudaMemcpy(ctx->d_part_key, pkey.data(), pkey.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    f.part_key = ctx->d_part_key;
   }
   ctx->fast = f;
   return GPA_OK;
@@ -395,7 +418,7 @@ int gpa_create(int cuda_device, gpa_ctx **out) {
         parts[n][k] = c > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)c;
       }
     CREATE_TRY(cudaMemcpyToSymbol(c_parts, parts, sizeof parts));
-    // bins by descending work; at most 13*13 = 169 shapes < kShapeBins
+    // bins by descending work: the 66 real shapes (2 <= k <= n <= 12) come first, so 2 * bin + 1 < kShapeBins
     std::vector<std::pair<uint32_t, int>> shapes;
     for (int n = 0; n <= 12; n++)
       for (int k = 0; k <= 12; k++) shapes.push_back({parts[n][k], n * 13 + k});
@@ -426,6 +449,7 @@ void gpa_destroy(gpa_ctx *ctx) {
   if (ctx->d_sfull) cudaFree(ctx->d_sfull);
   if (ctx->d_part_words) cudaFree(ctx->d_part_words);
   if (ctx->d_part_index) cudaFree(ctx->d_part_index);
+  if (ctx->d_part_key) cudaFree(ctx->d_part_key);
   if (ctx->d_sub_binom) cudaFree(ctx->d_sub_binom);
   if (ctx->d_sub_reqs) cudaFree(ctx->d_sub_reqs);
   if (ctx->d_sub_out) cudaFree(ctx->d_sub_out);
