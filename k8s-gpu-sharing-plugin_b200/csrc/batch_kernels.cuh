@@ -234,20 +234,25 @@ __device__ __forceinline__ int fast_table_search(const Geom &g, const FastTopo &
   if (rl == 0) {
     int i = 0;
     for (; i < count && ((reinterpret_cast<uintptr_t>(pk + i) & 15u) != 0); i++) best = max(best, __ldg(pk + i));
+#pragma unroll 2
     for (; i + 4 <= count; i += 4) {
       const uint4 q = __ldg(reinterpret_cast<const uint4 *>(pk + i));
       best = max(best, max(max(q.x, q.y), max(q.z, q.w)));
     }
     for (; i < count; i++) best = max(best, __ldg(pk + i));
   } else {
+    // :53 / :112-119 — some set holds every required device and is not the padded one.  Only the set that holds the
+    // LOWEST required device can do that, and every device is in exactly one byte of the word, so that set is picked out
+    // without a branch: no lane of the warp waits for another one's short-circuit.
+    const uint32_t low4 = (rl & (0u - rl)) * 0x01010101u;
+#pragma unroll 4
     for (int i = 0; i < count; i++) {
       const uint32_t word = __ldg(w + i);
       const uint32_t key = __ldg(pk + i);
-      const uint32_t s0 = word & 0xFFu, s1 = (word >> 8) & 0xFFu, s2 = (word >> 16) & 0xFFu, s3 = word >> 24;
-      // :53 / :112-119 — some set holds every required device and is not the padded one
-      const bool ok = ((s0 & rl) == rl && __popc(s0) == g.k) || ((s1 & rl) == rl && __popc(s1) == g.k) ||
-                      ((s2 & rl) == rl && __popc(s2) == g.k) || ((s3 & rl) == rl && __popc(s3) == g.k);
-      if (ok) best = max(best, key);
+      const int sh = (__ffs(word & low4) - 1) & 24;
+      const uint32_t set = (word >> sh) & 0xFFu;
+      const bool ok = ((set & rl) == rl) & (__popc(set) == g.k);
+      best = max(best, ok ? key : 0u);
     }
   }
   best_set = 0;
@@ -327,9 +332,10 @@ __global__ void __launch_bounds__(32) besteffort_small_kernel(const FastTopo ft,
 }
 
 __device__ __forceinline__ void res_set_byte(unsigned long long &r0, unsigned long long &r1, int i, int v) {
-  unsigned long long b = (unsigned long long)(v & 0xFF);
-  if (i < 8) r0 = (r0 & ~(0xFFull << (8 * i))) | (b << (8 * i));
-  else r1 = (r1 & ~(0xFFull << (8 * (i - 8)))) | (b << (8 * (i - 8)));
+  // every byte starts as GPA_RES_END (0x80) and is written at most once, so a XOR sets it
+  const unsigned long long b = (unsigned long long)((v ^ 0x80) & 0xFF);
+  if (i < 8) r0 ^= b << (8 * i);
+  else r1 ^= b << (8 * (i - 8));
 }
 __device__ __forceinline__ void res_store(gpa_result *dst, unsigned long long r0, unsigned long long r1) {
   uint4 v;
@@ -430,24 +436,35 @@ __global__ void __launch_bounds__(kFastThreads) besteffort_batch_fast_kernel(con
             res_set_byte(r0, r1, 0, kResDefer);
           } else {
             // relabel: device -> rank in the node order; the list must be strictly ascending
-            unsigned long long bytes = (unsigned long long)lo.x | ((unsigned long long)lo.y << 32);
-            const unsigned long long bytes_hi = (unsigned long long)lo.z | ((unsigned long long)lo.w << 32);
             uint32_t mask = 0, rlab = 0;
-            int prev = -1, first_req_dev = -1;
-            const int first_dev = (int)(lo.x & 0xFFu);
+            int prev = -1;
             bool defer = false;
-#pragma unroll 1
-            for (int p = 0; p < n; p++) {
-              const int d = (int)(bytes & 0xFFu);
-              bytes = p == 7 ? bytes_hi : bytes >> 8;
-              const int lab = d < GPA_MAX_TOPOLOGY ? s_rank[d] : 0xFF;
-              defer = defer || lab == 0xFF || lab <= prev;
-              prev = lab;
-              mask |= 1u << (lab & 31);
-              if (rmask >> p & 1u) {
-                rlab |= 1u << (lab & 31);
-                if (first_req_dev < 0) first_req_dev = d;
+            const int first_dev = (int)(lo.x & 0xFFu);
+            // one step per listed device, unrolled and predicated: the lanes of a warp hold requests of every length
+            auto relabel = [&](int p, uint32_t wd) {
+              if (p < n) {
+                const int d = (int)((wd >> (8 * (p & 3))) & 0xFFu);
+                const int lab = d < GPA_MAX_TOPOLOGY ? s_rank[d] : 0xFF;
+                defer = defer | (lab == 0xFF) | (lab <= prev);
+                prev = lab;
+                const uint32_t bit = 1u << (lab & 31);
+                mask |= bit;
+                rlab |= (rmask >> p & 1u) ? bit : 0u;
               }
+            };
+#pragma unroll
+            for (int p = 0; p < 4; p++) relabel(p, lo.x);
+#pragma unroll
+            for (int p = 4; p < 8; p++) relabel(p, lo.y);
+            if (n > 8) {
+#pragma unroll
+              for (int p = 8; p < 12; p++) relabel(p, lo.z);
+            }
+            int first_req_dev = -1;
+            if (rmask != 0) {
+              const int q = __ffs(rmask) - 1;
+              const uint32_t wd = q < 4 ? lo.x : (q < 8 ? lo.y : (q < 12 ? lo.z : lo.w));
+              first_req_dev = (int)((wd >> (8 * (q & 3))) & 0xFFu);
             }
             if (defer) {
               res_set_byte(r0, r1, 0, kResDefer);
