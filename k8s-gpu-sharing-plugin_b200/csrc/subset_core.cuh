@@ -126,66 +126,68 @@ inline void sub_fill_binom(uint64_t *b) {
     }
 }
 
-// Combination number `rank` (lexicographic) of K out of R -> e[0..K).  The combinations whose next pick lies d or more
-// places further on are the LAST C(n - d, k) of the C(n, k) that remain, so the pick follows from a binary search for the
-// largest d with C(n - d, k) >= (combinations from this one to the end): 8 probes per pick instead of a scan.
-template <int K>
-GPA_HD void sub_comb_unrank(const uint64_t *binom, int R, uint64_t rank, int (&e)[K]) {
-  int n = R;     // pool left
-  int base = 0;  // index of the pool's first member
+// prefix scores: ps[t + 1] = score of (required + e[0..t]) for t < N; ge[t] = 16 * group of e[t]
+template <int N>
+GPA_HD void sub_prefix_score(const uint8_t *grp, const uint32_t *wreq, const uint16_t *w, const int *e, int *ge, uint32_t *ps) {
 #pragma unroll
-  for (int i = 0; i < K; i++) {
-    const int k = K - i;
-    const uint64_t to_end = binom[n * kSubBinomCols + k] - rank;
-    int lo = 0, hi = n - k;
+  for (int t = 0; t < N; t++) {
+    const int g = grp[e[t]];
+    uint32_t s = ps[t] + wreq[e[t]];
+#pragma unroll
+    for (int u = 0; u < N; u++)
+      if (u < t) s += w[ge[u] + g];
+    ge[t] = g * kSubGroups;
+    ps[t + 1] = s;
+  }
+}
+
+// Number of work items of the literal walk: the (K-1)-prefixes, i.e. combinations of the first R-1 free positions.
+GPA_HD uint64_t sub_prefix_count(const uint64_t *binom, int R, int K) { return binom[(R - 1) * kSubBinomCols + (K - 1)]; }
+
+// One work item of the literal walk: all combinations that share their first K-1 picks, i.e. a run over the last pick.
+// Prefixes are numbered in COLEXICOGRAPHIC order (by their largest pick first), so neighbouring items - the lanes of a
+// warp - have runs of the same length and step through them together; the reference's visiting order survives in the
+// key, which carries each candidate's LEXICOGRAPHIC rank: C(R,K) - 1 - sum_i C(R-1-e_i, K-i).
+// Returns the larger of `best` and the run's first best candidate (score, earliest rank).
+template <int K>
+GPA_HD unsigned long long sub_walk_prefix(const uint64_t *binom, const uint8_t *grp, const uint32_t *wreq, const uint16_t *w, int R,
+                                          uint32_t base, uint64_t item, unsigned long long best) {
+  int e[K], ge[K];  // [K-1] unused
+  uint32_t ps[K + 1];
+  uint64_t rest = item;
+  uint64_t after = 0;  // sum_i C(R-1-e_i, K-i) over the prefix
+#pragma unroll
+  for (int i = K - 2; i >= 0; i--) {  // colex unrank: the largest c with C(c, i+1) <= rest, binary search
+    int lo = i, hi = R - 2;
     while (lo < hi) {
       const int mid = (lo + hi + 1) >> 1;
-      if (binom[(n - mid) * kSubBinomCols + k] >= to_end)
+      if (binom[mid * kSubBinomCols + i + 1] <= rest)
         lo = mid;
       else
         hi = mid - 1;
     }
-    rank -= binom[n * kSubBinomCols + k] - binom[(n - lo) * kSubBinomCols + k];
-    e[i] = base + lo;
-    base += lo + 1;
-    n -= lo + 1;
+    e[i] = lo;
+    rest -= binom[lo * kSubBinomCols + i + 1];
+    after += binom[(R - 1 - lo) * kSubBinomCols + (K - i)];
   }
-}
-
-// prefix scores: ps[t + 1] = score of (required + e[0..t]); levels < from are kept
-template <int K>
-GPA_HD void sub_comb_rescore(const uint8_t *grp, const uint32_t *wreq, const uint16_t *w, const int (&e)[K],
-                             int (&ge)[K], uint32_t (&ps)[K + 1], int from) {
+  ps[0] = base;
+  sub_prefix_score<K - 1>(grp, wreq, w, e, ge, ps);
+  const int x0 = K > 1 ? e[K > 1 ? K - 2 : 0] + 1 : 0;
+  const uint32_t pb = ps[K - 1];
+  int run_best = -1, run_x = x0;
+  for (int x = x0; x < R; x++) {
+    const int g = grp[x];
+    uint32_t sc = pb + wreq[x];
 #pragma unroll
-  for (int t = 0; t < K; t++) {
-    if (t >= from) {
-      const int g = grp[e[t]];
-      uint32_t s = ps[t] + wreq[e[t]];
-#pragma unroll
-      for (int u = 0; u < K; u++)
-        if (u < t) s += w[ge[u] + g];
-      ge[t] = g * kSubGroups;
-      ps[t + 1] = s;
+    for (int u = 0; u < K - 1; u++) sc += w[ge[u] + g];
+    if ((int)sc > run_best) {  // strict: the first best of the run
+      run_best = (int)sc;
+      run_x = x;
     }
   }
-}
-
-// next combination in lexicographic order; returns the lowest level that changed, or -1 after the last one
-template <int K>
-GPA_HD int sub_comb_next(int R, int (&e)[K]) {
-  int j = K - 1;
-#pragma unroll
-  for (int t = K - 1; t >= 0; t--)
-    if (j == t && e[t] == R - K + t) j = t - 1;
-  if (j < 0) return -1;
-#pragma unroll
-  for (int t = 0; t < K; t++) {
-    if (t == j)
-      e[t]++;
-    else if (t > j && t > 0)
-      e[t] = e[t > 0 ? t - 1 : 0] + 1;
-  }
-  return j;
+  const uint64_t rank = binom[R * kSubBinomCols + K] - 1 - after - (uint64_t)(R - 1 - run_x);
+  const unsigned long long key = pack_key(run_best, rank);
+  return key > best ? key : best;
 }
 
 }  // namespace gpa

@@ -20,8 +20,7 @@ struct SubsetCountsParams {
 
 struct SubsetEnumParams {
   SubsetEnum q;
-  unsigned long long total;  // C(R, K)
-  unsigned int chunk;        // consecutive ranks per thread visit
+  unsigned long long items;  // (K-1)-prefixes = C(R-1, K-1); a thread walks the last pick of one prefix at a time
   int32_t size;
   unsigned int seq;
 };
@@ -101,22 +100,9 @@ __global__ void __launch_bounds__(kSubThreads) subset_enum_kernel(const SubsetEn
   __syncthreads();
   const int R = p.q.R;
   unsigned long long best = 0;
-  const unsigned long long stride = (unsigned long long)gridDim.x * kSubThreads * p.chunk;
-  for (unsigned long long start = ((unsigned long long)blockIdx.x * kSubThreads + tid) * p.chunk; start < p.total; start += stride) {
-    int e[K], ge[K];
-    uint32_t ps[K + 1];
-    sub_comb_unrank<K>(s_binom, R, start, e);
-    ps[0] = p.q.base;
-    sub_comb_rescore<K>(grp, wreq, w, e, ge, ps, 0);
-    const unsigned long long end = start + p.chunk < p.total ? start + p.chunk : p.total;
-    for (unsigned long long rank = start;;) {
-      const unsigned long long key = pack_key((int)ps[K], rank);
-      best = key > best ? key : best;
-      if (++rank >= end) break;
-      const int j = sub_comb_next<K>(R, e);
-      sub_comb_rescore<K>(grp, wreq, w, e, ge, ps, j);
-    }
-  }
+  const unsigned long long stride = (unsigned long long)gridDim.x * kSubThreads;
+  for (unsigned long long item = (unsigned long long)blockIdx.x * kSubThreads + tid; item < p.items; item += stride)
+    best = sub_walk_prefix<K>(s_binom, grp, wreq, w, R, p.q.base, item, best);
   subset_reduce_publish(best, p.size, p.seq, g_scratch, g_ticket, g_res);
 }
 

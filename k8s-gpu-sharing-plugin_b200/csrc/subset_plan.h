@@ -147,7 +147,7 @@ inline bool subset_decode(SubsetPlan &pl, const uint64_t *binom, uint64_t key) {
       }
   } else {
     int v = 0;
-    for (int i = 0; i < pl.K; i++) {  // same walk as sub_comb_unrank
+    for (int i = 0; i < pl.K; i++) {  // lexicographic unrank: the i-th pick is the first v with rank < C(R-1-v, K-1-i)
       for (;; v++) {
         const uint64_t with_v = binom[(size_t)(pl.R - 1 - v) * kSubBinomCols + (pl.K - 1 - i)];
         if (rank < with_v) break;

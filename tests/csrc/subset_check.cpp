@@ -13,23 +13,13 @@ template <int K>
 uint64_t walk_literal(const gpa::SubsetPlan &pl, const uint64_t *binom, unsigned chunk) {
   using namespace gpa;
   uint64_t best = 0;
-  // the kernel's loop: every thread visit unranks the start of its run and steps through it
-  for (uint64_t start = 0; start < pl.total; start += chunk) {
-    int e[K], ge[K];
-    uint32_t ps[K + 1];
-    sub_comb_unrank<K>(binom, pl.qe.R, start, e);
-    ps[0] = pl.qe.base;
-    sub_comb_rescore<K>(pl.qe.grp, pl.qe.wreq, pl.qe.w, e, ge, ps, 0);
-    const uint64_t end = start + chunk < pl.total ? start + chunk : pl.total;
-    for (uint64_t rank = start;;) {
-      const uint64_t key = pack_key((int)ps[K], rank);
-      best = key > best ? key : best;
-      if (++rank >= end) break;
-      const int j = sub_comb_next<K>(pl.qe.R, e);
-      if (j < 0) return 0;  // ran off the end before `total`: the rank arithmetic is wrong
-      sub_comb_rescore<K>(pl.qe.grp, pl.qe.wreq, pl.qe.w, e, ge, ps, j);
-    }
-  }
+  // the kernel's loop: a work item per (K-1)-prefix, taken here in a scrambled order (`chunk` picks the stride) because
+  // the kernel's threads take them in no particular order either
+  const uint64_t items = sub_prefix_count(binom, pl.qe.R, K);
+  const uint64_t step = chunk | 1;
+  for (uint64_t s0 = 0; s0 < step && s0 < items; s0++)
+    for (uint64_t item = s0; item < items; item += step)
+      best = sub_walk_prefix<K>(binom, pl.qe.grp, pl.qe.wreq, pl.qe.w, pl.qe.R, pl.qe.base, item, best);
   return best;
 }
 
