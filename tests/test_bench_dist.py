@@ -55,3 +55,18 @@ def test_reference_arm_prints_one_json_line_on_cpu():
     r = json.loads(out.stdout.strip().splitlines()[-1])
     assert r["impl"] == "reference" and r["unit"] == "decisions/s" and r["value"] > 0
     assert r["cpu_baseline"]["kind"] == "port" and r["e2e"]["h2d_bytes_per_step"] == 0
+
+
+def test_no_collective_after_the_other_ranks_have_left():
+    """bench.py lets every rank but 0 return once the timed arms are done; a barrier or all_reduce after that point would
+    wait for ranks that no longer exist (it did once: every N > 1 run hung until the NCCL watchdog)."""
+    import ast
+    src = open(os.path.join(ROOT, "bench.py")).read()
+    tree = ast.parse(src)
+    fn = [n for n in ast.walk(tree) if isinstance(n, ast.FunctionDef) and n.name == "run_ours"][0]
+    leave = [n for n in fn.body if isinstance(n, ast.If) and "rank != 0" in ast.unparse(n.test)]
+    assert len(leave) == 1
+    after = [n for n in fn.body if n.lineno > leave[0].lineno]
+    calls = [ast.unparse(c.func) for n in after for c in ast.walk(n) if isinstance(c, ast.Call)]
+    bad = [c for c in calls if c in ("barrier", "dist.barrier", "dist.all_reduce", "dist.all_gather", "dist.broadcast")]
+    assert not bad, bad
