@@ -173,9 +173,7 @@ __global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_kernel(cons
 constexpr int kFastMaxTopo = 12;
 constexpr int kTile = 4096;
 constexpr int kFastThreads = 256;
-constexpr int kShapeBinsHalf = 88;  // shape bins of c_shape_bin: 66 shapes with 2 <= k <= n <= 12
-constexpr int kShapeBins = 2 * kShapeBinsHalf;  // requests WITH required devices first (they take the longer loop), then the rest;
-                                                // within each half by descending work, so a warp's 32 neighbours share a loop
+constexpr int kShapeBins = 176;  // 2 x (shape bin of c_shape_bin, 66 shapes with 2 <= k <= n <= 12) + (has required devices)
 
 // Partition lists for small nodes.  Which partitions iterate() visits, and in which order, depends only on the
 // availability mask and the size, not on the weights; for a node of up to 8 GPUs all of them (6 289 for 8 GPUs) fit a
@@ -417,7 +415,7 @@ __global__ void __launch_bounds__(kFastThreads) besteffort_batch_fast_kernel(con
               search = true;
               w_mr[i] = mask | (rlab_in << 16);
               w_k[i] = (uint8_t)size;
-              bin = (rlab_in != 0 ? 0 : kShapeBinsHalf) + c_shape_bin[n][size];
+              bin = 2 * c_shape_bin[n][size] + (rlab_in != 0);
               w_rank[i] = (uint16_t)atomicAdd(&hist[bin], 1u);
             }
           }
@@ -479,7 +477,7 @@ __global__ void __launch_bounds__(kFastThreads) besteffort_batch_fast_kernel(con
               search = true;
               w_mr[i] = (mask & 0xFFFFu) | (rlab << 16);
               w_k[i] = (uint8_t)size;
-              bin = (rlab != 0 ? 0 : kShapeBinsHalf) + c_shape_bin[n][size];
+              bin = 2 * c_shape_bin[n][size] + (rlab != 0);
               w_rank[i] = (uint16_t)atomicAdd(&hist[bin], 1u);
             }
           }
