@@ -190,4 +190,104 @@ GPA_HD unsigned long long sub_walk_prefix(const uint64_t *binom, const uint8_t *
   return key > best ? key : best;
 }
 
+// --------------------------------------------------------------------------------------------------------------------
+// count form, depth first (the batch kernel's walk; also driven by the CPU harness)
+//
+// The count vectors are walked one GPU per level, in descending order of the count at every level (= descending
+// lexicographic order of the vectors).  P = score of the levels above, L[h] = sum_{g above} c_g w[g][h]: a step at level g
+// costs G-g-1 additions and a leaf two operations.  f / r: free (clamped to K) and required replicas per GPU;
+// cap[g] = what the GPUs from g on can still absorb.
+
+template <int G, int g>
+struct SubDfs {
+  static GPA_HD void run(const uint8_t *f, const uint8_t *r, const uint16_t *cap, const uint16_t *w, int left, int P,
+                                             int (&L)[G], int (&xs)[G], int &bs, unsigned long long &bp) {
+    const int rg = r[g];
+    const int fg = f[g];
+    const int hi = fg < left ? fg : left;
+    const int rest = left - (int)cap[g + 1];  // what the GPUs below cannot absorb
+    const int lo = rest > 0 ? rest : 0;
+#pragma unroll
+    for (int h = g + 1; h < G; h++) L[h] += (rg + hi) * (int)w[g * kSubGroups + h];
+    for (int x = hi; x >= lo; x--) {
+      xs[g] = x;
+      SubDfs<G, g + 1>::run(f, r, cap, w, left - x, P + (rg + x) * L[g], L, xs, bs, bp);
+#pragma unroll
+      for (int h = g + 1; h < G; h++) L[h] -= (int)w[g * kSubGroups + h];
+    }
+#pragma unroll
+    for (int h = g + 1; h < G; h++) L[h] -= (rg + lo - 1) * (int)w[g * kSubGroups + h];  // back to the caller's L
+  }
+};
+
+template <int G>
+struct SubDfs<G, G - 1> {  // the last GPU takes what is left (the level above made sure it can)
+  static GPA_HD void run(const uint8_t *, const uint8_t *r, const uint16_t *, const uint16_t *, int left, int P,
+                                             int (&L)[G], int (&xs)[G], int &bs, unsigned long long &bp) {
+    const int score = P + ((int)r[G - 1] + left) * L[G - 1];
+    if (score > bs) {  // strict: the first best vector of the walk stays
+      bs = score;
+      xs[G - 1] = left;
+      unsigned long long pk = 0;
+#pragma unroll
+      for (int i = 0; i < G; i++) pk |= (unsigned long long)(unsigned)xs[i] << (4 * i);
+      bp = pk;
+    }
+  }
+};
+
+// exact[p * 16 + s] = ways for prefix GPUs p..D-1 to take exactly s (level D is {1, 0, ...}); one entry of level p
+GPA_HD uint32_t sub_exact_entry(const uint8_t *f, const uint32_t *exact, int p, int s) {
+  uint32_t sum = 0;
+  const int hi = (int)f[p] < s ? (int)f[p] : s;
+  for (int x = 0; x <= hi; x++) sum += exact[(p + 1) * 16 + s - x];
+  return sum;
+}
+
+// One work item = one valid count prefix of the first D GPUs (numbered class by class, most replicas left first; inside
+// a class in descending lexicographic order) and the whole walk below it; merges the item's first best vector into
+// (bs, bp, blex) - ties go to the lexicographically larger prefix, because items do not come in vector order.
+template <int G, int D>
+GPA_HD void sub_batch_item(const uint8_t *f, const uint8_t *r, const uint16_t *cap, const uint16_t *w, const uint32_t *exact, int K,
+                         int s_lo, uint32_t item, int &bs, unsigned long long &bp, uint32_t &blex) {
+  uint32_t rest = item;
+  int sp = s_lo;
+  while (rest >= exact[sp]) rest -= exact[sp++];
+  int xs[G];
+  int todo = sp;
+  uint32_t lex = 0;
+#pragma unroll
+  for (int p = 0; p < D; p++) {  // prefix number `rest` of its class, descending lexicographic order
+    int v = (int)f[p] < todo ? (int)f[p] : todo;
+    while (v > 0) {
+      const uint32_t with_v = exact[(p + 1) * 16 + todo - v];
+      if (rest < with_v) break;
+      rest -= with_v;
+      v--;
+    }
+    xs[p] = v;
+    todo -= v;
+    lex = (lex << 4) | (uint32_t)v;
+  }
+  int L[G];
+#pragma unroll
+  for (int h = 0; h < G; h++) L[h] = 0;
+  int P = 0;
+#pragma unroll
+  for (int p = 0; p < D; p++) {
+    const int c = (int)r[p] + xs[p];
+    P += c * L[p];
+#pragma unroll
+    for (int h = p + 1; h < G; h++) L[h] += c * (int)w[p * kSubGroups + h];
+  }
+  int is = -1;  // this item's first best
+  unsigned long long ip = 0;
+  SubDfs<G, D>::run(f, r, cap, w, K - sp, P, L, xs, is, ip);
+  if (is > bs || (is == bs && lex > blex)) {  // items do not come in vector order: ties go to the larger prefix
+    bs = is;
+    bp = ip;
+    blex = lex;
+  }
+}
+
 }  // namespace gpa

@@ -130,44 +130,6 @@ struct SubsetBatchTopo {
 
 static_assert(sizeof(gpa_subset_request) == 48 && sizeof(gpa_subset_result) == 24, "record layouts of gpualloc.h");
 
-template <int G, int g>
-struct SubDfs {
-  static __device__ __forceinline__ void run(const uint8_t *f, const uint8_t *r, const uint16_t *cap, const uint16_t *w, int left, int P,
-                                             int (&L)[G], int (&xs)[G], int &bs, unsigned long long &bp) {
-    const int rg = r[g];
-    const int fg = f[g];
-    const int hi = fg < left ? fg : left;
-    const int rest = left - (int)cap[g + 1];  // what the GPUs below cannot absorb
-    const int lo = rest > 0 ? rest : 0;
-#pragma unroll
-    for (int h = g + 1; h < G; h++) L[h] += (rg + hi) * (int)w[g * kSubGroups + h];
-    for (int x = hi; x >= lo; x--) {
-      xs[g] = x;
-      SubDfs<G, g + 1>::run(f, r, cap, w, left - x, P + (rg + x) * L[g], L, xs, bs, bp);
-#pragma unroll
-      for (int h = g + 1; h < G; h++) L[h] -= (int)w[g * kSubGroups + h];
-    }
-#pragma unroll
-    for (int h = g + 1; h < G; h++) L[h] -= (rg + lo - 1) * (int)w[g * kSubGroups + h];  // back to the caller's L
-  }
-};
-
-template <int G>
-struct SubDfs<G, G - 1> {  // the last GPU takes what is left (the level above made sure it can)
-  static __device__ __forceinline__ void run(const uint8_t *, const uint8_t *r, const uint16_t *, const uint16_t *, int left, int P,
-                                             int (&L)[G], int (&xs)[G], int &bs, unsigned long long &bp) {
-    const int score = P + ((int)r[G - 1] + left) * L[G - 1];
-    if (score > bs) {  // strict: the first best vector of the walk stays
-      bs = score;
-      xs[G - 1] = left;
-      unsigned long long pk = 0;
-#pragma unroll
-      for (int i = 0; i < G; i++) pk |= (unsigned long long)(unsigned)xs[i] << (4 * i);
-      bp = pk;
-    }
-  }
-};
-
 template <int G>
 __global__ void __launch_bounds__(kSubThreads, G <= 8 ? 3 : 1) subset_batch_kernel(const gpa_subset_request *__restrict__ reqs, int count,
                                                                     const SubsetBatchTopo t, gpa_subset_result *__restrict__ out) {
@@ -265,44 +227,7 @@ __global__ void __launch_bounds__(kSubThreads, G <= 8 ? 3 : 1) subset_batch_kern
       unsigned long long bp = 0;
       uint32_t blex = 0;
       for (uint32_t item = lane; item < n_items; item += 32) {
-        uint32_t rest = item;
-        int sp = s_lo;
-        while (rest >= exact[sp]) rest -= exact[sp++];
-        int xs[G];
-        int todo = sp;
-        uint32_t lex = 0;
-#pragma unroll
-        for (int p = 0; p < kSubPrefix; p++) {  // prefix number `rest` of its class, descending lexicographic order
-          int v = (int)f[p] < todo ? (int)f[p] : todo;
-          while (v > 0) {
-            const uint32_t with_v = exact[(p + 1) * 16 + todo - v];
-            if (rest < with_v) break;
-            rest -= with_v;
-            v--;
-          }
-          xs[p] = v;
-          todo -= v;
-          lex = (lex << 4) | (uint32_t)v;
-        }
-        int L[G];
-#pragma unroll
-        for (int h = 0; h < G; h++) L[h] = 0;
-        int P = 0;
-#pragma unroll
-        for (int p = 0; p < kSubPrefix; p++) {
-          const int c = (int)r[p] + xs[p];
-          P += c * L[p];
-#pragma unroll
-          for (int h = p + 1; h < G; h++) L[h] += c * (int)w[p * kSubGroups + h];
-        }
-        int is = -1;  // this item's first best
-        unsigned long long ip = 0;
-        SubDfs<G, kSubPrefix>::run(f, r, cap, w, K - sp, P, L, xs, is, ip);
-        if (is > bs || (is == bs && lex > blex)) {  // items do not come in vector order: ties go to the larger prefix
-          bs = is;
-          bp = ip;
-          blex = lex;
-        }
+        sub_batch_item<G, kSubPrefix>(f, r, cap, w, exact, K, s_lo, item, bs, bp, blex);
       }
       const unsigned long long mine = bs >= 0 ? ((unsigned long long)(unsigned)(bs + 1) << 32) | blex : 0ull;
       const unsigned long long best = warp_max_u64(mine);

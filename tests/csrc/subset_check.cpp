@@ -73,3 +73,55 @@ extern "C" int subset_check(int n_topo, const uint16_t *wq, const uint8_t *asym,
   *n_out = (int)pl.answer.size();
   return GPA_OK;
 }
+
+// The batch kernel's search for ONE count-form request, lanes emulated one after the other: free / must counts per GPU
+// label (G = 8 or 16 levels), label-space weights w[a * 16 + b] (a < b).  Guards and statuses are the kernel's own
+// (warp-parallel) code and are not restated here: the caller passes searchable requests only (0 < K <= 15 or K == 0 with
+// size == sum(must)).  -> take[16], *score
+template <int G>
+static void batch_search(const uint16_t *w, const uint8_t *free_in, const uint8_t *must, int size, uint8_t *take, int *score) {
+  using namespace gpa;
+  constexpr int D = 4;
+  int n_req = 0;
+  for (int g = 0; g < 16; g++) n_req += must[g];
+  const int K = size - n_req;
+  uint8_t f[16], r[16];
+  uint16_t cap[17];
+  for (int g = 0; g < 16; g++) {
+    f[g] = (uint8_t)(free_in[g] < K ? free_in[g] : K);
+    r[g] = must[g];
+  }
+  cap[16] = 0;
+  for (int g = 15; g >= 0; g--) cap[g] = (uint16_t)(cap[g + 1] + f[g]);
+  uint32_t exact[(D + 1) * 16] = {0};
+  exact[D * 16] = 1;
+  for (int p = D - 1; p >= 0; p--)
+    for (int s = 0; s <= K; s++) exact[p * 16 + s] = sub_exact_entry(f, exact, p, s);
+  const int s_lo = K > (int)cap[D] ? K - (int)cap[D] : 0;
+  uint32_t n_items = 0;
+  for (int sp = s_lo; sp <= K; sp++) n_items += exact[sp];
+  unsigned long long best = 0, best_path = 0;
+  int best_score = -1;
+  for (int lane = 0; lane < 32; lane++) {
+    int bs = -1;
+    unsigned long long bp = 0;
+    uint32_t blex = 0;
+    for (uint32_t item = (uint32_t)lane; item < n_items; item += 32) sub_batch_item<G, D>(f, r, cap, w, exact, K, s_lo, item, bs, bp, blex);
+    const unsigned long long mine = bs >= 0 ? ((unsigned long long)(unsigned)(bs + 1) << 32) | blex : 0ull;
+    if (mine > best) {  // the warp's shuffle max
+      best = mine;
+      best_path = bp;
+      best_score = bs;
+    }
+  }
+  for (int g = 0; g < 16; g++) take[g] = g < G ? (uint8_t)((best_path >> (4 * g)) & 0xF) : 0;
+  *score = best_score;
+}
+
+extern "C" void subset_batch_check(int nt, const uint16_t *w, const uint8_t *free_in, const uint8_t *must, int size, uint8_t *take,
+                                   int *score) {
+  if (nt <= 8)
+    batch_search<8>(w, free_in, must, size, take, score);
+  else
+    batch_search<16>(w, free_in, must, size, take, score);
+}

@@ -197,3 +197,45 @@ def test_fuzz_small_requests_any_order_any_weights(harness):
                 assert score == want[2]
 
     check()
+
+
+def batch_run(L, W, order, rec):
+    """tests/csrc/subset_check.cpp subset_batch_check: the batch kernel's search with its lanes run one after the other"""
+    nt = len(order)
+    w = np.zeros(256, dtype=np.uint16)
+    for a in range(nt):
+        for b in range(a + 1, nt):
+            w[a * 16 + b] = W[order[a], order[b]]
+    free = np.ascontiguousarray(rec["free"], dtype=np.uint8)
+    must = np.ascontiguousarray(rec["must"], dtype=np.uint8)
+    take = np.zeros(16, dtype=np.uint8)
+    score = C.c_int(0)
+    L.subset_batch_check.restype = None
+    L.subset_batch_check(nt, w.ctypes.data_as(C.POINTER(C.c_uint16)), free.ctypes.data_as(C.POINTER(C.c_uint8)),
+                         must.ctypes.data_as(C.POINTER(C.c_uint8)), int(rec["size"]), take.ctypes.data_as(C.POINTER(C.c_uint8)),
+                         C.byref(score))
+    return take.tolist(), score.value
+
+
+@pytest.mark.parametrize("n_gpus,replicas", [(8, 4), (8, 2), (5, 3), (12, 2)])
+def test_batch_walk_matches_the_oracle(harness, n_gpus, replicas):
+    """the depth-first walk of the batch kernel (count prefixes as work items, class-ordered, carried partial scores,
+    merge on (score, larger prefix)) against the literal oracle on the record's expansion to positions"""
+    rng = np.random.default_rng(n_gpus * 10 + replicas)
+    order = [int(x) for x in rng.permutation(n_gpus)]          # label -> NVML index
+    W, nl = syn.links_to_weights(syn.topo_random(n_gpus, 1000 + n_gpus))
+    reqs = syn.random_subset_batch(n_gpus, replicas, 250, seed=n_gpus + replicas, sizes=(1, 2, 3, 4, 5), p_must=0.4)
+    checked = 0
+    for rec in reqs:
+        n_avail = int(rec["free"].sum()) + int(rec["must"].sum())
+        size, n_req = int(rec["size"]), int(rec["must"].sum())
+        if not (0 < size <= n_avail and n_req <= size):
+            continue                                             # guards: the kernel's own code, GPU-tested
+        phys_lab, req = syn.subset_record_to_positions(rec, rng)
+        rc, pos, score, _ = orc.subset_besteffort(W, nl, [order[g] for g in phys_lab], req, size, True)
+        assert rc == 0 and len(pos) == size
+        take, got_score = batch_run(harness, W, order, rec)
+        assert take == syn.positions_to_take(phys_lab, set(req), pos), (rec, order)
+        assert got_score == score
+        checked += 1
+    assert checked > 120
