@@ -3,6 +3,7 @@
 // enumeration core); not compiled on its own.
 #pragma once
 #include "kernels_common.cuh"
+#include "part_table.cuh"
 
 namespace {
 
@@ -180,7 +181,6 @@ constexpr int kShapeBins = 176;  // 2 x (shape bin of c_shape_bin, 66 shapes wit
 // 25 KB table: one 32-bit word per partition, byte j = device mask of its j-th set (a padded set is the one with
 // fewer than k devices).  A lane then scores a partition with one table word and m score lookups instead of
 // stepping through combinations.  Built once per node size on the host with the same stepper (gpualloc.cu).
-constexpr int kPartTableMaxTopo = 8;
 
 struct FastTopo {
   const uint16_t *s_full;  // [1 << nt] scaled set scores over label masks
@@ -218,53 +218,10 @@ __device__ __forceinline__ int fast_tracked_search(const Geom &g, const uint16_t
   return choose_from_partition(g, stab, tr.sets, intended, best_set);
 }
 
-// Table-driven search for nodes of up to 8 GPUs (m <= 4 sets): same result as fast_tracked_search.
+// Table-driven search for nodes of up to 8 GPUs (m <= 4 sets): same result as fast_tracked_search (part_table.cuh).
 __device__ __forceinline__ int fast_table_search(const Geom &g, const FastTopo &ft, const uint16_t *S, bool intended,
                                                  uint32_t &best_set) {
-  const uint32_t entry = __ldg(ft.part_index + g.real_mask * 9 + g.k);
-  const uint32_t *w = ft.part_words + (entry & 0xFFFFu);
-  const int count = (int)(entry >> 16);
-  const uint32_t *pk = ft.part_key + (entry & 0xFFFFu);
-  const uint32_t rl = g.rmask;
-  // A partition's score depends on the node's weights only, so it is tabulated with them (like S), packed with the
-  // partition's place in its group: key = score << 16 | (0xFFFF - index).  The first best partition in visiting order
-  // (strict `>`, :57) is then simply the LARGEST key among the partitions the `required` filter lets through.
-  // Requests with and without required devices sit in different bins, so a warp takes one branch.
-  uint32_t best = 0;
-  if (rl == 0) {
-    int i = 0;
-    for (; i < count && ((reinterpret_cast<uintptr_t>(pk + i) & 15u) != 0); i++) best = max(best, __ldg(pk + i));
-#pragma unroll 2
-    for (; i + 4 <= count; i += 4) {
-      const uint4 q = __ldg(reinterpret_cast<const uint4 *>(pk + i));
-      best = max(best, max(max(q.x, q.y), max(q.z, q.w)));
-    }
-    for (; i < count; i++) best = max(best, __ldg(pk + i));
-  } else {
-    // :53 / :112-119 — some set holds every required device and is not the padded one.  Only the set that holds the
-    // LOWEST required device can do that, and every device is in exactly one byte of the word, so that set is picked out
-    // without a branch: no lane of the warp waits for another one's short-circuit.
-    const uint32_t low4 = (rl & (0u - rl)) * 0x01010101u;
-#pragma unroll 4
-    for (int i = 0; i < count; i++) {
-      const uint32_t word = __ldg(w + i);
-      const uint32_t key = __ldg(pk + i);
-      const int sh = (__ffs(word & low4) - 1) & 24;
-      const uint32_t set = (word >> sh) & 0xFFu;
-      const bool ok = ((set & rl) == rl) & (__popc(set) == g.k);
-      best = max(best, ok ? key : 0u);
-    }
-  }
-  best_set = 0;
-  if (best == 0) return 0;  // no accepted partition (a key is never 0: index < 0xFFFF)
-  const uint32_t best_word = __ldg(w + (0xFFFFu - (best & 0xFFFFu)));
-  uint32_t sets[kMaxSuffix];
-#pragma unroll
-  for (int j = 0; j < kMaxSuffix; j++) {
-    const uint32_t sj = (best_word >> (8 * j)) & 0xFFu;
-    sets[j] = sj | ((j < g.m && __popc(sj) < g.k) ? g.tok_bit : 0u);
-  }
-  return choose_from_partition(g, STab{S}, sets, intended, best_set);
+  return part_table_search(g, ft.part_words, ft.part_index, ft.part_key, STab{S}, intended, best_set);
 }
 
 // ONE small request on a small node, one warp: the partitions of (mask, size) come from the table, lanes stride over

@@ -199,43 +199,15 @@ int launch_batch(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_ava
   return launch_general(ctx, d_reqs, count, max_avail, mode_flags, d_out, stream, 1);
 }
 
-// Every partition iterate() visits for (availability mask, size) on a node of nt <= 8 GPUs, in visiting order, one word
-// each (byte j = device mask of set j); see FastTopo.  Generated with the same stepper the kernels walk with.
-void gen_partitions(const Geom &g, uint32_t rem, int level, uint32_t word, std::vector<uint32_t> &out) {
-  if (level == g.m - 1) {  // base case :245-248 — the remainder is the last set
-    out.push_back(word | ((rem & g.real_mask) << (8 * level)));
-    return;
-  }
-  uint32_t anchor;
-  Stepper st = make_stepper(g, rem, anchor);
-  uint32_t chosen;
-  if (!st.first(chosen)) return;
-  do {
-    const uint32_t set = anchor | chosen;
-    gen_partitions(g, rem & ~set, level + 1, word | ((set & g.real_mask) << (8 * level)), out);
-  } while (st.next(chosen));
-}
-
+// Partition words and index of a node of nt <= 8 GPUs on the device (part_table.cuh); rebuilt only when nt changes.
 int ensure_partition_table(gpa_ctx *ctx, int nt) {
   if (ctx->part_table_nt == nt) return GPA_OK;
   if (ctx->d_part_words) cudaFree(ctx->d_part_words);
   if (ctx->d_part_index) cudaFree(ctx->d_part_index);
   ctx->d_part_words = ctx->d_part_index = nullptr;
   ctx->part_table_nt = 0;
-  std::vector<uint32_t> words;
-  std::vector<uint32_t> index(256 * 9, 0);
-  for (uint32_t mask = 1; mask < (1u << nt); mask++) {
-    const int n = __builtin_popcount(mask);
-    for (int k = 2; k <= n; k++) {
-      const Geom g = make_geom_sparse(mask, k, 0, nt);
-      const size_t off = words.size();
-      gen_partitions(g, g.real_mask | g.tok_bit, 0, 0, words);
-      const size_t cnt = words.size() - off;
-      if (off > 0xFFFF || cnt > 0xFFFF) return GPA_ERR_TOO_LARGE;  // cannot happen for nt <= 8 (6 289 words)
-      index[mask * 9 + k] = (uint32_t)off | ((uint32_t)cnt << 16);
-    }
-  }
-  if (words.empty()) words.push_back(0);
+  std::vector<uint32_t> words, index;
+  if (!build_partition_words(nt, words, index)) return GPA_ERR_TOO_LARGE;  // cannot happen for nt <= 8 (6 289 words)
   CUDA_TRY(ctx, cudaMalloc(&ctx->d_part_words, words.size() * sizeof(uint32_t)));
   CUDA_TRY(ctx, cudaMalloc(&ctx->d_part_index, index.size() * sizeof(uint32_t)));
   CUDA_TRY(ctx, cudaMemcpy(ctx->d_part_words, words.data(), words.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
@@ -290,17 +262,8 @@ int rebuild_fast(gpa_ctx *ctx) {
     // partition keys under these weights: score << 16 | (0xFFFF - index in the (mask, size) group).  The score is the sum
     // of the set scores of the word's bytes and never exceeds 65 535: the sets of a partition are disjoint, so its pairs
     // are among the node's 120 at most, which gpa_set_topology bounds.
-    std::vector<uint32_t> pkey(ctx->h_part_words.size(), 0);
-    for (uint32_t mask = 1; mask < (1u << T.n); mask++)
-      for (int k = 2; k <= 8; k++) {
-        const uint32_t e = ctx->h_part_index[mask * 9 + k];
-        const uint32_t off = e & 0xFFFFu, cnt = e >> 16;
-        for (uint32_t i = 0; i < cnt; i++) {
-          const uint32_t wd = ctx->h_part_words[off + i];
-          const uint32_t sc = (uint32_t)sfull[wd & 0xFFu] + sfull[(wd >> 8) & 0xFFu] + sfull[(wd >> 16) & 0xFFu] + sfull[wd >> 24];
-          pkey[off + i] = ((sc > 0xFFFFu ? 0xFFFFu : sc) << 16) | (0xFFFFu - i);
-        }
-      }
+    std::vector<uint32_t> pkey;
+    build_partition_keys(T.n, ctx->h_part_words, ctx->h_part_index, sfull.data(), pkey);
     if (ctx->d_part_key) cudaFree(ctx->d_part_key);
     ctx->d_part_key = nullptr;
     CUDA_TRY(ctx, cudaMalloc(&ctx->d_part_key, (pkey.size() + 4) * sizeof(uint32_t)));

@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "../../k8s-gpu-sharing-plugin_b200/csrc/gpa_enum.cuh"
+#include "../../k8s-gpu-sharing-plugin_b200/csrc/part_table.cuh"
 
 extern "C" int enum_check_search(int nt, const int32_t *W, const int32_t *avail, int n_avail, uint32_t rmask, int size,
                                  int intended, unsigned long long want_items, int32_t *out, int *n_out,
@@ -180,6 +181,68 @@ extern "C" int enum_check_dp(int nt, const int32_t *W, const int32_t *avail, int
     int o = 0;
     for (int b = 0; b < n; b++)
       if (best_set >> b & 1) out[o++] = avail[b];
+    if (best_set & g.tok_bit)
+      for (int i = 0; i < g.P; i++) out[o++] = -1;
+    *n_out = o;
+  }
+  return 0;
+}
+
+// Partition tables of a small node (part_table.cuh, the fast batch kernel's path on up to 8 GPUs): words, index and keys
+// are built as the library builds them, then ONE request is answered by part_table_search.  `shift` moves the key
+// table to every 16-byte phase so that the aligned-vector body of the key scan and its scalar head / tail are all hit.
+struct EnumTables {
+  int nt = 0;
+  std::vector<uint16_t> S;
+  std::vector<uint32_t> words, index, keys;
+};
+
+extern "C" void *enum_check_tables_new(int nt, const int32_t *W) {
+  using namespace gpa;
+  if (nt < 1 || nt > kPartTableMaxTopo) return nullptr;
+  EnumTables *t = new EnumTables();
+  t->nt = nt;
+  t->S.assign((size_t)1 << nt, 0);
+  for (uint32_t mask = 1; mask < (1u << nt); mask++) {
+    int s = 0;
+    for (int a = 0; a < nt; a++)
+      if (mask >> a & 1)
+        for (int b = a + 1; b < nt; b++)
+          if (mask >> b & 1) s += W[a * nt + b];  // the earlier label's view (:314)
+    t->S[mask] = (uint16_t)s;
+  }
+  if (!build_partition_words(nt, t->words, t->index)) {
+    delete t;
+    return nullptr;
+  }
+  build_partition_keys(nt, t->words, t->index, t->S.data(), t->keys);
+  return t;
+}
+
+extern "C" void enum_check_tables_free(void *p) { delete static_cast<EnumTables *>(p); }
+
+extern "C" int enum_check_tables_words(void *p) { return (int)static_cast<EnumTables *>(p)->words.size(); }
+
+extern "C" int enum_check_table_search(void *p, uint32_t real_mask, uint32_t rmask, int size, int intended, int shift, int32_t *out,
+                                       int *n_out) {
+  using namespace gpa;
+  EnumTables *t = static_cast<EnumTables *>(p);
+  *n_out = 0;
+  Geom g = make_geom_sparse(real_mask, size, rmask, t->nt);
+  if (size < 2 || g.n < size || g.m > kMaxSuffix) return -1;
+  // a copy of the keys at a chosen 16-byte phase
+  std::vector<uint32_t> buf(t->keys.size() + 8);
+  uint32_t *base = buf.data();
+  while ((reinterpret_cast<uintptr_t>(base) & 15u) != 0) base++;
+  base += shift & 3;
+  for (size_t i = 0; i < t->keys.size(); i++) base[i] = t->keys[i];
+  const uint16_t *S = t->S.data();
+  auto Sf = [S](uint32_t mask) { return S[mask]; };
+  uint32_t best_set = 0;
+  if (part_table_search(g, t->words.data(), t->index.data(), base, Sf, intended != 0, best_set) > 0) {
+    int o = 0;
+    for (int b = 0; b < t->nt; b++)
+      if (best_set >> b & 1) out[o++] = b;
     if (best_set & g.tok_bit)
       for (int i = 0; i < g.P; i++) out[o++] = -1;
     *n_out = o;

@@ -15,12 +15,13 @@ from k8s_gpu_sharing_plugin_b200 import synthetic as syn
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "enum_check.cpp")
 HDR = os.path.join(HERE, "..", "k8s-gpu-sharing-plugin_b200", "csrc", "gpa_enum.cuh")
+HDR2 = os.path.join(HERE, "..", "k8s-gpu-sharing-plugin_b200", "csrc", "part_table.cuh")
 SO = os.path.join(HERE, "csrc", "libenum_check.so")
 
 
 @pytest.fixture(scope="module")
 def harness():
-    if not os.path.exists(SO) or os.path.getmtime(SO) < max(os.path.getmtime(SRC), os.path.getmtime(HDR)):
+    if not os.path.exists(SO) or os.path.getmtime(SO) < max(os.path.getmtime(SRC), os.path.getmtime(HDR), os.path.getmtime(HDR2)):
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", SO, SRC])
     L = C.CDLL(SO)
     L.enum_check_search.restype = C.c_int
@@ -244,3 +245,42 @@ def test_subset_dp_handles_ties_spikes_and_pads(harness, oracle):
             for req in ([], [n - 1]):
                 want = oracle.besteffort(W, nl, list(range(n)), req, k, oracle.GO_FAITHFUL, "fast")
                 assert (oracle.OK, run_dp(harness, W, list(range(n)), req, k, False)) == want, (n, k, req)
+
+
+@pytest.mark.parametrize("topo_i", [0, 1, 3, 6, 12])
+def test_partition_tables_match_oracle_exhaustive_n8(harness, oracle, topo_i):
+    """part_table.cuh (the fast batch kernel's path on nodes of up to 8 GPUs): words, index and keys built as the library
+    builds them, every (mask, size, required) answered by part_table_search, at every 16-byte phase of the key table"""
+    harness.enum_check_tables_new.restype = C.c_void_p
+    harness.enum_check_tables_new.argtypes = [C.c_int, C.POINTER(C.c_int32)]
+    harness.enum_check_tables_free.argtypes = [C.c_void_p]
+    harness.enum_check_tables_words.argtypes = [C.c_void_p]
+    harness.enum_check_table_search.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int,
+                                                C.POINTER(C.c_int32), C.POINTER(C.c_int)]
+    name, t = syn.standard_topologies()[topo_i]
+    W, nl = syn.links_to_weights(t)
+    Wc = np.ascontiguousarray(W, dtype=np.int32)
+    tab = harness.enum_check_tables_new(8, Wc.ctypes.data_as(C.POINTER(C.c_int32)))
+    assert tab and harness.enum_check_tables_words(tab) == 6289
+    rng = np.random.default_rng(topo_i)
+    out = np.zeros(64, dtype=np.int32)
+    n_out = C.c_int(0)
+    checked = 0
+    try:
+        for mask in range(1, 256):
+            labels = [b for b in range(8) if mask >> b & 1]
+            for k in range(2, len(labels) + 1):
+                reqs = [[]] + [[d] for d in labels]
+                if k >= 2 and len(labels) >= 2:
+                    reqs.append([int(x) for x in rng.choice(labels, size=2, replace=False)])
+                for req in reqs:
+                    rmask = sum(1 << r for r in req)
+                    for mode in (oracle.GO_FAITHFUL, oracle.INTENDED):
+                        want = oracle.besteffort(W, nl, labels, req, k, mode, "fast")
+                        rc = harness.enum_check_table_search(tab, mask, rmask, k, int(mode == oracle.INTENDED), checked & 3,
+                                                             out.ctypes.data_as(C.POINTER(C.c_int32)), C.byref(n_out))
+                        assert rc == 0 and (oracle.OK, [int(x) for x in out[:n_out.value]]) == want, (name, mask, k, req, mode)
+                        checked += 1
+    finally:
+        harness.enum_check_tables_free(tab)
+    assert checked > 10000
