@@ -47,9 +47,20 @@ int pack_out(const std::vector<std::string_view> &v, char *outbuf, int outbuf_le
 struct Replica {
   std::string_view id;
   std::string_view tail;
+  uint64_t key;  // the tail's bytes after "-replica-", big-endian and zero-padded: u64 order == byte-wise string order
 };
 
+// false when the tail does not have the usual shape ("-replica-" + at most 8 bytes): the group then sorts by string
+bool tail_key(std::string_view tail, uint64_t *key) {
+  if (tail.size() < kJoin.size() || tail.size() > kJoin.size() + 8 || memcmp(tail.data(), kJoin.data(), kJoin.size()) != 0) return false;
+  uint64_t k = 0;
+  for (size_t i = kJoin.size(); i < kJoin.size() + 8; i++) k = (k << 8) | (i < tail.size() ? (unsigned char)tail[i] : 0u);
+  *key = k;
+  return true;
+}
+
 struct Group {
+  bool keyed = true;  // every replica of the group has a packed key
   std::string_view phys;
   std::vector<Replica> names;  // free replicas; [head, names.size()) is the live window
   size_t head = 0;
@@ -139,10 +150,16 @@ int gpa_prioritize_devices(const char *const *avail, int n_avail, const char *co
       g->names.reserve(64);
       if (!index.empty()) index.emplace(phys, groups.size() - 1);
     }
-    g->names.push_back({id, id.substr(phys.size())});
+    Replica rep{id, id.substr(phys.size()), 0};
+    g->keyed = tail_key(rep.tail, &rep.key) && g->keyed;
+    g->names.push_back(rep);
   }
-  for (auto &g : groups)
-    std::sort(g.names.begin(), g.names.end(), [](const Replica &a, const Replica &b) { return a.tail < b.tail; });
+  for (auto &g : groups) {
+    if (g.keyed)
+      std::sort(g.names.begin(), g.names.end(), [](const Replica &a, const Replica &b) { return a.key < b.key; });
+    else
+      std::sort(g.names.begin(), g.names.end(), [](const Replica &a, const Replica &b) { return a.tail < b.tail; });
+  }
 
   // replica.go:121 — make([]string, len(must), allocationSize)
   if (size < 0 || n_must > size) return GPA_ERR_PANIC;

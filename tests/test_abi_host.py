@@ -124,3 +124,21 @@ def test_xids_match_oracle_random(oracle):
     for _ in range(500):
         s = "".join(rng.choice(alphabet, size=int(rng.integers(0, 24))))
         assert gpa.get_additional_xids(s) == oracle.get_additional_xids(s), repr(s)
+
+
+def test_prioritize_devices_with_unusual_replica_tails(oracle):
+    """the groups are sorted by a packed 8-byte key of what follows "-replica-"; tails that do not fit (long, empty,
+    no separator at all, a second separator) must fall back to the byte-wise string order of sort.Strings (replica.go:116)"""
+    rng = np.random.default_rng(77)
+    tails = ["-replica-0", "-replica-1", "-replica-10", "-replica-2", "-replica-", "-replica-123456789", "-replica-12345678",
+             "-replica-a", "-replica-1-replica-2", "", "-replica-01", "-replica-1x", "-replica-\x7f"]
+    gpus = ["GPU-%08d-aaaa-bbbb-cccc-dddddddddddd" % g for g in range(4)]
+    for trial in range(400):
+        ids = []
+        for g in gpus:
+            pick = rng.choice(len(tails), size=int(rng.integers(0, len(tails) + 1)), replace=False)
+            ids += [g + tails[i] for i in pick]
+        ids = [str(x) for x in rng.permutation(ids)]
+        size = int(rng.choice([0, 1, 2, 3, 5, 8]))
+        must = [str(x) for x in rng.choice(ids, size=min(len(ids), int(rng.integers(0, 3))), replace=False)] if ids else []
+        assert gpa.prioritize_devices(ids, must, size) == oracle.prioritize_devices(ids, must, size), (ids, must, size)
