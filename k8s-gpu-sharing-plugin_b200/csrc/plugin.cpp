@@ -283,7 +283,6 @@ int gpa_plugin_get_preferred_allocation(gpa_plugin *p, const char *const *avail,
   if (!p || !n_out || n_avail < 0 || n_must < 0) return GPA_ERR_INVALID;
   *n_out = 0;
   set_err(errbuf, errbuf_len, "");
-  std::vector<char> tmp((size_t)outbuf_len + 64);
 
   // :274 — NewDevicesFrom(stripReplicas(AvailableDeviceIDs)): uuid -> device, unknown uuid is an error
   auto resolve = [&](const char *const *ids, int n, const char *what, std::vector<int> &idx) -> int {
@@ -304,10 +303,33 @@ int gpa_plugin_get_preferred_allocation(gpa_plugin *p, const char *const *avail,
     return GPA_OK;
   };
   std::vector<int> available, required;
-  int rc = resolve(avail, n_avail, "available", available);
-  if (rc != GPA_OK) return rc;
-  rc = resolve(must, n_must, "required", required);  // :279
-  if (rc != GPA_OK) return rc;
+  int rc = GPA_OK;
+  // On the replica branch the two NewDevicesFrom calls (:274, :279) only matter for their error: the devices they return
+  // are not used (:285-296).  So the ids are first checked in place - a node has a handful of GPUs, a scan of their uuids
+  // needs no sort, no copy and no hash - and the sorted walk, which names the FIRST unknown uuid in sort.Strings order as
+  // the reference does, only runs when something is unknown.
+  const bool replica_branch = p->replicas > 1 || p->auto_replicas;
+  auto all_known = [&](const char *const *ids, int n) {
+    for (int i = 0; i < n; i++) {
+      const char *id = ids[i];
+      const char *cut = strstr(id, "-replica-");
+      const size_t len = cut ? (size_t)(cut - id) : strlen(id);
+      bool found = false;
+      for (const Device &d : p->cached)
+        if (d.id.size() == len && memcmp(d.id.data(), id, len) == 0) {
+          found = true;
+          break;
+        }
+      if (!found) return false;
+    }
+    return true;
+  };
+  if (!(replica_branch && p->cached.size() <= 32 && all_known(avail, n_avail) && all_known(must, n_must))) {
+    rc = resolve(avail, n_avail, "available", available);
+    if (rc != GPA_OK) return rc;
+    rc = resolve(must, n_must, "required", required);  // :279
+    if (rc != GPA_OK) return rc;
+  }
 
   if ((p->replicas > 1 || p->auto_replicas) && (p->fixes & GPA_OPT_REPLICA_TOPOLOGY) && p->ctx && p->has_policy)
     return preferred_by_topology(p, avail, n_avail, must, n_must, size, outbuf, outbuf_len, n_out, errbuf, errbuf_len);

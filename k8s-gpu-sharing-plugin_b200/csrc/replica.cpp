@@ -147,7 +147,7 @@ int gpa_prioritize_devices(const char *const *avail, int n_avail, const char *co
       groups.emplace_back();
       g = &groups.back();
       g->phys = phys;
-      g->names.reserve(64);
+      g->names.reserve((size_t)(n_avail < 64 ? n_avail : 64));  // a small request must not pay for a big node
       if (!index.empty()) index.emplace(phys, groups.size() - 1);
     }
     Replica rep{id, id.substr(phys.size()), 0};
