@@ -142,3 +142,28 @@ def test_prioritize_devices_with_unusual_replica_tails(oracle):
         size = int(rng.choice([0, 1, 2, 3, 5, 8]))
         must = [str(x) for x in rng.choice(ids, size=min(len(ids), int(rng.integers(0, 3))), replace=False)] if ids else []
         assert gpa.prioritize_devices(ids, must, size) == oracle.prioritize_devices(ids, must, size), (ids, must, size)
+
+
+def test_product_never_reaches_into_the_oracle():
+    """oracle/ is test infrastructure: nothing in the package imports it, the library does not link it, and no product
+    source names its symbols (ref_*)"""
+    import ast
+    pkg = os.path.join(ROOT, "k8s-gpu-sharing-plugin_b200")
+    for fn in os.listdir(pkg):
+        if fn.endswith(".py"):
+            tree = ast.parse(open(os.path.join(pkg, fn)).read())
+            for node in ast.walk(tree):
+                names = []
+                if isinstance(node, ast.Import):
+                    names = [a.name for a in node.names]
+                elif isinstance(node, ast.ImportFrom):
+                    names = [node.module or ""]
+                assert not any(n.split(".")[0] == "oracle" for n in names), (fn, names)
+    for fn in os.listdir(os.path.join(pkg, "csrc")):
+        if not fn.endswith((".cu", ".cuh", ".cpp", ".h", ".inc")) and fn != "Makefile":
+            continue
+        src = open(os.path.join(pkg, "csrc", fn)).read()
+        assert "liboracle" not in src and not re.search(r"\bref_[a-z_]+\s*\(", src), fn
+    needed = subprocess.run(["readelf", "-d", os.path.join(pkg, "libgpualloc.so")], capture_output=True, text=True).stdout
+    assert "NEEDED" in needed
+    assert "liboracle" not in needed
