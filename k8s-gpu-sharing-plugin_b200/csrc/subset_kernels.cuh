@@ -1,7 +1,11 @@
 // Replica-set search kernels: which `size` of the available shared replicas are best connected (subset_core.cuh has
-// the definition and says why there is no reference counterpart).  ONE request per launch, answered into the mailbox.
-//   subset_counts_kernel   per-GPU count vectors in descending lexicographic order, one rank per thread at a time
-//   subset_enum_kernel<K>  the literal walk over C(R, K) combinations, a run of consecutive ranks per thread
+// the definition and says why there is no reference counterpart).
+//   ONE request per launch, answered into the mailbox:
+//     subset_counts_kernel    per-GPU count vectors in descending lexicographic order, one rank per thread at a time
+//     subset_enum_kernel<K>   the literal walk over C(R, K) combinations: a thread per (K-1)-prefix in colex order, runs
+//                             over the last pick
+//   MANY requests per launch (count-form records in, "take this many more from each GPU" out):
+//     subset_batch_kernel<G>  one warp per request, depth-first walk of the count vectors with carried partial scores
 // Part of the single translation unit gpualloc.cu; not compiled on its own.
 #pragma once
 #include "kernels_common.cuh"
