@@ -16,13 +16,15 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "enum_check.cpp")
 HDR = os.path.join(HERE, "..", "k8s-gpu-sharing-plugin_b200", "csrc", "gpa_enum.cuh")
 HDR2 = os.path.join(HERE, "..", "k8s-gpu-sharing-plugin_b200", "csrc", "part_table.cuh")
-SO = os.path.join(HERE, "csrc", "libenum_check.so")
+# GPA_HARNESS_DIR / GPA_HARNESS_CXXFLAGS: build the harness elsewhere with other flags (tools/sanitize_cpu.sh: ASan + UBSan)
+SO = os.path.join(os.environ.get("GPA_HARNESS_DIR", os.path.join(HERE, "csrc")), "libenum_check.so")
+XFLAGS = os.environ.get("GPA_HARNESS_CXXFLAGS", "-O2").split()
 
 
 @pytest.fixture(scope="module")
 def harness():
     if not os.path.exists(SO) or os.path.getmtime(SO) < max(os.path.getmtime(SRC), os.path.getmtime(HDR), os.path.getmtime(HDR2)):
-        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", SO, SRC])
+        subprocess.check_call(["g++"] + XFLAGS + ["-std=c++17", "-fPIC", "-shared", "-o", SO, SRC])
     L = C.CDLL(SO)
     L.enum_check_search.restype = C.c_int
     L.enum_check_search.argtypes = [C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int, C.c_uint32, C.c_int,

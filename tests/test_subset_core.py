@@ -16,7 +16,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "subset_check.cpp")
 CSRC = os.path.join(HERE, "..", "k8s-gpu-sharing-plugin_b200", "csrc")
 DEPS = [SRC] + [os.path.join(CSRC, f) for f in ("subset_core.cuh", "subset_plan.h", "gpa_enum.cuh")]
-SO = os.path.join(HERE, "csrc", "libsubset_check.so")
+# GPA_HARNESS_DIR / GPA_HARNESS_CXXFLAGS: build the harness elsewhere with other flags (tools/sanitize_cpu.sh: ASan + UBSan)
+SO = os.path.join(os.environ.get("GPA_HARNESS_DIR", os.path.join(HERE, "csrc")), "libsubset_check.so")
+XFLAGS = os.environ.get("GPA_HARNESS_CXXFLAGS", "-O2").split()
 
 FORCE_ENUM = 2
 ERR_INVALID, ERR_ASYMMETRIC, ERR_TOO_LARGE = -1, -4, -5
@@ -25,7 +27,7 @@ ERR_INVALID, ERR_ASYMMETRIC, ERR_TOO_LARGE = -1, -4, -5
 @pytest.fixture(scope="module")
 def harness():
     if not os.path.exists(SO) or os.path.getmtime(SO) < max(os.path.getmtime(d) for d in DEPS):
-        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", SO, SRC])
+        subprocess.check_call(["g++"] + XFLAGS + ["-std=c++17", "-fPIC", "-shared", "-o", SO, SRC])
     L = C.CDLL(SO)
     L.subset_check.restype = C.c_int
     L.subset_check.argtypes = [C.c_int, C.POINTER(C.c_uint16), C.POINTER(C.c_uint8), C.POINTER(C.c_int32), C.c_int,
