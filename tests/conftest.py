@@ -11,6 +11,10 @@ import __graft_entry__ as entry  # noqa: E402
 
 entry.load_package()
 
+if os.environ.get("GPA_TEST_LIB"):  # a differently built libgpualloc.so (tools/sanitize_cpu.sh: ASan + UBSan on the host code)
+    from k8s_gpu_sharing_plugin_b200 import _lib as _gpa_lib
+    _gpa_lib.LIB_PATH = os.environ["GPA_TEST_LIB"]
+
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
