@@ -16,7 +16,7 @@ python -m pytest tests/test_enum_core.py tests/test_subset_core.py -x -q
 # sanitizers, under the host / wire / lifecycle tests (none of them needs a GPU).
 LIBDIR=$(mktemp -d)
 trap 'rm -rf "$DIR" "$LIBDIR"' EXIT
-(cd k8s-gpu-sharing-plugin_b200/csrc && /usr/local/cuda/bin/nvcc -O1 -g -std=c++17 -gencode arch=compute_100a,code=sm_100a \
+(cd k8s-gpu-sharing-plugin_b200/csrc && env -u LD_PRELOAD /usr/local/cuda/bin/nvcc -O1 -g -std=c++17 -gencode arch=compute_100a,code=sm_100a \
   -Xcompiler -fPIC,-fsanitize=address,-fsanitize=undefined,-fno-sanitize-recover=undefined -shared -o "$LIBDIR/libgpualloc.so" \
   gpualloc.cu probes.cu replica.cpp plugin.cpp nvml_host.cpp -lpthread -ldl)
 export GPA_TEST_LIB="$LIBDIR/libgpualloc.so"
