@@ -20,7 +20,6 @@ MIG strategies "single" / "mixed" need MIG enumeration through NVML and are out 
 import os
 import signal
 import threading
-import time
 
 import grpc
 

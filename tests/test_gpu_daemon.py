@@ -1,7 +1,6 @@
 """The daemon end to end on the GPU box: real NVML for devices and the link matrix, a fake kubelet for registration,
 GetPreferredAllocation over the unix socket answered by the CUDA policy (replicas = 1) and by the replica-set search
 (replicas = 4 with --replica-topology), each checked against the oracle on the matrix NVML gave."""
-import os
 import tempfile
 
 import grpc

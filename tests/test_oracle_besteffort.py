@@ -5,7 +5,6 @@ oracle to reference outputs; they check the literal slice-emulating restatement 
 closed forms, against hand-derived vectors, and against the allocation-free variant that
 is used for larger sizes.
 """
-import itertools
 import math
 
 import numpy as np
