@@ -286,3 +286,37 @@ def test_partition_tables_match_oracle_exhaustive_n8(harness, oracle, topo_i):
     finally:
         harness.enum_check_tables_free(tab)
     assert checked > 10000
+
+
+@pytest.mark.parametrize("nt", [2, 3, 5, 6, 7])
+def test_partition_tables_on_smaller_nodes(harness, oracle, nt):
+    """the tables are built per node size: every (mask, size, required) of a node of 2..7 GPUs, asymmetric weights too"""
+    harness.enum_check_tables_new.restype = C.c_void_p
+    harness.enum_check_tables_new.argtypes = [C.c_int, C.POINTER(C.c_int32)]
+    harness.enum_check_tables_free.argtypes = [C.c_void_p]
+    harness.enum_check_table_search.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int,
+                                                C.POINTER(C.c_int32), C.POINTER(C.c_int)]
+    W, nl = syn.links_to_weights(syn.topo_random(nt, 70 + nt))
+    W = W.copy()
+    W[np.triu_indices(nt, 1)] += 10          # the earlier label's view must be the one used (:314)
+    Wc = np.ascontiguousarray(W, dtype=np.int32)
+    tab = harness.enum_check_tables_new(nt, Wc.ctypes.data_as(C.POINTER(C.c_int32)))
+    assert tab
+    out = np.zeros(64, dtype=np.int32)
+    n_out = C.c_int(0)
+    checked = 0
+    try:
+        for mask in range(1, 1 << nt):
+            labels = [b for b in range(nt) if mask >> b & 1]
+            for k in range(2, len(labels) + 1):
+                for req in [[]] + [[d] for d in labels] + ([labels[:2]] if len(labels) >= 2 else []):
+                    rmask = sum(1 << r for r in req)
+                    for mode in (oracle.GO_FAITHFUL, oracle.INTENDED):
+                        want = oracle.besteffort(W, nl, labels, req, k, mode, "fast")
+                        rc = harness.enum_check_table_search(tab, mask, rmask, k, int(mode == oracle.INTENDED), checked & 3,
+                                                             out.ctypes.data_as(C.POINTER(C.c_int32)), C.byref(n_out))
+                        assert rc == 0 and (oracle.OK, [int(x) for x in out[:n_out.value]]) == want, (nt, mask, k, req, mode)
+                        checked += 1
+    finally:
+        harness.enum_check_tables_free(tab)
+    assert checked >= (2 if nt == 2 else 20)
