@@ -315,6 +315,11 @@ def run_ours(args):
         if use_dist:
             dist.destroy_process_group()
         return 0
+    if args.quick:  # profiling runs (ncu): the timed arms only
+        print(json.dumps({"quick": True, "value": value, "ms_per_step": total_ms / args.steps, "kernel_ms": kernel_ms,
+                          "e2e_value": e2e_value, "e2e_ms_per_step": e2e_s / args.steps * 1e3, "mask_format": mask_format,
+                          "mismatches": [mismatches, e2e_mismatch, masks_mismatch], "gpu_launches": int(launches)}))
+        return 0 if mismatches == 0 and e2e_mismatch == 0 and masks_mismatch == 0 else 1
 
     # ---- roofline of the dominant kernel (the batch kernel is the only one in the step) --
     pair_evals = algorithmic_pair_evals(reqs)
@@ -600,6 +605,7 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--quick", action="store_true", help="timed arms only (for profiler runs); prints a short line")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
     if args.impl == "reference":

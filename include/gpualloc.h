@@ -58,6 +58,9 @@ extern "C" {
                                   default: the DP for 15-16 devices or more than 1.5 x 10^5 candidate partitions, else enumeration.
                                   Same answers. */
 
+#define GPA_MODE_FORCE_KERNEL 8 /* gpa_besteffort(): answer with a kernel launch even where the installed answer table
+                                  (nodes of up to 8 GPUs, devices listed in node order) would answer without one */
+
 #define GPA_NIL (-1)     /* a nil *Device in a returned set (ref: SURVEY.md D5) */
 #define GPA_FOREIGN (-2) /* in `required`: a device pointer that is none of the `available` pointers — what the
                             reference's own call site passes (ref: server.go:274,279) */
@@ -106,6 +109,18 @@ int gpa_set_device_order(gpa_ctx *ctx, const int32_t *order, int n);
 /* Reads the installed matrix back (n*n entries each); either pointer may be NULL. */
 int gpa_get_topology(gpa_ctx *ctx, int *n, int32_t *W, uint8_t *nlinks, int cap);
 
+/* The answer table of the installed topology, for nodes of up to 8 GPUs with symmetric link counts: EVERY answer
+ * bestEffortPolicy.Allocate can give on that node, computed by a kernel when gpa_set_topology*() /
+ * gpa_set_device_order() ran, and kept both on the device (the batch kernels answer with one lookup) and on the host
+ * (gpa_besteffort() answers node-ordered requests without a launch).  Entries are indexed
+ *     ((tern[avail_mask] + tern[required_mask]) * 8 + size - 1,  tern[x] = sum of 3^b over the bits b of x
+ * (masks over the order of gpa_set_device_order(), required a subset of available, size 1..8) and hold
+ *     chosen mask | nil pads << 8, 0 = the empty answer.
+ * *n_entries = 8 * 3^n; returns GPA_ERR_TOO_LARGE when the topology has no table, GPA_ERR_BUFFER if cap is short
+ * (table may be NULL to query the size).
+ * ref: bestEffortPolicy.Allocate, gpuallocator/besteffort_policy.go:34-89 - the whole function, tabulated. */
+int gpa_get_answer_table(gpa_ctx *ctx, uint16_t *table, int cap, int *n_entries);
+
 /* ---- best-effort policy ------------------------------------------------------------- */
 
 /* One allocation decision.  avail[0..n_avail): NVML indices in the caller's order (the
@@ -130,8 +145,10 @@ typedef struct gpa_search_stats {
   int grid, block, smem_bytes;   /* launch shape of the search kernel, 0 if no kernel was needed */
   float kernel_ms;               /* device time of the search kernel(s) (CUDA events), 0 if none */
   int algorithm;                 /* 0 answered by the guards, 1 enumeration, 2 subset dynamic programme,
-                                    3 partition table (nodes of up to 8 GPUs, devices listed in node order),
-                                    4 / 5 gpa_subset_besteffort(): count vectors / literal combinations */
+                                    3 partition table, one-warp kernel (GPA_MODE_FORCE_KERNEL on a node of up to 8 GPUs),
+                                    4 / 5 gpa_subset_besteffort(): count vectors / literal combinations,
+                                    6 answer table: built by a kernel when the topology was installed, read on the host
+                                      (nodes of up to 8 GPUs, devices listed in node order; best_score is not kept: -1) */
 } gpa_search_stats;
 int gpa_last_search_stats(gpa_ctx *ctx, gpa_search_stats *out);
 

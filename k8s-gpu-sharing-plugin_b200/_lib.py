@@ -16,7 +16,7 @@ OK = 0
 ERR_INVALID, ERR_CUDA, ERR_NO_TOPOLOGY, ERR_ASYMMETRIC, ERR_TOO_LARGE, ERR_WEIGHT_RANGE, ERR_BUFFER = -1, -2, -3, -4, -5, -6, -7
 ERR_NVML, ERR_PANIC, ERR_NO_DEVICES_LEFT, ERR_MUST_MISSING, ERR_UNKNOWN_DEVICE, ERR_NOT_IMPLEMENTED = -8, -9, -10, -11, -12, -13
 MODE_GO_FAITHFUL, MODE_INTENDED = 0, 1
-MODE_FORCE_ENUM, MODE_FORCE_DP = 2, 4
+MODE_FORCE_ENUM, MODE_FORCE_DP, MODE_FORCE_KERNEL = 2, 4, 8
 NIL, FOREIGN = -1, -2
 RES_END, RES_ERROR = -128, -127
 MAX_AVAILABLE, BATCH_MAX_AVAILABLE = 16, 12
@@ -62,6 +62,8 @@ def lib():
     L.gpa_set_device_order.restype = C.c_int
     L.gpa_set_device_order.argtypes = [vp, i32p, C.c_int]
     L.gpa_get_topology.argtypes = [vp, C.POINTER(C.c_int), i32p, u8p, C.c_int]
+    L.gpa_get_answer_table.restype = C.c_int
+    L.gpa_get_answer_table.argtypes = [vp, C.POINTER(C.c_uint16), C.c_int, C.POINTER(C.c_int)]
     L.gpa_besteffort.argtypes = [vp, i32p, C.c_int, i32p, C.c_int, C.c_int, C.c_int, i32p, C.POINTER(C.c_int)]
     L.gpa_last_search_stats.argtypes = [vp, C.POINTER(SearchStats)]
     L.gpa_subset_batch.argtypes = [vp, vp, C.c_int, vp]
@@ -230,6 +232,17 @@ class Context:
         self._check(lib().gpa_get_topology(self._h, C.byref(n), W.ctypes.data_as(C.POINTER(C.c_int32)),
                                            nl.ctypes.data_as(C.POINTER(C.c_uint8)), n.value * n.value))
         return W, nl
+
+    def answer_table(self):
+        """the GPU-built answer table of the installed topology (nodes of up to 8 GPUs) as a uint16 array, or None"""
+        n = C.c_int(0)
+        rc = lib().gpa_get_answer_table(self._h, None, 0, C.byref(n))
+        if rc == ERR_TOO_LARGE:
+            return None
+        self._check(rc)
+        tab = np.zeros(n.value, dtype=np.uint16)
+        self._check(lib().gpa_get_answer_table(self._h, tab.ctypes.data_as(C.POINTER(C.c_uint16)), n.value, C.byref(n)))
+        return tab
 
     def besteffort(self, avail, req, size, mode=MODE_GO_FAITHFUL):
         """Policy.Allocate(available, required, size) -> (rc, [NVML indices, NIL for a pad])"""

@@ -26,9 +26,13 @@ __device__ __forceinline__ void write_result(gpa_result *out, const int8_t *dev)
 // General batch kernel: any `available` order, per-request score table, one warp per request.
 // With deferred_only it answers just the records the fast kernel marked GPA_RES_DEFER: each
 // warp scans 32 result records at a time (one coalesced load) and works on the marked ones.
+// defer_flags (optional, one byte per 32 records, written by the table kernel) says which
+// groups of 32 hold a marked record at all: a warp then reads 32 flags per load and touches
+// the result records of flagged groups only - 1/512 of the traffic when nothing was deferred.
 __global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_kernel(const gpa_request *__restrict__ reqs, int count,
                                                                             int n_cap, int intended, BatchTopo topo,
-                                                                            gpa_result *out, int deferred_only) {
+                                                                            gpa_result *out, int deferred_only,
+                                                                            const uint8_t *__restrict__ defer_flags) {
   extern __shared__ __align__(16) uint16_t smem[];
   __shared__ BinomTable s_binom;
   stage_binom(s_binom, threadIdx.x, kBatchWarps * 32);
@@ -136,8 +140,7 @@ __global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_kernel(cons
   if (!deferred_only) {
     for (int r = blockIdx.x * kBatchWarps + warp; r < count; r += gridDim.x * kBatchWarps) process(r);
   } else {
-    for (long long base = ((long long)blockIdx.x * kBatchWarps + warp) * 32; base < count;
-         base += (long long)gridDim.x * kBatchWarps * 32) {
+    auto scan_group = [&](long long base) {
       const long long r = base + lane;
       const bool marked = r < count && out[r].dev[0] == kResDefer;
       unsigned todo = __ballot_sync(0xffffffffu, marked);
@@ -146,6 +149,23 @@ __global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_kernel(cons
         todo &= todo - 1;
         process((int)(base + b));
         __syncwarp();
+      }
+    };
+    if (defer_flags == nullptr) {
+      for (long long base = ((long long)blockIdx.x * kBatchWarps + warp) * 32; base < count;
+           base += (long long)gridDim.x * kBatchWarps * 32)
+        scan_group(base);
+    } else {
+      const long long n_groups = ((long long)count + 31) / 32;
+      for (long long g0 = ((long long)blockIdx.x * kBatchWarps + warp) * 32; g0 < n_groups;
+           g0 += (long long)gridDim.x * kBatchWarps * 32) {
+        const long long gi = g0 + lane;
+        unsigned flagged = __ballot_sync(0xffffffffu, gi < n_groups && defer_flags[gi] != 0);
+        while (flagged) {
+          const int gb = __ffs(flagged) - 1;
+          flagged &= flagged - 1;
+          scan_group((g0 + gb) * 32);
+        }
       }
     }
   }
@@ -187,6 +207,8 @@ struct FastTopo {
   const uint32_t *part_words;  // partition words, grouped by (mask, size); nullptr: no table (more than 8 GPUs)
   const uint32_t *part_index;  // [256 * 9]: offset | count << 16 of the group of (mask, size)
   const uint32_t *part_key;    // per partition word: its score under the installed weights << 16 | (0xFFFF - index in its group)
+  const uint16_t *ans;         // answer table (ans_table.cuh), padded to 16 bytes; nullptr: none (more than 8 GPUs)
+  uint32_t ans_entries;
   int nt;
   uint8_t order[16];  // label -> NVML index
   uint8_t rank[GPA_MAX_TOPOLOGY];  // NVML index -> label, 0xFF = not on this node

@@ -12,7 +12,9 @@
 // gpa_enum.cuh:
 //   search_kernel.cuh  besteffort_search_kernel    ONE request, every partition visited, whole machine
 //   dp_kernels.cuh     dp_scores/layer/final       ONE large request by subset dynamic programme (a launch per layer)
-//   batch_kernels.cuh  besteffort_batch_fast_kernel  MANY requests in node order: tile-binned, one lane per request
+//   table_kernels.cuh  answer_table_build_kernel     every answer of a node of up to 8 GPUs, built when a topology is installed
+//                      besteffort_batch_table_kernel MANY requests in node order on such a node: one lookup per request
+//   batch_kernels.cuh  besteffort_batch_fast_kernel  MANY requests in node order, 9-12 GPUs: tile-binned, one lane per request
 //                      besteffort_batch_kernel       MANY requests, any order: one warp per request (also the
 //                                                    "deferred" pass after the fast kernel)
 //   subset_kernels.cuh subset_counts/enum_kernel   ONE request over shared replicas (no reference counterpart)
@@ -36,6 +38,7 @@
 #include "search_kernel.cuh"
 #include "dp_kernels.cuh"
 #include "batch_kernels.cuh"
+#include "table_kernels.cuh"
 #include "subset_kernels.cuh"
 #include "subset_plan.h"
 
@@ -102,6 +105,12 @@ struct gpa_ctx {
   gpa_subset_result *d_sub_out = nullptr;
   size_t sub_batch_cap = 0;
   int part_table_nt = 0;             // node size the table was built for, 0 = none
+  bool table_attr_set[2] = {false, false};
+  uint16_t *d_ans = nullptr;         // answer table of the installed topology (ans_table.cuh), built by a kernel
+  std::vector<uint16_t> h_ans;       // its host copy: gpa_besteffort() answers node-ordered requests from it
+  uint16_t h_tern[256];              // ans_tern() of every 8-bit mask
+  uint8_t *d_defer = nullptr;        // arena of "a record of these 32 was left to the general kernel" bytes
+  size_t defer_head = 0;
   FastTopo fast{};
   // batch staging
   gpa_request *d_reqs = nullptr;
@@ -151,8 +160,25 @@ int ensure_batch_capacity(gpa_ctx *ctx, size_t count, bool host_staging) {
   return GPA_OK;
 }
 
+// Each batch call on the table path takes one byte per 32 records from this arena and keeps it until its two kernels
+// have run.  The arena is a ring: a call's bytes are reused only after kDeferArena bytes' worth of later calls, i.e.
+// calls that are in flight at the same time on different streams stay apart as long as they cover fewer than
+// 32 x kDeferArena = 2^28 records together.  A batch too large for the arena goes without (nullptr): the general
+// kernel then scans every result record for the deferral mark, as it does after the tile-binned kernel.
+constexpr size_t kDeferArena = (size_t)8 << 20;
+
+uint8_t *take_defer_flags(gpa_ctx *ctx, int count) {
+  if (!ctx->d_defer) return nullptr;
+  const size_t need = (((size_t)count + 31) / 32 + 255) & ~(size_t)255;
+  if (need > kDeferArena) return nullptr;
+  if (ctx->defer_head + need > kDeferArena) ctx->defer_head = 0;
+  uint8_t *p = ctx->d_defer + ctx->defer_head;
+  ctx->defer_head += need;
+  return p;
+}
+
 int launch_general(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_avail, int mode_flags, gpa_result *d_out,
-                   cudaStream_t stream, int deferred_only) {
+                   cudaStream_t stream, int deferred_only, const uint8_t *defer_flags = nullptr) {
   int n_cap = max_avail < 2 ? 2 : max_avail;
   if (n_cap > GPA_BATCH_MAX_AVAILABLE) n_cap = GPA_BATCH_MAX_AVAILABLE;
   size_t smem = (size_t)kBatchWarps * (((size_t)1 << n_cap) + kMaxDevices * kMaxDevices) * sizeof(uint16_t);
@@ -161,13 +187,13 @@ int launch_general(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_a
   int occ = 1;
   CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, besteffort_batch_kernel, kBatchWarps * 32, smem));
   if (occ < 1) occ = 1;
-  long long per_block = deferred_only ? (long long)kBatchWarps * 32 : kBatchWarps;
+  long long per_block = deferred_only ? (long long)kBatchWarps * 32 * (defer_flags ? 32 : 1) : kBatchWarps;
   long long want = ((long long)count + per_block - 1) / per_block;
   long long cap = (long long)ctx->sm_count * occ;  // persistent: one wave, warps stride over the requests
   int grid = (int)(want < cap ? want : cap);
   BatchTopo t{ctx->d_wq, ctx->d_asym, ctx->topo.n};
   besteffort_batch_kernel<<<grid, kBatchWarps * 32, smem, stream>>>(d_reqs, count, n_cap, mode_flags & GPA_MODE_INTENDED, t,
-                                                                    d_out, deferred_only);
+                                                                    d_out, deferred_only, defer_flags);
   ctx->launches++;
   CUDA_TRY(ctx, cudaGetLastError());
   return GPA_OK;
@@ -189,14 +215,41 @@ int launch_fast(gpa_ctx *ctx, const void *d_reqs, int count, int mode_flags, voi
   return GPA_OK;
 }
 
+// Nodes of up to 8 GPUs: one lookup in the answer table per request (table_kernels.cuh).  The table holds the same
+// answers for both alias modes (no partition of such a node has the 7 sets the aliasing needs), so mode_flags is unused.
+int launch_table(gpa_ctx *ctx, const void *d_reqs, int count, void *d_out, cudaStream_t stream, bool masks, uint8_t *defer_flags) {
+  auto kern = masks ? besteffort_batch_table_kernel<true> : besteffort_batch_table_kernel<false>;
+  const size_t smem = table_smem_bytes(ctx->fast.ans_entries);
+  if (!ctx->table_attr_set[masks ? 1 : 0]) {
+    CUDA_TRY(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)table_smem_bytes(ans_entries(kAnsMaxTopo))));
+    ctx->table_attr_set[masks ? 1 : 0] = true;
+  }
+  const long long per_block = masks ? 2 * kTabThreads : kTabThreads;
+  long long want = ((long long)count + per_block - 1) / per_block;
+  long long cap = (long long)ctx->sm_count * kTabBlocksPerSm;  // persistent: every CTA stages the table once
+  int grid = (int)(want < cap ? want : cap);
+  kern<<<grid, kTabThreads, smem, stream>>>(d_reqs, count, ctx->fast, d_out, defer_flags);
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return GPA_OK;
+}
+
 int launch_batch(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_avail, int mode_flags, gpa_result *d_out,
                  cudaStream_t stream) {
   if (count == 0) return GPA_OK;
   if (!ctx->d_sfull) return launch_general(ctx, d_reqs, count, max_avail, mode_flags, d_out, stream, 0);
   // canonical-order fast path, then the general kernel mops up whatever was deferred
-  int rc = launch_fast(ctx, d_reqs, count, mode_flags, d_out, stream, false);
+  const bool table = ctx->fast.ans != nullptr && !(mode_flags & GPA_MODE_FORCE_ENUM);
+  uint8_t *flags = table ? take_defer_flags(ctx, count) : nullptr;
+  int rc = table ? launch_table(ctx, d_reqs, count, d_out, stream, false, flags)
+                 : launch_fast(ctx, d_reqs, count, mode_flags, d_out, stream, false);
   if (rc != GPA_OK) return rc;
-  return launch_general(ctx, d_reqs, count, max_avail, mode_flags, d_out, stream, 1);
+  return launch_general(ctx, d_reqs, count, max_avail, mode_flags, d_out, stream, 1, flags);
+}
+
+int launch_masks(gpa_ctx *ctx, const void *d_reqs, int count, int mode_flags, void *d_out, cudaStream_t stream) {
+  if (ctx->fast.ans != nullptr && !(mode_flags & GPA_MODE_FORCE_ENUM)) return launch_table(ctx, d_reqs, count, d_out, stream, true, nullptr);
+  return launch_fast(ctx, d_reqs, count, mode_flags, d_out, stream, true);
 }
 
 // Partition words and index of a node of nt <= 8 GPUs on the device (part_table.cuh); rebuilt only when nt changes.
@@ -227,6 +280,8 @@ int rebuild_fast(gpa_ctx *ctx) {
     cudaFree(ctx->d_sfull);
     ctx->d_sfull = nullptr;
   }
+  ctx->h_ans.clear();  // no table until the new one is built: gpa_besteffort() then asks a kernel
+  ctx->fast.ans = nullptr;
   if (T.n > kFastMaxTopo || T.any_asym) return GPA_OK;
   if ((int)T.order.size() != T.n) {
     T.order.resize(T.n);
@@ -269,6 +324,24 @@ int rebuild_fast(gpa_ctx *ctx) {
     CUDA_TRY(ctx, cudaMalloc(&ctx->d_part_key, (pkey.size() + 4) * sizeof(uint32_t)));
     CUDA_TRY(ctx, cudaMemcpy(ctx->d_part_key, pkey.data(), pkey.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
     f.part_key = ctx->d_part_key;
+    // every answer of this node, by a kernel (ans_table.cuh); the host keeps a copy for single decisions
+    const uint32_t n_ent = ans_entries(T.n);
+    const size_t ans_bytes = ((size_t)n_ent * sizeof(uint16_t) + 15) & ~(size_t)15;
+    if (ctx->d_ans) cudaFree(ctx->d_ans);
+    ctx->d_ans = nullptr;
+    ctx->h_ans.clear();
+    CUDA_TRY(ctx, cudaMalloc(&ctx->d_ans, ans_bytes));
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_ans, 0, ans_bytes, ctx->stream));
+    answer_table_build_kernel<<<(n_ent + 255) / 256, 256, 0, ctx->stream>>>(f, ctx->d_ans, n_ent, 0);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    std::vector<uint16_t> h(n_ent);
+    CUDA_TRY(ctx, cudaMemcpyAsync(h.data(), ctx->d_ans, (size_t)n_ent * sizeof(uint16_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->h_ans.swap(h);
+    f.ans = ctx->d_ans;
+    f.ans_entries = n_ent;
+    if (!ctx->d_defer) CUDA_TRY(ctx, cudaMalloc(&ctx->d_defer, kDeferArena));
   }
   ctx->fast = f;
   return GPA_OK;
@@ -371,6 +444,7 @@ int gpa_create(int cuda_device, gpa_ctx **out) {
   CREATE_TRY(cudaMemset(ctx->d_key, 0, 2 * sizeof(unsigned long long)));
   CREATE_TRY(cudaMemset(ctx->d_ticket, 0, sizeof(unsigned int)));
   fill_binom(ctx->binom);
+  for (uint32_t x = 0; x < 256; x++) ctx->h_tern[x] = (uint16_t)ans_tern(x);
   CREATE_TRY(cudaMemcpyToSymbol(c_binom, &ctx->binom, sizeof(BinomTable)));
   {
     uint32_t parts[13][13];
@@ -413,6 +487,8 @@ void gpa_destroy(gpa_ctx *ctx) {
   if (ctx->d_part_words) cudaFree(ctx->d_part_words);
   if (ctx->d_part_index) cudaFree(ctx->d_part_index);
   if (ctx->d_part_key) cudaFree(ctx->d_part_key);
+  if (ctx->d_ans) cudaFree(ctx->d_ans);
+  if (ctx->d_defer) cudaFree(ctx->d_defer);
   if (ctx->d_sub_binom) cudaFree(ctx->d_sub_binom);
   if (ctx->d_sub_reqs) cudaFree(ctx->d_sub_reqs);
   if (ctx->d_sub_out) cudaFree(ctx->d_sub_out);
@@ -536,6 +612,18 @@ int gpa_get_topology(gpa_ctx *ctx, int *n, int32_t *W, uint8_t *nlinks, int cap)
   return GPA_OK;
 }
 
+int gpa_get_answer_table(gpa_ctx *ctx, uint16_t *table, int cap, int *n_entries) {
+  if (!ctx || !n_entries) return GPA_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  if (!ctx->has_topo) return GPA_ERR_NO_TOPOLOGY;
+  if (ctx->h_ans.empty()) return GPA_ERR_TOO_LARGE;
+  *n_entries = (int)ctx->h_ans.size();
+  if (!table) return GPA_OK;
+  if (cap < (int)ctx->h_ans.size()) return GPA_ERR_BUFFER;
+  memcpy(table, ctx->h_ans.data(), ctx->h_ans.size() * sizeof(uint16_t));
+  return GPA_OK;
+}
+
 int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_t *req, int n_req, int size,
                    int mode_flags, int32_t *out, int *n_out) {
   if (!ctx || !n_out || n_avail < 0 || n_req < 0 || (n_avail > 0 && !avail) || (n_req > 0 && !req)) return GPA_ERR_INVALID;
@@ -591,6 +679,35 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
     return GPA_OK;
   }
 
+  // A node of up to 8 GPUs whose devices are listed in node order (the reference's sorted-UUID order): the answer is
+  // one entry of the table the GPU built when the topology was installed.  No launch, no PCIe round trip - this is
+  // what a single kubelet request costs.  (The table exists only for symmetric link counts, so :307-310 cannot fire.)
+  if (!ctx->h_ans.empty() && !(mode_flags & (GPA_MODE_FORCE_ENUM | GPA_MODE_FORCE_DP | GPA_MODE_FORCE_KERNEL))) {
+    uint32_t mask = 0, rlab = 0;
+    bool in_order = true;
+    for (int p = 0; p < n_avail && in_order; p++) {
+      const int lab = ctx->fast.rank[avail[p]];
+      const uint32_t bit = lab < kAnsMaxTopo ? 1u << lab : 0u;
+      in_order = bit > mask;  // strictly ascending labels; a device the table does not know fails the same test
+      mask |= bit;
+      if (rmask >> p & 1u) rlab |= bit;
+    }
+    if (in_order) {
+      const uint16_t e = ctx->h_ans[ans_index(ctx->h_tern, mask, rlab, size)];
+      int o = 0;
+      for (uint32_t c = ans_chosen(e); c; c &= c - 1) out[o++] = ctx->fast.order[__builtin_ctz(c)];
+      for (int q = 0; q < ans_nil(e); q++) out[o++] = GPA_NIL;
+      *n_out = o;
+      const Geom g = make_geom(n_avail, size, rmask);
+      ctx->stats.partitions = partition_count(g, ctx->binom);
+      ctx->stats.items = 1;
+      ctx->stats.sets = g.m;
+      ctx->stats.padding = g.P;
+      ctx->stats.algorithm = 6;
+      return GPA_OK;
+    }
+  }
+
   // where calculateGPUPairScore panics (:307-310); see DESIGN.md for the (conservative) scope of this check
   for (int a = 0; a < n_avail; a++)
     for (int b = 0; b < n_avail; b++)
@@ -610,7 +727,7 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
   // A small node with its partition table installed, devices listed in node order: one warp answers.
   bool use_small = false;
   uint32_t small_mask = 0, small_rlab = 0;
-  if (ctx->d_sfull && ctx->fast.part_words && !(mode_flags & (GPA_MODE_FORCE_ENUM | GPA_MODE_FORCE_DP))) {
+  if (ctx->d_sfull && ctx->fast.part_words && !(mode_flags & (GPA_MODE_FORCE_ENUM | GPA_MODE_FORCE_DP))) {  // incl. GPA_MODE_FORCE_KERNEL
     use_small = true;
     int prev = -1;
     for (int p = 0; p < n_avail && use_small; p++) {
@@ -801,7 +918,7 @@ int gpa_besteffort_batch_masks_device(gpa_ctx *ctx, const gpa_mask_request *d_re
   if (!ctx->d_sfull) return GPA_ERR_TOO_LARGE;  // masks need the node-wide score table: <= 12 GPUs, symmetric link counts
   if (count == 0) return GPA_OK;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-  return launch_fast(ctx, d_reqs, count, mode_flags, d_out, (cudaStream_t)stream, true);
+  return launch_masks(ctx, d_reqs, count, mode_flags, d_out, (cudaStream_t)stream);
 }
 
 int gpa_besteffort_batch_masks(gpa_ctx *ctx, const gpa_mask_request *reqs, int count, int mode_flags, gpa_mask_result *out) {
@@ -831,7 +948,7 @@ int gpa_besteffort_batch_masks(gpa_ctx *ctx, const gpa_mask_request *reqs, int c
     int cnt = count - off < kChunk ? count - off : kChunk;
     cudaStream_t st = ctx->pipe[c & 3];
     CUDA_TRY(ctx, cudaMemcpyAsync(d_in + off, src + off, (size_t)cnt * sizeof(gpa_mask_request), cudaMemcpyHostToDevice, st));
-    rc = launch_fast(ctx, d_in + off, cnt, mode_flags, d_res + off, st, true);
+    rc = launch_masks(ctx, d_in + off, cnt, mode_flags, d_res + off, st);
     if (rc != GPA_OK) break;
     CUDA_TRY(ctx, cudaMemcpyAsync(dst + off, d_res + off, (size_t)cnt * sizeof(gpa_mask_result), cudaMemcpyDeviceToHost, st));
   }
@@ -1025,7 +1142,7 @@ extern "C" int gpa_besteffort_batch_noalloc(int cuda_device, int n_topology, con
   int cap = d.sm_count * 4;
   int grid = blocks < cap ? blocks : cap;
   BatchTopo t{d_wq, d_asym, n};
-  besteffort_batch_kernel<<<grid, kBatchWarps * 32, smem, st>>>(d_reqs, count, n_cap, mode_flags & GPA_MODE_INTENDED, t, d_out, 0);
+  besteffort_batch_kernel<<<grid, kBatchWarps * 32, smem, st>>>(d_reqs, count, n_cap, mode_flags & GPA_MODE_INTENDED, t, d_out, 0, nullptr);
   NA_TRY(cudaGetLastError());
   NA_TRY(cudaMemcpyAsync(out, d_out, sizeof(gpa_result) * (size_t)count, cudaMemcpyDeviceToHost, st));
   NA_TRY(cudaStreamSynchronize(st));

@@ -9,6 +9,7 @@
 
 #include "../../k8s-gpu-sharing-plugin_b200/csrc/gpa_enum.cuh"
 #include "../../k8s-gpu-sharing-plugin_b200/csrc/part_table.cuh"
+#include "../../k8s-gpu-sharing-plugin_b200/csrc/ans_table.cuh"
 
 extern "C" int enum_check_search(int nt, const int32_t *W, const int32_t *avail, int n_avail, uint32_t rmask, int size,
                                  int intended, unsigned long long want_items, int32_t *out, int *n_out,
@@ -248,4 +249,29 @@ extern "C" int enum_check_table_search(void *p, uint32_t real_mask, uint32_t rma
     *n_out = o;
   }
   return 0;
+}
+
+// ans_table.cuh: every entry of the answer table as the build kernel computes it (one ans_compute_entry per index),
+// and the index arithmetic the batch kernels and gpa_besteffort() look an answer up with.
+extern "C" int enum_check_answer_table(void *p, int intended, uint16_t *out, int cap) {
+  using namespace gpa;
+  EnumTables *t = static_cast<EnumTables *>(p);
+  const uint32_t n = ans_entries(t->nt);
+  if ((uint32_t)cap < n) return -1;
+  const uint16_t *S = t->S.data();
+  auto Sf = [S](uint32_t mask) { return S[mask]; };
+  for (uint32_t e = 0; e < n; e++) {
+    uint32_t mask, rl;
+    ans_decode(e / (uint32_t)kAnsSizes, mask, rl);
+    const int size = (int)(e % (uint32_t)kAnsSizes) + 1;
+    out[e] = ans_compute_entry(t->nt, mask, rl, size, t->words.data(), t->index.data(), t->keys.data(), Sf, intended != 0);
+  }
+  return (int)n;
+}
+
+extern "C" uint32_t enum_check_answer_index(uint32_t mask, uint32_t rl, int size) {
+  using namespace gpa;
+  uint16_t tern[256];
+  for (uint32_t x = 0; x < 256; x++) tern[x] = (uint16_t)ans_tern(x);
+  return ans_index(tern, mask, rl, size);
 }

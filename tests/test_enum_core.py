@@ -16,6 +16,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "enum_check.cpp")
 HDR = os.path.join(HERE, "..", "k8s-gpu-sharing-plugin_b200", "csrc", "gpa_enum.cuh")
 HDR2 = os.path.join(HERE, "..", "k8s-gpu-sharing-plugin_b200", "csrc", "part_table.cuh")
+HDR3 = os.path.join(HERE, "..", "k8s-gpu-sharing-plugin_b200", "csrc", "ans_table.cuh")
 # GPA_HARNESS_DIR / GPA_HARNESS_CXXFLAGS: build the harness elsewhere with other flags (tools/sanitize_cpu.sh: ASan + UBSan)
 SO = os.path.join(os.environ.get("GPA_HARNESS_DIR", os.path.join(HERE, "csrc")), "libenum_check.so")
 XFLAGS = os.environ.get("GPA_HARNESS_CXXFLAGS", "-O2").split()
@@ -23,7 +24,7 @@ XFLAGS = os.environ.get("GPA_HARNESS_CXXFLAGS", "-O2").split()
 
 @pytest.fixture(scope="module")
 def harness():
-    if not os.path.exists(SO) or os.path.getmtime(SO) < max(os.path.getmtime(SRC), os.path.getmtime(HDR), os.path.getmtime(HDR2)):
+    if not os.path.exists(SO) or os.path.getmtime(SO) < max(os.path.getmtime(SRC), os.path.getmtime(HDR), os.path.getmtime(HDR2), os.path.getmtime(HDR3)):
         subprocess.check_call(["g++"] + XFLAGS + ["-std=c++17", "-fPIC", "-shared", "-o", SO, SRC])
     L = C.CDLL(SO)
     L.enum_check_search.restype = C.c_int
@@ -320,3 +321,66 @@ def test_partition_tables_on_smaller_nodes(harness, oracle, nt):
     finally:
         harness.enum_check_tables_free(tab)
     assert checked >= (2 if nt == 2 else 20)
+
+
+@pytest.mark.parametrize("nt,topo_i", [(8, 3), (8, 9), (5, 1), (3, 2)])
+def test_answer_table_every_entry_matches_oracle(harness, oracle, nt, topo_i):
+    """ans_table.cuh: the table the GPU builds at topology install, computed here entry by entry with the same function.
+    EVERY (mask, required subset, size) entry is compared with the oracle in both alias modes (the table is shared by
+    both: no partition of a node of up to 8 GPUs has the 7 sets the aliasing needs), and the index arithmetic of the
+    lookup is checked to be a bijection onto the table."""
+    harness.enum_check_tables_new.restype = C.c_void_p
+    harness.enum_check_tables_new.argtypes = [C.c_int, C.POINTER(C.c_int32)]
+    harness.enum_check_tables_free.argtypes = [C.c_void_p]
+    harness.enum_check_answer_table.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint16), C.c_int]
+    harness.enum_check_answer_index.restype = C.c_uint32
+    harness.enum_check_answer_index.argtypes = [C.c_uint32, C.c_uint32, C.c_int]
+    if nt == 8:
+        name, t = syn.standard_topologies()[topo_i]
+    else:
+        name, t = "random-%d" % nt, syn.topo_random(nt, 40 + topo_i)
+    W, nl = syn.links_to_weights(t)
+    Wc = np.ascontiguousarray(W, dtype=np.int32)
+    tab = harness.enum_check_tables_new(nt, Wc.ctypes.data_as(C.POINTER(C.c_int32)))
+    assert tab
+    n_ent = 3 ** nt * 8
+    try:
+        tables = []
+        for intended in (0, 1):
+            buf = np.zeros(n_ent, dtype=np.uint16)
+            assert harness.enum_check_answer_table(tab, intended, buf.ctypes.data_as(C.POINTER(C.c_uint16)), n_ent) == n_ent
+            tables.append(buf)
+        assert (tables[0] == tables[1]).all()
+    finally:
+        harness.enum_check_tables_free(tab)
+    table = tables[0]
+    seen = np.zeros(n_ent, dtype=bool)
+    # the oracle on every entry, batched: requests over labels 0..nt-1 in label order
+    reqs, where = [], []
+    for mask in range(1 << nt):
+        labels = [b for b in range(nt) if mask >> b & 1]
+        sub = mask
+        while True:  # every subset of mask, 0 included
+            req = [b for b in range(nt) if sub >> b & 1]
+            for size in range(1, 9):
+                idx = harness.enum_check_answer_index(mask, sub, size)
+                assert idx < n_ent and not seen[idx]
+                seen[idx] = True
+                if mask:
+                    reqs.append((labels, req, size))
+                    where.append(idx)
+                else:
+                    assert table[idx] == 0
+            if sub == 0:
+                break
+            sub = (sub - 1) & mask
+    assert seen.all()
+    packed = syn.pack_requests(reqs)
+    for mode in (oracle.GO_FAITHFUL, oracle.INTENDED):
+        want, _ = oracle.besteffort_batch(W, nl, packed, mode=mode, threads=8)
+        for i, idx in enumerate(where):
+            e = int(table[idx])
+            got = [b for b in range(8) if e >> b & 1] + [-1] * (e >> 8)
+            row = want["dev"][i].tolist()
+            exp = row[:row.index(-128)] if -128 in row else row
+            assert got == exp, (name, reqs[i], mode, got, exp)

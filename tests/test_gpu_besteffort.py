@@ -72,8 +72,9 @@ def test_single_request_api_matches_batch_and_oracle_n8(ctx, oracle):
 
 @pytest.mark.parametrize("topo_i", [0, 3, 8])
 def test_single_request_on_a_small_node_takes_the_one_warp_kernel(ctx, oracle, topo_i):
-    """8-GPU node, devices listed in node order: the partition-table kernel answers (algorithm 3), both modes,
-    with and without required devices, every mask and size"""
+    """8-GPU node, devices listed in node order, GPA_MODE_FORCE_KERNEL (without it the host copy of the answer table
+    answers, tests/test_gpu_table.py): the one-warp partition-table kernel answers (algorithm 3), both modes, with and
+    without required devices, every mask and size"""
     name, t = syn.standard_topologies()[topo_i]
     W, nl = install(ctx, t, ORDER8)
     n = 0
@@ -83,7 +84,7 @@ def test_single_request_on_a_small_node_takes_the_one_warp_kernel(ctx, oracle, t
             continue
         for mode in (gpa.MODE_GO_FAITHFUL, gpa.MODE_INTENDED):
             want = oracle.besteffort(W, nl, avail, req, k, mode)
-            assert ctx.besteffort(avail, req, k, mode) == (gpa.OK, want[1]), (name, avail, req, k, mode)
+            assert ctx.besteffort(avail, req, k, mode | gpa.MODE_FORCE_KERNEL) == (gpa.OK, want[1]), (name, avail, req, k, mode)
             assert ctx.search_stats()["algorithm"] == 3
         n += 1
     # the same node, devices listed in another order: falls back to the general search, same answer
@@ -96,7 +97,8 @@ def test_single_request_on_a_small_node_takes_the_one_warp_kernel(ctx, oracle, t
         t5[i, j, 0] = t5[j, i, 0] = 5
     t5[0, 1] = t5[1, 0] = (5, syn.nvlink_type(1))
     install(ctx, t5)
-    assert ctx.besteffort([0, 1, 2, 3, 4], [], 3) == (gpa.OK, [0, 1, gpa.NIL]) and ctx.search_stats()["algorithm"] == 3
+    assert ctx.besteffort([0, 1, 2, 3, 4], [], 3, gpa.MODE_FORCE_KERNEL) == (gpa.OK, [0, 1, gpa.NIL]) and ctx.search_stats()["algorithm"] == 3
+    assert ctx.besteffort([0, 1, 2, 3, 4], [], 3) == (gpa.OK, [0, 1, gpa.NIL]) and ctx.search_stats()["algorithm"] == 6
 
 
 def test_guards_and_trivial_answers(ctx, oracle):
@@ -449,7 +451,8 @@ def test_two_contexts_are_independent(oracle):
 def test_launch_counter_counts_kernels(ctx):
     install(ctx, syn.topo_two_sockets(8))
     before = ctx.launch_count
-    ctx.besteffort(list(range(8)), [], 4)
-    ctx.besteffort_batch(syn.random_request_batch(8, 100, seed=1))  # fast kernel + the general kernel's deferred pass
+    ctx.besteffort(list(range(8)), [], 4, gpa.MODE_FORCE_KERNEL)
+    ctx.besteffort(list(range(8)), [], 4)  # answered from the host copy of the answer table: no kernel
+    ctx.besteffort_batch(syn.random_request_batch(8, 100, seed=1))  # table kernel + the general kernel's deferred pass
     ctx.besteffort(list(range(8)), [], 1)  # answered by the guards: no kernel
     assert ctx.launch_count == before + 3

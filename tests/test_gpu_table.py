@@ -1,0 +1,202 @@
+"""The answer table of small nodes (csrc/ans_table.cuh, table_kernels.cuh) on the GPU, through the C ABI:
+
+* every entry the build kernel wrote equals the oracle's answer (all 3^8 (mask, required) pairs x 8 sizes);
+* gpa_set_topology* / gpa_set_device_order rebuild it;
+* the table batch kernels (32-byte records and 8-byte mask records) and the launch-free gpa_besteffort() give the
+  oracle's answers, in both alias modes, including records the table cannot answer (left to the general kernel).
+
+Bit-exact: integer work, no tolerance.  Nothing here reads /root/reference."""
+import numpy as np
+import pytest
+
+from k8s_gpu_sharing_plugin_b200 import _lib as gpa
+from k8s_gpu_sharing_plugin_b200 import synthetic as syn
+
+pytestmark = pytest.mark.gpu
+
+ORDER8 = syn.sorted_positions(syn.node_uuids(8, seed=1))
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = gpa.Context(0)
+    yield c
+    c.close()
+
+
+def tern(x):
+    return sum(3 ** b for b in range(8) if x >> b & 1)
+
+
+def all_table_requests(nt, order):
+    """every (mask, required subset, size) of a node of nt GPUs as (index, avail, required, size), devices as NVML indices"""
+    for mask in range(1, 1 << nt):
+        avail = [order[b] for b in range(nt) if mask >> b & 1]
+        sub = mask
+        while True:
+            req = [order[b] for b in range(nt) if sub >> b & 1]
+            for size in range(1, 9):
+                yield (tern(mask) + tern(sub)) * 8 + size - 1, avail, req, size
+            if sub == 0:
+                break
+            sub = (sub - 1) & mask
+
+
+def decode_entry(e, order):
+    return [order[b] for b in range(8) if e >> b & 1] + [gpa.NIL] * (e >> 8)
+
+
+def oracle_rows(oracle, W, nl, packed, mode):
+    want, _ = oracle.besteffort_batch(W, nl, packed, mode=mode, threads=8)
+    rows = []
+    for row in want["dev"].tolist():
+        rows.append(row[:row.index(gpa.RES_END)] if gpa.RES_END in row else row)
+    return rows
+
+
+@pytest.mark.parametrize("topo_i,order", [(3, ORDER8), (7, None), (12, ORDER8)], ids=["dgx1v-uuid-order", "random-index-order", "random-uuid-order"])
+def test_every_table_entry_equals_the_oracle(ctx, oracle, topo_i, order):
+    name, t = syn.standard_topologies()[topo_i]
+    W, nl = syn.links_to_weights(t)
+    launches0 = ctx.launch_count
+    ctx.set_topology_links(t)
+    order = list(range(8)) if order is None else order
+    ctx.set_device_order(order)
+    assert ctx.launch_count - launches0 == 2  # the build kernel ran at each install
+    table = ctx.answer_table()
+    assert table is not None and len(table) == 3 ** 8 * 8
+    items = list(all_table_requests(8, order))
+    assert len(items) == (3 ** 8 - 1) * 8
+    packed = syn.pack_requests([(a, r, s) for _, a, r, s in items])
+    for mode in (gpa.MODE_GO_FAITHFUL, gpa.MODE_INTENDED):
+        rows = oracle_rows(oracle, W, nl, packed, mode)
+        for (idx, avail, req, size), want in zip(items, rows):
+            assert decode_entry(int(table[idx]), order) == want, (name, avail, req, size, mode)
+    # entries of the empty mask: nothing is available
+    assert not table[:8].any()
+
+
+def test_install_rebuilds_the_table(ctx, oracle):
+    topos = syn.standard_topologies()
+    ctx.set_topology_links(topos[3][1])
+    ctx.set_device_order(ORDER8)
+    a = ctx.answer_table().copy()
+    ctx.set_topology_links(topos[5][1])
+    b = ctx.answer_table().copy()
+    assert (a != b).any()
+    W, nl = syn.links_to_weights(topos[5][1])
+    for avail, req, k in [(ORDER8, [], 4), (ORDER8[1:], [ORDER8[3]], 3), (ORDER8[:5], [], 2)]:
+        assert ctx.besteffort(avail, req, k) == (gpa.OK, oracle.besteffort(W, nl, avail, req, k)[1])
+        assert ctx.search_stats()["algorithm"] == 6
+    # the same weights under another node order: other labels, other table
+    ctx.set_device_order(list(range(8)))
+    c = ctx.answer_table().copy()
+    assert (b != c).any()
+    # a node the table does not cover: more than 8 GPUs, or asymmetric link counts
+    ctx.set_topology_links(syn.topo_random(9, 3))
+    assert ctx.answer_table() is None
+    W8, nl8 = syn.links_to_weights(topos[3][1])
+    nl_bad = nl8.copy()
+    nl_bad[0, 1] += 1
+    ctx.set_topology(W8, nl_bad)
+    assert ctx.answer_table() is None
+    ctx.set_topology(W8, nl8)
+    assert ctx.answer_table() is not None
+
+
+@pytest.mark.parametrize("nt", [1, 2, 5, 7])
+def test_smaller_nodes(ctx, oracle, nt):
+    t = syn.topo_random(nt, 90 + nt) if nt > 1 else syn.topo_zero(1)
+    W, nl = syn.links_to_weights(t)
+    order = [int(x) for x in np.random.default_rng(nt).permutation(nt)]
+    ctx.set_topology_links(t)
+    ctx.set_device_order(order)
+    table = ctx.answer_table()
+    assert len(table) == 3 ** nt * 8
+    items = list(all_table_requests(nt, order))
+    reqs = [(a, r, s) for _, a, r, s in items]
+    packed = syn.pack_requests(reqs)
+    for mode in (gpa.MODE_GO_FAITHFUL, gpa.MODE_INTENDED):
+        rows = oracle_rows(oracle, W, nl, packed, mode)
+        got = ctx.besteffort_batch(packed, mode)
+        for i, ((idx, avail, req, size), want) in enumerate(zip(items, rows)):
+            assert decode_entry(int(table[idx]), order + [0] * 8) == want, (nt, avail, req, size, mode)
+            assert gpa.decode_result(got[i]) == (gpa.OK, want), (nt, avail, req, size, mode)
+
+
+def test_single_decisions_need_no_launch(ctx, oracle):
+    name, t = syn.standard_topologies()[8]
+    W, nl = syn.links_to_weights(t)
+    ctx.set_topology_links(t)
+    ctx.set_device_order(ORDER8)
+    launches0 = ctx.launch_count
+    n = 0
+    for avail, req, k in syn.exhaustive_requests(ORDER8, seed=8, n_pairs=2):
+        if n % 7 == 0:
+            for mode in (gpa.MODE_GO_FAITHFUL, gpa.MODE_INTENDED):
+                want = oracle.besteffort(W, nl, avail, req, k, mode)
+                assert ctx.besteffort(avail, req, k, mode) == (gpa.OK, want[1]), (avail, req, k, mode)
+                if k >= 2 and len(req) <= k:
+                    st = ctx.search_stats()
+                    assert st["algorithm"] == 6 and st["partitions"] == oracle.partition_count(len(avail), k)
+        n += 1
+    assert ctx.launch_count == launches0
+    # a kernel on request, same answer
+    want = oracle.besteffort(W, nl, ORDER8, [ORDER8[2]], 3)
+    assert ctx.besteffort(ORDER8, [ORDER8[2]], 3, gpa.MODE_FORCE_KERNEL) == (gpa.OK, want[1])
+    assert ctx.search_stats()["algorithm"] == 3 and ctx.launch_count == launches0 + 1
+    # devices in another order than the node's: not a table request
+    rev = list(reversed(ORDER8))
+    assert ctx.besteffort(rev, [], 3) == (gpa.OK, oracle.besteffort(W, nl, rev, [], 3)[1])
+    assert ctx.search_stats()["algorithm"] == 1
+
+
+def test_batch_mixes_table_and_deferred_records(ctx, oracle):
+    """records in node order are answered from the table, the others are flagged for the general kernel: a batch that
+    mixes both, at sizes around the 32-record flag groups and the 1024-record blocks"""
+    name, t = syn.standard_topologies()[4]
+    W, nl = syn.links_to_weights(t)
+    ctx.set_topology_links(t)
+    ctx.set_device_order(ORDER8)
+    rng = np.random.default_rng(11)
+    canon = syn.random_request_batch(8, 70000, seed=21, order=ORDER8)
+    other = syn.random_request_batch(8, 70000, seed=22, order=[int(x) for x in rng.permutation(8)])
+    for count, p_other in ((1, 0.0), (31, 0.5), (33, 0.05), (1023, 0.01), (1025, 0.0), (4097, 0.002), (70000, 0.0005), (70000, 0.3)):
+        pick = rng.random(count) < p_other
+        reqs = canon[:count].copy()
+        reqs[pick] = other[:count][pick]
+        if count > 40:  # an unknown device, a duplicate, a foreign required pointer, more required than size
+            reqs[5:9] = syn.pack_requests([([77] + ORDER8[1:4], [], 2), ([ORDER8[0], ORDER8[0], ORDER8[2]], [], 2),
+                                           (ORDER8[:4], [gpa.FOREIGN], 2), (ORDER8[:4], [gpa.FOREIGN] * 3, 2)])
+        for mode in (gpa.MODE_GO_FAITHFUL, gpa.MODE_INTENDED):
+            want, _ = oracle.besteffort_batch(W, nl, reqs, mode=mode, threads=8)
+            got = ctx.besteffort_batch(reqs, mode)
+            bad = np.nonzero((got["dev"] != want["dev"]).any(axis=1))[0]
+            assert len(bad) == 0, (count, p_other, mode, int(bad[0]), syn.unpack_request(reqs[int(bad[0])]),
+                                   got["dev"][int(bad[0])].tolist(), want["dev"][int(bad[0])].tolist())
+            # the tile-binned kernel (what nodes of 9-12 GPUs use) on the same records
+            got2 = ctx.besteffort_batch(reqs, mode | gpa.MODE_FORCE_ENUM)
+            assert (got2["dev"] == want["dev"]).all()
+
+
+def test_mask_records_from_the_table(ctx, oracle):
+    name, t = syn.standard_topologies()[6]
+    W, nl = syn.links_to_weights(t)
+    ctx.set_topology_links(t)
+    ctx.set_device_order(ORDER8)
+    for count in (1, 2, 3, 1000, 2049, 100001):
+        reqs = syn.random_request_batch(8, count, seed=count, order=ORDER8)
+        masks = syn.records_to_masks(reqs, ORDER8)
+        if count > 100:
+            masks["avail_mask"][3] = 0x1FF     # a device the node does not have
+            masks["avail_mask"][4], masks["req_mask"][4], masks["size"][4], masks["flags"][4] = 0x0F, 0x10, 2, 0  # required, not available
+        want, _ = oracle.besteffort_batch(W, nl, reqs, threads=8)
+        for mode in (gpa.MODE_GO_FAITHFUL, gpa.MODE_FORCE_ENUM):
+            got = ctx.besteffort_batch_masks(masks, mode)
+            rec = syn.mask_results_to_records(got.copy(), ORDER8)
+            ok = (rec["dev"] == want["dev"]).all(axis=1)
+            if count > 100:
+                assert got["status"][3] == gpa.ERR_INVALID
+                assert got["chosen_mask"][4] == 0 and got["status"][4] == 0
+                ok[3] = ok[4] = True
+            assert ok.all(), (count, mode, int(np.nonzero(~ok)[0][0]))
