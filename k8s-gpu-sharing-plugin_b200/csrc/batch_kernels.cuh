@@ -35,6 +35,16 @@ __global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_kernel(cons
                                                                             const uint8_t *__restrict__ defer_flags) {
   extern __shared__ __align__(16) uint16_t smem[];
   __shared__ BinomTable s_binom;
+  if (deferred_only && defer_flags != nullptr) {
+    // nothing flagged among the groups this CTA would scan (the usual case: every record was in node order): leave
+    // before staging anything, so that the pass costs a launch and one byte per 32 records
+    const long long n_groups = ((long long)count + 31) / 32;
+    int any = 0;
+    for (long long gi = (long long)blockIdx.x * (kBatchWarps * 32) + threadIdx.x; gi < n_groups;
+         gi += (long long)gridDim.x * (kBatchWarps * 32))
+      any |= defer_flags[gi] != 0;
+    if (!__syncthreads_or(any)) return;
+  }
   stage_binom(s_binom, threadIdx.x, kBatchWarps * 32);
   __syncthreads();
   const int lane = threadIdx.x & 31;

@@ -218,17 +218,33 @@ int launch_fast(gpa_ctx *ctx, const void *d_reqs, int count, int mode_flags, voi
 // Nodes of up to 8 GPUs: one lookup in the answer table per request (table_kernels.cuh).  The table holds the same
 // answers for both alias modes (no partition of such a node has the 7 sets the aliasing needs), so mode_flags is unused.
 int launch_table(gpa_ctx *ctx, const void *d_reqs, int count, void *d_out, cudaStream_t stream, bool masks, uint8_t *defer_flags) {
-  auto kern = masks ? besteffort_batch_table_kernel<true> : besteffort_batch_table_kernel<false>;
-  const size_t smem = table_smem_bytes(ctx->fast.ans_entries);
+  const size_t smem_max = masks ? masks_smem_bytes(ans_entries(kAnsMaxTopo)) : table_smem_bytes(ans_entries(kAnsMaxTopo));
   if (!ctx->table_attr_set[masks ? 1 : 0]) {
-    CUDA_TRY(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)table_smem_bytes(ans_entries(kAnsMaxTopo))));
+    if (masks)
+      CUDA_TRY(ctx, cudaFuncSetAttribute(besteffort_masks_table_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max));
+    else
+      CUDA_TRY(ctx, cudaFuncSetAttribute(besteffort_batch_table_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max));
     ctx->table_attr_set[masks ? 1 : 0] = true;
   }
-  const long long per_block = masks ? 2 * kTabThreads : kTabThreads;
-  long long want = ((long long)count + per_block - 1) / per_block;
-  long long cap = (long long)ctx->sm_count * kTabBlocksPerSm;  // persistent: every CTA stages the table once
-  int grid = (int)(want < cap ? want : cap);
-  kern<<<grid, kTabThreads, smem, stream>>>(d_reqs, count, ctx->fast, d_out, defer_flags);
+  if (masks) {
+    // persistent: every CTA stages the table once; two 107 KB CTAs fit an SM
+    long long want = ((long long)count + 2 * kMaskThreads - 1) / (2 * kMaskThreads);
+    long long cap = (long long)ctx->sm_count * 2;
+    int grid = (int)(want < cap ? want : cap);
+    besteffort_masks_table_kernel<<<grid, kMaskThreads, masks_smem_bytes(ctx->fast.ans_entries), stream>>>(
+        static_cast<const uint2 *>(d_reqs), count, ctx->fast, static_cast<uint32_t *>(d_out));
+  } else {
+    // the bulk copies that feed the kernel need 16-byte aligned records (anything from cudaMalloc is 256-byte aligned)
+    if ((reinterpret_cast<uintptr_t>(d_reqs) & 15u) || (reinterpret_cast<uintptr_t>(d_out) & 15u)) {
+      ctx->last_error = "device request / result buffers must be 16-byte aligned";
+      return GPA_ERR_INVALID;
+    }
+    // persistent: one CTA per SM (answer table + a ring of request tiles in its shared memory)
+    long long want = ((long long)count + kTabTile - 1) / kTabTile;
+    int grid = (int)(want < ctx->sm_count ? want : ctx->sm_count);
+    besteffort_batch_table_kernel<<<grid, kTabThreads, table_smem_bytes(ctx->fast.ans_entries), stream>>>(
+        static_cast<const gpa_request *>(d_reqs), count, ctx->fast, static_cast<gpa_result *>(d_out), defer_flags);
+  }
   ctx->launches++;
   CUDA_TRY(ctx, cudaGetLastError());
   return GPA_OK;

@@ -3,10 +3,13 @@
 //
 //   answer_table_build_kernel        one thread per (mask, required, size): the partition-table search of
 //                                    part_table.cuh, run once when a topology is installed (52 488 entries for 8 GPUs)
-//   besteffort_batch_table_kernel    MANY requests in node order, one LANE per request, requests and answers in RECORD
-//                                    order: 256-bit load of the record, relabel to a device mask, one table lookup from
-//                                    shared memory, 128-bit store.  No sort, no divergence: the kernel moves 48 bytes per
-//                                    decision and its ceiling is HBM bandwidth.
+//   besteffort_batch_table_kernel    MANY 32-byte requests in node order, one LANE per request, requests and answers in
+//                                    RECORD order.  One CTA per SM keeps the answer table in shared memory and streams
+//                                    32 KB request tiles through a ring of shared-memory stages filled by bulk
+//                                    asynchronous copies (cp.async.bulk + mbarrier), so that several tiles are in flight
+//                                    per SM while the lanes relabel, look up and store.  No sort, no divergence: the
+//                                    kernel moves 48 bytes per decision and its ceiling is HBM bandwidth.
+//   besteffort_masks_table_kernel    the same for 8-byte mask records (4-byte answers): nothing to relabel.
 // Replaces, for such nodes, bestEffortPolicy.Allocate
 // (vendor/github.com/NVIDIA/go-gpuallocator/gpuallocator/besteffort_policy.go:34-89) per request.
 #pragma once
@@ -16,7 +19,8 @@
 namespace {
 
 constexpr int kTabThreads = 1024;
-constexpr int kTabBlocksPerSm = 2;  // 2 x (105 KB answers + 3 KB of small tables) of shared memory per SM
+constexpr int kTabTile = kTabThreads;  // records per tile: one per thread
+constexpr int kTabStages = 3;          // request tiles in flight per SM (3 x 32 KB)
 
 __global__ void __launch_bounds__(256) answer_table_build_kernel(const FastTopo ft, uint16_t *__restrict__ table, uint32_t n_entries,
                                                                  int intended) {
@@ -29,149 +33,213 @@ __global__ void __launch_bounds__(256) answer_table_build_kernel(const FastTopo 
   }
 }
 
+// ---- shared-memory layout common to both batch kernels ---------------------------------------------------------
+__host__ __device__ constexpr size_t table_ans_bytes(uint32_t n_entries) { return ((size_t)n_entries * sizeof(uint16_t) + 15) & ~(size_t)15; }
+constexpr size_t kTabSmallTables = 256 * sizeof(unsigned long long) + 256 * sizeof(uint16_t);  // s_dev + tern
+constexpr size_t masks_smem_bytes(uint32_t n_entries) { return kTabSmallTables + table_ans_bytes(n_entries); }
 constexpr size_t table_smem_bytes(uint32_t n_entries) {
-  return (size_t)256 * sizeof(unsigned long long)   // s_dev: chosen mask -> its devices' NVML indices, one per byte
-         + (((size_t)n_entries * sizeof(uint16_t) + 15) & ~(size_t)15)  // answers
-         + 256 * sizeof(uint16_t)                   // tern
-         + 256;                                     // s_bit: NVML index -> label bit
+  return (size_t)kTabStages * kTabTile * sizeof(gpa_request)  // request ring (first: 128-byte aligned)
+         + kTabSmallTables + table_ans_bytes(n_entries) + kTabStages * sizeof(unsigned long long);  // + the stages' mbarriers
 }
 
-__device__ __forceinline__ void ld_record_256(const gpa_request *p, uint32_t (&w)[8]) {
-  // the whole 32-byte record in one load: a warp reads 1 KiB of consecutive records per instruction; streamed, no reuse
-  asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-               : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
-               : "l"(p));
-}
-
-// kMasks = false: 32-byte gpa_request in, 16-byte gpa_result out; a record the table cannot answer (devices not in
-//                 node order, unknown device) is marked kResDefer for the general kernel and its warp's byte in
-//                 `defer_flags` (one per 32 records, optional) is set so that the general kernel finds it without
-//                 reading every result back.
-// kMasks = true : 8-byte gpa_mask_request in, 4-byte gpa_mask_result out; nothing is ever deferred.
-template <bool kMasks>
-__global__ void __launch_bounds__(kTabThreads, kTabBlocksPerSm) besteffort_batch_table_kernel(const void *__restrict__ reqs_v, int count,
-                                                                                const FastTopo ft, void *__restrict__ out_v,
-                                                                                uint8_t *__restrict__ defer_flags) {
-  extern __shared__ __align__(16) unsigned char tsmem[];
-  const uint32_t n_entries = ft.ans_entries;
-  unsigned long long *s_dev = reinterpret_cast<unsigned long long *>(tsmem);
-  uint16_t *s_ans = reinterpret_cast<uint16_t *>(s_dev + 256);
-  uint16_t *s_tern = reinterpret_cast<uint16_t *>(reinterpret_cast<unsigned char *>(s_ans) +
-                                                  (((size_t)n_entries * sizeof(uint16_t) + 15) & ~(size_t)15));
-  uint8_t *s_bit = reinterpret_cast<uint8_t *>(s_tern + 256);
-
-  const int tid = threadIdx.x;
-  {
-    // answers: 16 bytes per thread per step (the table is padded to a multiple of 16 bytes on the device)
-    const uint4 *src = reinterpret_cast<const uint4 *>(ft.ans);
-    uint4 *dst = reinterpret_cast<uint4 *>(s_ans);
-    const uint32_t n16 = (n_entries * (uint32_t)sizeof(uint16_t) + 15u) / 16u;
-    for (uint32_t i = tid; i < n16; i += kTabThreads) dst[i] = __ldg(src + i);
-  }
+__device__ __forceinline__ void stage_tables(const FastTopo &ft, unsigned long long *s_dev, uint16_t *s_tern, uint16_t *s_ans, int tid,
+                                             int nthreads) {
+  // answers: 16 bytes per thread per step (the table is padded to a multiple of 16 bytes on the device)
+  const uint4 *src = reinterpret_cast<const uint4 *>(ft.ans);
+  uint4 *dst = reinterpret_cast<uint4 *>(s_ans);
+  const uint32_t n16 = (uint32_t)(table_ans_bytes(ft.ans_entries) / 16);
+  for (uint32_t i = tid; i < n16; i += nthreads) dst[i] = __ldg(src + i);
   if (tid < 256) {
     s_tern[tid] = (uint16_t)ans_tern((uint32_t)tid);
-    const int lab = tid < GPA_MAX_TOPOLOGY ? ft.rank[tid] : 0xFF;
-    s_bit[tid] = lab < 8 ? (uint8_t)(1u << lab) : (uint8_t)0;
-    unsigned long long dev = 0x8080808080808080ull;  // 8 x GPA_RES_END
+    // chosen label mask -> the NVML indices of its devices, one per byte in label order, then GPA_RES_END
+    unsigned long long dev = 0x8080808080808080ull;
     int o = 0;
-    for (int lab2 = 0; lab2 < 8; lab2++)
-      if (tid >> lab2 & 1) {
-        dev ^= (unsigned long long)((ft.order[lab2] ^ 0x80) & 0xFF) << (8 * o);
+#pragma unroll
+    for (int lab = 0; lab < 8; lab++)
+      if (tid >> lab & 1) {
+        dev ^= (unsigned long long)((ft.order[lab] ^ 0x80) & 0xFF) << (8 * o);
         o++;
       }
     s_dev[tid] = dev;
   }
+}
+
+// ---- mbarrier / bulk-copy primitives (sm_90+ PTX; the copy reads this GPU's own memory, no multicast) -------------
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, uint32_t arrivals) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(arrivals));
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_addr(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_load(void *smem_dst, const void *gmem_src, uint32_t bytes, unsigned long long *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_addr(smem_dst)),
+               "l"(gmem_src), "r"(bytes), "r"(smem_addr(bar))
+               : "memory");
+}
+
+// 32-byte gpa_request in, 16-byte gpa_result out.  A record the table cannot answer (devices not in node order, unknown
+// device) is marked kResDefer for the general kernel, and its warp's byte in `defer_flags` (one per 32 records,
+// optional) is set so that the general kernel finds it without reading every result back.
+// reqs must be 16-byte aligned (bulk copies), out 16-byte aligned.
+__global__ void __launch_bounds__(kTabThreads, 1) besteffort_batch_table_kernel(const gpa_request *__restrict__ reqs, int count,
+                                                                                const FastTopo ft, gpa_result *__restrict__ out,
+                                                                                uint8_t *__restrict__ defer_flags) {
+  extern __shared__ __align__(128) unsigned char tsmem[];
+  gpa_request *ring = reinterpret_cast<gpa_request *>(tsmem);
+  unsigned long long *s_dev = reinterpret_cast<unsigned long long *>(ring + (size_t)kTabStages * kTabTile);
+  uint16_t *s_tern = reinterpret_cast<uint16_t *>(s_dev + 256);
+  uint16_t *s_ans = s_tern + 256;
+  unsigned long long *full = reinterpret_cast<unsigned long long *>(reinterpret_cast<unsigned char *>(s_ans) + table_ans_bytes(ft.ans_entries));
+
+  const int tid = threadIdx.x;
+  const long long n_tiles = ((long long)count + kTabTile - 1) / kTabTile;
+  // tile i of this CTA is global tile blockIdx.x + i * gridDim.x
+  const long long my_tiles = blockIdx.x < n_tiles ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  auto issue = [&](long long i) {  // one thread: fill stage i % kTabStages with this CTA's tile i
+    const long long base = (blockIdx.x + i * (long long)gridDim.x) * kTabTile;
+    const long long left = (long long)count - base;
+    const uint32_t bytes = (uint32_t)(left < kTabTile ? left : kTabTile) * (uint32_t)sizeof(gpa_request);
+    const int s = (int)(i % kTabStages);
+    mbar_expect_tx(&full[s], bytes);
+    bulk_load(ring + (size_t)s * kTabTile, reqs + base, bytes, &full[s]);
+  };
+  if (tid == 0) {
+    for (int s = 0; s < kTabStages; s++) mbar_init(&full[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    // the first tiles are on their way while the CTA stages its tables
+    for (long long i = 0; i < kTabStages && i < my_tiles; i++) issue(i);
+  }
+  stage_tables(ft, s_dev, s_tern, s_ans, tid, kTabThreads);
+  // device NVML index -> its bit in the node order, 8 x 8 bits (a node of up to 8 GPUs has NVML indices 0..7)
+  unsigned long long bit_of = 0;
+#pragma unroll
+  for (int d = 0; d < 8; d++) {
+    const int lab = ft.rank[d];
+    bit_of |= (unsigned long long)(lab < 8 ? (1u << lab) : 0u) << (8 * d);
+  }
   __syncthreads();
 
-  if constexpr (kMasks) {
-    const uint2 *__restrict__ mreqs = static_cast<const uint2 *>(reqs_v);
-    uint32_t *__restrict__ mout = static_cast<uint32_t *>(out_v);
-    const uint32_t node_mask = (1u << ft.nt) - 1u;
-    auto answer = [&](uint32_t x, uint32_t y) -> uint32_t {
-      // {avail_mask:16, req_mask:16} {size:8, flags:8, n_req_extra:8, reserved:8} -> {chosen_mask:16, n_nil:8, status:8}
-      const uint32_t mask = x & 0xFFFFu, rl = x >> 16;
-      const int size = (int)(y & 0xFFu), flags = (int)((y >> 8) & 0xFFu);
-      const int n = __popc(mask);
-      const int n_req = __popc(rl) + (int)((y >> 16) & 0xFFu);
-      if (((mask | rl) & ~node_mask) != 0) return (uint32_t)(GPA_ERR_INVALID & 0xFF) << 24;
-      // guards of besteffort_policy.go:35-45; a required device that is not available is in no set (:53)
-      if (size <= 0 || n < size || n_req > size || (flags & GPA_REQ_FOREIGN) || (rl & ~mask) != 0) return 0u;
-      const uint32_t e = s_ans[ans_index(s_tern, mask, rl, size)];
-      return (e & 0xFFu) | ((e >> 8) << 16);
-    };
-    if (((reinterpret_cast<uintptr_t>(reqs_v) & 15u) | (reinterpret_cast<uintptr_t>(out_v) & 7u)) == 0) {
-      // two records per lane per step: 16 bytes in, 8 bytes out
-      const long long n_pairs = (long long)count >> 1;
-      for (long long p = (long long)blockIdx.x * kTabThreads + tid; p < n_pairs; p += (long long)gridDim.x * kTabThreads) {
-        const uint4 rec = __ldg(reinterpret_cast<const uint4 *>(mreqs) + p);
-        uint2 res;
-        res.x = answer(rec.x, rec.y);
-        res.y = answer(rec.z, rec.w);
-        reinterpret_cast<uint2 *>(mout)[p] = res;
-      }
-      if ((count & 1) && blockIdx.x == 0 && tid == 0) {
-        const uint2 rec = __ldg(mreqs + (count - 1));
-        mout[count - 1] = answer(rec.x, rec.y);
-      }
-    } else {  // buffers that only have the records' own 8 / 4-byte alignment
-      for (long long r = (long long)blockIdx.x * kTabThreads + tid; r < count; r += (long long)gridDim.x * kTabThreads) {
-        const uint2 rec = __ldg(mreqs + r);
-        mout[r] = answer(rec.x, rec.y);
-      }
+  for (long long i = 0; i < my_tiles; i++) {
+    const int s = (int)(i % kTabStages);
+    const long long r = (blockIdx.x + i * (long long)gridDim.x) * kTabTile + tid;
+    mbar_wait(&full[s], (uint32_t)((i / kTabStages) & 1));
+    // this lane's record: device bytes 0..7 and the 8 bytes of masks / sizes / flags (devices 8..15 cannot belong to a
+    // request this table answers)
+    uint2 dv = make_uint2(0, 0), hd = make_uint2(0, 0);
+    if (r < count) {
+      const uint2 *rec = reinterpret_cast<const uint2 *>(ring + (size_t)s * kTabTile + tid);
+      dv = rec[0];
+      hd = rec[2];
     }
-  } else {
-    const gpa_request *__restrict__ reqs = static_cast<const gpa_request *>(reqs_v);
-    gpa_result *__restrict__ out = static_cast<gpa_result *>(out_v);
-    const long long n_blocks = ((long long)count + kTabThreads - 1) / kTabThreads;
-    for (long long blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
-      const long long r = blk * kTabThreads + tid;
-      bool defer = false;
-      if (r < count) {
-        uint32_t w[8];
-        ld_record_256(reqs + r, w);
-        const uint32_t rmask = w[4] & 0xFFFFu;
-        const int n = (int)((w[4] >> 16) & 0xFFu);
-        const int size = (int)(w[4] >> 24);
-        const int flags = (int)(w[5] & 0xFFu);
-        const int n_req = __popc(rmask) + (int)((w[5] >> 8) & 0xFFu);
-        unsigned long long r0 = 0x8080808080808080ull;  // 8 x GPA_RES_END: the empty answer
-        // guards of besteffort_policy.go:35-45
-        if (!(size <= 0 || n < size || n_req > size)) {
-          // relabel: device -> its bit in the node order.  The list must be strictly ascending in that order, i.e. every
-          // bit must lie above all bits so far; a device the node does not have maps to 0 and fails the same test.
-          uint32_t mask = 0, rl = 0;
-          bool bad = n > 8 || (rmask >> n) != 0;
+    __syncthreads();  // every lane has its record: the stage can be refilled
+    if (tid == 0 && i + kTabStages < my_tiles) issue(i + kTabStages);
+
+    bool defer = false;
+    if (r < count) {
+      const uint32_t rmask = hd.x & 0xFFFFu;
+      const int n = (int)((hd.x >> 16) & 0xFFu);
+      const int size = (int)(hd.x >> 24);
+      const int flags = (int)(hd.y & 0xFFu);
+      const int n_req = __popc(rmask) + (int)((hd.y >> 8) & 0xFFu);
+      unsigned long long r0 = 0x8080808080808080ull;  // 8 x GPA_RES_END: the empty answer
+      // guards of besteffort_policy.go:35-45
+      if (!(size <= 0 || n < size || n_req > size)) {
+        // relabel: device -> its bit in the node order.  The list must be strictly ascending in that order, i.e. every
+        // bit must lie above all bits so far; a device the node does not have maps to 0 and fails the same test.
+        uint32_t mask = 0, rl = 0;
+        bool bad = n > 8 || (rmask >> n) != 0;
 #pragma unroll
-          for (int p = 0; p < 8; p++) {
-            const uint32_t d = (w[p >> 2] >> (8 * (p & 3))) & 0xFFu;
-            const uint32_t bit = p < n ? (uint32_t)s_bit[d] : 0x100u;
-            bad = bad | (bit <= mask);
-            mask |= bit & 0xFFu;
-            rl |= (rmask >> p & 1u) ? (bit & 0xFFu) : 0u;
-          }
-          if (bad) {
-            defer = true;
-            r0 ^= (unsigned long long)((kResDefer ^ 0x80) & 0xFF);
-          } else if (!(flags & GPA_REQ_FOREIGN)) {  // a required pointer that is in no set: every candidate is rejected (:53)
-            const uint32_t e = s_ans[ans_index(s_tern, mask, rl, size)];
-            const uint32_t chosen = e & 0xFFu;
-            const int n_nil = (int)(e >> 8);
-            r0 = s_dev[chosen];
-            // nil pads follow the devices (D5): GPA_RES_END (0x80) -> GPA_NIL (0xFF) in n_nil bytes
-            if (n_nil) r0 ^= (0x7F7F7F7F7F7F7F7Full >> (8 * (8 - n_nil))) << (8 * __popc(chosen));
-          }
+        for (int p = 0; p < 8; p++) {
+          const uint32_t d = ((p < 4 ? dv.x : dv.y) >> (8 * (p & 3))) & 0xFFu;
+          uint32_t bit = d < 8u ? (uint32_t)(bit_of >> (8 * d)) & 0xFFu : 0u;
+          bit = p < n ? bit : 0x100u;
+          bad = bad | (bit <= mask);
+          mask |= bit & 0xFFu;
+          rl |= (rmask >> p & 1u) ? (bit & 0xFFu) : 0u;
         }
-        uint4 v;
-        v.x = (uint32_t)r0;
-        v.y = (uint32_t)(r0 >> 32);
-        v.z = 0x80808080u;
-        v.w = 0x80808080u;
-        __stcs(reinterpret_cast<uint4 *>(out + r), v);
+        if (bad) {
+          defer = true;
+          r0 ^= (unsigned long long)((kResDefer ^ 0x80) & 0xFF);
+        } else if (!(flags & GPA_REQ_FOREIGN)) {  // a required pointer that is in no set: every candidate is rejected (:53)
+          const uint32_t e = s_ans[ans_index(s_tern, mask, rl, size)];
+          const uint32_t chosen = e & 0xFFu;
+          const int n_nil = (int)(e >> 8);
+          r0 = s_dev[chosen];
+          // nil pads follow the devices (D5): GPA_RES_END (0x80) -> GPA_NIL (0xFF) in n_nil bytes
+          if (n_nil) r0 ^= (0x7F7F7F7F7F7F7F7Full >> (8 * (8 - n_nil))) << (8 * __popc(chosen));
+        }
       }
-      if (defer_flags != nullptr) {
-        const unsigned any = __ballot_sync(0xffffffffu, defer);
-        if ((tid & 31) == 0 && r < count) defer_flags[r >> 5] = any ? 1 : 0;
-      }
+      uint4 v;
+      v.x = (uint32_t)r0;
+      v.y = (uint32_t)(r0 >> 32);
+      v.z = 0x80808080u;
+      v.w = 0x80808080u;
+      __stcs(reinterpret_cast<uint4 *>(out + r), v);
+    }
+    if (defer_flags != nullptr) {
+      const unsigned any = __ballot_sync(0xffffffffu, defer);
+      if ((tid & 31) == 0 && r < count) defer_flags[r >> 5] = any ? 1 : 0;
+    }
+  }
+}
+
+// 8-byte gpa_mask_request in, 4-byte gpa_mask_result out; nothing is ever deferred.
+constexpr int kMaskThreads = 512;
+__global__ void __launch_bounds__(kMaskThreads) besteffort_masks_table_kernel(const uint2 *__restrict__ mreqs, int count,
+                                                                              const FastTopo ft, uint32_t *__restrict__ mout) {
+  extern __shared__ __align__(128) unsigned char tsmem[];
+  unsigned long long *s_dev = reinterpret_cast<unsigned long long *>(tsmem);
+  uint16_t *s_tern = reinterpret_cast<uint16_t *>(s_dev + 256);
+  uint16_t *s_ans = s_tern + 256;
+  const int tid = threadIdx.x;
+  stage_tables(ft, s_dev, s_tern, s_ans, tid, kMaskThreads);
+  __syncthreads();
+
+  const uint32_t node_mask = (1u << ft.nt) - 1u;
+  auto answer = [&](uint32_t x, uint32_t y) -> uint32_t {
+    // {avail_mask:16, req_mask:16} {size:8, flags:8, n_req_extra:8, reserved:8} -> {chosen_mask:16, n_nil:8, status:8}
+    const uint32_t mask = x & 0xFFFFu, rl = x >> 16;
+    const int size = (int)(y & 0xFFu), flags = (int)((y >> 8) & 0xFFu);
+    const int n = __popc(mask);
+    const int n_req = __popc(rl) + (int)((y >> 16) & 0xFFu);
+    if (((mask | rl) & ~node_mask) != 0) return (uint32_t)(GPA_ERR_INVALID & 0xFF) << 24;
+    // guards of besteffort_policy.go:35-45; a required device that is not available is in no set (:53)
+    if (size <= 0 || n < size || n_req > size || (flags & GPA_REQ_FOREIGN) || (rl & ~mask) != 0) return 0u;
+    const uint32_t e = s_ans[ans_index(s_tern, mask, rl, size)];
+    return (e & 0xFFu) | ((e >> 8) << 16);
+  };
+  if (((reinterpret_cast<uintptr_t>(mreqs) & 15u) | (reinterpret_cast<uintptr_t>(mout) & 7u)) == 0) {
+    // two records per lane per step: 16 bytes in, 8 bytes out
+    const long long n_pairs = (long long)count >> 1;
+    for (long long p = (long long)blockIdx.x * kMaskThreads + tid; p < n_pairs; p += (long long)gridDim.x * kMaskThreads) {
+      const uint4 rec = __ldg(reinterpret_cast<const uint4 *>(mreqs) + p);
+      uint2 res;
+      res.x = answer(rec.x, rec.y);
+      res.y = answer(rec.z, rec.w);
+      reinterpret_cast<uint2 *>(mout)[p] = res;
+    }
+    if ((count & 1) && blockIdx.x == 0 && tid == 0) {
+      const uint2 rec = __ldg(mreqs + (count - 1));
+      mout[count - 1] = answer(rec.x, rec.y);
+    }
+  } else {  // buffers that only have the records' own 8 / 4-byte alignment
+    for (long long r = (long long)blockIdx.x * kMaskThreads + tid; r < count; r += (long long)gridDim.x * kMaskThreads) {
+      const uint2 rec = __ldg(mreqs + r);
+      mout[r] = answer(rec.x, rec.y);
     }
   }
 }

@@ -102,6 +102,41 @@ def topo_spiked(n, seed, spike_pair=None, spike=250):
     return t
 
 
+def spiked_uniform(n, pair, w=1, heavy=5):
+    """uniform PCIe weight 10*w everywhere, 10*heavy on one pair"""
+    t = topo_uniform(n, w)
+    a, b = pair
+    t[a, b, 0] = t[b, a, 0] = heavy
+    return links_to_weights(t)
+
+
+# Known answers derived BY HAND from besteffort_policy.go (not from the oracle), n = 14, k = 2 (m = 7 sets, no padding),
+# all pairs weigh 10 except one that weighs 50.  Every partition holding the heavy pair ties for the best score, so the
+# first one visited is saved (:57).  accum is grown at lengths 0, 1, 2, 4 (cap 1, 2, 4, 8): the array that holds a
+# candidate's sets 5..7 is made when its 5th set is appended, so the candidates sharing the first 5 sets share those two
+# slots, written in place by each of them in turn (:285, :247).  Under the first prefix (0,1)(2,3)(4,5)(6,7)(8,9) the
+# candidates are, in order, (10,11)(12,13) / (10,12)(11,13) / (10,13)(11,12).
+#   heavy pair   first best candidate      what bestPartition holds at :65      go_faithful   intended
+#   (12,13)      1st under the prefix      ...(10,13)(11,12): no heavy set      [0, 1]        [12, 13]
+#   (10,12)      2nd under the prefix      ...(10,13)(11,12): no heavy set      [0, 1]        [10, 12]
+#   (10,13)      3rd (last): not rewritten ...(10,13)(11,12)                    [10, 13]      [10, 13]
+#   (0,1)        1st                       tail rewritten, set (0,1) intact     [0, 1]        [0, 1]
+#   (2,5)        first with (2,5) is the first candidate under prefix (0,1)(2,5)(3,4)(6,7)(8,9); its tail ends as
+#                (10,13)(11,12), the heavy set sits in the private part         [2, 5]        [2, 5]
+# With 13 devices (one nil pad, m = 7) and the heavy pair (11,12): the first candidate holding it is
+# (0,1)(2,3)(4,5)(6,7)(8,9)(10,nil)(11,12) - (10,nil) passes the padding filter (:273-276) - and it is the LAST
+# candidate under its prefix, so nothing rewrites it: [11, 12] in both modes.
+HAND_DERIVED_D6 = [
+    (14, (12, 13), [0, 1], [12, 13]),
+    (14, (10, 12), [0, 1], [10, 12]),
+    (14, (10, 13), [10, 13], [10, 13]),
+    (14, (0, 1), [0, 1], [0, 1]),
+    (14, (2, 5), [2, 5], [2, 5]),
+    (13, (11, 12), [11, 12], [11, 12]),
+]
+
+
+
 def standard_topologies():
     """The 14 eight-GPU topologies of config 1: T0..T3 + ten seeded random ones."""
     topos = [("T0_zero", topo_zero(8)), ("T1_uniform", topo_uniform(8)), ("T2_b200_as_ref_sees_it", topo_two_sockets(8)),

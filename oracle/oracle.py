@@ -47,6 +47,8 @@ def lib():
                           C.POINTER(C.c_int), C.POINTER(C.c_ulonglong)]
         L.ref_partition_count.restype = C.c_ulonglong
         L.ref_partition_count.argtypes = [C.c_int, C.c_int]
+        L.ref_go_growcap.restype = C.c_int
+        L.ref_go_growcap.argtypes = [C.c_int, C.c_int, C.c_int]
         L.ref_link_type_score.restype = C.c_int
         L.ref_link_type_score.argtypes = [C.c_int]
         L.ref_links_to_weights.restype = None
@@ -87,6 +89,11 @@ def besteffort(W, nlinks, avail, req, size, mode=GO_FAITHFUL, variant="fast", wa
            len(rq), int(size), int(mode), out.ctypes.data_as(C.POINTER(C.c_int32)), C.byref(n_out), C.byref(visited))
     res = (rc, [int(x) for x in out[:n_out.value]])
     return res + (visited.value,) if want_visited else res
+
+
+def go_growcap(oldcap, needed, elemsize):
+    """capacity after an append() that had to grow (Go 1.17 runtime.growslice + roundupsize, restated)"""
+    return int(lib().ref_go_growcap(oldcap, needed, elemsize))
 
 
 def partition_count(n, k):

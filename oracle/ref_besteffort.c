@@ -143,7 +143,19 @@ static void *aalloc(ctx_t *c, size_t n)
     return p;
 }
 
-/* Go 1.17 runtime size classes (runtime/sizeclasses.go), enough for the sizes met here. */
+/* Go 1.17 runtime size classes, enough for the sizes met here.  This table is the ONE part of the oracle that cannot be
+ * derived from /root/reference (the Go runtime is not vendored): it restates, from the published Go 1.17 source,
+ *   src/runtime/sizeclasses.go  `var class_to_size = [_NumSizeClasses]uint16{0, 8, 16, 24, 32, 48, 64, 80, 96, 112,
+ *                               128, 144, ... 28672, 32768}` (68 classes, generated by mksizeclasses.go), and
+ *   src/runtime/msize.go        roundupsize(): sizes up to _MaxSmallSize (32768) round up to their class through
+ *                               size_to_class8 / size_to_class128, larger ones to a multiple of the 8 KiB page.
+ * growslice (src/runtime/slice.go, func growslice, "newcap := old.cap; doublecap := newcap + newcap; if cap >
+ * doublecap ... else if old.cap < 1024 { newcap = doublecap }", then `capmem = roundupsize(uintptr(newcap) *
+ * et.size); newcap = int(capmem / et.size)`) is restated below in go_growcap.  What the D6 analysis needs from all
+ * this is only the capacity sequence of a [][]*Device (24-byte headers) that starts empty: append grows it
+ * 0 -> 1 (24 B, class 24) -> 2 (48) -> 4 (96) -> 8 (192) -> 16 (384) -> 32 (768): every doubled capacity x 24 is
+ * itself a size class, so roundupsize never adds slack and cap is exactly 1, 2, 4, 8, 16, 32.
+ * tests/test_oracle_besteffort.py::test_go_growslice_capacity_sequence pins that sequence. */
 static const int go_size_classes[] = {8,    16,   24,   32,   48,   64,   80,   96,   112,  128,  144,  160,
                                       176,  192,  208,  224,  240,  256,  288,  320,  352,  384,  416,  448,
                                       480,  512,  576,  640,  704,  768,  896,  1024, 1152, 1280, 1408, 1536,
@@ -178,6 +190,9 @@ static int go_growcap(int oldcap, int needed, int elemsize)
     size_t mem = go_roundupsize((size_t)newcap * (size_t)elemsize);
     return (int)(mem / (size_t)elemsize);
 }
+
+/* the capacity rule alone, for tests/test_oracle_besteffort.py */
+int ref_go_growcap(int oldcap, int needed, int elemsize) { return go_growcap(oldcap, needed, elemsize); }
 
 /* append(s, v) for []*Device (8-byte elements). */
 static devslice append_dev(ctx_t *c, devslice s, int32_t v)
@@ -771,9 +786,18 @@ int ref_besteffort_fast(int nt, const int32_t *W, const uint8_t *nlinks, const i
     if (size <= 0 || n_avail < size || n_req > size)
         return REF_OK;
 
-    fast_t *f = (fast_t *)calloc(1, sizeof *f);
-    if (!f)
-        return REF_ERR_NOMEM;
+    /* on the stack, and only the scalars are initialised: cur[] / best[] / cur_score[] / cur_asym[] are always
+     * written before they are read (cur[d] when level d picks its set, best[] when have_best is set), so the
+     * restatement neither allocates nor clears 13 KB per request */
+    fast_t fast_storage;
+    fast_t *f = &fast_storage;
+    f->padding = 0;
+    f->prefix_id = f->prefix_ctr = 0;
+    f->have_best = 0;
+    f->bestScore = 0;
+    f->best_prefix_id = 0;
+    f->visited = 0;
+    f->panic_code = 0;
     f->W = W;
     f->nlinks = nlinks;
     f->nt = nt;
@@ -834,7 +858,6 @@ int ref_besteffort_fast(int nt, const int32_t *W, const uint8_t *nlinks, const i
             *n_out = size;
         }
     }
-    free(f);
     return rc;
 }
 

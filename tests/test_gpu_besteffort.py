@@ -222,6 +222,28 @@ def test_slice_aliasing_D6(ctx, oracle, n):
         assert ctx.besteffort(avail, [], 2, gpa.MODE_INTENDED)[1] == [n - 2, n - 1]
 
 
+def test_hand_derived_slice_aliasing_vectors(ctx):
+    """The known answers of synthetic.HAND_DERIVED_D6 - derived on paper from
+    besteffort_policy.go:57,247,285 and Go's append growth, NOT from the oracle - against the CUDA path itself."""
+    for n, pair, faithful, intended in syn.HAND_DERIVED_D6:
+        W, nl = syn.spiked_uniform(n, pair)
+        ctx.set_topology(W, nl)
+        ctx.set_device_order(list(range(n)))
+        for algo in (gpa.MODE_FORCE_ENUM, gpa.MODE_FORCE_DP, 0):
+            assert ctx.besteffort(list(range(n)), [], 2, gpa.MODE_GO_FAITHFUL | algo) == (gpa.OK, faithful), (n, pair, algo)
+            assert ctx.besteffort(list(range(n)), [], 2, gpa.MODE_INTENDED | algo) == (gpa.OK, intended), (n, pair, algo)
+    # SURVEY.md 8c (1), also derived by hand: 5 GPUs, k = 3, W01 = 150, W23 = W24 = W34 = 50, rest 10 -> [0, 1, nil]
+    W = np.full((5, 5), 10, dtype=np.int32)
+    np.fill_diagonal(W, 0)
+    W[0, 1] = W[1, 0] = 150
+    for i, j in ((2, 3), (2, 4), (3, 4)):
+        W[i, j] = W[j, i] = 50
+    ctx.set_topology(W, np.ones((5, 5), dtype=np.uint8))
+    ctx.set_device_order(list(range(5)))
+    for algo in (gpa.MODE_FORCE_ENUM, gpa.MODE_FORCE_DP, gpa.MODE_FORCE_KERNEL, 0):
+        assert ctx.besteffort([0, 1, 2, 3, 4], [], 3, algo) == (gpa.OK, [0, 1, gpa.NIL])
+
+
 @pytest.mark.parametrize("canonical", [True, False])
 def test_batch_n9_to_n12(ctx, oracle, canonical):
     """the batch kernels up to GPA_BATCH_MAX_AVAILABLE devices per request"""

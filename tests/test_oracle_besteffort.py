@@ -150,3 +150,37 @@ def test_alias_free_set_counts_agree_between_modes(oracle):
             a = oracle.besteffort(W, nl, list(range(n)), [], k, oracle.GO_FAITHFUL, "fast")
             b = oracle.besteffort(W, nl, list(range(n)), [], k, oracle.INTENDED, "fast")
             assert a == b
+
+
+def test_go_growslice_capacity_sequence(oracle):
+    """The D6 analysis rests on how append() grows a [][]*Device (24-byte slice headers) that starts empty: cap 1, 2, 4,
+    8, 16, 32 (Go 1.17 runtime.growslice doubles below 1024 elements and rounds the byte size up to a malloc size class;
+    24, 48, 96, 192, 384 and 768 bytes are all classes, so nothing is added).  Two published examples of the rounding
+    pin the size-class table itself: append to an empty []int64 of 5 elements gives cap 6 (40 -> 48 bytes), and 3
+    24-byte elements give cap 3 (72 -> 80 bytes)."""
+    cap, seq = 0, []
+    for length in range(1, 33):
+        if length > cap:
+            cap = oracle.go_growcap(cap, length, 24)
+            seq.append(cap)
+    assert seq == [1, 2, 4, 8, 16, 32]
+    cap, seq = 0, []
+    for length in range(1, 17):
+        if length > cap:
+            cap = oracle.go_growcap(cap, length, 8)
+            seq.append(cap)
+    assert seq == [1, 2, 4, 8, 16]
+    assert oracle.go_growcap(0, 5, 8) == 6
+    assert oracle.go_growcap(0, 3, 24) == 3
+
+
+HAND_DERIVED_D6 = syn.HAND_DERIVED_D6
+spiked_uniform = syn.spiked_uniform
+
+
+@pytest.mark.parametrize("n,pair,faithful,intended", HAND_DERIVED_D6)
+def test_hand_derived_slice_aliasing_vectors(oracle, n, pair, faithful, intended):
+    W, nl = spiked_uniform(n, pair)
+    for variant in ("literal", "fast"):
+        assert oracle.besteffort(W, nl, list(range(n)), [], 2, oracle.GO_FAITHFUL, variant) == (oracle.OK, faithful)
+        assert oracle.besteffort(W, nl, list(range(n)), [], 2, oracle.INTENDED, variant) == (oracle.OK, intended)
