@@ -3,22 +3,28 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 
-One step = one batch of container requests (the r.ContainerRequests loop of
+One step = one batch of 4 Mi container requests (the r.ContainerRequests loop of
 GetPreferredAllocation, cmd/nvidia-device-plugin/server.go:273-311, each answered by
 Policy.Allocate at :298) over one seeded synthetic stream:
 
-    8-GPU node, replicas = 1 (the best-effort branch, server.go:297-301), topology T2
-    "B200 as the reference sees it" (NVSwitch links invisible to nvml.GetNVLink, so PCIe
-    ancestry only: SameCPU inside each socket, CrossCPU across), free-GPU count uniform in
-    1..8, allocation size uniform in 1..|free|, a required device with p = 0.25.
+    8-GPU node, replicas = 1 (the best-effort branch, server.go:297-301), SYNTHETIC topology
+    T2 (two sockets: SameCPU = 20 inside each half, CrossCPU = 10 across, PCIe ancestry only,
+    as NVSwitch links are invisible to nvml.GetNVLink), free-GPU count uniform in 1..8,
+    allocation size uniform in 1..|free|, a required device with p = 0.25.
 
-Metric: decisions/s.  `value` times the batch kernel alone with inputs resident in HBM
-(CUDA events on the launching stream); `e2e` times the host-buffer C-ABI call
-gpa_besteffort_batch (pinned host memory -> HBM -> kernel -> pinned host memory);
-`cpu_baseline` is the oracle (the C restatement of the Go reference: there is no Go
-toolchain on this image) on a bounded sample, one core.  The line also carries the
-single-request machine-wide search (n = 16 physical, k = 3: 22.4 M candidate partitions)
-under "search_n16".
+Metric: decisions/s.
+  value  the batch kernels alone on 32-byte request records resident in HBM (CUDA events on
+         the launching stream);
+  e2e    the host-buffer C-ABI call a caller makes, pinned host memory -> HBM -> kernel ->
+         pinned host memory, on the 8-byte device-mask records (gpa_besteffort_batch_masks:
+         the format a cgo caller builds straight from its []*Device, INTEGRATION.md);
+         `e2e_records` is the same through the 32-byte id-list records (gpa_besteffort_batch)
+         and `e2e_packed` packs those id lists into mask records on the host INSIDE the timed
+         region (gpa_pack_mask_requests) before the mask call;
+  cpu_baseline  the oracle (the C restatement of the Go reference: there is no Go toolchain on
+         this image) on a bounded sample, one core, plus the all-thread figure.
+The line also carries the single-request machine-wide search (n = 16 physical, k = 3: 22.4 M
+candidate partitions) under "search_n16", single-decision latencies, and the replica sections.
 
 Multi-GPU: the path does not shard: --gpus N runs N independent replicas,
 one process per GPU, each on its own seeded batch; value = total decisions / max time.
@@ -44,16 +50,16 @@ from k8s_gpu_sharing_plugin_b200 import synthetic as syn  # noqa: E402
 METRIC = "GetPreferredAllocation decisions/sec (best-effort policy, 8 physical GPUs)"
 UNIT = "decisions/s"
 BATCH = 1 << 22           # requests per step per GPU: 128 MiB in + 64 MiB out > 126 MB of L2
-REF_BATCH = 1 << 18       # requests per step of the reference arm (bounded CPU sample)
+REF_BATCH = BATCH          # the reference arm runs the same step (about 0.4 s on 16 host threads)
 CPU_SAMPLE = 1 << 21      # requests of the one-core cpu_baseline sample
 N_DEV = 8
 
 
 def workload_config(n_gpus):
     return {
-        "workload": "configs[0]/[1] shape: 8-GPU node, replicas=1 (best-effort branch), topology T2 "
-                    "'B200 as the reference sees it', i.i.d. seeded stream: free GPUs U{1..8}, size U{1..free}, "
-                    "required device p=0.25",
+        "workload": "configs[0]/[1] shape: 8-GPU node, replicas=1 (best-effort branch), SYNTHETIC topology T2 "
+                    "(two sockets: 20 inside a half, 10 across; the box's own NVML matrix is timed as `box_topology`), "
+                    "i.i.d. seeded stream: free GPUs U{1..8}, size U{1..free}, required device p=0.25",
         "batch_requests_per_gpu": BATCH,
         "request_bytes": 32, "result_bytes": 16,
         "l2_policy": "inputs_larger_than_L2 (192 MiB touched per step)",
@@ -154,8 +160,10 @@ def dist_env():
 # ---------------------------------------------------------------------------------------
 def run_reference(args):
     """--impl reference: the reference's CPU implementation of the path.  The Go code cannot be
-    built here (no Go toolchain), so this times the oracle, its C restatement ("port"), sharded
-    over all host threads; rank 0 only."""
+    built here (no Go toolchain), so this times the oracle, its C restatement ("port"), on the
+    SAME step as the GPU arm (4 Mi requests of the same seeded stream), sharded over all host
+    threads; the one-core figure (the Go policy is single-threaded per request and kubelet
+    issues requests serially) is measured beside it on a bounded sample.  Rank 0 only."""
     rank, world, _ = dist_env()
     if rank != 0:
         return 0
@@ -171,14 +179,18 @@ def run_reference(args):
         orc.besteffort_batch(W, nl, reqs, threads=cores, out=out)
     dt = time.perf_counter() - t0
     value = args.steps * len(reqs) / dt
-    sample = "%d requests/step of the same seeded stream, %d host threads" % (len(reqs), cores)
-    cfg = workload_config(args.gpus)
-    cfg["batch_requests_per_gpu"] = REF_BATCH
+    one = reqs[:1 << 20]
+    t0 = time.perf_counter()
+    orc.besteffort_batch(W, nl, one, threads=1)
+    one_core = len(one) / (time.perf_counter() - t0)
+    sample = "%d requests/step, the GPU arm's own step (seed 1000), %d host threads" % (len(reqs), cores)
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "int32", "data": "synthetic", "config": cfg,
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "vs_baseline": None, "dtype": "int32", "data": "synthetic", "config": workload_config(args.gpus),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                         "one_core": {"value": one_core, "unit": UNIT, "cores": 1,
+                                      "sample": "first %d requests of the step, one thread" % len(one)}},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
         "note": "C restatement of the Go reference (oracle/), not Go: no Go toolchain on this image",
@@ -187,6 +199,29 @@ def run_reference(args):
 
 
 # ---------------------------------------------------------------------------------------
+def pin_to_gpu_cpus(gpu_index):
+    """Runs this rank on the CPUs NVML names as local to its GPU (and so first-touches its pinned buffers there).
+    Returns a description for the bench line; never fails the run."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = [64 * w + b for w, word in enumerate(words) for b in range(64) if word >> b & 1]
+        numa = None
+        try:
+            bus = pynvml.nvmlDeviceGetPciInfo(h).busId
+            bus = bus.decode() if isinstance(bus, bytes) else bus
+            numa = int(open("/sys/bus/pci/devices/%s/numa_node" % bus[-12:].lower()).read())
+        except Exception:  # noqa: BLE001
+            pass
+        if cpus:
+            os.sched_setaffinity(0, set(cpus) & os.sched_getaffinity(0) or os.sched_getaffinity(0))
+        return {"cpus": "%d-%d (%d)" % (min(cpus), max(cpus), len(cpus)) if cpus else None, "numa_node": numa}
+    except Exception as e:  # noqa: BLE001
+        return {"error": str(e)[:80]}
+
+
 def run_ours(args):
     import torch
     from k8s_gpu_sharing_plugin_b200 import _lib as gpa
@@ -194,6 +229,7 @@ def run_ours(args):
     rank, world, local = dist_env()
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fall-back")
+    affinity = pin_to_gpu_cpus(local)  # before any pinned buffer is allocated
     torch.cuda.set_device(local)
     use_dist = world > 1
     if use_dist:
@@ -205,19 +241,57 @@ def run_ours(args):
     ctx.set_topology_links(t)
     order = syn.sorted_positions(syn.node_uuids(N_DEV, seed=1))
     ctx.set_device_order(order)  # the node's sorted-UUID order, which is how the reference lists devices
-
-    # ---- device-resident arm: `value` -------------------------------------------------
-    d_in = torch.from_numpy(reqs.view(np.uint8).reshape(-1, 32)).cuda()
-    d_out = torch.empty((len(reqs), 16), dtype=torch.int8, device="cuda")
-    stream = torch.cuda.Stream()  # a non-default stream: the kernel and the events that time it share it
-
-    def step_device():
-        ctx.besteffort_batch_device(d_in.data_ptr(), len(reqs), N_DEV, d_out.data_ptr(), stream=stream.cuda_stream)
+    stream = torch.cuda.Stream()  # a non-default stream: the kernels and the events that time them share it
 
     def barrier():
         if use_dist:
             dist.barrier()
         torch.cuda.synchronize()
+
+    def max_over_ranks(*vals):
+        if not use_dist:
+            return [float(v) for v in vals]
+        tt = torch.tensor(list(vals), device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return [float(x) for x in tt.tolist()]
+
+    def min_over_ranks(*vals):
+        if not use_dist:
+            return [float(v) for v in vals]
+        tt = torch.tensor(list(vals), device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MIN)
+        return [float(x) for x in tt.tolist()]
+
+    # ---- host <-> device copy rate of this rank while every rank copies (what bounds every e2e number below) -------
+    pcie_buf = gpa.PinnedBuffer(1 << 28, np.dtype(np.uint8))
+    pcie_t = torch.from_numpy(pcie_buf.array)
+    pcie_d = torch.empty(1 << 28, dtype=torch.uint8, device="cuda")
+    rates = {}
+    for name, dst, src in (("h2d", pcie_d, pcie_t), ("d2h", pcie_t, pcie_d)):
+        dst.copy_(src, non_blocking=True)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(4):
+            dst.copy_(src, non_blocking=True)
+        e1.record()
+        torch.cuda.synchronize()
+        rates[name] = 4 * (1 << 28) / (e0.elapsed_time(e1) * 1e-3) / 1e9
+    barrier()
+    h2d_min, d2h_min = min_over_ranks(rates["h2d"], rates["d2h"])
+    pcie = {"h2d_gbs_this_rank": rates["h2d"], "d2h_gbs_this_rank": rates["d2h"], "h2d_gbs_min_over_ranks": h2d_min,
+            "d2h_gbs_min_over_ranks": d2h_min, "ranks_copying_at_once": world,
+            "what": "cudaMemcpyAsync of 256 MiB pinned <-> HBM, 4 reps, all ranks at the same time, one direction at a time",
+            "affinity": affinity}
+    del pcie_d, pcie_t
+    pcie_buf.free()
+
+    # ---- device-resident arm: `value` -------------------------------------------------
+    d_in = torch.from_numpy(reqs.view(np.uint8).reshape(-1, 32)).cuda()
+    d_out = torch.empty((len(reqs), 16), dtype=torch.int8, device="cuda")
+
+    def step_device():
+        ctx.besteffort_batch_device(d_in.data_ptr(), len(reqs), N_DEV, d_out.data_ptr(), stream=stream.cuda_stream)
 
     for _ in range(args.warmup):
         step_device()
@@ -235,12 +309,8 @@ def run_ours(args):
     e_all1.record(stream)
     barrier()
     launches = ctx.launch_count - launches0
-    total_ms = e_all0.elapsed_time(e_all1)
     kernel_ms = [a.elapsed_time(b) for a, b in evs]
-    if use_dist:
-        tt = torch.tensor([total_ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        total_ms = float(tt.item())
+    (total_ms,) = max_over_ranks(e_all0.elapsed_time(e_all1))
     value = world * args.steps * len(reqs) / (total_ms * 1e-3)
 
     # ---- parity of what was just timed (outside the timed region) -----------------------
@@ -252,28 +322,48 @@ def run_ours(args):
     want, _ = orc.besteffort_batch(W, nl, reqs[idx], threads=os.cpu_count() or 1)
     mismatches = int((got["dev"][idx] != want["dev"]).any(axis=1).sum())
 
-    # ---- end-to-end arm: host buffers through the C ABI ---------------------------------
+    def timed_host_arm(fn):
+        """W warm-up calls, then K calls between barriers; wall clock around calls that return only when their results
+        are in host memory; max over ranks -> (seconds per step, launches per step)"""
+        for _ in range(args.warmup):
+            fn()
+        barrier()
+        l0 = ctx.launch_count
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            fn()
+        dt = time.perf_counter() - t0
+        (dt,) = max_over_ranks(dt)
+        return dt / args.steps, (ctx.launch_count - l0) / args.steps
+
+    # ---- end-to-end arm (headline): mask records through the host-buffer C-ABI call ------------------------------
+    masks = syn.records_to_masks(reqs, order)
+    pin_min = gpa.PinnedBuffer(len(reqs), syn.MASK_REQ_DTYPE)
+    pin_mout = gpa.PinnedBuffer(len(reqs), syn.MASK_RES_DTYPE)
+    pin_min.array[:] = masks
+    e2e_s, e2e_launches = timed_host_arm(lambda: ctx.besteffort_batch_masks(pin_min.array, out=pin_mout.array))
+    e2e_value = world * len(reqs) / e2e_s
+    got_m = syn.mask_results_to_records(pin_mout.array[idx].copy(), order)
+    e2e_mismatch = int((got_m["dev"] != want["dev"]).any(axis=1).sum())
+
+    # ---- the same decisions from the 32-byte id-list records ----------------------------------------------------------
     pin_in = gpa.PinnedBuffer(len(reqs), syn.REQ_DTYPE)
     pin_out = gpa.PinnedBuffer(len(reqs), syn.RES_DTYPE)
     pin_in.array[:] = reqs
-    for _ in range(args.warmup):
-        ctx.besteffort_batch(pin_in.array, out=pin_out.array, max_avail=N_DEV)
-    barrier()
-    t0 = time.perf_counter()
-    launches_e2e0 = ctx.launch_count
-    for _ in range(args.steps):
-        ctx.besteffort_batch(pin_in.array, out=pin_out.array, max_avail=N_DEV)
-    e2e_s = time.perf_counter() - t0
-    if use_dist:
-        tt = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        e2e_s = float(tt.item())
-    launches_e2e = ctx.launch_count - launches_e2e0
-    e2e_value = world * args.steps * len(reqs) / e2e_s
-    e2e_mismatch = int((pin_out.array["dev"][idx] != want["dev"]).any(axis=1).sum())
+    rec_s, rec_launches = timed_host_arm(lambda: ctx.besteffort_batch(pin_in.array, out=pin_out.array, max_avail=N_DEV))
+    rec_mismatch = int((pin_out.array["dev"][idx] != want["dev"]).any(axis=1).sum())
 
-    # ---- the same stream as 8-byte device-mask records (gpa_besteffort_batch_masks): device-resident and end to end
-    masks = syn.records_to_masks(reqs, order)
+    # ---- id-list records packed into mask records on the host inside the timed region, results unpacked again ----------
+    def packed_step():
+        ctx.pack_mask_requests(pin_in.array, out=pin_min.array)
+        ctx.besteffort_batch_masks(pin_min.array, out=pin_mout.array)
+        ctx.unpack_mask_results(pin_mout.array, out=pin_out.array)
+
+    pin_out.array["dev"][:] = 0
+    packed_s, _ = timed_host_arm(packed_step)
+    packed_mismatch = int((pin_out.array["dev"][idx] != want["dev"]).any(axis=1).sum())
+
+    # ---- mask records resident in HBM ---------------------------------------------------------------------------------------
     d_min = torch.from_numpy(masks.view(np.uint8).reshape(-1, 8)).cuda()
     d_mout = torch.empty((len(reqs), 4), dtype=torch.uint8, device="cuda")
     for _ in range(args.warmup):
@@ -285,31 +375,22 @@ def run_ours(args):
         ctx.besteffort_batch_masks_device(d_min.data_ptr(), len(reqs), d_mout.data_ptr(), stream=stream.cuda_stream)
     m1.record(stream)
     barrier()
-    masks_ms = m0.elapsed_time(m1) / args.steps
-    pin_min = gpa.PinnedBuffer(len(reqs), syn.MASK_REQ_DTYPE)
-    pin_mout = gpa.PinnedBuffer(len(reqs), syn.MASK_RES_DTYPE)
-    pin_min.array[:] = masks
-    for _ in range(args.warmup):
-        ctx.besteffort_batch_masks(pin_min.array, out=pin_mout.array)
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        ctx.besteffort_batch_masks(pin_min.array, out=pin_mout.array)
-    masks_e2e_s = (time.perf_counter() - t0) / args.steps
     sampler.stop()
-    got_m = syn.mask_results_to_records(pin_mout.array[idx].copy(), order)
-    masks_mismatch = int((got_m["dev"] != want["dev"]).any(axis=1).sum())
-    if use_dist:
-        tt = torch.tensor([masks_ms, masks_e2e_s], device="cuda", dtype=torch.float64)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        masks_ms, masks_e2e_s = float(tt[0].item()), float(tt[1].item())
-    mask_format = {
-        "what": "same decisions from 8-byte device-mask records, 4-byte results (gpa_besteffort_batch_masks)",
-        "value": world * len(reqs) / (masks_ms * 1e-3), "ms_per_step": masks_ms,
-        "e2e": {"value": world * len(reqs) / masks_e2e_s, "unit": UNIT, "ms_per_step": masks_e2e_s * 1e3,
-                "h2d_bytes_per_step": 8 * len(reqs), "d2h_bytes_per_step": 4 * len(reqs)},
-        "mismatches": masks_mismatch,
+    (masks_ms,) = max_over_ranks(m0.elapsed_time(m1) / args.steps)
+    masks_dev_same = bool((d_mout.cpu().numpy().view(syn.MASK_RES_DTYPE).reshape(-1)[idx] == pin_mout.array[idx]).all())
+    other_formats = {
+        "mask_records_in_hbm": {"value": world * len(reqs) / (masks_ms * 1e-3), "unit": UNIT, "ms_per_step": masks_ms,
+                                "same_as_e2e_arm": masks_dev_same},
+        "e2e_records": {"value": world * len(reqs) / rec_s, "unit": UNIT, "ms_per_step": rec_s * 1e3,
+                        "h2d_bytes_per_step": 32 * len(reqs), "d2h_bytes_per_step": 16 * len(reqs), "mismatches": rec_mismatch,
+                        "gpu_launches_per_step": rec_launches,
+                        "path": "gpa_besteffort_batch: 32-byte id-list records, 256 Ki-request chunks pipelined over 4 streams"},
+        "e2e_packed": {"value": world * len(reqs) / packed_s, "unit": UNIT, "ms_per_step": packed_s * 1e3,
+                       "mismatches": packed_mismatch, "host_threads": os.cpu_count(),
+                       "path": "gpa_pack_mask_requests (host threads) -> gpa_besteffort_batch_masks -> gpa_unpack_mask_results, "
+                               "all three inside the timed region"},
     }
+    all_ok = mismatches == 0 and e2e_mismatch == 0 and rec_mismatch == 0 and packed_mismatch == 0 and masks_dev_same
 
     if rank != 0:
         if use_dist:
@@ -317,17 +398,17 @@ def run_ours(args):
         return 0
     if args.quick:  # profiling runs (ncu): the timed arms only
         print(json.dumps({"quick": True, "value": value, "ms_per_step": total_ms / args.steps, "kernel_ms": kernel_ms,
-                          "e2e_value": e2e_value, "e2e_ms_per_step": e2e_s / args.steps * 1e3, "mask_format": mask_format,
-                          "mismatches": [mismatches, e2e_mismatch, masks_mismatch], "gpu_launches": int(launches)}))
-        return 0 if mismatches == 0 and e2e_mismatch == 0 and masks_mismatch == 0 else 1
+                          "e2e_value": e2e_value, "e2e_ms_per_step": e2e_s * 1e3, "other_formats": other_formats, "pcie": pcie,
+                          "mismatches": [mismatches, e2e_mismatch, rec_mismatch, packed_mismatch], "gpu_launches": int(launches)}))
+        return 0 if all_ok else 1
 
-    # ---- roofline of the dominant kernel (the batch kernel is the only one in the step) --
+    # ---- roofline of the dominant kernel: besteffort_batch_table_kernel moves 48 bytes per decision; HBM binds ----------
     pair_evals = algorithmic_pair_evals(reqs)
-    alg_bytes = 4.0 * pair_evals
     avg_kernel_s = float(np.mean(kernel_ms)) * 1e-3
     peak, peak_src = measured_peak()
-    achieved = alg_bytes / avg_kernel_s / 1e9
-    traffic, traffic_src = None, None
+    io_bytes = 48.0 * len(reqs)
+    achieved = io_bytes / avg_kernel_s / 1e9
+    traffic, traffic_src, tj = None, None, {}
     tp = os.path.join(ROOT, "profiles", "latest_traffic.json")
     if os.path.exists(tp):
         tj = json.load(open(tp))
@@ -335,40 +416,79 @@ def run_ours(args):
             traffic = float(tj["dram_bytes_read"] + tj["dram_bytes_write"])
             traffic_src = tj["source"]
     issue = None
-    if traffic is not None and tj.get("warp_instructions"):
+    if tj.get("warp_instructions"):
         sm_count = torch.cuda.get_device_properties(local).multi_processor_count
         issue_peak = sm_count * 4 * 1.965e9  # 4 schedulers per SM, one warp instruction per clock each, max SM clock
         issue = {"warp_instructions_per_launch": tj["warp_instructions"], "achieved_per_s": tj["warp_instructions"] / avg_kernel_s,
                  "peak_per_s": issue_peak, "frac": tj["warp_instructions"] / avg_kernel_s / issue_peak,
-                 "note": "the binding ceiling of this kernel: warp instructions (ncu, profiles/) over SM issue slots"}
-    lut = None
-    try:
-        g = gpa.probe_lut(local, 8, 5)  # 2^8 entries = the score table of an 8-GPU node
-        lut = {"ceiling_glookups_per_s": g, "what": "dependent uint16 gathers from a 256-entry shared-memory table + IADD (SURVEY.md 8d)"}
-    except Exception as e:  # noqa: BLE001
-        lut = {"error": str(e)}
+                 "note": "warp instructions of one launch (ncu, profiles/) over SM issue slots: the second ceiling"}
     roofline = {
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
         "traffic_source": traffic_src,
-        "kernel": "besteffort_batch_fast_kernel (+ besteffort_batch_kernel deferred pass, ~1% of the step)",
+        "kernel": "besteffort_batch_table_kernel (+ the general kernel's deferred pass, which finds nothing to do)",
         "peak_source": peak_src + ", burst",
-        "algorithmic_bytes_per_launch": alg_bytes,
-        "io_bytes_per_launch": 48.0 * len(reqs), "io_gbs": 48.0 * len(reqs) / avg_kernel_s / 1e9,
-        "issue": issue, "smem_lut": lut,
-        "note": "algorithmic bytes = 4 B x pair evaluations the reference performs (SURVEY.md 8d); the kernel reads "
-                "set scores from a shared-memory table instead, so this is not DRAM traffic; io_* is the real "
-                "request+result traffic and `traffic` the DRAM bytes ncu saw for one launch. The kernel is "
-                "instruction-issue bound, not HBM bound (DESIGN.md 4)",
+        "bytes_per_launch": io_bytes,
+        "what": "achieved = the bytes the step must move (32-byte request + 16-byte result per decision) / event-timed step; "
+                "traffic = DRAM bytes ncu saw for one launch",
+        "issue": issue,
+        "reference_work_equivalent": {
+            "pair_evaluations_per_launch": pair_evals, "bytes": 4.0 * pair_evals, "gbs": 4.0 * pair_evals / avg_kernel_s / 1e9,
+            "note": "SURVEY.md 8d counts 4 B per pair evaluation the REFERENCE performs (partitions x m x C(k,2)); the kernel "
+                    "performs none of them per request (every answer of the node is tabulated once, at topology install), so "
+                    "this is a rate of reference work replaced, not memory traffic, and is not a roofline fraction"},
     }
 
-    # ---- CPU baseline: the oracle on one core, bounded sample ---------------------------
+    # ---- CPU baseline: the oracle on one core (the Go policy is single-threaded per request), bounded sample; the
+    #      all-thread figure beside it (independent requests sharded over the host's threads) ---------------------------
     sample = reqs[:CPU_SAMPLE]
     t0 = time.perf_counter()
     orc.besteffort_batch(W, nl, sample, threads=1)
     cpu_s = time.perf_counter() - t0
+    cores = os.cpu_count() or 1
+    t0 = time.perf_counter()
+    orc.besteffort_batch(W, nl, reqs, threads=cores)
+    cpu_all_s = time.perf_counter() - t0
     cpu_baseline = {"value": len(sample) / cpu_s, "unit": UNIT, "cores": 1, "kind": "port",
-                    "sample": "first %d requests of the step's batch, oracle/ref_besteffort.c (allocation-free "
-                              "restatement of the Go policy), one thread" % len(sample)}
+                    "sample": "first %d requests of the step's batch, oracle/ref_besteffort.c (C restatement of the Go "
+                              "policy; stack only, no heap), one thread" % len(sample),
+                    "all_cores": {"value": len(reqs) / cpu_all_s, "unit": UNIT, "cores": cores,
+                                  "sample": "the whole %d-request step, sharded over %d host threads" % (len(reqs), cores)}}
+
+    # ---- the box's own topology as a second timed matrix: what gpa_nvml_read_topology() returns in parity mode on this
+    #      machine when NVML shows the whole node, else the matrix recorded on the 8-GPU box (every pair SameCPU) ----
+    box_links, box_src = None, None
+    try:
+        nv = gpa.Nvml()
+        if nv.device_count() == N_DEV:
+            box_links, _ = nv.read_topology(gpa.TOPO_PARITY)
+            box_src = "NVML on this box, parity mode (%d GPUs visible)" % N_DEV
+        nv.close()
+    except Exception:  # noqa: BLE001
+        pass
+    if box_links is None:
+        box_links = syn.topo_uniform(N_DEV, 2)
+        box_src = "as recorded on the 8 x B200 box (profiles/r01_probe_8gpu.json: every pair SameCPU, no NVLink visible)"
+    Wb, nlb = syn.links_to_weights(box_links)
+    ctx.set_topology_links(box_links)
+    ctx.set_device_order(order)
+    for _ in range(3):
+        step_device()
+    torch.cuda.synchronize()
+    b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    b0.record(stream)
+    for _ in range(10):
+        step_device()
+    b1.record(stream)
+    torch.cuda.synchronize()
+    got["dev"] = d_out.cpu().numpy()
+    want_b, _ = orc.besteffort_batch(Wb, nlb, reqs[idx], threads=cores)
+    box_topology = {"source": box_src, "pair_weights": sorted(set(int(x) for x in Wb[~np.eye(N_DEV, dtype=bool)])),
+                    "value": len(reqs) / (b0.elapsed_time(b1) / 10 * 1e-3), "unit": UNIT, "ms_per_step": b0.elapsed_time(b1) / 10,
+                    "mismatches": int((got["dev"][idx] != want_b["dev"]).any(axis=1).sum()),
+                    "note": "same request stream, device-resident; the step time does not depend on the weights (one table "
+                            "lookup per request), the answers do"}
+    ctx.set_topology_links(t)
+    ctx.set_device_order(order)
 
     # ---- the machine-wide single search (config 3b): n = 16 physical, k = 3 ---------------
     t16 = syn.topo_random(16, 77)
@@ -398,74 +518,30 @@ def run_ours(args):
     ctx.set_topology_links(t)
     ctx.set_device_order(order)
 
-    # ---- latency of ONE decision through the C ABI, next to the oracle: small searches lose to the CPU -------
-    lat_n8 = []
-    for i in range(2200):
-        t0 = time.perf_counter()
-        ctx.besteffort(order, [], 3)          # n = 8, k = 3: 280 candidate partitions, one launch + D2H + sync
-        lat_n8.append(time.perf_counter() - t0)
-    lat_n8 = np.array(lat_n8[200:]) * 1e6
-    cpu_n8 = []
-    for i in range(2200):
-        t0 = time.perf_counter()
-        orc.besteffort(W, nl, order, [], 3)
-        cpu_n8.append(time.perf_counter() - t0)
-    cpu_n8 = np.array(cpu_n8[200:]) * 1e6
+    # ---- latency of ONE decision and the replica branch, timed natively (tools/*.cpp: C++ against the C ABI and the oracle,
+    #      no Python or ctypes inside the timed calls) ----------------------------------------------------------------------
+    def run_tool(name, *argv, timeout=300):
+        exe = os.path.join(ROOT, "tools", "bin", name)
+        if not os.path.exists(exe):
+            return {"error": "tools/bin/%s is not built (make -C tools)" % name}
+        try:
+            out = subprocess.run([exe] + [str(a) for a in argv], capture_output=True, text=True, timeout=timeout)
+            return json.loads(out.stdout)
+        except Exception as e:  # noqa: BLE001
+            return {"error": str(e)[:200]}
+
     t0 = time.perf_counter()
     orc.besteffort(W16, nl16, list(range(16)), [], 3)
     cpu_n16_ms = (time.perf_counter() - t0) * 1e3
     latency = {
-        "single_decision_n8_k3_us": {"gpu_call_p50": float(np.percentile(lat_n8, 50)), "gpu_call_p99": float(np.percentile(lat_n8, 99)),
-                                     "oracle_call_p50": float(np.percentile(cpu_n8, 50)), "oracle_call_p99": float(np.percentile(cpu_n8, 99)),
-                                     "note": "both timed from Python through ctypes; for n <= 8 the CPU path wins on latency"},
+        "single_decision_n8": run_tool("latency"),
         "single_decision_n16_k3_ms": {"gpu_call_p50": search16["call_ms_p50"], "oracle_call": cpu_n16_ms},
     }
-
-    # ---- replica mode (replicas > 1): the reference answers with prioritizeDevices (server.go:285-296), host code
-    #      here too; decisions/s and Allocate latency at 32 / 128 / 256 virtual devices through the plugin mirror ----
-    replica_mode = {}
-    for reps in (4, 16, 32):
-        uu = syn.node_uuids(N_DEV, seed=1)
-        devs = [{"id": uu[i], "index": str(i), "paths": ["/dev/nvidia%d" % i], "total_memory": 183359, "numa": i // 4,
-                 "nvml_index": i} for i in range(N_DEV)]
-        plug = gpa.Plugin(devs, ctx=ctx, replicas=reps, has_policy=True)
-        ids = [d["ID"] for d in plug.api_devices()]
-        rng = np.random.default_rng(reps)
-        streams = []
-        for _ in range(300):
-            free = [x for x in ids if rng.random() < 0.5]
-            rng.shuffle(free)
-            streams.append(([str(x) for x in free], int(rng.choice([1, 2, 4, 8]))))
-        t0 = time.perf_counter()
-        n_dec = 0
-        answers = []
-        for free, size in streams:
-            try:
-                answers.append(plug.get_preferred_allocation(free, [], size))
-            except gpa.PluginError:
-                answers.append(None)
-            n_dec += 1
-        dt_ours = time.perf_counter() - t0
-        t0 = time.perf_counter()
-        ref_answers = []
-        for free, size in streams:
-            res, kind, _ = orc.prioritize_devices(free, [], size)
-            ref_answers.append(res if kind in ("none", "non_unique") else None)
-        dt_ref = time.perf_counter() - t0
-        alloc_lat = []
-        for a in [x for x in answers if x][:300] * 4:
-            t0 = time.perf_counter()
-            plug.allocate(a)
-            alloc_lat.append(time.perf_counter() - t0)
-        alloc_lat = np.array(alloc_lat) * 1e6
-        replica_mode["%d_virtual_devices" % (N_DEV * reps)] = {
-            "get_preferred_allocation_per_s": n_dec / dt_ours, "oracle_prioritize_per_s": n_dec / dt_ref,
-            "mismatches": int(sum(1 for a, b in zip(answers, ref_answers) if a != b)),
-            "allocate_call_us_p50": float(np.percentile(alloc_lat, 50)), "allocate_call_us_p99": float(np.percentile(alloc_lat, 99)),
-        }
-        plug.close()
-    replica_mode["note"] = ("host C++ behind the C ABI on both sides of the comparison (no parallel work on this branch); timed from "
-                            "Python through ctypes, string marshalling included")
+    # replicas > 1: the reference answers with prioritizeDevices (server.go:285-296): host C++ here as well
+    replica_mode = {"get_preferred_allocation": run_tool("replica_bench"),
+                    "config2_stream": {"%d_virtual_devices" % (N_DEV * r): run_tool("stream", r, 100000) for r in (4, 16, 32)},
+                    "note": "prioritizeDevices / the GetPreferredAllocation -> Allocate stream at 32 / 128 / 256 virtual devices, "
+                            "one host thread, native on both sides of the comparison; no parallel work on this branch"}
 
     # ---- replica-set search (north_star's "k-subsets of the available replica set"; no reference counterpart - the
     #      reference answers replicas with prioritizeDevices above): one request at 32 / 128 / 256 virtual devices, half of
@@ -584,19 +660,20 @@ def run_ours(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "int32", "data": "synthetic", "config": workload_config(world),
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 32 * len(reqs), "d2h_bytes_per_step": 16 * len(reqs),
-                "ms_per_step": e2e_s / args.steps * 1e3, "gpu_launches": int(launches_e2e),
-                "path": "gpa_besteffort_batch: pinned host buffers, 256 Ki-request chunks pipelined over 4 streams"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 8 * len(reqs), "d2h_bytes_per_step": 4 * len(reqs),
+                "ms_per_step": e2e_s * 1e3, "gpu_launches_per_step": e2e_launches, "mismatches": e2e_mismatch,
+                "path": "gpa_besteffort_batch_masks: 8-byte device-mask records in pinned host memory -> HBM -> table kernel -> "
+                        "4-byte results back in pinned host memory; 1 Mi-request chunks pipelined over 4 streams"},
         "gpu_launches": int(launches),
-        "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": sampler.summary(),
+        "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": sampler.summary(), "pcie": pcie,
         "parity": {"checked": int(len(idx)), "mismatches_device_arm": mismatches, "mismatches_e2e_arm": e2e_mismatch},
-        "mask_format": mask_format, "search_n16": search16, "latency": latency, "replica_mode": replica_mode,
-        "replica_set": replica_set,
+        "other_formats": other_formats, "box_topology": box_topology, "search_n16": search16, "latency": latency,
+        "replica_mode": replica_mode, "replica_set": replica_set,
     }
     print(json.dumps(line))
     if use_dist:
         dist.destroy_process_group()
-    return 0 if mismatches == 0 and e2e_mismatch == 0 and masks_mismatch == 0 else 1
+    return 0 if all_ok and box_topology["mismatches"] == 0 else 1
 
 
 def main():

@@ -207,6 +207,19 @@ int gpa_besteffort_batch_masks(gpa_ctx *ctx, const gpa_mask_request *reqs, int c
 int gpa_besteffort_batch_masks_device(gpa_ctx *ctx, const gpa_mask_request *d_reqs, int count, int mode_flags,
                                       gpa_mask_result *d_out, void *stream);
 
+/* Host-side helpers for callers that hold id-list records but want the smaller transfer: gpa_pack_mask_requests()
+ * turns 32-byte gpa_request records into mask records (labels = the order of gpa_set_device_order()),
+ * gpa_unpack_mask_results() turns mask results back into device lists.  Plain host code on `threads` threads
+ * (0 = all hardware threads); nothing is decided here - the decisions are still made by the kernels.  A record whose
+ * device list is not ascending in the node order, or names a device the node does not have, cannot be a mask: it is
+ * packed as avail_mask 0xFFFF, which gpa_besteffort_batch_masks() answers with status GPA_ERR_INVALID, and counted in
+ * *n_unpackable (optional) - send those through gpa_besteffort_batch().
+ * ref: what the cgo glue does with available []*Device before the call, cmd/nvidia-device-plugin/
+ * server.go:274-279 (NewDevicesFrom keeps the order of the sorted uuids). */
+int gpa_pack_mask_requests(gpa_ctx *ctx, const gpa_request *reqs, int count, gpa_mask_request *out, int threads,
+                           int *n_unpackable);
+int gpa_unpack_mask_results(gpa_ctx *ctx, const gpa_mask_result *res, int count, gpa_result *out, int threads);
+
 /* Page-locked host memory for batch buffers: gpa_besteffort_batch() DMAs such buffers directly and stages pageable
  * ones through an internal pinned mailbox.  (No reference counterpart: Go has no device copies to feed.) */
 void *gpa_alloc_host(size_t bytes);

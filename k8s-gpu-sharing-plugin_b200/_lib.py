@@ -75,6 +75,10 @@ def lib():
     L.gpa_besteffort_batch_masks.argtypes = [vp, vp, C.c_int, C.c_int, vp]
     L.gpa_besteffort_batch_masks_device.restype = C.c_int
     L.gpa_besteffort_batch_masks_device.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp]
+    L.gpa_pack_mask_requests.restype = C.c_int
+    L.gpa_pack_mask_requests.argtypes = [vp, vp, C.c_int, vp, C.c_int, C.POINTER(C.c_int)]
+    L.gpa_unpack_mask_results.restype = C.c_int
+    L.gpa_unpack_mask_results.argtypes = [vp, vp, C.c_int, vp, C.c_int]
     L.gpa_alloc_host.restype = vp
     L.gpa_alloc_host.argtypes = [C.c_size_t]
     L.gpa_free_host.restype = None
@@ -305,6 +309,27 @@ class Context:
         if out is None:
             out = np.zeros(len(reqs), dtype=syn.MASK_RES_DTYPE)
         self._check(lib().gpa_besteffort_batch_masks(self._h, reqs.ctypes.data, len(reqs), int(mode), out.ctypes.data))
+        return out
+
+    def pack_mask_requests(self, reqs, out=None, threads=0):
+        """REQ_DTYPE id-list records -> (MASK_REQ_DTYPE records, number that cannot be masks); host code"""
+        from . import synthetic as syn
+        reqs = np.ascontiguousarray(reqs)
+        assert reqs.dtype == syn.REQ_DTYPE
+        if out is None:
+            out = np.zeros(len(reqs), dtype=syn.MASK_REQ_DTYPE)
+        bad = C.c_int(0)
+        self._check(lib().gpa_pack_mask_requests(self._h, reqs.ctypes.data, len(reqs), out.ctypes.data, int(threads), C.byref(bad)))
+        return out, bad.value
+
+    def unpack_mask_results(self, res, out=None, threads=0):
+        """MASK_RES_DTYPE results -> RES_DTYPE device lists; host code"""
+        from . import synthetic as syn
+        res = np.ascontiguousarray(res)
+        assert res.dtype == syn.MASK_RES_DTYPE
+        if out is None:
+            out = np.zeros(len(res), dtype=syn.RES_DTYPE)
+        self._check(lib().gpa_unpack_mask_results(self._h, res.ctypes.data, len(res), out.ctypes.data, int(threads)))
         return out
 
     def besteffort_batch_masks_device(self, d_reqs_ptr, count, d_out_ptr, mode=MODE_GO_FAITHFUL, stream=None):

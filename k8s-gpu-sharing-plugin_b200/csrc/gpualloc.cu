@@ -28,6 +28,7 @@
 #include <atomic>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <utility>
 #include <vector>
 
@@ -393,6 +394,27 @@ unsigned int next_seq(gpa_ctx *ctx) {
   return s;
 }
 
+}  // namespace
+
+namespace {
+template <typename F>
+void parallel_ranges(long long count, int threads, F &&fn) {
+  if (threads <= 0) threads = (int)std::thread::hardware_concurrency();
+  if (threads < 1) threads = 1;
+  if (threads > 64) threads = 64;
+  if (count < (1 << 16)) threads = 1;
+  if (threads == 1) {
+    fn(0, count);
+    return;
+  }
+  std::vector<std::thread> pool;
+  const long long per = (count + threads - 1) / threads;
+  for (int t = 0; t < threads; t++) {
+    const long long b = per * t < count ? per * t : count, e = per * (t + 1) < count ? per * (t + 1) : count;
+    if (b < e) pool.emplace_back([&fn, b, e] { fn(b, e); });
+  }
+  for (auto &th : pool) th.join();
+}
 }  // namespace
 
 extern "C" {
@@ -980,6 +1002,76 @@ int gpa_besteffort_batch_masks(gpa_ctx *ctx, const gpa_mask_request *reqs, int c
   return GPA_OK;
 }
 
+// ---- host-side conversion between the two batch formats (plain C++, no device work) ---------------------------
+int gpa_pack_mask_requests(gpa_ctx *ctx, const gpa_request *reqs, int count, gpa_mask_request *out, int threads,
+                           int *n_unpackable) {
+  if (!ctx || count < 0 || (count > 0 && (!reqs || !out))) return GPA_ERR_INVALID;
+  uint8_t rank[GPA_MAX_TOPOLOGY];
+  {
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!ctx->has_topo) return GPA_ERR_NO_TOPOLOGY;
+    if (!ctx->d_sfull) return GPA_ERR_TOO_LARGE;  // no node-wide label space: more than 12 GPUs or asymmetric link counts
+    memcpy(rank, ctx->fast.rank, sizeof rank);
+  }
+  std::atomic<int> bad_total{0};
+  parallel_ranges(count, threads, [&](long long b, long long e) {
+    int bad_here = 0;
+    for (long long i = b; i < e; i++) {
+      const gpa_request &r = reqs[i];
+      uint32_t mask = 0, rl = 0;
+      bool bad = r.n_avail > GPA_MAX_AVAILABLE || (r.n_avail < 16 && (r.req_mask >> r.n_avail) != 0);
+      const int n = r.n_avail > GPA_MAX_AVAILABLE ? 0 : r.n_avail;
+      for (int p = 0; p < n; p++) {
+        const int lab = r.avail[p] < GPA_MAX_TOPOLOGY ? rank[r.avail[p]] : 0xFF;
+        const uint32_t bit = lab < 16 ? 1u << lab : 0u;
+        bad = bad || bit <= mask;  // strictly ascending labels; an unknown device fails the same test
+        mask |= bit;
+        if (r.req_mask >> p & 1u) rl |= bit;
+      }
+      gpa_mask_request m;
+      m.avail_mask = bad ? (uint16_t)0xFFFF : (uint16_t)mask;
+      m.req_mask = bad ? (uint16_t)0 : (uint16_t)rl;
+      m.size = r.size;
+      m.flags = r.flags;
+      m.n_req_extra = r.n_req_extra;
+      m.reserved = 0;
+      out[i] = m;
+      bad_here += bad;
+    }
+    bad_total += bad_here;
+  });
+  if (n_unpackable) *n_unpackable = bad_total.load();
+  return GPA_OK;
+}
+
+int gpa_unpack_mask_results(gpa_ctx *ctx, const gpa_mask_result *res, int count, gpa_result *out, int threads) {
+  if (!ctx || count < 0 || (count > 0 && (!res || !out))) return GPA_ERR_INVALID;
+  uint8_t order[16];
+  {
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!ctx->has_topo) return GPA_ERR_NO_TOPOLOGY;
+    if (!ctx->d_sfull) return GPA_ERR_TOO_LARGE;
+    memcpy(order, ctx->fast.order, sizeof order);
+  }
+  parallel_ranges(count, threads, [&](long long b, long long e) {
+    for (long long i = b; i < e; i++) {
+      gpa_result o;
+      memset(o.dev, GPA_RES_END, sizeof o.dev);
+      const gpa_mask_result &m = res[i];
+      if (m.status != GPA_OK) {
+        o.dev[0] = GPA_RES_ERROR;
+        o.dev[1] = m.status;
+      } else {
+        int k = 0;
+        for (uint32_t c = m.chosen_mask; c; c &= c - 1) o.dev[k++] = (int8_t)order[__builtin_ctz(c)];
+        for (int q = 0; q < m.n_nil && k < GPA_MAX_AVAILABLE; q++) o.dev[k++] = GPA_NIL;
+      }
+      out[i] = o;
+    }
+  });
+  return GPA_OK;
+}
+
 #include "subset_host.inc"
 
 /* pinned host memory for batch buffers (so gpa_besteffort_batch can skip its staging copy) */
@@ -1044,7 +1136,7 @@ void na_msg(char *errbuf, int errbuf_len, const std::string &m) {
 
 // Once per device, with that device current: resolve the array's device address and load the
 // constant table the kernels read.  Neither call allocates.
-int noalloc_setup(int dev, char *errbuf, int errbuf_len) {
+int noalloc_setup(int dev, cudaStream_t st, char *errbuf, int errbuf_len) {
   NoallocDevice &d = g_noalloc_dev[dev];
   if (d.ready) return GPA_OK;
   void *p = nullptr;
@@ -1053,9 +1145,12 @@ int noalloc_setup(int dev, char *errbuf, int errbuf_len) {
     na_msg(errbuf, errbuf_len, std::string("cudaGetSymbolAddress(g_noalloc_scratch): ") + cudaGetErrorString(e));
     return GPA_ERR_CUDA;
   }
+  // The table goes in on the CALLER's stream, in front of the kernel that reads it, and the host waits for it (the
+  // source is a local): a copy on the default stream would not be ordered with a non-blocking caller stream.
   BinomTable b;
   fill_binom(b);
-  e = cudaMemcpyToSymbol(c_binom, &b, sizeof b);
+  e = cudaMemcpyToSymbolAsync(c_binom, &b, sizeof b, 0, cudaMemcpyHostToDevice, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, dev);
   if (e != cudaSuccess) {
     na_msg(errbuf, errbuf_len, std::string("no-alloc set-up: ") + cudaGetErrorString(e));
@@ -1125,20 +1220,23 @@ extern "C" int gpa_besteffort_batch_noalloc(int cuda_device, int n_topology, con
     na_msg(errbuf, errbuf_len, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
     return GPA_ERR_CUDA;
   }
-  int rc = noalloc_setup(cuda_device, errbuf, errbuf_len);
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc = noalloc_setup(cuda_device, st, errbuf, errbuf_len);
   if (rc != GPA_OK) return rc;
   const NoallocDevice &d = g_noalloc_dev[cuda_device];
-  cudaStream_t st = (cudaStream_t)stream;
   uint16_t *d_wq = reinterpret_cast<uint16_t *>(d.base + kNaWqOff);
   uint8_t *d_asym = d.base + kNaAsymOff;
   gpa_request *d_reqs = reinterpret_cast<gpa_request *>(d.base + kNaReqOff);
   gpa_result *d_out = reinterpret_cast<gpa_result *>(d.base + kNaResOff);
 
+  // On a failure the stream is drained before the lock on the array is given up: copies or the kernel queued so far
+  // may still be touching it, and the next caller must not overlap them.
 #define NA_TRY(expr)                                                              \
   do {                                                                            \
     cudaError_t e_ = (expr);                                                      \
     if (e_ != cudaSuccess) {                                                      \
       na_msg(errbuf, errbuf_len, std::string(#expr) + ": " + cudaGetErrorString(e_)); \
+      cudaStreamSynchronize(st);                                                  \
       return GPA_ERR_CUDA;                                                        \
     }                                                                             \
   } while (0)
@@ -1146,8 +1244,9 @@ extern "C" int gpa_besteffort_batch_noalloc(int cuda_device, int n_topology, con
   NA_TRY(cudaMemcpyAsync(d_asym, asym, (size_t)n * n, cudaMemcpyHostToDevice, st));
   NA_TRY(cudaMemcpyAsync(d_reqs, reqs, sizeof(gpa_request) * (size_t)count, cudaMemcpyHostToDevice, st));
   // The array still holds the previous call's answers.  The kernel writes every record it is
-  // asked for; clearing them first means a launch that fails cannot hand back stale answers.
-  NA_TRY(cudaMemsetAsync(d_out, 0, sizeof(gpa_result) * (size_t)count, st));
+  // asked for; clearing them first - to GPA_RES_END bytes, i.e. to empty answers - means a
+  // launch that fails cannot hand back stale ones.
+  NA_TRY(cudaMemsetAsync(d_out, 0x80, sizeof(gpa_result) * (size_t)count, st));
 
   int n_cap = max_avail < 2 ? 2 : max_avail;
   if (n_cap > GPA_BATCH_MAX_AVAILABLE) n_cap = GPA_BATCH_MAX_AVAILABLE;

@@ -91,6 +91,14 @@ __device__ __forceinline__ void bulk_load(void *smem_dst, const void *gmem_src, 
                : "memory");
 }
 
+// bit_of holds one byte per NVML index 0..7: that device's bit in the node order.  shr.b64 clamps shift amounts above
+// 63, so any other index (and the 0x80 filler) yields 0 without a compare.
+__device__ __forceinline__ uint32_t bit_of_device(unsigned long long bit_of, uint32_t d) {
+  unsigned long long r;
+  asm("shr.b64 %0, %1, %2;" : "=l"(r) : "l"(bit_of), "r"(d * 8u));
+  return (uint32_t)r & 0xFFu;
+}
+
 // 32-byte gpa_request in, 16-byte gpa_result out.  A record the table cannot answer (devices not in node order, unknown
 // device) is marked kResDefer for the general kernel, and its warp's byte in `defer_flags` (one per 32 records,
 // optional) is set so that the general kernel finds it without reading every result back.
@@ -106,14 +114,13 @@ __global__ void __launch_bounds__(kTabThreads, 1) besteffort_batch_table_kernel(
   unsigned long long *full = reinterpret_cast<unsigned long long *>(reinterpret_cast<unsigned char *>(s_ans) + table_ans_bytes(ft.ans_entries));
 
   const int tid = threadIdx.x;
-  const long long n_tiles = ((long long)count + kTabTile - 1) / kTabTile;
+  const int n_tiles = (int)(((long long)count + kTabTile - 1) / kTabTile);  // <= 2^21
   // tile i of this CTA is global tile blockIdx.x + i * gridDim.x
-  const long long my_tiles = blockIdx.x < n_tiles ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
-  auto issue = [&](long long i) {  // one thread: fill stage i % kTabStages with this CTA's tile i
-    const long long base = (blockIdx.x + i * (long long)gridDim.x) * kTabTile;
+  const int my_tiles = (int)blockIdx.x < n_tiles ? (n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  auto issue = [&](int i, int s) {  // one thread: fill stage s with this CTA's tile i
+    const long long base = ((long long)blockIdx.x + (long long)i * gridDim.x) * kTabTile;
     const long long left = (long long)count - base;
     const uint32_t bytes = (uint32_t)(left < kTabTile ? left : kTabTile) * (uint32_t)sizeof(gpa_request);
-    const int s = (int)(i % kTabStages);
     mbar_expect_tx(&full[s], bytes);
     bulk_load(ring + (size_t)s * kTabTile, reqs + base, bytes, &full[s]);
   };
@@ -121,7 +128,7 @@ __global__ void __launch_bounds__(kTabThreads, 1) besteffort_batch_table_kernel(
     for (int s = 0; s < kTabStages; s++) mbar_init(&full[s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     // the first tiles are on their way while the CTA stages its tables
-    for (long long i = 0; i < kTabStages && i < my_tiles; i++) issue(i);
+    for (int i = 0; i < kTabStages && i < my_tiles; i++) issue(i, i);
   }
   stage_tables(ft, s_dev, s_tern, s_ans, tid, kTabThreads);
   // device NVML index -> its bit in the node order, 8 x 8 bits (a node of up to 8 GPUs has NVML indices 0..7)
@@ -133,10 +140,11 @@ __global__ void __launch_bounds__(kTabThreads, 1) besteffort_batch_table_kernel(
   }
   __syncthreads();
 
-  for (long long i = 0; i < my_tiles; i++) {
-    const int s = (int)(i % kTabStages);
-    const long long r = (blockIdx.x + i * (long long)gridDim.x) * kTabTile + tid;
-    mbar_wait(&full[s], (uint32_t)((i / kTabStages) & 1));
+  int s = 0;
+  uint32_t parity = 0;
+  long long r = (long long)blockIdx.x * kTabTile + tid;
+  for (int i = 0; i < my_tiles; i++, r += (long long)gridDim.x * kTabTile) {
+    mbar_wait(&full[s], parity);
     // this lane's record: device bytes 0..7 and the 8 bytes of masks / sizes / flags (devices 8..15 cannot belong to a
     // request this table answers)
     uint2 dv = make_uint2(0, 0), hd = make_uint2(0, 0);
@@ -146,7 +154,11 @@ __global__ void __launch_bounds__(kTabThreads, 1) besteffort_batch_table_kernel(
       hd = rec[2];
     }
     __syncthreads();  // every lane has its record: the stage can be refilled
-    if (tid == 0 && i + kTabStages < my_tiles) issue(i + kTabStages);
+    if (tid == 0 && i + kTabStages < my_tiles) issue(i + kTabStages, s);
+    if (++s == kTabStages) {
+      s = 0;
+      parity ^= 1u;
+    }
 
     bool defer = false;
     if (r < count) {
@@ -158,19 +170,21 @@ __global__ void __launch_bounds__(kTabThreads, 1) besteffort_batch_table_kernel(
       unsigned long long r0 = 0x8080808080808080ull;  // 8 x GPA_RES_END: the empty answer
       // guards of besteffort_policy.go:35-45
       if (!(size <= 0 || n < size || n_req > size)) {
-        // relabel: device -> its bit in the node order.  The list must be strictly ascending in that order, i.e. every
-        // bit must lie above all bits so far; a device the node does not have maps to 0 and fails the same test.
-        uint32_t mask = 0, rl = 0;
-        bool bad = n > 8 || (rmask >> n) != 0;
+        // relabel: device -> its bit in the node order (a 64-bit shift picks the bit out of bit_of; a device the node
+        // does not have, and the filler beyond the n listed devices, shift everything out and add nothing).
+        const int nc = n < 8 ? n : 8;
+        const unsigned long long keep = nc >= 8 ? ~0ull : ((1ull << (8 * nc)) - 1ull);
+        const unsigned long long listed = ((unsigned long long)dv.x | ((unsigned long long)dv.y << 32)) & keep;
+        const unsigned long long actual = listed | (0x8080808080808080ull & ~keep);
+        uint32_t mask = 0;
 #pragma unroll
-        for (int p = 0; p < 8; p++) {
-          const uint32_t d = ((p < 4 ? dv.x : dv.y) >> (8 * (p & 3))) & 0xFFu;
-          uint32_t bit = d < 8u ? (uint32_t)(bit_of >> (8 * d)) & 0xFFu : 0u;
-          bit = p < n ? bit : 0x100u;
-          bad = bad | (bit <= mask);
-          mask |= bit & 0xFFu;
-          rl |= (rmask >> p & 1u) ? (bit & 0xFFu) : 0u;
-        }
+        for (int p = 0; p < 8; p++) mask |= bit_of_device(bit_of, (uint32_t)(actual >> (8 * p)) & 0xFFu);
+        // The list must be strictly ascending in the node order.  A set of devices has exactly one such list, the one
+        // the result path keeps in s_dev[mask]: n distinct known devices whose bytes equal it are in order.
+        const bool bad = n > 8 || (rmask >> nc) != 0 || __popc(mask) != n || s_dev[mask] != actual;
+        uint32_t rl = 0;
+        for (uint32_t rm = bad ? 0u : rmask; rm; rm &= rm - 1u)
+          rl |= bit_of_device(bit_of, (uint32_t)(actual >> (8 * (__ffs(rm) - 1))) & 0xFFu);
         if (bad) {
           defer = true;
           r0 ^= (unsigned long long)((kResDefer ^ 0x80) & 0xFF);

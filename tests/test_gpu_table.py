@@ -200,3 +200,27 @@ def test_mask_records_from_the_table(ctx, oracle):
                 assert got["chosen_mask"][4] == 0 and got["status"][4] == 0
                 ok[3] = ok[4] = True
             assert ok.all(), (count, mode, int(np.nonzero(~ok)[0][0]))
+
+
+def test_host_pack_and_unpack_helpers(ctx, oracle):
+    """gpa_pack_mask_requests / gpa_unpack_mask_results: id-list records -> mask records -> decisions -> device lists gives
+    the oracle's answers; records that cannot be masks are counted and come back as GPA_ERR_INVALID"""
+    name, t = syn.standard_topologies()[5]
+    W, nl = syn.links_to_weights(t)
+    ctx.set_topology_links(t)
+    ctx.set_device_order(ORDER8)
+    for count in (5, 70001):
+        reqs = syn.random_request_batch(8, count, seed=count, order=ORDER8)
+        packed, n_bad = ctx.pack_mask_requests(reqs)
+        assert n_bad == 0
+        ref = syn.records_to_masks(reqs, ORDER8)
+        assert (packed.view(np.uint8) == ref.view(np.uint8)).all()
+        res = ctx.unpack_mask_results(ctx.besteffort_batch_masks(packed))
+        want, _ = oracle.besteffort_batch(W, nl, reqs, threads=8)
+        assert (res["dev"] == want["dev"]).all()
+    bad = syn.pack_requests([(list(reversed(ORDER8)), [], 2), ([ORDER8[0], 9], [], 1), (ORDER8[:3], [], 2)])
+    packed, n_bad = ctx.pack_mask_requests(bad)
+    assert n_bad == 2 and packed["avail_mask"].tolist()[:2] == [0xFFFF, 0xFFFF] and packed["avail_mask"][2] == 0b111
+    res = ctx.unpack_mask_results(ctx.besteffort_batch_masks(packed))
+    assert gpa.decode_result(res[0]) == (gpa.ERR_INVALID, []) and gpa.decode_result(res[1]) == (gpa.ERR_INVALID, [])
+    assert gpa.decode_result(res[2])[0] == gpa.OK

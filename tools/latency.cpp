@@ -43,27 +43,44 @@ int main() {
   if (gpa_create(0, &ctx) != GPA_OK) return 2;
   if (gpa_set_topology(ctx, n, W, nl) != GPA_OK) return 3;
   int32_t avail[8] = {0, 1, 2, 3, 4, 5, 6, 7}, out[16], out2[16];
-  printf("{\"what\": \"one decision, n=8, native C ABI vs oracle (one host thread), microseconds\", \"cases\": [");
-  for (int k = 1; k <= 8; k++) {
-    std::vector<double> g, c;
-    int n_out = 0, n_out2 = 0;
-    for (int i = 0; i < 2200; i++) {
-      auto t0 = std::chrono::steady_clock::now();
-      gpa_besteffort(ctx, avail, n, nullptr, 0, k, GPA_MODE_GO_FAITHFUL, out, &n_out);
-      auto t1 = std::chrono::steady_clock::now();
-      ref_besteffort_fast(n, W, nl, avail, n, nullptr, 0, k, 0, out2, &n_out2, nullptr);
-      auto t2 = std::chrono::steady_clock::now();
-      if (i >= 200) {
-        g.push_back(std::chrono::duration<double, std::micro>(t1 - t0).count());
-        c.push_back(std::chrono::duration<double, std::micro>(t2 - t1).count());
+  printf("{\"what\": \"one decision on an 8-GPU node, native C ABI vs oracle (one host thread), microseconds; "
+         "table = gpa_besteffort default (host copy of the GPU-built answer table, no launch), kernel = GPA_MODE_FORCE_KERNEL "
+         "(one-warp kernel + mapped mailbox)\", \"cases\": [");
+  bool first = true;
+  for (int with_req = 0; with_req < 2; with_req++)
+    for (int k = 1; k <= 8; k++) {
+      const int32_t req[1] = {3};
+      const int n_req = with_req;
+      std::vector<double> tb, g, c;
+      int n_out = 0, n_out2 = 0, n_out3 = 0;
+      int32_t out3[16];
+      for (int i = 0; i < 4200; i++) {
+        auto t0 = std::chrono::steady_clock::now();
+        gpa_besteffort(ctx, avail, n, req, n_req, k, GPA_MODE_GO_FAITHFUL, out3, &n_out3);
+        auto t1 = std::chrono::steady_clock::now();
+        ref_besteffort_fast(n, W, nl, avail, n, req, n_req, k, 0, out2, &n_out2, nullptr);
+        auto t2 = std::chrono::steady_clock::now();
+        if (i >= 200) {
+          tb.push_back(std::chrono::duration<double, std::micro>(t1 - t0).count());
+          c.push_back(std::chrono::duration<double, std::micro>(t2 - t1).count());
+        }
+        if (i % 2 == 0) {
+          auto t3 = std::chrono::steady_clock::now();
+          gpa_besteffort(ctx, avail, n, req, n_req, k, GPA_MODE_GO_FAITHFUL | GPA_MODE_FORCE_KERNEL, out, &n_out);
+          auto t4 = std::chrono::steady_clock::now();
+          if (i >= 200) g.push_back(std::chrono::duration<double, std::micro>(t4 - t3).count());
+        }
       }
+      bool same = n_out == n_out2 && std::equal(out, out + n_out, out2) && n_out3 == n_out2 && std::equal(out3, out3 + n_out3, out2);
+      std::sort(tb.begin(), tb.end());
+      std::sort(g.begin(), g.end());
+      std::sort(c.begin(), c.end());
+      printf("%s{\"k\": %d, \"required\": %d, \"table_p50\": %.3f, \"table_p99\": %.3f, \"kernel_p50\": %.1f, \"kernel_p99\": %.1f, "
+             "\"oracle_p50\": %.3f, \"oracle_p99\": %.3f, \"same\": %s}",
+             first ? "" : ", ", k, n_req, tb[tb.size() / 2], tb[(size_t)(tb.size() * 0.99)], g[g.size() / 2], g[(size_t)(g.size() * 0.99)],
+             c[c.size() / 2], c[(size_t)(c.size() * 0.99)], same ? "true" : "false");
+      first = false;
     }
-    bool same = n_out == n_out2 && std::equal(out, out + n_out, out2);
-    std::sort(g.begin(), g.end());
-    std::sort(c.begin(), c.end());
-    printf("%s{\"k\": %d, \"gpu_p50\": %.1f, \"gpu_p99\": %.1f, \"oracle_p50\": %.2f, \"oracle_p99\": %.2f, \"same\": %s}", k > 1 ? ", " : "", k,
-           g[g.size() / 2], g[(size_t)(g.size() * 0.99)], c[c.size() / 2], c[(size_t)(c.size() * 0.99)], same ? "true" : "false");
-  }
   printf("],\n \"replica_set\": [");
   // replica-set search (gpa_subset_besteffort, count-vector kernel): 4 of the free replicas, every second replica free
   const int reps_of[3] = {4, 16, 32};

@@ -124,7 +124,7 @@ int main(int argc, char **argv) {
   printf("{\"what\": \"config 2: stateful GetPreferredAllocation -> Allocate / free stream, seed 2, host C++ behind the C ABI, one "
          "thread\", \"virtual_devices\": %zu, \"steps\": %ld, \"decisions\": %ld, \"allocations\": %ld, \"frees\": %ld, "
          "\"request_errors_no_devices_left\": %ld, \"mismatches_vs_oracle\": %ld, \"decisions_per_s\": %.0f, "
-         "\"oracle_decisions_per_s\": %.0f, \"preferred_us\": {\"p50\": %.2f, \"p99\": %.2f}, \"allocate_us\": {\"p50\": %.2f, "
+         "\"oracle_prioritize_only_per_s\": %.0f, \"preferred_us\": {\"p50\": %.2f, \"p99\": %.2f}, \"allocate_us\": {\"p50\": %.2f, "
          "\"p99\": %.2f}}\n",
          n_virtual, steps, decisions, allocs, frees, errors, mismatches, decisions / t_pref, decisions / t_ref, pct(lat_pref, 0.5),
          pct(lat_pref, 0.99), pct(lat_alloc, 0.5), pct(lat_alloc, 0.99));
