@@ -91,13 +91,17 @@ __device__ __forceinline__ void bulk_load(void *smem_dst, const void *gmem_src, 
                : "memory");
 }
 
-// bit_of holds one byte per NVML index 0..7: that device's bit in the node order.  shr.b64 clamps shift amounts above
-// 63, so any other index (and the 0x80 filler) yields 0 without a compare.
-__device__ __forceinline__ uint32_t bit_of_device(unsigned long long bit_of, uint32_t d) {
-  unsigned long long r;
-  asm("shr.b64 %0, %1, %2;" : "=l"(r) : "l"(bit_of), "r"(d * 8u));
-  return (uint32_t)r & 0xFFu;
+// Byte tricks of the relabel step.  nibbles_of_bytes: bytes 0x0a 0x0b 0x0c 0x0d (low to high) -> 0xdcba, the selector
+// of a byte permute; or_of_bytes: OR of the four bytes; bytes_of_bits: bits 0..3 -> bytes 0x00 / 0xFF.
+__device__ __forceinline__ uint32_t nibbles_of_bytes(uint32_t w) {
+  const uint32_t t = (w | (w >> 4)) & 0x00FF00FFu;
+  return (t | (t >> 8)) & 0xFFFFu;
 }
+__device__ __forceinline__ uint32_t or_of_bytes(uint32_t x) {
+  x |= x >> 16;
+  return (x | (x >> 8)) & 0xFFu;
+}
+__device__ __forceinline__ uint32_t bytes_of_bits(uint32_t b4) { return ((b4 * 0x00204081u) & 0x01010101u) * 0xFFu; }
 
 // 32-byte gpa_request in, 16-byte gpa_result out.  A record the table cannot answer (devices not in node order, unknown
 // device) is marked kResDefer for the general kernel, and its warp's byte in `defer_flags` (one per 32 records,
@@ -131,12 +135,15 @@ __global__ void __launch_bounds__(kTabThreads, 1) besteffort_batch_table_kernel(
     for (int i = 0; i < kTabStages && i < my_tiles; i++) issue(i, i);
   }
   stage_tables(ft, s_dev, s_tern, s_ans, tid, kTabThreads);
-  // device NVML index -> its bit in the node order, 8 x 8 bits (a node of up to 8 GPUs has NVML indices 0..7)
-  unsigned long long bit_of = 0;
+  // device NVML index -> its bit in the node order, an 8-byte table in two registers (a node of up to 8 GPUs has NVML
+  // indices 0..7)
+  uint32_t bit_lo = 0, bit_hi = 0;
 #pragma unroll
   for (int d = 0; d < 8; d++) {
     const int lab = ft.rank[d];
-    bit_of |= (unsigned long long)(lab < 8 ? (1u << lab) : 0u) << (8 * d);
+    const uint32_t b = (lab < 8 ? (1u << lab) : 0u) << (8 * (d & 3));
+    if (d < 4) bit_lo |= b;
+    else bit_hi |= b;
   }
   __syncthreads();
 
@@ -170,21 +177,22 @@ __global__ void __launch_bounds__(kTabThreads, 1) besteffort_batch_table_kernel(
       unsigned long long r0 = 0x8080808080808080ull;  // 8 x GPA_RES_END: the empty answer
       // guards of besteffort_policy.go:35-45
       if (!(size <= 0 || n < size || n_req > size)) {
-        // relabel: device -> its bit in the node order (a 64-bit shift picks the bit out of bit_of; a device the node
-        // does not have, and the filler beyond the n listed devices, shift everything out and add nothing).
+        // relabel: device -> its bit in the node order, four devices per PRMT: bit_of is an 8-byte table, a byte-permute
+        // selector holds four table indices, one per nibble.  Bytes beyond the n listed devices are cleared afterwards;
+        // a listed byte that is no device of the node (>= 8) makes the lookup meaningless, and is caught below.
         const int nc = n < 8 ? n : 8;
         const unsigned long long keep = nc >= 8 ? ~0ull : ((1ull << (8 * nc)) - 1ull);
-        const unsigned long long listed = ((unsigned long long)dv.x | ((unsigned long long)dv.y << 32)) & keep;
-        const unsigned long long actual = listed | (0x8080808080808080ull & ~keep);
-        uint32_t mask = 0;
-#pragma unroll
-        for (int p = 0; p < 8; p++) mask |= bit_of_device(bit_of, (uint32_t)(actual >> (8 * p)) & 0xFFu);
+        const uint32_t keep_lo = (uint32_t)keep, keep_hi = (uint32_t)(keep >> 32);
+        const uint32_t bits_lo = __byte_perm(bit_lo, bit_hi, nibbles_of_bytes(dv.x)) & keep_lo;
+        const uint32_t bits_hi = __byte_perm(bit_lo, bit_hi, nibbles_of_bytes(dv.y)) & keep_hi;
+        const uint32_t mask = or_of_bytes(bits_lo | bits_hi);
+        const unsigned long long actual = (((unsigned long long)dv.x | ((unsigned long long)dv.y << 32)) & keep) |
+                                          (0x8080808080808080ull & ~keep);
         // The list must be strictly ascending in the node order.  A set of devices has exactly one such list, the one
-        // the result path keeps in s_dev[mask]: n distinct known devices whose bytes equal it are in order.
+        // the result path keeps in s_dev[mask]: n distinct devices whose bytes equal it are known, and in order.
         const bool bad = n > 8 || (rmask >> nc) != 0 || __popc(mask) != n || s_dev[mask] != actual;
-        uint32_t rl = 0;
-        for (uint32_t rm = bad ? 0u : rmask; rm; rm &= rm - 1u)
-          rl |= bit_of_device(bit_of, (uint32_t)(actual >> (8 * (__ffs(rm) - 1))) & 0xFFu);
+        // required positions -> label bits: spread the 8 position bits into byte masks and select
+        const uint32_t rl = or_of_bytes((bits_lo & bytes_of_bits(rmask & 0xFu)) | (bits_hi & bytes_of_bits((rmask >> 4) & 0xFu)));
         if (bad) {
           defer = true;
           r0 ^= (unsigned long long)((kResDefer ^ 0x80) & 0xFF);
