@@ -357,6 +357,14 @@ const char *gpa_nvml_last_error(gpa_nvml *nv);
 int gpa_nvml_device_count(gpa_nvml *nv, int *n);
 int gpa_nvml_device_uuid(gpa_nvml *nv, int index, char *buf, int cap);
 
+/* What the daemon needs to know about GPU `index` besides its UUID: TotalMemory in MiB as the plugin computes it (free +
+ * used, each already divided down to MiB; it sizes auto replicas, server.go:100-103), the minor number behind
+ * /dev/nvidia<minor>, the NUMA node for TopologyInfo (-1 = none) and the PCI bus id.  Any output may be NULL.
+ * ref: GpuDeviceManager.Devices + buildDevice, cmd/nvidia-device-plugin/nvidia.go:85-99,162-178; nvml.NewDeviceLite,
+ * nvml/nvml.go:449-486; numaNode, nvml.go:314-332; deviceGetMemoryInfo, nvml/bindings.go:491-520. */
+int gpa_nvml_device_info(gpa_nvml *nv, int index, unsigned long long *total_memory_mib, int *minor, int *numa_node, char *bus_id,
+                         int bus_id_cap);
+
 #define GPA_TOPO_PARITY 0          /* the matrix the reference builds: NVLinks counted only when the far end of a
                                       link IS the peer GPU (so none through an NVSwitch), links 0..11 only */
 #define GPA_TOPO_NVSWITCH_AWARE 1  /* extension, no reference counterpart: all 18 links, and two GPUs that both

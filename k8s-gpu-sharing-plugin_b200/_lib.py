@@ -469,6 +469,17 @@ class Nvml:
         self._check(lib().gpa_nvml_device_uuid(self._h, i, buf, len(buf)))
         return buf.value.decode()
 
+    def device_info(self, i):
+        """-> {"total_memory": MiB, "minor": n or -1, "numa": node or -1, "bus_id": str} (gpa_nvml_device_info)"""
+        L = lib()
+        L.gpa_nvml_device_info.restype = C.c_int
+        L.gpa_nvml_device_info.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_ulonglong), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                           C.c_char_p, C.c_int]
+        mem, minor, numa = C.c_ulonglong(0), C.c_int(-1), C.c_int(-1)
+        bus = C.create_string_buffer(64)
+        self._check(L.gpa_nvml_device_info(self._h, int(i), C.byref(mem), C.byref(minor), C.byref(numa), bus, len(bus)))
+        return {"total_memory": int(mem.value), "minor": minor.value, "numa": numa.value, "bus_id": bus.value.decode()}
+
     def read_topology(self, flags=TOPO_PARITY):
         """-> (links2[n, n, 2] int32, nvml_calls)"""
         n = C.c_int(0)

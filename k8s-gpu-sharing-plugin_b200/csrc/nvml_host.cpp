@@ -67,6 +67,8 @@ struct gpa_nvml {
   nvmlReturn_t (*DeviceGetHandleByIndex)(unsigned int, nvmlDevice_t *) = nullptr;
   nvmlReturn_t (*DeviceGetUUID)(nvmlDevice_t, char *, unsigned int) = nullptr;
   nvmlReturn_t (*DeviceGetPciInfo)(nvmlDevice_t, nvmlPciInfo_t *) = nullptr;
+  nvmlReturn_t (*DeviceGetMemoryInfo)(nvmlDevice_t, nvmlMemory_t *) = nullptr;
+  nvmlReturn_t (*DeviceGetMinorNumber)(nvmlDevice_t, unsigned int *) = nullptr;
   nvmlReturn_t (*DeviceGetTopologyCommonAncestor)(nvmlDevice_t, nvmlDevice_t, nvmlGpuTopologyLevel_t *) = nullptr;
   nvmlReturn_t (*DeviceGetNvLinkState)(nvmlDevice_t, unsigned int, nvmlEnableState_t *) = nullptr;
   nvmlReturn_t (*DeviceGetNvLinkRemotePciInfo)(nvmlDevice_t, unsigned int, nvmlPciInfo_t *) = nullptr;
@@ -129,6 +131,8 @@ int gpa_nvml_open(const char *libpath, gpa_nvml **out) {
   // optional ones: the reference treats a missing symbol as "unknown" (bindings.go:249-252) or falls back (:100-103)
   load_sym(nv->handle, "nvmlDeviceGetTopologyCommonAncestor", nv->DeviceGetTopologyCommonAncestor);
   load_sym(nv->handle, "nvmlDeviceGetNvLinkRemoteDeviceType", nv->DeviceGetNvLinkRemoteDeviceType);
+  load_sym(nv->handle, "nvmlDeviceGetMemoryInfo", nv->DeviceGetMemoryInfo);
+  load_sym(nv->handle, "nvmlDeviceGetMinorNumber", nv->DeviceGetMinorNumber);
   if (!load_sym(nv->handle, "nvmlEventSetWait_v2", nv->EventSetWait)) ok &= load_sym(nv->handle, "nvmlEventSetWait", nv->EventSetWait);
   if (!ok) {
     fprintf(stderr, "gpa_nvml_open: %s lacks a required NVML symbol\n", path);
@@ -183,6 +187,80 @@ int gpa_nvml_device_uuid(gpa_nvml *nv, int index, char *buf, int cap) {
   if (r != NVML_SUCCESS) {
     nv->last_error = nv->err("nvmlDeviceGetUUID", r);
     return GPA_ERR_NVML;
+  }
+  return GPA_OK;
+}
+
+int gpa_nvml_device_info(gpa_nvml *nv, int index, unsigned long long *total_memory_mib, int *minor, int *numa_node, char *bus_id,
+                         int bus_id_cap) {
+  if (!nv || index < 0) return GPA_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(nv->mu);
+  nvmlDevice_t d;
+  nvmlReturn_t r = nv->DeviceGetHandleByIndex((unsigned)index, &d);
+  nv->calls++;
+  if (r != NVML_SUCCESS) {
+    nv->last_error = nv->err("nvmlDeviceGetHandleByIndex", r);
+    return GPA_ERR_NVML;
+  }
+  if (total_memory_mib) {
+    // totalMemory := uint(*status.Memory.Global.Free + *status.Memory.Global.Used), both already in MiB
+    // (cmd/nvidia-device-plugin/nvidia.go:90-92; nvml/bindings.go:491-520)
+    *total_memory_mib = 0;
+    nvmlMemory_t mem;
+    if (nv->DeviceGetMemoryInfo) {
+      r = nv->DeviceGetMemoryInfo(d, &mem);
+      nv->calls++;
+      if (r == NVML_SUCCESS) {
+        *total_memory_mib = mem.free / (1024ull * 1024ull) + mem.used / (1024ull * 1024ull);
+      } else if (r != NVML_ERROR_NOT_SUPPORTED) {
+        nv->last_error = nv->err("nvmlDeviceGetMemoryInfo", r);
+        return GPA_ERR_NVML;
+      }
+    }
+  }
+  if (minor) {
+    *minor = -1;
+    unsigned int m = 0;
+    if (nv->DeviceGetMinorNumber) {
+      r = nv->DeviceGetMinorNumber(d, &m);
+      nv->calls++;
+      if (r == NVML_SUCCESS) {
+        *minor = (int)m;
+      } else if (r != NVML_ERROR_NOT_SUPPORTED) {  // bindings.go:316-324: NOT_SUPPORTED is "no minor number"
+        nv->last_error = nv->err("nvmlDeviceGetMinorNumber", r);
+        return GPA_ERR_NVML;
+      }
+    }
+  }
+  if (numa_node || bus_id) {
+    nvmlPciInfo_t pci;
+    r = nv->DeviceGetPciInfo(d, &pci);
+    nv->calls++;
+    if (r != NVML_SUCCESS) {
+      nv->last_error = nv->err("nvmlDeviceGetPciInfo", r);
+      return GPA_ERR_NVML;
+    }
+    if (bus_id && bus_id_cap > 0) snprintf(bus_id, (size_t)bus_id_cap, "%s", pci.busId);
+    if (numa_node) {
+      // numaNode(), nvml.go:314-332: /sys/bus/pci/devices/<bus id without its first four characters, lower case>/numa_node;
+      // unreadable or negative = no NUMA information
+      *numa_node = -1;
+      const char *root = getenv("GPA_SYSFS_PCI_DEVICES");  // tests point this at a scratch directory
+      std::string path = std::string(root && *root ? root : "/sys/bus/pci/devices") + "/";
+      const char *b = pci.busId;
+      if (strlen(b) > 4) b += 4;
+      for (; *b; b++) path += (char)tolower((unsigned char)*b);
+      path += "/numa_node";
+      if (FILE *f = fopen(path.c_str(), "r")) {
+        char buf[32] = {0};
+        if (fgets(buf, sizeof buf, f)) {
+          char *end = nullptr;
+          const long v = strtol(buf, &end, 10);
+          if (end != buf && v >= 0) *numa_node = (int)v;
+        }
+        fclose(f);
+      }
+    }
   }
   return GPA_OK;
 }

@@ -186,8 +186,14 @@ def node_from_nvml(nvml, ctx=None, topology_flags=gpa.TOPO_PARITY):
     path /dev/nvidia<minor>) and, when a context is given, the NVML link matrix installed in it ONCE (the reference
     re-enumerates NVML twice per request, server.go:274,279)."""
     n = nvml.device_count()
-    devices = [{"id": nvml.device_uuid(i), "index": str(i), "paths": ["/dev/nvidia%d" % i], "total_memory": 0, "numa": -1,
-                "nvml_index": i} for i in range(n)]
+    devices = []
+    for i in range(n):
+        info = nvml.device_info(i)
+        if info["minor"] < 0:
+            raise RuntimeError("unsupported GPU device")  # nvml.ErrUnsupportedGPU, nvml.go:467-469: no minor number
+        # buildDevice, nvidia.go:162-178: TotalMemory = free + used MiB (sizes auto replicas), Topology from the NUMA node
+        devices.append({"id": nvml.device_uuid(i), "index": str(i), "paths": ["/dev/nvidia%d" % info["minor"]],
+                        "total_memory": info["total_memory"], "numa": info["numa"], "nvml_index": i})
     if ctx is not None and n > 0:
         nvml.install_topology(ctx, topology_flags)
     return devices

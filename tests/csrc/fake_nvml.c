@@ -34,6 +34,10 @@ static int g_qh, g_qt;
 static pthread_mutex_t g_mu = PTHREAD_MUTEX_INITIALIZER;
 static pthread_cond_t g_cv = PTHREAD_COND_INITIALIZER;
 
+/* memory and minor numbers: scripted per device (defaults: 183359 MiB free, 0 used, minor = index) */
+static unsigned long long g_mem_free[64], g_mem_used[64];
+static int g_minor[64], g_mem_scripted[64], g_minor_scripted[64];
+
 static nvmlDevice_t H(int i) { return (nvmlDevice_t)(size_t)(i + 1); }
 static int I(nvmlDevice_t d) { return (int)(size_t)d - 1; }
 
@@ -48,6 +52,8 @@ void fake_nvml_reset(int n)
     g_links_supported = MAXL;
     g_calls = 0;
     g_qh = g_qt = 0;
+    memset(g_mem_scripted, 0, sizeof g_mem_scripted);
+    memset(g_minor_scripted, 0, sizeof g_minor_scripted);
     for (int i = 0; i < MAXD; i++) {
         snprintf(g_uuid[i], sizeof g_uuid[i], "GPU-%08x-0000-0000-0000-000000000000", i);
         snprintf(g_bus[i], sizeof g_bus[i], "00000000:%02X:00.0", 0x10 + i);
@@ -135,6 +141,31 @@ nvmlReturn_t nvmlDeviceGetPciInfo_v3(nvmlDevice_t d, nvmlPciInfo_t *pci)
     snprintf(pci->busId, sizeof pci->busId, "%s", g_bus[i]);
     return NVML_SUCCESS;
 }
+void fake_nvml_set_memory(int i, unsigned long long free_bytes, unsigned long long used_bytes)
+{
+    g_mem_free[i] = free_bytes; g_mem_used[i] = used_bytes; g_mem_scripted[i] = 1;
+}
+void fake_nvml_set_minor(int i, int minor) { g_minor[i] = minor; g_minor_scripted[i] = 1; }
+nvmlReturn_t nvmlDeviceGetMemoryInfo(nvmlDevice_t d, nvmlMemory_t *mem)
+{
+    g_calls++;
+    int i = (int)(size_t)d - 1;
+    if (i < 0 || i >= g_n) return NVML_ERROR_INVALID_ARGUMENT;
+    mem->free = g_mem_scripted[i] ? g_mem_free[i] : 183359ull * 1024 * 1024;
+    mem->used = g_mem_scripted[i] ? g_mem_used[i] : 0;
+    mem->total = mem->free + mem->used;
+    return NVML_SUCCESS;
+}
+nvmlReturn_t nvmlDeviceGetMinorNumber(nvmlDevice_t d, unsigned int *minor)
+{
+    g_calls++;
+    int i = (int)(size_t)d - 1;
+    if (i < 0 || i >= g_n) return NVML_ERROR_INVALID_ARGUMENT;
+    if (g_minor_scripted[i] && g_minor[i] < 0) return NVML_ERROR_NOT_SUPPORTED;
+    *minor = (unsigned)(g_minor_scripted[i] ? g_minor[i] : i);
+    return NVML_SUCCESS;
+}
+
 nvmlReturn_t nvmlDeviceGetTopologyCommonAncestor(nvmlDevice_t a, nvmlDevice_t b, nvmlGpuTopologyLevel_t *lvl)
 {
     g_calls++;
