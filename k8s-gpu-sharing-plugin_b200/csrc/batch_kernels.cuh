@@ -98,21 +98,13 @@ __global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_kernel(cons
       done = true;
     }
     if (!done) {
-      // link-count symmetry over the available devices (where calculateGPUPairScore would panic, :307-310)
-      int bad = 0;
+      // the request's weights by position; a pair whose link counts differ is poisoned, so that the search itself finds
+      // out whether Go would ever have scored it (kAsymPoison, kernels_common.cuh)
       for (int i = lane; i < n * n; i += 32) {
         int a = i / n, b = i - a * n;
         int da = dev_at(a), db = dev_at(b);
-        bad |= topo.asym[da * topo.nt + db];
-        if (a < b) wp[a * kMaxDevices + b] = topo.wq[da * topo.nt + db];
+        if (a < b) wp[a * kMaxDevices + b] = topo.asym[da * topo.nt + db] ? (uint16_t)kAsymPoison : topo.wq[da * topo.nt + db];
       }
-      bad = __any_sync(0xffffffffu, bad);
-      if (bad) {
-        err = GPA_ERR_ASYMMETRIC;
-        done = true;
-      }
-    }
-    if (!done) {
       __syncwarp();
       const Geom g = make_geom(n, size, rmask);
       fill_score_table(S, wp, g, lane, 32);
@@ -130,10 +122,21 @@ __global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_kernel(cons
       if (lane == 0) {
         int8_t pos[32];
         int cnt = finalize(g, cut, s_binom, stab, best, intended != 0, pos);
-        if (cnt < 0) {
+        if (best != 0 && key_score(best) >= (int)kAsymPoison) {
+          err = GPA_ERR_ASYMMETRIC;  // an accepted candidate holds such a pair: the panic of :307-310 while iterating
+        } else if (cnt < 0) {
           err = GPA_ERR_INVALID;
         } else {
-          for (int i = 0; i < cnt; i++) res[i] = pos[i] < 0 ? (int8_t)GPA_NIL : (int8_t)dev_at(pos[i]);
+          // the chosen set is the best-scoring set of the saved partition that holds the required devices: if any of
+          // those sets held such a pair it is this one (the panic inside the loop of :77-85)
+          uint32_t chosen = 0;
+          for (int i = 0; i < cnt; i++)
+            if (pos[i] >= 0) chosen |= 1u << pos[i];
+          if (cnt > 0 && S[chosen] >= kAsymPoison) {
+            err = GPA_ERR_ASYMMETRIC;
+          } else {
+            for (int i = 0; i < cnt; i++) res[i] = pos[i] < 0 ? (int8_t)GPA_NIL : (int8_t)dev_at(pos[i]);
+          }
         }
       }
       __syncwarp();  // S / wp are reused by the next request of this warp

@@ -575,6 +575,11 @@ int gpa_set_topology(gpa_ctx *ctx, int n, const int32_t *W, const uint8_t *nlink
     }
   if (g == 0) g = 1;
   if ((long long)(mx / g) * kMaxPairs > kScoreCap) return GPA_ERR_WEIGHT_RANGE;
+  bool asym_any = false;
+  for (int i = 0; i < n; i++)
+    for (int j = 0; j < n; j++) asym_any = asym_any || (i != j && nlinks[i * n + j] != nlinks[j * n + i]);
+  // with asymmetric link counts a partition's honest score must stay below the poison weight (kernels_common.cuh)
+  if (asym_any && (long long)(mx / g) * kMaxPairs >= (long long)kAsymPoison) return GPA_ERR_WEIGHT_RANGE;
   t.unit = g;
   t.wq.assign((size_t)n * n, 0);
   t.asym.assign((size_t)n * n, 0);
@@ -746,10 +751,13 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
     }
   }
 
-  // where calculateGPUPairScore panics (:307-310); see DESIGN.md for the (conservative) scope of this check
-  for (int a = 0; a < n_avail; a++)
+  // Pairs on which calculateGPUPairScore would panic (:307-310).  Go only panics when such a pair is SCORED, so the
+  // search decides: the pair gets the weight kAsymPoison and the answer is GPA_ERR_ASYMMETRIC exactly when an accepted
+  // candidate - or a set the final choice scores - holds one (kernels_common.cuh).
+  bool asym_avail = false;
+  for (int a = 0; a < n_avail && T.any_asym; a++)
     for (int b = 0; b < n_avail; b++)
-      if (a != b && T.asym[avail[a] * T.n + avail[b]]) return GPA_ERR_ASYMMETRIC;
+      if (a != b && T.asym[avail[a] * T.n + avail[b]]) asym_avail = true;
 
   SearchParams sp;
   memset(&sp, 0, sizeof sp);
@@ -757,7 +765,8 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
   sp.intended = (mode_flags & GPA_MODE_INTENDED) ? 1 : 0;
   sp.seq = next_seq(ctx);
   for (int a = 0; a < n_avail; a++)
-    for (int b = a + 1; b < n_avail; b++) sp.wp[a * kMaxDevices + b] = T.wq[avail[a] * T.n + avail[b]];
+    for (int b = a + 1; b < n_avail; b++)
+      sp.wp[a * kMaxDevices + b] = T.asym[avail[a] * T.n + avail[b]] ? (uint16_t)kAsymPoison : T.wq[avail[a] * T.n + avail[b]];
   const uint64_t parts = partition_count(sp.g, ctx->binom);
   if (parts > GPA_MAX_PARTITIONS) return GPA_ERR_TOO_LARGE;
 
@@ -783,8 +792,9 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
   // DP with its tables in shared memory was tried for <= 14 devices and measured 3-12x SLOWER than the layered launches
   // (one SM cannot issue the ~10^5..10^6 stepper iterations fast enough), so it is not kept.
   // With 15-16 devices the enumeration kernel's per-CTA score table (64-128 KB) costs more than the whole DP, whatever k.
-  const bool use_dp = (mode_flags & GPA_MODE_FORCE_DP) ||
-                      (!(mode_flags & GPA_MODE_FORCE_ENUM) && (parts > 150000ull || n_avail >= 15));
+  // (the DP's 16-bit tables have no room for poisoned scores: requests over such a pair are always enumerated)
+  const bool use_dp = !asym_avail && ((mode_flags & GPA_MODE_FORCE_DP) ||
+                                      (!(mode_flags & GPA_MODE_FORCE_ENUM) && (parts > 150000ull || n_avail >= 15)));
   int grid = 0, block = 0;
   size_t smem = 0;
   if (use_small) {
@@ -870,6 +880,15 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
   ctx->stats.algorithm = use_small ? 3 : (use_dp ? 2 : 1);
 
   const SearchResult &r = *ctx->h_res;
+  if (asym_avail) {
+    // an accepted candidate held such a pair (panic while iterating, :56), or the chosen set - the best-scoring one
+    // among those the final loop scores, :77-85 - does
+    bool chosen_asym = false;
+    for (int i = 0; i < r.count; i++)
+      for (int j = 0; j < r.count; j++)
+        if (i != j && r.pos[i] >= 0 && r.pos[j] >= 0 && T.asym[avail[r.pos[i]] * T.n + avail[r.pos[j]]]) chosen_asym = true;
+    if (r.best_score >= (int)kAsymPoison || chosen_asym) return GPA_ERR_ASYMMETRIC;
+  }
   if (r.count < 0) {
     ctx->last_error = "search epilogue could not replay the winning item";
     return GPA_ERR_CUDA;
@@ -1204,11 +1223,17 @@ extern "C" int gpa_besteffort_batch_noalloc(int cuda_device, int n_topology, con
     na_msg(errbuf, errbuf_len, "pair weights too large for the 16-bit score table");
     return GPA_ERR_WEIGHT_RANGE;
   }
+  bool asym_any = false;
   for (int i = 0; i < n; i++)
     for (int j = 0; j < n; j++) {
       wq[i * n + j] = i == j ? 0 : (uint16_t)(W[i * n + j] / g);
       asym[i * n + j] = i != j && nlinks[i * n + j] != nlinks[j * n + i];
+      asym_any = asym_any || asym[i * n + j];
     }
+  if (asym_any && (long long)(mx / g) * kMaxPairs >= (long long)kAsymPoison) {  // same rule as gpa_set_topology
+    na_msg(errbuf, errbuf_len, "pair weights too large for a topology with asymmetric link counts");
+    return GPA_ERR_WEIGHT_RANGE;
+  }
   if (max_avail == 0)
     for (int i = 0; i < count; i++)
       if (reqs[i].n_avail > max_avail && reqs[i].n_avail <= GPA_BATCH_MAX_AVAILABLE) max_avail = reqs[i].n_avail;

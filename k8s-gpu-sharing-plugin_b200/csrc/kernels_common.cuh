@@ -20,6 +20,14 @@ constexpr int kSearchBlockLarge = 1024;  // 64-128 KB table: one or two CTAs per
 constexpr int kBatchWarps = 8;
 constexpr int kScoreCap = 65535;                        // uint16 set-score table
 constexpr int kMaxPairs = (kMaxDevices * (kMaxDevices - 1)) / 2;  // 120
+// calculateGPUPairScore panics on a pair whose two link lists differ in length (besteffort_policy.go:307-310), but only
+// when such a pair is actually SCORED: inside a candidate partition that passed the `required` filter (:53-56), or inside
+// a set of the saved bestPartition that holds every required device (:77-80).  The kernels reproduce that by giving such a
+// pair the weight kAsymPoison: on a topology with asymmetric link counts the scaled weights are kept small enough
+// (gpa_set_topology) that a whole partition without such a pair scores below kAsymPoison, so "the best accepted
+// partition scores >= kAsymPoison" says exactly "some accepted partition holds such a pair", and the same for the
+// final set choice.
+constexpr uint32_t kAsymPoison = 0x8000u;
 
 // The binomial table is read with a DIFFERENT index in every lane while item ranks are decoded; constant memory
 // serialises such reads one address at a time, shared memory does not, so kernels that decode stage it first.
@@ -86,7 +94,7 @@ __device__ __forceinline__ void fill_score_table(uint16_t *S, const uint16_t *wp
         sum += wp[a * kMaxDevices + b];
       }
     }
-    S[mask] = (uint16_t)sum;
+    S[mask] = (uint16_t)(sum > 0xFFFFu ? 0xFFFFu : sum);  // only poisoned sets (kAsymPoison) can get there
   }
 }
 

@@ -15,6 +15,7 @@
 #include <sys/stat.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
@@ -106,7 +107,34 @@ struct gpa_plugin {
   std::unordered_set<std::string> replica_ids;
   std::unordered_map<std::string, int> cached_by_id;
   std::mutex mu;
+  // Which control nodes exist on the host (apiDeviceSpecs, server.go:446-463), one bit per path.  The reference stats the
+  // four paths in every Allocate; here the answer is kept and refreshed at most once a second, so a node that appears
+  // later (nvidia-uvm is created on first use) is still picked up, and a burst of Allocate calls pays for one round of
+  // stat() calls.
+  int control_mask = 0;
+  std::chrono::steady_clock::time_point control_checked{};
+  bool control_valid = false;
 };
+
+namespace {
+const char *const kControlNodes[4] = {"/dev/nvidiactl", "/dev/nvidia-uvm", "/dev/nvidia-uvm-tools", "/dev/nvidia-modeset"};
+
+int control_nodes_of(gpa_plugin *p) {
+  const auto now = std::chrono::steady_clock::now();
+  std::lock_guard<std::mutex> lk(p->mu);
+  if (!p->control_valid || now - p->control_checked > std::chrono::seconds(1)) {
+    int m = 0;
+    for (int i = 0; i < 4; i++) {
+      struct stat st;
+      if (stat(kControlNodes[i], &st) == 0) m |= 1 << i;  // os.Stat(p) on the HOST path (:454)
+    }
+    p->control_mask = m;
+    p->control_checked = now;
+    p->control_valid = true;
+  }
+  return p->control_mask;
+}
+}  // namespace
 
 extern "C" {
 
@@ -164,6 +192,7 @@ int gpa_plugin_create(gpa_ctx *ctx, const gpa_plugin_config *cfg, const gpa_plug
       if (ok) gpa_set_device_order(ctx, order.data(), nt);  // a non-permutation is refused there and changes nothing
     }
   }
+  if (p->pass_device_specs) control_nodes_of(p);
   *out = p;
   return GPA_OK;
 }
@@ -448,10 +477,9 @@ int gpa_plugin_allocate(gpa_plugin *p, const char *const *ids, int n, char *json
            json_escape(path_join(p->driver_root, path)) + "\",\"permissions\":\"rw\"}";
       first = false;
     };
-    for (const char *ctl : {"/dev/nvidiactl", "/dev/nvidia-uvm", "/dev/nvidia-uvm-tools", "/dev/nvidia-modeset"}) {
-      struct stat st;
-      if (stat(ctl, &st) == 0) spec(ctl);  // os.Stat(p) on the HOST path (:454)
-    }
+    const int ctl_mask = control_nodes_of(p);
+    for (int i = 0; i < 4; i++)
+      if (ctl_mask >> i & 1) spec(kControlNodes[i]);
     for (const Device &d : p->cached)
       for (const std::string &u : uuids)
         if (d.id == u)

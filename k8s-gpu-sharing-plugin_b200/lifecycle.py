@@ -199,8 +199,15 @@ def node_from_nvml(nvml, ctx=None, topology_flags=gpa.TOPO_PARITY):
     return devices
 
 
-def nvml_health_source(nvml, device_ids, disable_env=None, wait_timeout_ms=500):
-    """checkHealth (cmd/nvidia.go:181-269) as a PluginDaemon health source: XID events -> device_unhealthy(index)"""
+def nvml_health_source(nvml, device_ids, disable_env=None, wait_timeout_ms=500, refresh_topology=None, log=print):
+    """checkHealth (cmd/nvidia.go:181-269) as a PluginDaemon health source: XID events -> device_unhealthy(index).
+
+    refresh_topology: called after every event, before the list is re-sent.  The reference rebuilds its link matrix from
+    NVML inside every request (server.go:274,279), so the request after an XID already sees whatever the event did to the
+    links (an NVLink that went down no longer counts); this daemon reads the matrix once, so the event is where its cache
+    - the matrix and the answer table built from it - is invalidated and re-read.  A GPU that fell off the bus can make
+    the re-read fail; the old matrix then stays (kubelet no longer offers that GPU once its replicas are Unhealthy, so
+    its rows are not consulted), which is logged."""
     def loop(stop_event, on_unhealthy):
         watcher = gpa.HealthWatcher(nvml, device_ids, disable_env=disable_env, wait_timeout_ms=wait_timeout_ms)
         try:
@@ -209,6 +216,11 @@ def nvml_health_source(nvml, device_ids, disable_env=None, wait_timeout_ms=500):
                 if ev is None:
                     continue
                 idx, _xid = ev
+                if refresh_topology is not None:
+                    try:
+                        refresh_topology()
+                    except Exception as e:  # noqa: BLE001
+                        log("XID %s: link matrix could not be re-read, keeping the cached one (%s)" % (_xid, e))
                 for i in (range(len(device_ids)) if idx < 0 else [idx]):  # an event without a UUID marks every device (:243-250)
                     on_unhealthy(i)
         finally:
@@ -245,7 +257,8 @@ def main(argv=None):
                                            fixes=a.fixes | (gpa.OPT_REPLICA_TOPOLOGY if a.replica_topology else 0)):
         daemons.append(PluginDaemon(kw, plugin_dir=a.plugin_dir, socket_name=sock,
                                     health_source=nvml_health_source(nvml, [d["id"] for d in devices],
-                                                                     disable_env=os.environ.get("DP_DISABLE_HEALTHCHECKS"))))
+                                                                     disable_env=os.environ.get("DP_DISABLE_HEALTHCHECKS"),
+                                                                     refresh_topology=lambda: nvml.install_topology(ctx, flags))))
     try:
         run(daemons, install_signals=True)
     finally:

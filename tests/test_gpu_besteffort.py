@@ -150,6 +150,52 @@ def test_asymmetric_link_counts_are_reported_where_go_panics(ctx, oracle):
     assert gpa.decode_result(got[0])[0] == gpa.ERR_ASYMMETRIC
 
 
+def test_asymmetric_pair_panics_only_where_go_scores_it(ctx, oracle):
+    """calculateGPUPairScore panics lazily (besteffort_policy.go:307-310): only for a pair inside a candidate that passed
+    the `required` filter (:53-56), or inside a set the final loop scores (:77-85).  Hand-derived: 4 devices, size 2,
+    link counts of (0, 2) differ.  required = {0, 1}: the only accepted partition is (0,1)(2,3), the pair (0, 2) is never
+    scored, Go answers [0, 1].  required = {0}: (0,2)(1,3) is accepted and scored -> panic.  required = {} -> panic.
+    Then seeded topologies with several such pairs, every mask / size / required, single and batched, against the
+    oracle (which restates the lazy rule, ref_besteffort.c fast_leaf / final loop)."""
+    W, nl = syn.links_to_weights(syn.topo_uniform(4))
+    nl = nl.copy()
+    nl[0, 2] = 2
+    ctx.set_topology(W, nl)
+    assert ctx.besteffort([0, 1, 2, 3], [0, 1], 2) == (gpa.OK, [0, 1])
+    assert ctx.besteffort([0, 1, 2, 3], [2, 3], 2) == (gpa.OK, [2, 3])
+    assert ctx.besteffort([0, 1, 2, 3], [0], 2)[0] == gpa.ERR_ASYMMETRIC
+    assert ctx.besteffort([0, 1, 2, 3], [], 2)[0] == gpa.ERR_ASYMMETRIC
+    assert ctx.besteffort([0, 1, 2, 3], [], 4)[0] == gpa.ERR_ASYMMETRIC      # one set: every pair is scored
+    assert ctx.besteffort([0, 1, 3], [], 2) == (gpa.OK, [0, 1])             # the pair is not even available
+    got = ctx.besteffort_batch(syn.pack_requests([([0, 1, 2, 3], [0, 1], 2), ([0, 1, 2, 3], [0], 2)]))
+    assert gpa.decode_result(got[0]) == (gpa.OK, [0, 1]) and gpa.decode_result(got[1])[0] == gpa.ERR_ASYMMETRIC
+    rng = np.random.default_rng(17)
+    for n, seed in ((6, 1), (7, 2), (8, 3)):
+        W, nl = syn.links_to_weights(syn.topo_random(n, 60 + seed))
+        nl = nl.copy()
+        for _ in range(2):
+            a, b = (int(x) for x in rng.choice(n, 2, replace=False))
+            nl[a, b] += 1
+        ctx.set_topology(W, nl)
+        assert ctx.answer_table() is None
+        order = [int(x) for x in rng.permutation(n)]
+        all_reqs = list(syn.exhaustive_requests(order, seed=seed, n_pairs=4))
+        reqs = syn.pack_requests(all_reqs)
+        n_ok = n_panic = 0
+        for mode in (gpa.MODE_GO_FAITHFUL, gpa.MODE_INTENDED):
+            want = oracle_batch(oracle, W, nl, reqs, mode)
+            assert_batch_equal(ctx.besteffort_batch(reqs, mode), want, reqs, "lazy-asym n=%d" % n)
+            n_panic += int((want["dev"][:, 0] == gpa.RES_ERROR).sum())
+            n_ok += int((want["dev"][:, 0] != gpa.RES_ERROR).sum())
+            for i in rng.choice(len(all_reqs), 150, replace=False):
+                avail, req, k = all_reqs[int(i)]
+                rc_o, out_o = oracle.besteffort(W, nl, avail, req, k, mode)
+                rc, out = ctx.besteffort(avail, req, k, mode)
+                assert (rc == gpa.ERR_ASYMMETRIC) == (rc_o == oracle.PANIC_ASYMMETRIC), (n, avail, req, k, mode)
+                assert rc != gpa.OK or out == out_o, (n, avail, req, k, mode)
+        assert n_ok > 100 and n_panic > 100   # both outcomes are well represented
+
+
 def test_asymmetric_weights_use_the_earlier_devices_view(ctx, oracle):
     W = np.zeros((3, 3), dtype=np.int32)
     nl = np.ones((3, 3), dtype=np.uint8)

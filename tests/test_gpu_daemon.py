@@ -78,3 +78,53 @@ def test_daemon_with_real_nvml_and_cuda_policy(config, fixes):
     finally:
         ctx.close()
         nv.close()
+
+
+def test_xid_event_rereads_the_matrix_and_rebuilds_the_answer_table(fake_nvml):
+    """SURVEY.md 8f rank 2 on the device: a scripted NVML whose topology changes under the daemon; the XID makes the
+    health source re-install the matrix in the CUDA context, which rebuilds the answer table (one more build kernel),
+    and decisions after the event follow the new matrix like the reference's per-request re-enumeration would."""
+    import threading
+    import time
+    F, FAKE_SO = fake_nvml
+    n = 4
+    F.fake_nvml_reset(n)
+    uuids = ["GPU-%08x-1111-2222-3333-444444444444" % i for i in range(n)]
+    for i, u in enumerate(uuids):
+        F.fake_nvml_set_device(i, u.encode(), None)
+    for i in range(n):
+        for j in range(n):
+            F.fake_nvml_set_level(i, j, 50)          # NVML_TOPOLOGY_SYSTEM: CrossCPU, 10 per pair
+    nv = gpa.Nvml(FAKE_SO)
+    ctx = gpa.Context(0)
+    try:
+        nv.install_topology(ctx)
+        W0, _ = ctx.get_topology()
+        table0 = ctx.answer_table().copy()
+        assert ctx.besteffort([0, 1, 2, 3], [], 2) == (gpa.OK, [0, 1])
+        launches0 = ctx.launch_count
+        F.fake_nvml_set_level(2, 3, 10)              # NVML_TOPOLOGY_SINGLE: GPUs 2 and 3 now share a switch (50)
+        F.fake_nvml_set_level(3, 2, 10)
+        src = lifecycle.nvml_health_source(nv, uuids, disable_env="", wait_timeout_ms=50,
+                                           refresh_topology=lambda: nv.install_topology(ctx))
+        stop, seen = threading.Event(), []
+        t = threading.Thread(target=src, args=(stop, seen.append))
+        t.start()
+        try:
+            time.sleep(0.2)
+            F.fake_nvml_inject(1, 8, 79)             # nvmlEventTypeXidCriticalError on GPU 1
+            deadline = time.time() + 5
+            while not seen and time.time() < deadline:
+                time.sleep(0.02)
+        finally:
+            stop.set()
+            t.join()
+        assert seen == [1]
+        W1, nl1 = ctx.get_topology()
+        assert W0[2, 3] == 10 and W1[2, 3] == 50 and (W1 != W0).sum() == 2
+        assert ctx.launch_count == launches0 + 1 and (ctx.answer_table() != table0).any()
+        want = orc.besteffort(W1, nl1, [0, 1, 2, 3], [], 2)
+        assert want == (orc.OK, [2, 3]) and ctx.besteffort([0, 1, 2, 3], [], 2) == (gpa.OK, [2, 3])
+    finally:
+        ctx.close()
+        nv.close()

@@ -42,3 +42,41 @@ def test_lut_probe_reports_a_plausible_ceiling():
     assert 500 < g < 12000
     with pytest.raises(gpa.GpaError):
         gpa.probe_lut(0, 20, 1)
+
+
+def test_p2p_matrix_against_nvml_on_two_or_more_gpus():
+    """config 5 on a multi-GPU box (skipped on one GPU): the n x n peer bandwidth matrix, both ways of moving the bytes,
+    against what NVML reports.  On an NVSwitch machine every off-diagonal pair runs at NVLink speed (the pool measures
+    ~770 GB/s one way of 900 nominal); nvml.GetNVLink as the reference calls it sees NO link there (the far end of every
+    link is the switch, nvml.go:617-658 with its TODO at :655), while GPA_TOPO_NVSWITCH_AWARE reports links for exactly
+    the pairs the probe finds fast."""
+    import numpy as np
+    import torch
+    n = min(torch.cuda.device_count(), 8)
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs")
+    kern, acc = gpa.probe_p2p(n, 1 << 30, 5, mode=0)
+    copy, _ = gpa.probe_p2p(n, 1 << 30, 5, mode=1)
+    off = ~np.eye(n, dtype=bool)
+    assert acc[off].all()
+    nvlink_measured = 770.0
+    assert kern[off].min() >= 0.8 * nvlink_measured, kern
+    assert copy[off].min() >= 0.8 * nvlink_measured, copy
+    assert abs(kern[off].mean() - copy[off].mean()) <= 0.03 * copy[off].mean()      # the two modes agree
+    assert (np.abs(kern[off] - copy[off]) <= 0.10 * copy[off]).all()
+    # the same pairs as NVML sees them; CUDA device i -> NVML index by UUID
+    nv = gpa.Nvml()
+    try:
+        nvml_uuids = [nv.device_uuid(j) for j in range(nv.device_count())]
+        to_nvml = [nvml_uuids.index("GPU-" + str(torch.cuda.get_device_properties(i).uuid)) for i in range(n)]
+        parity, _ = nv.read_topology(gpa.TOPO_PARITY)
+        aware, _ = nv.read_topology(gpa.TOPO_NVSWITCH_AWARE)
+        for i in range(n):
+            for j in range(n):
+                if i == j:
+                    continue
+                fast = kern[i, j] > 300.0          # PCIe peer traffic would stay below ~60 GB/s
+                assert (aware[to_nvml[i], to_nvml[j], 1] != 0) == fast, (i, j, kern[i, j])
+                assert parity[to_nvml[i], to_nvml[j], 1] == 0
+    finally:
+        nv.close()

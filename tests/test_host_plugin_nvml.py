@@ -343,3 +343,20 @@ def test_health_churn_under_concurrent_allocate(fake):
     h.close()
     nv.close()
     plugin.close()
+
+
+@pytest.mark.parametrize("mode", ["parity", "fixed"])
+def test_config4_churn_counts_in_parity_and_fixed_mode(fake, mode):
+    """SURVEY.md 8d config 4 (tools/churn.cpp, shortened from 30 s to 2 s): 8 Allocate clients while XIDs arrive at 50 Hz.
+    One ListAndWatch re-send per critical event (an event without a UUID counts once per device); the re-sent list
+    never changes in parity mode (D1) and loses every replica of a hit GPU in fixed mode; no Allocate error."""
+    import json
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    subprocess.check_call(["make", "-C", os.path.join(root, "tools"), "-s", "bin/churn"])
+    out = subprocess.run([os.path.join(root, "tools", "bin", "churn"), FAKE_SO, "2", mode], capture_output=True, text=True, timeout=120)
+    r = json.loads(out.stdout)
+    assert out.returncode == 0 and r["as_specified"] and r["allocate_errors"] == 0, r
+    assert r["unhealthy_notifications"] == r["list_resends"] == r["expected_notifications"] > 0
+    assert r["list_entries_changed"] == (0 if mode == "parity" else r["expected_entries_changed"])
+    assert mode == "parity" or r["list_entries_changed"] > 0

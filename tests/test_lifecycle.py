@@ -2,6 +2,7 @@
 when kubelet.sock is re-created.  CPU only: replicas > 1 takes the host branch of GetPreferredAllocation
 (prioritizeDevices), so no CUDA context is needed.  The reference has no test for any of this (parity unpinned);
 the parser is checked against the literal restatement in oracle/ref_server.py, the rest against the cited behaviour."""
+import ctypes as C
 import os
 import tempfile
 import threading
@@ -213,3 +214,83 @@ def test_daemon_on_a_scripted_nvml_node_resends_the_list_on_an_xid(fake_nvml):
                 daemon.stop()
                 kubelet.stop()
     nv.close()
+
+
+def test_node_from_nvml_takes_memory_minor_and_numa_node_from_nvml(fake_nvml, monkeypatch, tmp_path):
+    """buildDevice (cmd/nvidia-device-plugin/nvidia.go:162-178): TotalMemory = free + used MiB, path /dev/nvidia<MINOR>,
+    Topology from the bus id's numa_node.  With auto replicas (`gpu:gpu:-1`) the daemon must advertise
+    TotalMemory / 1000 replicas per GPU (server.go:100-103), each with its TopologyInfo."""
+    F, FAKE_SO = fake_nvml
+    F.fake_nvml_set_memory.argtypes = [C.c_int, C.c_ulonglong, C.c_ulonglong]
+    F.fake_nvml_set_minor.argtypes = [C.c_int, C.c_int]
+    F.fake_nvml_reset(2)
+    uuids = ["GPU-%08x-1111-2222-3333-444444444444" % i for i in range(2)]
+    buses = ["00000000:1B:00.0", "00000000:9C:00.0"]
+    for i, u in enumerate(uuids):
+        F.fake_nvml_set_device(i, u.encode(), buses[i].encode())
+    MiB = 1024 * 1024
+    F.fake_nvml_set_memory(0, 4000 * MiB + 5, 999 * MiB + MiB - 1)   # 4000 + 999 MiB: each part rounds down on its own
+    F.fake_nvml_set_memory(1, 2500 * MiB, 0)
+    F.fake_nvml_set_minor(0, 3)
+    F.fake_nvml_set_minor(1, 0)
+    # /sys/bus/pci/devices/<bus id without its first four characters, lower case>/numa_node (nvml.go:314-332)
+    for bus, node in ((buses[0], "1\n"), (buses[1], "-1\n")):
+        d = tmp_path / bus[4:].lower()
+        d.mkdir()
+        (d / "numa_node").write_text(node)
+    monkeypatch.setenv("GPA_SYSFS_PCI_DEVICES", str(tmp_path))
+    nv = gpa.Nvml(FAKE_SO)
+    try:
+        assert nv.device_info(0) == {"total_memory": 4999, "minor": 3, "numa": 1, "bus_id": buses[0]}
+        devices = lifecycle.node_from_nvml(nv)
+        assert [(x["paths"], x["total_memory"], x["numa"]) for x in devices] == [(["/dev/nvidia3"], 4999, 1), (["/dev/nvidia0"], 2500, -1)]
+        (_, sock, kw), = lifecycle.plugins_for("none", gpa.parse_resource_config("gpu:gpu:-1"), devices)
+        plug = gpa.Plugin(**kw)
+        try:
+            listed = plug.api_devices()
+            assert len(listed) == 4 + 2                                # 4999 / 1000 and 2500 / 1000 replicas
+            assert [x["ID"] for x in listed][:2] == [uuids[0] + "-replica-0", uuids[0] + "-replica-1"]
+            assert all(x.get("topology") == {"nodes": [{"ID": 1}]} for x in listed[:4])
+            assert all("topology" not in x for x in listed[4:])        # a negative numa_node means none (nvml.go:325-328)
+        finally:
+            plug.close()
+        F.fake_nvml_set_minor(1, -1)                                   # NVML_ERROR_NOT_SUPPORTED: ErrUnsupportedGPU (nvml.go:467-469)
+        with pytest.raises(RuntimeError):
+            lifecycle.node_from_nvml(nv)
+    finally:
+        nv.close()
+
+
+def test_health_event_refreshes_the_link_matrix_before_the_list_is_resent(fake_nvml):
+    """the daemon reads the NVML link matrix once, so an XID is where that cache is invalidated:
+    refresh_topology runs for every event, before device_unhealthy; a failing re-read keeps the old matrix and is logged"""
+    F, FAKE_SO = fake_nvml
+    F.fake_nvml_reset(2)
+    uuids = ["GPU-%08x-1111-2222-3333-444444444444" % i for i in range(2)]
+    for i, u in enumerate(uuids):
+        F.fake_nvml_set_device(i, u.encode(), None)
+    nv = gpa.Nvml(FAKE_SO)
+    order, logs = [], []
+
+    def refresh():
+        order.append("refresh")
+        if len([x for x in order if x == "refresh"]) == 2:
+            raise RuntimeError("GPU is lost")
+
+    src = lifecycle.nvml_health_source(nv, uuids, disable_env="", wait_timeout_ms=50, refresh_topology=refresh, log=logs.append)
+    stop = threading.Event()
+    t = threading.Thread(target=src, args=(stop, lambda i: order.append(("unhealthy", i))))
+    t.start()
+    try:
+        time.sleep(0.2)
+        F.fake_nvml_inject(1, XID, 79)
+        F.fake_nvml_inject(0, XID, 48)
+        deadline = time.time() + 5
+        while len(order) < 4 and time.time() < deadline:
+            time.sleep(0.02)
+    finally:
+        stop.set()
+        t.join()
+        nv.close()
+    assert order == ["refresh", ("unhealthy", 1), "refresh", ("unhealthy", 0)]
+    assert len(logs) == 1 and "keeping the cached one" in logs[0] and "GPU is lost" in logs[0]
