@@ -16,9 +16,10 @@ Metric: decisions/s.
   value  the batch kernels alone on 32-byte request records resident in HBM (CUDA events on
          the launching stream);
   e2e    the host-buffer C-ABI call a caller makes, pinned host memory -> HBM -> kernel ->
-         pinned host memory, on the 8-byte device-mask records (gpa_besteffort_batch_masks:
-         the format a cgo caller builds straight from its []*Device, INTEGRATION.md);
-         `e2e_records` is the same through the 32-byte id-list records (gpa_besteffort_batch)
+         pinned host memory, on the compact 4-byte mask records of nodes of up to 8 GPUs
+         (gpa_besteffort_batch_masks8: what a cgo caller builds straight from its []*Device,
+         INTEGRATION.md); `e2e_masks` is the same through the 8-byte mask records (up to 12
+         GPUs), `e2e_records` through the 32-byte id-list records (gpa_besteffort_batch)
          and `e2e_packed` packs those id lists into mask records on the host INSIDE the timed
          region (gpa_pack_mask_requests) before the mask call;
   cpu_baseline  the oracle (the C restatement of the Go reference: there is no Go toolchain on
@@ -336,15 +337,25 @@ def run_ours(args):
         (dt,) = max_over_ranks(dt)
         return dt / args.steps, (ctx.launch_count - l0) / args.steps
 
-    # ---- end-to-end arm (headline): mask records through the host-buffer C-ABI call ------------------------------
+    # ---- end-to-end arm (headline): compact mask records (4 bytes in, 2 bytes out: the format of nodes of up to 8 GPUs)
+    #      through the host-buffer C-ABI call ---------------------------------------------------------------------------
     masks = syn.records_to_masks(reqs, order)
+    masks8 = syn.masks_to_masks8(masks)
+    pin_m8in = gpa.PinnedBuffer(len(reqs), syn.MASK8_REQ_DTYPE)
+    pin_m8out = gpa.PinnedBuffer(len(reqs), syn.MASK8_RES_DTYPE)
+    pin_m8in.array[:] = masks8
+    e2e_s, e2e_launches = timed_host_arm(lambda: ctx.besteffort_batch_masks8(pin_m8in.array, out=pin_m8out.array))
+    e2e_value = world * len(reqs) / e2e_s
+    got_m8 = syn.mask_results_to_records(syn.masks8_results_to_masks(pin_m8out.array[idx].copy()), order)
+    e2e_mismatch = int((got_m8["dev"] != want["dev"]).any(axis=1).sum())
+
+    # ---- the same decisions from 8-byte mask records (4-byte results; nodes of up to 12 GPUs) --------------------------
     pin_min = gpa.PinnedBuffer(len(reqs), syn.MASK_REQ_DTYPE)
     pin_mout = gpa.PinnedBuffer(len(reqs), syn.MASK_RES_DTYPE)
     pin_min.array[:] = masks
-    e2e_s, e2e_launches = timed_host_arm(lambda: ctx.besteffort_batch_masks(pin_min.array, out=pin_mout.array))
-    e2e_value = world * len(reqs) / e2e_s
+    m16_s, m16_launches = timed_host_arm(lambda: ctx.besteffort_batch_masks(pin_min.array, out=pin_mout.array))
     got_m = syn.mask_results_to_records(pin_mout.array[idx].copy(), order)
-    e2e_mismatch = int((got_m["dev"] != want["dev"]).any(axis=1).sum())
+    m16_mismatch = int((got_m["dev"] != want["dev"]).any(axis=1).sum())
 
     # ---- the same decisions from the 32-byte id-list records ----------------------------------------------------------
     pin_in = gpa.PinnedBuffer(len(reqs), syn.REQ_DTYPE)
@@ -354,12 +365,13 @@ def run_ours(args):
     rec_mismatch = int((pin_out.array["dev"][idx] != want["dev"]).any(axis=1).sum())
 
     # ---- id-list records packed into mask records on the host inside the timed region, results unpacked again ----------
+    pin_out.array["dev"][:] = 0
+
     def packed_step():
         ctx.pack_mask_requests(pin_in.array, out=pin_min.array)
         ctx.besteffort_batch_masks(pin_min.array, out=pin_mout.array)
         ctx.unpack_mask_results(pin_mout.array, out=pin_out.array)
 
-    pin_out.array["dev"][:] = 0
     packed_s, _ = timed_host_arm(packed_step)
     packed_mismatch = int((pin_out.array["dev"][idx] != want["dev"]).any(axis=1).sum())
 
@@ -381,6 +393,10 @@ def run_ours(args):
     other_formats = {
         "mask_records_in_hbm": {"value": world * len(reqs) / (masks_ms * 1e-3), "unit": UNIT, "ms_per_step": masks_ms,
                                 "same_as_e2e_arm": masks_dev_same},
+        "e2e_masks": {"value": world * len(reqs) / m16_s, "unit": UNIT, "ms_per_step": m16_s * 1e3,
+                      "h2d_bytes_per_step": 8 * len(reqs), "d2h_bytes_per_step": 4 * len(reqs), "mismatches": m16_mismatch,
+                      "gpu_launches_per_step": m16_launches,
+                      "path": "gpa_besteffort_batch_masks: 8-byte mask records, 1 Mi-request chunks pipelined over 4 streams"},
         "e2e_records": {"value": world * len(reqs) / rec_s, "unit": UNIT, "ms_per_step": rec_s * 1e3,
                         "h2d_bytes_per_step": 32 * len(reqs), "d2h_bytes_per_step": 16 * len(reqs), "mismatches": rec_mismatch,
                         "gpu_launches_per_step": rec_launches,
@@ -390,7 +406,8 @@ def run_ours(args):
                        "path": "gpa_pack_mask_requests (host threads) -> gpa_besteffort_batch_masks -> gpa_unpack_mask_results, "
                                "all three inside the timed region"},
     }
-    all_ok = mismatches == 0 and e2e_mismatch == 0 and rec_mismatch == 0 and packed_mismatch == 0 and masks_dev_same
+    all_ok = (mismatches == 0 and e2e_mismatch == 0 and m16_mismatch == 0 and rec_mismatch == 0 and packed_mismatch == 0 and
+              masks_dev_same)
 
     if rank != 0:
         if use_dist:
@@ -660,10 +677,10 @@ def run_ours(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "int32", "data": "synthetic", "config": workload_config(world),
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 8 * len(reqs), "d2h_bytes_per_step": 4 * len(reqs),
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 4 * len(reqs), "d2h_bytes_per_step": 2 * len(reqs),
                 "ms_per_step": e2e_s * 1e3, "gpu_launches_per_step": e2e_launches, "mismatches": e2e_mismatch,
-                "path": "gpa_besteffort_batch_masks: 8-byte device-mask records in pinned host memory -> HBM -> table kernel -> "
-                        "4-byte results back in pinned host memory; 1 Mi-request chunks pipelined over 4 streams"},
+                "path": "gpa_besteffort_batch_masks8: 4-byte compact mask records in pinned host memory -> HBM -> table kernel -> "
+                        "2-byte results back in pinned host memory; 1 Mi-request chunks pipelined over 4 streams"},
         "gpu_launches": int(launches),
         "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": sampler.summary(), "pcie": pcie,
         "parity": {"checked": int(len(idx)), "mismatches_device_arm": mismatches, "mismatches_e2e_arm": e2e_mismatch},

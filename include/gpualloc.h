@@ -207,6 +207,27 @@ int gpa_besteffort_batch_masks(gpa_ctx *ctx, const gpa_mask_request *reqs, int c
 int gpa_besteffort_batch_masks_device(gpa_ctx *ctx, const gpa_mask_request *d_reqs, int count, int mode_flags,
                                       gpa_mask_result *d_out, void *stream);
 
+/* The compact form of the same batch for nodes of up to 8 GPUs - every node the reference runs on: 4 bytes in, 2 bytes
+ * out per decision.  The result record is the answer-table entry itself.  Needs the answer table (gpa_get_answer_table():
+ * at most 8 GPUs, symmetric link counts), else GPA_ERR_TOO_LARGE.  Both alias modes give the same answers there, so there
+ * is no mode argument.
+ * ref: the same loop over r.ContainerRequests, server.go:273-311 -> Policy.Allocate (:298). */
+typedef struct gpa_mask8_request {
+  uint8_t avail_mask;  /* available devices, bit b = rank b in the order of gpa_set_device_order() */
+  uint8_t req_mask;    /* required devices; one that is not available makes the answer empty */
+  uint8_t size;        /* allocation size */
+  uint8_t flags;       /* GPA_REQ_FOREIGN: some required device cannot be expressed in req_mask (the answer is empty:
+                          either len(required) > size, besteffort_policy.go:43-45, or no set holds it, :53) */
+} gpa_mask8_request;
+typedef struct gpa_mask8_result {
+  uint8_t chosen_mask; /* chosen devices; 0 with n_nil == 0: the empty answer */
+  uint8_t n_nil;       /* nil pads in the returned set; GPA_MASK8_INVALID: a mask names a device the node lacks */
+} gpa_mask8_result;
+#define GPA_MASK8_INVALID 0x80
+int gpa_besteffort_batch_masks8(gpa_ctx *ctx, const gpa_mask8_request *reqs, int count, gpa_mask8_result *out);
+int gpa_besteffort_batch_masks8_device(gpa_ctx *ctx, const gpa_mask8_request *d_reqs, int count, gpa_mask8_result *d_out,
+                                       void *stream);
+
 /* Host-side helpers for callers that hold id-list records but want the smaller transfer: gpa_pack_mask_requests()
  * turns 32-byte gpa_request records into mask records (labels = the order of gpa_set_device_order()),
  * gpa_unpack_mask_results() turns mask results back into device lists.  Plain host code on `threads` threads

@@ -75,6 +75,10 @@ def lib():
     L.gpa_besteffort_batch_masks.argtypes = [vp, vp, C.c_int, C.c_int, vp]
     L.gpa_besteffort_batch_masks_device.restype = C.c_int
     L.gpa_besteffort_batch_masks_device.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp]
+    L.gpa_besteffort_batch_masks8.restype = C.c_int
+    L.gpa_besteffort_batch_masks8.argtypes = [vp, vp, C.c_int, vp]
+    L.gpa_besteffort_batch_masks8_device.restype = C.c_int
+    L.gpa_besteffort_batch_masks8_device.argtypes = [vp, vp, C.c_int, vp, vp]
     L.gpa_pack_mask_requests.restype = C.c_int
     L.gpa_pack_mask_requests.argtypes = [vp, vp, C.c_int, vp, C.c_int, C.POINTER(C.c_int)]
     L.gpa_unpack_mask_results.restype = C.c_int
@@ -310,6 +314,20 @@ class Context:
             out = np.zeros(len(reqs), dtype=syn.MASK_RES_DTYPE)
         self._check(lib().gpa_besteffort_batch_masks(self._h, reqs.ctypes.data, len(reqs), int(mode), out.ctypes.data))
         return out
+
+    def besteffort_batch_masks8(self, reqs, out=None):
+        """reqs: numpy array of synthetic.MASK8_REQ_DTYPE (host memory) -> array of MASK8_RES_DTYPE; nodes of up to 8 GPUs"""
+        from . import synthetic as syn
+        reqs = np.ascontiguousarray(reqs)
+        assert reqs.dtype == syn.MASK8_REQ_DTYPE
+        if out is None:
+            out = np.zeros(len(reqs), dtype=syn.MASK8_RES_DTYPE)
+        self._check(lib().gpa_besteffort_batch_masks8(self._h, reqs.ctypes.data, len(reqs), out.ctypes.data))
+        return out
+
+    def besteffort_batch_masks8_device(self, d_reqs_ptr, count, d_out_ptr, stream=None):
+        self._check(lib().gpa_besteffort_batch_masks8_device(self._h, C.c_void_p(d_reqs_ptr), int(count), C.c_void_p(d_out_ptr),
+                                                             C.c_void_p(stream or 0)))
 
     def pack_mask_requests(self, reqs, out=None, threads=0):
         """REQ_DTYPE id-list records -> (MASK_REQ_DTYPE records, number that cannot be masks); host code"""

@@ -22,6 +22,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -106,7 +107,8 @@ struct gpa_ctx {
   gpa_subset_result *d_sub_out = nullptr;
   size_t sub_batch_cap = 0;
   int part_table_nt = 0;             // node size the table was built for, 0 = none
-  bool table_attr_set[2] = {false, false};
+  bool table_attr_set[3] = {false, false, false};
+  bool zero_copy = false;  // GPA_ZERO_COPY=1: kernels read / write the caller's pinned buffers directly
   uint16_t *d_ans = nullptr;         // answer table of the installed topology (ans_table.cuh), built by a kernel
   std::vector<uint16_t> h_ans;       // its host copy: gpa_besteffort() answers node-ordered requests from it
   uint16_t h_tern[256];              // ans_tern() of every 8-bit mask
@@ -264,6 +266,22 @@ int launch_batch(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_ava
   return launch_general(ctx, d_reqs, count, max_avail, mode_flags, d_out, stream, 1, flags);
 }
 
+int launch_masks8(gpa_ctx *ctx, const void *d_reqs, int count, void *d_out, cudaStream_t stream) {
+  if (!ctx->table_attr_set[2]) {
+    CUDA_TRY(ctx, cudaFuncSetAttribute(besteffort_masks8_table_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)masks_smem_bytes(ans_entries(kAnsMaxTopo))));
+    ctx->table_attr_set[2] = true;
+  }
+  long long want = ((long long)count + 4 * kMaskThreads - 1) / (4 * kMaskThreads);
+  long long cap = (long long)ctx->sm_count * 2;
+  int grid = (int)(want < cap ? want : cap);
+  besteffort_masks8_table_kernel<<<grid, kMaskThreads, masks_smem_bytes(ctx->fast.ans_entries), stream>>>(
+      static_cast<const uint32_t *>(d_reqs), count, ctx->fast, static_cast<uint16_t *>(d_out));
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return GPA_OK;
+}
+
 int launch_masks(gpa_ctx *ctx, const void *d_reqs, int count, int mode_flags, void *d_out, cudaStream_t stream) {
   if (ctx->fast.ans != nullptr && !(mode_flags & GPA_MODE_FORCE_ENUM)) return launch_table(ctx, d_reqs, count, d_out, stream, true, nullptr);
   return launch_fast(ctx, d_reqs, count, mode_flags, d_out, stream, true);
@@ -415,6 +433,69 @@ void parallel_ranges(long long count, int threads, F &&fn) {
   }
   for (auto &th : pool) th.join();
 }
+
+// Host buffers in, host buffers out, for every batch format: the records ride a ring of four streams in chunks, so that
+// while chunk i is in its kernel, chunk i+1 is on the H2D copy engine and chunk i-1 on the D2H one.  Pinned caller
+// buffers (gpa_alloc_host / cudaHostRegister) are DMA'd directly; pageable ones are staged through the context's pinned
+// buffers so that every copy stays asynchronous.  Whatever fails, the streams are drained before the call returns: no
+// copy may still be writing into the caller's buffer afterwards.
+// With GPA_ZERO_COPY=1 in the environment and pinned buffers, nothing is staged at all: the kernels read the records
+// from, and write the answers to, the caller's pinned memory across PCIe (one launch).
+template <typename Launch>
+int host_batch(gpa_ctx *ctx, const void *reqs, void *out, int count, size_t in_size, size_t out_size, int chunk, Launch &&launch) {
+  cudaPointerAttributes pa_in{}, pa_out{};
+  const bool pinned = cudaPointerGetAttributes(&pa_in, reqs) == cudaSuccess && pa_in.type == cudaMemoryTypeHost &&
+                      cudaPointerGetAttributes(&pa_out, out) == cudaSuccess && pa_out.type == cudaMemoryTypeHost;
+  cudaGetLastError();
+  if (pinned && ctx->zero_copy) {
+    void *d_in = nullptr, *d_out = nullptr;
+    if (cudaHostGetDevicePointer(&d_in, const_cast<void *>(reqs), 0) == cudaSuccess && cudaHostGetDevicePointer(&d_out, out, 0) == cudaSuccess) {
+      int rc = launch(d_in, count, d_out, ctx->pipe[0]);
+      cudaError_t e = cudaStreamSynchronize(ctx->pipe[0]);
+      if (e != cudaSuccess && rc == GPA_OK) {
+        ctx->last_error = std::string("cudaStreamSynchronize: ") + cudaGetErrorString(e);
+        rc = GPA_ERR_CUDA;
+      }
+      return rc;
+    }
+    cudaGetLastError();
+  }
+  // the staging buffers are sized in 32 / 16-byte record units
+  const size_t units = std::max(((size_t)count * in_size + sizeof(gpa_request) - 1) / sizeof(gpa_request),
+                                ((size_t)count * out_size + sizeof(gpa_result) - 1) / sizeof(gpa_result)) + 1;
+  int rc = ensure_batch_capacity(ctx, units, !pinned);
+  if (rc != GPA_OK) return rc;
+  if (!pinned) memcpy(ctx->h_reqs, reqs, (size_t)count * in_size);
+  const char *src = static_cast<const char *>(pinned ? reqs : (const void *)ctx->h_reqs);
+  char *dst = static_cast<char *>(pinned ? out : (void *)ctx->h_out);
+  char *d_in = reinterpret_cast<char *>(ctx->d_reqs), *d_out = reinterpret_cast<char *>(ctx->d_out);
+  int c = 0;
+  for (int off = 0; off < count && rc == GPA_OK; off += chunk, c++) {
+    const int cnt = count - off < chunk ? count - off : chunk;
+    cudaStream_t st = ctx->pipe[c & 3];
+    cudaError_t e = cudaMemcpyAsync(d_in + (size_t)off * in_size, src + (size_t)off * in_size, (size_t)cnt * in_size, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) {
+      rc = launch(d_in + (size_t)off * in_size, cnt, d_out + (size_t)off * out_size, st);
+      if (rc != GPA_OK) break;
+      e = cudaMemcpyAsync(dst + (size_t)off * out_size, d_out + (size_t)off * out_size, (size_t)cnt * out_size, cudaMemcpyDeviceToHost, st);
+    }
+    if (e != cudaSuccess) {
+      ctx->last_error = std::string("cudaMemcpyAsync: ") + cudaGetErrorString(e);
+      rc = GPA_ERR_CUDA;
+    }
+  }
+  for (auto &ps : ctx->pipe) {
+    cudaError_t e = cudaStreamSynchronize(ps);
+    if (e != cudaSuccess && rc == GPA_OK) {
+      ctx->last_error = std::string("cudaStreamSynchronize: ") + cudaGetErrorString(e);
+      rc = GPA_ERR_CUDA;
+    }
+  }
+  if (rc != GPA_OK) return rc;
+  if (!pinned) memcpy(out, ctx->h_out, (size_t)count * out_size);
+  return GPA_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -481,6 +562,10 @@ int gpa_create(int cuda_device, gpa_ctx **out) {
   CREATE_TRY(cudaMalloc(&ctx->d_dp_ok, ((size_t)1 << (kMaxDevices - 1)) * sizeof(uint16_t)));
   CREATE_TRY(cudaMemset(ctx->d_key, 0, 2 * sizeof(unsigned long long)));
   CREATE_TRY(cudaMemset(ctx->d_ticket, 0, sizeof(unsigned int)));
+  {
+    const char *zc = getenv("GPA_ZERO_COPY");
+    ctx->zero_copy = zc && *zc == '1';
+  }
   fill_binom(ctx->binom);
   for (uint32_t x = 0; x < 256; x++) ctx->h_tern[x] = (uint16_t)ans_tern(x);
   CREATE_TRY(cudaMemcpyToSymbol(c_binom, &ctx->binom, sizeof(BinomTable)));
@@ -926,45 +1011,17 @@ int gpa_besteffort_batch(gpa_ctx *ctx, const gpa_request *reqs, int count, int m
   std::lock_guard<std::mutex> lk(ctx->mu);
   if (!ctx->has_topo) return GPA_ERR_NO_TOPOLOGY;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-  // Pinned caller buffers (gpa_alloc_host / cudaHostRegister) are DMA'd directly; pageable
-  // ones are staged through the context's pinned mailbox so that every copy stays async.
-  cudaPointerAttributes pa_in{}, pa_out{};
-  bool pinned = cudaPointerGetAttributes(&pa_in, reqs) == cudaSuccess && pa_in.type == cudaMemoryTypeHost &&
-                cudaPointerGetAttributes(&pa_out, out) == cudaSuccess && pa_out.type == cudaMemoryTypeHost;
-  cudaGetLastError();
-  int rc = ensure_batch_capacity(ctx, (size_t)count, !pinned);
-  if (rc != GPA_OK) return rc;
   if (max_avail == 0) {  // caller does not know: one pass over the records
     for (int i = 0; i < count; i++) {
       int na = reqs[i].n_avail;
       if (na > max_avail && na <= GPA_BATCH_MAX_AVAILABLE) max_avail = na;
     }
   }
-  if (!pinned) memcpy(ctx->h_reqs, reqs, (size_t)count * sizeof(gpa_request));
-  const gpa_request *src = pinned ? reqs : ctx->h_reqs;
-  gpa_result *dst = pinned ? out : ctx->h_out;
-  // Chunks ride a ring of streams: while chunk i is in the kernel, chunk i+1 is on the H2D
-  // copy engine and chunk i-1 on the D2H one.
-  const int kChunk = 1 << 18;
-  int c = 0;
-  for (int off = 0; off < count; off += kChunk, c++) {
-    int cnt = count - off < kChunk ? count - off : kChunk;
-    cudaStream_t st = ctx->pipe[c & 3];
-    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->d_reqs + off, src + off, (size_t)cnt * sizeof(gpa_request), cudaMemcpyHostToDevice, st));
-    rc = launch_batch(ctx, ctx->d_reqs + off, cnt, max_avail, mode_flags, ctx->d_out + off, st);
-    if (rc != GPA_OK) break;
-    CUDA_TRY(ctx, cudaMemcpyAsync(dst + off, ctx->d_out + off, (size_t)cnt * sizeof(gpa_result), cudaMemcpyDeviceToHost, st));
-  }
-  for (auto &ps : ctx->pipe) {
-    cudaError_t e = cudaStreamSynchronize(ps);
-    if (e != cudaSuccess && rc == GPA_OK) {
-      ctx->last_error = std::string("cudaStreamSynchronize: ") + cudaGetErrorString(e);
-      rc = GPA_ERR_CUDA;
-    }
-  }
-  if (rc != GPA_OK) return rc;
-  if (!pinned) memcpy(out, ctx->h_out, (size_t)count * sizeof(gpa_result));
-  return GPA_OK;
+  return host_batch(ctx, reqs, out, count, sizeof(gpa_request), sizeof(gpa_result), 1 << 18,
+                    [&](void *d_in, int cnt, void *d_out, cudaStream_t st) {
+                      return launch_batch(ctx, static_cast<const gpa_request *>(d_in), cnt, max_avail, mode_flags,
+                                          static_cast<gpa_result *>(d_out), st);
+                    });
 }
 
 int gpa_besteffort_batch_masks_device(gpa_ctx *ctx, const gpa_mask_request *d_reqs, int count, int mode_flags,
@@ -985,40 +1042,29 @@ int gpa_besteffort_batch_masks(gpa_ctx *ctx, const gpa_mask_request *reqs, int c
   if (!ctx->has_topo) return GPA_ERR_NO_TOPOLOGY;
   if (!ctx->d_sfull) return GPA_ERR_TOO_LARGE;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-  cudaPointerAttributes pa_in{}, pa_out{};
-  bool pinned = cudaPointerGetAttributes(&pa_in, reqs) == cudaSuccess && pa_in.type == cudaMemoryTypeHost &&
-                cudaPointerGetAttributes(&pa_out, out) == cudaSuccess && pa_out.type == cudaMemoryTypeHost;
-  cudaGetLastError();
-  // the staging buffers are sized for the 32/16-byte records, so count/4 of them hold count mask records
-  int rc = ensure_batch_capacity(ctx, (size_t)count / 4 + 1, !pinned);
-  if (rc != GPA_OK) return rc;
-  gpa_mask_request *d_in = reinterpret_cast<gpa_mask_request *>(ctx->d_reqs);
-  gpa_mask_result *d_res = reinterpret_cast<gpa_mask_result *>(ctx->d_out);
-  gpa_mask_request *h_in = reinterpret_cast<gpa_mask_request *>(ctx->h_reqs);
-  gpa_mask_result *h_res = reinterpret_cast<gpa_mask_result *>(ctx->h_out);
-  if (!pinned) memcpy(h_in, reqs, (size_t)count * sizeof(gpa_mask_request));
-  const gpa_mask_request *src = pinned ? reqs : h_in;
-  gpa_mask_result *dst = pinned ? out : h_res;
-  const int kChunk = 1 << 20;
-  int c = 0;
-  for (int off = 0; off < count; off += kChunk, c++) {
-    int cnt = count - off < kChunk ? count - off : kChunk;
-    cudaStream_t st = ctx->pipe[c & 3];
-    CUDA_TRY(ctx, cudaMemcpyAsync(d_in + off, src + off, (size_t)cnt * sizeof(gpa_mask_request), cudaMemcpyHostToDevice, st));
-    rc = launch_masks(ctx, d_in + off, cnt, mode_flags, d_res + off, st);
-    if (rc != GPA_OK) break;
-    CUDA_TRY(ctx, cudaMemcpyAsync(dst + off, d_res + off, (size_t)cnt * sizeof(gpa_mask_result), cudaMemcpyDeviceToHost, st));
-  }
-  for (auto &ps : ctx->pipe) {
-    cudaError_t e = cudaStreamSynchronize(ps);
-    if (e != cudaSuccess && rc == GPA_OK) {
-      ctx->last_error = std::string("cudaStreamSynchronize: ") + cudaGetErrorString(e);
-      rc = GPA_ERR_CUDA;
-    }
-  }
-  if (rc != GPA_OK) return rc;
-  if (!pinned) memcpy(out, h_res, (size_t)count * sizeof(gpa_mask_result));
-  return GPA_OK;
+  return host_batch(ctx, reqs, out, count, sizeof(gpa_mask_request), sizeof(gpa_mask_result), 1 << 20,
+                    [&](void *d_in, int cnt, void *d_out, cudaStream_t st) { return launch_masks(ctx, d_in, cnt, mode_flags, d_out, st); });
+}
+
+int gpa_besteffort_batch_masks8_device(gpa_ctx *ctx, const gpa_mask8_request *d_reqs, int count, gpa_mask8_result *d_out, void *stream) {
+  if (!ctx || count < 0 || (count > 0 && (!d_reqs || !d_out))) return GPA_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  if (!ctx->has_topo) return GPA_ERR_NO_TOPOLOGY;
+  if (!ctx->fast.ans) return GPA_ERR_TOO_LARGE;  // the compact format is answered from the answer table only: <= 8 GPUs
+  if (count == 0) return GPA_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  return launch_masks8(ctx, d_reqs, count, d_out, (cudaStream_t)stream);
+}
+
+int gpa_besteffort_batch_masks8(gpa_ctx *ctx, const gpa_mask8_request *reqs, int count, gpa_mask8_result *out) {
+  if (!ctx || count < 0 || (count > 0 && (!reqs || !out))) return GPA_ERR_INVALID;
+  if (count == 0) return GPA_OK;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  if (!ctx->has_topo) return GPA_ERR_NO_TOPOLOGY;
+  if (!ctx->fast.ans) return GPA_ERR_TOO_LARGE;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  return host_batch(ctx, reqs, out, count, sizeof(gpa_mask8_request), sizeof(gpa_mask8_result), 1 << 20,
+                    [&](void *d_in, int cnt, void *d_out, cudaStream_t st) { return launch_masks8(ctx, d_in, cnt, d_out, st); });
 }
 
 // ---- host-side conversion between the two batch formats (plain C++, no device work) ---------------------------

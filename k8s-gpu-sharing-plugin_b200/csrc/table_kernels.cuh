@@ -266,4 +266,45 @@ __global__ void __launch_bounds__(kMaskThreads) besteffort_masks_table_kernel(co
   }
 }
 
+// 4-byte gpa_mask8_request in, 2-byte gpa_mask8_result out: the compact format of nodes of up to 8 GPUs.  Four records
+// per lane per step (16 bytes in, 8 bytes out) when the buffers are aligned for it.
+__global__ void __launch_bounds__(kMaskThreads) besteffort_masks8_table_kernel(const uint32_t *__restrict__ reqs, int count,
+                                                                               const FastTopo ft, uint16_t *__restrict__ out) {
+  extern __shared__ __align__(128) unsigned char tsmem[];
+  unsigned long long *s_dev = reinterpret_cast<unsigned long long *>(tsmem);
+  uint16_t *s_tern = reinterpret_cast<uint16_t *>(s_dev + 256);
+  uint16_t *s_ans = s_tern + 256;
+  const int tid = threadIdx.x;
+  stage_tables(ft, s_dev, s_tern, s_ans, tid, kMaskThreads);
+  __syncthreads();
+
+  const uint32_t node_mask = (1u << ft.nt) - 1u;
+  auto answer = [&](uint32_t x) -> uint32_t {
+    // {avail_mask:8, req_mask:8, size:8, flags:8} -> {chosen_mask:8, n_nil:8}; n_nil 0x80 = a device the node does not have
+    const uint32_t mask = x & 0xFFu, rl = (x >> 8) & 0xFFu;
+    const int size = (int)((x >> 16) & 0xFFu);
+    if (((mask | rl) & ~node_mask) != 0) return 0x8000u;
+    // guards of besteffort_policy.go:35-45; a required device that is not available is in no set (:53)
+    if (size <= 0 || __popc(mask) < size || __popc(rl) > size || ((x >> 24) & GPA_REQ_FOREIGN) || (rl & ~mask) != 0) return 0u;
+    return s_ans[ans_index(s_tern, mask, rl, size)];  // the table entry IS the result record
+  };
+  if (((reinterpret_cast<uintptr_t>(reqs) & 15u) | (reinterpret_cast<uintptr_t>(out) & 7u)) == 0) {
+    const long long n_quads = (long long)count >> 2;
+    for (long long q = (long long)blockIdx.x * kMaskThreads + tid; q < n_quads; q += (long long)gridDim.x * kMaskThreads) {
+      const uint4 rec = __ldg(reinterpret_cast<const uint4 *>(reqs) + q);
+      uint2 res;
+      res.x = answer(rec.x) | (answer(rec.y) << 16);
+      res.y = answer(rec.z) | (answer(rec.w) << 16);
+      reinterpret_cast<uint2 *>(out)[q] = res;
+    }
+    if (blockIdx.x == 0 && tid < (count & 3)) {
+      const long long r = (n_quads << 2) + tid;
+      out[r] = (uint16_t)answer(__ldg(reqs + r));
+    }
+  } else {
+    for (long long r = (long long)blockIdx.x * kMaskThreads + tid; r < count; r += (long long)gridDim.x * kMaskThreads)
+      out[r] = (uint16_t)answer(__ldg(reqs + r));
+  }
+}
+
 }  // namespace

@@ -273,6 +273,31 @@ MASK_RES_DTYPE = np.dtype([("chosen_mask", np.uint16), ("n_nil", np.uint8), ("st
 assert MASK_REQ_DTYPE.itemsize == 8 and MASK_RES_DTYPE.itemsize == 4
 
 
+MASK8_REQ_DTYPE = np.dtype([("avail_mask", np.uint8), ("req_mask", np.uint8), ("size", np.uint8), ("flags", np.uint8)])
+MASK8_RES_DTYPE = np.dtype([("chosen_mask", np.uint8), ("n_nil", np.uint8)])
+assert MASK8_REQ_DTYPE.itemsize == 4 and MASK8_RES_DTYPE.itemsize == 2
+
+
+def masks_to_masks8(masks):
+    """MASK_REQ_DTYPE records of a node of up to 8 GPUs -> the compact MASK8_REQ_DTYPE; required devices that the mask
+    format only counts (n_req_extra) become the FOREIGN flag: the answer is empty either way"""
+    assert (masks["avail_mask"] < 256).all() and (masks["req_mask"] < 256).all()
+    out = np.zeros(len(masks), dtype=MASK8_REQ_DTYPE)
+    out["avail_mask"], out["req_mask"], out["size"] = masks["avail_mask"], masks["req_mask"], masks["size"]
+    out["flags"] = (masks["flags"] & FLAG_REQ_FOREIGN) | (masks["n_req_extra"] > 0)
+    return out
+
+
+def masks8_results_to_masks(res):
+    """MASK8_RES_DTYPE -> MASK_RES_DTYPE (n_nil 0x80 = GPA_ERR_INVALID)"""
+    out = np.zeros(len(res), dtype=MASK_RES_DTYPE)
+    bad = res["n_nil"] == 0x80
+    out["chosen_mask"] = np.where(bad, 0, res["chosen_mask"])
+    out["n_nil"] = np.where(bad, 0, res["n_nil"])
+    out["status"] = np.where(bad, -1, 0)
+    return out
+
+
 def records_to_masks(reqs, order):
     """REQ_DTYPE records whose device lists follow `order` (label -> NVML index) -> MASK_REQ_DTYPE records"""
     rank = np.full(256, 255, dtype=np.int64)

@@ -122,7 +122,7 @@ def test_xid_event_rereads_the_matrix_and_rebuilds_the_answer_table(fake_nvml):
         assert seen == [1]
         W1, nl1 = ctx.get_topology()
         assert W0[2, 3] == 10 and W1[2, 3] == 50 and (W1 != W0).sum() == 2
-        assert ctx.launch_count == launches0 + 1 and (ctx.answer_table() != table0).any()
+        assert ctx.launch_count > launches0 and (ctx.answer_table() != table0).any()  # the build kernel ran again
         want = orc.besteffort(W1, nl1, [0, 1, 2, 3], [], 2)
         assert want == (orc.OK, [2, 3]) and ctx.besteffort([0, 1, 2, 3], [], 2) == (gpa.OK, [2, 3])
     finally:

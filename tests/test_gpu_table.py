@@ -224,3 +224,42 @@ def test_host_pack_and_unpack_helpers(ctx, oracle):
     res = ctx.unpack_mask_results(ctx.besteffort_batch_masks(packed))
     assert gpa.decode_result(res[0]) == (gpa.ERR_INVALID, []) and gpa.decode_result(res[1]) == (gpa.ERR_INVALID, [])
     assert gpa.decode_result(res[2])[0] == gpa.OK
+
+
+def test_compact_mask8_records(ctx, oracle):
+    """the 4-byte / 2-byte format of nodes of up to 8 GPUs: same answers as the mask format and the oracle, at every
+    alignment of the record count; unknown devices and unavailable required devices as in the mask format"""
+    name, t = syn.standard_topologies()[9]
+    W, nl = syn.links_to_weights(t)
+    ctx.set_topology_links(t)
+    ctx.set_device_order(ORDER8)
+    for count in (1, 2, 3, 4, 5, 7, 4096, 100003):
+        reqs = syn.random_request_batch(8, count, seed=1000 + count, order=ORDER8)
+        if count > 100:
+            reqs[10:12] = syn.pack_requests([(ORDER8[:4], [gpa.FOREIGN], 2), (ORDER8[:4], [gpa.FOREIGN] * 3, 2)])
+        masks = syn.records_to_masks(reqs, ORDER8)
+        m8 = syn.masks_to_masks8(masks)
+        if count > 100:
+            m8["avail_mask"][4], m8["req_mask"][4], m8["size"][4], m8["flags"][4] = 0x0F, 0x10, 2, 0   # required, not available
+        got = syn.masks8_results_to_masks(ctx.besteffort_batch_masks8(m8))
+        want, _ = oracle.besteffort_batch(W, nl, reqs, threads=8)
+        rec = syn.mask_results_to_records(got.copy(), ORDER8)
+        ok = (rec["dev"] == want["dev"]).all(axis=1)
+        if count > 100:
+            assert got["chosen_mask"][4] == 0 and got["status"][4] == 0
+            ok[4] = True
+        assert ok.all(), (count, int(np.nonzero(~ok)[0][0]))
+    # a smaller node: a mask bit beyond it is an invalid record
+    t5 = syn.topo_random(5, 3)
+    ctx.set_topology_links(t5)
+    ctx.set_device_order(list(range(5)))
+    m8 = np.zeros(3, dtype=syn.MASK8_REQ_DTYPE)
+    m8["avail_mask"], m8["size"] = [0b11111, 0b100011, 0b00111], [2, 2, 2]
+    m8["req_mask"][2] = 0b1000000
+    got = ctx.besteffort_batch_masks8(m8)
+    assert got["n_nil"].tolist()[1:] == [0x80, 0x80] and got["n_nil"][0] == 0 and bin(int(got["chosen_mask"][0])).count("1") == 2
+    # nodes without an answer table have no compact format
+    ctx.set_topology_links(syn.topo_random(9, 3))
+    with pytest.raises(gpa.GpaError) as e:
+        ctx.besteffort_batch_masks8(m8)
+    assert e.value.code == gpa.ERR_TOO_LARGE
