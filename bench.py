@@ -396,7 +396,8 @@ def run_ours(args):
         "e2e_masks": {"value": world * len(reqs) / m16_s, "unit": UNIT, "ms_per_step": m16_s * 1e3,
                       "h2d_bytes_per_step": 8 * len(reqs), "d2h_bytes_per_step": 4 * len(reqs), "mismatches": m16_mismatch,
                       "gpu_launches_per_step": m16_launches,
-                      "path": "gpa_besteffort_batch_masks: 8-byte mask records, 1 Mi-request chunks pipelined over 4 streams"},
+                      "path": "gpa_besteffort_batch_masks: 8-byte mask records read from / 4-byte results written to pinned host "
+                              "memory by the kernel (one launch)"},
         "e2e_records": {"value": world * len(reqs) / rec_s, "unit": UNIT, "ms_per_step": rec_s * 1e3,
                         "h2d_bytes_per_step": 32 * len(reqs), "d2h_bytes_per_step": 16 * len(reqs), "mismatches": rec_mismatch,
                         "gpu_launches_per_step": rec_launches,
@@ -679,8 +680,9 @@ def run_ours(args):
         "dtype": "int32", "data": "synthetic", "config": workload_config(world),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 4 * len(reqs), "d2h_bytes_per_step": 2 * len(reqs),
                 "ms_per_step": e2e_s * 1e3, "gpu_launches_per_step": e2e_launches, "mismatches": e2e_mismatch,
-                "path": "gpa_besteffort_batch_masks8: 4-byte compact mask records in pinned host memory -> HBM -> table kernel -> "
-                        "2-byte results back in pinned host memory; 1 Mi-request chunks pipelined over 4 streams"},
+                "path": "gpa_besteffort_batch_masks8: 4-byte compact mask records in pinned host memory; the table kernel reads "
+                        "them across PCIe and writes the 2-byte results back into pinned host memory (one launch, nothing "
+                        "staged; GPA_ZERO_COPY=0 selects the staged copy/kernel/copy pipeline instead)"},
         "gpu_launches": int(launches),
         "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": sampler.summary(), "pcie": pcie,
         "parity": {"checked": int(len(idx)), "mismatches_device_arm": mismatches, "mismatches_e2e_arm": e2e_mismatch},
