@@ -72,29 +72,37 @@ struct Group {
 
 namespace {
 
-// strings.TrimSpace: ASCII white space plus the two Latin-1 spaces U+0085 / U+00A0 (as UTF-8)
+// strings.TrimSpace trims every rune with unicode.IsSpace: '\t' '\n' '\v' '\f' '\r' ' ', U+0085, U+00A0 and the Unicode
+// Z category / White_Space property: U+1680, U+2000..U+200A, U+2028, U+2029, U+202F, U+205F, U+3000 (as UTF-8 here).
+// length in bytes of the white-space rune that STARTS at p (0 = none)
+size_t space_rune_at(const unsigned char *p, size_t n) {
+  if (n == 0) return 0;
+  const unsigned char c = p[0];
+  if (c == ' ' || (c >= '\t' && c <= '\r')) return 1;
+  if (c == 0xC2 && n >= 2 && (p[1] == 0x85 || p[1] == 0xA0)) return 2;
+  if (n >= 3) {
+    if (c == 0xE1 && p[1] == 0x9A && p[2] == 0x80) return 3;                               // U+1680
+    if (c == 0xE2 && p[1] == 0x80 && ((p[2] >= 0x80 && p[2] <= 0x8A) || p[2] == 0xA8 || p[2] == 0xA9 || p[2] == 0xAF)) return 3;
+    if (c == 0xE2 && p[1] == 0x81 && p[2] == 0x9F) return 3;                               // U+205F
+    if (c == 0xE3 && p[1] == 0x80 && p[2] == 0x80) return 3;                               // U+3000
+  }
+  return 0;
+}
+
 std::string_view go_trim_space(std::string_view v) {
   for (;;) {
-    if (v.empty()) return v;
-    const unsigned char c = (unsigned char)v[0];
-    if (c == ' ' || (c >= '\t' && c <= '\r')) {
-      v.remove_prefix(1);
-    } else if (c == 0xC2 && v.size() >= 2 && ((unsigned char)v[1] == 0x85 || (unsigned char)v[1] == 0xA0)) {
-      v.remove_prefix(2);
-    } else {
-      break;
-    }
+    const size_t k = space_rune_at(reinterpret_cast<const unsigned char *>(v.data()), v.size());
+    if (k == 0) break;
+    v.remove_prefix(k);
   }
   for (;;) {
-    if (v.empty()) return v;
-    const unsigned char c = (unsigned char)v.back();
-    if (c == ' ' || (c >= '\t' && c <= '\r')) {
-      v.remove_suffix(1);
-    } else if ((c == 0x85 || c == 0xA0) && v.size() >= 2 && (unsigned char)v[v.size() - 2] == 0xC2) {
-      v.remove_suffix(2);
-    } else {
-      break;
+    size_t k = 0;
+    for (size_t len = 1; len <= 3 && len <= v.size() && k == 0; len++) {
+      const unsigned char *p = reinterpret_cast<const unsigned char *>(v.data()) + v.size() - len;
+      if (space_rune_at(p, len) == len) k = len;
     }
+    if (k == 0) break;
+    v.remove_suffix(k);
   }
   return v;
 }

@@ -260,27 +260,28 @@ done:
     return rc;
 }
 
-/* strings.TrimSpace for the ASCII range plus U+0085 / U+00A0 (the Latin-1 spaces) */
-static int is_go_space(const unsigned char *p, int *adv)
+/* unicode.IsSpace, which strings.TrimSpace trims by: '\t' '\n' '\v' '\f' '\r' ' ', U+0085, U+00A0, U+1680,
+ * U+2000..U+200A, U+2028, U+2029, U+202F, U+205F, U+3000.  Returns the UTF-8 length of the white-space rune that
+ * starts at p (n bytes are readable), 0 if there is none. */
+static int go_space_len(const unsigned char *p, long n)
 {
-    *adv = 1;
-    switch (*p) {
-    case ' ':
-    case '\t':
-    case '\n':
-    case '\v':
-    case '\f':
-    case '\r':
+    if (n <= 0)
+        return 0;
+    if (*p == ' ' || (*p >= '\t' && *p <= '\r'))
         return 1;
-    case 0xC2:
-        if (p[1] == 0x85 || p[1] == 0xA0) {
-            *adv = 2;
-            return 1;
-        }
-        return 0;
-    default:
-        return 0;
+    if (n >= 2 && p[0] == 0xC2 && (p[1] == 0x85 || p[1] == 0xA0))
+        return 2;
+    if (n >= 3) {
+        if (p[0] == 0xE1 && p[1] == 0x9A && p[2] == 0x80)
+            return 3;
+        if (p[0] == 0xE2 && p[1] == 0x80 && ((p[2] >= 0x80 && p[2] <= 0x8A) || p[2] == 0xA8 || p[2] == 0xA9 || p[2] == 0xAF))
+            return 3;
+        if (p[0] == 0xE2 && p[1] == 0x81 && p[2] == 0x9F)
+            return 3;
+        if (p[0] == 0xE3 && p[1] == 0x80 && p[2] == 0x80)
+            return 3;
     }
+    return 0;
 }
 
 /*
@@ -300,15 +301,16 @@ int ref_get_additional_xids(const char *input, uint64_t *out, int out_cap)
         /* :281 TrimSpace */
         const unsigned char *b = (const unsigned char *)p, *e = b + len;
         int adv;
-        while (b < e && is_go_space(b, &adv))
+        while ((adv = go_space_len(b, e - b)) > 0)
             b += adv;
-        while (e > b) {
-            if (e - b >= 2 && e[-2] == 0xC2 && (e[-1] == 0x85 || e[-1] == 0xA0))
-                e -= 2;
-            else if (is_go_space(e - 1, &adv) && adv == 1)
-                e -= 1;
-            else
+        for (;;) {
+            int cut = 0;
+            for (int len = 1; len <= 3 && len <= e - b && !cut; len++)
+                if (go_space_len(e - len, len) == len)
+                    cut = len;
+            if (!cut)
                 break;
+            e -= cut;
         }
         if (b < e) { /* :282-284 */
             int ok = 1;

@@ -167,3 +167,13 @@ def test_product_never_reaches_into_the_oracle():
     needed = subprocess.run(["readelf", "-d", os.path.join(pkg, "libgpualloc.so")], capture_output=True, text=True).stdout
     assert "NEEDED" in needed
     assert "liboracle" not in needed
+
+
+def test_additional_xids_trim_every_unicode_space(oracle):
+    """strings.TrimSpace (cmd/nvidia-device-plugin/nvidia.go:281) trims by unicode.IsSpace: not only ASCII white space and
+    the Latin-1 NEL / NBSP but also U+1680, U+2000..U+200A, U+2028, U+2029, U+202F, U+205F and U+3000.  A space INSIDE a
+    token is not trimmed and makes it malformed (skipped)."""
+    s = " 13\u2003,\u300045\u00a0,\u168031\u2028\u2029,\u202f\u205f68\t\v,7\u20039,\u0085\n94\r\f, \u200b5"
+    want = [13, 45, 31, 68, 94]     # "7<em space>9" and "<zero width space>5" (not White_Space) are malformed
+    assert gpa.get_additional_xids(s) == want
+    assert oracle.get_additional_xids(s) == want
