@@ -555,6 +555,11 @@ def run_ours(args):
         "single_decision_n8": run_tool("latency"),
         "single_decision_n16_k3_ms": {"gpu_call_p50": search16["call_ms_p50"], "oracle_call": cpu_n16_ms},
     }
+    # what the reference pays in NVML calls per request (2 x gpuallocator.NewDevices, device.go:33-72) on THIS box's driver,
+    # next to one gpa_nvml_read_topology(); a 1-GPU box has no pairs - the 8-GPU figure is profiles/r02_nvml_reenumeration.json
+    nvml_reenumeration = run_tool("nvml_reenum", 10)
+    nvml_reenumeration["on_8_gpus"] = ("profiles/r02_nvml_reenumeration.json: 3010 NVML calls, 303 ms p50 / 604 ms p99 per request in "
+                                       "the reference's sequence; 265 calls, 100 ms once at start-up here")
     # replicas > 1: the reference answers with prioritizeDevices (server.go:285-296): host C++ here as well
     replica_mode = {"get_preferred_allocation": run_tool("replica_bench"),
                     "config2_stream": {"%d_virtual_devices" % (N_DEV * r): run_tool("stream", r, 100000) for r in (4, 16, 32)},
@@ -687,7 +692,7 @@ def run_ours(args):
         "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": sampler.summary(), "pcie": pcie,
         "parity": {"checked": int(len(idx)), "mismatches_device_arm": mismatches, "mismatches_e2e_arm": e2e_mismatch},
         "other_formats": other_formats, "box_topology": box_topology, "search_n16": search16, "latency": latency,
-        "replica_mode": replica_mode, "replica_set": replica_set,
+        "replica_mode": replica_mode, "replica_set": replica_set, "nvml_reenumeration": nvml_reenumeration,
     }
     print(json.dumps(line))
     if use_dist:
