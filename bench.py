@@ -443,7 +443,7 @@ def run_ours(args):
     roofline = {
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
         "traffic_source": traffic_src,
-        "kernel": "besteffort_batch_table_kernel (+ the general kernel's deferred pass, which finds nothing to do)",
+        "kernel": "besteffort_batch_table_kernel (the whole step is this one launch)",
         "peak_source": peak_src + ", burst",
         "bytes_per_launch": io_bytes,
         "what": "achieved = the bytes the step must move (32-byte request + 16-byte result per decision) / event-timed step; "

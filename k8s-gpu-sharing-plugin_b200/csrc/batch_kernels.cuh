@@ -23,162 +23,140 @@ __device__ __forceinline__ void write_result(gpa_result *out, const int8_t *dev)
   *reinterpret_cast<int4 *>(out->dev) = *src;
 }
 
-// General batch kernel: any `available` order, per-request score table, one warp per request.
-// With deferred_only it answers just the records the fast kernel marked GPA_RES_DEFER: each
-// warp scans 32 result records at a time (one coalesced load) and works on the marked ones.
-// defer_flags (optional, one byte per 32 records, written by the table kernel) says which
-// groups of 32 hold a marked record at all: a warp then reads 32 flags per load and touches
-// the result records of flagged groups only - 1/512 of the traffic when nothing was deferred.
+// One request answered by one WARP: any `available` order, per-request score table S (2^s_log2 uint16) and weights wp
+// (kMaxDevices^2 uint16) in this warp's shared memory.  The general path of the batch kernels.
+__device__ __noinline__ void general_request(const gpa_request *__restrict__ reqs, long long r, int n_cap, int s_log2, int intended,
+                                             const BatchTopo topo, gpa_result *out, uint16_t *S, uint16_t *wp,
+                                             const BinomTable &s_binom, int lane) {
+  const STab stab{S};
+  // 32-byte record, same address in every lane: one broadcast transaction each
+  const uint4 lo = __ldg(reinterpret_cast<const uint4 *>(reqs + r));
+  const uint4 hi = __ldg(reinterpret_cast<const uint4 *>(reqs + r) + 1);
+  const uint32_t availw[4] = {lo.x, lo.y, lo.z, lo.w};
+  const uint32_t rmask = hi.x & 0xFFFFu;
+  const int n = (hi.x >> 16) & 0xFF;
+  const int size = (hi.x >> 24) & 0xFF;
+  const int flags = hi.y & 0xFF;
+  const int n_req = __popc(rmask) + ((hi.y >> 8) & 0xFF);
+  auto dev_at = [&](int pidx) -> int { return (availw[pidx >> 2] >> ((pidx & 3) * 8)) & 0xFF; };
+
+  __align__(16) int8_t res[GPA_MAX_AVAILABLE];
+#pragma unroll
+  for (int i = 0; i < GPA_MAX_AVAILABLE; i++) res[i] = GPA_RES_END;
+  int err = 0;
+  bool done = false;
+
+  // guards of besteffort_policy.go:35-45, in the reference's order
+  if (size <= 0 || n < size || n_req > size) done = true;
+  if (!done) {
+    if (n > n_cap || n > GPA_BATCH_MAX_AVAILABLE) {
+      err = GPA_ERR_TOO_LARGE;
+    } else {
+      unsigned long long seen = 0;
+      for (int a = 0; a < n; a++) {
+        int d = dev_at(a);
+        if (d >= topo.nt) {
+          err = GPA_ERR_INVALID;
+        } else {
+          if (seen >> d & 1ull) err = GPA_ERR_INVALID;  // the same device twice
+          seen |= 1ull << d;
+        }
+      }
+      if ((rmask >> n) != 0) err = GPA_ERR_INVALID;
+      // the caller's S holds 2^s_log2 masks (the table kernel passes 8: more distinct devices than its node has cannot
+      // be listed, so a longer list has failed the checks above already)
+      if (!err && n > s_log2) err = GPA_ERR_INVALID;
+    }
+    if (err) done = true;
+  }
+  if (!done && (flags & GPA_REQ_FOREIGN)) done = true;  // no candidate can contain a foreign pointer (:53)
+  if (!done && size == 1) {
+    // :219-224 — single-device candidates in `available` order, first accepted wins (score 0 never beats 0)
+    res[0] = (int8_t)dev_at(rmask ? __ffs(rmask) - 1 : 0);
+    done = true;
+  }
+  if (!done) {
+    // the request's weights by position; a pair whose link counts differ is poisoned, so that the search itself finds
+    // out whether Go would ever have scored it (kAsymPoison, kernels_common.cuh)
+    for (int i = lane; i < n * n; i += 32) {
+      int a = i / n, b = i - a * n;
+      int da = dev_at(a), db = dev_at(b);
+      if (a < b) wp[a * kMaxDevices + b] = topo.asym[da * topo.nt + db] ? (uint16_t)kAsymPoison : topo.wq[da * topo.nt + db];
+    }
+    __syncwarp();
+    const Geom g = make_geom(n, size, rmask);
+    fill_score_table(S, wp, g, lane, 32);
+    __syncwarp();
+    const Cut cut = choose_cut(g, s_binom, 64);
+    unsigned long long best = 0;
+    for (unsigned long long item = lane; item < cut.n_items; item += 32) {
+      int sc = search_item(g, cut, s_binom, stab, item);
+      if (sc >= 0) {
+        unsigned long long kk = pack_key(sc, item);
+        best = kk > best ? kk : best;
+      }
+    }
+    best = warp_max_u64(best);
+    if (lane == 0) {
+      int8_t pos[32];
+      int cnt = finalize(g, cut, s_binom, stab, best, intended != 0, pos);
+      if (best != 0 && key_score(best) >= (int)kAsymPoison) {
+        err = GPA_ERR_ASYMMETRIC;  // an accepted candidate holds such a pair: the panic of :307-310 while iterating
+      } else if (cnt < 0) {
+        err = GPA_ERR_INVALID;
+      } else {
+        // the chosen set is the best-scoring set of the saved partition that holds the required devices: if any of
+        // those sets held such a pair it is this one (the panic inside the loop of :77-85)
+        uint32_t chosen = 0;
+        for (int i = 0; i < cnt; i++)
+          if (pos[i] >= 0) chosen |= 1u << pos[i];
+        if (cnt > 0 && S[chosen] >= kAsymPoison) {
+          err = GPA_ERR_ASYMMETRIC;
+        } else {
+          for (int i = 0; i < cnt; i++) res[i] = pos[i] < 0 ? (int8_t)GPA_NIL : (int8_t)dev_at(pos[i]);
+        }
+      }
+    }
+    __syncwarp();  // S / wp are reused by the next request of this warp
+  }
+  if (lane == 0) {
+    if (err) {
+      res[0] = GPA_RES_ERROR;
+      res[1] = (int8_t)err;
+    }
+    write_result(out + r, res);
+  }
+}
+
+// General batch kernel: one warp per request through general_request().
+// With deferred_only it answers just the records the tile-binned kernel marked kResDefer: each warp scans 32 result
+// records at a time (one coalesced load) and works on the marked ones.
 __global__ void __launch_bounds__(kBatchWarps * 32) besteffort_batch_kernel(const gpa_request *__restrict__ reqs, int count,
                                                                             int n_cap, int intended, BatchTopo topo,
-                                                                            gpa_result *out, int deferred_only,
-                                                                            const uint8_t *__restrict__ defer_flags) {
+                                                                            gpa_result *out, int deferred_only) {
   extern __shared__ __align__(16) uint16_t smem[];
   __shared__ BinomTable s_binom;
-  if (deferred_only && defer_flags != nullptr) {
-    // nothing flagged among the groups this CTA would scan (the usual case: every record was in node order): leave
-    // before staging anything, so that the pass costs a launch and one byte per 32 records
-    const long long n_groups = ((long long)count + 31) / 32;
-    int any = 0;
-    for (long long gi = (long long)blockIdx.x * (kBatchWarps * 32) + threadIdx.x; gi < n_groups;
-         gi += (long long)gridDim.x * (kBatchWarps * 32))
-      any |= defer_flags[gi] != 0;
-    if (!__syncthreads_or(any)) return;
-  }
   stage_binom(s_binom, threadIdx.x, kBatchWarps * 32);
   __syncthreads();
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   uint16_t *S = smem + (size_t)warp * ((1u << n_cap) + kMaxDevices * kMaxDevices);
   uint16_t *wp = S + (1u << n_cap);
-  const STab stab{S};
-
-  auto process = [&](int r) {
-    // 32-byte record, same address in every lane: one broadcast transaction each
-    const uint4 lo = __ldg(reinterpret_cast<const uint4 *>(reqs + r));
-    const uint4 hi = __ldg(reinterpret_cast<const uint4 *>(reqs + r) + 1);
-    const uint32_t availw[4] = {lo.x, lo.y, lo.z, lo.w};
-    const uint32_t rmask = hi.x & 0xFFFFu;
-    const int n = (hi.x >> 16) & 0xFF;
-    const int size = (hi.x >> 24) & 0xFF;
-    const int flags = hi.y & 0xFF;
-    const int n_req = __popc(rmask) + ((hi.y >> 8) & 0xFF);
-    auto dev_at = [&](int pidx) -> int { return (availw[pidx >> 2] >> ((pidx & 3) * 8)) & 0xFF; };
-
-    __align__(16) int8_t res[GPA_MAX_AVAILABLE];
-#pragma unroll
-    for (int i = 0; i < GPA_MAX_AVAILABLE; i++) res[i] = GPA_RES_END;
-    int err = 0;
-    bool done = false;
-
-    // guards of besteffort_policy.go:35-45, in the reference's order
-    if (size <= 0 || n < size || n_req > size) done = true;
-    if (!done) {
-      if (n > n_cap || n > GPA_BATCH_MAX_AVAILABLE) {
-        err = GPA_ERR_TOO_LARGE;
-      } else {
-        unsigned long long seen = 0;
-        for (int a = 0; a < n; a++) {
-          int d = dev_at(a);
-          if (d >= topo.nt) {
-            err = GPA_ERR_INVALID;
-          } else {
-            if (seen >> d & 1ull) err = GPA_ERR_INVALID;  // the same device twice
-            seen |= 1ull << d;
-          }
-        }
-        if ((rmask >> n) != 0) err = GPA_ERR_INVALID;
-      }
-      if (err) done = true;
-    }
-    if (!done && (flags & GPA_REQ_FOREIGN)) done = true;  // no candidate can contain a foreign pointer (:53)
-    if (!done && size == 1) {
-      // :219-224 — single-device candidates in `available` order, first accepted wins (score 0 never beats 0)
-      res[0] = (int8_t)dev_at(rmask ? __ffs(rmask) - 1 : 0);
-      done = true;
-    }
-    if (!done) {
-      // the request's weights by position; a pair whose link counts differ is poisoned, so that the search itself finds
-      // out whether Go would ever have scored it (kAsymPoison, kernels_common.cuh)
-      for (int i = lane; i < n * n; i += 32) {
-        int a = i / n, b = i - a * n;
-        int da = dev_at(a), db = dev_at(b);
-        if (a < b) wp[a * kMaxDevices + b] = topo.asym[da * topo.nt + db] ? (uint16_t)kAsymPoison : topo.wq[da * topo.nt + db];
-      }
-      __syncwarp();
-      const Geom g = make_geom(n, size, rmask);
-      fill_score_table(S, wp, g, lane, 32);
-      __syncwarp();
-      const Cut cut = choose_cut(g, s_binom, 64);
-      unsigned long long best = 0;
-      for (unsigned long long item = lane; item < cut.n_items; item += 32) {
-        int sc = search_item(g, cut, s_binom, stab, item);
-        if (sc >= 0) {
-          unsigned long long kk = pack_key(sc, item);
-          best = kk > best ? kk : best;
-        }
-      }
-      best = warp_max_u64(best);
-      if (lane == 0) {
-        int8_t pos[32];
-        int cnt = finalize(g, cut, s_binom, stab, best, intended != 0, pos);
-        if (best != 0 && key_score(best) >= (int)kAsymPoison) {
-          err = GPA_ERR_ASYMMETRIC;  // an accepted candidate holds such a pair: the panic of :307-310 while iterating
-        } else if (cnt < 0) {
-          err = GPA_ERR_INVALID;
-        } else {
-          // the chosen set is the best-scoring set of the saved partition that holds the required devices: if any of
-          // those sets held such a pair it is this one (the panic inside the loop of :77-85)
-          uint32_t chosen = 0;
-          for (int i = 0; i < cnt; i++)
-            if (pos[i] >= 0) chosen |= 1u << pos[i];
-          if (cnt > 0 && S[chosen] >= kAsymPoison) {
-            err = GPA_ERR_ASYMMETRIC;
-          } else {
-            for (int i = 0; i < cnt; i++) res[i] = pos[i] < 0 ? (int8_t)GPA_NIL : (int8_t)dev_at(pos[i]);
-          }
-        }
-      }
-      __syncwarp();  // S / wp are reused by the next request of this warp
-    }
-    if (lane == 0) {
-      if (err) {
-        res[0] = GPA_RES_ERROR;
-        res[1] = (int8_t)err;
-      }
-      write_result(out + r, res);
-    }
-  };
 
   if (!deferred_only) {
-    for (int r = blockIdx.x * kBatchWarps + warp; r < count; r += gridDim.x * kBatchWarps) process(r);
+    for (long long r = (long long)blockIdx.x * kBatchWarps + warp; r < count; r += (long long)gridDim.x * kBatchWarps)
+      general_request(reqs, r, n_cap, n_cap, intended, topo, out, S, wp, s_binom, lane);
   } else {
-    auto scan_group = [&](long long base) {
+    for (long long base = ((long long)blockIdx.x * kBatchWarps + warp) * 32; base < count;
+         base += (long long)gridDim.x * kBatchWarps * 32) {
       const long long r = base + lane;
       const bool marked = r < count && out[r].dev[0] == kResDefer;
       unsigned todo = __ballot_sync(0xffffffffu, marked);
       while (todo) {
         const int b = __ffs(todo) - 1;
         todo &= todo - 1;
-        process((int)(base + b));
+        general_request(reqs, base + b, n_cap, n_cap, intended, topo, out, S, wp, s_binom, lane);
         __syncwarp();
-      }
-    };
-    if (defer_flags == nullptr) {
-      for (long long base = ((long long)blockIdx.x * kBatchWarps + warp) * 32; base < count;
-           base += (long long)gridDim.x * kBatchWarps * 32)
-        scan_group(base);
-    } else {
-      const long long n_groups = ((long long)count + 31) / 32;
-      for (long long g0 = ((long long)blockIdx.x * kBatchWarps + warp) * 32; g0 < n_groups;
-           g0 += (long long)gridDim.x * kBatchWarps * 32) {
-        const long long gi = g0 + lane;
-        unsigned flagged = __ballot_sync(0xffffffffu, gi < n_groups && defer_flags[gi] != 0);
-        while (flagged) {
-          const int gb = __ffs(flagged) - 1;
-          flagged &= flagged - 1;
-          scan_group((g0 + gb) * 32);
-        }
       }
     }
   }

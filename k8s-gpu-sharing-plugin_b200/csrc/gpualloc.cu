@@ -112,8 +112,6 @@ struct gpa_ctx {
   uint16_t *d_ans = nullptr;         // answer table of the installed topology (ans_table.cuh), built by a kernel
   std::vector<uint16_t> h_ans;       // its host copy: gpa_besteffort() answers node-ordered requests from it
   uint16_t h_tern[256];              // ans_tern() of every 8-bit mask
-  uint8_t *d_defer = nullptr;        // arena of "a record of these 32 was left to the general kernel" bytes
-  size_t defer_head = 0;
   FastTopo fast{};
   // batch staging
   gpa_request *d_reqs = nullptr;
@@ -163,25 +161,8 @@ int ensure_batch_capacity(gpa_ctx *ctx, size_t count, bool host_staging) {
   return GPA_OK;
 }
 
-// Each batch call on the table path takes one byte per 32 records from this arena and keeps it until its two kernels
-// have run.  The arena is a ring: a call's bytes are reused only after kDeferArena bytes' worth of later calls, i.e.
-// calls that are in flight at the same time on different streams stay apart as long as they cover fewer than
-// 32 x kDeferArena = 2^28 records together.  A batch too large for the arena goes without (nullptr): the general
-// kernel then scans every result record for the deferral mark, as it does after the tile-binned kernel.
-constexpr size_t kDeferArena = (size_t)8 << 20;
-
-uint8_t *take_defer_flags(gpa_ctx *ctx, int count) {
-  if (!ctx->d_defer) return nullptr;
-  const size_t need = (((size_t)count + 31) / 32 + 255) & ~(size_t)255;
-  if (need > kDeferArena) return nullptr;
-  if (ctx->defer_head + need > kDeferArena) ctx->defer_head = 0;
-  uint8_t *p = ctx->d_defer + ctx->defer_head;
-  ctx->defer_head += need;
-  return p;
-}
-
 int launch_general(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_avail, int mode_flags, gpa_result *d_out,
-                   cudaStream_t stream, int deferred_only, const uint8_t *defer_flags = nullptr) {
+                   cudaStream_t stream, int deferred_only) {
   int n_cap = max_avail < 2 ? 2 : max_avail;
   if (n_cap > GPA_BATCH_MAX_AVAILABLE) n_cap = GPA_BATCH_MAX_AVAILABLE;
   size_t smem = (size_t)kBatchWarps * (((size_t)1 << n_cap) + kMaxDevices * kMaxDevices) * sizeof(uint16_t);
@@ -190,13 +171,13 @@ int launch_general(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_a
   int occ = 1;
   CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, besteffort_batch_kernel, kBatchWarps * 32, smem));
   if (occ < 1) occ = 1;
-  long long per_block = deferred_only ? (long long)kBatchWarps * 32 * (defer_flags ? 32 : 1) : kBatchWarps;
+  long long per_block = deferred_only ? (long long)kBatchWarps * 32 : kBatchWarps;
   long long want = ((long long)count + per_block - 1) / per_block;
   long long cap = (long long)ctx->sm_count * occ;  // persistent: one wave, warps stride over the requests
   int grid = (int)(want < cap ? want : cap);
   BatchTopo t{ctx->d_wq, ctx->d_asym, ctx->topo.n};
   besteffort_batch_kernel<<<grid, kBatchWarps * 32, smem, stream>>>(d_reqs, count, n_cap, mode_flags & GPA_MODE_INTENDED, t,
-                                                                    d_out, deferred_only, defer_flags);
+                                                                    d_out, deferred_only);
   ctx->launches++;
   CUDA_TRY(ctx, cudaGetLastError());
   return GPA_OK;
@@ -220,7 +201,7 @@ int launch_fast(gpa_ctx *ctx, const void *d_reqs, int count, int mode_flags, voi
 
 // Nodes of up to 8 GPUs: one lookup in the answer table per request (table_kernels.cuh).  The table holds the same
 // answers for both alias modes (no partition of such a node has the 7 sets the aliasing needs), so mode_flags is unused.
-int launch_table(gpa_ctx *ctx, const void *d_reqs, int count, void *d_out, cudaStream_t stream, bool masks, uint8_t *defer_flags) {
+int launch_table(gpa_ctx *ctx, const void *d_reqs, int count, int max_avail, int mode_flags, void *d_out, cudaStream_t stream, bool masks) {
   const size_t smem_max = masks ? masks_smem_bytes(ans_entries(kAnsMaxTopo)) : table_smem_bytes(ans_entries(kAnsMaxTopo));
   if (!ctx->table_attr_set[masks ? 1 : 0]) {
     if (masks)
@@ -245,8 +226,12 @@ int launch_table(gpa_ctx *ctx, const void *d_reqs, int count, void *d_out, cudaS
     // persistent: one CTA per SM (answer table + a ring of request tiles in its shared memory)
     long long want = ((long long)count + kTabTile - 1) / kTabTile;
     int grid = (int)(want < ctx->sm_count ? want : ctx->sm_count);
+    int n_cap = max_avail < 2 ? 2 : max_avail;  // as the general kernel sees it: a longer list is GPA_ERR_TOO_LARGE
+    if (n_cap > GPA_BATCH_MAX_AVAILABLE) n_cap = GPA_BATCH_MAX_AVAILABLE;
+    const BatchTopo t{ctx->d_wq, ctx->d_asym, ctx->topo.n};
     besteffort_batch_table_kernel<<<grid, kTabThreads, table_smem_bytes(ctx->fast.ans_entries), stream>>>(
-        static_cast<const gpa_request *>(d_reqs), count, ctx->fast, static_cast<gpa_result *>(d_out), defer_flags);
+        static_cast<const gpa_request *>(d_reqs), count, ctx->fast, static_cast<gpa_result *>(d_out), t, n_cap,
+        mode_flags & GPA_MODE_INTENDED);
   }
   ctx->launches++;
   CUDA_TRY(ctx, cudaGetLastError());
@@ -257,13 +242,13 @@ int launch_batch(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_ava
                  cudaStream_t stream) {
   if (count == 0) return GPA_OK;
   if (!ctx->d_sfull) return launch_general(ctx, d_reqs, count, max_avail, mode_flags, d_out, stream, 0);
-  // canonical-order fast path, then the general kernel mops up whatever was deferred
-  const bool table = ctx->fast.ans != nullptr && !(mode_flags & GPA_MODE_FORCE_ENUM);
-  uint8_t *flags = table ? take_defer_flags(ctx, count) : nullptr;
-  int rc = table ? launch_table(ctx, d_reqs, count, d_out, stream, false, flags)
-                 : launch_fast(ctx, d_reqs, count, mode_flags, d_out, stream, false);
+  // nodes of up to 8 GPUs: one launch - the table kernel also answers the records it cannot look up
+  if (ctx->fast.ans != nullptr && !(mode_flags & GPA_MODE_FORCE_ENUM))
+    return launch_table(ctx, d_reqs, count, max_avail, mode_flags, d_out, stream, false);
+  // 9-12 GPUs: tile-binned kernel for the records in node order, then the general kernel mops up whatever was deferred
+  int rc = launch_fast(ctx, d_reqs, count, mode_flags, d_out, stream, false);
   if (rc != GPA_OK) return rc;
-  return launch_general(ctx, d_reqs, count, max_avail, mode_flags, d_out, stream, 1, flags);
+  return launch_general(ctx, d_reqs, count, max_avail, mode_flags, d_out, stream, 1);
 }
 
 int launch_masks8(gpa_ctx *ctx, const void *d_reqs, int count, void *d_out, cudaStream_t stream) {
@@ -283,7 +268,7 @@ int launch_masks8(gpa_ctx *ctx, const void *d_reqs, int count, void *d_out, cuda
 }
 
 int launch_masks(gpa_ctx *ctx, const void *d_reqs, int count, int mode_flags, void *d_out, cudaStream_t stream) {
-  if (ctx->fast.ans != nullptr && !(mode_flags & GPA_MODE_FORCE_ENUM)) return launch_table(ctx, d_reqs, count, d_out, stream, true, nullptr);
+  if (ctx->fast.ans != nullptr && !(mode_flags & GPA_MODE_FORCE_ENUM)) return launch_table(ctx, d_reqs, count, 0, mode_flags, d_out, stream, true);
   return launch_fast(ctx, d_reqs, count, mode_flags, d_out, stream, true);
 }
 
@@ -376,7 +361,6 @@ int rebuild_fast(gpa_ctx *ctx) {
     ctx->h_ans.swap(h);
     f.ans = ctx->d_ans;
     f.ans_entries = n_ent;
-    if (!ctx->d_defer) CUDA_TRY(ctx, cudaMalloc(&ctx->d_defer, kDeferArena));
   }
   ctx->fast = f;
   return GPA_OK;
@@ -614,7 +598,6 @@ void gpa_destroy(gpa_ctx *ctx) {
   if (ctx->d_part_index) cudaFree(ctx->d_part_index);
   if (ctx->d_part_key) cudaFree(ctx->d_part_key);
   if (ctx->d_ans) cudaFree(ctx->d_ans);
-  if (ctx->d_defer) cudaFree(ctx->d_defer);
   if (ctx->d_sub_binom) cudaFree(ctx->d_sub_binom);
   if (ctx->d_sub_reqs) cudaFree(ctx->d_sub_reqs);
   if (ctx->d_sub_out) cudaFree(ctx->d_sub_out);
@@ -1331,7 +1314,7 @@ extern "C" int gpa_besteffort_batch_noalloc(int cuda_device, int n_topology, con
   int cap = d.sm_count * 4;
   int grid = blocks < cap ? blocks : cap;
   BatchTopo t{d_wq, d_asym, n};
-  besteffort_batch_kernel<<<grid, kBatchWarps * 32, smem, st>>>(d_reqs, count, n_cap, mode_flags & GPA_MODE_INTENDED, t, d_out, 0, nullptr);
+  besteffort_batch_kernel<<<grid, kBatchWarps * 32, smem, st>>>(d_reqs, count, n_cap, mode_flags & GPA_MODE_INTENDED, t, d_out, 0);
   NA_TRY(cudaGetLastError());
   NA_TRY(cudaMemcpyAsync(out, d_out, sizeof(gpa_result) * (size_t)count, cudaMemcpyDeviceToHost, st));
   NA_TRY(cudaStreamSynchronize(st));

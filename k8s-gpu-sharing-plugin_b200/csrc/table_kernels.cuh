@@ -104,18 +104,22 @@ __device__ __forceinline__ uint32_t or_of_bytes(uint32_t x) {
 __device__ __forceinline__ uint32_t bytes_of_bits(uint32_t b4) { return ((b4 * 0x00204081u) & 0x01010101u) * 0xFFu; }
 
 // 32-byte gpa_request in, 16-byte gpa_result out.  A record the table cannot answer (devices not in node order, unknown
-// device) is marked kResDefer for the general kernel, and its warp's byte in `defer_flags` (one per 32 records,
-// optional) is set so that the general kernel finds it without reading every result back.
+// device) is marked kResDefer while the tiles stream through; a CTA that marked any goes over those tiles once more when
+// it is done and answers them itself, one warp per record, through general_request() - with the request ring, idle by
+// then, as the warps' scratch.  A batch in node order (every batch the reference's call site can produce) never enters
+// that part, and the whole step is ONE launch.
 // reqs must be 16-byte aligned (bulk copies), out 16-byte aligned.
+constexpr int kTabFlagWords = 64;  // tiles of one CTA whose "has a marked record" bit is kept; later tiles share the last bit
 __global__ void __launch_bounds__(kTabThreads, 1) besteffort_batch_table_kernel(const gpa_request *__restrict__ reqs, int count,
                                                                                 const FastTopo ft, gpa_result *__restrict__ out,
-                                                                                uint8_t *__restrict__ defer_flags) {
+                                                                                const BatchTopo topo, int n_cap, int intended) {
   extern __shared__ __align__(128) unsigned char tsmem[];
   gpa_request *ring = reinterpret_cast<gpa_request *>(tsmem);
   unsigned long long *s_dev = reinterpret_cast<unsigned long long *>(ring + (size_t)kTabStages * kTabTile);
   uint16_t *s_tern = reinterpret_cast<uint16_t *>(s_dev + 256);
   uint16_t *s_ans = s_tern + 256;
   unsigned long long *full = reinterpret_cast<unsigned long long *>(reinterpret_cast<unsigned char *>(s_ans) + table_ans_bytes(ft.ans_entries));
+  __shared__ uint32_t s_marked[kTabFlagWords];
 
   const int tid = threadIdx.x;
   const int n_tiles = (int)(((long long)count + kTabTile - 1) / kTabTile);  // <= 2^21
@@ -128,6 +132,7 @@ __global__ void __launch_bounds__(kTabThreads, 1) besteffort_batch_table_kernel(
     mbar_expect_tx(&full[s], bytes);
     bulk_load(ring + (size_t)s * kTabTile, reqs + base, bytes, &full[s]);
   };
+  if (tid < kTabFlagWords) s_marked[tid] = 0;
   if (tid == 0) {
     for (int s = 0; s < kTabStages; s++) mbar_init(&full[s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -212,9 +217,37 @@ __global__ void __launch_bounds__(kTabThreads, 1) besteffort_batch_table_kernel(
       v.w = 0x80808080u;
       __stcs(reinterpret_cast<uint4 *>(out + r), v);
     }
-    if (defer_flags != nullptr) {
-      const unsigned any = __ballot_sync(0xffffffffu, defer);
-      if ((tid & 31) == 0 && r < count) defer_flags[r >> 5] = any ? 1 : 0;
+    if (__any_sync(0xffffffffu, defer) && (tid & 31) == 0) {
+      const int bit = i < kTabFlagWords * 32 ? i : kTabFlagWords * 32 - 1;
+      atomicOr(&s_marked[bit >> 5], 1u << (bit & 31));
+    }
+  }
+
+  // ---- the records this CTA marked (none for a batch in node order) ------------------------------------------------
+  __syncthreads();  // every lane's marks and results are visible to the CTA; the ring is idle
+  bool any_marked = false;
+  for (int w = 0; w < kTabFlagWords; w++) any_marked = any_marked || s_marked[w] != 0;
+  if (!any_marked) return;
+  // scratch in the ring: the binomial table, then per warp a 256-entry score table and the position weights
+  BinomTable *s_binom = reinterpret_cast<BinomTable *>(ring);
+  uint16_t *scratch = reinterpret_cast<uint16_t *>(reinterpret_cast<unsigned char *>(ring) + ((sizeof(BinomTable) + 127) & ~(size_t)127));
+  stage_binom(*s_binom, tid, kTabThreads);
+  __syncthreads();
+  const int lane = tid & 31, warp = tid >> 5;
+  uint16_t *S = scratch + (size_t)warp * (256 + kMaxDevices * kMaxDevices);
+  uint16_t *wp = S + 256;
+  for (int i = 0; i < my_tiles; i++) {
+    const int bit = i < kTabFlagWords * 32 ? i : kTabFlagWords * 32 - 1;
+    if (!(s_marked[bit >> 5] >> (bit & 31) & 1u)) continue;
+    const long long base = ((long long)blockIdx.x + (long long)i * gridDim.x) * kTabTile + warp * 32;
+    const long long r = base + lane;
+    const bool marked = r < count && out[r].dev[0] == kResDefer;
+    unsigned todo = __ballot_sync(0xffffffffu, marked);
+    while (todo) {
+      const int b = __ffs(todo) - 1;
+      todo &= todo - 1;
+      general_request(reqs, base + b, n_cap, 8, intended, topo, out, S, wp, *s_binom, lane);
+      __syncwarp();
     }
   }
 }

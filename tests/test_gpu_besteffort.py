@@ -521,6 +521,8 @@ def test_launch_counter_counts_kernels(ctx):
     before = ctx.launch_count
     ctx.besteffort(list(range(8)), [], 4, gpa.MODE_FORCE_KERNEL)
     ctx.besteffort(list(range(8)), [], 4)  # answered from the host copy of the answer table: no kernel
-    ctx.besteffort_batch(syn.random_request_batch(8, 100, seed=1))  # table kernel + the general kernel's deferred pass
+    ctx.besteffort_batch(syn.random_request_batch(8, 100, seed=1))  # one launch: the table kernel also answers what it cannot look up
     ctx.besteffort(list(range(8)), [], 1)  # answered by the guards: no kernel
-    assert ctx.launch_count == before + 3
+    assert ctx.launch_count == before + 2
+    ctx.besteffort_batch(syn.random_request_batch(8, 100, seed=1), gpa.MODE_FORCE_ENUM)  # tile-binned kernel + deferred pass
+    assert ctx.launch_count == before + 4
