@@ -104,6 +104,43 @@ __global__ void __launch_bounds__(kDpThreads) dp_layer_warp_kernel(const DpParam
   }
 }
 
+// layer j, HALF A WARP per remainder, one lane per lowest pick: lane l takes the first sets whose lowest pick besides the
+// anchor is the l-th candidate of R (dp_value_share), lane 15 the set made of the anchor and the pads alone, and each
+// lane steps through its share with the register-only stepper - nothing is unranked.  For layers whose remainders have
+// ~100-1000 first sets (large k): n = 16, k = 5 has 4 384 remainders of 1 001 first sets in its third layer.
+__global__ void __launch_bounds__(kDpThreads) dp_layer_share_kernel(const DpParams p, int j, uint16_t *T, uint16_t *Tok) {
+  const uint32_t total = 1u << p.g.n;
+  const TabAny tany{T};
+  const TabOk tok{Tok, p.rbit};
+  const int lane = threadIdx.x & 15;
+  const unsigned hmask = 0xFFFFu << (threadIdx.x & 16);  // the two halves of a warp work on different remainders
+  const uint32_t halves = gridDim.x * (kDpThreads / 16);
+  for (uint32_t R = blockIdx.x * (kDpThreads / 16) + (threadIdx.x >> 4); R < total; R += halves) {
+    if (dp_layer_of(p.g, R) != j) continue;  // uniform over the half warp
+    // this lane's pick: the lane-th candidate (R without its lowest bit, the anchor), or the token for lane 15
+    uint32_t cand = R & (R - 1u);
+    uint32_t pick = 0;
+    if (lane == 15) {
+      pick = p.g.tok_bit;
+    } else {
+      for (int q = 0; q < lane && cand; q++) cand &= cand - 1u;
+      pick = cand & (0u - cand);
+    }
+    const bool has_req = p.g.rmask != 0 && (R & p.g.rmask) == p.g.rmask;
+    int va = dp_value_share(p.g, tany, tok, R, false, pick);
+    int vo = has_req ? dp_value_share(p.g, tany, tok, R, true, pick) : -1;
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) {  // max over the 16 lanes of this half
+      va = max(va, __shfl_xor_sync(hmask, va, o));
+      vo = max(vo, __shfl_xor_sync(hmask, vo, o));
+    }
+    if (lane == 0) {
+      T[R] = (uint16_t)(va < 0 ? kDpInvalid : (uint32_t)va);
+      if (has_req) Tok[dp_ok_index(R, p.rbit)] = (uint16_t)(vo < 0 ? kDpInvalid : (uint32_t)vo);
+    }
+  }
+}
+
 // top layer + reconstruction in one CTA: level by level, all threads value the first sets of the current remainder,
 // the block-wide max key names the first best one, and the remainder shrinks by it.  No serial replay.
 __device__ __forceinline__ void dp_final_stage(const DpParams &p, const uint16_t *T, const uint16_t *Tok, SearchResult *g_res) {

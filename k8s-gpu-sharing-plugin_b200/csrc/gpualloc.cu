@@ -896,9 +896,10 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
         // A thread per remainder walks its first sets one after the other; a warp per remainder spreads them over its
         // lanes by literal rank.  Measured: the warp form wins once a remainder has ~100 first sets.
         if (binom_at(ctx->binom, j * dp.g.k - 1, dp.g.k - 1) >= 96u) {
-          int wgrid = (int)((total + kDpThreads / 32 - 1) / (kDpThreads / 32));
+          // half a warp per remainder, a lane per lowest pick (at most 15 candidates + the pads: n <= 16)
+          int wgrid = (int)((total + kDpThreads / 16 - 1) / (kDpThreads / 16));
           if (wgrid > ctx->sm_count * 8) wgrid = ctx->sm_count * 8;
-          dp_layer_warp_kernel<<<wgrid, kDpThreads, 0, ctx->stream>>>(dp, j, ctx->d_dp_any, ctx->d_dp_ok);
+          dp_layer_share_kernel<<<wgrid, kDpThreads, 0, ctx->stream>>>(dp, j, ctx->d_dp_any, ctx->d_dp_ok);
         } else {
           dp_layer_kernel<<<grid, kDpThreads, 0, ctx->stream>>>(dp, j, ctx->d_dp_any, ctx->d_dp_ok);
         }
