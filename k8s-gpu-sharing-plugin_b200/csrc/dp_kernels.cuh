@@ -79,19 +79,38 @@ __device__ __forceinline__ unsigned long long dp_level_key(const Geom &g, const 
   return best;
 }
 
+// the idx-th mask with s of the n lowest bits set (colex order; any bijection onto the C(n, s) masks would do)
+__device__ __forceinline__ uint32_t nth_mask(const BinomTable &B, int n, int s, uint32_t idx) {
+  uint32_t m = 0;
+  for (int pos = n - 1; pos >= 0 && s > 0; pos--) {
+    const uint32_t c = binom_at(B, pos, s);  // masks of s bits below pos
+    if (idx >= c) {
+      m |= 1u << pos;
+      idx -= c;
+      s--;
+    }
+  }
+  return m;
+}
+
 // layer j, ONE WARP per remainder: for layers whose remainders have many first sets (large k) a single thread
-// walking them one after the other would be the tail of the whole search
+// walking them one after the other would be the tail of the whole search.  The remainders of a layer are the masks of
+// j*k devices and, with pads, of j*k - P devices; they are NUMBERED (nth_mask) so that every warp gets its share of them -
+// striding over all 2^n masks instead left most warps without a remainder and a few with several (n = 16, k = 5: the
+// third layer has 4 384 remainders among 65 536 masks and took 224 us; numbered, they fit one round of the grid).
 __global__ void __launch_bounds__(kDpThreads) dp_layer_warp_kernel(const DpParams p, int j, uint16_t *T, uint16_t *Tok) {
   __shared__ BinomTable s_binom;
   stage_binom(s_binom, threadIdx.x, kDpThreads);
   __syncthreads();
-  const uint32_t total = 1u << p.g.n;
   const TabAny tany{T};
   const TabOk tok{Tok, p.rbit};
   const int lane = threadIdx.x & 31;
   const uint32_t warps = gridDim.x * (kDpThreads / 32);
-  for (uint32_t R = blockIdx.x * (kDpThreads / 32) + (threadIdx.x >> 5); R < total; R += warps) {
-    if (dp_layer_of(p.g, R) != j) continue;
+  const int s1 = j * p.g.k, s2 = p.g.P ? j * p.g.k - p.g.P : 0;
+  const uint32_t c1 = s1 <= p.g.n ? binom_at(s_binom, p.g.n, s1) : 0u;
+  const uint32_t c2 = (s2 >= 1 && s2 <= p.g.n) ? binom_at(s_binom, p.g.n, s2) : 0u;
+  for (uint32_t idx = blockIdx.x * (kDpThreads / 32) + (threadIdx.x >> 5); idx < c1 + c2; idx += warps) {
+    const uint32_t R = idx < c1 ? nth_mask(s_binom, p.g.n, s1, idx) : nth_mask(s_binom, p.g.n, s2, idx - c1);
     Cut cut;
     unsigned long long ka = warp_max_u64(dp_level_key(p.g, s_binom, R, false, tany, tok, lane, 32, cut));
     unsigned long long ko = 0;
@@ -100,43 +119,6 @@ __global__ void __launch_bounds__(kDpThreads) dp_layer_warp_kernel(const DpParam
     if (lane == 0) {
       T[R] = (uint16_t)(ka ? (uint32_t)key_score(ka) : kDpInvalid);
       if (has_req) Tok[dp_ok_index(R, p.rbit)] = (uint16_t)(ko ? (uint32_t)key_score(ko) : kDpInvalid);
-    }
-  }
-}
-
-// layer j, HALF A WARP per remainder, one lane per lowest pick: lane l takes the first sets whose lowest pick besides the
-// anchor is the l-th candidate of R (dp_value_share), lane 15 the set made of the anchor and the pads alone, and each
-// lane steps through its share with the register-only stepper - nothing is unranked.  For layers whose remainders have
-// ~100-1000 first sets (large k): n = 16, k = 5 has 4 384 remainders of 1 001 first sets in its third layer.
-__global__ void __launch_bounds__(kDpThreads) dp_layer_share_kernel(const DpParams p, int j, uint16_t *T, uint16_t *Tok) {
-  const uint32_t total = 1u << p.g.n;
-  const TabAny tany{T};
-  const TabOk tok{Tok, p.rbit};
-  const int lane = threadIdx.x & 15;
-  const unsigned hmask = 0xFFFFu << (threadIdx.x & 16);  // the two halves of a warp work on different remainders
-  const uint32_t halves = gridDim.x * (kDpThreads / 16);
-  for (uint32_t R = blockIdx.x * (kDpThreads / 16) + (threadIdx.x >> 4); R < total; R += halves) {
-    if (dp_layer_of(p.g, R) != j) continue;  // uniform over the half warp
-    // this lane's pick: the lane-th candidate (R without its lowest bit, the anchor), or the token for lane 15
-    uint32_t cand = R & (R - 1u);
-    uint32_t pick = 0;
-    if (lane == 15) {
-      pick = p.g.tok_bit;
-    } else {
-      for (int q = 0; q < lane && cand; q++) cand &= cand - 1u;
-      pick = cand & (0u - cand);
-    }
-    const bool has_req = p.g.rmask != 0 && (R & p.g.rmask) == p.g.rmask;
-    int va = dp_value_share(p.g, tany, tok, R, false, pick);
-    int vo = has_req ? dp_value_share(p.g, tany, tok, R, true, pick) : -1;
-#pragma unroll
-    for (int o = 8; o > 0; o >>= 1) {  // max over the 16 lanes of this half
-      va = max(va, __shfl_xor_sync(hmask, va, o));
-      vo = max(vo, __shfl_xor_sync(hmask, vo, o));
-    }
-    if (lane == 0) {
-      T[R] = (uint16_t)(va < 0 ? kDpInvalid : (uint32_t)va);
-      if (has_req) Tok[dp_ok_index(R, p.rbit)] = (uint16_t)(vo < 0 ? kDpInvalid : (uint32_t)vo);
     }
   }
 }

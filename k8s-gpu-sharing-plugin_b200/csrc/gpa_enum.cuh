@@ -578,39 +578,6 @@ GPA_HD uint32_t dp_value(const Geom &g, const TAny &Tany, const TOk &Tok, uint32
   return best < 0 ? kDpInvalid : (uint32_t)best;
 }
 
-// The share of dp_value() that belongs to the first sets whose LOWEST pick besides the anchor is `pick` (one bit of
-// R's candidates), or - pick == g.tok_bit - to the set made of the anchor and the pads alone.  The shares of all picks
-// partition the first sets of R, so the maximum over them is dp_value(): this is how a layer with ~1000 first sets per
-// remainder is spread over lanes without unranking anything.  -1 = no acceptable set in this share.
-template <typename TAny, typename TOk>
-GPA_HD int dp_value_share(const Geom &g, const TAny &Tany, const TOk &Tok, uint32_t R, bool want_ok, uint32_t pick) {
-  const bool last_pair = dp_layer_of(g, R) == 2;
-  const bool has_tok = g.P != 0 && (popc32(R) % g.k) != 0;
-  const uint32_t rem = R | (has_tok ? g.tok_bit : 0u);
-  uint32_t anchor;
-  const Stepper st = make_stepper(g, rem, anchor);
-  if (pick == 0) return -1;
-  if (pick == g.tok_bit) {  // the token directly after the anchor: a set of k - P = 1 real device
-    if (st.tok == 0 || st.tp != 0) return -1;
-    return dp_set_value(g, Tany, Tok, R, anchor | st.tok, want_ok, last_pair);
-  }
-  if (!(st.cand & pick)) return -1;
-  Stepper s2;
-  s2.cand = st.cand & ~((pick << 1) - 1u);  // the other picks lie above
-  s2.tok = st.tp >= 1 ? st.tok : 0u;  // the pads follow exactly tp real picks; with tp == 0 a set that starts with a real pick has none
-  s2.t = st.t - 1;
-  s2.tp = st.tp - 1;
-  uint32_t chosen;
-  int best = -1;
-  if (!s2.first(chosen)) return -1;
-  do {
-    const int v = dp_set_value(g, Tany, Tok, R, anchor | pick | chosen, want_ok, last_pair);
-    best = v > best ? v : best;
-  } while (s2.next(chosen));
-  return best;
-}
-
-
 // Rebuilds the first best partition from filled tables, starting below `level0` sets already fixed in sets[]
 // (R = what is left, need_ok = no fixed set holds the required devices yet).  Returns false if none is acceptable.
 template <typename TAny, typename TOk>

@@ -896,10 +896,14 @@ int gpa_besteffort(gpa_ctx *ctx, const int32_t *avail, int n_avail, const int32_
         // A thread per remainder walks its first sets one after the other; a warp per remainder spreads them over its
         // lanes by literal rank.  Measured: the warp form wins once a remainder has ~100 first sets.
         if (binom_at(ctx->binom, j * dp.g.k - 1, dp.g.k - 1) >= 96u) {
-          // half a warp per remainder, a lane per lowest pick (at most 15 candidates + the pads: n <= 16)
-          int wgrid = (int)((total + kDpThreads / 16 - 1) / (kDpThreads / 16));
+          // one warp per remainder of the layer (numbered: masks of j*k and of j*k - P devices)
+          const int s1 = j * dp.g.k, s2 = dp.g.P ? j * dp.g.k - dp.g.P : 0;
+          const uint64_t rems = (s1 <= n_avail ? binom_at(ctx->binom, n_avail, s1) : 0u) +
+                                ((s2 >= 1 && s2 <= n_avail) ? binom_at(ctx->binom, n_avail, s2) : 0u);
+          int wgrid = (int)((rems + kDpThreads / 32 - 1) / (kDpThreads / 32));
           if (wgrid > ctx->sm_count * 8) wgrid = ctx->sm_count * 8;
-          dp_layer_share_kernel<<<wgrid, kDpThreads, 0, ctx->stream>>>(dp, j, ctx->d_dp_any, ctx->d_dp_ok);
+          if (wgrid < 1) wgrid = 1;
+          dp_layer_warp_kernel<<<wgrid, kDpThreads, 0, ctx->stream>>>(dp, j, ctx->d_dp_any, ctx->d_dp_ok);
         } else {
           dp_layer_kernel<<<grid, kDpThreads, 0, ctx->stream>>>(dp, j, ctx->d_dp_any, ctx->d_dp_ok);
         }

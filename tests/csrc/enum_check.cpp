@@ -172,22 +172,6 @@ extern "C" int enum_check_dp(int nt, const int32_t *W, const int32_t *avail, int
       // both tables of layer j are computed from layer j-1 before either is stored
       uint32_t va = dp_value(g, Tany, TokF, mask, false);
       uint32_t vo = (rmask && (mask & rmask) == rmask) ? dp_value(g, Tany, TokF, mask, true) : kDpInvalid;
-      // the same value as the maximum over the per-pick shares (what dp_layer_share_kernel's lanes compute): the picks
-      // are the candidates of the remainder - everything but its lowest device - and the token
-      for (int want_ok = 0; want_ok < 2; want_ok++) {
-        if (want_ok && !(rmask && (mask & rmask) == rmask)) continue;
-        int best = -1;
-        for (uint32_t c = mask & (mask - 1u); c; c &= c - 1u) {
-          const int v = dp_value_share(g, Tany, TokF, mask, want_ok != 0, c & (0u - c));
-          best = v > best ? v : best;
-        }
-        if (g.tok_bit) {
-          const int v = dp_value_share(g, Tany, TokF, mask, want_ok != 0, g.tok_bit);
-          best = v > best ? v : best;
-        }
-        const uint32_t whole = want_ok ? vo : va;
-        if ((best < 0 ? kDpInvalid : (uint32_t)best) != whole) return -2;
-      }
       T[mask] = (uint16_t)va;
       if (rmask && (mask & rmask) == rmask) Tok[dp_ok_index(mask, rbit)] = (uint16_t)vo;
     }
