@@ -199,6 +199,7 @@ struct FastTopo {
   const uint32_t *part_index;  // [256 * 9]: offset | count << 16 of the group of (mask, size)
   const uint32_t *part_key;    // per partition word: its score under the installed weights << 16 | (0xFFFF - index in its group)
   const uint16_t *ans;         // answer table (ans_table.cuh), padded to 16 bytes; nullptr: none (more than 8 GPUs)
+  const uint8_t *ans8;         // its chosen masks alone, one byte per entry, padded to 16 bytes
   uint32_t ans_entries;
   int nt;
   uint8_t order[16];  // label -> NVML index

@@ -18,34 +18,38 @@
 
 namespace {
 
-constexpr int kTabThreads = 1024;
-constexpr int kTabTile = kTabThreads;  // records per tile: one per thread
-constexpr int kTabStages = 3;          // request tiles in flight per SM (3 x 32 KB)
+// The record kernel is a template over (threads per CTA = records per tile, stages of the request ring); which
+// instantiation runs is chosen on the host (launch_table).
 
-__global__ void __launch_bounds__(256) answer_table_build_kernel(const FastTopo ft, uint16_t *__restrict__ table, uint32_t n_entries,
-                                                                 int intended) {
+// table: the 2-byte entries of ans_table.cuh (what gpa_get_answer_table() hands out); table8: the chosen masks alone, for
+// the batch kernels' shared memory - the nil pads of an answer follow from it: a non-empty answer of `size` entries that
+// names fewer devices is padded with size - popc(chosen) nils.
+__global__ void __launch_bounds__(256) answer_table_build_kernel(const FastTopo ft, uint16_t *__restrict__ table,
+                                                                 uint8_t *__restrict__ table8, uint32_t n_entries, int intended) {
   const GlobalScores S{ft.s_full};
   for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n_entries; e += gridDim.x * blockDim.x) {
     uint32_t mask, rl;
     ans_decode(e / (uint32_t)kAnsSizes, mask, rl);
     const int size = (int)(e % (uint32_t)kAnsSizes) + 1;
-    table[e] = ans_compute_entry(ft.nt, mask, rl, size, ft.part_words, ft.part_index, ft.part_key, S, intended != 0);
+    const uint16_t a = ans_compute_entry(ft.nt, mask, rl, size, ft.part_words, ft.part_index, ft.part_key, S, intended != 0);
+    table[e] = a;
+    table8[e] = (uint8_t)ans_chosen(a);
   }
 }
 
-// ---- shared-memory layout common to both batch kernels ---------------------------------------------------------
-__host__ __device__ constexpr size_t table_ans_bytes(uint32_t n_entries) { return ((size_t)n_entries * sizeof(uint16_t) + 15) & ~(size_t)15; }
+// ---- shared-memory layout common to the batch kernels ---------------------------------------------------------
+__host__ __device__ constexpr size_t table_ans_bytes(uint32_t n_entries) { return ((size_t)n_entries + 15) & ~(size_t)15; }  // one byte each
 constexpr size_t kTabSmallTables = 256 * sizeof(unsigned long long) + 256 * sizeof(uint16_t);  // s_dev + tern
 constexpr size_t masks_smem_bytes(uint32_t n_entries) { return kTabSmallTables + table_ans_bytes(n_entries); }
-constexpr size_t table_smem_bytes(uint32_t n_entries) {
-  return (size_t)kTabStages * kTabTile * sizeof(gpa_request)  // request ring (first: 128-byte aligned)
-         + kTabSmallTables + table_ans_bytes(n_entries) + kTabStages * sizeof(unsigned long long);  // + the stages' mbarriers
+constexpr size_t table_smem_bytes(uint32_t n_entries, int threads, int stages) {
+  return (size_t)stages * threads * sizeof(gpa_request)  // request ring (first: 128-byte aligned)
+         + kTabSmallTables + table_ans_bytes(n_entries) + (size_t)stages * sizeof(unsigned long long);  // + the stages' mbarriers
 }
 
-__device__ __forceinline__ void stage_tables(const FastTopo &ft, unsigned long long *s_dev, uint16_t *s_tern, uint16_t *s_ans, int tid,
+__device__ __forceinline__ void stage_tables(const FastTopo &ft, unsigned long long *s_dev, uint16_t *s_tern, uint8_t *s_ans, int tid,
                                              int nthreads) {
   // answers: 16 bytes per thread per step (the table is padded to a multiple of 16 bytes on the device)
-  const uint4 *src = reinterpret_cast<const uint4 *>(ft.ans);
+  const uint4 *src = reinterpret_cast<const uint4 *>(ft.ans8);
   uint4 *dst = reinterpret_cast<uint4 *>(s_ans);
   const uint32_t n16 = (uint32_t)(table_ans_bytes(ft.ans_entries) / 16);
   for (uint32_t i = tid; i < n16; i += nthreads) dst[i] = __ldg(src + i);
@@ -110,15 +114,17 @@ __device__ __forceinline__ uint32_t bytes_of_bits(uint32_t b4) { return ((b4 * 0
 // that part, and the whole step is ONE launch.
 // reqs must be 16-byte aligned (bulk copies), out 16-byte aligned.
 constexpr int kTabFlagWords = 64;  // tiles of one CTA whose "has a marked record" bit is kept; later tiles share the last bit
-__global__ void __launch_bounds__(kTabThreads, 1) besteffort_batch_table_kernel(const gpa_request *__restrict__ reqs, int count,
+template <int kTabThreads, int kTabStages>
+__global__ void __launch_bounds__(kTabThreads, kTabThreads >= 1024 ? 1 : 2) besteffort_batch_table_kernel(const gpa_request *__restrict__ reqs, int count,
                                                                                 const FastTopo ft, gpa_result *__restrict__ out,
                                                                                 const BatchTopo topo, int n_cap, int intended) {
+  constexpr int kTabTile = kTabThreads;  // records per tile: one per thread
   extern __shared__ __align__(128) unsigned char tsmem[];
   gpa_request *ring = reinterpret_cast<gpa_request *>(tsmem);
   unsigned long long *s_dev = reinterpret_cast<unsigned long long *>(ring + (size_t)kTabStages * kTabTile);
   uint16_t *s_tern = reinterpret_cast<uint16_t *>(s_dev + 256);
-  uint16_t *s_ans = s_tern + 256;
-  unsigned long long *full = reinterpret_cast<unsigned long long *>(reinterpret_cast<unsigned char *>(s_ans) + table_ans_bytes(ft.ans_entries));
+  uint8_t *s_ans = reinterpret_cast<uint8_t *>(s_tern + 256);
+  unsigned long long *full = reinterpret_cast<unsigned long long *>(s_ans + table_ans_bytes(ft.ans_entries));
   __shared__ uint32_t s_marked[kTabFlagWords];
 
   const int tid = threadIdx.x;
@@ -202,9 +208,8 @@ __global__ void __launch_bounds__(kTabThreads, 1) besteffort_batch_table_kernel(
           defer = true;
           r0 ^= (unsigned long long)((kResDefer ^ 0x80) & 0xFF);
         } else if (!(flags & GPA_REQ_FOREIGN)) {  // a required pointer that is in no set: every candidate is rejected (:53)
-          const uint32_t e = s_ans[ans_index(s_tern, mask, rl, size)];
-          const uint32_t chosen = e & 0xFFu;
-          const int n_nil = (int)(e >> 8);
+          const uint32_t chosen = s_ans[ans_index(s_tern, mask, rl, size)];
+          const int n_nil = chosen ? size - __popc(chosen) : 0;  // a set of fewer than `size` devices is the padded one
           r0 = s_dev[chosen];
           // nil pads follow the devices (D5): GPA_RES_END (0x80) -> GPA_NIL (0xFF) in n_nil bytes
           if (n_nil) r0 ^= (0x7F7F7F7F7F7F7F7Full >> (8 * (8 - n_nil))) << (8 * __popc(chosen));
@@ -259,7 +264,7 @@ __global__ void __launch_bounds__(kMaskThreads) besteffort_masks_table_kernel(co
   extern __shared__ __align__(128) unsigned char tsmem[];
   unsigned long long *s_dev = reinterpret_cast<unsigned long long *>(tsmem);
   uint16_t *s_tern = reinterpret_cast<uint16_t *>(s_dev + 256);
-  uint16_t *s_ans = s_tern + 256;
+  uint8_t *s_ans = reinterpret_cast<uint8_t *>(s_tern + 256);
   const int tid = threadIdx.x;
   stage_tables(ft, s_dev, s_tern, s_ans, tid, kMaskThreads);
   __syncthreads();
@@ -274,8 +279,8 @@ __global__ void __launch_bounds__(kMaskThreads) besteffort_masks_table_kernel(co
     if (((mask | rl) & ~node_mask) != 0) return (uint32_t)(GPA_ERR_INVALID & 0xFF) << 24;
     // guards of besteffort_policy.go:35-45; a required device that is not available is in no set (:53)
     if (size <= 0 || n < size || n_req > size || (flags & GPA_REQ_FOREIGN) || (rl & ~mask) != 0) return 0u;
-    const uint32_t e = s_ans[ans_index(s_tern, mask, rl, size)];
-    return (e & 0xFFu) | ((e >> 8) << 16);
+    const uint32_t chosen = s_ans[ans_index(s_tern, mask, rl, size)];
+    return chosen | ((chosen ? (uint32_t)(size - __popc(chosen)) : 0u) << 16);
   };
   if (((reinterpret_cast<uintptr_t>(mreqs) & 15u) | (reinterpret_cast<uintptr_t>(mout) & 7u)) == 0) {
     // two records per lane per step: 16 bytes in, 8 bytes out
@@ -306,7 +311,7 @@ __global__ void __launch_bounds__(kMaskThreads) besteffort_masks8_table_kernel(c
   extern __shared__ __align__(128) unsigned char tsmem[];
   unsigned long long *s_dev = reinterpret_cast<unsigned long long *>(tsmem);
   uint16_t *s_tern = reinterpret_cast<uint16_t *>(s_dev + 256);
-  uint16_t *s_ans = s_tern + 256;
+  uint8_t *s_ans = reinterpret_cast<uint8_t *>(s_tern + 256);
   const int tid = threadIdx.x;
   stage_tables(ft, s_dev, s_tern, s_ans, tid, kMaskThreads);
   __syncthreads();
@@ -319,7 +324,8 @@ __global__ void __launch_bounds__(kMaskThreads) besteffort_masks8_table_kernel(c
     if (((mask | rl) & ~node_mask) != 0) return 0x8000u;
     // guards of besteffort_policy.go:35-45; a required device that is not available is in no set (:53)
     if (size <= 0 || __popc(mask) < size || __popc(rl) > size || ((x >> 24) & GPA_REQ_FOREIGN) || (rl & ~mask) != 0) return 0u;
-    return s_ans[ans_index(s_tern, mask, rl, size)];  // the table entry IS the result record
+    const uint32_t chosen = s_ans[ans_index(s_tern, mask, rl, size)];
+    return chosen | ((chosen ? (uint32_t)(size - __popc(chosen)) : 0u) << 8);  // the 2-byte entry of ans_table.cuh
   };
   if (((reinterpret_cast<uintptr_t>(reqs) & 15u) | (reinterpret_cast<uintptr_t>(out) & 7u)) == 0) {
     const long long n_quads = (long long)count >> 2;
