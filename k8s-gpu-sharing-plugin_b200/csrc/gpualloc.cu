@@ -685,8 +685,10 @@ int gpa_set_topology(gpa_ctx *ctx, int n, const int32_t *W, const uint8_t *nlink
   std::lock_guard<std::mutex> lk(ctx->mu);
   if ((int)ctx->topo.order.size() == n) t.order = ctx->topo.order;  // a device order set earlier survives a re-install
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-  // Requests are serialised on ctx->mu and each one finishes before it returns, so no
-  // kernel can still be reading the old tables here.
+  // Host-buffer requests are serialised on ctx->mu and finish before they return; the *_device entry points only
+  // enqueue on the caller's stream, so a kernel of theirs may still be reading the tables that are replaced below:
+  // wait for the device before anything is freed (installing a topology is rare and rebuilds tables anyway).
+  CUDA_TRY(ctx, cudaDeviceSynchronize());
   uint16_t *d_wq = nullptr;
   uint8_t *d_asym = nullptr;
   CUDA_TRY(ctx, cudaMalloc(&d_wq, t.wq.size() * sizeof(uint16_t)));
@@ -713,6 +715,7 @@ int gpa_set_device_order(gpa_ctx *ctx, const int32_t *order, int n) {
     seen |= 1ull << order[i];
   }
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  CUDA_TRY(ctx, cudaDeviceSynchronize());  // a batch enqueued through a *_device entry point may still read the old tables
   ctx->topo.order.assign(order, order + n);
   return rebuild_fast(ctx);
 }
