@@ -562,9 +562,10 @@ def run_ours(args):
                                        "the reference's sequence; 265 calls, 100 ms once at start-up here")
     # replicas > 1: the reference answers with prioritizeDevices (server.go:285-296): host C++ here as well
     replica_mode = {"get_preferred_allocation": run_tool("replica_bench"),
-                    "config2_stream": {"%d_virtual_devices" % (N_DEV * r): run_tool("stream", r, 100000) for r in (4, 16, 32)},
-                    "note": "prioritizeDevices / the GetPreferredAllocation -> Allocate stream at 32 / 128 / 256 virtual devices, "
-                            "one host thread, native on both sides of the comparison; no parallel work on this branch"}
+                    "config2_stream": {"%d_virtual_devices" % (N_DEV * r): run_tool("stream", r, 100000) for r in (1, 4, 16, 32)},
+                    "note": "the GetPreferredAllocation -> Allocate stream through the handler bodies at 8 virtual devices (replicas = 1: "
+                            "best-effort policy, answered from the GPU-built table) and at 32 / 128 / 256 (replicas > 1: "
+                            "prioritizeDevices, no parallel work on that branch); one host thread, native on both sides"}
 
     # ---- replica-set search (north_star's "k-subsets of the available replica set"; no reference counterpart - the
     #      reference answers replicas with prioritizeDevices above): one request at 32 / 128 / 256 virtual devices, half of

@@ -162,3 +162,18 @@ def test_replica_requests_by_topology_option():
         plug.close()
         plain.close()
         ctx.close()
+
+
+def test_config2_stream_through_the_best_effort_branch():
+    """tools/stream.cpp with replicas = 1 (8 virtual devices): the stateful GetPreferredAllocation -> Allocate / free stream
+    through the handler bodies on the best-effort branch, every answer compared with ref_besteffort_fast; the decisions
+    come from the host copy of the GPU-built answer table, so the stream itself launches nothing."""
+    import json
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    subprocess.check_call(["make", "-C", os.path.join(root, "tools"), "-s", "bin/stream"])
+    out = subprocess.run([os.path.join(root, "tools", "bin", "stream"), "1", "20000"], capture_output=True, text=True, timeout=300)
+    r = json.loads(out.stdout)
+    assert out.returncode == 0 and r["mismatches_vs_oracle"] == 0 and r["virtual_devices"] == 8, r
+    assert r["decisions"] > 5000 and r["allocations"] > 1000 and r["kernel_launches_during_the_stream"] == 0

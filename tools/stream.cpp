@@ -6,6 +6,11 @@
 // decisions/s, call latency percentiles of GetPreferredAllocation and Allocate, mismatches.
 //   g++ -O2 -std=c++17 tools/stream.cpp -o /tmp/stream -I include -L k8s-gpu-sharing-plugin_b200 -lgpualloc -L oracle -loracle
 //   /tmp/stream [replicas] [steps]
+// replicas = 1 (8 virtual devices) takes the OTHER branch of the handler (server.go:297-301): the best-effort policy on the
+// GPU context - answered from the host copy of the answer table the GPU built - compared with ref_besteffort_fast.  That
+// branch only closes its loop with two of the reference's defects switched off (GPA_FIX_REPLICA_SUFFIX: the answer carries the
+// "-replica-0" suffix Allocate knows; GPA_FIX_REQUIRED_IDENTITY: a must-include device is honoured, D4), so
+// the stream runs with those two fixes and says so.  Needs a CUDA device.
 #include <algorithm>
 #include <chrono>
 #include <cstdio>
@@ -17,6 +22,8 @@
 
 #include "gpualloc.h"
 
+extern "C" int ref_besteffort_fast(int nt, const int32_t *W, const uint8_t *nlinks, const int32_t *avail, int n_avail, const int32_t *req,
+                                   int n_req, int size, int mode, int32_t *out, int *n_out, unsigned long long *visited);
 extern "C" int ref_prioritize_devices(const char *const *availableDeviceIDs, int n_avail, const char *const *mustIncludeDeviceIDs,
                                       int n_must, int allocationSize, char *outbuf, int outbuf_len, int *n_out, char *errbuf,
                                       int errbuf_len);
@@ -55,10 +62,64 @@ int main(int argc, char **argv) {
     index[i] = std::to_string(i);
     devs[i] = {uuids[i].c_str(), index[i].c_str(), &path_ptrs[i], 1, 183359ull, i / 4, i};
   }
+  const bool best_effort = replicas == 1;
+  gpa_ctx *ctx = nullptr;
+  int32_t W[64];
+  uint8_t nl[64];
+  if (best_effort) {
+    // synthetic hybrid cube mesh (synthetic.topo_dgx1v_like): PCIe + NVLink weights, as tools/latency.cpp
+    auto pcie = [](int i, int j) {
+      if ((i ^ j) == 1 && (i / 2) == (j / 2)) return 50;
+      return (i < 4) == (j < 4) ? 20 : 10;
+    };
+    const int two[8][2] = {{0, 3}, {0, 4}, {1, 2}, {1, 5}, {2, 3}, {4, 7}, {5, 6}, {6, 7}};
+    const int one[8][2] = {{0, 1}, {0, 2}, {1, 3}, {2, 6}, {3, 7}, {4, 5}, {4, 6}, {5, 7}};
+    for (int i = 0; i < n; i++)
+      for (int j = 0; j < n; j++) {
+        W[i * n + j] = i == j ? 0 : pcie(i, j);
+        nl[i * n + j] = i == j ? 0 : 1;
+      }
+    for (auto &p : two) {
+      W[p[0] * n + p[1]] += 200; W[p[1] * n + p[0]] += 200;
+      nl[p[0] * n + p[1]] = nl[p[1] * n + p[0]] = 2;
+    }
+    for (auto &p : one) {
+      W[p[0] * n + p[1]] += 100; W[p[1] * n + p[0]] += 100;
+      nl[p[0] * n + p[1]] = nl[p[1] * n + p[0]] = 2;
+    }
+    if (gpa_create(0, &ctx) != GPA_OK) return 2;
+    if (gpa_set_topology(ctx, n, W, nl) != GPA_OK) return 2;
+  }
   gpa_plugin_config cfg = {"nvidia.com/sharedgpu", "NVIDIA_VISIBLE_DEVICES", "/", (uint32_t)replicas, 0, GPA_LIST_STRATEGY_ENVVAR,
-                           GPA_ID_STRATEGY_UUID, 0, 1, 0};
+                           GPA_ID_STRATEGY_UUID, 0, 1, best_effort ? (GPA_FIX_REPLICA_SUFFIX | GPA_FIX_REQUIRED_IDENTITY) : 0};
   gpa_plugin *plugin = nullptr;
-  if (gpa_plugin_create(nullptr, &cfg, devs.data(), n, &plugin) != GPA_OK) return 3;
+  if (gpa_plugin_create(ctx, &cfg, devs.data(), n, &plugin) != GPA_OK) return 3;
+  const unsigned long long launches0 = ctx ? gpa_launch_count(ctx) : 0;
+  // the oracle of the best-effort branch: devices in sorted-uuid order (stripReplicas, replica.go:43), answer as ids
+  std::vector<int> by_uuid(n);
+  for (int i = 0; i < n; i++) by_uuid[i] = i;
+  std::sort(by_uuid.begin(), by_uuid.end(), [&](int a, int b) { return uuids[a] < uuids[b]; });
+  auto oracle_besteffort = [&](const std::vector<const char *> &avail, const std::vector<const char *> &must, int size, char *outbuf,
+                               int *n_out) -> int {
+    auto strip = [](const char *id) { std::string s(id); const size_t c = s.find("-replica-"); return c == std::string::npos ? s : s.substr(0, c); };
+    std::vector<std::string> au, mu;
+    for (auto *a : avail) au.push_back(strip(a));
+    for (auto *m : must) mu.push_back(strip(m));
+    int32_t av[8], rq[8], out[16];
+    int na = 0, nr = 0, cnt = 0;
+    for (int d : by_uuid)
+      if (std::find(au.begin(), au.end(), uuids[d]) != au.end()) av[na++] = d;
+    for (int d : by_uuid)
+      if (std::find(mu.begin(), mu.end(), uuids[d]) != mu.end()) rq[nr++] = d;
+    const int rc = ref_besteffort_fast(n, W, nl, av, na, rq, nr, size, 0, out, &cnt, nullptr);
+    char *o = outbuf;
+    for (int i = 0; i < cnt; i++) {
+      if (out[i] < 0) return 99;  // a nil in the answer: the Go handler dies on device.UUID (server.go:299-301)
+      o += sprintf(o, "%s-replica-0", uuids[out[i]].c_str()) + 1;
+    }
+    *n_out = cnt;
+    return rc;
+  };
   std::vector<std::string> free_ids;
   for (auto &u : uuids)
     for (int r = 0; r < replicas; r++) free_ids.push_back(u + "-replica-" + std::to_string(r));
@@ -87,8 +148,9 @@ int main(int argc, char **argv) {
       const int rc = gpa_plugin_get_preferred_allocation(plugin, avail.data(), (int)avail.size(), must.data(), (int)must.size(), size,
                                                          out.data(), (int)out.size(), &n_out, err, sizeof err);
       auto t1 = std::chrono::steady_clock::now();
-      const int rc2 = ref_prioritize_devices(avail.data(), (int)avail.size(), must.data(), (int)must.size(), size, out2.data(),
-                                             (int)out2.size(), &n_out2, err2, sizeof err2);
+      const int rc2 = best_effort ? oracle_besteffort(avail, must, size, out2.data(), &n_out2)
+                                  : ref_prioritize_devices(avail.data(), (int)avail.size(), must.data(), (int)must.size(), size, out2.data(),
+                                                           (int)out2.size(), &n_out2, err2, sizeof err2);
       auto t2 = std::chrono::steady_clock::now();
       t_pref += std::chrono::duration<double>(t1 - t0).count();
       t_ref += std::chrono::duration<double>(t2 - t1).count();
@@ -122,12 +184,16 @@ int main(int argc, char **argv) {
     }
   }
   printf("{\"what\": \"config 2: stateful GetPreferredAllocation -> Allocate / free stream, seed 2, host C++ behind the C ABI, one "
-         "thread\", \"virtual_devices\": %zu, \"steps\": %ld, \"decisions\": %ld, \"allocations\": %ld, \"frees\": %ld, "
+         "thread\", \"branch\": \"%s\", \"kernel_launches_during_the_stream\": %llu, \"virtual_devices\": %zu, \"steps\": %ld, \"decisions\": %ld, \"allocations\": %ld, \"frees\": %ld, "
          "\"request_errors_no_devices_left\": %ld, \"mismatches_vs_oracle\": %ld, \"decisions_per_s\": %.0f, "
-         "\"oracle_prioritize_only_per_s\": %.0f, \"preferred_us\": {\"p50\": %.2f, \"p99\": %.2f}, \"allocate_us\": {\"p50\": %.2f, "
+         "\"oracle_decision_only_per_s\": %.0f, \"preferred_us\": {\"p50\": %.2f, \"p99\": %.2f}, \"allocate_us\": {\"p50\": %.2f, "
          "\"p99\": %.2f}}\n",
-         n_virtual, steps, decisions, allocs, frees, errors, mismatches, decisions / t_pref, decisions / t_ref, pct(lat_pref, 0.5),
+         best_effort ? "best-effort policy (replicas = 1), answers from the host copy of the GPU-built answer table; fixes D3 + D4 on, "
+                       "oracle = ref_besteffort_fast"
+                     : "prioritizeDevices (replicas > 1), oracle = ref_prioritize_devices",
+         ctx ? gpa_launch_count(ctx) - launches0 : 0ull, n_virtual, steps, decisions, allocs, frees, errors, mismatches, decisions / t_pref, decisions / t_ref, pct(lat_pref, 0.5),
          pct(lat_pref, 0.99), pct(lat_alloc, 0.5), pct(lat_alloc, 0.99));
   gpa_plugin_destroy(plugin);
+  if (ctx) gpa_destroy(ctx);
   return mismatches == 0 ? 0 : 1;
 }
