@@ -126,6 +126,7 @@ __global__ void __launch_bounds__(kTabThreads, kTabThreads >= 1024 ? 1 : 2) best
   uint8_t *s_ans = reinterpret_cast<uint8_t *>(s_tern + 256);
   unsigned long long *full = reinterpret_cast<unsigned long long *>(s_ans + table_ans_bytes(ft.ans_entries));
   __shared__ uint32_t s_marked[kTabFlagWords];
+  __shared__ uint2 s_keep[9];  // s_keep[n] = byte mask of the first n of 8 bytes, as two words
 
   const int tid = threadIdx.x;
   const int n_tiles = (int)(((long long)count + kTabTile - 1) / kTabTile);  // <= 2^21
@@ -139,6 +140,7 @@ __global__ void __launch_bounds__(kTabThreads, kTabThreads >= 1024 ? 1 : 2) best
     bulk_load(ring + (size_t)s * kTabTile, reqs + base, bytes, &full[s]);
   };
   if (tid < kTabFlagWords) s_marked[tid] = 0;
+  if (tid < 9) s_keep[tid] = make_uint2(tid >= 4 ? 0xFFFFFFFFu : (1u << (8 * tid)) - 1u, tid <= 4 ? 0u : (tid >= 8 ? 0xFFFFFFFFu : (1u << (8 * (tid - 4))) - 1u));
   if (tid == 0) {
     for (int s = 0; s < kTabStages; s++) mbar_init(&full[s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -180,44 +182,44 @@ __global__ void __launch_bounds__(kTabThreads, kTabThreads >= 1024 ? 1 : 2) best
 
     bool defer = false;
     if (r < count) {
+      // Straight-line code: every lane computes a lookup (with indices made safe) and the guards select afterwards - the
+      // lanes of a warp hold requests of every kind, so branches would only serialise them.
       const uint32_t rmask = hd.x & 0xFFFFu;
       const int n = (int)((hd.x >> 16) & 0xFFu);
       const int size = (int)(hd.x >> 24);
-      const int flags = (int)(hd.y & 0xFFu);
       const int n_req = __popc(rmask) + (int)((hd.y >> 8) & 0xFFu);
-      unsigned long long r0 = 0x8080808080808080ull;  // 8 x GPA_RES_END: the empty answer
-      // guards of besteffort_policy.go:35-45
-      if (!(size <= 0 || n < size || n_req > size)) {
-        // relabel: device -> its bit in the node order, four devices per PRMT: bit_of is an 8-byte table, a byte-permute
-        // selector holds four table indices, one per nibble.  Bytes beyond the n listed devices are cleared afterwards;
-        // a listed byte that is no device of the node (>= 8) makes the lookup meaningless, and is caught below.
-        const int nc = n < 8 ? n : 8;
-        const unsigned long long keep = nc >= 8 ? ~0ull : ((1ull << (8 * nc)) - 1ull);
-        const uint32_t keep_lo = (uint32_t)keep, keep_hi = (uint32_t)(keep >> 32);
-        const uint32_t bits_lo = __byte_perm(bit_lo, bit_hi, nibbles_of_bytes(dv.x)) & keep_lo;
-        const uint32_t bits_hi = __byte_perm(bit_lo, bit_hi, nibbles_of_bytes(dv.y)) & keep_hi;
-        const uint32_t mask = or_of_bytes(bits_lo | bits_hi);
-        const unsigned long long actual = (((unsigned long long)dv.x | ((unsigned long long)dv.y << 32)) & keep) |
-                                          (0x8080808080808080ull & ~keep);
-        // The list must be strictly ascending in the node order.  A set of devices has exactly one such list, the one
-        // the result path keeps in s_dev[mask]: n distinct devices whose bytes equal it are known, and in order.
-        const bool bad = n > 8 || (rmask >> nc) != 0 || __popc(mask) != n || s_dev[mask] != actual;
-        // required positions -> label bits: spread the 8 position bits into byte masks and select
-        const uint32_t rl = or_of_bytes((bits_lo & bytes_of_bits(rmask & 0xFu)) | (bits_hi & bytes_of_bits((rmask >> 4) & 0xFu)));
-        if (bad) {
-          defer = true;
-          r0 ^= (unsigned long long)((kResDefer ^ 0x80) & 0xFF);
-        } else if (!(flags & GPA_REQ_FOREIGN)) {  // a required pointer that is in no set: every candidate is rejected (:53)
-          const uint32_t chosen = s_ans[ans_index(s_tern, mask, rl, size)];
-          const int n_nil = chosen ? size - __popc(chosen) : 0;  // a set of fewer than `size` devices is the padded one
-          r0 = s_dev[chosen];
-          // nil pads follow the devices (D5): GPA_RES_END (0x80) -> GPA_NIL (0xFF) in n_nil bytes
-          if (n_nil) r0 ^= (0x7F7F7F7F7F7F7F7Full >> (8 * (8 - n_nil))) << (8 * __popc(chosen));
-        }
-      }
+      // guards of besteffort_policy.go:35-45: the empty answer, whatever the device list holds
+      const bool empty = size <= 0 || n < size || n_req > size;
+      // relabel: device -> its bit in the node order, four devices per PRMT: the 8-byte "device -> label bit" table sits in
+      // two registers, a byte-permute selector holds four table indices, one per nibble.  Bytes beyond the n listed
+      // devices are cleared afterwards (s_keep[n] = byte mask of the first n bytes); a listed byte that is no device of
+      // the node (>= 8) makes the lookup meaningless, and is caught by the comparison below.
+      const int nc = n < 8 ? n : 8;
+      const uint2 keep = s_keep[nc];
+      const uint32_t bits_lo = __byte_perm(bit_lo, bit_hi, nibbles_of_bytes(dv.x)) & keep.x;
+      const uint32_t bits_hi = __byte_perm(bit_lo, bit_hi, nibbles_of_bytes(dv.y)) & keep.y;
+      const uint32_t mask = or_of_bytes(bits_lo | bits_hi);
+      // The list must be strictly ascending in the node order.  A set of devices has exactly one such list, the one the
+      // result path keeps in s_dev[mask] (devices, then GPA_RES_END bytes): n distinct devices whose bytes equal it are
+      // known, and in order.
+      const unsigned long long want = s_dev[mask];
+      const uint32_t act_lo = (dv.x & keep.x) | (0x80808080u & ~keep.x), act_hi = (dv.y & keep.y) | (0x80808080u & ~keep.y);
+      const bool bad = n > 8 || (rmask >> nc) != 0 || __popc(mask) != n || (uint32_t)want != act_lo || (uint32_t)(want >> 32) != act_hi;
+      // required positions -> label bits: spread the 8 position bits into byte masks and select
+      const uint32_t rl = or_of_bytes((bits_lo & bytes_of_bits(rmask & 0xFu)) | (bits_hi & bytes_of_bits((rmask >> 4) & 0xFu)));
+      const int sz = size < 1 ? 1 : (size > 8 ? 8 : size);
+      uint32_t chosen = s_ans[ans_index(s_tern, mask, rl, sz)];
+      // no answer to look up: guards, a list the table does not know, or a required pointer that is in no set (:53)
+      if (empty || bad || (hd.y & GPA_REQ_FOREIGN)) chosen = 0;
+      const int pc = __popc(chosen);
+      // nil pads follow the devices (D5): bytes pc .. size-1 turn from GPA_RES_END (0x80) into GPA_NIL (0xFF)
+      const uint2 k_sz = s_keep[chosen ? sz : 0], k_pc = s_keep[pc];
+      const unsigned long long devs = s_dev[chosen];
       uint4 v;
-      v.x = (uint32_t)r0;
-      v.y = (uint32_t)(r0 >> 32);
+      v.x = (uint32_t)devs ^ (k_sz.x & ~k_pc.x & 0x7F7F7F7Fu);
+      v.y = (uint32_t)(devs >> 32) ^ (k_sz.y & ~k_pc.y & 0x7F7F7F7Fu);
+      defer = bad && !empty;
+      if (defer) v.x = 0x80808000u | (uint32_t)(uint8_t)kResDefer;
       v.z = 0x80808080u;
       v.w = 0x80808080u;
       __stcs(reinterpret_cast<uint4 *>(out + r), v);
