@@ -263,3 +263,39 @@ def test_compact_mask8_records(ctx, oracle):
     with pytest.raises(gpa.GpaError) as e:
         ctx.besteffort_batch_masks8(m8)
     assert e.value.code == gpa.ERR_TOO_LARGE
+
+
+def test_mask_formats_from_pinned_buffers_take_the_zero_copy_path(ctx, oracle):
+    """with page-locked caller buffers the mask kernels read the records from, and write the answers to, host memory
+    directly (no staging copies): same answers as from pageable buffers (staged pipeline) and as the oracle; the pinned
+    call is ONE launch whatever the batch size, the staged one a launch per chunk"""
+    name, t = syn.standard_topologies()[10]
+    W, nl = syn.links_to_weights(t)
+    ctx.set_topology_links(t)
+    ctx.set_device_order(ORDER8)
+    count = (1 << 20) + 12345          # more than one chunk of the staged pipeline
+    reqs = syn.random_request_batch(8, count, seed=5, order=ORDER8)
+    masks = syn.records_to_masks(reqs, ORDER8)
+    m8 = syn.masks_to_masks8(masks)
+    want, _ = oracle.besteffort_batch(W, nl, reqs, threads=8)
+    for fmt, data, call, res_dtype, to_masks in (
+            ("masks", masks, ctx.besteffort_batch_masks, syn.MASK_RES_DTYPE, lambda x: x),
+            ("masks8", m8, ctx.besteffort_batch_masks8, syn.MASK8_RES_DTYPE, syn.masks8_results_to_masks)):
+        pin_in = gpa.PinnedBuffer(count, data.dtype)
+        pin_out = gpa.PinnedBuffer(count, res_dtype)
+        try:
+            pin_in.array[:] = data
+            pin_out.array.view(np.uint8)[:] = 0x55
+            before = ctx.launch_count
+            call(pin_in.array, out=pin_out.array)
+            assert ctx.launch_count == before + 1, fmt
+            got_pinned = pin_out.array.copy()
+        finally:
+            pin_in.free()
+            pin_out.free()
+        before = ctx.launch_count
+        got_pageable = call(data)
+        assert ctx.launch_count == before + 2, fmt
+        assert (got_pinned.view(np.uint8) == got_pageable.view(np.uint8)).all(), fmt
+        rec = syn.mask_results_to_records(to_masks(got_pinned), ORDER8)
+        assert (rec["dev"] == want["dev"]).all(), fmt
