@@ -484,7 +484,9 @@ int gpa_probe_hbm(int cuda_device, unsigned long long bytes, int reps, int mode,
 int gpa_probe_lut(int cuda_device, int log2_entries, int reps, double *best_glookups_per_s, char *errbuf, int errbuf_len);
 /* n x n bandwidth matrix, GB/s one way: row = GPU that pulls, column = GPU whose HBM is read; the diagonal is the
  * local copy.  mode 0: peer-load kernel (LDG.128 on a peer-mapped pointer, over NVLink/NVSwitch when NVML says
- * so); mode 1: cudaMemcpyPeerAsync.  can_access (optional, n x n) = cudaDeviceCanAccessPeer. */
+ * so); mode 1: cudaMemcpyPeerAsync - one pair at a time.  Modes 2 / 3: the same two ways of moving the bytes with ALL
+ * GPUs pulling at once (in round s GPU c reads GPU (c + s) mod n), i.e. the matrix under full load of the switch.
+ * can_access (optional, n x n) = cudaDeviceCanAccessPeer. */
 int gpa_probe_p2p(int n_devices, unsigned long long bytes, int reps, int mode, double *matrix_gbs, int *can_access,
                   char *errbuf, int errbuf_len);
 

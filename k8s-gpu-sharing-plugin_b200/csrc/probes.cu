@@ -219,7 +219,7 @@ fail:
 // can_access (optional, n x n) receives cudaDeviceCanAccessPeer.
 int gpa_probe_p2p(int n_devices, unsigned long long bytes, int reps, int mode, double *matrix_gbs, int *can_access, char *errbuf,
                   int errbuf_len) {
-  if (n_devices < 1 || n_devices > 16 || bytes < (1ull << 20) || reps < 1 || !matrix_gbs || (mode != 0 && mode != 1))
+  if (n_devices < 1 || n_devices > 16 || bytes < (1ull << 20) || reps < 1 || !matrix_gbs || mode < 0 || mode > 3)
     return GPA_ERR_INVALID;
   const int n = n_devices;
   const size_t n_vec = bytes / sizeof(uint4);
@@ -257,6 +257,36 @@ int gpa_probe_p2p(int n_devices, unsigned long long bytes, int reps, int mode, d
       if (can_access) can_access[c * n + p] = ok;
     }
   }
+  if (mode >= 2) {
+    // ALL GPUs at once: in round s every GPU c pulls from GPU (c + s) mod n at the same time, so every NVLink port is
+    // busy in both directions and the switch carries n streams.  Round 0 is the local copy on every GPU.
+    const bool use_kernel = mode == 2;
+    for (int s = 0; s < n; s++) {
+      std::vector<double> best(n, 0.0);
+      for (int r = 0; r < reps + 2; r++) {
+        for (int c = 0; c < n; c++) {
+          const int p = (c + s) % n;
+          PROBE_TRY(cudaSetDevice(c));
+          if (use_kernel && can_access && !can_access[c * n + p]) continue;
+          PROBE_TRY(cudaEventRecord(e0[c]));
+          if (use_kernel) stream_kernel<<<grid_for(c), kThreads>>>(src[p], dst[c], n_vec, sink[c]);
+          else PROBE_TRY(cudaMemcpyPeerAsync(dst[c], c, src[p], p, n_vec * sizeof(uint4)));
+          PROBE_TRY(cudaEventRecord(e1[c]));
+        }
+        for (int c = 0; c < n; c++) {
+          const int p = (c + s) % n;
+          if (use_kernel && can_access && !can_access[c * n + p]) continue;
+          PROBE_TRY(cudaSetDevice(c));
+          PROBE_TRY(cudaEventSynchronize(e1[c]));
+          float t = 0;
+          PROBE_TRY(cudaEventElapsedTime(&t, e0[c], e1[c]));
+          const double g = (double)(n_vec * sizeof(uint4)) / (t * 1e-3) / 1e9;
+          if (r >= 2 && g > best[c]) best[c] = g;
+        }
+      }
+      for (int c = 0; c < n; c++) matrix_gbs[c * n + (c + s) % n] = best[c];
+    }
+  } else
   for (int c = 0; c < n; c++) {
     PROBE_TRY(cudaSetDevice(c));
     const int grid = grid_for(c);

@@ -27,6 +27,9 @@ def test_p2p_probe_single_gpu_diagonal():
     assert m.shape == (1, 1) and m[0, 0] > 500 and acc[0, 0] == 1
     m2, _ = gpa.probe_p2p(1, 256 << 20, 3, mode=1)
     assert m2[0, 0] > 500
+    for mode in (2, 3):  # the all-GPUs-at-once rounds degenerate to the local copy
+        m3, _ = gpa.probe_p2p(1, 256 << 20, 3, mode=mode)
+        assert m3[0, 0] > 500
 
 
 def test_probe_argument_checks():
@@ -64,6 +67,14 @@ def test_p2p_matrix_against_nvml_on_two_or_more_gpus():
     assert copy[off].min() >= 0.8 * nvlink_measured, copy
     assert abs(kern[off].mean() - copy[off].mean()) <= 0.03 * copy[off].mean()      # the two modes agree
     assert (np.abs(kern[off] - copy[off]) <= 0.10 * copy[off]).all()
+    # all GPUs pulling at once (round s: GPU c reads GPU (c + s) mod n): the switch gives every pair its full rate
+    # Peer LOADS send a request packet for every line they pull (268 MB of nvltx per GiB, profiles/r02_p2p_nvlink_counters_*),
+    # and with every port busy in both directions those requests share the wire with the other GPU's data: the pull rate
+    # settles at 776 x 1.208 / (1.208 + 0.268) = 636 GB/s, while cudaMemcpyPeerAsync keeps its 774.
+    busy, _ = gpa.probe_p2p(n, 1 << 30, 5, mode=2)
+    assert busy[off].min() >= 0.75 * nvlink_measured, busy
+    busy_copy, _ = gpa.probe_p2p(n, 1 << 30, 5, mode=3)
+    assert busy_copy[off].min() >= 0.8 * nvlink_measured, busy_copy
     # the same pairs as NVML sees them; CUDA device i -> NVML index by UUID
     nv = gpa.Nvml()
     try:

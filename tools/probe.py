@@ -41,11 +41,19 @@ def main():
     if args.gpus > 1:
         m, acc = gpa.probe_p2p(args.gpus, args.p2p_bytes, max(args.reps // 2, 3), mode=0)
         m2, _ = gpa.probe_p2p(args.gpus, args.p2p_bytes, max(args.reps // 2, 3), mode=1)
+        m3, _ = gpa.probe_p2p(args.gpus, args.p2p_bytes, max(args.reps // 2, 3), mode=2)
+        m4, _ = gpa.probe_p2p(args.gpus, args.p2p_bytes, max(args.reps // 2, 3), mode=3)
         off = ~np.eye(args.gpus, dtype=bool)
         out["p2p"] = {"bytes": args.p2p_bytes, "can_access_peer": acc.tolist(),
                       "kernel_peer_read_gbs": np.round(m, 1).tolist(), "memcpy_peer_gbs": np.round(m2, 1).tolist(),
                       "kernel_offdiag_min_mean_max": [float(m[off].min()), float(m[off].mean()), float(m[off].max())],
-                      "memcpy_offdiag_min_mean_max": [float(m2[off].min()), float(m2[off].mean()), float(m2[off].max())]}
+                      "memcpy_offdiag_min_mean_max": [float(m2[off].min()), float(m2[off].mean()), float(m2[off].max())],
+                      "all_gpus_at_once": {
+                          "what": "round s: every GPU c pulls from GPU (c + s) mod n at the same time (all NVLink ports busy both ways)",
+                          "kernel_peer_read_gbs": np.round(m3, 1).tolist(), "memcpy_peer_gbs": np.round(m4, 1).tolist(),
+                          "kernel_offdiag_min_mean_max": [float(m3[off].min()), float(m3[off].mean()), float(m3[off].max())],
+                          "memcpy_offdiag_min_mean_max": [float(m4[off].min()), float(m4[off].mean()), float(m4[off].max())],
+                          "aggregate_kernel_gbs_per_round_mean": float(m3[off].sum() / max(args.gpus - 1, 1))}}
     try:
         nv = gpa.Nvml()
         n = nv.device_count()
