@@ -73,8 +73,8 @@ def test_p2p_matrix_against_nvml_on_two_or_more_gpus():
     # settles at 776 x 1.208 / (1.208 + 0.268) = 636 GB/s, while cudaMemcpyPeerAsync keeps its 774.
     busy, _ = gpa.probe_p2p(n, 1 << 30, 5, mode=2)
     assert busy[off].min() >= 0.75 * nvlink_measured, busy
-    busy_copy, _ = gpa.probe_p2p(n, 1 << 30, 5, mode=3)
-    assert busy_copy[off].min() >= 0.8 * nvlink_measured, busy_copy
+    # (mode 3, cudaMemcpyPeerAsync from every GPU at once, is reported by tools/probe.py but not asserted: on 8 GPUs the
+    # driver runs some of those copies one after the other - 110 to 775 GB/s per pair - which says nothing about a link)
     # the same pairs as NVML sees them; CUDA device i -> NVML index by UUID
     nv = gpa.Nvml()
     try:
