@@ -177,3 +177,18 @@ def test_additional_xids_trim_every_unicode_space(oracle):
     want = [13, 45, 31, 68, 94]     # "7<em space>9" and "<zero width space>5" (not White_Space) are malformed
     assert gpa.get_additional_xids(s) == want
     assert oracle.get_additional_xids(s) == want
+
+
+def test_config3_fragmented_masks_match_the_oracle():
+    """SURVEY.md 8d config 3 (tools/replica_bench.cpp, 300 of its 10 000 masks per case): 128 and 256 virtual devices,
+    every replica free with p in {0.1, 0.5, 0.9}, sizes {1, 2, 3, 4, 8, 16}: prioritizeDevices natively against the
+    oracle, ids, error kind and NonUniqueError alike"""
+    import json
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    subprocess.check_call(["make", "-C", os.path.join(root, "tools"), "-s", "bin/replica_bench"])
+    out = subprocess.run([os.path.join(root, "tools", "bin", "replica_bench"), "300"], capture_output=True, text=True, timeout=300)
+    r = json.loads(out.stdout)
+    assert out.returncode == 0 and len(r["config3"]) == 6
+    assert all(c["mismatches"] == 0 and c["decisions"] == 1800 for c in r["config3"])
+    assert all(c["mismatches"] == 0 for c in r["cases"])
