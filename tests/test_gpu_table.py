@@ -299,3 +299,34 @@ def test_mask_formats_from_pinned_buffers_take_the_zero_copy_path(ctx, oracle):
         assert (got_pinned.view(np.uint8) == got_pageable.view(np.uint8)).all(), fmt
         rec = syn.mask_results_to_records(to_masks(got_pinned), ORDER8)
         assert (rec["dev"] == want["dev"]).all(), fmt
+
+
+def test_full_size_step_all_formats_agree(ctx, oracle):
+    """bench.py's full step (4 Mi requests on the 8-GPU node): the three record formats must give the SAME decisions on
+    every one of them (a size-independent property: one table, three wire formats), the id-list answers must be sets of
+    the right size drawn from the available devices and holding the required one, and a 50 000-record sample must equal
+    the oracle"""
+    t = syn.topo_two_sockets(8)
+    W, nl = syn.links_to_weights(t)
+    ctx.set_topology_links(t)
+    ctx.set_device_order(ORDER8)
+    count = 1 << 22
+    reqs = syn.random_request_batch(8, count, seed=1000, order=ORDER8)
+    masks = syn.records_to_masks(reqs, ORDER8)
+    got = ctx.besteffort_batch(reqs, max_avail=8)
+    got_m = ctx.besteffort_batch_masks(masks)
+    got_m8 = syn.masks8_results_to_masks(ctx.besteffort_batch_masks8(syn.masks_to_masks8(masks)))
+    assert (got_m.view(np.uint8) == got_m8.view(np.uint8)).all()
+    assert (syn.mask_results_to_records(got_m, ORDER8)["dev"] == got["dev"]).all()
+    # structure of every answer: `size` entries (devices then nil pads) or empty; devices available; required one inside
+    n_real = (got_m["chosen_mask"][:, None] >> np.arange(8) & 1).sum(axis=1)
+    answered = got_m["chosen_mask"] != 0
+    assert (got_m["status"] == 0).all()
+    assert ((n_real + got_m["n_nil"])[answered] == reqs["size"][answered]).all()
+    assert (got_m["chosen_mask"] & ~masks["avail_mask"] == 0).all()
+    assert ((masks["req_mask"] & ~got_m["chosen_mask"])[answered] == 0).all()
+    # the guards say exactly when the answer is empty: here size <= |available| always holds and nothing is foreign
+    assert answered.all()
+    idx = np.random.default_rng(7).choice(count, 50000, replace=False)
+    want, _ = oracle.besteffort_batch(W, nl, reqs[idx], threads=8)
+    assert (got["dev"][idx] == want["dev"]).all()
