@@ -202,20 +202,20 @@ int launch_fast(gpa_ctx *ctx, const void *d_reqs, int count, int mode_flags, voi
 
 // Nodes of up to 8 GPUs: one lookup in the answer table per request (table_kernels.cuh).  The table holds the same
 // answers for both alias modes (no partition of such a node has the 7 sets the aliasing needs), so mode_flags is unused.
-template <int kThreads, int kStages>
+template <int kThreads, int kStages, int kRec>
 int launch_table_records(gpa_ctx *ctx, const void *d_reqs, int count, int n_cap, int intended, void *d_out, cudaStream_t stream, int slot) {
-  auto kern = besteffort_batch_table_kernel<kThreads, kStages>;
+  auto kern = besteffort_batch_table_kernel<kThreads, kStages, kRec>;
   if (!ctx->table_attr_set[slot]) {
     CUDA_TRY(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)table_smem_bytes(ans_entries(kAnsMaxTopo), kThreads, kStages)));
+                                       (int)table_smem_bytes(ans_entries(kAnsMaxTopo), kThreads * kRec, kStages)));
     ctx->table_attr_set[slot] = true;
   }
   // persistent: every CTA stages the answer table once and streams its share of the request tiles
-  const long long want = ((long long)count + kThreads - 1) / kThreads;
+  const long long want = ((long long)count + kThreads * kRec - 1) / (kThreads * kRec);
   const long long cap = (long long)ctx->sm_count * (kThreads >= 1024 ? 1 : 2);
   const int grid = (int)(want < cap ? want : cap);
   const BatchTopo t{ctx->d_wq, ctx->d_asym, ctx->topo.n};
-  kern<<<grid, kThreads, table_smem_bytes(ctx->fast.ans_entries, kThreads, kStages), stream>>>(
+  kern<<<grid, kThreads, table_smem_bytes(ctx->fast.ans_entries, kThreads * kRec, kStages), stream>>>(
       static_cast<const gpa_request *>(d_reqs), count, ctx->fast, static_cast<gpa_result *>(d_out), t, n_cap, intended);
   return GPA_OK;
 }
@@ -242,10 +242,11 @@ int launch_table(gpa_ctx *ctx, const void *d_reqs, int count, int max_avail, int
     int n_cap = max_avail < 2 ? 2 : max_avail;  // as the general kernel sees it: a longer list is GPA_ERR_TOO_LARGE
     if (n_cap > GPA_BATCH_MAX_AVAILABLE) n_cap = GPA_BATCH_MAX_AVAILABLE;
     const int intended = mode_flags & GPA_MODE_INTENDED;
-    // One 1024-thread CTA per SM with a 3-stage ring.  Measured against it on B200 (4 Mi requests, event-timed median):
-    // 5 stages 45.5 us, 4 stages 45.4 us, two 512-thread CTAs per SM with 3 stages each 43.3 us, this one 43.3 us - neither
-    // a deeper ring nor decoupling the CTAs' barriers buys anything, so the simplest shape stays.
-    int rc = launch_table_records<1024, 3>(ctx, d_reqs, count, n_cap, intended, d_out, stream, 0);
+    // One 1024-thread CTA per SM, TWO records per thread and tile (2 048 records = 64 KB), a 2-stage ring.  Measured on
+    // B200 (4 Mi requests, event-timed median of the step): one record per thread with 3 / 4 / 5 stages 41.4 / 45.4 / 45.5 us,
+    // two 512-thread CTAs per SM with 3 stages each 41.4 us, this shape 39.5 us - neither a deeper ring nor decoupling the
+    // CTAs' barriers buys anything; halving the per-tile overhead and giving each lane two independent records does.
+    int rc = launch_table_records<1024, 2, 2>(ctx, d_reqs, count, n_cap, intended, d_out, stream, 0);
     if (rc != GPA_OK) return rc;
   }
   ctx->launches++;

@@ -5,7 +5,7 @@
 //                                    part_table.cuh, run once when a topology is installed (52 488 entries for 8 GPUs)
 //   besteffort_batch_table_kernel    MANY 32-byte requests in node order, one LANE per request, requests and answers in
 //                                    RECORD order.  One CTA per SM keeps the answer table in shared memory and streams
-//                                    32 KB request tiles through a ring of shared-memory stages filled by bulk
+//                                    64 KB request tiles through a ring of shared-memory stages filled by bulk
 //                                    asynchronous copies (cp.async.bulk + mbarrier), so that several tiles are in flight
 //                                    per SM while the lanes relabel, look up and store.  No sort, no divergence: the
 //                                    kernel moves 48 bytes per decision and its ceiling is HBM bandwidth.
@@ -18,7 +18,7 @@
 
 namespace {
 
-// The record kernel is a template over (threads per CTA = records per tile, stages of the request ring); which
+// The record kernel is a template over (threads per CTA, stages of the request ring, records per thread and tile); which
 // instantiation runs is chosen on the host (launch_table).
 
 // table: the 2-byte entries of ans_table.cuh (what gpa_get_answer_table() hands out); table8: the chosen masks alone, for
@@ -41,8 +41,8 @@ __global__ void __launch_bounds__(256) answer_table_build_kernel(const FastTopo 
 __host__ __device__ constexpr size_t table_ans_bytes(uint32_t n_entries) { return ((size_t)n_entries + 15) & ~(size_t)15; }  // one byte each
 constexpr size_t kTabSmallTables = 256 * sizeof(unsigned long long) + 256 * sizeof(uint16_t);  // s_dev + tern
 constexpr size_t masks_smem_bytes(uint32_t n_entries) { return kTabSmallTables + table_ans_bytes(n_entries); }
-constexpr size_t table_smem_bytes(uint32_t n_entries, int threads, int stages) {
-  return (size_t)stages * threads * sizeof(gpa_request)  // request ring (first: 128-byte aligned)
+constexpr size_t table_smem_bytes(uint32_t n_entries, int tile_records, int stages) {
+  return (size_t)stages * tile_records * sizeof(gpa_request)  // request ring (first: 128-byte aligned)
          + kTabSmallTables + table_ans_bytes(n_entries) + (size_t)stages * sizeof(unsigned long long);  // + the stages' mbarriers
 }
 
@@ -114,11 +114,11 @@ __device__ __forceinline__ uint32_t bytes_of_bits(uint32_t b4) { return ((b4 * 0
 // that part, and the whole step is ONE launch.
 // reqs must be 16-byte aligned (bulk copies), out 16-byte aligned.
 constexpr int kTabFlagWords = 64;  // tiles of one CTA whose "has a marked record" bit is kept; later tiles share the last bit
-template <int kTabThreads, int kTabStages>
+template <int kTabThreads, int kTabStages, int kRec>
 __global__ void __launch_bounds__(kTabThreads, kTabThreads >= 1024 ? 1 : 2) besteffort_batch_table_kernel(const gpa_request *__restrict__ reqs, int count,
                                                                                 const FastTopo ft, gpa_result *__restrict__ out,
                                                                                 const BatchTopo topo, int n_cap, int intended) {
-  constexpr int kTabTile = kTabThreads;  // records per tile: one per thread
+  constexpr int kTabTile = kTabThreads * kRec;  // records per tile: kRec per thread, kTabThreads apart
   extern __shared__ __align__(128) unsigned char tsmem[];
   gpa_request *ring = reinterpret_cast<gpa_request *>(tsmem);
   unsigned long long *s_dev = reinterpret_cast<unsigned long long *>(ring + (size_t)kTabStages * kTabTile);
@@ -165,15 +165,20 @@ __global__ void __launch_bounds__(kTabThreads, kTabThreads >= 1024 ? 1 : 2) best
   long long r = (long long)blockIdx.x * kTabTile + tid;
   for (int i = 0; i < my_tiles; i++, r += (long long)gridDim.x * kTabTile) {
     mbar_wait(&full[s], parity);
-    // this lane's record: device bytes 0..7 and the 8 bytes of masks / sizes / flags (devices 8..15 cannot belong to a
+    // this lane's records: device bytes 0..7 and the 8 bytes of masks / sizes / flags (devices 8..15 cannot belong to a
     // request this table answers)
-    uint2 dv = make_uint2(0, 0), hd = make_uint2(0, 0);
-    if (r < count) {
-      const uint2 *rec = reinterpret_cast<const uint2 *>(ring + (size_t)s * kTabTile + tid);
-      dv = rec[0];
-      hd = rec[2];
+    uint2 dv[kRec], hd[kRec];
+#pragma unroll
+    for (int q = 0; q < kRec; q++) {
+      dv[q] = make_uint2(0, 0);
+      hd[q] = make_uint2(0, 0);
+      if (r + q * kTabThreads < count) {
+        const uint2 *rec = reinterpret_cast<const uint2 *>(ring + (size_t)s * kTabTile + q * kTabThreads + tid);
+        dv[q] = rec[0];
+        hd[q] = rec[2];
+      }
     }
-    __syncthreads();  // every lane has its record: the stage can be refilled
+    __syncthreads();  // every lane has its records: the stage can be refilled
     if (tid == 0 && i + kTabStages < my_tiles) issue(i + kTabStages, s);
     if (++s == kTabStages) {
       s = 0;
@@ -181,13 +186,17 @@ __global__ void __launch_bounds__(kTabThreads, kTabThreads >= 1024 ? 1 : 2) best
     }
 
     bool defer = false;
-    if (r < count) {
+#pragma unroll
+    for (int q = 0; q < kRec; q++) {
+      const long long rq = r + q * kTabThreads;
+      if (rq >= count) continue;
+      const uint2 dvq = dv[q], hdq = hd[q];
       // Straight-line code: every lane computes a lookup (with indices made safe) and the guards select afterwards - the
       // lanes of a warp hold requests of every kind, so branches would only serialise them.
-      const uint32_t rmask = hd.x & 0xFFFFu;
-      const int n = (int)((hd.x >> 16) & 0xFFu);
-      const int size = (int)(hd.x >> 24);
-      const int n_req = __popc(rmask) + (int)((hd.y >> 8) & 0xFFu);
+      const uint32_t rmask = hdq.x & 0xFFFFu;
+      const int n = (int)((hdq.x >> 16) & 0xFFu);
+      const int size = (int)(hdq.x >> 24);
+      const int n_req = __popc(rmask) + (int)((hdq.y >> 8) & 0xFFu);
       // guards of besteffort_policy.go:35-45: the empty answer, whatever the device list holds
       const bool empty = size <= 0 || n < size || n_req > size;
       // relabel: device -> its bit in the node order, four devices per PRMT: the 8-byte "device -> label bit" table sits in
@@ -196,21 +205,21 @@ __global__ void __launch_bounds__(kTabThreads, kTabThreads >= 1024 ? 1 : 2) best
       // the node (>= 8) makes the lookup meaningless, and is caught by the comparison below.
       const int nc = n < 8 ? n : 8;
       const uint2 keep = s_keep[nc];
-      const uint32_t bits_lo = __byte_perm(bit_lo, bit_hi, nibbles_of_bytes(dv.x)) & keep.x;
-      const uint32_t bits_hi = __byte_perm(bit_lo, bit_hi, nibbles_of_bytes(dv.y)) & keep.y;
+      const uint32_t bits_lo = __byte_perm(bit_lo, bit_hi, nibbles_of_bytes(dvq.x)) & keep.x;
+      const uint32_t bits_hi = __byte_perm(bit_lo, bit_hi, nibbles_of_bytes(dvq.y)) & keep.y;
       const uint32_t mask = or_of_bytes(bits_lo | bits_hi);
       // The list must be strictly ascending in the node order.  A set of devices has exactly one such list, the one the
       // result path keeps in s_dev[mask] (devices, then GPA_RES_END bytes): n distinct devices whose bytes equal it are
       // known, and in order.
       const unsigned long long want = s_dev[mask];
-      const uint32_t act_lo = (dv.x & keep.x) | (0x80808080u & ~keep.x), act_hi = (dv.y & keep.y) | (0x80808080u & ~keep.y);
+      const uint32_t act_lo = (dvq.x & keep.x) | (0x80808080u & ~keep.x), act_hi = (dvq.y & keep.y) | (0x80808080u & ~keep.y);
       const bool bad = n > 8 || (rmask >> nc) != 0 || __popc(mask) != n || (uint32_t)want != act_lo || (uint32_t)(want >> 32) != act_hi;
       // required positions -> label bits: spread the 8 position bits into byte masks and select
       const uint32_t rl = or_of_bytes((bits_lo & bytes_of_bits(rmask & 0xFu)) | (bits_hi & bytes_of_bits((rmask >> 4) & 0xFu)));
       const int sz = size < 1 ? 1 : (size > 8 ? 8 : size);
       uint32_t chosen = s_ans[ans_index(s_tern, mask, rl, sz)];
       // no answer to look up: guards, a list the table does not know, or a required pointer that is in no set (:53)
-      if (empty || bad || (hd.y & GPA_REQ_FOREIGN)) chosen = 0;
+      if (empty || bad || (hdq.y & GPA_REQ_FOREIGN)) chosen = 0;
       const int pc = __popc(chosen);
       // nil pads follow the devices (D5): bytes pc .. size-1 turn from GPA_RES_END (0x80) into GPA_NIL (0xFF)
       const uint2 k_sz = s_keep[chosen ? sz : 0], k_pc = s_keep[pc];
@@ -218,11 +227,12 @@ __global__ void __launch_bounds__(kTabThreads, kTabThreads >= 1024 ? 1 : 2) best
       uint4 v;
       v.x = (uint32_t)devs ^ (k_sz.x & ~k_pc.x & 0x7F7F7F7Fu);
       v.y = (uint32_t)(devs >> 32) ^ (k_sz.y & ~k_pc.y & 0x7F7F7F7Fu);
-      defer = bad && !empty;
-      if (defer) v.x = 0x80808000u | (uint32_t)(uint8_t)kResDefer;
+      const bool defer_q = bad && !empty;
+      if (defer_q) v.x = 0x80808000u | (uint32_t)(uint8_t)kResDefer;
+      defer = defer || defer_q;
       v.z = 0x80808080u;
       v.w = 0x80808080u;
-      __stcs(reinterpret_cast<uint4 *>(out + r), v);
+      __stcs(reinterpret_cast<uint4 *>(out + rq), v);
     }
     if (__any_sync(0xffffffffu, defer) && (tid & 31) == 0) {
       const int bit = i < kTabFlagWords * 32 ? i : kTabFlagWords * 32 - 1;
@@ -246,15 +256,17 @@ __global__ void __launch_bounds__(kTabThreads, kTabThreads >= 1024 ? 1 : 2) best
   for (int i = 0; i < my_tiles; i++) {
     const int bit = i < kTabFlagWords * 32 ? i : kTabFlagWords * 32 - 1;
     if (!(s_marked[bit >> 5] >> (bit & 31) & 1u)) continue;
-    const long long base = ((long long)blockIdx.x + (long long)i * gridDim.x) * kTabTile + warp * 32;
-    const long long r = base + lane;
-    const bool marked = r < count && out[r].dev[0] == kResDefer;
-    unsigned todo = __ballot_sync(0xffffffffu, marked);
-    while (todo) {
-      const int b = __ffs(todo) - 1;
-      todo &= todo - 1;
-      general_request(reqs, base + b, n_cap, 8, intended, topo, out, S, wp, *s_binom, lane);
-      __syncwarp();
+    for (int q = 0; q < kRec; q++) {
+      const long long base = ((long long)blockIdx.x + (long long)i * gridDim.x) * kTabTile + q * kTabThreads + warp * 32;
+      const long long r = base + lane;
+      const bool marked = r < count && out[r].dev[0] == kResDefer;
+      unsigned todo = __ballot_sync(0xffffffffu, marked);
+      while (todo) {
+        const int b = __ffs(todo) - 1;
+        todo &= todo - 1;
+        general_request(reqs, base + b, n_cap, 8, intended, topo, out, S, wp, *s_binom, lane);
+        __syncwarp();
+      }
     }
   }
 }
