@@ -201,7 +201,8 @@ int launch_fast(gpa_ctx *ctx, const void *d_reqs, int count, int mode_flags, voi
 }
 
 // Nodes of up to 8 GPUs: one lookup in the answer table per request (table_kernels.cuh).  The table holds the same
-// answers for both alias modes (no partition of such a node has the 7 sets the aliasing needs), so mode_flags is unused.
+// answers for both alias modes (no partition of such a node has the 7 sets the aliasing needs); the mode only reaches the
+// records the kernel cannot look up and answers through general_request().
 template <int kThreads, int kStages, int kRec>
 int launch_table_records(gpa_ctx *ctx, const void *d_reqs, int count, int n_cap, int intended, void *d_out, cudaStream_t stream, int slot) {
   auto kern = besteffort_batch_table_kernel<kThreads, kStages, kRec>;
