@@ -330,3 +330,32 @@ def test_full_size_step_all_formats_agree(ctx, oracle):
     idx = np.random.default_rng(7).choice(count, 50000, replace=False)
     want, _ = oracle.besteffort_batch(W, nl, reqs[idx], threads=8)
     assert (got["dev"][idx] == want["dev"]).all()
+
+
+@pytest.mark.parametrize("seed", range(5))
+def test_table_on_random_asymmetric_weight_matrices(ctx, oracle, seed):
+    """weights that differ by direction (W[i][j] != W[j][i], equal link counts): calculateGPUPairScore sums the EARLIER
+    device's links (besteffort_policy.go:314), so the table depends on the node order through more than relabelling.
+    Every entry against the oracle, random node order, nodes of 6-8 GPUs."""
+    rng = np.random.default_rng(500 + seed)
+    nt = int(rng.integers(6, 9))
+    alphabet = np.array([0, 10, 20, 30, 40, 50, 60, 100, 110, 150, 200, 260, 300, 640], dtype=np.int32)
+    W = alphabet[rng.integers(0, len(alphabet), size=(nt, nt))].astype(np.int32)
+    np.fill_diagonal(W, 0)
+    nl = np.ones((nt, nt), dtype=np.uint8)
+    np.fill_diagonal(nl, 0)
+    order = [int(x) for x in rng.permutation(nt)]
+    ctx.set_topology(W, nl)
+    ctx.set_device_order(order)
+    table = ctx.answer_table()
+    assert table is not None and len(table) == 3 ** nt * 8
+    items = list(all_table_requests(nt, order))
+    packed = syn.pack_requests([(a, r, s) for _, a, r, s in items])
+    rows = oracle_rows(oracle, W, nl, packed, gpa.MODE_GO_FAITHFUL)
+    pad = order + [0] * 8
+    for (idx, avail, req, size), want in zip(items, rows):
+        assert decode_entry(int(table[idx]), pad) == want, (seed, nt, avail, req, size)
+    # and the batch kernel on the same records, through its relabelling
+    got = ctx.besteffort_batch(packed[::7])
+    for i, want in enumerate(rows[::7]):
+        assert gpa.decode_result(got[i]) == (gpa.OK, want)
