@@ -179,8 +179,9 @@ typedef struct gpa_result {
 int gpa_besteffort_batch(gpa_ctx *ctx, const gpa_request *reqs, int count, int max_avail, int mode_flags,
                          gpa_result *out);
 /* device buffers, asynchronous on `stream` (a cudaStream_t; NULL = the legacy default stream): inputs already
- * resident in HBM, nothing copied, nothing synchronised.  The call only enqueues; it must not overlap with a
- * gpa_set_topology*() on the same context. */
+ * resident in HBM, nothing copied, nothing synchronised.  The call only enqueues; gpa_set_topology*() /
+ * gpa_set_device_order() wait for the device before they replace the tables such a batch may still be reading.
+ * Both buffers must be 16-byte aligned (anything from cudaMalloc is), else GPA_ERR_INVALID. */
 int gpa_besteffort_batch_device(gpa_ctx *ctx, const gpa_request *d_reqs, int count, int max_avail, int mode_flags,
                                 gpa_result *d_out, void *stream);
 #define GPA_BATCH_MAX_AVAILABLE 12 /* larger requests go through gpa_besteffort() one by one */
