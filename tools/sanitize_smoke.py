@@ -28,6 +28,13 @@ assert (ctx.besteffort_batch(reqs)["dev"] == want["dev"]).all()                 
 ctx.set_device_order(order)
 m = syn.records_to_masks(reqs, order)
 assert (syn.mask_results_to_records(ctx.besteffort_batch_masks(m), order)["dev"] == want["dev"]).all()  # mask format
+m8 = syn.masks_to_masks8(m)
+assert (syn.mask_results_to_records(syn.masks8_results_to_masks(ctx.besteffort_batch_masks8(m8)), order)["dev"] == want["dev"]).all()
+assert (ctx.besteffort_batch(reqs, gpa.MODE_FORCE_ENUM)["dev"] == want["dev"]).all()  # tile-binned kernel + deferred pass
+mixed = reqs.copy()
+mixed[::3] = syn.random_request_batch(8, 20000, seed=4)[::3]                           # identity order: foreign to this context
+want_mixed, _ = orc.besteffort_batch(W, nl, mixed)
+assert (ctx.besteffort_batch(mixed)["dev"] == want_mixed["dev"]).all()                 # table kernel answering its deferred records
 for n, k in ((8, 3), (12, 3), (13, 2), (14, 5), (16, 8)):
     tt = syn.topo_random(n, 5)
     Wn, nln = syn.links_to_weights(tt)
