@@ -448,8 +448,9 @@ void parallel_ranges(long long count, int threads, F &&fn) {
 // zero_copy_ok (the mask formats) and pinned buffers: nothing is staged at all, the kernel reads the records from, and
 // writes the answers to, the caller's pinned memory across PCIe in one launch - measured 6-13 % faster than the staged
 // pipeline for 4- and 8-byte records (and than copying the records in while the kernel writes the answers straight out:
-// 10.3 vs 11.4 G decisions/s) and 4 % slower for the 32-byte ones, which therefore stay staged.  GPA_ZERO_COPY=0 / 1
-// in the environment forces it off / on for every format.
+// 10.3 vs 11.4 G decisions/s, and 10.7 with all the copies back to back on one stream and the kernels chained to it by
+// events) and 4 % slower for the 32-byte ones, which therefore stay staged.  GPA_ZERO_COPY=0 / 1 in the environment
+// forces it off / on for every format.
 template <typename Launch>
 int host_batch(gpa_ctx *ctx, const void *reqs, void *out, int count, size_t in_size, size_t out_size, int chunk, bool zero_copy_ok,
                Launch &&launch) {
