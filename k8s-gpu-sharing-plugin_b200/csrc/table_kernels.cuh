@@ -280,6 +280,13 @@ __global__ void __launch_bounds__(kMaskThreads) besteffort_masks_table_kernel(co
   uint16_t *s_tern = reinterpret_cast<uint16_t *>(s_dev + 256);
   uint8_t *s_ans = reinterpret_cast<uint8_t *>(s_tern + 256);
   const int tid = threadIdx.x;
+  // the first records are asked for before the tables are staged: across PCIe (pinned caller buffers) they take
+  // longer to arrive than the staging does
+  const bool wide = ((reinterpret_cast<uintptr_t>(mreqs) & 15u) | (reinterpret_cast<uintptr_t>(mout) & 7u)) == 0;
+  const long long n_pairs = (long long)count >> 1, stride = (long long)gridDim.x * kMaskThreads;
+  long long p = (long long)blockIdx.x * kMaskThreads + tid;
+  uint4 rec = make_uint4(0, 0, 0, 0);
+  if (wide && p < n_pairs) rec = __ldg(reinterpret_cast<const uint4 *>(mreqs) + p);
   stage_tables(ft, s_dev, s_tern, s_ans, tid, kMaskThreads);
   __syncthreads();
 
@@ -296,15 +303,18 @@ __global__ void __launch_bounds__(kMaskThreads) besteffort_masks_table_kernel(co
     const uint32_t chosen = s_ans[ans_index(s_tern, mask, rl, size)];
     return chosen | ((chosen ? (uint32_t)(size - __popc(chosen)) : 0u) << 16);
   };
-  if (((reinterpret_cast<uintptr_t>(mreqs) & 15u) | (reinterpret_cast<uintptr_t>(mout) & 7u)) == 0) {
-    // two records per lane per step: 16 bytes in, 8 bytes out
-    const long long n_pairs = (long long)count >> 1;
-    for (long long p = (long long)blockIdx.x * kMaskThreads + tid; p < n_pairs; p += (long long)gridDim.x * kMaskThreads) {
-      const uint4 rec = __ldg(reinterpret_cast<const uint4 *>(mreqs) + p);
+  if (wide) {
+    // two records per lane per step: 16 bytes in, 8 bytes out; the next step's records are in flight during this one
+    while (p < n_pairs) {
+      const long long nxt = p + stride;
+      uint4 rec_next = make_uint4(0, 0, 0, 0);
+      if (nxt < n_pairs) rec_next = __ldg(reinterpret_cast<const uint4 *>(mreqs) + nxt);
       uint2 res;
       res.x = answer(rec.x, rec.y);
       res.y = answer(rec.z, rec.w);
       reinterpret_cast<uint2 *>(mout)[p] = res;
+      rec = rec_next;
+      p = nxt;
     }
     if ((count & 1) && blockIdx.x == 0 && tid == 0) {
       const uint2 rec = __ldg(mreqs + (count - 1));
@@ -327,6 +337,12 @@ __global__ void __launch_bounds__(kMaskThreads) besteffort_masks8_table_kernel(c
   uint16_t *s_tern = reinterpret_cast<uint16_t *>(s_dev + 256);
   uint8_t *s_ans = reinterpret_cast<uint8_t *>(s_tern + 256);
   const int tid = threadIdx.x;
+  // as in the 8-byte kernel: first records requested before the tables are staged
+  const bool wide = ((reinterpret_cast<uintptr_t>(reqs) & 15u) | (reinterpret_cast<uintptr_t>(out) & 7u)) == 0;
+  const long long n_quads = (long long)count >> 2, stride = (long long)gridDim.x * kMaskThreads;
+  long long q = (long long)blockIdx.x * kMaskThreads + tid;
+  uint4 rec = make_uint4(0, 0, 0, 0);
+  if (wide && q < n_quads) rec = __ldg(reinterpret_cast<const uint4 *>(reqs) + q);
   stage_tables(ft, s_dev, s_tern, s_ans, tid, kMaskThreads);
   __syncthreads();
 
@@ -341,14 +357,17 @@ __global__ void __launch_bounds__(kMaskThreads) besteffort_masks8_table_kernel(c
     const uint32_t chosen = s_ans[ans_index(s_tern, mask, rl, size)];
     return chosen | ((chosen ? (uint32_t)(size - __popc(chosen)) : 0u) << 8);  // the 2-byte entry of ans_table.cuh
   };
-  if (((reinterpret_cast<uintptr_t>(reqs) & 15u) | (reinterpret_cast<uintptr_t>(out) & 7u)) == 0) {
-    const long long n_quads = (long long)count >> 2;
-    for (long long q = (long long)blockIdx.x * kMaskThreads + tid; q < n_quads; q += (long long)gridDim.x * kMaskThreads) {
-      const uint4 rec = __ldg(reinterpret_cast<const uint4 *>(reqs) + q);
+  if (wide) {
+    while (q < n_quads) {
+      const long long nxt = q + stride;
+      uint4 rec_next = make_uint4(0, 0, 0, 0);
+      if (nxt < n_quads) rec_next = __ldg(reinterpret_cast<const uint4 *>(reqs) + nxt);
       uint2 res;
       res.x = answer(rec.x) | (answer(rec.y) << 16);
       res.y = answer(rec.z) | (answer(rec.w) << 16);
       reinterpret_cast<uint2 *>(out)[q] = res;
+      rec = rec_next;
+      q = nxt;
     }
     if (blockIdx.x == 0 && tid < (count & 3)) {
       const long long r = (n_quads << 2) + tid;
