@@ -106,6 +106,9 @@ struct gpa_ctx {
   gpa_subset_request *d_sub_reqs = nullptr;  // staging of gpa_subset_batch()
   gpa_subset_result *d_sub_out = nullptr;
   size_t sub_batch_cap = 0;
+  uint32_t *d_sub_pair = nullptr;  // half-vector table of the replica-set batch kernel on nodes of up to 8 GPUs (sub_pair_fill)
+  bool sub_pair_valid = false;     // false after every topology / order change
+  bool sub_dfs_only = false;       // GPA_SUBSET_WALK=dfs: the depth-first batch kernel on every node (A/B measurements)
   int part_table_nt = 0;             // node size the table was built for, 0 = none
   bool table_attr_set[3] = {false, false, false};
   int zero_copy = -1;  // GPA_ZERO_COPY: 1 / 0 = kernels always / never work on the caller's pinned buffers; -1 = per format
@@ -313,6 +316,7 @@ int ensure_partition_table(gpa_ctx *ctx, int nt) {
 // for nodes of up to kFastMaxTopo devices whose link counts are symmetric.
 int rebuild_fast(gpa_ctx *ctx) {
   Topology &T = ctx->topo;
+  ctx->sub_pair_valid = false;
   if (ctx->d_sfull) {
     cudaFree(ctx->d_sfull);
     ctx->d_sfull = nullptr;
@@ -576,6 +580,8 @@ int gpa_create(int cuda_device, gpa_ctx **out) {
   {
     const char *zc = getenv("GPA_ZERO_COPY");
     ctx->zero_copy = (zc && *zc) ? (*zc == '1' ? 1 : 0) : -1;
+    const char *walk = getenv("GPA_SUBSET_WALK");
+    ctx->sub_dfs_only = walk && strcmp(walk, "dfs") == 0;
   }
   fill_binom(ctx->binom);
   for (uint32_t x = 0; x < 256; x++) ctx->h_tern[x] = (uint16_t)ans_tern(x);
@@ -626,6 +632,7 @@ void gpa_destroy(gpa_ctx *ctx) {
   if (ctx->d_sub_binom) cudaFree(ctx->d_sub_binom);
   if (ctx->d_sub_reqs) cudaFree(ctx->d_sub_reqs);
   if (ctx->d_sub_out) cudaFree(ctx->d_sub_out);
+  if (ctx->d_sub_pair) cudaFree(ctx->d_sub_pair);
   if (ctx->d_reqs) cudaFree(ctx->d_reqs);
   if (ctx->d_out) cudaFree(ctx->d_out);
   if (ctx->h_reqs) cudaFreeHost(ctx->h_reqs);

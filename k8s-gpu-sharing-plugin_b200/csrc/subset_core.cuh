@@ -290,4 +290,152 @@ GPA_HD void sub_batch_item(const uint8_t *f, const uint8_t *r, const uint16_t *c
   }
 }
 
+// --------------------------------------------------------------------------------------------------------------------
+// count form, two halves (the batch kernel's walk on nodes of up to 8 GPUs, K <= kSubHalfMaxK)
+//
+// With c_g = r_g + x_g the score of a count vector splits over the GPU labels 0..3 ("prefix") and 4..7 ("suffix"):
+//   sum_{g<h} c_g c_h w[g][h] = R0 + [P(xp) + xp . lin_p] + [S(xs) + xs . (lin_s + L(xp))]
+//   R0      = sum_{g<h} r_g r_h w[g][h]                       the must-include replicas among themselves
+//   lin_h   = sum_{g != h} r_g w[min(g,h)][max(g,h)]          what one more replica of GPU h adds against them
+//   P / S   = sum_{g<h} x_g x_h w[g][h] inside a half         a property of the half-vector and the node alone
+//   L_h(xp) = sum_{g<4} x_g w[g][h], h = 4..7                 likewise
+// so every 4-part composition of 0..kSubHalfMaxK gets its P, L and S ONCE per node (sub_pair_fill, 495 entries), and a
+// request only has to (1) drop the compositions its free counts do not allow and (2) visit the pairs (xp, xs) with
+// sum(xp) + sum(xs) = K at one multiply-add chain each.  The compositions are stored class by class (sum ascending) and
+// in descending lexicographic order inside a class, GPU 0 / 4 of the half in the HIGHEST byte, so that "first in
+// descending order of the count vector" (subset_core's tie-break) is: larger xp word first, then larger xs word, and a
+// walk through a suffix class with strict `>` keeps the right one.
+constexpr int kSubHalfMaxK = 8;
+constexpr int kSubHalfEntries = 495;  // C(8 + 4, 4)
+GPA_HD int sub_half_start(int t) { return t * (t + 1) * (t + 2) * (t + 3) / 24; }  // compositions with sum < t
+
+// blob layout (bytes): comp u32[495] | P u32[495] | suffix {S, x} u32x2[495] | L u32x4[495]
+constexpr int kSubPairCompOff = 0;
+constexpr int kSubPairPOff = 4 * kSubHalfEntries;
+constexpr int kSubPairSufOff = 8 * kSubHalfEntries;
+constexpr int kSubPairLOff = 16 * kSubHalfEntries;
+constexpr int kSubPairBlobBytes = 32 * kSubHalfEntries;
+
+struct alignas(8) SubWord2 {
+  uint32_t x, y;
+};
+struct alignas(16) SubWord4 {
+  uint32_t x, y, z, w;
+};
+
+// w: label-space pair weights [a * 16 + b], a < b (labels 0..7 used)
+inline void sub_pair_fill(const uint16_t *w, uint32_t *blob) {
+  uint32_t *comp = blob + kSubPairCompOff / 4, *P = blob + kSubPairPOff / 4, *suf = blob + kSubPairSufOff / 4, *L = blob + kSubPairLOff / 4;
+  int e = 0;
+  for (int t = 0; t <= kSubHalfMaxK; t++)
+    for (int a = t; a >= 0; a--)
+      for (int b = t - a; b >= 0; b--)
+        for (int c = t - a - b; c >= 0; c--) {
+          const int x[4] = {a, b, c, t - a - b - c};
+          comp[e] = (uint32_t)x[0] << 24 | (uint32_t)x[1] << 16 | (uint32_t)x[2] << 8 | (uint32_t)x[3];
+          uint32_t p = 0, s = 0;
+          for (int g = 0; g < 4; g++)
+            for (int h = g + 1; h < 4; h++) {
+              p += (uint32_t)(x[g] * x[h]) * w[g * kSubGroups + h];
+              s += (uint32_t)(x[g] * x[h]) * w[(4 + g) * kSubGroups + 4 + h];
+            }
+          P[e] = p;
+          suf[2 * e] = s;
+          suf[2 * e + 1] = comp[e];
+          for (int h = 0; h < 4; h++) {
+            uint32_t l = 0;
+            for (int g = 0; g < 4; g++) l += (uint32_t)x[g] * w[g * kSubGroups + 4 + h];
+            L[4 * e + h] = l;
+          }
+          e++;
+        }
+}
+
+// does composition x respect the free counts of the half?  Both words hold one count per byte, all below 128.
+GPA_HD bool sub_half_fits(uint32_t x, uint32_t fpack) { return (((fpack | 0x80808080u) - x) & 0x80808080u) == 0x80808080u; }
+
+GPA_HD uint32_t sub_dp2a_lo(uint32_t a, uint32_t b, uint32_t c) {  // c + a.lo16 * b.byte0 + a.hi16 * b.byte1
+#ifdef __CUDA_ARCH__
+  return __dp2a_lo(a, b, c);
+#else
+  return c + (a & 0xFFFFu) * (b & 0xFFu) + (a >> 16) * ((b >> 8) & 0xFFu);
+#endif
+}
+GPA_HD uint32_t sub_dp2a_hi(uint32_t a, uint32_t b, uint32_t c) {  // c + a.lo16 * b.byte2 + a.hi16 * b.byte3
+#ifdef __CUDA_ARCH__
+  return __dp2a_hi(a, b, c);
+#else
+  return c + (a & 0xFFFFu) * ((b >> 16) & 0xFFu) + (a >> 16) * (b >> 24);
+#endif
+}
+
+// A lane's running best: score, prefix word, suffix word (the tie-break order)
+struct SubPairBest {
+  int score;
+  uint32_t xp, xs;
+};
+GPA_HD bool sub_pair_better(int s, uint32_t xp, uint32_t xs, const SubPairBest &b) {
+  return s > b.score || (s == b.score && (xp > b.xp || (xp == b.xp && xs > b.xs)));
+}
+
+// One work item: prefix composition `pe` against the suffixes slist[s_first], slist[s_first + step], ... below s_end (one
+// suffix class, in list order = descending).  r0 = R0; lin[0..7] as above.
+GPA_HD void sub_pair_item(const uint32_t *blob, int pe, const uint16_t *slist, int s_first, int s_end, int step, uint32_t r0,
+                          const uint32_t *lin, SubPairBest &best) {
+  const uint32_t *comp = blob + kSubPairCompOff / 4, *P = blob + kSubPairPOff / 4, *L = blob + kSubPairLOff / 4;
+  const SubWord2 *suf = reinterpret_cast<const SubWord2 *>(blob + kSubPairSufOff / 4);
+  const uint32_t xp = comp[pe];
+  const uint32_t base = r0 + P[pe] + (xp >> 24) * lin[0] + ((xp >> 16) & 0xFFu) * lin[1] + ((xp >> 8) & 0xFFu) * lin[2] + (xp & 0xFFu) * lin[3];
+  const SubWord4 l = *reinterpret_cast<const SubWord4 *>(L + 4 * pe);
+  const uint32_t l0 = l.x + lin[4], l1 = l.y + lin[5], l2 = l.z + lin[6], l3 = l.w + lin[7];
+  // 16-bit halves, paired for the 2-way dot products: {lo16: GPU 7, hi16: GPU 6} and {lo16: GPU 5, hi16: GPU 4}
+  const uint32_t q67lo = (l3 & 0xFFFFu) | (l2 << 16), q45lo = (l1 & 0xFFFFu) | (l0 << 16);
+  const uint32_t q67hi = (l3 >> 16) | (l2 & 0xFFFF0000u), q45hi = (l1 >> 16) | (l0 & 0xFFFF0000u);
+  int is = -1;
+  uint32_t ixs = 0;
+  for (int s = s_first; s < s_end; s += step) {
+    const SubWord2 rec = suf[slist[s]];
+    const uint32_t lo = sub_dp2a_lo(q67lo, rec.y, sub_dp2a_hi(q45lo, rec.y, base + rec.x));
+    const uint32_t hi = sub_dp2a_lo(q67hi, rec.y, sub_dp2a_hi(q45hi, rec.y, 0u));
+    const int score = (int)(lo + (hi << 16));
+    if (score > is) {  // strict: the first (largest) suffix of the walk stays
+      is = score;
+      ixs = rec.y;
+    }
+  }
+  if (is >= 0 && sub_pair_better(is, xp, ixs, best)) {
+    best.score = is;
+    best.xp = xp;
+    best.xs = ixs;
+  }
+}
+
+// When fewer than 32 prefixes of a class are left, each gets m = 32 / rem lanes and the suffix class is dealt to them
+// round-robin.  Table entry for rem = 1..31: m | ceil(1024 / m) << 8; lane / m = lane * that >> 10, exact for lane < 32.
+GPA_HD uint32_t sub_pair_split_entry(int rem) {
+  const uint32_t m = rem >= 1 && rem < 32 ? 32u / (uint32_t)rem : 1u;
+  return m | ((1024u + m - 1u) / m) << 8;
+}
+
+// Everything lane `lane` of the warp does for one request once the lists stand: plist / slist = the compositions each half
+// allows (indices into the blob, class by class), poff / soff[t] = where class t starts, [K + 1] = the end.
+GPA_HD void sub_pair_lane(const uint32_t *blob, const uint16_t *plist, const uint16_t *poff, const uint16_t *slist, const uint16_t *soff,
+                          int K, uint32_t r0, const uint32_t *lin, const uint32_t *split_tab, int lane, SubPairBest &best) {
+  for (int t = 0; t <= K; t++) {
+    const int pb = poff[t], pe = poff[t + 1], sb = soff[K - t], se = soff[K - t + 1];
+    if (pe == pb || se == sb) continue;
+    for (int base = pb; base < pe; base += 32) {
+      const int rem = pe - base;
+      int j = lane, sub = 0, m = 1;
+      if (rem < 32) {
+        const uint32_t e = split_tab[rem];
+        m = (int)(e & 0xFFu);
+        j = (int)(((uint32_t)lane * (e >> 8)) >> 10);
+        sub = lane - j * m;
+      }
+      if (j < rem) sub_pair_item(blob, plist[base + j], slist, sb + sub, se, m, r0, lin, best);
+    }
+  }
+}
+
 }  // namespace gpa

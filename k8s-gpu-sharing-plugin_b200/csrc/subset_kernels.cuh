@@ -134,6 +134,128 @@ struct SubsetBatchTopo {
 
 static_assert(sizeof(gpa_subset_request) == 48 && sizeof(gpa_subset_result) == 24, "record layouts of gpualloc.h");
 
+// What a warp knows about its request after the guards (besteffort_policy.go:35-45 and the limits of gpualloc.h)
+struct SubBatchDecoded {
+  int my_f, my_r;  // lane g < 16: free / must-include replicas of GPU label g
+  int size, K;     // K = replicas to choose beyond the must-include ones
+  int n_req;
+  int status;
+  bool search;
+};
+
+__device__ __forceinline__ SubBatchDecoded sub_batch_decode(const gpa_subset_request *reqs, long long i, int nt, const uint16_t *asym_row,
+                                                            const BinomTable &s_binom, int lane) {
+  SubBatchDecoded d;
+  // 48-byte record = 12 words: 0-3 free[], 4-7 must[], 8 size
+  const uint32_t *rec = reinterpret_cast<const uint32_t *>(reqs + i);
+  const uint32_t word = lane < 12 ? __ldg(rec + lane) : 0u;
+  d.size = (int)__shfl_sync(0xffffffffu, word, 8);
+  const uint32_t fw = __shfl_sync(0xffffffffu, word, (lane >> 2) & 3);
+  const uint32_t rw = __shfl_sync(0xffffffffu, word, 4 + ((lane >> 2) & 3));
+  d.my_f = lane < kSubGroups ? (int)((fw >> (8 * (lane & 3))) & 0xFFu) : 0;
+  d.my_r = lane < kSubGroups ? (int)((rw >> (8 * (lane & 3))) & 0xFFu) : 0;
+  const unsigned present = __ballot_sync(0xffffffffu, d.my_f + d.my_r > 0);
+  const unsigned has_free = __ballot_sync(0xffffffffu, d.my_f > 0);
+  int n_free = d.my_f, n_req = d.my_r;
+#pragma unroll
+  for (int o = 8; o > 0; o >>= 1) {  // lanes 16.. hold zeros
+    n_free += __shfl_xor_sync(0xffffffffu, n_free, o);
+    n_req += __shfl_xor_sync(0xffffffffu, n_req, o);
+  }
+  n_free = __shfl_sync(0xffffffffu, n_free, 0);
+  n_req = __shfl_sync(0xffffffffu, n_req, 0);
+  d.n_req = n_req;
+  d.K = d.size - n_req;
+  d.status = GPA_OK;
+  d.search = true;
+  if (present >> nt) {
+    d.status = GPA_ERR_INVALID;  // replicas of a GPU the node does not have
+    d.search = false;
+  } else if (d.size <= 0 || n_free + n_req < d.size || n_req > d.size) {
+    d.search = false;  // besteffort_policy.go:35-45: the empty answer
+  } else if (d.size > GPA_SUBSET_MAX_SIZE || d.K > kSubBatchMaxExtra ||
+             binom_at(s_binom, d.K + __popc(has_free) - 1, __popc(has_free) - 1) > (uint32_t)GPA_SUBSET_BATCH_MAX_CLASSES) {
+    d.status = GPA_ERR_TOO_LARGE;  // (K > 0 implies a GPU with free replicas here, so the binomial is well formed)
+    d.search = false;
+  } else if (d.size >= 2) {
+    const bool bad = lane < kSubGroups && (present >> lane & 1u) && (asym_row[lane] & present);
+    if (__any_sync(0xffffffffu, bad)) {
+      d.status = GPA_ERR_ASYMMETRIC;
+      d.search = false;
+    }
+  }
+  return d;
+}
+
+__device__ __forceinline__ void sub_batch_write_empty(gpa_subset_result *out, long long i, int status, int lane) {
+  if (lane == 0) {
+    uint2 *dst = reinterpret_cast<uint2 *>(out + i);
+    dst[0] = make_uint2(0u, 0u);
+    dst[1] = make_uint2(0u, 0u);
+    dst[2] = make_uint2(0xFFFFFFFFu, (uint32_t)(uint16_t)0 | ((uint32_t)(uint16_t)(int16_t)status << 16));
+  }
+}
+
+// The depth-first walk for one request, whole warp: f / r / cap / exact are the warp's scratch in shared memory.
+template <int G>
+__device__ __forceinline__ void sub_batch_dfs(const SubBatchDecoded &d, uint8_t *f, uint8_t *r, uint16_t *cap, uint32_t *exact,
+                                              const uint16_t *w, gpa_subset_result *out, long long i, int lane) {
+  const int K = d.K, my_f = d.my_f, my_r = d.my_r, size = d.size;
+  // free counts clamped to K, required counts, and what the GPUs from g on can still absorb
+  const int fc = my_f < K ? my_f : K;
+  int suffix = lane < kSubGroups ? fc : 0;
+#pragma unroll
+  for (int o = 1; o < kSubGroups; o <<= 1) {  // inclusive suffix sum over lanes 0..15
+    const int up = __shfl_down_sync(0xffffffffu, suffix, o);
+    if (lane + o < kSubGroups) suffix += up;
+  }
+  if (lane < kSubGroups) {
+    f[lane] = (uint8_t)fc;
+    r[lane] = (uint8_t)my_r;
+    cap[lane] = (uint16_t)suffix;
+  }
+  if (lane == 0) cap[kSubGroups] = 0;
+  __syncwarp();
+
+  // Items = count prefixes of the first kSubPrefix GPUs that respect the free counts and leave no more than the GPUs
+  // below can absorb.  Items that leave the SAME number of replicas walk identical subtrees below the prefix (only P
+  // and L differ), so they are numbered class by class - most left first - and a warp's 32 lanes run in lockstep
+  // except where a round straddles two classes.  exact[p][s] = ways for prefix GPUs p.. to take exactly s.
+  if (lane <= K) exact[kSubPrefix * 16 + lane] = lane == 0 ? 1u : 0u;
+  __syncwarp();
+#pragma unroll
+  for (int p = kSubPrefix - 1; p >= 0; p--) {
+    if (lane <= K) {
+      uint32_t sum = 0;
+      const int hi = (int)f[p] < lane ? (int)f[p] : lane;
+      for (int x = 0; x <= hi; x++) sum += exact[(p + 1) * 16 + lane - x];
+      exact[p * 16 + lane] = sum;
+    }
+    __syncwarp();
+  }
+  const int s_lo = K > (int)cap[kSubPrefix] ? K - (int)cap[kSubPrefix] : 0;  // the prefix must take at least this much
+  uint32_t n_items = 0;
+  for (int sp = s_lo; sp <= K; sp++) n_items += exact[sp];
+  int bs = -1;
+  unsigned long long bp = 0;
+  uint32_t blex = 0;
+  for (uint32_t item = lane; item < n_items; item += 32) {
+    sub_batch_item<G, kSubPrefix>(f, r, cap, w, exact, K, s_lo, item, bs, bp, blex);
+  }
+  const unsigned long long mine = bs >= 0 ? ((unsigned long long)(unsigned)(bs + 1) << 32) | blex : 0ull;
+  const unsigned long long best = warp_max_u64(mine);
+  if (mine == best && best) {  // exactly one lane: prefixes are distinct
+    uint2 *dst = reinterpret_cast<uint2 *>(out + i);
+    uint32_t take[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+    for (int g = 0; g < G; g++) take[g >> 2] |= (uint32_t)((bp >> (4 * g)) & 0xFull) << (8 * (g & 3));
+    dst[0] = make_uint2(take[0], take[1]);
+    dst[1] = make_uint2(take[2], take[3]);
+    dst[2] = make_uint2((uint32_t)bs, (uint32_t)(uint16_t)size | ((uint32_t)(uint16_t)GPA_OK << 16));
+  }
+  __syncwarp();  // f / r / cap are rewritten for the warp's next request
+}
+
 template <int G>
 __global__ void __launch_bounds__(kSubThreads, G <= 8 ? 3 : 1) subset_batch_kernel(const gpa_subset_request *__restrict__ reqs, int count,
                                                                     const SubsetBatchTopo t, gpa_subset_result *__restrict__ out) {
@@ -148,109 +270,131 @@ __global__ void __launch_bounds__(kSubThreads, G <= 8 ? 3 : 1) subset_batch_kern
   for (int i = tid; i < kSubGroups * kSubGroups; i += kSubThreads) w[i] = t.w[i];
   if (tid < kSubGroups) asym_row[tid] = t.asym_row[tid];
   __syncthreads();
-  uint8_t *f = fr_all[warp];
-  uint8_t *r = f + kSubGroups;
-  uint16_t *cap = cap_all[warp];
-  uint32_t *exact = exact_all[warp];
+  for (long long i = (long long)blockIdx.x * kSubBatchWarps + warp; i < count; i += (long long)gridDim.x * kSubBatchWarps) {
+    const SubBatchDecoded d = sub_batch_decode(reqs, i, t.nt, asym_row, s_binom, lane);
+    if (d.search)
+      sub_batch_dfs<G>(d, fr_all[warp], fr_all[warp] + kSubGroups, cap_all[warp], exact_all[warp], w, out, i, lane);
+    else
+      sub_batch_write_empty(out, i, d.status, lane);
+  }
+}
+
+// --------------------------------------------------------------------------------------------------------------------
+// Nodes of up to 8 GPUs: the two-halves walk (subset_core.cuh "count form, two halves").  The node's table of
+// half-vectors (16 KB, built by sub_pair_fill when the topology or the order is installed) is staged in shared memory
+// once per CTA; a warp filters it down to what its request's free counts allow - two ballots per 32 compositions - and
+// then visits (prefix, suffix) pairs at one shared-memory load and five integer operations each.  Requests that choose
+// more than kSubHalfMaxK further replicas take the depth-first walk above.
+constexpr int kSubListLen = (kSubHalfEntries + 1 + 7) & ~7;
+
+template <int G>
+__device__ __noinline__ void sub_batch_dfs_call(const SubBatchDecoded &d, uint8_t *f, uint8_t *r, uint16_t *cap, uint32_t *exact,
+                                                const uint16_t *w, gpa_subset_result *out, long long i, int lane) {
+  sub_batch_dfs<G>(d, f, r, cap, exact, w, out, i, lane);
+}
+
+__global__ void __launch_bounds__(kSubThreads, 4) subset_batch_pair_kernel(const gpa_subset_request *__restrict__ reqs, int count,
+                                                                           const SubsetBatchTopo t, const uint4 *__restrict__ g_blob,
+                                                                           gpa_subset_result *__restrict__ out) {
+  __shared__ __align__(16) uint32_t blob[kSubPairBlobBytes / 4];
+  __shared__ uint32_t split_tab[32];
+  __shared__ uint16_t plist_all[kSubBatchWarps][kSubListLen], slist_all[kSubBatchWarps][kSubListLen];
+  __shared__ uint16_t off_all[kSubBatchWarps][2 * (kSubHalfMaxK + 2)];
+  __shared__ uint32_t lin_all[kSubBatchWarps][8];
+  __shared__ uint16_t w[kSubGroups * kSubGroups];
+  __shared__ uint8_t fr_all[kSubBatchWarps][2 * kSubGroups];
+  __shared__ uint16_t cap_all[kSubBatchWarps][kSubGroups + 1];
+  __shared__ uint32_t exact_all[kSubBatchWarps][(kSubPrefix + 1) * 16];
+  __shared__ uint16_t asym_row[kSubGroups];
+  __shared__ BinomTable s_binom;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  stage_binom(s_binom, tid, kSubThreads);
+  for (int i = tid; i < kSubPairBlobBytes / 16; i += kSubThreads) reinterpret_cast<uint4 *>(blob)[i] = __ldg(g_blob + i);
+  for (int i = tid; i < kSubGroups * kSubGroups; i += kSubThreads) w[i] = t.w[i];
+  if (tid < kSubGroups) asym_row[tid] = t.asym_row[tid];
+  if (tid < 32) split_tab[tid] = sub_pair_split_entry(tid);
+  __syncthreads();
+  uint16_t *plist = plist_all[warp], *slist = slist_all[warp];
+  uint16_t *poff = off_all[warp], *soff = off_all[warp] + kSubHalfMaxK + 2;
+  uint32_t *lin = lin_all[warp];
+  const int my_start = sub_half_start(lane < kSubHalfMaxK + 2 ? lane : 0);  // where class `lane` starts in the table
+  const uint32_t lt = (1u << lane) - 1u;
 
   for (long long i = (long long)blockIdx.x * kSubBatchWarps + warp; i < count; i += (long long)gridDim.x * kSubBatchWarps) {
-    // 48-byte record = 12 words: 0-3 free[], 4-7 must[], 8 size
-    const uint32_t *rec = reinterpret_cast<const uint32_t *>(reqs + i);
-    const uint32_t word = lane < 12 ? __ldg(rec + lane) : 0u;
-    const int size = (int)__shfl_sync(0xffffffffu, word, 8);
-    const uint32_t fw = __shfl_sync(0xffffffffu, word, (lane >> 2) & 3);
-    const uint32_t rw = __shfl_sync(0xffffffffu, word, 4 + ((lane >> 2) & 3));
-    const int my_f = lane < kSubGroups ? (int)((fw >> (8 * (lane & 3))) & 0xFFu) : 0;
-    const int my_r = lane < kSubGroups ? (int)((rw >> (8 * (lane & 3))) & 0xFFu) : 0;
-    const unsigned present = __ballot_sync(0xffffffffu, my_f + my_r > 0);
-    const unsigned has_free = __ballot_sync(0xffffffffu, my_f > 0);
-    int n_free = my_f, n_req = my_r;
-#pragma unroll
-    for (int o = 8; o > 0; o >>= 1) {  // lanes 16.. hold zeros
-      n_free += __shfl_xor_sync(0xffffffffu, n_free, o);
-      n_req += __shfl_xor_sync(0xffffffffu, n_req, o);
+    const SubBatchDecoded d = sub_batch_decode(reqs, i, t.nt, asym_row, s_binom, lane);
+    if (!d.search) {
+      sub_batch_write_empty(out, i, d.status, lane);
+      continue;
     }
-    n_free = __shfl_sync(0xffffffffu, n_free, 0);
-    n_req = __shfl_sync(0xffffffffu, n_req, 0);
-    const int K = size - n_req;
-    int status = GPA_OK;
-    bool search = true;
-    if (present >> t.nt) {
-      status = GPA_ERR_INVALID;  // replicas of a GPU the node does not have
-      search = false;
-    } else if (size <= 0 || n_free + n_req < size || n_req > size) {
-      search = false;  // besteffort_policy.go:35-45: the empty answer
-    } else if (size > GPA_SUBSET_MAX_SIZE || K > kSubBatchMaxExtra ||
-               binom_at(s_binom, K + __popc(has_free) - 1, __popc(has_free) - 1) > (uint32_t)GPA_SUBSET_BATCH_MAX_CLASSES) {
-      status = GPA_ERR_TOO_LARGE;  // (K > 0 implies a GPU with free replicas here, so the binomial is well formed)
-      search = false;
-    } else if (size >= 2) {
-      const bool bad = lane < kSubGroups && (present >> lane & 1u) && (asym_row[lane] & present);
-      if (__any_sync(0xffffffffu, bad)) {
-        status = GPA_ERR_ASYMMETRIC;
-        search = false;
-      }
+    if (d.K > kSubHalfMaxK) {
+      sub_batch_dfs_call<8>(d, fr_all[warp], fr_all[warp] + kSubGroups, cap_all[warp], exact_all[warp], w, out, i, lane);
+      continue;
     }
-    if (search) {
-      // free counts clamped to K, required counts, and what the GPUs from g on can still absorb
-      const int fc = my_f < K ? my_f : K;
-      int suffix = lane < kSubGroups ? fc : 0;
+    const int K = d.K;
+    // free counts clamped to K, one byte per GPU, label 0 / 4 in the highest byte of its half
+    uint32_t fsh = lane < 8 ? (uint32_t)(d.my_f < K ? d.my_f : K) << (8 * (3 - (lane & 3))) : 0u;
+    fsh |= __shfl_xor_sync(0xffffffffu, fsh, 1);
+    fsh |= __shfl_xor_sync(0xffffffffu, fsh, 2);
+    const uint32_t fpack_p = __shfl_sync(0xffffffffu, fsh, 0), fpack_s = __shfl_sync(0xffffffffu, fsh, 4);
+    // the must-include replicas: among themselves (r0) and against one more replica of GPU `lane` (lin)
+    uint32_t r0 = 0, my_lin = 0;
+    if (d.n_req > 0) {
+      uint32_t above = 0;
 #pragma unroll
-      for (int o = 1; o < kSubGroups; o <<= 1) {  // inclusive suffix sum over lanes 0..15
-        const int up = __shfl_down_sync(0xffffffffu, suffix, o);
-        if (lane + o < kSubGroups) suffix += up;
-      }
-      if (lane < kSubGroups) {
-        f[lane] = (uint8_t)fc;
-        r[lane] = (uint8_t)my_r;
-        cap[lane] = (uint16_t)suffix;
-      }
-      if (lane == 0) cap[kSubGroups] = 0;
-      __syncwarp();
-
-      // Items = count prefixes of the first kSubPrefix GPUs that respect the free counts and leave no more than the GPUs
-      // below can absorb.  Items that leave the SAME number of replicas walk identical subtrees below the prefix (only P
-      // and L differ), so they are numbered class by class - most left first - and a warp's 32 lanes run in lockstep
-      // except where a round straddles two classes.  exact[p][s] = ways for prefix GPUs p.. to take exactly s.
-      if (lane <= K) exact[kSubPrefix * 16 + lane] = lane == 0 ? 1u : 0u;
-      __syncwarp();
-#pragma unroll
-      for (int p = kSubPrefix - 1; p >= 0; p--) {
-        if (lane <= K) {
-          uint32_t sum = 0;
-          const int hi = (int)f[p] < lane ? (int)f[p] : lane;
-          for (int x = 0; x <= hi; x++) sum += exact[(p + 1) * 16 + lane - x];
-          exact[p * 16 + lane] = sum;
+      for (int g = 0; g < 8; g++) {
+        const uint32_t rg = (uint32_t)__shfl_sync(0xffffffffu, d.my_r, g);
+        if (lane < 8 && g != lane) {
+          const uint32_t wgl = w[(g < lane ? g : lane) * kSubGroups + (g < lane ? lane : g)];
+          my_lin += rg * wgl;
+          if (g > lane) above += rg * wgl;
         }
-        __syncwarp();
       }
-      const int s_lo = K > (int)cap[kSubPrefix] ? K - (int)cap[kSubPrefix] : 0;  // the prefix must take at least this much
-      uint32_t n_items = 0;
-      for (int sp = s_lo; sp <= K; sp++) n_items += exact[sp];
-      int bs = -1;
-      unsigned long long bp = 0;
-      uint32_t blex = 0;
-      for (uint32_t item = lane; item < n_items; item += 32) {
-        sub_batch_item<G, kSubPrefix>(f, r, cap, w, exact, K, s_lo, item, bs, bp, blex);
-      }
-      const unsigned long long mine = bs >= 0 ? ((unsigned long long)(unsigned)(bs + 1) << 32) | blex : 0ull;
-      const unsigned long long best = warp_max_u64(mine);
-      if (mine == best && best) {  // exactly one lane: prefixes are distinct
-        uint2 *dst = reinterpret_cast<uint2 *>(out + i);
-        uint32_t take[4] = {0u, 0u, 0u, 0u};
+      r0 = (uint32_t)d.my_r * above;
 #pragma unroll
-        for (int g = 0; g < G; g++) take[g >> 2] |= (uint32_t)((bp >> (4 * g)) & 0xFull) << (8 * (g & 3));
-        dst[0] = make_uint2(take[0], take[1]);
-        dst[1] = make_uint2(take[2], take[3]);
-        dst[2] = make_uint2((uint32_t)bs, (uint32_t)(uint16_t)size | ((uint32_t)(uint16_t)GPA_OK << 16));
-      }
-      __syncwarp();  // f / r / cap are rewritten for the warp's next request
-    } else if (lane == 0) {
-      uint2 *dst = reinterpret_cast<uint2 *>(out + i);
-      dst[0] = make_uint2(0u, 0u);
-      dst[1] = make_uint2(0u, 0u);
-      dst[2] = make_uint2(0xFFFFFFFFu, (uint32_t)(uint16_t)0 | ((uint32_t)(uint16_t)(int16_t)status << 16));
+      for (int o = 4; o > 0; o >>= 1) r0 += __shfl_xor_sync(0xffffffffu, r0, o);  // lanes 8.. hold zeros
+      r0 = __shfl_sync(0xffffffffu, r0, 0);
     }
+    if (lane < 8) lin[lane] = my_lin;
+    // the lists: compositions of classes 0..K that fit, for each half, and where every class starts in them
+    const int n_static = sub_half_start(K + 1);
+    int base_p = 0, base_s = 0;
+    for (int i0 = 0; i0 < n_static; i0 += 32) {
+      const int e = i0 + lane;
+      const bool in = e < n_static;
+      const uint32_t x = in ? blob[kSubPairCompOff / 4 + e] : 0u;
+      const bool okp = in && sub_half_fits(x, fpack_p), oks = in && sub_half_fits(x, fpack_s);
+      const unsigned bp = __ballot_sync(0xffffffffu, okp), bsf = __ballot_sync(0xffffffffu, oks);
+      if (okp) plist[base_p + __popc(bp & lt)] = (uint16_t)e;
+      if (oks) slist[base_s + __popc(bsf & lt)] = (uint16_t)e;
+      if (lane <= K && my_start >= i0 && my_start < i0 + 32) {
+        const uint32_t before = (1u << (my_start - i0)) - 1u;
+        poff[lane] = (uint16_t)(base_p + __popc(bp & before));
+        soff[lane] = (uint16_t)(base_s + __popc(bsf & before));
+      }
+      base_p += __popc(bp);
+      base_s += __popc(bsf);
+    }
+    if (lane == 0) {
+      poff[K + 1] = (uint16_t)base_p;
+      soff[K + 1] = (uint16_t)base_s;
+    }
+    __syncwarp();
+    SubPairBest best{-1, 0u, 0u};
+    sub_pair_lane(blob, plist, poff, slist, soff, K, r0, lin, split_tab, lane, best);
+    // the warp's first best: score, then the larger prefix word, then the larger suffix word
+    const unsigned long long k1 = best.score >= 0 ? ((unsigned long long)(unsigned)(best.score + 1) << 32) | best.xp : 0ull;
+    const unsigned long long b1 = warp_max_u64(k1);
+    const unsigned long long k2 = (b1 && k1 == b1) ? (1ull << 32) | best.xs : 0ull;
+    const unsigned long long b2 = warp_max_u64(k2);
+    if (b1 == 0) {
+      sub_batch_write_empty(out, i, GPA_OK, lane);
+    } else if (k2 == b2 && k2) {  // exactly one lane: every pair was visited by one lane
+      uint2 *dst = reinterpret_cast<uint2 *>(out + i);
+      dst[0] = make_uint2(__byte_perm(best.xp, 0u, 0x0123), __byte_perm(best.xs, 0u, 0x0123));
+      dst[1] = make_uint2(0u, 0u);
+      dst[2] = make_uint2((uint32_t)best.score, (uint32_t)(uint16_t)d.size | ((uint32_t)(uint16_t)GPA_OK << 16));
+    }
+    __syncwarp();  // the lists are rewritten for the warp's next request
   }
 }
 

@@ -3,6 +3,7 @@
 // Test infrastructure; built by tests/test_subset_core.py with g++.
 #include <stdint.h>
 
+#include <algorithm>
 #include <vector>
 
 #include "../../k8s-gpu-sharing-plugin_b200/csrc/subset_plan.h"
@@ -116,6 +117,86 @@ static void batch_search(const uint16_t *w, const uint8_t *free_in, const uint8_
   }
   for (int g = 0; g < 16; g++) take[g] = g < G ? (uint8_t)((best_path >> (4 * g)) & 0xF) : 0;
   *score = best_score;
+}
+
+// The two-halves walk of the batch kernel on nodes of up to 8 GPUs (subset_core.cuh "count form, two halves"): the
+// per-node blob, the per-request lists (built here one composition after the other; the kernel compacts them with
+// ballots), then the product's own lane routine for lanes 0..31 and the warp's two-step maximum.
+static void batch_pair_search(const uint16_t *w, const uint8_t *free_in, const uint8_t *must, int size, uint8_t *take, int *score) {
+  using namespace gpa;
+  static std::vector<uint32_t> blob;
+  static std::vector<uint16_t> blob_w;
+  if (blob.empty() || !std::equal(blob_w.begin(), blob_w.end(), w)) {
+    blob.assign(kSubPairBlobBytes / 4, 0u);
+    blob_w.assign(w, w + kSubGroups * kSubGroups);
+    sub_pair_fill(w, blob.data());
+  }
+  int n_req = 0;
+  for (int g = 0; g < 8; g++) n_req += must[g];
+  const int K = size - n_req;
+  uint32_t fpack[2] = {0, 0}, lin[8], r0 = 0;
+  for (int g = 0; g < 8; g++) {
+    const uint32_t fc = (uint32_t)(free_in[g] < K ? free_in[g] : K);
+    fpack[g >> 2] |= fc << (8 * (3 - (g & 3)));
+    lin[g] = 0;
+    for (int h = 0; h < 8; h++)
+      if (h != g) lin[g] += (uint32_t)must[h] * w[(g < h ? g : h) * kSubGroups + (g < h ? h : g)];
+    for (int h = g + 1; h < 8; h++) r0 += (uint32_t)must[g] * must[h] * w[g * kSubGroups + h];
+  }
+  uint16_t plist[kSubHalfEntries], slist[kSubHalfEntries], poff[kSubHalfMaxK + 2], soff[kSubHalfMaxK + 2];
+  int np = 0, ns = 0;
+  for (int t = 0; t <= K; t++) {
+    poff[t] = (uint16_t)np;
+    soff[t] = (uint16_t)ns;
+    for (int e = sub_half_start(t); e < sub_half_start(t + 1); e++) {
+      if (sub_half_fits(blob[e], fpack[0])) plist[np++] = (uint16_t)e;
+      if (sub_half_fits(blob[e], fpack[1])) slist[ns++] = (uint16_t)e;
+    }
+  }
+  poff[K + 1] = (uint16_t)np;
+  soff[K + 1] = (uint16_t)ns;
+  uint32_t split_tab[32];
+  for (int i = 0; i < 32; i++) split_tab[i] = sub_pair_split_entry(i);
+  SubPairBest lanes[32];
+  unsigned long long b1 = 0, b2 = 0;
+  for (int lane = 0; lane < 32; lane++) {
+    lanes[lane] = SubPairBest{-1, 0u, 0u};
+    sub_pair_lane(blob.data(), plist, poff, slist, soff, K, r0, lin, split_tab, lane, lanes[lane]);
+    const unsigned long long k1 = lanes[lane].score >= 0 ? ((unsigned long long)(unsigned)(lanes[lane].score + 1) << 32) | lanes[lane].xp : 0ull;
+    if (k1 > b1) b1 = k1;
+  }
+  int win = -1;
+  for (int lane = 0; lane < 32; lane++) {
+    const unsigned long long k1 = lanes[lane].score >= 0 ? ((unsigned long long)(unsigned)(lanes[lane].score + 1) << 32) | lanes[lane].xp : 0ull;
+    const unsigned long long k2 = (b1 && k1 == b1) ? (1ull << 32) | lanes[lane].xs : 0ull;
+    if (k2 > b2) {
+      b2 = k2;
+      win = lane;
+    }
+  }
+  for (int g = 0; g < 16; g++) take[g] = 0;
+  *score = -1;
+  if (win >= 0) {
+    for (int g = 0; g < 4; g++) {
+      take[g] = (uint8_t)(lanes[win].xp >> (8 * (3 - g)));
+      take[4 + g] = (uint8_t)(lanes[win].xs >> (8 * (3 - g)));
+    }
+    *score = lanes[win].score;
+  }
+}
+
+// form: 0 = what the kernel would pick, 1 = the depth-first walk, 2 = the two-halves walk (nt <= 8, K <= 8 only)
+extern "C" void subset_batch_check_form(int nt, const uint16_t *w, const uint8_t *free_in, const uint8_t *must, int size, int form,
+                                        uint8_t *take, int *score) {
+  int n_req = 0;
+  for (int g = 0; g < 16; g++) n_req += must[g];
+  const bool pair_ok = nt <= 8 && size - n_req <= gpa::kSubHalfMaxK;
+  if (form == 2 || (form == 0 && pair_ok))
+    batch_pair_search(w, free_in, must, size, take, score);
+  else if (nt <= 8)
+    batch_search<8>(w, free_in, must, size, take, score);
+  else
+    batch_search<16>(w, free_in, must, size, take, score);
 }
 
 extern "C" void subset_batch_check(int nt, const uint16_t *w, const uint8_t *free_in, const uint8_t *must, int size, uint8_t *take,

@@ -2,6 +2,8 @@
 the C ABI.  Bit-exact positions on every request.  There is no reference function for this search as a whole - it is
 BASELINE.json north_star's "k-subsets of the available replica set", built from the reference's own combination order,
 pair score and first-best rule (see include/gpualloc.h) - so the oracle is the definition and parity is UNPINNED."""
+import os
+
 import numpy as np
 import pytest
 
@@ -214,3 +216,43 @@ def test_batch_statuses_and_larger_nodes(ctx, oracle):
             assert got["take"][i].tolist() == syn.positions_to_take(phys, set(req), pos), i
             assert int(got["score"][i]) == ctx.search_stats()["best_score"] or len(req) == int(rec["size"])
     assert 0 < n_large < len(big) // 2
+
+
+def test_batch_two_halves_walk_equals_depth_first_walk_and_single_call(ctx):
+    """nodes of up to 8 GPUs answer the count-form batch with the two-halves walk (K <= 8; the depth-first walk beyond):
+    the same take[], score, n_out and status as the depth-first kernel (GPA_SUBSET_WALK=dfs) on every record, at 4 / 16 / 32
+    replicas per GPU, sizes up to 15 and up to three must-include replicas; a sample against the single-request kernel"""
+    os.environ["GPA_SUBSET_WALK"] = "dfs"
+    try:
+        dfs = gpa.Context(0)
+    finally:
+        del os.environ["GPA_SUBSET_WALK"]
+    try:
+        for n_gpus, topo in ((8, syn.topo_random(8, 31)), (8, syn.topo_uniform(8)), (5, syn.topo_random(5, 32)),
+                             (8, syn.standard_topologies()[3][1])):
+            order = syn.sorted_positions(syn.node_uuids(n_gpus, seed=n_gpus))
+            for c in (ctx, dfs):
+                c.set_topology_links(topo)
+                c.set_device_order(order)
+            for reps in (4, 16, 32):
+                reqs = syn.random_subset_batch(n_gpus, reps, 6000, seed=900 + reps + n_gpus, sizes=(1, 2, 3, 4, 6, 8, 9, 12, 15), p_must=0.3)
+                rng = np.random.default_rng(reps)
+                extra = rng.integers(0, len(reqs), 600)          # second and third must-include replicas
+                for i in extra:
+                    g = int(rng.integers(0, n_gpus))
+                    reqs["must"][i, g] += 1
+                reqs["size"][:3] = (0, -2, 200)
+                a, b = ctx.subset_batch(reqs), dfs.subset_batch(reqs)
+                for field in ("status", "n_out", "score", "take"):
+                    assert (a[field] == b[field]).all(), (n_gpus, reps, field, np.nonzero((a[field] != b[field]).reshape(len(reqs), -1).any(axis=1))[0][:5])
+                assert (a["status"] == 0).sum() > 5000 and (reps < 16 or (a["n_out"] > 8).sum() > 300)
+                for i in range(40):
+                    phys, req = syn.subset_record_to_positions(reqs[i])
+                    if a["status"][i] != 0:
+                        continue
+                    rc, pos = ctx.subset_besteffort([order[g] for g in phys], req, int(reqs["size"][i]))
+                    assert rc == 0 and len(pos) == int(a["n_out"][i])
+                    if pos:
+                        assert a["take"][i].tolist() == syn.positions_to_take(phys, set(req), pos), (n_gpus, reps, i)
+    finally:
+        dfs.close()

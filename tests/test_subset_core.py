@@ -241,3 +241,83 @@ def test_batch_walk_matches_the_oracle(harness, n_gpus, replicas):
         assert got_score == score
         checked += 1
     assert checked > 120
+
+
+def batch_run_form(L, W, order, rec, form):
+    """subset_batch_check_form: 1 = depth-first walk, 2 = two-halves walk (nodes of up to 8 GPUs, K <= 8)"""
+    nt = len(order)
+    w = np.zeros(256, dtype=np.uint16)
+    for a in range(nt):
+        for b in range(a + 1, nt):
+            w[a * 16 + b] = W[order[a], order[b]]
+    free = np.ascontiguousarray(rec["free"], dtype=np.uint8)
+    must = np.ascontiguousarray(rec["must"], dtype=np.uint8)
+    take = np.zeros(16, dtype=np.uint8)
+    score = C.c_int(0)
+    L.subset_batch_check_form.restype = None
+    L.subset_batch_check_form(nt, w.ctypes.data_as(C.POINTER(C.c_uint16)), free.ctypes.data_as(C.POINTER(C.c_uint8)),
+                              must.ctypes.data_as(C.POINTER(C.c_uint8)), int(rec["size"]), int(form),
+                              take.ctypes.data_as(C.POINTER(C.c_uint8)), C.byref(score))
+    return take.tolist(), score.value
+
+
+@pytest.mark.parametrize("n_gpus,replicas", [(8, 4), (8, 2), (5, 3), (3, 6)])
+def test_two_halves_walk_matches_the_oracle(harness, n_gpus, replicas):
+    """the batch kernel's walk on nodes of up to 8 GPUs (per-node table of half-vectors, per-request lists, pairs of a
+    prefix and a suffix class) against the literal oracle on the record's expansion to positions"""
+    rng = np.random.default_rng(n_gpus * 100 + replicas)
+    order = [int(x) for x in rng.permutation(n_gpus)]
+    W, nl = syn.links_to_weights(syn.topo_random(n_gpus, 2000 + n_gpus))
+    reqs = syn.random_subset_batch(n_gpus, replicas, 250, seed=7 * n_gpus + replicas, sizes=(1, 2, 3, 4, 5), p_must=0.4)
+    checked = 0
+    for rec in reqs:
+        n_avail = int(rec["free"].sum()) + int(rec["must"].sum())
+        size, n_req = int(rec["size"]), int(rec["must"].sum())
+        if not (0 < size <= n_avail and n_req <= size):
+            continue
+        phys_lab, req = syn.subset_record_to_positions(rec, rng)
+        rc, pos, score, _ = orc.subset_besteffort(W, nl, [order[g] for g in phys_lab], req, size, True)
+        assert rc == 0 and len(pos) == size
+        take, got_score = batch_run_form(harness, W, order, rec, 2)
+        assert take == syn.positions_to_take(phys_lab, set(req), pos), (rec, order)
+        assert got_score == score
+        checked += 1
+    assert checked > 120
+
+
+@pytest.mark.parametrize("topo", ["random", "uniform", "two_islands"])
+def test_two_halves_walk_equals_the_depth_first_walk(harness, topo):
+    """larger requests than the literal oracle can take: both walks of the batch kernel give the same take[] and score,
+    K up to 8, several must-include replicas, ties everywhere on the uniform node"""
+    rng = np.random.default_rng({"random": 1, "uniform": 2, "two_islands": 3}[topo])
+    n_gpus = 8
+    if topo == "random":
+        W, _ = syn.links_to_weights(syn.topo_random(n_gpus, 77))
+    elif topo == "uniform":
+        W = np.full((n_gpus, n_gpus), 40, dtype=np.int64)
+        np.fill_diagonal(W, 0)
+    else:
+        W = np.full((n_gpus, n_gpus), 10, dtype=np.int64)
+        W[:4, :4] = 180
+        W[4:, 4:] = 180
+        np.fill_diagonal(W, 0)
+    order = [int(x) for x in rng.permutation(n_gpus)]
+    checked = 0
+    for _ in range(600):
+        rec = np.zeros((), dtype=syn.SUBSET_REQ_DTYPE)
+        reps = int(rng.choice([1, 2, 4, 16, 32]))
+        rec["free"][:n_gpus] = rng.binomial(reps, float(rng.choice([0.2, 0.5, 0.9])), size=n_gpus)
+        n_must = int(rng.choice([0, 0, 1, 2, 5]))
+        for _ in range(n_must):
+            rec["must"][int(rng.integers(0, n_gpus))] += 1
+        K = int(rng.integers(0, 9))
+        size = K + int(rec["must"].sum())
+        if not (0 < size and int(rec["free"].sum()) >= K):
+            continue
+        rec["size"] = size
+        a = batch_run_form(harness, W, order, rec, 1)
+        b = batch_run_form(harness, W, order, rec, 2)
+        assert a == b, (rec, order)
+        assert sum(b[0]) == K
+        checked += 1
+    assert checked > 300
