@@ -107,6 +107,7 @@ struct gpa_ctx {
   gpa_subset_result *d_sub_out = nullptr;
   size_t sub_batch_cap = 0;
   uint32_t *d_sub_pair = nullptr;  // half-vector table of the replica-set batch kernel on nodes of up to 8 GPUs (sub_pair_fill)
+  unsigned int *d_sub_next = nullptr;  // request counter the warps of that kernel draw from; zeroed on the stream before each launch
   bool sub_pair_valid = false;     // false after every topology / order change
   bool sub_dfs_only = false;       // GPA_SUBSET_WALK=dfs: the depth-first batch kernel on every node (A/B measurements)
   int part_table_nt = 0;             // node size the table was built for, 0 = none
@@ -633,6 +634,7 @@ void gpa_destroy(gpa_ctx *ctx) {
   if (ctx->d_sub_reqs) cudaFree(ctx->d_sub_reqs);
   if (ctx->d_sub_out) cudaFree(ctx->d_sub_out);
   if (ctx->d_sub_pair) cudaFree(ctx->d_sub_pair);
+  if (ctx->d_sub_next) cudaFree(ctx->d_sub_next);
   if (ctx->d_reqs) cudaFree(ctx->d_reqs);
   if (ctx->d_out) cudaFree(ctx->d_out);
   if (ctx->h_reqs) cudaFreeHost(ctx->h_reqs);

@@ -309,12 +309,13 @@ constexpr int kSubHalfMaxK = 8;
 constexpr int kSubHalfEntries = 495;  // C(8 + 4, 4)
 GPA_HD int sub_half_start(int t) { return t * (t + 1) * (t + 2) * (t + 3) / 24; }  // compositions with sum < t
 
-// blob layout (bytes): comp u32[495] | P u32[495] | suffix {S, x} u32x2[495] | L u32x4[495]
+// blob layout (bytes): comp u32[495] | P u32[495] | suffix {S, x} u32x2[495] | L u32x4[495] | meta u32[4]
 constexpr int kSubPairCompOff = 0;
 constexpr int kSubPairPOff = 4 * kSubHalfEntries;
 constexpr int kSubPairSufOff = 8 * kSubHalfEntries;
 constexpr int kSubPairLOff = 16 * kSubHalfEntries;
-constexpr int kSubPairBlobBytes = 32 * kSubHalfEntries;
+constexpr int kSubPairMetaOff = 32 * kSubHalfEntries;  // u32[4]: [0] = largest weight between a prefix and a suffix GPU
+constexpr int kSubPairBlobBytes = 32 * kSubHalfEntries + 16;
 
 struct alignas(8) SubWord2 {
   uint32_t x, y;
@@ -326,6 +327,11 @@ struct alignas(16) SubWord4 {
 // w: label-space pair weights [a * 16 + b], a < b (labels 0..7 used)
 inline void sub_pair_fill(const uint16_t *w, uint32_t *blob) {
   uint32_t *comp = blob + kSubPairCompOff / 4, *P = blob + kSubPairPOff / 4, *suf = blob + kSubPairSufOff / 4, *L = blob + kSubPairLOff / 4;
+  uint32_t *meta = blob + kSubPairMetaOff / 4;
+  meta[0] = meta[1] = meta[2] = meta[3] = 0;
+  for (int g = 0; g < 4; g++)
+    for (int h = 4; h < 8; h++)
+      if (w[g * kSubGroups + h] > meta[0]) meta[0] = w[g * kSubGroups + h];
   int e = 0;
   for (int t = 0; t <= kSubHalfMaxK; t++)
     for (int a = t; a >= 0; a--)
@@ -369,17 +375,19 @@ GPA_HD uint32_t sub_dp2a_hi(uint32_t a, uint32_t b, uint32_t c) {  // c + a.lo16
 #endif
 }
 
-// A lane's running best: score, prefix word, suffix word (the tie-break order)
+// A lane's running best in tie-break order: (score + 1) << 32 | prefix word, then the suffix word.  key 0 = nothing yet.
 struct SubPairBest {
-  int score;
-  uint32_t xp, xs;
+  unsigned long long key;
+  uint32_t xs;
 };
-GPA_HD bool sub_pair_better(int s, uint32_t xp, uint32_t xs, const SubPairBest &b) {
-  return s > b.score || (s == b.score && (xp > b.xp || (xp == b.xp && xs > b.xs)));
-}
+GPA_HD int sub_pair_score(const SubPairBest &b) { return (int)(b.key >> 32) - 1; }
+GPA_HD uint32_t sub_pair_prefix(const SubPairBest &b) { return (uint32_t)b.key; }
 
-// One work item: prefix composition `pe` against the suffixes slist[s_first], slist[s_first + step], ... below s_end (one
+// One work item: prefix composition `pe` against suffixes number s_first, s_first + step, ... below s_end of the list (one
 // suffix class, in list order = descending).  r0 = R0; lin[0..7] as above.
+//   kIdent  the suffix half dropped nothing, so the list is the table itself and is not read
+//   kSmall  every L + lin of this request stays below 65 536 (sub_pair_small): the high halves of the products vanish
+template <bool kIdent, bool kSmall>
 GPA_HD void sub_pair_item(const uint32_t *blob, int pe, const uint16_t *slist, int s_first, int s_end, int step, uint32_t r0,
                           const uint32_t *lin, SubPairBest &best) {
   const uint32_t *comp = blob + kSubPairCompOff / 4, *P = blob + kSubPairPOff / 4, *L = blob + kSubPairLOff / 4;
@@ -393,22 +401,25 @@ GPA_HD void sub_pair_item(const uint32_t *blob, int pe, const uint16_t *slist, i
   const uint32_t q67hi = (l3 >> 16) | (l2 & 0xFFFF0000u), q45hi = (l1 >> 16) | (l0 & 0xFFFF0000u);
   int is = -1;
   uint32_t ixs = 0;
+#pragma unroll 4
   for (int s = s_first; s < s_end; s += step) {
-    const SubWord2 rec = suf[slist[s]];
-    const uint32_t lo = sub_dp2a_lo(q67lo, rec.y, sub_dp2a_hi(q45lo, rec.y, base + rec.x));
-    const uint32_t hi = sub_dp2a_lo(q67hi, rec.y, sub_dp2a_hi(q45hi, rec.y, 0u));
-    const int score = (int)(lo + (hi << 16));
-    if (score > is) {  // strict: the first (largest) suffix of the walk stays
-      is = score;
+    const SubWord2 rec = suf[kIdent ? s : (int)slist[s]];
+    uint32_t sc = sub_dp2a_lo(q67lo, rec.y, sub_dp2a_hi(q45lo, rec.y, base + rec.x));
+    if (!kSmall) sc += sub_dp2a_lo(q67hi, rec.y, sub_dp2a_hi(q45hi, rec.y, 0u)) << 16;
+    if ((int)sc > is) {  // strict: the first (largest) suffix of the walk stays
+      is = (int)sc;
       ixs = rec.y;
     }
   }
-  if (is >= 0 && sub_pair_better(is, xp, ixs, best)) {
-    best.score = is;
-    best.xp = xp;
+  const unsigned long long key = ((unsigned long long)(unsigned)(is + 1) << 32) | xp;  // is = -1: key < any real one
+  if (is >= 0 && (key > best.key || (key == best.key && ixs > best.xs))) {
+    best.key = key;
     best.xs = ixs;
   }
 }
+
+// can the high halves be skipped?  wmax = largest weight between a prefix and a suffix GPU; lin_max over the suffix GPUs
+GPA_HD bool sub_pair_small(int K, uint32_t wmax, uint32_t lin_max) { return (uint32_t)K * wmax + lin_max < 65536u && lin_max < 65536u; }
 
 // When fewer than 32 prefixes of a class are left, each gets m = 32 / rem lanes and the suffix class is dealt to them
 // round-robin.  Table entry for rem = 1..31: m | ceil(1024 / m) << 8; lane / m = lane * that >> 10, exact for lane < 32.
@@ -419,8 +430,12 @@ GPA_HD uint32_t sub_pair_split_entry(int rem) {
 
 // Everything lane `lane` of the warp does for one request once the lists stand: plist / slist = the compositions each half
 // allows (indices into the blob, class by class), poff / soff[t] = where class t starts, [K + 1] = the end.
-GPA_HD void sub_pair_lane(const uint32_t *blob, const uint16_t *plist, const uint16_t *poff, const uint16_t *slist, const uint16_t *soff,
-                          int K, uint32_t r0, const uint32_t *lin, const uint32_t *split_tab, int lane, SubPairBest &best) {
+template <bool kIdent, bool kSmall>
+GPA_HD void sub_pair_lane_t(const uint32_t *blob, const uint16_t *plist, const uint16_t *poff, const uint16_t *slist, const uint16_t *soff,
+                            int K, uint32_t r0, const uint32_t *lin_in, const uint32_t *split_tab, int lane, SubPairBest &best) {
+  uint32_t lin[8];
+#pragma unroll
+  for (int g = 0; g < 8; g++) lin[g] = lin_in[g];
   for (int t = 0; t <= K; t++) {
     const int pb = poff[t], pe = poff[t + 1], sb = soff[K - t], se = soff[K - t + 1];
     if (pe == pb || se == sb) continue;
@@ -433,8 +448,25 @@ GPA_HD void sub_pair_lane(const uint32_t *blob, const uint16_t *plist, const uin
         j = (int)(((uint32_t)lane * (e >> 8)) >> 10);
         sub = lane - j * m;
       }
-      if (j < rem) sub_pair_item(blob, plist[base + j], slist, sb + sub, se, m, r0, lin, best);
+      if (j < rem) sub_pair_item<kIdent, kSmall>(blob, plist[base + j], slist, sb + sub, se, m, r0, lin, best);
     }
+  }
+}
+
+// ident / small: the same for every lane of the warp
+GPA_HD void sub_pair_lane(const uint32_t *blob, const uint16_t *plist, const uint16_t *poff, const uint16_t *slist, const uint16_t *soff,
+                          int K, uint32_t r0, const uint32_t *lin, const uint32_t *split_tab, bool ident, bool small, int lane,
+                          SubPairBest &best) {
+  if (ident) {
+    if (small)
+      sub_pair_lane_t<true, true>(blob, plist, poff, slist, soff, K, r0, lin, split_tab, lane, best);
+    else
+      sub_pair_lane_t<true, false>(blob, plist, poff, slist, soff, K, r0, lin, split_tab, lane, best);
+  } else {
+    if (small)
+      sub_pair_lane_t<false, true>(blob, plist, poff, slist, soff, K, r0, lin, split_tab, lane, best);
+    else
+      sub_pair_lane_t<false, false>(blob, plist, poff, slist, soff, K, r0, lin, split_tab, lane, best);
   }
 }
 

@@ -286,6 +286,7 @@ __global__ void __launch_bounds__(kSubThreads, G <= 8 ? 3 : 1) subset_batch_kern
 // then visits (prefix, suffix) pairs at one shared-memory load and five integer operations each.  Requests that choose
 // more than kSubHalfMaxK further replicas take the depth-first walk above.
 constexpr int kSubListLen = (kSubHalfEntries + 1 + 7) & ~7;
+constexpr int kSubDraw = 4;  // requests a warp takes from the counter at a time
 
 template <int G>
 __device__ __noinline__ void sub_batch_dfs_call(const SubBatchDecoded &d, uint8_t *f, uint8_t *r, uint16_t *cap, uint32_t *exact,
@@ -295,6 +296,7 @@ __device__ __noinline__ void sub_batch_dfs_call(const SubBatchDecoded &d, uint8_
 
 __global__ void __launch_bounds__(kSubThreads, 4) subset_batch_pair_kernel(const gpa_subset_request *__restrict__ reqs, int count,
                                                                            const SubsetBatchTopo t, const uint4 *__restrict__ g_blob,
+                                                                           unsigned int *__restrict__ g_next,
                                                                            gpa_subset_result *__restrict__ out) {
   __shared__ __align__(16) uint32_t blob[kSubPairBlobBytes / 4];
   __shared__ uint32_t split_tab[32];
@@ -320,7 +322,17 @@ __global__ void __launch_bounds__(kSubThreads, 4) subset_batch_pair_kernel(const
   const int my_start = sub_half_start(lane < kSubHalfMaxK + 2 ? lane : 0);  // where class `lane` starts in the table
   const uint32_t lt = (1u << lane) - 1u;
 
-  for (long long i = (long long)blockIdx.x * kSubBatchWarps + warp; i < count; i += (long long)gridDim.x * kSubBatchWarps) {
+  const uint32_t wmax = blob[kSubPairMetaOff / 4];
+  // Requests cost between a few hundred and several thousand instructions (1 to 6 435 count vectors), so the warps
+  // draw them kSubDraw at a time from a counter (*g_next, zeroed by the host before the launch) instead of striding:
+  // no SM waits for its slowest warp's fixed share.
+  for (;;) {
+    unsigned int first = 0;
+    if (lane == 0) first = atomicAdd(g_next, (unsigned int)kSubDraw);
+    first = __shfl_sync(0xffffffffu, first, 0);
+    if (first >= (unsigned int)count) break;
+    const unsigned int last = first + kSubDraw < (unsigned int)count ? first + kSubDraw : (unsigned int)count;
+  for (long long i = first; i < last; i++) {
     const SubBatchDecoded d = sub_batch_decode(reqs, i, t.nt, asym_row, s_binom, lane);
     if (!d.search) {
       sub_batch_write_empty(out, i, d.status, lane);
@@ -355,6 +367,13 @@ __global__ void __launch_bounds__(kSubThreads, 4) subset_batch_pair_kernel(const
       r0 = __shfl_sync(0xffffffffu, r0, 0);
     }
     if (lane < 8) lin[lane] = my_lin;
+    uint32_t lin_max = lane >= 4 && lane < 8 ? my_lin : 0u;
+    if (d.n_req > 0) {
+      lin_max = max(lin_max, __shfl_xor_sync(0xffffffffu, lin_max, 1));
+      lin_max = max(lin_max, __shfl_xor_sync(0xffffffffu, lin_max, 2));
+      lin_max = __shfl_sync(0xffffffffu, lin_max, 4);
+    }
+    const bool small = sub_pair_small(K, wmax, lin_max);
     // the lists: compositions of classes 0..K that fit, for each half, and where every class starts in them
     const int n_static = sub_half_start(K + 1);
     int base_p = 0, base_s = 0;
@@ -379,10 +398,10 @@ __global__ void __launch_bounds__(kSubThreads, 4) subset_batch_pair_kernel(const
       soff[K + 1] = (uint16_t)base_s;
     }
     __syncwarp();
-    SubPairBest best{-1, 0u, 0u};
-    sub_pair_lane(blob, plist, poff, slist, soff, K, r0, lin, split_tab, lane, best);
+    SubPairBest best{0ull, 0u};
+    sub_pair_lane(blob, plist, poff, slist, soff, K, r0, lin, split_tab, base_s == n_static, small, lane, best);
     // the warp's first best: score, then the larger prefix word, then the larger suffix word
-    const unsigned long long k1 = best.score >= 0 ? ((unsigned long long)(unsigned)(best.score + 1) << 32) | best.xp : 0ull;
+    const unsigned long long k1 = best.key;
     const unsigned long long b1 = warp_max_u64(k1);
     const unsigned long long k2 = (b1 && k1 == b1) ? (1ull << 32) | best.xs : 0ull;
     const unsigned long long b2 = warp_max_u64(k2);
@@ -390,11 +409,12 @@ __global__ void __launch_bounds__(kSubThreads, 4) subset_batch_pair_kernel(const
       sub_batch_write_empty(out, i, GPA_OK, lane);
     } else if (k2 == b2 && k2) {  // exactly one lane: every pair was visited by one lane
       uint2 *dst = reinterpret_cast<uint2 *>(out + i);
-      dst[0] = make_uint2(__byte_perm(best.xp, 0u, 0x0123), __byte_perm(best.xs, 0u, 0x0123));
+      dst[0] = make_uint2(__byte_perm(sub_pair_prefix(best), 0u, 0x0123), __byte_perm(best.xs, 0u, 0x0123));
       dst[1] = make_uint2(0u, 0u);
-      dst[2] = make_uint2((uint32_t)best.score, (uint32_t)(uint16_t)d.size | ((uint32_t)(uint16_t)GPA_OK << 16));
+      dst[2] = make_uint2((uint32_t)sub_pair_score(best), (uint32_t)(uint16_t)d.size | ((uint32_t)(uint16_t)GPA_OK << 16));
     }
     __syncwarp();  // the lists are rewritten for the warp's next request
+  }
   }
 }
 

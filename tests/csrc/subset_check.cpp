@@ -157,17 +157,20 @@ static void batch_pair_search(const uint16_t *w, const uint8_t *free_in, const u
   soff[K + 1] = (uint16_t)ns;
   uint32_t split_tab[32];
   for (int i = 0; i < 32; i++) split_tab[i] = sub_pair_split_entry(i);
+  const bool ident = ns == sub_half_start(K + 1);
+  uint32_t lin_max = 0;
+  for (int g = 4; g < 8; g++) lin_max = lin[g] > lin_max ? lin[g] : lin_max;
+  const bool small = sub_pair_small(K, blob[kSubPairMetaOff / 4], lin_max);
   SubPairBest lanes[32];
   unsigned long long b1 = 0, b2 = 0;
   for (int lane = 0; lane < 32; lane++) {
-    lanes[lane] = SubPairBest{-1, 0u, 0u};
-    sub_pair_lane(blob.data(), plist, poff, slist, soff, K, r0, lin, split_tab, lane, lanes[lane]);
-    const unsigned long long k1 = lanes[lane].score >= 0 ? ((unsigned long long)(unsigned)(lanes[lane].score + 1) << 32) | lanes[lane].xp : 0ull;
-    if (k1 > b1) b1 = k1;
+    lanes[lane] = SubPairBest{0ull, 0u};
+    sub_pair_lane(blob.data(), plist, poff, slist, soff, K, r0, lin, split_tab, ident, small, lane, lanes[lane]);
+    if (lanes[lane].key > b1) b1 = lanes[lane].key;
   }
   int win = -1;
   for (int lane = 0; lane < 32; lane++) {
-    const unsigned long long k1 = lanes[lane].score >= 0 ? ((unsigned long long)(unsigned)(lanes[lane].score + 1) << 32) | lanes[lane].xp : 0ull;
+    const unsigned long long k1 = lanes[lane].key;
     const unsigned long long k2 = (b1 && k1 == b1) ? (1ull << 32) | lanes[lane].xs : 0ull;
     if (k2 > b2) {
       b2 = k2;
@@ -178,10 +181,10 @@ static void batch_pair_search(const uint16_t *w, const uint8_t *free_in, const u
   *score = -1;
   if (win >= 0) {
     for (int g = 0; g < 4; g++) {
-      take[g] = (uint8_t)(lanes[win].xp >> (8 * (3 - g)));
+      take[g] = (uint8_t)(sub_pair_prefix(lanes[win]) >> (8 * (3 - g)));
       take[4 + g] = (uint8_t)(lanes[win].xs >> (8 * (3 - g)));
     }
-    *score = lanes[win].score;
+    *score = sub_pair_score(lanes[win]);
   }
 }
 

@@ -254,5 +254,25 @@ def test_batch_two_halves_walk_equals_depth_first_walk_and_single_call(ctx):
                     assert rc == 0 and len(pos) == int(a["n_out"][i])
                     if pos:
                         assert a["take"][i].tolist() == syn.positions_to_take(phys, set(req), pos), (n_gpus, reps, i)
+        # weights at the score table's limit (546 units a pair) and 124 must-include replicas on one GPU: one more replica
+        # elsewhere adds more than 65 535 units against them, which takes the kernel's second pair of dot products
+        rng = np.random.default_rng(5)
+        W = np.zeros((8, 8), dtype=np.int32)
+        iu = np.triu_indices(8, 1)
+        W[iu] = rng.integers(530, 547, size=len(iu[0]))
+        W[0, 1], W[0, 2] = 541, 546                              # no common unit to divide away
+        W = W + W.T
+        nl = np.ones((8, 8), dtype=np.uint8) - np.eye(8, dtype=np.uint8)
+        for c in (ctx, dfs):
+            c.set_topology(W, nl)
+            c.set_device_order(list(range(8)))
+        reqs = syn.random_subset_batch(8, 16, 3000, seed=77, sizes=(1, 2, 3, 4), p_must=0.0)
+        for i in range(0, len(reqs), 2):
+            reqs["must"][i, int(rng.integers(0, 8))] = 124
+        reqs["size"] = reqs["size"] + reqs["must"].sum(axis=1)          # K = 1 .. 4 further replicas
+        a, b = ctx.subset_batch(reqs), dfs.subset_batch(reqs)
+        for field in ("status", "n_out", "score", "take"):
+            assert (a[field] == b[field]).all(), field
+        assert (a["status"] == 0).all() and int(a["score"].max()) > 124 * 541 * 2
     finally:
         dfs.close()

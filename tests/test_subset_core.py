@@ -285,17 +285,20 @@ def test_two_halves_walk_matches_the_oracle(harness, n_gpus, replicas):
     assert checked > 120
 
 
-@pytest.mark.parametrize("topo", ["random", "uniform", "two_islands"])
+@pytest.mark.parametrize("topo", ["random", "uniform", "two_islands", "heavy"])
 def test_two_halves_walk_equals_the_depth_first_walk(harness, topo):
     """larger requests than the literal oracle can take: both walks of the batch kernel give the same take[] and score,
     K up to 8, several must-include replicas, ties everywhere on the uniform node"""
-    rng = np.random.default_rng({"random": 1, "uniform": 2, "two_islands": 3}[topo])
+    rng = np.random.default_rng({"random": 1, "uniform": 2, "two_islands": 3, "heavy": 4}[topo])
     n_gpus = 8
     if topo == "random":
         W, _ = syn.links_to_weights(syn.topo_random(n_gpus, 77))
     elif topo == "uniform":
         W = np.full((n_gpus, n_gpus), 40, dtype=np.int64)
         np.fill_diagonal(W, 0)
+    elif topo == "heavy":                                        # products beyond 16 bits: the high halves are needed
+        W = rng.integers(3000, 30000, size=(n_gpus, n_gpus)).astype(np.int64)
+        W = np.triu(W, 1) + np.triu(W, 1).T
     else:
         W = np.full((n_gpus, n_gpus), 10, dtype=np.int64)
         W[:4, :4] = 180
