@@ -309,13 +309,16 @@ constexpr int kSubHalfMaxK = 8;
 constexpr int kSubHalfEntries = 495;  // C(8 + 4, 4)
 GPA_HD int sub_half_start(int t) { return t * (t + 1) * (t + 2) * (t + 3) / 24; }  // compositions with sum < t
 
-// blob layout (bytes): comp u32[495] | P u32[495] | suffix {S, x} u32x2[495] | L u32x4[495] | meta u32[4]
+// blob layout (bytes): comp u32[495] | P u32[495] | suffix {S, x} u32x2[495] | L u32x4[495] | Q u32x2[495] | meta u32[2]
+// Q = the low 16 bits of L, paired for the 2-way dot products: {GPU 5 | GPU 4 << 16, GPU 7 | GPU 6 << 16}
 constexpr int kSubPairCompOff = 0;
 constexpr int kSubPairPOff = 4 * kSubHalfEntries;
 constexpr int kSubPairSufOff = 8 * kSubHalfEntries;
 constexpr int kSubPairLOff = 16 * kSubHalfEntries;
-constexpr int kSubPairMetaOff = 32 * kSubHalfEntries;  // u32[4]: [0] = largest weight between a prefix and a suffix GPU
-constexpr int kSubPairBlobBytes = 32 * kSubHalfEntries + 16;
+constexpr int kSubPairQOff = 32 * kSubHalfEntries;
+constexpr int kSubPairMetaOff = 40 * kSubHalfEntries;  // [0] = largest weight between a prefix and a suffix GPU
+constexpr int kSubPairBlobBytes = 40 * kSubHalfEntries + 8;
+static_assert(kSubPairBlobBytes % 16 == 0 && kSubPairLOff % 16 == 0 && kSubPairQOff % 8 == 0, "staged and read with vector accesses");
 
 struct alignas(8) SubWord2 {
   uint32_t x, y;
@@ -327,8 +330,8 @@ struct alignas(16) SubWord4 {
 // w: label-space pair weights [a * 16 + b], a < b (labels 0..7 used)
 inline void sub_pair_fill(const uint16_t *w, uint32_t *blob) {
   uint32_t *comp = blob + kSubPairCompOff / 4, *P = blob + kSubPairPOff / 4, *suf = blob + kSubPairSufOff / 4, *L = blob + kSubPairLOff / 4;
-  uint32_t *meta = blob + kSubPairMetaOff / 4;
-  meta[0] = meta[1] = meta[2] = meta[3] = 0;
+  uint32_t *meta = blob + kSubPairMetaOff / 4, *Q = blob + kSubPairQOff / 4;
+  meta[0] = meta[1] = 0;
   for (int g = 0; g < 4; g++)
     for (int h = 4; h < 8; h++)
       if (w[g * kSubGroups + h] > meta[0]) meta[0] = w[g * kSubGroups + h];
@@ -353,6 +356,8 @@ inline void sub_pair_fill(const uint16_t *w, uint32_t *blob) {
             for (int g = 0; g < 4; g++) l += (uint32_t)x[g] * w[g * kSubGroups + 4 + h];
             L[4 * e + h] = l;
           }
+          Q[2 * e] = (L[4 * e + 1] & 0xFFFFu) | (L[4 * e + 0] << 16);
+          Q[2 * e + 1] = (L[4 * e + 3] & 0xFFFFu) | (L[4 * e + 2] << 16);
           e++;
         }
 }
@@ -375,51 +380,96 @@ GPA_HD uint32_t sub_dp2a_hi(uint32_t a, uint32_t b, uint32_t c) {  // c + a.lo16
 #endif
 }
 
-// A lane's running best in tie-break order: (score + 1) << 32 | prefix word, then the suffix word.  key 0 = nothing yet.
+// A lane's running best: (score + 1) << 32 | prefix word, and which composition that prefix is.  key 0 = nothing yet.
+// The suffix is not tracked: the warp finds it again for the one winning prefix (sub_pair_find_suffix).
 struct SubPairBest {
   unsigned long long key;
-  uint32_t xs;
+  int pe;
 };
 GPA_HD int sub_pair_score(const SubPairBest &b) { return (int)(b.key >> 32) - 1; }
 GPA_HD uint32_t sub_pair_prefix(const SubPairBest &b) { return (uint32_t)b.key; }
 
-// One work item: prefix composition `pe` against suffixes number s_first, s_first + step, ... below s_end of the list (one
-// suffix class, in list order = descending).  r0 = R0; lin[0..7] as above.
-//   kIdent  the suffix half dropped nothing, so the list is the table itself and is not read
-//   kSmall  every L + lin of this request stays below 65 536 (sub_pair_small): the high halves of the products vanish
-template <bool kIdent, bool kSmall>
-GPA_HD void sub_pair_item(const uint32_t *blob, int pe, const uint16_t *slist, int s_first, int s_end, int step, uint32_t r0,
-                          const uint32_t *lin, SubPairBest &best) {
+// What a prefix contributes to every pair it is part of: the score without the suffix, and its L (+ lin) in 16-bit halves
+struct SubPairPrefix {
+  uint32_t base, q45lo, q67lo, q45hi, q67hi;
+};
+// kMode 0: no must-include replicas (r0 = 0, lin = 0): straight from the table, low halves only (8 * 546 < 65 536)
+//       1: every L + lin of this request stays below 65 536 (sub_pair_small): low halves only
+//       2: the general case
+template <int kMode>
+GPA_HD SubPairPrefix sub_pair_prefix_terms(const uint32_t *blob, int pe, uint32_t r0, const uint32_t *lin) {
   const uint32_t *comp = blob + kSubPairCompOff / 4, *P = blob + kSubPairPOff / 4, *L = blob + kSubPairLOff / 4;
-  const SubWord2 *suf = reinterpret_cast<const SubWord2 *>(blob + kSubPairSufOff / 4);
+  SubPairPrefix t;
+  t.q45hi = t.q67hi = 0;
+  if (kMode == 0) {
+    const SubWord2 q = *reinterpret_cast<const SubWord2 *>(blob + kSubPairQOff / 4 + 2 * pe);
+    t.base = P[pe];
+    t.q45lo = q.x;
+    t.q67lo = q.y;
+    return t;
+  }
   const uint32_t xp = comp[pe];
-  const uint32_t base = r0 + P[pe] + (xp >> 24) * lin[0] + ((xp >> 16) & 0xFFu) * lin[1] + ((xp >> 8) & 0xFFu) * lin[2] + (xp & 0xFFu) * lin[3];
+  t.base = r0 + P[pe] + (xp >> 24) * lin[0] + ((xp >> 16) & 0xFFu) * lin[1] + ((xp >> 8) & 0xFFu) * lin[2] + (xp & 0xFFu) * lin[3];
   const SubWord4 l = *reinterpret_cast<const SubWord4 *>(L + 4 * pe);
   const uint32_t l0 = l.x + lin[4], l1 = l.y + lin[5], l2 = l.z + lin[6], l3 = l.w + lin[7];
-  // 16-bit halves, paired for the 2-way dot products: {lo16: GPU 7, hi16: GPU 6} and {lo16: GPU 5, hi16: GPU 4}
-  const uint32_t q67lo = (l3 & 0xFFFFu) | (l2 << 16), q45lo = (l1 & 0xFFFFu) | (l0 << 16);
-  const uint32_t q67hi = (l3 >> 16) | (l2 & 0xFFFF0000u), q45hi = (l1 >> 16) | (l0 & 0xFFFF0000u);
+  // {lo16: GPU 7, hi16: GPU 6} and {lo16: GPU 5, hi16: GPU 4}
+  t.q67lo = (l3 & 0xFFFFu) | (l2 << 16);
+  t.q45lo = (l1 & 0xFFFFu) | (l0 << 16);
+  if (kMode == 2) {
+    t.q67hi = (l3 >> 16) | (l2 & 0xFFFF0000u);
+    t.q45hi = (l1 >> 16) | (l0 & 0xFFFF0000u);
+  }
+  return t;
+}
+
+template <bool kFull>
+GPA_HD int sub_pair_score_of(const SubPairPrefix &t, const SubWord2 &rec) {
+  uint32_t sc = sub_dp2a_lo(t.q67lo, rec.y, sub_dp2a_hi(t.q45lo, rec.y, t.base + rec.x));
+  if (kFull) sc += sub_dp2a_lo(t.q67hi, rec.y, sub_dp2a_hi(t.q45hi, rec.y, 0u)) << 16;
+  return (int)sc;
+}
+
+// One work item: the best score of prefix composition `pe` with suffixes number s_first, s_first + step, ... below s_end
+// of the list (one suffix class); -1 when there is none.
+//   kIdent  the suffix half dropped nothing, so the list is the table itself and is not read
+template <bool kIdent, int kMode>
+GPA_HD int sub_pair_item(const uint32_t *blob, int pe, const uint16_t *slist, int s_first, int s_end, int step, uint32_t r0,
+                         const uint32_t *lin) {
+  const SubWord2 *suf = reinterpret_cast<const SubWord2 *>(blob + kSubPairSufOff / 4);
+  const SubPairPrefix t = sub_pair_prefix_terms<kMode>(blob, pe, r0, lin);
   int is = -1;
-  uint32_t ixs = 0;
-#pragma unroll 4
-  for (int s = s_first; s < s_end; s += step) {
-    const SubWord2 rec = suf[kIdent ? s : (int)slist[s]];
-    uint32_t sc = sub_dp2a_lo(q67lo, rec.y, sub_dp2a_hi(q45lo, rec.y, base + rec.x));
-    if (!kSmall) sc += sub_dp2a_lo(q67hi, rec.y, sub_dp2a_hi(q45hi, rec.y, 0u)) << 16;
-    if ((int)sc > is) {  // strict: the first (largest) suffix of the walk stays
-      is = (int)sc;
-      ixs = rec.y;
-    }
+  int s = s_first;
+  for (; s + step < s_end; s += 2 * step) {  // two a turn: half the loop control, two loads in flight
+    const SubWord2 a = suf[kIdent ? s : (int)slist[s]], b = suf[kIdent ? s + step : (int)slist[s + step]];
+    const int sa = sub_pair_score_of<kMode == 2>(t, a), sb = sub_pair_score_of<kMode == 2>(t, b);
+    is = sa > is ? sa : is;
+    is = sb > is ? sb : is;
   }
-  const unsigned long long key = ((unsigned long long)(unsigned)(is + 1) << 32) | xp;  // is = -1: key < any real one
-  if (is >= 0 && (key > best.key || (key == best.key && ixs > best.xs))) {
-    best.key = key;
-    best.xs = ixs;
+  if (s < s_end) {
+    const int sa = sub_pair_score_of<kMode == 2>(t, suf[kIdent ? s : (int)slist[s]]);
+    is = sa > is ? sa : is;
   }
+  return is;
+}
+
+// The winning prefix once more, by the whole warp: the first suffix of its class (list order = descending, so the one the
+// tie-break wants) that reaches `target`.  Returns this lane's first list position that does, or 0xFFFFFFFF; the warp
+// takes the minimum.
+GPA_HD uint32_t sub_pair_find_suffix(const uint32_t *blob, int pe, const uint16_t *slist, int s_begin, int s_end, uint32_t r0,
+                                     const uint32_t *lin, int target, int lane) {
+  const SubWord2 *suf = reinterpret_cast<const SubWord2 *>(blob + kSubPairSufOff / 4);
+  const SubPairPrefix t = sub_pair_prefix_terms<2>(blob, pe, r0, lin);
+  for (int s = s_begin + lane; s < s_end; s += 32)
+    if (sub_pair_score_of<true>(t, suf[slist[s]]) == target) return (uint32_t)s;
+  return 0xFFFFFFFFu;
 }
 
 // can the high halves be skipped?  wmax = largest weight between a prefix and a suffix GPU; lin_max over the suffix GPUs
 GPA_HD bool sub_pair_small(int K, uint32_t wmax, uint32_t lin_max) { return (uint32_t)K * wmax + lin_max < 65536u && lin_max < 65536u; }
+// kMode of sub_pair_prefix_terms for a request
+GPA_HD int sub_pair_mode(int K, uint32_t wmax, uint32_t lin_max, int n_req) {
+  return !sub_pair_small(K, wmax, lin_max) ? 2 : (n_req == 0 ? 0 : 1);
+}
 
 // When fewer than 32 prefixes of a class are left, each gets m = 32 / rem lanes and the suffix class is dealt to them
 // round-robin.  Table entry for rem = 1..31: m | ceil(1024 / m) << 8; lane / m = lane * that >> 10, exact for lane < 32.
@@ -430,12 +480,12 @@ GPA_HD uint32_t sub_pair_split_entry(int rem) {
 
 // Everything lane `lane` of the warp does for one request once the lists stand: plist / slist = the compositions each half
 // allows (indices into the blob, class by class), poff / soff[t] = where class t starts, [K + 1] = the end.
-template <bool kIdent, bool kSmall>
+template <bool kIdent, int kMode>
 GPA_HD void sub_pair_lane_t(const uint32_t *blob, const uint16_t *plist, const uint16_t *poff, const uint16_t *slist, const uint16_t *soff,
                             int K, uint32_t r0, const uint32_t *lin_in, const uint32_t *split_tab, int lane, SubPairBest &best) {
   uint32_t lin[8];
 #pragma unroll
-  for (int g = 0; g < 8; g++) lin[g] = lin_in[g];
+  for (int g = 0; g < 8; g++) lin[g] = kMode == 0 ? 0u : lin_in[g];
   for (int t = 0; t <= K; t++) {
     const int pb = poff[t], pe = poff[t + 1], sb = soff[K - t], se = soff[K - t + 1];
     if (pe == pb || se == sb) continue;
@@ -448,26 +498,40 @@ GPA_HD void sub_pair_lane_t(const uint32_t *blob, const uint16_t *plist, const u
         j = (int)(((uint32_t)lane * (e >> 8)) >> 10);
         sub = lane - j * m;
       }
-      if (j < rem) sub_pair_item<kIdent, kSmall>(blob, plist[base + j], slist, sb + sub, se, m, r0, lin, best);
+      if (j < rem) {
+        const int entry = plist[base + j];
+        const int is = sub_pair_item<kIdent, kMode>(blob, entry, slist, sb + sub, se, m, r0, lin);
+        const unsigned long long key = ((unsigned long long)(unsigned)(is + 1) << 32) | blob[kSubPairCompOff / 4 + entry];
+        if (is >= 0 && key > best.key) {
+          best.key = key;
+          best.pe = entry;
+        }
+      }
     }
   }
 }
 
-// ident / small: the same for every lane of the warp
+// ident / mode: the same for every lane of the warp
 GPA_HD void sub_pair_lane(const uint32_t *blob, const uint16_t *plist, const uint16_t *poff, const uint16_t *slist, const uint16_t *soff,
-                          int K, uint32_t r0, const uint32_t *lin, const uint32_t *split_tab, bool ident, bool small, int lane,
+                          int K, uint32_t r0, const uint32_t *lin, const uint32_t *split_tab, bool ident, int mode, int lane,
                           SubPairBest &best) {
+#define GPA_SUB_LANE(I, M) sub_pair_lane_t<I, M>(blob, plist, poff, slist, soff, K, r0, lin, split_tab, lane, best)
   if (ident) {
-    if (small)
-      sub_pair_lane_t<true, true>(blob, plist, poff, slist, soff, K, r0, lin, split_tab, lane, best);
+    if (mode == 0)
+      GPA_SUB_LANE(true, 0);
+    else if (mode == 1)
+      GPA_SUB_LANE(true, 1);
     else
-      sub_pair_lane_t<true, false>(blob, plist, poff, slist, soff, K, r0, lin, split_tab, lane, best);
+      GPA_SUB_LANE(true, 2);
   } else {
-    if (small)
-      sub_pair_lane_t<false, true>(blob, plist, poff, slist, soff, K, r0, lin, split_tab, lane, best);
+    if (mode == 0)
+      GPA_SUB_LANE(false, 0);
+    else if (mode == 1)
+      GPA_SUB_LANE(false, 1);
     else
-      sub_pair_lane_t<false, false>(blob, plist, poff, slist, soff, K, r0, lin, split_tab, lane, best);
+      GPA_SUB_LANE(false, 2);
   }
+#undef GPA_SUB_LANE
 }
 
 }  // namespace gpa

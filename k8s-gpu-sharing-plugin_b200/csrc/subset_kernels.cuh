@@ -373,7 +373,7 @@ __global__ void __launch_bounds__(kSubThreads, 4) subset_batch_pair_kernel(const
       lin_max = max(lin_max, __shfl_xor_sync(0xffffffffu, lin_max, 2));
       lin_max = __shfl_sync(0xffffffffu, lin_max, 4);
     }
-    const bool small = sub_pair_small(K, wmax, lin_max);
+    const int mode = sub_pair_mode(K, wmax, lin_max, d.n_req);
     // the lists: compositions of classes 0..K that fit, for each half, and where every class starts in them
     const int n_static = sub_half_start(K + 1);
     int base_p = 0, base_s = 0;
@@ -398,20 +398,29 @@ __global__ void __launch_bounds__(kSubThreads, 4) subset_batch_pair_kernel(const
       soff[K + 1] = (uint16_t)base_s;
     }
     __syncwarp();
-    SubPairBest best{0ull, 0u};
-    sub_pair_lane(blob, plist, poff, slist, soff, K, r0, lin, split_tab, base_s == n_static, small, lane, best);
-    // the warp's first best: score, then the larger prefix word, then the larger suffix word
-    const unsigned long long k1 = best.key;
-    const unsigned long long b1 = warp_max_u64(k1);
-    const unsigned long long k2 = (b1 && k1 == b1) ? (1ull << 32) | best.xs : 0ull;
-    const unsigned long long b2 = warp_max_u64(k2);
+    SubPairBest best{0ull, 0};
+    sub_pair_lane(blob, plist, poff, slist, soff, K, r0, lin, split_tab, base_s == n_static, mode, lane, best);
+    // the warp's best (score, prefix word); lanes that share it hold the same prefix.  Then the first suffix of that
+    // prefix's class that reaches the score: the whole warp walks the class once more.
+    const unsigned long long b1 = warp_max_u64(best.key);
     if (b1 == 0) {
       sub_batch_write_empty(out, i, GPA_OK, lane);
-    } else if (k2 == b2 && k2) {  // exactly one lane: every pair was visited by one lane
-      uint2 *dst = reinterpret_cast<uint2 *>(out + i);
-      dst[0] = make_uint2(__byte_perm(sub_pair_prefix(best), 0u, 0x0123), __byte_perm(best.xs, 0u, 0x0123));
-      dst[1] = make_uint2(0u, 0u);
-      dst[2] = make_uint2((uint32_t)sub_pair_score(best), (uint32_t)(uint16_t)d.size | ((uint32_t)(uint16_t)GPA_OK << 16));
+    } else {
+      const unsigned holders = __ballot_sync(0xffffffffu, best.key == b1);
+      const int pe = __shfl_sync(0xffffffffu, best.pe, __ffs(holders) - 1);
+      const uint32_t xp = (uint32_t)b1;
+      const int score = (int)(b1 >> 32) - 1;
+      const int tp = (int)__dp4a(xp, 0x01010101u, 0u);  // sum of the prefix counts
+      const uint32_t first = __reduce_min_sync(0xffffffffu, sub_pair_find_suffix(blob, pe, slist, soff[K - tp], soff[K - tp + 1], r0, lin, score, lane));
+      if (first == 0xFFFFFFFFu) {  // cannot happen: some lane measured `score` on this very class
+        sub_batch_write_empty(out, i, GPA_ERR_CUDA, lane);
+      } else if (lane == 0) {
+        const uint32_t xs = blob[kSubPairCompOff / 4 + slist[first]];
+        uint2 *dst = reinterpret_cast<uint2 *>(out + i);
+        dst[0] = make_uint2(__byte_perm(xp, 0u, 0x0123), __byte_perm(xs, 0u, 0x0123));
+        dst[1] = make_uint2(0u, 0u);
+        dst[2] = make_uint2((uint32_t)score, (uint32_t)(uint16_t)d.size | ((uint32_t)(uint16_t)GPA_OK << 16));
+      }
     }
     __syncwarp();  // the lists are rewritten for the warp's next request
   }

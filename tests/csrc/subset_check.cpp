@@ -160,29 +160,28 @@ static void batch_pair_search(const uint16_t *w, const uint8_t *free_in, const u
   const bool ident = ns == sub_half_start(K + 1);
   uint32_t lin_max = 0;
   for (int g = 4; g < 8; g++) lin_max = lin[g] > lin_max ? lin[g] : lin_max;
-  const bool small = sub_pair_small(K, blob[kSubPairMetaOff / 4], lin_max);
+  const int mode = sub_pair_mode(K, blob[kSubPairMetaOff / 4], lin_max, n_req);
   SubPairBest lanes[32];
-  unsigned long long b1 = 0, b2 = 0;
-  for (int lane = 0; lane < 32; lane++) {
-    lanes[lane] = SubPairBest{0ull, 0u};
-    sub_pair_lane(blob.data(), plist, poff, slist, soff, K, r0, lin, split_tab, ident, small, lane, lanes[lane]);
-    if (lanes[lane].key > b1) b1 = lanes[lane].key;
-  }
   int win = -1;
   for (int lane = 0; lane < 32; lane++) {
-    const unsigned long long k1 = lanes[lane].key;
-    const unsigned long long k2 = (b1 && k1 == b1) ? (1ull << 32) | lanes[lane].xs : 0ull;
-    if (k2 > b2) {
-      b2 = k2;
-      win = lane;
-    }
+    lanes[lane] = SubPairBest{0ull, 0};
+    sub_pair_lane(blob.data(), plist, poff, slist, soff, K, r0, lin, split_tab, ident, mode, lane, lanes[lane]);
+    if (lanes[lane].key > (win < 0 ? 0ull : lanes[win].key)) win = lane;  // the warp's shuffle max; equal keys hold the same prefix
   }
   for (int g = 0; g < 16; g++) take[g] = 0;
   *score = -1;
   if (win >= 0) {
+    const uint32_t xp = sub_pair_prefix(lanes[win]);
+    const int t = (int)((xp >> 24) + ((xp >> 16) & 0xFF) + ((xp >> 8) & 0xFF) + (xp & 0xFF));
+    uint32_t first = 0xFFFFFFFFu;
+    for (int lane = 0; lane < 32; lane++) {
+      const uint32_t f = sub_pair_find_suffix(blob.data(), lanes[win].pe, slist, soff[K - t], soff[K - t + 1], r0, lin, sub_pair_score(lanes[win]), lane);
+      first = f < first ? f : first;
+    }
+    const uint32_t xs = blob[kSubPairCompOff / 4 + slist[first]];
     for (int g = 0; g < 4; g++) {
-      take[g] = (uint8_t)(sub_pair_prefix(lanes[win]) >> (8 * (3 - g)));
-      take[4 + g] = (uint8_t)(lanes[win].xs >> (8 * (3 - g)));
+      take[g] = (uint8_t)(xp >> (8 * (3 - g)));
+      take[4 + g] = (uint8_t)(xs >> (8 * (3 - g)));
     }
     *score = sub_pair_score(lanes[win]);
   }
