@@ -107,8 +107,14 @@ struct gpa_ctx {
   gpa_subset_result *d_sub_out = nullptr;
   size_t sub_batch_cap = 0;
   uint32_t *d_sub_pair = nullptr;  // half-vector table of the replica-set batch kernel on nodes of up to 8 GPUs (sub_pair_fill)
-  unsigned int *d_sub_next = nullptr;  // request counter the warps of that kernel draw from; zeroed on the stream before each launch
-  bool sub_pair_valid = false;     // false after every topology / order change
+  // request counters the warps of that kernel draw from: one per launch in flight (kSubSlots of them, each guarded by an
+  // event; a launch that finds its slot still busy, or is being captured into a graph, strides instead)
+  static constexpr int kSubSlots = 8;
+  unsigned int *d_sub_next = nullptr;
+  cudaEvent_t sub_ev[kSubSlots] = {};
+  bool sub_ev_used[kSubSlots] = {};
+  int sub_slot = 0;
+  SubsetBatchTopo sub_bt;          // label-space weights of the replica-set batch kernels, per topology / order
   bool sub_dfs_only = false;       // GPA_SUBSET_WALK=dfs: the depth-first batch kernel on every node (A/B measurements)
   int part_table_nt = 0;             // node size the table was built for, 0 = none
   bool table_attr_set[3] = {false, false, false};
@@ -315,9 +321,40 @@ int ensure_partition_table(gpa_ctx *ctx, int nt) {
 // (Re)builds what the fast batch path needs from the installed topology and device order: the
 // label <-> NVML index maps and the score table over all label masks.  The path is available
 // for nodes of up to kFastMaxTopo devices whose link counts are symmetric.
+// Label-space tables of the replica-set batch kernels (subset_kernels.cuh): the weights every launch passes by value and,
+// on nodes of up to 8 GPUs, the half-vector table of the two-halves walk.  Called with the device drained.
+int rebuild_subset_tables(gpa_ctx *ctx) {
+  const Topology &T = ctx->topo;
+  SubsetBatchTopo &bt = ctx->sub_bt;
+  memset(&bt, 0, sizeof bt);
+  bt.nt = T.n;
+  if (T.n > kSubGroups) return GPA_OK;
+  for (int a = 0; a < T.n; a++) {
+    const int da = (int)T.order.size() == T.n ? T.order[a] : a;
+    for (int b = 0; b < T.n; b++) {
+      const int db = (int)T.order.size() == T.n ? T.order[b] : b;
+      if (a < b) bt.w[a * kSubGroups + b] = T.wq[da * T.n + db];
+      if (a != b && T.asym[da * T.n + db]) bt.asym_row[a] |= (uint16_t)(1u << b);
+    }
+  }
+  if (T.n > 8) return GPA_OK;
+  std::vector<uint32_t> blob(kSubPairBlobBytes / 4);
+  sub_pair_fill(bt.w, blob.data());
+  if (!ctx->d_sub_pair) CUDA_TRY(ctx, cudaMalloc(&ctx->d_sub_pair, kSubPairBlobBytes));
+  if (!ctx->d_sub_next) {
+    CUDA_TRY(ctx, cudaMalloc(&ctx->d_sub_next, gpa_ctx::kSubSlots * sizeof(unsigned int)));
+    for (auto &ev : ctx->sub_ev) CUDA_TRY(ctx, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  }
+  CUDA_TRY(ctx, cudaMemcpy(ctx->d_sub_pair, blob.data(), kSubPairBlobBytes, cudaMemcpyHostToDevice));
+  return GPA_OK;
+}
+
 int rebuild_fast(gpa_ctx *ctx) {
   Topology &T = ctx->topo;
-  ctx->sub_pair_valid = false;
+  {
+    const int rc = rebuild_subset_tables(ctx);
+    if (rc != GPA_OK) return rc;
+  }
   if (ctx->d_sfull) {
     cudaFree(ctx->d_sfull);
     ctx->d_sfull = nullptr;
@@ -635,6 +672,8 @@ void gpa_destroy(gpa_ctx *ctx) {
   if (ctx->d_sub_out) cudaFree(ctx->d_sub_out);
   if (ctx->d_sub_pair) cudaFree(ctx->d_sub_pair);
   if (ctx->d_sub_next) cudaFree(ctx->d_sub_next);
+  for (auto &ev : ctx->sub_ev)
+    if (ev) cudaEventDestroy(ev);
   if (ctx->d_reqs) cudaFree(ctx->d_reqs);
   if (ctx->d_out) cudaFree(ctx->d_out);
   if (ctx->h_reqs) cudaFreeHost(ctx->h_reqs);

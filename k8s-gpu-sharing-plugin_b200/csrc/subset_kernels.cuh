@@ -325,11 +325,13 @@ __global__ void __launch_bounds__(kSubThreads, 4) subset_batch_pair_kernel(const
   const uint32_t wmax = blob[kSubPairMetaOff / 4];
   // Requests cost between a few hundred and several thousand instructions (1 to 6 435 count vectors), so the warps
   // draw them kSubDraw at a time from a counter (*g_next, zeroed by the host before the launch) instead of striding:
-  // no SM waits for its slowest warp's fixed share.
-  for (;;) {
-    unsigned int first = 0;
-    if (lane == 0) first = atomicAdd(g_next, (unsigned int)kSubDraw);
-    first = __shfl_sync(0xffffffffu, first, 0);
+  // no SM waits for its slowest warp's fixed share.  Without a counter (g_next == nullptr) they stride.
+  for (unsigned int turn = 0;; turn++) {
+    unsigned int first = ((unsigned int)(blockIdx.x * kSubBatchWarps + warp) + turn * (unsigned int)(gridDim.x * kSubBatchWarps)) * kSubDraw;
+    if (g_next) {
+      if (lane == 0) first = atomicAdd(g_next, (unsigned int)kSubDraw);
+      first = __shfl_sync(0xffffffffu, first, 0);
+    }
     if (first >= (unsigned int)count) break;
     const unsigned int last = first + kSubDraw < (unsigned int)count ? first + kSubDraw : (unsigned int)count;
   for (long long i = first; i < last; i++) {

@@ -276,3 +276,37 @@ def test_batch_two_halves_walk_equals_depth_first_walk_and_single_call(ctx):
         assert (a["status"] == 0).all() and int(a["score"].max()) > 124 * 541 * 2
     finally:
         dfs.close()
+
+
+def test_batch_launches_in_flight_on_several_streams_and_in_a_graph(ctx):
+    """every launch of the two-halves kernel draws its requests from a counter of its own; with more launches in flight than
+    there are counters, or while a stream is being captured, the warps stride instead.  Same answers every time."""
+    import torch
+    ctx.set_topology_links(syn.topo_two_sockets(8))
+    ctx.set_device_order(syn.sorted_positions(syn.node_uuids(8, seed=1)))
+    reqs = syn.random_subset_batch(8, 16, 1 << 17, seed=41)
+    want = ctx.subset_batch(reqs)
+    d_in = torch.from_numpy(reqs.view(np.uint8).reshape(-1, 48)).cuda()
+    streams = [torch.cuda.Stream() for _ in range(3)]
+    outs = [torch.zeros((len(reqs), 24), dtype=torch.uint8, device="cuda") for _ in range(24)]
+    torch.cuda.synchronize()
+    for i, o in enumerate(outs):                                  # 24 launches, no synchronisation in between
+        ctx.subset_batch_device(d_in.data_ptr(), len(reqs), o.data_ptr(), stream=streams[i % 3].cuda_stream)
+    torch.cuda.synchronize()
+    for o in outs:
+        got = o.cpu().numpy().view(syn.SUBSET_RES_DTYPE).reshape(-1)
+        for field in ("status", "n_out", "score", "take"):
+            assert (got[field] == want[field]).all(), field
+    # captured into a CUDA graph and replayed
+    out_g = torch.zeros((len(reqs), 24), dtype=torch.uint8, device="cuda")
+    s = torch.cuda.Stream()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=s):
+        ctx.subset_batch_device(d_in.data_ptr(), len(reqs), out_g.data_ptr(), stream=s.cuda_stream)
+    for _ in range(2):
+        out_g.zero_()
+        g.replay()
+        torch.cuda.synchronize()
+        got = out_g.cpu().numpy().view(syn.SUBSET_RES_DTYPE).reshape(-1)
+        for field in ("status", "n_out", "score", "take"):
+            assert (got[field] == want[field]).all(), field
