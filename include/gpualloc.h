@@ -310,7 +310,10 @@ int gpa_subset_besteffort(gpa_ctx *ctx, const int32_t *phys, int n_avail, const 
  * Index g of the arrays is the LABEL of a GPU in the node order given to gpa_set_device_order() (the plugin's sorted
  * id order), i.e. the request is gpa_subset_besteffort() over positions grouped by label.  The answer is how many
  * FURTHER replicas to take from each GPU; the first candidate of the winning class takes the first `take[g]` free
- * replicas of GPU g in id order next to the must-include ones.  One warp per request, one launch per call.
+ * replicas of GPU g in id order next to the must-include ones.  One warp per request, one launch per call (nodes of
+ * up to 8 GPUs: pairs of precomputed half-vectors; GPA_SUBSET_WALK=dfs in the environment at gpa_create()
+ * selects the depth-first walk that larger nodes use, for A/B measurements).  The _device form may be captured into a
+ * CUDA graph and may be in flight on several streams at once.
  * Per-record status: GPA_OK, GPA_ERR_INVALID (replicas of a GPU the node does not have), GPA_ERR_ASYMMETRIC,
  * GPA_ERR_TOO_LARGE (size > GPA_SUBSET_MAX_SIZE, size - sum(must) > GPA_SUBSET_BATCH_MAX_EXTRA, or more than
  * GPA_SUBSET_BATCH_MAX_CLASSES count vectors by the estimate C(K + g - 1, g - 1), K = size - sum(must), g = GPUs with free
