@@ -103,9 +103,6 @@ struct gpa_ctx {
   uint64_t *d_sub_binom = nullptr;   // C(n, j) table of the literal replica-set kernel, built on first use
   std::vector<uint64_t> sub_binom;
   SubsetPlan sub_plan;               // plan of the last gpa_subset_besteffort() (kept for its buffers)
-  gpa_subset_request *d_sub_reqs = nullptr;  // staging of gpa_subset_batch()
-  gpa_subset_result *d_sub_out = nullptr;
-  size_t sub_batch_cap = 0;
   uint32_t *d_sub_pair = nullptr;  // half-vector table of the replica-set batch kernel on nodes of up to 8 GPUs (sub_pair_fill)
   // request counters the warps of that kernel draw from: one per launch in flight (kSubSlots of them, each guarded by an
   // event; a launch that finds its slot still busy, or is being captured into a graph, strides instead)
@@ -668,8 +665,6 @@ void gpa_destroy(gpa_ctx *ctx) {
   if (ctx->d_ans) cudaFree(ctx->d_ans);
   if (ctx->d_ans8) cudaFree(ctx->d_ans8);
   if (ctx->d_sub_binom) cudaFree(ctx->d_sub_binom);
-  if (ctx->d_sub_reqs) cudaFree(ctx->d_sub_reqs);
-  if (ctx->d_sub_out) cudaFree(ctx->d_sub_out);
   if (ctx->d_sub_pair) cudaFree(ctx->d_sub_pair);
   if (ctx->d_sub_next) cudaFree(ctx->d_sub_next);
   for (auto &ev : ctx->sub_ev)
