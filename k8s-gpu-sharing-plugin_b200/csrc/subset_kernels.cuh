@@ -300,6 +300,7 @@ __global__ void __launch_bounds__(kSubThreads, 4) subset_batch_pair_kernel(const
                                                                            gpa_subset_result *__restrict__ out) {
   __shared__ __align__(16) uint32_t blob[kSubPairBlobBytes / 4];
   __shared__ uint32_t split_tab[32];
+  __shared__ uint16_t ident_list[kSubListLen], start_tab[kSubHalfMaxK + 2];  // the lists of a request no free count binds
   __shared__ uint16_t plist_all[kSubBatchWarps][kSubListLen], slist_all[kSubBatchWarps][kSubListLen];
   __shared__ uint16_t off_all[kSubBatchWarps][2 * (kSubHalfMaxK + 2)];
   __shared__ uint32_t lin_all[kSubBatchWarps][8];
@@ -315,9 +316,11 @@ __global__ void __launch_bounds__(kSubThreads, 4) subset_batch_pair_kernel(const
   for (int i = tid; i < kSubGroups * kSubGroups; i += kSubThreads) w[i] = t.w[i];
   if (tid < kSubGroups) asym_row[tid] = t.asym_row[tid];
   if (tid < 32) split_tab[tid] = sub_pair_split_entry(tid);
+  for (int i = tid; i < kSubListLen; i += kSubThreads) ident_list[i] = (uint16_t)i;
+  if (tid < kSubHalfMaxK + 2) start_tab[tid] = (uint16_t)sub_half_start(tid);
   __syncthreads();
-  uint16_t *plist = plist_all[warp], *slist = slist_all[warp];
-  uint16_t *poff = off_all[warp], *soff = off_all[warp] + kSubHalfMaxK + 2;
+  uint16_t *const my_plist = plist_all[warp], *const my_slist = slist_all[warp];
+  uint16_t *const my_poff = off_all[warp], *const my_soff = off_all[warp] + kSubHalfMaxK + 2;
   uint32_t *lin = lin_all[warp];
   const int my_start = sub_half_start(lane < kSubHalfMaxK + 2 ? lane : 0);  // where class `lane` starts in the table
   const uint32_t lt = (1u << lane) - 1u;
@@ -376,28 +379,40 @@ __global__ void __launch_bounds__(kSubThreads, 4) subset_batch_pair_kernel(const
       lin_max = __shfl_sync(0xffffffffu, lin_max, 4);
     }
     const int mode = sub_pair_mode(K, wmax, lin_max, d.n_req);
-    // the lists: compositions of classes 0..K that fit, for each half, and where every class starts in them
+    // the lists: compositions of classes 0..K that fit, for each half, and where every class starts in them.  Where every
+    // GPU has K replicas free (deep replica sets, most requests) nothing is dropped and the table itself is the list.
     const int n_static = sub_half_start(K + 1);
-    int base_p = 0, base_s = 0;
-    for (int i0 = 0; i0 < n_static; i0 += 32) {
-      const int e = i0 + lane;
-      const bool in = e < n_static;
-      const uint32_t x = in ? blob[kSubPairCompOff / 4 + e] : 0u;
-      const bool okp = in && sub_half_fits(x, fpack_p), oks = in && sub_half_fits(x, fpack_s);
-      const unsigned bp = __ballot_sync(0xffffffffu, okp), bsf = __ballot_sync(0xffffffffu, oks);
-      if (okp) plist[base_p + __popc(bp & lt)] = (uint16_t)e;
-      if (oks) slist[base_s + __popc(bsf & lt)] = (uint16_t)e;
-      if (lane <= K && my_start >= i0 && my_start < i0 + 32) {
-        const uint32_t before = (1u << (my_start - i0)) - 1u;
-        poff[lane] = (uint16_t)(base_p + __popc(bp & before));
-        soff[lane] = (uint16_t)(base_s + __popc(bsf & before));
+    const uint32_t all_k = (uint32_t)K * 0x01010101u;
+    const bool whole = fpack_p == all_k && fpack_s == all_k;
+    const uint16_t *plist = ident_list, *slist = ident_list, *poff = start_tab, *soff = start_tab;
+    int base_s = n_static;
+    if (!whole) {
+      plist = my_plist;
+      slist = my_slist;
+      poff = my_poff;
+      soff = my_soff;
+      int base_p = 0;
+      base_s = 0;
+      for (int i0 = 0; i0 < n_static; i0 += 32) {
+        const int e = i0 + lane;
+        const bool in = e < n_static;
+        const uint32_t x = in ? blob[kSubPairCompOff / 4 + e] : 0u;
+        const bool okp = in && sub_half_fits(x, fpack_p), oks = in && sub_half_fits(x, fpack_s);
+        const unsigned bp = __ballot_sync(0xffffffffu, okp), bsf = __ballot_sync(0xffffffffu, oks);
+        if (okp) my_plist[base_p + __popc(bp & lt)] = (uint16_t)e;
+        if (oks) my_slist[base_s + __popc(bsf & lt)] = (uint16_t)e;
+        if (lane <= K && my_start >= i0 && my_start < i0 + 32) {
+          const uint32_t before = (1u << (my_start - i0)) - 1u;
+          my_poff[lane] = (uint16_t)(base_p + __popc(bp & before));
+          my_soff[lane] = (uint16_t)(base_s + __popc(bsf & before));
+        }
+        base_p += __popc(bp);
+        base_s += __popc(bsf);
       }
-      base_p += __popc(bp);
-      base_s += __popc(bsf);
-    }
-    if (lane == 0) {
-      poff[K + 1] = (uint16_t)base_p;
-      soff[K + 1] = (uint16_t)base_s;
+      if (lane == 0) {
+        my_poff[K + 1] = (uint16_t)base_p;
+        my_soff[K + 1] = (uint16_t)base_s;
+      }
     }
     __syncwarp();
     SubPairBest best{0ull, 0};
