@@ -294,7 +294,7 @@ __device__ __noinline__ void sub_batch_dfs_call(const SubBatchDecoded &d, uint8_
   sub_batch_dfs<G>(d, f, r, cap, exact, w, out, i, lane);
 }
 
-__global__ void __launch_bounds__(kSubThreads, 4) subset_batch_pair_kernel(const gpa_subset_request *__restrict__ reqs, int count,
+__global__ void __launch_bounds__(kSubThreads, 5) subset_batch_pair_kernel(const gpa_subset_request *__restrict__ reqs, int count,
                                                                            const SubsetBatchTopo t, const uint4 *__restrict__ g_blob,
                                                                            unsigned int *__restrict__ g_next,
                                                                            gpa_subset_result *__restrict__ out) {
