@@ -422,9 +422,10 @@ GPA_HD SubPairPrefix sub_pair_prefix_terms(const uint32_t *blob, int pe, uint32_
   return t;
 }
 
+// what the suffix adds to the prefix's base: S + xs . (L + lin)
 template <bool kFull>
-GPA_HD int sub_pair_score_of(const SubPairPrefix &t, const SubWord2 &rec) {
-  uint32_t sc = sub_dp2a_lo(t.q67lo, rec.y, sub_dp2a_hi(t.q45lo, rec.y, t.base + rec.x));
+GPA_HD int sub_pair_gain(const SubPairPrefix &t, const SubWord2 &rec) {
+  uint32_t sc = sub_dp2a_lo(t.q67lo, rec.y, sub_dp2a_hi(t.q45lo, rec.y, rec.x));
   if (kFull) sc += sub_dp2a_lo(t.q67hi, rec.y, sub_dp2a_hi(t.q45hi, rec.y, 0u)) << 16;
   return (int)sc;
 }
@@ -437,19 +438,22 @@ GPA_HD int sub_pair_item(const uint32_t *blob, int pe, const uint16_t *slist, in
                          const uint32_t *lin) {
   const SubWord2 *suf = reinterpret_cast<const SubWord2 *>(blob + kSubPairSufOff / 4);
   const SubPairPrefix t = sub_pair_prefix_terms<kMode>(blob, pe, r0, lin);
-  int is = -1;
+  int gain = -1;
   int s = s_first;
-  for (; s + step < s_end; s += 2 * step) {  // two a turn: half the loop control, two loads in flight
+  for (; s + 3 * step < s_end; s += 4 * step) {  // four a turn: a quarter of the loop control, four loads in flight
     const SubWord2 a = suf[kIdent ? s : (int)slist[s]], b = suf[kIdent ? s + step : (int)slist[s + step]];
-    const int sa = sub_pair_score_of<kMode == 2>(t, a), sb = sub_pair_score_of<kMode == 2>(t, b);
-    is = sa > is ? sa : is;
-    is = sb > is ? sb : is;
+    const SubWord2 c = suf[kIdent ? s + 2 * step : (int)slist[s + 2 * step]], d = suf[kIdent ? s + 3 * step : (int)slist[s + 3 * step]];
+    const int ga = sub_pair_gain<kMode == 2>(t, a), gb = sub_pair_gain<kMode == 2>(t, b);
+    const int gc = sub_pair_gain<kMode == 2>(t, c), gd = sub_pair_gain<kMode == 2>(t, d);
+    const int m1 = ga > gb ? ga : gb, m2 = gc > gd ? gc : gd;
+    const int m3 = m1 > m2 ? m1 : m2;
+    gain = m3 > gain ? m3 : gain;
   }
-  if (s < s_end) {
-    const int sa = sub_pair_score_of<kMode == 2>(t, suf[kIdent ? s : (int)slist[s]]);
-    is = sa > is ? sa : is;
+  for (; s < s_end; s += step) {
+    const int ga = sub_pair_gain<kMode == 2>(t, suf[kIdent ? s : (int)slist[s]]);
+    gain = ga > gain ? ga : gain;
   }
-  return is;
+  return gain < 0 ? -1 : (int)t.base + gain;  // the base is the same for every pair of the item
 }
 
 // The winning prefix once more, by the whole warp: the first suffix of its class (list order = descending, so the one the
@@ -460,7 +464,7 @@ GPA_HD uint32_t sub_pair_find_suffix(const uint32_t *blob, int pe, const uint16_
   const SubWord2 *suf = reinterpret_cast<const SubWord2 *>(blob + kSubPairSufOff / 4);
   const SubPairPrefix t = sub_pair_prefix_terms<2>(blob, pe, r0, lin);
   for (int s = s_begin + lane; s < s_end; s += 32)
-    if (sub_pair_score_of<true>(t, suf[slist[s]]) == target) return (uint32_t)s;
+    if ((int)t.base + sub_pair_gain<true>(t, suf[slist[s]]) == target) return (uint32_t)s;
   return 0xFFFFFFFFu;
 }
 
