@@ -43,7 +43,7 @@ constexpr size_t kTabSmallTables = 256 * sizeof(unsigned long long) + 256 * size
 constexpr size_t masks_smem_bytes(uint32_t n_entries) { return kTabSmallTables + table_ans_bytes(n_entries); }
 constexpr size_t table_smem_bytes(uint32_t n_entries, int tile_records, int stages) {
   return (size_t)stages * tile_records * sizeof(gpa_request)  // request ring (first: 128-byte aligned)
-         + kTabSmallTables + table_ans_bytes(n_entries) + (size_t)stages * sizeof(unsigned long long);  // + the stages' mbarriers
+         + kTabSmallTables + table_ans_bytes(n_entries) + (size_t)2 * stages * sizeof(unsigned long long);  // + the stages' mbarriers (full, empty)
 }
 
 __device__ __forceinline__ void stage_tables(const FastTopo &ft, unsigned long long *s_dev, uint16_t *s_tern, uint8_t *s_ans, int tid,
@@ -89,6 +89,14 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, uint32_t pari
       "r"(parity)
       : "memory");
 }
+// arrive, and say how many arrivals the phase was still waiting for BEFORE this one (1 = this one completed it)
+__device__ __forceinline__ uint32_t mbar_arrive_pending(unsigned long long *bar) {
+  unsigned long long state;
+  uint32_t pending;
+  asm volatile("mbarrier.arrive.shared::cta.b64 %0, [%1];" : "=l"(state) : "r"(smem_addr(bar)) : "memory");
+  asm volatile("mbarrier.pending_count.b64 %0, %1;" : "=r"(pending) : "l"(state));
+  return pending;
+}
 __device__ __forceinline__ void bulk_load(void *smem_dst, const void *gmem_src, uint32_t bytes, unsigned long long *bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_addr(smem_dst)),
                "l"(gmem_src), "r"(bytes), "r"(smem_addr(bar))
@@ -125,6 +133,7 @@ __global__ void __launch_bounds__(kTabThreads, kTabThreads >= 1024 ? 1 : 2) best
   uint16_t *s_tern = reinterpret_cast<uint16_t *>(s_dev + 256);
   uint8_t *s_ans = reinterpret_cast<uint8_t *>(s_tern + 256);
   unsigned long long *full = reinterpret_cast<unsigned long long *>(s_ans + table_ans_bytes(ft.ans_entries));
+  unsigned long long *empty = full + kTabStages;  // one arrival per warp: "my lanes hold their records of this stage"
   __shared__ uint32_t s_marked[kTabFlagWords];
   __shared__ uint2 s_keep[9];  // s_keep[n] = byte mask of the first n of 8 bytes, as two words
 
@@ -142,7 +151,10 @@ __global__ void __launch_bounds__(kTabThreads, kTabThreads >= 1024 ? 1 : 2) best
   if (tid < kTabFlagWords) s_marked[tid] = 0;
   if (tid < 9) s_keep[tid] = make_uint2(tid >= 4 ? 0xFFFFFFFFu : (1u << (8 * tid)) - 1u, tid <= 4 ? 0u : (tid >= 8 ? 0xFFFFFFFFu : (1u << (8 * (tid - 4))) - 1u));
   if (tid == 0) {
-    for (int s = 0; s < kTabStages; s++) mbar_init(&full[s], 1);
+    for (int s = 0; s < kTabStages; s++) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], kTabThreads / 32);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     // the first tiles are on their way while the CTA stages its tables
     for (int i = 0; i < kTabStages && i < my_tiles; i++) issue(i, i);
@@ -178,8 +190,14 @@ __global__ void __launch_bounds__(kTabThreads, kTabThreads >= 1024 ? 1 : 2) best
         hd[q] = rec[2];
       }
     }
-    __syncthreads();  // every lane has its records: the stage can be refilled
-    if (tid == 0 && i + kTabStages < my_tiles) issue(i + kTabStages, s);
+    // The warps do not wait for each other here: each says "my lanes hold their records" on the stage's second barrier,
+    // and the warp whose arrival is the last one refills the stage.  A block-wide barrier in this place makes all 32 warps
+    // start every tile together, and then queue for the same pipes together.
+    __syncwarp();
+    if ((tid & 31) == 0 && mbar_arrive_pending(&empty[s]) == 1 && i + kTabStages < my_tiles) {
+      mbar_wait(&empty[s], parity);  // complete already: taken for its acquire of the other warps' arrivals
+      issue(i + kTabStages, s);
+    }
     if (++s == kTabStages) {
       s = 0;
       parity ^= 1u;
