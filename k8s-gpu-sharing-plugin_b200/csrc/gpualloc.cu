@@ -251,12 +251,12 @@ int launch_table(gpa_ctx *ctx, const void *d_reqs, int count, int max_avail, int
     if (n_cap > GPA_BATCH_MAX_AVAILABLE) n_cap = GPA_BATCH_MAX_AVAILABLE;
     const int intended = mode_flags & GPA_MODE_INTENDED;
     // One 1024-thread CTA per SM, TWO records per thread and tile (2 048 records = 64 KB), a 2-stage ring.  Measured on
-    // B200 (4 Mi requests, event-timed median of the step): one record per thread with 3 / 4 / 5 stages 41.4 / 45.4 / 45.5 us,
-    // two 512-thread CTAs per SM with 3 stages each 41.4 us, this shape 39.5 us - neither a deeper ring nor decoupling the
-    // CTAs' barriers buys anything; halving the per-tile overhead and giving each lane two independent records does.
-    // Fewer, fatter threads on the same tile: 512 x 4 records (100 registers) 39.2 us median with 4 steps in 10 at 37.3,
-    // 256 x 8 records 45.4 us.  512 x 4 is 2.5 % faster on this workload and leaves half the warps for the records the
-    // kernel answers by search afterwards, so it is not the shape shipped.
+    // B200 (4 Mi requests, event-timed median of the kernel).  With a block-wide barrier per tile: one record per thread
+    // with 3 / 4 / 5 stages 41.4 / 45.4 / 45.5 us, two 512-thread CTAs per SM with 3 stages each 41.4 us, this shape
+    // 39.4 us, 512 threads x 4 records 39.2 us, 256 x 8 records 45.4 us.  With the warps releasing the stages one by one
+    // (table_kernels.cuh) the shape stops mattering: 1024 x 2, 1024 x 1 with 3 or 4 stages and 512 x 2 with 4 stages all
+    // land on 37.2-37.4 us (512 x 4: 39.1) - 201 MB of requests and answers at 5.4 TB/s, against ~33 us for a plain copy
+    // of the same bytes at the measured 6.55 TB/s plus the launch's ramp.
     int rc = launch_table_records<1024, 2, 2>(ctx, d_reqs, count, n_cap, intended, d_out, stream, 0);
     if (rc != GPA_OK) return rc;
   }
