@@ -380,6 +380,37 @@ GPA_HD uint32_t sub_dp2a_hi(uint32_t a, uint32_t b, uint32_t c) {  // c + a.lo16
 #endif
 }
 
+// One or two further replicas (what most containers ask for): no lists, no pairs - candidate c of at most 36 is "one more
+// of GPU g and one more of GPU h", g <= h (for K = 1: of GPU g alone), worth R0 + lin_g + lin_h + w[g][h].  fpack_p / fpack_s:
+// free counts per byte, GPU 0 / 4 in the highest byte.  Returns false if the free counts do not allow the candidate;
+// *lex = its count vector as prefix word << 32 | suffix word (the tie-break order: larger first).
+GPA_HD bool sub_small_candidate(int c, int K, uint32_t fpack_p, uint32_t fpack_s, uint32_t r0, const uint32_t *lin, const uint16_t *w,
+                                int *score, unsigned long long *lex) {
+  int g = c, h = c;
+  if (K == 2) {  // c = 0..35 -> (g, h), g <= h, row by row: g = 0 has 8 candidates, g = 1 seven, ...
+    g = 0;
+    int left = c;
+    while (left >= 8 - g) {
+      left -= 8 - g;
+      g++;
+    }
+    h = g + left;
+  }
+  const unsigned long long fpack = ((unsigned long long)fpack_p << 32) | fpack_s;
+  const int fg = (int)((fpack >> (8 * (7 - g))) & 0xFFu), fh = (int)((fpack >> (8 * (7 - h))) & 0xFFu);
+  if (K == 1) {
+    if (fg < 1) return false;
+    *score = (int)(r0 + lin[g]);
+    *lex = 1ull << (8 * (7 - g));
+    return true;
+  }
+  if (g == h ? fg < 2 : (fg < 1 || fh < 1)) return false;
+  *score = (int)(r0 + lin[g] + lin[h] + (g < h ? (uint32_t)w[g * kSubGroups + h] : 0u));
+  *lex = (1ull << (8 * (7 - g))) + (1ull << (8 * (7 - h)));
+  return true;
+}
+GPA_HD int sub_small_candidates(int K) { return K == 1 ? 8 : 36; }
+
 // A lane's running best: (score + 1) << 32 | prefix word, and which composition that prefix is.  key 0 = nothing yet.
 // The suffix is not tracked: the warp finds it again for the one winning prefix (sub_pair_find_suffix).
 struct SubPairBest {

@@ -378,6 +378,33 @@ __global__ void __launch_bounds__(kSubThreads, 5) subset_batch_pair_kernel(const
       lin_max = max(lin_max, __shfl_xor_sync(0xffffffffu, lin_max, 2));
       lin_max = __shfl_sync(0xffffffffu, lin_max, 4);
     }
+    if (K == 1 || K == 2) {
+      // one or two further replicas: a lane per candidate (sub_small_candidate), max on (score, count vector)
+      __syncwarp();  // lin[] is read by every lane
+      int bs = -1;
+      unsigned long long bl = 0;
+      for (int c = lane; c < sub_small_candidates(K); c += 32) {
+        int sc;
+        unsigned long long lex;
+        if (!sub_small_candidate(c, K, fpack_p, fpack_s, r0, lin, w, &sc, &lex)) continue;
+        if (sc > bs || (sc == bs && lex > bl)) {
+          bs = sc;
+          bl = lex;
+        }
+      }
+      const int top = (int)__reduce_max_sync(0xffffffffu, (unsigned)(bs + 1)) - 1;
+      const unsigned long long lex = warp_max_u64(bs == top ? bl : 0ull);
+      if (top < 0) {
+        sub_batch_write_empty(out, i, GPA_OK, lane);
+      } else if (lane == 0) {
+        uint2 *dst = reinterpret_cast<uint2 *>(out + i);
+        dst[0] = make_uint2(__byte_perm((uint32_t)(lex >> 32), 0u, 0x0123), __byte_perm((uint32_t)lex, 0u, 0x0123));
+        dst[1] = make_uint2(0u, 0u);
+        dst[2] = make_uint2((uint32_t)top, (uint32_t)(uint16_t)d.size | ((uint32_t)(uint16_t)GPA_OK << 16));
+      }
+      __syncwarp();  // lin[] is rewritten for the warp's next request
+      continue;
+    }
     const int mode = sub_pair_mode(K, wmax, lin_max, d.n_req);
     // the lists: compositions of classes 0..K that fit, for each half, and where every class starts in them.  Where every
     // GPU has K replicas free (deep replica sets, most requests) nothing is dropped and the table itself is the list.

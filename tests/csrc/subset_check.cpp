@@ -143,6 +143,22 @@ static void batch_pair_search(const uint16_t *w, const uint8_t *free_in, const u
       if (h != g) lin[g] += (uint32_t)must[h] * w[(g < h ? g : h) * kSubGroups + (g < h ? h : g)];
     for (int h = g + 1; h < 8; h++) r0 += (uint32_t)must[g] * must[h] * w[g * kSubGroups + h];
   }
+  if (K == 1 || K == 2) {  // the kernel's short cut: a lane per candidate, max on (score, count vector)
+    int bs = -1;
+    unsigned long long bl = 0;
+    for (int c = 0; c < sub_small_candidates(K); c++) {
+      int sc;
+      unsigned long long lex;
+      if (!sub_small_candidate(c, K, fpack[0], fpack[1], r0, lin, w, &sc, &lex)) continue;
+      if (sc > bs || (sc == bs && lex > bl)) {
+        bs = sc;
+        bl = lex;
+      }
+    }
+    for (int g = 0; g < 16; g++) take[g] = g < 8 ? (uint8_t)(bl >> (8 * (7 - g))) : 0;
+    *score = bs;
+    return;
+  }
   uint16_t plist[kSubHalfEntries], slist[kSubHalfEntries], poff[kSubHalfMaxK + 2], soff[kSubHalfMaxK + 2];
   int np = 0, ns = 0;
   for (int t = 0; t <= K; t++) {
