@@ -156,14 +156,8 @@ __device__ __forceinline__ SubBatchDecoded sub_batch_decode(const gpa_subset_req
   d.my_r = lane < kSubGroups ? (int)((rw >> (8 * (lane & 3))) & 0xFFu) : 0;
   const unsigned present = __ballot_sync(0xffffffffu, d.my_f + d.my_r > 0);
   const unsigned has_free = __ballot_sync(0xffffffffu, d.my_f > 0);
-  int n_free = d.my_f, n_req = d.my_r;
-#pragma unroll
-  for (int o = 8; o > 0; o >>= 1) {  // lanes 16.. hold zeros
-    n_free += __shfl_xor_sync(0xffffffffu, n_free, o);
-    n_req += __shfl_xor_sync(0xffffffffu, n_req, o);
-  }
-  n_free = __shfl_sync(0xffffffffu, n_free, 0);
-  n_req = __shfl_sync(0xffffffffu, n_req, 0);
+  const int n_free = (int)__reduce_add_sync(0xffffffffu, (unsigned)d.my_f);  // lanes 16.. hold zeros
+  const int n_req = (int)__reduce_add_sync(0xffffffffu, (unsigned)d.my_r);
   d.n_req = n_req;
   d.K = d.size - n_req;
   d.status = GPA_OK;
