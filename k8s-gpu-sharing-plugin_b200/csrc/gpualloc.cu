@@ -338,14 +338,16 @@ int rebuild_subset_tables(gpa_ctx *ctx) {
     }
   }
   if (T.n > 8) return GPA_OK;
-  std::vector<uint32_t> blob(kSubPairBlobBytes / 4);
+  // the half-vector table of the two-halves walk, then the table of all count vectors of up to 4 further replicas
+  std::vector<uint32_t> blob((kSubPairBlobBytes + kSubFlatBytes) / 4);
   sub_pair_fill(bt.w, blob.data());
-  if (!ctx->d_sub_pair) CUDA_TRY(ctx, cudaMalloc(&ctx->d_sub_pair, kSubPairBlobBytes));
+  sub_flat_fill(bt.w, blob.data() + kSubPairBlobBytes / 4);
+  if (!ctx->d_sub_pair) CUDA_TRY(ctx, cudaMalloc(&ctx->d_sub_pair, kSubPairBlobBytes + kSubFlatBytes));
   if (!ctx->d_sub_next) {
     CUDA_TRY(ctx, cudaMalloc(&ctx->d_sub_next, gpa_ctx::kSubSlots * sizeof(unsigned int)));
     for (auto &ev : ctx->sub_ev) CUDA_TRY(ctx, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   }
-  CUDA_TRY(ctx, cudaMemcpy(ctx->d_sub_pair, blob.data(), kSubPairBlobBytes, cudaMemcpyHostToDevice));
+  CUDA_TRY(ctx, cudaMemcpy(ctx->d_sub_pair, blob.data(), kSubPairBlobBytes + kSubFlatBytes, cudaMemcpyHostToDevice));
   return GPA_OK;
 }
 

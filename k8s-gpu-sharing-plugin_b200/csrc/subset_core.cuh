@@ -380,36 +380,65 @@ GPA_HD uint32_t sub_dp2a_hi(uint32_t a, uint32_t b, uint32_t c) {  // c + a.lo16
 #endif
 }
 
-// One or two further replicas (what most containers ask for): no lists, no pairs - candidate c of at most 36 is "one more
-// of GPU g and one more of GPU h", g <= h (for K = 1: of GPU g alone), worth R0 + lin_g + lin_h + w[g][h].  fpack_p / fpack_s:
-// free counts per byte, GPU 0 / 4 in the highest byte.  Returns false if the free counts do not allow the candidate;
-// *lex = its count vector as prefix word << 32 | suffix word (the tie-break order: larger first).
-GPA_HD bool sub_small_candidate(int c, int K, uint32_t fpack_p, uint32_t fpack_s, uint32_t r0, const uint32_t *lin, const uint16_t *w,
-                                int *score, unsigned long long *lex) {
-  int g = c, h = c;
-  if (K == 2) {  // c = 0..35 -> (g, h), g <= h, row by row: g = 0 has 8 candidates, g = 1 seven, ...
-    g = 0;
-    int left = c;
-    while (left >= 8 - g) {
-      left -= 8 - g;
-      g++;
-    }
-    h = g + left;
-  }
-  const unsigned long long fpack = ((unsigned long long)fpack_p << 32) | fpack_s;
-  const int fg = (int)((fpack >> (8 * (7 - g))) & 0xFFu), fh = (int)((fpack >> (8 * (7 - h))) & 0xFFu);
-  if (K == 1) {
-    if (fg < 1) return false;
-    *score = (int)(r0 + lin[g]);
-    *lex = 1ull << (8 * (7 - g));
-    return true;
-  }
-  if (g == h ? fg < 2 : (fg < 1 || fh < 1)) return false;
-  *score = (int)(r0 + lin[g] + lin[h] + (g < h ? (uint32_t)w[g * kSubGroups + h] : 0u));
-  *lex = (1ull << (8 * (7 - g))) + (1ull << (8 * (7 - h)));
-  return true;
+// Up to kSubFlatMaxK further replicas (what most containers ask for): no lists, no pairs.  All count vectors over 8 GPUs
+// with sum <= 4 are 495; the node's table holds each one (prefix word, suffix word) and its score without must-include
+// replicas, class by class (sum) and in descending order inside a class, so a request is one pass over its class: does
+// the vector fit the free counts, table score + x . lin, maximum on (score, earliest entry).
+constexpr int kSubFlatMaxK = 4;
+constexpr int kSubFlatEntries = 495;  // C(4 + 8, 8)
+GPA_HD int sub_flat_start(int t) {    // vectors with sum < t = C(t + 7, 8)
+  return t <= 0 ? 0 : (t == 1 ? 1 : (t == 2 ? 9 : (t == 3 ? 45 : (t == 4 ? 165 : 495))));
 }
-GPA_HD int sub_small_candidates(int K) { return K == 1 ? 8 : 36; }
+// table layout (bytes): x {prefix word, suffix word} u32x2[495] | score u32[495] (+ 12 bytes of padding)
+constexpr int kSubFlatScoreOff = 8 * kSubFlatEntries;
+constexpr int kSubFlatBytes = 12 * kSubFlatEntries + 12;
+static_assert(kSubFlatBytes % 16 == 0, "uploaded and addressed in 16-byte units");
+
+inline void sub_flat_fill(const uint16_t *w, uint32_t *tab) {
+  int e = 0;
+  int x[8];
+  for (int t = 0; t <= kSubFlatMaxK; t++) {
+    // descending lexicographic order: odometer over x[0..6], x[7] takes the rest
+    for (int i = 0; i < 8; i++) x[i] = 0;
+    x[0] = t;
+    for (;;) {
+      uint32_t xp = 0, xs = 0, sc = 0;
+      for (int g = 0; g < 4; g++) {
+        xp |= (uint32_t)x[g] << (8 * (3 - g));
+        xs |= (uint32_t)x[4 + g] << (8 * (3 - g));
+      }
+      for (int g = 0; g < 8; g++)
+        for (int h = g + 1; h < 8; h++) sc += (uint32_t)(x[g] * x[h]) * w[g * kSubGroups + h];
+      tab[2 * e] = xp;
+      tab[2 * e + 1] = xs;
+      tab[kSubFlatScoreOff / 4 + e] = sc;
+      e++;
+      // next vector: move one unit from the last non-zero position before x[7] to its right neighbour, and pull
+      // everything right of that neighbour back to it
+      int p = 6;
+      while (p >= 0 && x[p] == 0) p--;
+      if (p < 0) break;  // everything sits in x[7]: the class is done
+      x[p]--;
+      const int carry = x[7] + 1;
+      x[7] = 0;
+      x[p + 1] += carry;
+    }
+  }
+  for (int i = 3 * kSubFlatEntries; i < kSubFlatBytes / 4; i++) tab[i] = 0;
+}
+
+// Entry e for a request: 0 if the free counts do not allow it, else (score + 1) << 32 | ~e (the maximum is the first best)
+GPA_HD unsigned long long sub_flat_key(const uint32_t *tab, int e, uint32_t fpack_p, uint32_t fpack_s, uint32_t r0, const uint32_t *lin,
+                                       bool has_req) {
+  const SubWord2 x = *reinterpret_cast<const SubWord2 *>(tab + 2 * e);
+  if (!sub_half_fits(x.x, fpack_p) || !sub_half_fits(x.y, fpack_s)) return 0ull;
+  uint32_t sc = tab[kSubFlatScoreOff / 4 + e];
+  if (has_req) {
+    sc += r0 + (x.x >> 24) * lin[0] + ((x.x >> 16) & 0xFFu) * lin[1] + ((x.x >> 8) & 0xFFu) * lin[2] + (x.x & 0xFFu) * lin[3] +
+          (x.y >> 24) * lin[4] + ((x.y >> 16) & 0xFFu) * lin[5] + ((x.y >> 8) & 0xFFu) * lin[6] + (x.y & 0xFFu) * lin[7];
+  }
+  return ((unsigned long long)(sc + 1u) << 32) | (uint32_t)~(uint32_t)e;
+}
 
 // A lane's running best: (score + 1) << 32 | prefix word, and which composition that prefix is.  key 0 = nothing yet.
 // The suffix is not tracked: the warp finds it again for the one winning prefix (sub_pair_find_suffix).

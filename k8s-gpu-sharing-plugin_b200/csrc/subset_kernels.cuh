@@ -290,6 +290,7 @@ __device__ __noinline__ void sub_batch_dfs_call(const SubBatchDecoded &d, uint8_
 
 __global__ void __launch_bounds__(kSubThreads, 5) subset_batch_pair_kernel(const gpa_subset_request *__restrict__ reqs, int count,
                                                                            const SubsetBatchTopo t, const uint4 *__restrict__ g_blob,
+                                                                           const uint32_t *__restrict__ g_flat,
                                                                            unsigned int *__restrict__ g_next,
                                                                            gpa_subset_result *__restrict__ out) {
   __shared__ __align__(16) uint32_t blob[kSubPairBlobBytes / 4];
@@ -372,29 +373,23 @@ __global__ void __launch_bounds__(kSubThreads, 5) subset_batch_pair_kernel(const
       lin_max = max(lin_max, __shfl_xor_sync(0xffffffffu, lin_max, 2));
       lin_max = __shfl_sync(0xffffffffu, lin_max, 4);
     }
-    if (K == 1 || K == 2) {
-      // one or two further replicas: a lane per candidate (sub_small_candidate), max on (score, count vector)
+    if (K >= 1 && K <= kSubFlatMaxK) {
+      // a few further replicas: one pass over the class in the node's table of all count vectors (sub_flat_key)
       __syncwarp();  // lin[] is read by every lane
-      int bs = -1;
-      unsigned long long bl = 0;
-      for (int c = lane; c < sub_small_candidates(K); c += 32) {
-        int sc;
-        unsigned long long lex;
-        if (!sub_small_candidate(c, K, fpack_p, fpack_s, r0, lin, w, &sc, &lex)) continue;
-        if (sc > bs || (sc == bs && lex > bl)) {
-          bs = sc;
-          bl = lex;
-        }
+      unsigned long long best = 0;
+      for (int e = sub_flat_start(K) + lane; e < sub_flat_start(K + 1); e += 32) {
+        const unsigned long long k = sub_flat_key(g_flat, e, fpack_p, fpack_s, r0, lin, d.n_req > 0);
+        best = k > best ? k : best;
       }
-      const int top = (int)__reduce_max_sync(0xffffffffu, (unsigned)(bs + 1)) - 1;
-      const unsigned long long lex = warp_max_u64(bs == top ? bl : 0ull);
-      if (top < 0) {
+      best = warp_max_u64(best);
+      if (best == 0) {
         sub_batch_write_empty(out, i, GPA_OK, lane);
       } else if (lane == 0) {
+        const int e = (int)~(uint32_t)best;
         uint2 *dst = reinterpret_cast<uint2 *>(out + i);
-        dst[0] = make_uint2(__byte_perm((uint32_t)(lex >> 32), 0u, 0x0123), __byte_perm((uint32_t)lex, 0u, 0x0123));
+        dst[0] = make_uint2(__byte_perm(g_flat[2 * e], 0u, 0x0123), __byte_perm(g_flat[2 * e + 1], 0u, 0x0123));
         dst[1] = make_uint2(0u, 0u);
-        dst[2] = make_uint2((uint32_t)top, (uint32_t)(uint16_t)d.size | ((uint32_t)(uint16_t)GPA_OK << 16));
+        dst[2] = make_uint2((uint32_t)(best >> 32) - 1u, (uint32_t)(uint16_t)d.size | ((uint32_t)(uint16_t)GPA_OK << 16));
       }
       __syncwarp();  // lin[] is rewritten for the warp's next request
       continue;

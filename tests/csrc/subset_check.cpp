@@ -143,20 +143,30 @@ static void batch_pair_search(const uint16_t *w, const uint8_t *free_in, const u
       if (h != g) lin[g] += (uint32_t)must[h] * w[(g < h ? g : h) * kSubGroups + (g < h ? h : g)];
     for (int h = g + 1; h < 8; h++) r0 += (uint32_t)must[g] * must[h] * w[g * kSubGroups + h];
   }
-  if (K == 1 || K == 2) {  // the kernel's short cut: a lane per candidate, max on (score, count vector)
-    int bs = -1;
-    unsigned long long bl = 0;
-    for (int c = 0; c < sub_small_candidates(K); c++) {
-      int sc;
-      unsigned long long lex;
-      if (!sub_small_candidate(c, K, fpack[0], fpack[1], r0, lin, w, &sc, &lex)) continue;
-      if (sc > bs || (sc == bs && lex > bl)) {
-        bs = sc;
-        bl = lex;
-      }
+  if (K >= 1 && K <= kSubFlatMaxK) {  // the kernel's short cut: one pass over the class in the node's table of all vectors
+    static std::vector<uint32_t> flat;
+    static std::vector<uint16_t> flat_w;
+    if (flat.empty() || !std::equal(flat_w.begin(), flat_w.end(), w)) {
+      flat.assign(kSubFlatBytes / 4, 0u);
+      flat_w.assign(w, w + kSubGroups * kSubGroups);
+      sub_flat_fill(w, flat.data());
     }
-    for (int g = 0; g < 16; g++) take[g] = g < 8 ? (uint8_t)(bl >> (8 * (7 - g))) : 0;
-    *score = bs;
+    unsigned long long best = 0;
+    for (int lane = 0; lane < 32; lane++)
+      for (int e = sub_flat_start(K) + lane; e < sub_flat_start(K + 1); e += 32) {
+        const unsigned long long k = sub_flat_key(flat.data(), e, fpack[0], fpack[1], r0, lin, n_req > 0);
+        best = k > best ? k : best;
+      }
+    for (int g = 0; g < 16; g++) take[g] = 0;
+    *score = -1;
+    if (best) {
+      const int e = (int)~(uint32_t)best;
+      for (int g = 0; g < 4; g++) {
+        take[g] = (uint8_t)(flat[2 * e] >> (8 * (3 - g)));
+        take[4 + g] = (uint8_t)(flat[2 * e + 1] >> (8 * (3 - g)));
+      }
+      *score = (int)(best >> 32) - 1;
+    }
     return;
   }
   uint16_t plist[kSubHalfEntries], slist[kSubHalfEntries], poff[kSubHalfMaxK + 2], soff[kSubHalfMaxK + 2];
