@@ -427,17 +427,39 @@ inline void sub_flat_fill(const uint16_t *w, uint32_t *tab) {
   for (int i = 3 * kSubFlatEntries; i < kSubFlatBytes / 4; i++) tab[i] = 0;
 }
 
-// Entry e for a request: 0 if the free counts do not allow it, else (score + 1) << 32 | ~e (the maximum is the first best)
+// Entry e for a request: 0 if the free counts do not allow it, else (score + 1) << 32 | ~e (the maximum is the first best).
+// kPlain: every GPU has K replicas free and none is must-include - the table score is the answer's score.
+template <bool kPlain>
 GPA_HD unsigned long long sub_flat_key(const uint32_t *tab, int e, uint32_t fpack_p, uint32_t fpack_s, uint32_t r0, const uint32_t *lin,
                                        bool has_req) {
-  const SubWord2 x = *reinterpret_cast<const SubWord2 *>(tab + 2 * e);
-  if (!sub_half_fits(x.x, fpack_p) || !sub_half_fits(x.y, fpack_s)) return 0ull;
   uint32_t sc = tab[kSubFlatScoreOff / 4 + e];
-  if (has_req) {
-    sc += r0 + (x.x >> 24) * lin[0] + ((x.x >> 16) & 0xFFu) * lin[1] + ((x.x >> 8) & 0xFFu) * lin[2] + (x.x & 0xFFu) * lin[3] +
-          (x.y >> 24) * lin[4] + ((x.y >> 16) & 0xFFu) * lin[5] + ((x.y >> 8) & 0xFFu) * lin[6] + (x.y & 0xFFu) * lin[7];
+  if (!kPlain) {
+    const SubWord2 x = *reinterpret_cast<const SubWord2 *>(tab + 2 * e);
+    if (!sub_half_fits(x.x, fpack_p) || !sub_half_fits(x.y, fpack_s)) return 0ull;
+    if (has_req) {
+      sc += r0 + (x.x >> 24) * lin[0] + ((x.x >> 16) & 0xFFu) * lin[1] + ((x.x >> 8) & 0xFFu) * lin[2] + (x.x & 0xFFu) * lin[3] +
+            (x.y >> 24) * lin[4] + ((x.y >> 16) & 0xFFu) * lin[5] + ((x.y >> 8) & 0xFFu) * lin[6] + (x.y & 0xFFu) * lin[7];
+    }
   }
   return ((unsigned long long)(sc + 1u) << 32) | (uint32_t)~(uint32_t)e;
+}
+// the best key of lane `lane` over class K
+GPA_HD unsigned long long sub_flat_lane(const uint32_t *tab, int K, uint32_t fpack_p, uint32_t fpack_s, uint32_t r0, const uint32_t *lin,
+                                        bool has_req, int lane) {
+  const uint32_t all_k = (uint32_t)K * 0x01010101u;
+  unsigned long long best = 0;
+  if (!has_req && fpack_p == all_k && fpack_s == all_k) {
+    for (int e = sub_flat_start(K) + lane; e < sub_flat_start(K + 1); e += 32) {
+      const unsigned long long k = sub_flat_key<true>(tab, e, fpack_p, fpack_s, r0, lin, false);
+      best = k > best ? k : best;
+    }
+  } else {
+    for (int e = sub_flat_start(K) + lane; e < sub_flat_start(K + 1); e += 32) {
+      const unsigned long long k = sub_flat_key<false>(tab, e, fpack_p, fpack_s, r0, lin, has_req);
+      best = k > best ? k : best;
+    }
+  }
+  return best;
 }
 
 // A lane's running best: (score + 1) << 32 | prefix word, and which composition that prefix is.  key 0 = nothing yet.

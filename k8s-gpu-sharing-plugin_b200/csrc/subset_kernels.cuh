@@ -376,12 +376,7 @@ __global__ void __launch_bounds__(kSubThreads, 5) subset_batch_pair_kernel(const
     if (K >= 1 && K <= kSubFlatMaxK) {
       // a few further replicas: one pass over the class in the node's table of all count vectors (sub_flat_key)
       __syncwarp();  // lin[] is read by every lane
-      unsigned long long best = 0;
-      for (int e = sub_flat_start(K) + lane; e < sub_flat_start(K + 1); e += 32) {
-        const unsigned long long k = sub_flat_key(g_flat, e, fpack_p, fpack_s, r0, lin, d.n_req > 0);
-        best = k > best ? k : best;
-      }
-      best = warp_max_u64(best);
+      const unsigned long long best = warp_max_u64(sub_flat_lane(g_flat, K, fpack_p, fpack_s, r0, lin, d.n_req > 0, lane));
       if (best == 0) {
         sub_batch_write_empty(out, i, GPA_OK, lane);
       } else if (lane == 0) {

@@ -152,11 +152,10 @@ static void batch_pair_search(const uint16_t *w, const uint8_t *free_in, const u
       sub_flat_fill(w, flat.data());
     }
     unsigned long long best = 0;
-    for (int lane = 0; lane < 32; lane++)
-      for (int e = sub_flat_start(K) + lane; e < sub_flat_start(K + 1); e += 32) {
-        const unsigned long long k = sub_flat_key(flat.data(), e, fpack[0], fpack[1], r0, lin, n_req > 0);
-        best = k > best ? k : best;
-      }
+    for (int lane = 0; lane < 32; lane++) {
+      const unsigned long long k = sub_flat_lane(flat.data(), K, fpack[0], fpack[1], r0, lin, n_req > 0, lane);
+      best = k > best ? k : best;
+    }
     for (int g = 0; g < 16; g++) take[g] = 0;
     *score = -1;
     if (best) {
