@@ -447,14 +447,15 @@ GPA_HD unsigned long long sub_flat_key(const uint32_t *tab, int e, uint32_t fpac
 GPA_HD unsigned long long sub_flat_lane(const uint32_t *tab, int K, uint32_t fpack_p, uint32_t fpack_s, uint32_t r0, const uint32_t *lin,
                                         bool has_req, int lane) {
   const uint32_t all_k = (uint32_t)K * 0x01010101u;
+  const int e_end = sub_flat_start(K + 1);
   unsigned long long best = 0;
   if (!has_req && fpack_p == all_k && fpack_s == all_k) {
-    for (int e = sub_flat_start(K) + lane; e < sub_flat_start(K + 1); e += 32) {
+    for (int e = sub_flat_start(K) + lane; e < e_end; e += 32) {
       const unsigned long long k = sub_flat_key<true>(tab, e, fpack_p, fpack_s, r0, lin, false);
       best = k > best ? k : best;
     }
   } else {
-    for (int e = sub_flat_start(K) + lane; e < sub_flat_start(K + 1); e += 32) {
+    for (int e = sub_flat_start(K) + lane; e < e_end; e += 32) {
       const unsigned long long k = sub_flat_key<false>(tab, e, fpack_p, fpack_s, r0, lin, has_req);
       best = k > best ? k : best;
     }
