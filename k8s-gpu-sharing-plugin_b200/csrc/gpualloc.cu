@@ -323,6 +323,13 @@ int ensure_partition_table(gpa_ctx *ctx, int nt) {
 // for nodes of up to kFastMaxTopo devices whose link counts are symmetric.
 // Label-space tables of the replica-set batch kernels (subset_kernels.cuh): the weights every launch passes by value and,
 // on nodes of up to 8 GPUs, the half-vector table of the two-halves walk.  Called with the device drained.
+// device blob of the two-halves kernel: half-vector table | table of all small count vectors | the empty node's answers for
+// K = 0..15 further replicas (gpa_subset_result each) | the 16 requests they are computed from
+constexpr int kSubFreeNodeOff = kSubPairBlobBytes + kSubFlatBytes;
+constexpr int kSubFreeNodeReqOff = kSubFreeNodeOff + 16 * (int)sizeof(gpa_subset_result);
+constexpr int kSubBlobTotal = kSubFreeNodeReqOff + 16 * (int)sizeof(gpa_subset_request);
+static_assert(kSubFreeNodeOff % 16 == 0 && kSubFreeNodeReqOff % 16 == 0, "records are read with 8- and 16-byte accesses");
+
 int rebuild_subset_tables(gpa_ctx *ctx) {
   const Topology &T = ctx->topo;
   SubsetBatchTopo &bt = ctx->sub_bt;
@@ -342,12 +349,28 @@ int rebuild_subset_tables(gpa_ctx *ctx) {
   std::vector<uint32_t> blob((kSubPairBlobBytes + kSubFlatBytes) / 4);
   sub_pair_fill(bt.w, blob.data());
   sub_flat_fill(bt.w, blob.data() + kSubPairBlobBytes / 4);
-  if (!ctx->d_sub_pair) CUDA_TRY(ctx, cudaMalloc(&ctx->d_sub_pair, kSubPairBlobBytes + kSubFlatBytes));
+  if (!ctx->d_sub_pair) CUDA_TRY(ctx, cudaMalloc(&ctx->d_sub_pair, kSubBlobTotal));
   if (!ctx->d_sub_next) {
     CUDA_TRY(ctx, cudaMalloc(&ctx->d_sub_next, gpa_ctx::kSubSlots * sizeof(unsigned int)));
     for (auto &ev : ctx->sub_ev) CUDA_TRY(ctx, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   }
   CUDA_TRY(ctx, cudaMemcpy(ctx->d_sub_pair, blob.data(), kSubPairBlobBytes + kSubFlatBytes, cudaMemcpyHostToDevice));
+  // the empty node's answers: "K replicas, every GPU has K free", K = 0..15, by the kernel itself (no short cut: nullptr)
+  gpa_subset_request free_node[16];
+  memset(free_node, 0, sizeof free_node);
+  for (int K = 0; K < 16; K++) {
+    for (int g = 0; g < T.n; g++) free_node[K].free_replicas[g] = (uint8_t)K;
+    free_node[K].size = K;
+  }
+  unsigned char *base = reinterpret_cast<unsigned char *>(ctx->d_sub_pair);
+  CUDA_TRY(ctx, cudaMemcpy(base + kSubFreeNodeReqOff, free_node, sizeof free_node, cudaMemcpyHostToDevice));
+  subset_batch_pair_kernel<<<2, kSubThreads, 0, ctx->stream>>>(reinterpret_cast<const gpa_subset_request *>(base + kSubFreeNodeReqOff), 16, bt,
+                                                              reinterpret_cast<const uint4 *>(ctx->d_sub_pair),
+                                                              ctx->d_sub_pair + kSubPairBlobBytes / 4, nullptr, nullptr,
+                                                              reinterpret_cast<gpa_subset_result *>(base + kSubFreeNodeOff));
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   return GPA_OK;
 }
 

@@ -291,6 +291,7 @@ __device__ __noinline__ void sub_batch_dfs_call(const SubBatchDecoded &d, uint8_
 __global__ void __launch_bounds__(kSubThreads, 5) subset_batch_pair_kernel(const gpa_subset_request *__restrict__ reqs, int count,
                                                                            const SubsetBatchTopo t, const uint4 *__restrict__ g_blob,
                                                                            const uint32_t *__restrict__ g_flat,
+                                                                           const gpa_subset_result *__restrict__ g_free_node,
                                                                            unsigned int *__restrict__ g_next,
                                                                            gpa_subset_result *__restrict__ out) {
   __shared__ __align__(16) uint32_t blob[kSubPairBlobBytes / 4];
@@ -336,6 +337,13 @@ __global__ void __launch_bounds__(kSubThreads, 5) subset_batch_pair_kernel(const
     const SubBatchDecoded d = sub_batch_decode(reqs, i, t.nt, asym_row, s_binom, lane);
     if (!d.search) {
       sub_batch_write_empty(out, i, d.status, lane);
+      continue;
+    }
+    // A request that no free count binds - every GPU of the node has K replicas free, none is must-include - has the
+    // answer of "K replicas on the empty node", which this kernel worked out itself when the topology was installed
+    // (g_free_node[K], rebuild_subset_tables(); nullptr while it does).  On a lightly loaded node that is most requests.
+    if (g_free_node != nullptr && d.n_req == 0 && __all_sync(0xffffffffu, lane >= t.nt || d.my_f >= d.K)) {
+      if (lane < 3) reinterpret_cast<uint2 *>(out + i)[lane] = __ldg(reinterpret_cast<const uint2 *>(g_free_node + d.K) + lane);
       continue;
     }
     if (d.K > kSubHalfMaxK) {

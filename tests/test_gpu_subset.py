@@ -254,6 +254,22 @@ def test_batch_two_halves_walk_equals_depth_first_walk_and_single_call(ctx):
                     assert rc == 0 and len(pos) == int(a["n_out"][i])
                     if pos:
                         assert a["take"][i].tolist() == syn.positions_to_take(phys, set(req), pos), (n_gpus, reps, i)
+        # requests no free count binds (every GPU has at least K free, no must-include): the kernel hands out the answer it
+        # worked out for the empty node when the topology was installed - the same as searching
+        for n_gpus, topo in ((8, syn.topo_random(8, 33)), (6, syn.topo_random(6, 34))):
+            for c in (ctx, dfs):
+                c.set_topology_links(topo)
+                c.set_device_order(list(range(n_gpus))[::-1])
+            reqs = np.zeros(45, dtype=syn.SUBSET_REQ_DTYPE)
+            for i in range(45):
+                K = i % 15 + 1
+                reqs["size"][i] = K
+                reqs["free"][i, :n_gpus] = K + i // 15 * 7       # exactly K, K + 7, K + 14 free on every GPU
+            reqs["free"][44, 0] = 3                              # ... but not here: GPU 0 has 3 of the 15 wanted
+            a, b = ctx.subset_batch(reqs), dfs.subset_batch(reqs)
+            for field in ("status", "n_out", "score", "take"):
+                assert (a[field] == b[field]).all(), (n_gpus, field)
+            assert (a["status"] == 0).all() and (a["n_out"] == reqs["size"]).all()
         # weights at the score table's limit (546 units a pair) and 124 must-include replicas on one GPU: one more replica
         # elsewhere adds more than 65 535 units against them, which takes the kernel's second pair of dot products
         rng = np.random.default_rng(5)
