@@ -115,6 +115,7 @@ struct gpa_ctx {
   bool sub_dfs_only = false;       // GPA_SUBSET_WALK=dfs: the depth-first batch kernel on every node (A/B measurements)
   int part_table_nt = 0;             // node size the table was built for, 0 = none
   bool table_attr_set[3] = {false, false, false};
+  bool launch_on_host_memory = false;  // set around the launch of a zero-copy host call
   int zero_copy = -1;  // GPA_ZERO_COPY: 1 / 0 = kernels always / never work on the caller's pinned buffers; -1 = per format
   uint16_t *d_ans = nullptr;         // answer table of the installed topology (ans_table.cuh), built by a kernel
   uint8_t *d_ans8 = nullptr;         // its chosen masks alone (what the batch kernels stage into shared memory)
@@ -237,7 +238,7 @@ int launch_table(gpa_ctx *ctx, const void *d_reqs, int count, int max_avail, int
     }
     // persistent: every CTA stages the table once
     long long want = ((long long)count + 2 * kMaskThreads - 1) / (2 * kMaskThreads);
-    long long cap = (long long)ctx->sm_count * 2;
+    long long cap = (long long)ctx->sm_count * (ctx->launch_on_host_memory ? 1 : 2);  // as in launch_masks8()
     int grid = (int)(want < cap ? want : cap);
     besteffort_masks_table_kernel<<<grid, kMaskThreads, masks_smem_bytes(ctx->fast.ans_entries), stream>>>(
         static_cast<const uint2 *>(d_reqs), count, ctx->fast, static_cast<uint32_t *>(d_out));
@@ -285,7 +286,8 @@ int launch_masks8(gpa_ctx *ctx, const void *d_reqs, int count, void *d_out, cuda
     ctx->table_attr_set[2] = true;
   }
   long long want = ((long long)count + 4 * kMaskThreads - 1) / (4 * kMaskThreads);
-  long long cap = (long long)ctx->sm_count * 2;
+  // records in the caller's pinned memory: one CTA per SM keeps PCIe as busy as two (tools/pcie_sm_read: 48.0 vs 47.2 GB/s)
+  long long cap = (long long)ctx->sm_count * (ctx->launch_on_host_memory ? 1 : 2);
   int grid = (int)(want < cap ? want : cap);
   besteffort_masks8_table_kernel<<<grid, kMaskThreads, masks_smem_bytes(ctx->fast.ans_entries), stream>>>(
       static_cast<const uint32_t *>(d_reqs), count, ctx->fast, static_cast<uint16_t *>(d_out));
@@ -528,7 +530,9 @@ int host_batch(gpa_ctx *ctx, const void *reqs, void *out, int count, size_t in_s
   if (pinned && (ctx->zero_copy == 1 || (ctx->zero_copy < 0 && zero_copy_ok))) {
     void *d_in = nullptr, *d_out = nullptr;
     if (cudaHostGetDevicePointer(&d_in, const_cast<void *>(reqs), 0) == cudaSuccess && cudaHostGetDevicePointer(&d_out, out, 0) == cudaSuccess) {
+      ctx->launch_on_host_memory = true;
       int rc = launch(d_in, count, d_out, ctx->pipe[0]);
+      ctx->launch_on_host_memory = false;
       cudaError_t e = cudaStreamSynchronize(ctx->pipe[0]);
       if (e != cudaSuccess && rc == GPA_OK) {
         ctx->last_error = std::string("cudaStreamSynchronize: ") + cudaGetErrorString(e);
