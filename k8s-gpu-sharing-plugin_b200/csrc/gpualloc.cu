@@ -346,11 +346,13 @@ int rebuild_subset_tables(gpa_ctx *ctx) {
       if (a != b && T.asym[da * T.n + db]) bt.asym_row[a] |= (uint16_t)(1u << b);
     }
   }
-  if (T.n > 8) return GPA_OK;
-  // the half-vector table of the two-halves walk, then the table of all count vectors of up to 4 further replicas
-  std::vector<uint32_t> blob((kSubPairBlobBytes + kSubFlatBytes) / 4);
-  sub_pair_fill(bt.w, blob.data());
-  sub_flat_fill(bt.w, blob.data() + kSubPairBlobBytes / 4);
+  // nodes of up to 8 GPUs: the half-vector table of the two-halves walk, then the table of all count vectors of up to 4
+  // further replicas (zeros on larger nodes, whose kernel does not read them)
+  std::vector<uint32_t> blob((kSubPairBlobBytes + kSubFlatBytes) / 4, 0u);
+  if (T.n <= 8) {
+    sub_pair_fill(bt.w, blob.data());
+    sub_flat_fill(bt.w, blob.data() + kSubPairBlobBytes / 4);
+  }
   if (!ctx->d_sub_pair) CUDA_TRY(ctx, cudaMalloc(&ctx->d_sub_pair, kSubBlobTotal));
   if (!ctx->d_sub_next) {
     CUDA_TRY(ctx, cudaMalloc(&ctx->d_sub_next, gpa_ctx::kSubSlots * sizeof(unsigned int)));
@@ -366,10 +368,13 @@ int rebuild_subset_tables(gpa_ctx *ctx) {
   }
   unsigned char *base = reinterpret_cast<unsigned char *>(ctx->d_sub_pair);
   CUDA_TRY(ctx, cudaMemcpy(base + kSubFreeNodeReqOff, free_node, sizeof free_node, cudaMemcpyHostToDevice));
-  subset_batch_pair_kernel<<<2, kSubThreads, 0, ctx->stream>>>(reinterpret_cast<const gpa_subset_request *>(base + kSubFreeNodeReqOff), 16, bt,
-                                                              reinterpret_cast<const uint4 *>(ctx->d_sub_pair),
-                                                              ctx->d_sub_pair + kSubPairBlobBytes / 4, nullptr, nullptr,
-                                                              reinterpret_cast<gpa_subset_result *>(base + kSubFreeNodeOff));
+  const gpa_subset_request *d_free_reqs = reinterpret_cast<const gpa_subset_request *>(base + kSubFreeNodeReqOff);
+  gpa_subset_result *d_free_node = reinterpret_cast<gpa_subset_result *>(base + kSubFreeNodeOff);
+  if (T.n <= 8)
+    subset_batch_pair_kernel<<<2, kSubThreads, 0, ctx->stream>>>(d_free_reqs, 16, bt, reinterpret_cast<const uint4 *>(ctx->d_sub_pair),
+                                                                ctx->d_sub_pair + kSubPairBlobBytes / 4, nullptr, nullptr, d_free_node);
+  else
+    subset_batch_kernel<16><<<2, kSubThreads, 0, ctx->stream>>>(d_free_reqs, 16, bt, nullptr, nullptr, d_free_node);
   ctx->launches++;
   CUDA_TRY(ctx, cudaGetLastError());
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));

@@ -124,6 +124,7 @@ __global__ void __launch_bounds__(kSubThreads) subset_enum_kernel(const SubsetEn
 constexpr int kSubBatchMaxExtra = GPA_SUBSET_BATCH_MAX_EXTRA;  // replicas to choose beyond the required ones
 constexpr int kSubBatchWarps = kSubThreads / 32;
 constexpr int kSubPrefix = 4;
+constexpr int kSubDraw = 4;  // requests a warp takes from the launch's counter at a time
 static_assert(kSubBatchMaxExtra <= 15, "a count beyond the required ones is packed in 4 bits");
 
 struct SubsetBatchTopo {
@@ -252,7 +253,10 @@ __device__ __forceinline__ void sub_batch_dfs(const SubBatchDecoded &d, uint8_t 
 
 template <int G>
 __global__ void __launch_bounds__(kSubThreads, G <= 8 ? 3 : 1) subset_batch_kernel(const gpa_subset_request *__restrict__ reqs, int count,
-                                                                    const SubsetBatchTopo t, gpa_subset_result *__restrict__ out) {
+                                                                    const SubsetBatchTopo t,
+                                                                    const gpa_subset_result *__restrict__ g_free_node,
+                                                                    unsigned int *__restrict__ g_next,
+                                                                    gpa_subset_result *__restrict__ out) {
   __shared__ uint16_t w[kSubGroups * kSubGroups];
   __shared__ uint8_t fr_all[kSubBatchWarps][2 * kSubGroups];
   __shared__ uint16_t cap_all[kSubBatchWarps][kSubGroups + 1];
@@ -264,12 +268,25 @@ __global__ void __launch_bounds__(kSubThreads, G <= 8 ? 3 : 1) subset_batch_kern
   for (int i = tid; i < kSubGroups * kSubGroups; i += kSubThreads) w[i] = t.w[i];
   if (tid < kSubGroups) asym_row[tid] = t.asym_row[tid];
   __syncthreads();
-  for (long long i = (long long)blockIdx.x * kSubBatchWarps + warp; i < count; i += (long long)gridDim.x * kSubBatchWarps) {
-    const SubBatchDecoded d = sub_batch_decode(reqs, i, t.nt, asym_row, s_binom, lane);
-    if (d.search)
-      sub_batch_dfs<G>(d, fr_all[warp], fr_all[warp] + kSubGroups, cap_all[warp], exact_all[warp], w, out, i, lane);
-    else
-      sub_batch_write_empty(out, i, d.status, lane);
+  // requests drawn from a counter and the empty node's answers: as in subset_batch_pair_kernel below (both optional)
+  for (unsigned int turn = 0;; turn++) {
+    unsigned int first = ((unsigned int)(blockIdx.x * kSubBatchWarps + warp) + turn * (unsigned int)(gridDim.x * kSubBatchWarps)) * kSubDraw;
+    if (g_next) {
+      if (lane == 0) first = atomicAdd(g_next, (unsigned int)kSubDraw);
+      first = __shfl_sync(0xffffffffu, first, 0);
+    }
+    if (first >= (unsigned int)count) break;
+    const unsigned int last = first + kSubDraw < (unsigned int)count ? first + kSubDraw : (unsigned int)count;
+    for (long long i = first; i < last; i++) {
+      const SubBatchDecoded d = sub_batch_decode(reqs, i, t.nt, asym_row, s_binom, lane);
+      if (!d.search) {
+        sub_batch_write_empty(out, i, d.status, lane);
+      } else if (g_free_node != nullptr && d.n_req == 0 && __all_sync(0xffffffffu, lane >= t.nt || d.my_f >= d.K)) {
+        if (lane < 3) reinterpret_cast<uint2 *>(out + i)[lane] = __ldg(reinterpret_cast<const uint2 *>(g_free_node + d.K) + lane);
+      } else {
+        sub_batch_dfs<G>(d, fr_all[warp], fr_all[warp] + kSubGroups, cap_all[warp], exact_all[warp], w, out, i, lane);
+      }
+    }
   }
 }
 
@@ -280,7 +297,6 @@ __global__ void __launch_bounds__(kSubThreads, G <= 8 ? 3 : 1) subset_batch_kern
 // then visits (prefix, suffix) pairs at one shared-memory load and five integer operations each.  Requests that choose
 // more than kSubHalfMaxK further replicas take the depth-first walk above.
 constexpr int kSubListLen = (kSubHalfEntries + 1 + 7) & ~7;
-constexpr int kSubDraw = 4;  // requests a warp takes from the counter at a time
 
 template <int G>
 __device__ __noinline__ void sub_batch_dfs_call(const SubBatchDecoded &d, uint8_t *f, uint8_t *r, uint16_t *cap, uint32_t *exact,

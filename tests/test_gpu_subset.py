@@ -256,7 +256,7 @@ def test_batch_two_halves_walk_equals_depth_first_walk_and_single_call(ctx):
                         assert a["take"][i].tolist() == syn.positions_to_take(phys, set(req), pos), (n_gpus, reps, i)
         # requests no free count binds (every GPU has at least K free, no must-include): the kernel hands out the answer it
         # worked out for the empty node when the topology was installed - the same as searching
-        for n_gpus, topo in ((8, syn.topo_random(8, 33)), (6, syn.topo_random(6, 34))):
+        for n_gpus, topo in ((8, syn.topo_random(8, 33)), (6, syn.topo_random(6, 34)), (12, syn.topo_random(12, 35))):
             for c in (ctx, dfs):
                 c.set_topology_links(topo)
                 c.set_device_order(list(range(n_gpus))[::-1])
@@ -269,7 +269,8 @@ def test_batch_two_halves_walk_equals_depth_first_walk_and_single_call(ctx):
             a, b = ctx.subset_batch(reqs), dfs.subset_batch(reqs)
             for field in ("status", "n_out", "score", "take"):
                 assert (a[field] == b[field]).all(), (n_gpus, field)
-            assert (a["status"] == 0).all() and (a["n_out"] == reqs["size"]).all()
+            ok = a["status"] == 0                                # 12 GPUs: the larger requests are beyond the batch form
+            assert ok.sum() >= 20 and (a["n_out"][ok] == reqs["size"][ok]).all() and (ok.all() or n_gpus > 8)
         # weights at the score table's limit (546 units a pair) and 124 must-include replicas on one GPU: one more replica
         # elsewhere adds more than 65 535 units against them, which takes the kernel's second pair of dot products
         rng = np.random.default_rng(5)
